@@ -1,0 +1,522 @@
+"""CPU oracle for the CMBPO model-rollout hot path.  TEST INFRASTRUCTURE ONLY.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import this module.  The product (``constrainedmbpo_b200``)
+never does: it fails loudly when its CUDA extension is missing.
+
+PARITY UNPINNED: the reference (anyboby/ConstrainedMBPO) ships no tests, golden vectors or
+fixtures for this path, and its model code needs TensorFlow 1.14, which cannot be imported
+here.  What *is* pinned: the static termination / cost functions (``mbpo/static/*.py`` are
+pure NumPy; ``tests/golden/static_fns.npz`` was produced by importing those files, see
+``tests/golden/make_golden.py``) and ``average_dkl`` (same script executes the reference's own
+source lines ``mbpo/models/utils.py:7-57``).  Everything else below is a restatement reviewed
+line by line against the cited reference code; all citations are relative to /root/reference.
+
+Arithmetic runs in the dtype of the parameters handed in: float64 as the arbiter, float32 to
+mirror the reference's own precision (TF variables and placeholders are tf.float32,
+``mbpo/models/bnn.py:210-213,345-347``).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+EPS_KL = 1e-10  # mbpo/models/utils.py:7
+
+
+# --------------------------------------------------------------------------------------
+# activations: mbpo/models/fc.py:14-21
+# --------------------------------------------------------------------------------------
+def _sigmoid(x):
+    return 1.0 / (1.0 + np.exp(-x))
+
+
+def _softmax(x):
+    z = x - np.max(x, axis=-1, keepdims=True)
+    e = np.exp(z)
+    return e / np.sum(e, axis=-1, keepdims=True)
+
+
+ACTIVATIONS = {
+    None: lambda x: x,
+    "ReLU": lambda x: np.maximum(x, 0),
+    "tanh": np.tanh,
+    "sigmoid": _sigmoid,
+    "softmax": _softmax,
+    "swish": lambda x: x * _sigmoid(x),  # fc.py:20
+}
+
+
+# --------------------------------------------------------------------------------------
+# ensemble parameters
+# --------------------------------------------------------------------------------------
+class EnsembleParams:
+    """State the forward pass reads: per-layer weights ``[E,in,out]`` and biases
+    ``[E,1,out]`` (fc.py:154-185), layer activations, the two scalers' ``mu``/``var``
+    ``[1,dim]`` (utils.py:98-115; ``var`` is the TF variable *named* ``_std``), ``sc_factor``,
+    whether the head is doubled into mean|logvar (bnn.py:111-112, :190-191), the output
+    activation applied to the mean (bnn.py:194-196, :880-881) and the elite list
+    (bnn.py:98-102, :428-431)."""
+
+    def __init__(self, weights, biases, activations, mu_in=None, var_in=None, mu_out=None,
+                 var_out=None, sc_factor=1.0, probabilistic=True, end_act=None, elites=None):
+        self.weights = list(weights)
+        self.biases = list(biases)
+        self.activations = list(activations)
+        self.mu_in, self.var_in = mu_in, var_in
+        self.mu_out, self.var_out = mu_out, var_out
+        self.sc_factor = sc_factor
+        self.probabilistic = probabilistic
+        self.end_act = end_act
+        self.num_nets = self.weights[0].shape[0]
+        self.elites = list(range(self.num_nets)) if elites is None else list(elites)
+
+    @property
+    def dtype(self):
+        return self.weights[0].dtype
+
+    @property
+    def in_dim(self):
+        return self.weights[0].shape[1]
+
+    @property
+    def out_dim(self):
+        w = self.weights[-1].shape[2]
+        return w // 2 if self.probabilistic else w
+
+    def astype(self, dt):
+        c = lambda a: None if a is None else np.asarray(a, dtype=dt)
+        return EnsembleParams([c(w) for w in self.weights], [c(b) for b in self.biases],
+                              self.activations, c(self.mu_in), c(self.var_in), c(self.mu_out),
+                              c(self.var_out), self.sc_factor, self.probabilistic, self.end_act,
+                              self.elites)
+
+
+def truncated_normal(rng, shape, std):
+    """tf.truncated_normal_initializer: N(0, std) re-drawn until |x| <= 2 std (fc.py:157)."""
+    x = rng.standard_normal(shape)
+    bad = np.abs(x) > 2.0
+    while bad.any():
+        x[bad] = rng.standard_normal(int(bad.sum()))
+        bad = np.abs(x) > 2.0
+    return x * std
+
+
+def init_ensemble(rng, in_dim, out_dim, hidden_dims, num_networks, probabilistic=True,
+                  activation="swish", output_activation=None, use_scaler_in=False,
+                  use_scaler_out=False, sc_factor=1.0, logit_bias_std=1.0, elites=None,
+                  dtype=np.float32):
+    """Random ensemble of the shape ``construct_model`` builds (constructor.py:41-67):
+    weights ~ TruncNormal(0, 1/(2 sqrt(in))) (last layer scaled by ``logit_bias_std``,
+    bnn.py:216-219), zero biases (fc.py:180-184), identity scalers (utils.py:108-115).
+    Distribution only -- TF's RNG stream is not reproduced."""
+    dims = [in_dim] + list(hidden_dims) + [2 * out_dim if probabilistic else out_dim]
+    acts = [activation] * len(hidden_dims) + [None]  # last activation stripped, bnn.py:194-196
+    W, B = [], []
+    for li in range(len(dims) - 1):
+        std = 1.0 / (2.0 * np.sqrt(dims[li]))
+        if li == len(dims) - 2:
+            std *= logit_bias_std
+        W.append(truncated_normal(rng, (num_networks, dims[li], dims[li + 1]), std).astype(dtype))
+        B.append(np.zeros((num_networks, 1, dims[li + 1]), dtype=dtype))
+    mk = lambda d, v: np.full((1, d), v, dtype=dtype)
+    return EnsembleParams(
+        W, B, acts,
+        mu_in=mk(in_dim, 0.0) if use_scaler_in else None,
+        var_in=mk(in_dim, 1.0) if use_scaler_in else None,
+        mu_out=mk(out_dim, 0.0) if use_scaler_out else None,
+        var_out=mk(out_dim, 1.0) if use_scaler_out else None,
+        sc_factor=sc_factor, probabilistic=probabilistic, end_act=output_activation, elites=elites)
+
+
+# --------------------------------------------------------------------------------------
+# scalers: mbpo/models/utils.py:141-192
+# --------------------------------------------------------------------------------------
+def scaler_divisor(var, sc_factor):
+    """max(sqrt(var) * sc_factor, 1e-2) -- utils.py:161, :172, :192 (quirk Q6)."""
+    return np.maximum(np.sqrt(var) * sc_factor, np.asarray(1e-2, dtype=var.dtype))
+
+
+def scaler_transform(x, mu, var, sc_factor):  # utils.py:141-162
+    return (x - mu) / scaler_divisor(var, sc_factor)
+
+
+def scaler_inverse(x, mu, var, sc_factor):  # utils.py:164-172
+    return scaler_divisor(var, sc_factor) * x + mu
+
+
+def scaler_inverse_logvar(x, var, sc_factor):  # utils.py:184-192
+    return 2.0 * np.log(scaler_divisor(var, sc_factor)) + x
+
+
+# --------------------------------------------------------------------------------------
+# forward pass: fc.py:83-114 driven by bnn.py:852-903
+# --------------------------------------------------------------------------------------
+def fc_forward(x, W, b, activation):
+    """2-D input: einsum('ij,ajk->aik') (fc.py:105-106); 3-D input with leading E:
+    batched matmul (fc.py:107-108); anything else raises (fc.py:110-111)."""
+    if x.ndim == 2:
+        raw = np.einsum("ij,ajk->aik", x, W) + b
+    elif x.ndim == 3 and x.shape[0] == W.shape[0]:
+        raw = np.matmul(x, W) + b
+    else:
+        raise ValueError("Invalid input dimension.")
+    return ACTIVATIONS[activation](raw)
+
+
+def compile_outputs(p: EnsembleParams, inputs, ret_log_var=False, logvar_bound=None):
+    """bnn.py:852-903 with ``scale_output=True`` (the form create_prediction_tensors uses,
+    bnn.py:781-782).  ``logvar_bound`` is None for the live reference (softplus bounding is
+    commented out, bnn.py:888-889) or ``(max_logvar, min_logvar)`` for the optional PETS form
+    (bnn_chua.py:400-401)."""
+    dt = p.dtype
+    cur = np.asarray(inputs, dtype=dt)
+    if p.mu_in is not None:
+        cur = scaler_transform(cur, p.mu_in, p.var_in, p.sc_factor)  # bnn.py:867-868
+    for W, b, act in zip(p.weights, p.biases, p.activations):
+        cur = fc_forward(cur, W, b, act)  # bnn.py:873-876
+    dim_output = p.weights[-1].shape[2]
+    mean = cur[..., : dim_output // 2] if p.probabilistic else cur  # bnn.py:878
+    if p.end_act is not None:
+        mean = ACTIVATIONS[p.end_act](mean)  # bnn.py:880-881
+    if p.mu_out is not None:
+        mean = scaler_inverse(mean, p.mu_out, p.var_out, p.sc_factor)  # bnn.py:883-884
+    if not p.probabilistic:
+        return mean
+    logvar = cur[..., dim_output // 2:]  # bnn.py:891
+    if logvar_bound is not None:  # bnn_chua.py:400-401 (off in the live reference)
+        max_lv, min_lv = (np.asarray(v, dtype=dt) for v in logvar_bound)
+        logvar = max_lv - np.logaddexp(0.0, max_lv - logvar)
+        logvar = min_lv + np.logaddexp(0.0, logvar - min_lv)
+    if p.mu_out is not None:
+        logvar = scaler_inverse_logvar(logvar, p.var_out, p.sc_factor)  # bnn.py:892-893
+    if ret_log_var:
+        return mean, logvar
+    with np.errstate(over="ignore"):
+        return mean, np.exp(logvar)  # bnn.py:898
+
+
+def predict(p: EnsembleParams, inputs, factored=False, inc_var=True, logvar_bound=None):
+    """BNN.predict dispatch, bnn.py:671-776 (shape table: SURVEY appendix B)."""
+    inputs = np.asarray(inputs)
+    if inputs.ndim == 2:
+        if p.probabilistic:
+            mean_fac, var_fac = compile_outputs(p, inputs, logvar_bound=logvar_bound)
+        else:
+            mean_fac = compile_outputs(p, inputs)
+        if factored:
+            if inc_var and p.probabilistic:
+                return mean_fac, var_fac  # :713-717
+            if inc_var:
+                rep = np.repeat(np.var(mean_fac, axis=0)[None], mean_fac.shape[0], axis=0)
+                return mean_fac, rep  # :718-724
+            return mean_fac  # :725-729
+        if inc_var and p.probabilistic:
+            m = np.mean(mean_fac, axis=0)  # bnn.py:350
+            v = np.mean(var_fac, axis=0) + np.mean(np.square(mean_fac - m), axis=0)  # :351-352
+            return m, v
+        if inc_var:
+            return np.mean(mean_fac, axis=0), np.var(mean_fac, axis=0)  # :736-743
+        return np.mean(mean_fac, axis=0)  # :744-748
+    # 3-D inputs, bnn.py:749-776
+    if inc_var and p.probabilistic:
+        return compile_outputs(p, inputs, logvar_bound=logvar_bound)  # :750-754
+    if inc_var:
+        mean3d = compile_outputs(p, inputs)
+        flat = inputs.reshape(-1, inputs.shape[-1])  # :762-763
+        mean2d = compile_outputs(p, flat)
+        var3d = np.var(mean2d, axis=0).reshape(inputs.shape[0], inputs.shape[1], -1)  # :768-770
+        return mean3d, var3d
+    out = compile_outputs(p, inputs)
+    return out[0] if p.probabilistic else out  # :772-776
+
+
+# --------------------------------------------------------------------------------------
+# ensemble KL: mbpo/models/utils.py:15-57
+# --------------------------------------------------------------------------------------
+def gaussian_kl(mu0, log_std0, mu1, log_std1):  # utils.py:15-25
+    var0, var1 = np.exp(2 * log_std0), np.exp(2 * log_std1)
+    pre_sum = 0.5 * (((mu1 - mu0) ** 2 + var0) / (var1 + EPS_KL) - 1) + log_std1 - log_std0
+    return np.clip(pre_sum, 0, 1 / EPS_KL)
+
+
+def average_dkl(mu, std):
+    """utils.py:30-57: sum over ALL ordered pairs (i==j included, quirk Q5), divided by
+    E(E-1)+EPS; ``log std`` clipped to [-100, 1e8]."""
+    with np.errstate(divide="ignore", over="ignore", invalid="ignore"):
+        log_std = np.clip(np.log(std), -100, 1e8)
+        n = len(mu)
+        d_kl = None
+        for i in range(n):
+            for j in range(n):
+                t = gaussian_kl(mu[i], log_std[i], mu[j], log_std[j])
+                d_kl = t if d_kl is None else d_kl + t
+    return d_kl / (n * (n - 1) + EPS_KL)
+
+
+# --------------------------------------------------------------------------------------
+# static termination / cost functions: mbpo/static/*.py (quirks Q1, Q2 reproduced)
+# --------------------------------------------------------------------------------------
+def _antsafe_notdone(next_obs):  # antsafe.py:9-19 -- note the precedence: (a*b*c*z_rot) >= -0.7
+    z = next_obs[..., 0]
+    q = next_obs[..., 1:5]
+    z_rot = 1 - 2 * (q[..., 1] ** 2 + q[..., 2] ** 2)
+    with np.errstate(invalid="ignore", over="ignore"):
+        return np.isfinite(next_obs).all(axis=-1) * (z >= 0.2) * (z <= 1.0) * z_rot >= -0.7
+
+
+def term_antsafe(obs, act, next_obs):  # antsafe.py:6-22
+    return (~_antsafe_notdone(next_obs))[..., None]
+
+
+def cost_antsafe(obs, act, next_obs):  # antsafe.py:25-46
+    y_dist = next_obs[..., -1:]
+    obj_cost = np.any(abs(y_dist) > 3.2, axis=-1)[..., None] * 1.0
+    done_cost = term_antsafe(obs, act, next_obs) * 1.0
+    return np.clip(done_cost + obj_cost, 0, 1)
+
+
+def term_ant(obs, act, next_obs):  # ant.py:6-16
+    x = next_obs[..., 0]
+    not_done = np.isfinite(next_obs).all(axis=-1) * (x >= 0.2) * (x <= 1.0)
+    return (~not_done)[..., None]
+
+
+def term_never(obs, act, next_obs):  # halfcheetah.py:6-11, halfcheetahsafe.py:6-11
+    return np.zeros(obs.shape[:-1], dtype=bool)[..., None]
+
+
+def cost_halfcheetahsafe(obs, act, next_obs):  # halfcheetahsafe.py:14-20
+    xdist = next_obs[..., -1] * 10
+    return np.array(np.abs(xdist) < 2.0, dtype=np.float32)[..., None]
+
+
+def term_humanoid(obs, act, next_obs):  # humanoid.py:8-15, humanoidsafe.py:8-15
+    z = next_obs[..., 0]
+    return ((z < 1.0) + (z > 2.0))[..., None]
+
+
+def cost_humanoidsafe(obs, act, next_obs):  # humanoidsafe.py:18-33
+    done_cost = term_humanoid(obs, act, next_obs) * 1.0
+    y_dist = next_obs[..., -1:]
+    obj_cost = np.any(abs(y_dist) > 3, axis=-1)[..., None] * 1.0
+    return np.clip(done_cost + obj_cost, 0, 1)
+
+
+def term_hopper(obs, act, next_obs):  # hopper.py:6-18, hoppersafe.py:6-18 (Q2: abs of a bool)
+    height = next_obs[..., 0]
+    angle = next_obs[..., 1]
+    not_done = np.isfinite(next_obs).all(axis=-1) \
+        * np.abs(next_obs[..., 1:] < 100).all(axis=-1) \
+        * (height > .7) * (np.abs(angle) < .2)
+    return (~not_done)[..., None]
+
+
+def cost_hoppersafe(obs, act, next_obs):  # hoppersafe.py:21-26
+    xdist = next_obs[..., -1]
+    return np.array(np.abs(xdist) < 1, dtype=np.float32)[..., None]
+
+
+def term_walker2d(obs, act, next_obs):  # walker2d.py:6-17
+    height = next_obs[..., 0]
+    angle = next_obs[..., 1]
+    not_done = (height > 0.8) * (height < 2.0) * (angle > -1.0) * (angle < 1.0)
+    return (~not_done)[..., None]
+
+
+STATIC_FNS = {  # name -> (termination_fn, cost_f or None); mbpo/static/__init__.py:7-24
+    "ant": (term_ant, None),
+    "antsafe": (term_antsafe, cost_antsafe),
+    "halfcheetah": (term_never, None),
+    "halfcheetahsafe": (term_never, cost_halfcheetahsafe),
+    "humanoid": (term_humanoid, None),
+    "humanoidsafe": (term_humanoid, cost_humanoidsafe),
+    "hopper": (term_hopper, None),
+    "hoppersafe": (term_hopper, cost_hoppersafe),
+    "walker2d": (term_walker2d, None),
+}
+
+
+# --------------------------------------------------------------------------------------
+# FakeEnv.step: mbpo/models/fake_env.py:131-222
+# --------------------------------------------------------------------------------------
+def fake_env_step(p: EnsembleParams, env: str, obs, act, elite_idx=None, perm=None,
+                  cares_about_cost=False, cost_params: EnsembleParams | None = None,
+                  logvar_bound=None, noise=None):
+    """One rollout step.  RNG draws are injected (SURVEY §8b "Threading"): ``elite_idx`` is
+    what ``BNN.random_inds(B)`` returned (values from the elite list, bnn.py:437-439), ``perm``
+    the permutation ``forward_shuffle`` drew (fake_env.py:309-316; 3-D inputs only).
+
+    ``noise`` (``[B,D]`` 2-D / ``[E,B,D]`` 3-D standard normals, default None) is the optional
+    north_star mode ``sample = mean + noise*std``; the live reference adds none
+    (fake_env.py:164-170) so None is the parity setting.
+    """
+    dt = p.dtype
+    obs = np.asarray(obs, dtype=dt)
+    act = np.asarray(act, dtype=dt)
+    assert obs.ndim == act.ndim  # fake_env.py:132
+    depth = obs.ndim
+    assert depth in (2, 3), "1-D inputs hit a NameError in the reference (quirk Q3)"
+    inputs = np.concatenate((obs, act), axis=-1)  # :145
+    if depth == 3:
+        inputs = inputs[perm]  # forward_shuffle :147-148
+    means, variances = predict(p, inputs, factored=True, inc_var=True, logvar_bound=logvar_bound)
+    means = np.array(means)
+    if depth == 3:  # "inverse" shuffle re-applies perm (quirk Q4) :152-153, :318-324
+        means, variances = means[perm], variances[perm]
+    means[:, :, :-1] += obs  # :156
+    with np.errstate(invalid="ignore"):
+        stds = np.sqrt(variances)  # :157
+    dkl_path = np.mean(average_dkl(means, stds), axis=-1)  # :158
+    dkl_mean = np.mean(dkl_path)  # :159
+    ep_var = np.var(means, axis=0)  # :160
+    if depth == 3:
+        samples = means  # :164-165
+        if noise is not None:
+            samples = means + np.asarray(noise, dtype=dt) * stds
+    else:
+        B = means.shape[1]
+        samples = means[np.asarray(elite_idx), np.arange(B)]  # :167-170
+        if noise is not None:
+            samples = samples + np.asarray(noise, dtype=dt) * stds[np.asarray(elite_idx), np.arange(B)]
+    next_obs = samples[..., :-1]  # :173
+    rewards = samples[..., -1:]  # :180
+    term_fn, cost_fn = STATIC_FNS[env]
+    terminals = term_fn(obs, act, next_obs)  # :185
+    if cares_about_cost:
+        if cost_fn is not None:
+            costs = cost_fn(obs, act, next_obs)  # :189
+        elif cost_params is not None:
+            inputs_cost = np.concatenate((obs, act, next_obs), axis=-1)  # :194
+            costs = predict(cost_params, inputs_cost, factored=False, inc_var=False)  # :196
+        else:
+            raise ValueError("cares_about_cost without a static cost_f needs a cost model")
+    else:
+        costs = np.zeros_like(rewards)  # :202
+    with np.errstate(over="ignore", invalid="ignore"):
+        info = {
+            "ensemble_dkl_mean": dkl_mean,
+            "ensemble_dkl_path": dkl_path,
+            "ensemble_mean_var": variances.mean(),
+            "ensemble_ep_var": ep_var,
+            "rew": rewards,
+            "rew_mean": rewards.mean(),
+            "cost": costs,
+            "cost_mean": np.asarray(costs).mean(),
+            # not part of the reference's dict; kept for tolerance analysis in the tests
+            "_means": means,
+            "_vars": variances,
+        }
+    return next_obs, rewards, terminals, info
+
+
+# --------------------------------------------------------------------------------------
+# rollout cutoff + model-pool layout:
+#   softlearning/samplers/model_sampler.py:220-263, :265-474
+#   softlearning/replay_pools/modelbuffer.py:45-173
+# --------------------------------------------------------------------------------------
+def rollout(p: EnsembleParams, env: str, start_obs, policy, max_path_length, rollout_mode,
+            dkl_lim=None, max_samples=None, elite_idx_fn=None, cares_about_cost=False,
+            max_steps=None):
+    """Restatement of the loop ``CMBPO._train`` runs (cmbpo.py:335-348): ``sampler.reset`` then
+    ``sampler.sample`` until no path is alive, restricted to what the hot path owns: the
+    step, the DKL-accumulate cutoff (:311-313), the ``max_samples`` early termination
+    (:327-332), the length mask (:437-438, quirk Q8), the terminal mask (:453-456) and the
+    pool writes of ``store_multiple`` (modelbuffer.py:130-173).  Critic values, log-probs and
+    GAE are out of scope and not modelled.
+
+    ``policy(obs) -> act`` and ``elite_idx_fn(step, n_alive) -> int[n_alive]`` are injected.
+    2-D modes only ('schedule' / 'uncertainty'); returns the pool arrays.
+    """
+    assert rollout_mode in ("schedule", "uncertainty")
+    dt = p.dtype
+    start_obs = np.asarray(start_obs, dtype=dt)
+    B, obs_dim = start_obs.shape
+    T = max_path_length
+    act_dim = None
+    pool = {
+        "obs": np.zeros((B, T, obs_dim), np.float32),
+        "next_obs": np.zeros((B, T, obs_dim), np.float32),
+        "rew": np.zeros((B, T), np.float32),
+        "cost": np.zeros((B, T), np.float32),
+        "term": np.zeros((B, T), bool),
+        "dyn_error": np.zeros((B, T), np.float32),  # mean_d(ep_var), model_sampler.py:428
+        "populated": np.zeros((B, T), bool),
+    }
+    terminated = np.zeros(B, bool)  # modelbuffer.py:114 terminated_paths_mask
+    ptr = 0
+    cur = start_obs
+    path_length = np.zeros(B)
+    dkl_accum = np.zeros(B)  # _dyn_dkl_path, model_sampler.py:240
+    total_samples = 0
+    step = 0
+    while (~terminated).any() and (max_steps is None or step < max_steps):
+        alive = ~terminated
+        n_alive = int(alive.sum())
+        a = np.asarray(policy(cur), dtype=dt)
+        if act_dim is None:
+            act_dim = a.shape[-1]
+            pool["act"] = np.zeros((B, T, act_dim), np.float32)
+        eidx = elite_idx_fn(step, n_alive)
+        next_obs, rew, term, info = fake_env_step(p, env, cur, a, elite_idx=eidx,
+                                                  cares_about_cost=cares_about_cost)
+        rew = np.squeeze(rew, -1)
+        c = np.squeeze(info["cost"], -1)
+        term = np.squeeze(term, -1)
+        dkl_path = info["ensemble_dkl_path"]
+        ep_var = info["ensemble_ep_var"]
+        if rollout_mode == "uncertainty":  # :311-313
+            too_uncertain = dkl_accum[alive] + dkl_path >= dkl_lim
+        else:
+            too_uncertain = np.zeros(n_alive, bool)  # :315
+        if max_samples:  # :327-332
+            n = total_samples + n_alive - int(too_uncertain.sum())
+            n = max(n - max_samples, 0)
+            early = np.zeros(int((~too_uncertain).sum()), bool)
+            early[:n] = True
+            too_uncertain[~too_uncertain] = early
+        # _finish_paths(too_uncertain): pool.finish_path_multiple marks them terminated
+        idx_alive = np.where(alive)[0]
+        terminated[idx_alive[too_uncertain]] = True
+        remaining = ~too_uncertain
+        alive = ~terminated
+        if not alive.any():  # :339-342
+            break
+        cur_r, a_r, nobs_r = cur[remaining], a[remaining], next_obs[remaining]
+        rew_r, c_r, term_r = rew[remaining], c[remaining], term[remaining]
+        dkl_r, epv_r = dkl_path[remaining], ep_var[remaining]
+        total_samples += int(alive.sum())  # :386
+        path_length[alive] += 1  # :400
+        dkl_accum[alive] += dkl_r  # :415
+        # store_multiple, modelbuffer.py:130-173
+        pool["obs"][alive, ptr] = cur_r
+        pool["act"][alive, ptr] = a_r
+        pool["next_obs"][alive, ptr] = nobs_r
+        pool["rew"][alive, ptr] = rew_r
+        pool["cost"][alive, ptr] = c_r
+        pool["term"][alive, ptr] = term_r
+        pool["dyn_error"][alive, ptr] = np.mean(epv_r, axis=-1)
+        pool["populated"][alive, ptr] = True
+        ptr += 1
+        cur = nobs_r  # :435
+        path_end = (path_length >= max_path_length - 1)[alive]  # :437 (Q8)
+        idx_alive = np.where(alive)[0]
+        terminated[idx_alive[path_end]] = True
+        rem2 = ~path_end
+        if not rem2.any():  # :439-441
+            break
+        cur = cur[rem2]
+        prem_term = term_r  # :452 (all alive paths share one length, so rem2 is all-True here)
+        alive = ~terminated
+        idx_alive = np.where(alive)[0]
+        terminated[idx_alive[prem_term]] = True  # :456
+        rem3 = ~prem_term
+        if not rem3.any():
+            break
+        cur = cur[rem3]  # :465
+        step += 1
+    pool["ptr"] = ptr
+    pool["total_samples"] = total_samples
+    pool["terminated"] = terminated
+    pool["dkl_accum"] = dkl_accum
+    pool["path_length"] = path_length
+    return pool
