@@ -1,0 +1,23 @@
+# Builds libcmbpo_b200.so (the C-ABI library) for sm_100a, in-tree.
+NVCC ?= nvcc
+ARCH := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xptxas -v
+SRC := constrainedmbpo_b200/csrc
+OUT := constrainedmbpo_b200/libcmbpo_b200.so
+OBJS := build/ensemble_fwd.o build/step_post.o build/cmbpo_abi.o build/rollout_ops.o
+
+all: $(OUT) build/umma_probe
+
+build/%.o: $(SRC)/%.cu $(wildcard $(SRC)/*.cuh) include/cmbpo_b200.h
+	@mkdir -p build
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(OUT): $(OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart
+
+build/umma_probe: tools/umma_probe.cu $(SRC)/sm100_ptx.cuh
+	@mkdir -p build
+	$(NVCC) $(ARCH) -O3 -lineinfo -std=c++17 -o $@ $<
+
+clean:
+	rm -rf build $(OUT)

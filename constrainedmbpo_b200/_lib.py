@@ -1,0 +1,131 @@
+"""ctypes binding of libcmbpo_b200.so (C ABI declared in include/cmbpo_b200.h).
+
+There is no fallback: if the library was not built (``python -c "import __graft_entry__ as g;
+g.build()"`` or ``make``) or no sm_100 GPU is visible, every compute entry point raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcmbpo_b200.so")
+
+MAX_LAYERS = 8
+MAX_SEGMENTS = 3
+
+ACT_IDS = {None: 0, "swish": 1, "ReLU": 2, "tanh": 3, "sigmoid": 4}  # fc.py:14-21
+
+# mbpo/static/__init__.py:7-24
+ENV_IDS = {
+    None: 0, "none": 0, "ant": 1, "antsafe": 2, "halfcheetah": 3, "halfcheetahsafe": 4,
+    "humanoid": 5, "humanoidsafe": 6, "hopper": 7, "hoppersafe": 8, "walker2d": 9,
+}
+ENVS_WITH_STATIC_COST = {"antsafe", "halfcheetahsafe", "humanoidsafe", "hoppersafe"}
+
+
+class CmbpoError(RuntimeError):
+    pass
+
+
+class cmbpo_cfg(C.Structure):
+    _fields_ = [
+        ("num_members", C.c_int32), ("num_layers", C.c_int32), ("in_dim", C.c_int32),
+        ("out_dim", C.c_int32), ("probabilistic", C.c_int32),
+        ("layer_width", C.c_int32 * MAX_LAYERS), ("layer_act", C.c_int32 * MAX_LAYERS),
+    ]
+
+
+class cmbpo_predict_io(C.Structure):
+    _fields_ = [
+        ("seg_dev", C.c_void_p * MAX_SEGMENTS), ("seg_width", C.c_int32 * MAX_SEGMENTS),
+        ("n_rows", C.c_int64), ("ndim", C.c_int32), ("agg", C.c_int32),
+        ("mean_dev", C.c_void_p), ("var_dev", C.c_void_p),
+        ("workspace_dev", C.c_void_p), ("workspace_bytes", C.c_size_t),
+    ]
+
+
+class cmbpo_step_io(C.Structure):
+    _fields_ = [
+        ("obs_dev", C.c_void_p), ("act_dev", C.c_void_p), ("n_rows", C.c_int64),
+        ("n_rows_dev", C.c_void_p), ("ndim", C.c_int32), ("perm", C.POINTER(C.c_int32)),
+        ("elite_idx_dev", C.c_void_p), ("row_id_dev", C.c_void_p), ("noise_dev", C.c_void_p),
+        ("seed", C.c_uint64), ("rng_offset", C.c_uint64), ("row_offset", C.c_int64),
+        ("env_id", C.c_int32), ("cost_mode", C.c_int32),
+        ("next_obs_dev", C.c_void_p), ("rew_dev", C.c_void_p), ("term_dev", C.c_void_p),
+        ("cost_dev", C.c_void_p), ("dkl_path_dev", C.c_void_p), ("ep_var_mean_dev", C.c_void_p),
+        ("ep_var_dev", C.c_void_p), ("scalars_dev", C.c_void_p),
+        ("workspace_dev", C.c_void_p), ("workspace_bytes", C.c_size_t),
+    ]
+
+
+class cmbpo_rollout_io(C.Structure):
+    _fields_ = [
+        ("n_paths", C.c_int64), ("max_path_length", C.c_int32), ("mode", C.c_int32),
+        ("dkl_lim", C.c_float), ("max_samples", C.c_int64), ("step_index", C.c_int32),
+        ("obs_dim", C.c_int32), ("act_dim", C.c_int32),
+        ("cur_obs_dev", C.c_void_p), ("act_dev", C.c_void_p), ("next_obs_dev", C.c_void_p),
+        ("rew_dev", C.c_void_p), ("term_dev", C.c_void_p), ("cost_dev", C.c_void_p),
+        ("dkl_path_dev", C.c_void_p), ("ep_var_mean_dev", C.c_void_p),
+        ("path_id_dev", C.c_void_p), ("state_dev", C.c_void_p), ("dkl_accum_dev", C.c_void_p),
+        ("pool_obs_dev", C.c_void_p), ("pool_act_dev", C.c_void_p), ("pool_next_obs_dev", C.c_void_p),
+        ("pool_rew_dev", C.c_void_p), ("pool_cost_dev", C.c_void_p), ("pool_term_dev", C.c_void_p),
+        ("pool_dyn_error_dev", C.c_void_p), ("pool_populated_dev", C.c_void_p),
+        ("new_obs_dev", C.c_void_p), ("new_path_id_dev", C.c_void_p),
+        ("scratch_dev", C.c_void_p), ("scratch_bytes", C.c_size_t),
+    ]
+
+
+# every symbol include/cmbpo_b200.h declares: (restype, argtypes)
+SYMBOLS = {
+    "cmbpo_create": (C.c_int, [C.POINTER(cmbpo_cfg), C.c_int, C.POINTER(C.c_void_p)]),
+    "cmbpo_destroy": (None, [C.c_void_p]),
+    "cmbpo_last_error": (C.c_char_p, []),
+    "cmbpo_device_ok": (C.c_int, [C.c_int]),
+    "cmbpo_set_weights": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cmbpo_set_scalers": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_float, C.c_void_p]),
+    "cmbpo_set_elites": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_void_p]),
+    "cmbpo_workspace_bytes": (C.c_size_t, [C.c_void_p, C.c_int64]),
+    "cmbpo_predict": (C.c_int, [C.c_void_p, C.POINTER(cmbpo_predict_io), C.c_void_p]),
+    "cmbpo_step": (C.c_int, [C.c_void_p, C.POINTER(cmbpo_step_io), C.c_void_p]),
+    "cmbpo_status": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "cmbpo_rollout_scratch_bytes": (C.c_size_t, [C.c_int64]),
+    "cmbpo_rollout_advance": (C.c_int, [C.POINTER(cmbpo_rollout_io), C.c_void_p]),
+    "cmbpo_stub_policy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                    C.c_int32, C.c_int32, C.c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen the library and bind prototypes (no GPU needed for this)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CmbpoError(
+            f"{LIB_PATH} is missing: build it with `make` or `__graft_entry__.build()`; "
+            "constrainedmbpo_b200 has no CPU or PyTorch fallback for the rollout path")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int):
+    if rc != 0:
+        msg = load().cmbpo_last_error()
+        raise CmbpoError(f"libcmbpo_b200 error {rc}: {msg.decode() if msg else '?'}")
+
+
+def require_device(device_index: int = 0):
+    lib = load()
+    if not lib.cmbpo_device_ok(device_index):
+        raise CmbpoError("no sm_100 (B200) CUDA device visible: the rollout path is CUDA-only, "
+                         "there is no CPU fallback")
+    return lib

@@ -1,0 +1,343 @@
+// cmbpo_abi.cu -- extern "C" surface of libcmbpo_b200.so (declared in include/cmbpo_b200.h).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../include/cmbpo_b200.h"
+#include "cmbpo_internal.cuh"
+#include "step_post.cuh"
+
+namespace cmbpo {
+uint32_t fwd_smem_bytes(const ModelPlan& pl);
+cudaError_t pack_layer(const float* W, const float* b, uint8_t* img, int E, const LayerPlan& lp,
+                       uint32_t blk_bytes, cudaStream_t stream);
+cudaError_t launch_ensemble_fwd(const FwdParams& p, int hidden_act, int num_sms, cudaStream_t stream);
+}  // namespace cmbpo
+
+using namespace cmbpo;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+static int fail_cuda(cudaError_t e, const char* where) {
+  g_err = std::string(where) + ": " + cudaGetErrorString(e);
+  return CMBPO_ERR_CUDA;
+}
+#define CU(x, where) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail_cuda(e_, where); } while (0)
+
+struct Handle {
+  cmbpo_cfg cfg;
+  ModelPlan plan;
+  int device = 0;
+  int num_sms = 0;
+  uint8_t* wimg = nullptr;
+  float* consts = nullptr;     // in_mu | in_inv | head_scale | head_shift
+  int* elites_dev = nullptr;
+  int n_elites = 0;
+  int* status_dev = nullptr;
+  uint32_t layers_set = 0;
+  int hidden_act = 0;
+  bool scalers_set = false;
+};
+
+static inline int roundup(int x, int m) { return (x + m - 1) / m * m; }
+
+extern "C" const char* cmbpo_last_error(void) { return g_err.c_str(); }
+
+extern "C" int cmbpo_device_ok(int device) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device >= n) { cudaGetLastError(); return 0; }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return prop.major == 10 ? 1 : 0;
+}
+
+extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
+  if (!cfg || !handle) return fail(CMBPO_ERR_ARG, "cmbpo_create: null argument");
+  *handle = nullptr;
+  const int E = cfg->num_members, L = cfg->num_layers;
+  if (E < 1 || E > 8) return fail(CMBPO_ERR_UNSUPPORTED, "num_members must be in [1, 8]");
+  if (L < 1 || L > kMaxLayers) return fail(CMBPO_ERR_UNSUPPORTED, "num_layers must be in [1, 8]");
+  if (cfg->in_dim < 1 || cfg->out_dim < 1) return fail(CMBPO_ERR_ARG, "in_dim/out_dim must be positive");
+  const int n_head = cfg->probabilistic ? 2 * cfg->out_dim : cfg->out_dim;
+  if (cfg->layer_width[L - 1] != n_head)
+    return fail(CMBPO_ERR_ARG, "last layer width must be out_dim (x2 if probabilistic), bnn.py:190-191");
+  if (cfg->layer_act[L - 1] != CMBPO_ACT_NONE)
+    return fail(CMBPO_ERR_UNSUPPORTED, "output activation must be None on this path (bnn.py:194-196)");
+  if (!cmbpo_device_ok(device))
+    return fail(CMBPO_ERR_CUDA, "no sm_100 CUDA device: this library has no CPU or other-arch fallback");
+
+  Handle* h = new Handle();
+  h->cfg = *cfg;
+  h->device = device;
+  ModelPlan& pl = h->plan;
+  memset(&pl, 0, sizeof(pl));
+  pl.E = E; pl.L = L; pl.in_dim = cfg->in_dim; pl.n_head = n_head; pl.D = cfg->out_dim;
+  pl.probabilistic = cfg->probabilistic ? 1 : 0;
+  uint32_t off = 0;
+  for (int l = 0; l < L; ++l) {
+    LayerPlan& lp = pl.layer[l];
+    lp.k_real = (l == 0) ? cfg->in_dim : cfg->layer_width[l - 1];
+    lp.n_real = cfg->layer_width[l];
+    if (lp.n_real < 1) { delete h; return fail(CMBPO_ERR_ARG, "layer width must be positive"); }
+    lp.kpad = roundup(lp.k_real + 2, 16);
+    lp.npad = (l < L - 1) ? roundup(lp.n_real + 2, 16) : roundup(lp.n_real, 16);
+    lp.act = cfg->layer_act[l];
+    if (lp.act < 0 || lp.act > CMBPO_ACT_SIGMOID) { delete h; return fail(CMBPO_ERR_ARG, "unknown activation id"); }
+    lp.prescale = (lp.act == CMBPO_ACT_SWISH || lp.act == CMBPO_ACT_SIGMOID) ? 0.5f : 1.0f;
+    if (lp.kpad > kRegionCols || lp.npad > kRegionCols) {
+      delete h;
+      return fail(CMBPO_ERR_UNSUPPORTED, "layer wider than 254: outside the resident-weight kernel (TMEM ping-pong of 2x256 columns)");
+    }
+    lp.bytes = (uint32_t)(lp.npad / 2) * lp.kpad * 2u;
+    lp.smem_off = off;
+    lp.img_off = off;
+    off += lp.bytes;
+  }
+  h->hidden_act = (L > 1) ? cfg->layer_act[0] : CMBPO_ACT_NONE;
+  for (int l = 1; l < L - 1; ++l)
+    if (cfg->layer_act[l] != h->hidden_act) {
+      delete h;
+      return fail(CMBPO_ERR_UNSUPPORTED, "hidden layers must share one activation (constructor.py:57-60)");
+    }
+  pl.w_smem_bytes = off;
+  pl.blk_bytes = off;
+  pl.a0_bytes = (uint32_t)kTileRows * pl.layer[0].kpad * 2u;
+  pl.smem_total = fwd_smem_bytes(pl);
+  if (pl.smem_total > 227u * 1024u) {
+    delete h;
+    return fail(CMBPO_ERR_UNSUPPORTED, "ensemble member does not fit the 227 KB resident-weight budget of a CTA pair");
+  }
+  CU(cudaSetDevice(device), "cudaSetDevice");
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+  h->num_sms = prop.multiProcessorCount;
+  CU(cudaMalloc(&h->wimg, (size_t)E * 2 * pl.blk_bytes), "cudaMalloc(wimg)");
+  CU(cudaMemset(h->wimg, 0, (size_t)E * 2 * pl.blk_bytes), "cudaMemset(wimg)");
+  CU(cudaMalloc(&h->consts, sizeof(float) * (2 * pl.in_dim + 2 * n_head)), "cudaMalloc(consts)");
+  CU(cudaMalloc(&h->elites_dev, sizeof(int) * 64), "cudaMalloc(elites)");
+  CU(cudaMalloc(&h->status_dev, sizeof(int)), "cudaMalloc(status)");
+  CU(cudaMemset(h->status_dev, 0, sizeof(int)), "cudaMemset(status)");
+  // defaults: identity scalers (utils.py:108-115), every member elite
+  int rc = cmbpo_set_scalers(h, nullptr, nullptr, nullptr, nullptr, 1.0f, nullptr);
+  if (rc != 0) { cmbpo_destroy(h); return rc; }
+  std::vector<int32_t> all(E);
+  for (int e = 0; e < E; ++e) all[e] = e;
+  rc = cmbpo_set_elites(h, all.data(), E, nullptr);
+  if (rc != 0) { cmbpo_destroy(h); return rc; }
+  h->scalers_set = false;
+  *handle = h;
+  return CMBPO_OK;
+}
+
+extern "C" void cmbpo_destroy(void* handle) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaFree(h->wimg); cudaFree(h->consts); cudaFree(h->elites_dev); cudaFree(h->status_dev);
+  delete h;
+}
+
+extern "C" int cmbpo_set_weights(void* handle, int32_t layer, const float* w_dev, const float* b_dev, void* stream) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || !w_dev) return fail(CMBPO_ERR_ARG, "cmbpo_set_weights: null argument");
+  if (layer < 0 || layer >= h->plan.L) return fail(CMBPO_ERR_ARG, "cmbpo_set_weights: layer out of range");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  CU(pack_layer(w_dev, b_dev, h->wimg, h->plan.E, h->plan.layer[layer], h->plan.blk_bytes, (cudaStream_t)stream),
+     "pack_layer");
+  h->layers_set |= (1u << layer);
+  return CMBPO_OK;
+}
+
+extern "C" int cmbpo_set_scalers(void* handle, const float* mu_in, const float* var_in, const float* mu_out,
+                                 const float* var_out, float sc_factor, void* stream) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h) return fail(CMBPO_ERR_ARG, "cmbpo_set_scalers: null handle");
+  if ((mu_in == nullptr) != (var_in == nullptr) || (mu_out == nullptr) != (var_out == nullptr))
+    return fail(CMBPO_ERR_ARG, "cmbpo_set_scalers: mu and var must be given together");
+  const ModelPlan& pl = h->plan;
+  std::vector<float> c(2 * pl.in_dim + 2 * pl.n_head);
+  float* in_mu = c.data();
+  float* in_inv = in_mu + pl.in_dim;
+  float* hs = in_inv + pl.in_dim;
+  float* hb = hs + pl.n_head;
+  for (int i = 0; i < pl.in_dim; ++i) {
+    in_mu[i] = mu_in ? mu_in[i] : 0.f;
+    // utils.py:161  max(sqrt(var)*sc_factor, 1e-2)
+    const float s = var_in ? fmaxf(sqrtf(var_in[i]) * sc_factor, 1e-2f) : 1.f;
+    in_inv[i] = 1.0f / s;
+  }
+  for (int j = 0; j < pl.n_head; ++j) {
+    const int d = j % pl.D;
+    const float s = var_out ? fmaxf(sqrtf(var_out[d]) * sc_factor, 1e-2f) : 1.f;
+    if (j < pl.D) {            // mean columns: utils.py:172
+      hs[j] = s; hb[j] = mu_out ? mu_out[d] : 0.f;
+    } else {                   // log-variance columns: utils.py:192
+      hs[j] = 1.f; hb[j] = var_out ? 2.0f * logf(s) : 0.f;
+    }
+  }
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  CU(cudaMemcpyAsync(h->consts, c.data(), c.size() * sizeof(float), cudaMemcpyHostToDevice, (cudaStream_t)stream),
+     "cudaMemcpyAsync(consts)");
+  CU(cudaStreamSynchronize((cudaStream_t)stream), "cudaStreamSynchronize");
+  h->scalers_set = true;
+  return CMBPO_OK;
+}
+
+extern "C" int cmbpo_set_elites(void* handle, const int32_t* elites, int32_t k, void* stream) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || !elites) return fail(CMBPO_ERR_ARG, "cmbpo_set_elites: null argument");
+  if (k < 1 || k > 64) return fail(CMBPO_ERR_ARG, "cmbpo_set_elites: k must be in [1, 64]");
+  for (int i = 0; i < k; ++i)
+    if (elites[i] < 0 || elites[i] >= h->plan.E) return fail(CMBPO_ERR_ARG, "cmbpo_set_elites: index out of range");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  CU(cudaMemcpyAsync(h->elites_dev, elites, sizeof(int32_t) * k, cudaMemcpyHostToDevice, (cudaStream_t)stream),
+     "cudaMemcpyAsync(elites)");
+  CU(cudaStreamSynchronize((cudaStream_t)stream), "cudaStreamSynchronize");
+  h->n_elites = k;
+  return CMBPO_OK;
+}
+
+static inline long long row_stride_for(long long n_rows) { return (n_rows + 31) / 32 * 32; }
+
+extern "C" size_t cmbpo_workspace_bytes(void* handle, int64_t max_rows) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || max_rows < 0) return 0;
+  const ModelPlan& pl = h->plan;
+  const size_t heads = (size_t)pl.E * pl.n_head * row_stride_for(max_rows) * sizeof(float);
+  const size_t partials = (size_t)step_post_blocks(max_rows, h->num_sms) * 4 * sizeof(float);
+  return heads + partials + 256;
+}
+
+static int check_ready(Handle* h) {
+  if (h->layers_set != (1u << h->plan.L) - 1u)
+    return fail(CMBPO_ERR_STATE, "weights of every layer must be set before predict/step");
+  return CMBPO_OK;
+}
+
+static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_width, int nseg, long long n_rows,
+                       const int* n_rows_dev, int ndim, const int32_t* perm, float* heads, cudaStream_t stream) {
+  const ModelPlan& pl = h->plan;
+  FwdParams p;
+  memset(&p, 0, sizeof(p));
+  p.plan = pl;
+  p.wimg = h->wimg;
+  p.in_mu = h->consts;
+  p.in_inv = h->consts + pl.in_dim;
+  p.head_scale = h->consts + 2 * pl.in_dim;
+  p.head_shift = h->consts + 2 * pl.in_dim + pl.n_head;
+  int wsum = 0;
+  for (int s = 0; s < kMaxSeg; ++s) {
+    p.seg_ptr[s] = (s < nseg) ? seg[s] : nullptr;
+    p.seg_width[s] = (s < nseg && seg[s]) ? seg_width[s] : 0;
+    p.seg_slot_stride[s] = (ndim == 3) ? n_rows * (long long)p.seg_width[s] : 0;
+    wsum += p.seg_width[s];
+  }
+  if (wsum != pl.in_dim) return fail(CMBPO_ERR_ARG, "Invalid input dimension.");  // fc.py:111
+  p.per_slot_input = (ndim == 3) ? 1 : 0;
+  for (int e = 0; e < pl.E; ++e) {
+    const int m = (ndim == 3 && perm) ? perm[e] : e;
+    if (m < 0 || m >= pl.E) return fail(CMBPO_ERR_ARG, "perm entry out of range");
+    p.member_of_slot[e] = m;
+    p.input_of_slot[e] = (ndim == 3 && perm) ? perm[m] : e;
+  }
+  p.n_rows_dev = n_rows_dev;
+  p.n_rows = n_rows;
+  p.row_stride = row_stride_for(n_rows);
+  p.heads = heads;
+  p.status = h->status_dev;
+  CU(launch_ensemble_fwd(p, h->hidden_act, h->num_sms, stream), "launch_ensemble_fwd");
+  return CMBPO_OK;
+}
+
+extern "C" int cmbpo_predict(void* handle, const cmbpo_predict_io* io, void* stream_) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || !io) return fail(CMBPO_ERR_ARG, "cmbpo_predict: null argument");
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (io->ndim != 2 && io->ndim != 3) return fail(CMBPO_ERR_ARG, "Invalid input dimension.");
+  if (io->n_rows < 0 || !io->mean_dev) return fail(CMBPO_ERR_ARG, "cmbpo_predict: bad rows/outputs");
+  if (io->workspace_bytes < cmbpo_workspace_bytes(h, io->n_rows) || !io->workspace_dev)
+    return fail(CMBPO_ERR_WORKSPACE, "cmbpo_predict: workspace too small");
+  if (io->n_rows == 0) return CMBPO_OK;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  const ModelPlan& pl = h->plan;
+  float* heads = static_cast<float*>(io->workspace_dev);
+  rc = run_forward(h, io->seg_dev, io->seg_width, CMBPO_MAX_SEGMENTS, io->n_rows, nullptr, io->ndim, nullptr, heads, stream);
+  if (rc) return rc;
+  const long long stride = row_stride_for(io->n_rows);
+  if (io->agg == 0 || io->ndim == 3) {
+    CU(launch_finalize_predict(heads, stride, io->n_rows, pl.E, pl.D, pl.probabilistic, io->mean_dev, io->var_dev,
+                               h->num_sms, stream), "finalize_predict");
+  } else {
+    CU(launch_aggregate_predict(heads, stride, io->n_rows, pl.E, pl.D, pl.probabilistic, io->mean_dev, io->var_dev,
+                                h->num_sms, stream), "aggregate_predict");
+  }
+  return CMBPO_OK;
+}
+
+extern "C" int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream_) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || !io) return fail(CMBPO_ERR_ARG, "cmbpo_step: null argument");
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const ModelPlan& pl = h->plan;
+  if (!pl.probabilistic) return fail(CMBPO_ERR_STATE, "cmbpo_step needs a probabilistic dynamics ensemble (fake_env.py:59)");
+  if (io->ndim != 2 && io->ndim != 3) return fail(CMBPO_ERR_ARG, "obs/act must be 2-D or 3-D (fake_env.py:132-139)");
+  const int obs_dim = pl.D - 1, act_dim = pl.in_dim - obs_dim;
+  if (act_dim < 0) return fail(CMBPO_ERR_ARG, "in_dim smaller than obs_dim");
+  if (obs_dim > 64) return fail(CMBPO_ERR_UNSUPPORTED, "obs_dim > 64 not supported by the post-processing tile");
+  if (!io->obs_dev || (act_dim > 0 && !io->act_dev) || !io->next_obs_dev || !io->rew_dev || !io->term_dev ||
+      !io->dkl_path_dev || !io->scalars_dev)
+    return fail(CMBPO_ERR_ARG, "cmbpo_step: null input/output pointer");
+  if (io->n_rows < 0) return fail(CMBPO_ERR_ARG, "cmbpo_step: negative row count");
+  if (io->workspace_bytes < cmbpo_workspace_bytes(h, io->n_rows) || !io->workspace_dev)
+    return fail(CMBPO_ERR_WORKSPACE, "cmbpo_step: workspace too small");
+  if (io->env_id < 0 || io->env_id > CMBPO_ENV_WALKER2D) return fail(CMBPO_ERR_ARG, "unknown env id");
+  if (io->n_rows == 0) return CMBPO_OK;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  float* heads = static_cast<float*>(io->workspace_dev);
+  const long long stride = row_stride_for(io->n_rows);
+  float* partials = heads + (size_t)pl.E * pl.n_head * stride;
+  const float* segs[CMBPO_MAX_SEGMENTS] = {io->obs_dev, io->act_dev, nullptr};
+  const int32_t widths[CMBPO_MAX_SEGMENTS] = {obs_dim, act_dim, 0};
+  rc = run_forward(h, segs, widths, 2, io->n_rows, io->n_rows_dev, io->ndim, io->perm, heads, stream);
+  if (rc) return rc;
+  StepParams sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.heads = heads; sp.row_stride = stride; sp.D = pl.D; sp.obs_dim = obs_dim;
+  sp.per_slot = io->ndim == 3;
+  sp.obs = io->obs_dev;
+  sp.elite_idx = io->elite_idx_dev; sp.row_ids = io->row_id_dev;
+  sp.elites = h->elites_dev; sp.n_elites = h->n_elites;
+  sp.seed = io->seed; sp.rng_offset = io->rng_offset; sp.row_offset = io->row_offset;
+  sp.noise = io->noise_dev;
+  sp.env_id = io->env_id; sp.cost_mode = io->cost_mode;
+  sp.n_rows_dev = io->n_rows_dev; sp.n_rows = io->n_rows;
+  sp.next_obs = io->next_obs_dev; sp.rew = io->rew_dev; sp.term = io->term_dev; sp.cost = io->cost_dev;
+  sp.dkl_path = io->dkl_path_dev; sp.ep_var_mean = io->ep_var_mean_dev; sp.ep_var = io->ep_var_dev;
+  sp.partials = partials;
+  const int n_blocks = step_post_blocks(io->n_rows, h->num_sms);
+  CU(launch_step_post(sp, pl.E, n_blocks, stream), "launch_step_post");
+  CU(launch_reduce_scalars(partials, n_blocks, io->n_rows_dev, io->n_rows, pl.E, pl.D, sp.per_slot ? pl.E : 1,
+                           io->scalars_dev, stream), "launch_reduce_scalars");
+  return CMBPO_OK;
+}
+
+extern "C" int cmbpo_status(void* handle, void* stream) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h) return fail(CMBPO_ERR_ARG, "cmbpo_status: null handle");
+  int st = 0;
+  cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+  if (e != cudaSuccess) return fail_cuda(e, "cmbpo_status: stream");
+  e = cudaMemcpy(&st, h->status_dev, sizeof(int), cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) return fail_cuda(e, "cmbpo_status: memcpy");
+  if (st != 0) {
+    char buf[96];
+    snprintf(buf, sizeof(buf), "device watchdog tripped: wait code %d", st & 0xFFFF);
+    return fail(CMBPO_ERR_CUDA, buf);
+  }
+  return CMBPO_OK;
+}

@@ -1,0 +1,63 @@
+// cmbpo_internal.cuh -- structures shared by the kernels and the C-ABI layer.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace cmbpo {
+
+constexpr int kMaxLayers = 8;
+constexpr int kMaxSeg = 3;     // input row = concat of up to 3 segments (obs | act | next_obs)
+constexpr int kMaxMembers = 16;
+constexpr int kTileRows = 128;  // rows per CTA tile (= TMEM lanes)
+constexpr int kRegionCols = 256;  // two ping-pong accumulator regions of 256 TMEM columns
+
+enum Activation : int { ACT_NONE = 0, ACT_SWISH = 1, ACT_RELU = 2, ACT_TANH = 3, ACT_SIGMOID = 4 };
+
+// One FC layer of the ensemble (mbpo/models/fc.py:83-114) as the kernel sees it.
+// B operand (= W^T, K-major) of each member is split in two N-halves, one per CTA of the pair.
+struct LayerPlan {
+  int k_real, n_real;   // in / out width of the layer
+  int kpad, npad;       // kpad = roundup(k_real + 2, 16): two extra K rows carry the bias (hi+lo bf16)
+  int act;              // Activation
+  float prescale;       // 0.5 for swish/sigmoid (tanh form works on x/2), else 1
+  uint32_t smem_off;    // byte offset of the layer's slot inside the weight region of smem
+  uint32_t img_off;     // byte offset inside one (member, half) block of the packed image
+  uint32_t bytes;       // (npad/2) * kpad * 2
+};
+
+struct ModelPlan {
+  int E;                // ensemble members (bnn.py:96 num_nets)
+  int L;                // FC layers including the head
+  int in_dim;           // input width
+  int n_head;           // width of the last layer (2*D if probabilistic else D)
+  int D;                // output dim per head
+  int probabilistic;    // head split into mean | logvar (bnn.py:111-112, :190-191)
+  LayerPlan layer[kMaxLayers];
+  uint32_t w_smem_bytes;  // sum of slot bytes
+  uint32_t blk_bytes;     // bytes of one (member, half) image block
+  uint32_t a0_bytes;      // 128 * k0pad * 2
+  uint32_t smem_total;    // dynamic smem the forward kernel needs
+};
+
+// Arguments of one ensemble forward launch.
+struct FwdParams {
+  ModelPlan plan;
+  const uint8_t* wimg;          // packed bf16 weight image [E][2][blk_bytes]
+  const float* in_mu;           // [in_dim] scaler_in mean          (utils.py:161)
+  const float* in_inv;          // [in_dim] 1 / max(sqrt(var)*sc, 1e-2)
+  const float* head_scale;      // [n_head] s_out for mean cols, 1 for logvar cols (utils.py:172,192)
+  const float* head_shift;      // [n_head] mu_out for mean cols, 2*log(s_out) for logvar cols
+  const float* seg_ptr[kMaxSeg];   // input segments; row-major [slots?][B][width]
+  int seg_width[kMaxSeg];
+  long long seg_slot_stride[kMaxSeg];  // elements between ensemble slots (0 => shared by all slots)
+  int per_slot_input;           // 0: 2-D input shared by all members; 1: 3-D input (fc.py:107-108)
+  int member_of_slot[kMaxMembers];  // weights used for output slot j
+  int input_of_slot[kMaxMembers];   // input slot feeding output slot j (3-D only)
+  const int* n_rows_dev;        // optional device scalar with the live row count (rollout loop)
+  long long n_rows;             // row count if n_rows_dev == nullptr
+  long long row_stride;         // B stride of the head scratch (>= n_rows)
+  float* heads;                 // out: [E][n_head][row_stride] scaled mean | shifted logvar
+  int* status;                  // watchdog / error word
+};
+
+}  // namespace cmbpo

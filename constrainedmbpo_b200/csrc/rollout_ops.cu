@@ -1,0 +1,272 @@
+// rollout_ops.cu -- device-resident bookkeeping of the batched model rollout: what
+// ModelSampler.sample does around env.step (softlearning/samplers/model_sampler.py:311-332,
+// :386-474) and what ModelBuffer.store_multiple writes (softlearning/replay_pools/
+// modelbuffer.py:130-173), restricted to the quantities the hot path owns.
+//
+// The reference compacts ~25 host arrays with boolean masks every step; here one call keeps
+// everything on the device: decide (DKL-accumulate cutoff, max_samples early termination) ->
+// stable rank -> pool write at column `ptr` -> length / terminal masks -> stable compaction of
+// the surviving rows.  Row order is preserved exactly (boolean-mask semantics).
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <cuda_runtime.h>
+#include "../../include/cmbpo_b200.h"
+
+namespace cmbpo {
+
+constexpr int kRB = 256;  // rows per block
+
+// device-resident rollout state = cmbpo_rollout_state of the public header
+struct RolloutState {
+  int n_alive;
+  int ptr;
+  long long total_samples;
+  int n_stored_last;
+  int finished;
+  int tmp_total_certain, tmp_n_early, tmp_n_keep, tmp_do_store;
+};
+static_assert(sizeof(RolloutState) == sizeof(cmbpo_rollout_state), "state layout");
+
+__device__ __forceinline__ int block_exclusive_scan(int flag, int* total) {
+  // 256 threads; returns exclusive prefix of `flag` inside the block
+  __shared__ int warp_sums[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned ballot = __ballot_sync(0xffffffffu, flag);
+  const int intra = __popc(ballot & ((1u << lane) - 1u));
+  if (lane == 0) warp_sums[warp] = __popc(ballot);
+  __syncthreads();
+  int base = 0, tot = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) { if (w < warp) base += warp_sums[w]; tot += warp_sums[w]; }
+  __syncthreads();
+  if (total) *total = tot;
+  return base + intra;
+}
+
+// A: too_uncertain flags (model_sampler.py:311-315) -> per-block count of still-certain rows
+__global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* certain, int* blk_cnt) {
+  const RolloutState* st = static_cast<const RolloutState*>(io.state_dev);
+  const int n = st->n_alive;
+  const int i = blockIdx.x * kRB + threadIdx.x;
+  int c = 0;
+  if (i < n) {
+    bool unc = false;
+    if (io.mode == 1) {  // 'uncertainty': next_dkl = accum[alive] + dkl_path >= dkl_lim
+      const int pid = static_cast<const int*>(io.path_id_dev)[i];
+      const float nd = static_cast<const float*>(io.dkl_accum_dev)[pid] + static_cast<const float*>(io.dkl_path_dev)[i];
+      unc = nd >= io.dkl_lim;
+    }
+    c = unc ? 0 : 1;
+    certain[i] = (uint8_t)c;
+  }
+  int tot;
+  block_exclusive_scan(c, &tot);
+  if (threadIdx.x == 0) blk_cnt[blockIdx.x] = tot;
+}
+
+// B/D: single-block exclusive scan of per-block counts (in place), then a small epilogue
+template <int PHASE>
+__global__ void __launch_bounds__(1024) k_scan(cmbpo_rollout_io io, int* blk_cnt, int n_blocks_max) {
+  RolloutState* st = static_cast<RolloutState*>(io.state_dev);
+  const int n_blocks = (st->n_alive + kRB - 1) / kRB;
+  __shared__ int sh[1024];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n_blocks; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = (i < n_blocks) ? blk_cnt[i] : 0;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {  // Hillis-Steele inclusive scan
+      int t = (threadIdx.x >= off) ? sh[threadIdx.x - off] : 0;
+      __syncthreads();
+      sh[threadIdx.x] += t;
+      __syncthreads();
+    }
+    const int incl = sh[threadIdx.x];
+    if (i < n_blocks) blk_cnt[i] = carry + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry += incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const int total = carry;
+    if (PHASE == 1) {
+      // model_sampler.py:327-332: n = total_samples + alive - too_uncertain - max_samples
+      long long n_early = 0;
+      if (io.max_samples > 0) {
+        n_early = st->total_samples + (long long)total - io.max_samples;
+        if (n_early < 0) n_early = 0;
+        if (n_early > total) n_early = total;
+      }
+      st->tmp_total_certain = total;
+      st->tmp_n_early = (int)n_early;
+      const int n_remaining = total - (int)n_early;
+      st->tmp_do_store = n_remaining > 0 ? 1 : 0;   // model_sampler.py:339-342: nothing alive -> return
+      st->n_stored_last = n_remaining;
+    } else {
+      st->tmp_n_keep = total;
+      if (st->tmp_do_store) {
+        st->total_samples += st->n_stored_last;      // :386
+        st->ptr += 1;                                // modelbuffer.py:173
+      }
+      st->n_alive = st->tmp_do_store ? total : 0;
+      st->finished = (st->n_alive == 0) ? 1 : 0;
+    }
+  }
+}
+
+// C: stable rank among certain rows -> remaining mask -> pool write (modelbuffer.py:130-173),
+//    dkl accumulate (:415), length mask (:437, quirk Q8) and terminal mask (:453-456) -> keep flag
+__global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_t* certain, const int* blk_off,
+                                                uint8_t* keep, int* blk_keep_cnt) {
+  const RolloutState* st = static_cast<const RolloutState*>(io.state_dev);
+  const int n = st->n_alive;
+  const int i = blockIdx.x * kRB + threadIdx.x;
+  const int c = (i < n) ? certain[i] : 0;
+  const int rank = blk_off[blockIdx.x] + block_exclusive_scan(c, nullptr);
+  const bool remaining = c && rank >= st->tmp_n_early && st->tmp_do_store;
+  const int ptr = st->ptr;
+  const int T = io.max_path_length;
+  const bool path_end = (ptr + 1) >= (T - 1);  // path_length after increment >= max_path_length-1
+  __shared__ int s_pid[kRB];
+  __shared__ uint8_t s_rem[kRB];
+  int pid = 0;
+  bool term = false;
+  if (i < n) {
+    pid = static_cast<const int*>(io.path_id_dev)[i];
+    term = static_cast<const uint8_t*>(io.term_dev)[i] != 0;
+  }
+  s_pid[threadIdx.x] = pid;
+  s_rem[threadIdx.x] = remaining ? 1 : 0;
+  if (remaining) {
+    const size_t slot = (size_t)pid * T + ptr;
+    static_cast<float*>(io.pool_rew_dev)[slot] = static_cast<const float*>(io.rew_dev)[i];
+    static_cast<float*>(io.pool_cost_dev)[slot] = io.cost_dev ? static_cast<const float*>(io.cost_dev)[i] : 0.f;
+    static_cast<uint8_t*>(io.pool_term_dev)[slot] = term ? 1 : 0;
+    static_cast<float*>(io.pool_dyn_error_dev)[slot] =
+        io.ep_var_mean_dev ? static_cast<const float*>(io.ep_var_mean_dev)[i] : 0.f;
+    static_cast<uint8_t*>(io.pool_populated_dev)[slot] = 1;
+    static_cast<float*>(io.dkl_accum_dev)[pid] += static_cast<const float*>(io.dkl_path_dev)[i];
+  }
+  const int k = (remaining && !term && !path_end) ? 1 : 0;
+  if (i < n) keep[i] = (uint8_t)k;
+  int tot;
+  block_exclusive_scan(k, &tot);   // includes the __syncthreads that publishes s_pid / s_rem
+  if (threadIdx.x == 0) blk_keep_cnt[blockIdx.x] = tot;
+  // row payloads: one warp per row so each 4*dim-byte row moves as one coalesced segment
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int OD = io.obs_dim, AD = io.act_dim;
+  for (int r = warp; r < kRB; r += 8) {
+    const int gi = blockIdx.x * kRB + r;
+    if (gi >= n || !s_rem[r]) continue;
+    const size_t slot = (size_t)s_pid[r] * T + ptr;
+    const float* so = static_cast<const float*>(io.cur_obs_dev) + (size_t)gi * OD;
+    const float* sn = static_cast<const float*>(io.next_obs_dev) + (size_t)gi * OD;
+    float* po = static_cast<float*>(io.pool_obs_dev) + slot * OD;
+    float* pn = static_cast<float*>(io.pool_next_obs_dev) + slot * OD;
+    for (int d = lane; d < OD; d += 32) { po[d] = so[d]; pn[d] = sn[d]; }
+    if (AD > 0) {
+      const float* sa = static_cast<const float*>(io.act_dev) + (size_t)gi * AD;
+      float* pa = static_cast<float*>(io.pool_act_dev) + slot * AD;
+      for (int d = lane; d < AD; d += 32) pa[d] = sa[d];
+    }
+  }
+}
+
+// synthetic benchmark policy a = tanh(obs @ P); not part of the reference
+__global__ void __launch_bounds__(256) k_stub_policy(const float* __restrict__ obs, const float* __restrict__ P,
+                                                     float* __restrict__ act, const int* n_rows_dev,
+                                                     long long n_rows, int OD, int AD) {
+  extern __shared__ float sP[];
+  for (int i = threadIdx.x; i < OD * AD; i += blockDim.x) sP[i] = P[i];
+  __syncthreads();
+  const long long n = n_rows_dev ? (long long)(*n_rows_dev) : n_rows;
+  const long long total = n * AD;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long r = idx / AD;
+    const int a = (int)(idx % AD);
+    float s = 0.f;
+    for (int d = 0; d < OD; ++d) s = fmaf(obs[(size_t)r * OD + d], sP[d * AD + a], s);
+    act[idx] = tanhf(s);
+  }
+}
+
+}  // namespace cmbpo
+
+using namespace cmbpo;
+
+static thread_local char g_roll_err[160];
+extern "C" size_t cmbpo_rollout_scratch_bytes(int64_t n_paths) {
+  const size_t nb = (size_t)((n_paths + kRB - 1) / kRB) + 1;
+  // certain[n] + keep[n] (u8) + two int arrays of per-block counts + snapshot word
+  return (size_t)n_paths * 2 + 64 + nb * 2 * sizeof(int) + 64;
+}
+
+namespace cmbpo {
+// the pre-advance alive count is needed by the compaction after k_scan<2> overwrote it
+__global__ void k_snapshot(const void* state, int* out) { *out = static_cast<const RolloutState*>(state)->n_alive; }
+
+// E: stable compaction of the surviving rows: next_obs -> new cur_obs, path ids follow
+__global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const uint8_t* keep, const int* blk_off,
+                                                      const int* n_before_dev) {
+  const int n_before = *n_before_dev;
+  const int i = blockIdx.x * kRB + threadIdx.x;
+  const int k = (i < n_before) ? keep[i] : 0;
+  const int dst = blk_off[blockIdx.x] + block_exclusive_scan(k, nullptr);
+  __shared__ int s_dst[kRB];
+  s_dst[threadIdx.x] = k ? dst : -1;
+  if (k) static_cast<int*>(io.new_path_id_dev)[dst] = static_cast<const int*>(io.path_id_dev)[i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int OD = io.obs_dim;
+  for (int r = warp; r < kRB; r += 8) {
+    const int d0 = s_dst[r];
+    if (d0 < 0) continue;
+    const float* src = static_cast<const float*>(io.next_obs_dev) + (size_t)(blockIdx.x * kRB + r) * OD;
+    float* dstp = static_cast<float*>(io.new_obs_dev) + (size_t)d0 * OD;
+    for (int d = lane; d < OD; d += 32) dstp[d] = src[d];
+  }
+}
+}  // namespace cmbpo
+
+// One sampler step after env.step: see the file header.  `n_paths` bounds the grid; the live row
+// count is read from state_dev on the device, so the host never synchronises inside a rollout.
+extern "C" int cmbpo_rollout_advance(const cmbpo_rollout_io* io_, void* stream_) {
+  if (!io_ || !io_->state_dev || !io_->scratch_dev) return CMBPO_ERR_ARG;
+  const cmbpo_rollout_io io = *io_;
+  if (io.scratch_bytes < cmbpo_rollout_scratch_bytes(io.n_paths)) return CMBPO_ERR_WORKSPACE;
+  if (io.n_paths <= 0) return CMBPO_OK;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  const int nb = (int)((io.n_paths + kRB - 1) / kRB);
+  uint8_t* certain = static_cast<uint8_t*>(io.scratch_dev);
+  uint8_t* keep = certain + io.n_paths;
+  size_t off = ((size_t)io.n_paths * 2 + 63) & ~(size_t)63;
+  int* blk_a = reinterpret_cast<int*>(static_cast<uint8_t*>(io.scratch_dev) + off);
+  int* blk_b = blk_a + nb + 1;
+  int* snap = blk_b + nb;   // last word of blk_b's slack
+  k_snapshot<<<1, 1, 0, stream>>>(io.state_dev, snap);
+  k_decide<<<nb, kRB, 0, stream>>>(io, certain, blk_a);
+  k_scan<1><<<1, 1024, 0, stream>>>(io, blk_a, nb);
+  k_store<<<nb, kRB, 0, stream>>>(io, certain, blk_a, keep, blk_b);
+  k_scan<2><<<1, 1024, 0, stream>>>(io, blk_b, nb);
+  k_compact_dev<<<nb, kRB, 0, stream>>>(io, keep, blk_b, snap);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { snprintf(g_roll_err, sizeof(g_roll_err), "rollout_advance: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }
+  return CMBPO_OK;
+}
+
+extern "C" int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* act_dev, const void* n_rows_dev,
+                                 int64_t n_rows, int32_t obs_dim, int32_t act_dim, void* stream_) {
+  if (!obs_dev || !P_dev || !act_dev || n_rows < 0) return CMBPO_ERR_ARG;
+  if (n_rows == 0) return CMBPO_OK;
+  long long blocks = (n_rows * act_dim + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  k_stub_policy<<<(int)blocks, 256, obs_dim * act_dim * sizeof(float), (cudaStream_t)stream_>>>(
+      static_cast<const float*>(obs_dev), static_cast<const float*>(P_dev), static_cast<float*>(act_dev),
+      static_cast<const int*>(n_rows_dev), n_rows, obs_dim, act_dim);
+  return cudaGetLastError() == cudaSuccess ? CMBPO_OK : CMBPO_ERR_CUDA;
+}

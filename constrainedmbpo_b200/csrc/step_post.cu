@@ -1,0 +1,414 @@
+// step_post.cu -- per-row post-processing of the ensemble heads: everything FakeEnv.step does
+// after BNN.predict returns (mbpo/models/fake_env.py:156-222), plus the transposing
+// "finalize" used by the plain BNN.predict boundary.
+//
+// One thread per rollout row.  The heads arrive as [slot][column][row] (written coalesced by
+// ensemble_fwd.cu), so every load below is a fully coalesced 128-byte warp access.  Row-major
+// tensors (obs in, next_obs out) go through a shared-memory tile so global traffic stays
+// coalesced too.
+#include "cmbpo_internal.cuh"
+#include "step_post.cuh"
+
+namespace cmbpo {
+
+// ---------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al. 2011), counter = (row, stream, 0, 0), key = seed
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                              uint32_t k0, uint32_t k1, uint32_t (&out)[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+__device__ __forceinline__ float u32_to_unit(uint32_t x) {  // (0,1]
+  return ((float)(x >> 8) + 1.0f) * (1.0f / 16777216.0f);
+}
+
+// np.clip(x, 0, 1e10) including NumPy's NaN propagation (mbpo/models/utils.py:24)
+__device__ __forceinline__ float clip_kl_exact(float x) {
+  const float r = fminf(fmaxf(x, 0.f), 1e10f);
+  return (x != x) ? x : r;
+}
+__device__ __forceinline__ float clip_kl_fast(float x) { return fminf(fmaxf(x, 0.f), 1e10f); }
+
+// static termination / cost functions, mbpo/static/<env>.py.  `x` = next_obs features the
+// functions look at; comparisons are done in fp32 exactly as NumPy does on fp32 arrays.
+struct RowFeatures {
+  float x0, x1, x2, x3, last;
+  bool finite_all;      // np.isfinite(next_obs).all(-1)
+  bool lt100_from1;     // (next_obs[..., 1:] < 100).all(-1)   (hopper, quirk Q2)
+};
+
+__device__ __forceinline__ bool termination(int env, const RowFeatures& f) {
+  switch (env) {
+    case ENV_ANT: {  // ant.py:9-14
+      const bool nd = f.finite_all && (f.x0 >= 0.2f) && (f.x0 <= 1.0f);
+      return !nd;
+    }
+    case ENV_ANTSAFE: {  // antsafe.py:9-21 -- precedence quirk Q1: (a*b*c*z_rot) >= -0.7
+      const float zr = __fsub_rn(1.0f, __fmul_rn(2.0f, __fadd_rn(__fmul_rn(f.x2, f.x2), __fmul_rn(f.x3, f.x3))));
+      const float gate = (f.finite_all && (f.x0 >= 0.2f) && (f.x0 <= 1.0f)) ? 1.0f : 0.0f;
+      const bool nd = __fmul_rn(gate, zr) >= -0.7f;
+      return !nd;
+    }
+    case ENV_HUMANOID:
+    case ENV_HUMANOIDSAFE:  // humanoid.py:11-12
+      return (f.x0 < 1.0f) || (f.x0 > 2.0f);
+    case ENV_HOPPER:
+    case ENV_HOPPERSAFE: {  // hopper.py:9-15
+      const bool nd = f.finite_all && f.lt100_from1 && (f.x0 > 0.7f) && (fabsf(f.x1) < 0.2f);
+      return !nd;
+    }
+    case ENV_WALKER2D: {  // walker2d.py:9-14
+      const bool nd = (f.x0 > 0.8f) && (f.x0 < 2.0f) && (f.x1 > -1.0f) && (f.x1 < 1.0f);
+      return !nd;
+    }
+    default:  // halfcheetah.py:9, halfcheetahsafe.py:9: never terminates
+      return false;
+  }
+}
+__device__ __forceinline__ float static_cost(int env, const RowFeatures& f, bool done) {
+  switch (env) {
+    case ENV_ANTSAFE: {  // antsafe.py:32-46
+      const float obj = (fabsf(f.last) > 3.2f) ? 1.0f : 0.0f;
+      return fminf(fmaxf((done ? 1.0f : 0.0f) + obj, 0.f), 1.f);
+    }
+    case ENV_HUMANOIDSAFE: {  // humanoidsafe.py:21-33
+      const float obj = (fabsf(f.last) > 3.0f) ? 1.0f : 0.0f;
+      return fminf(fmaxf((done ? 1.0f : 0.0f) + obj, 0.f), 1.f);
+    }
+    case ENV_HALFCHEETAHSAFE:  // halfcheetahsafe.py:17-19
+      return (fabsf(__fmul_rn(f.last, 10.0f)) < 2.0f) ? 1.0f : 0.0f;
+    case ENV_HOPPERSAFE:  // hoppersafe.py:24-25
+      return (fabsf(f.last) < 1.0f) ? 1.0f : 0.0f;
+    default:
+      return 0.0f;
+  }
+}
+
+template <int E>
+__device__ __forceinline__ float pick(const float (&m)[E], int idx) {
+  float r = m[0];
+#pragma unroll
+  for (int e = 1; e < E; ++e) r = (idx == e) ? m[e] : r;
+  return r;
+}
+
+// One column d of one row: all-pairs KL (utils.py:30-57, quirk Q5), var_E(mean) (fake_env.py:160)
+template <int E, bool EXACT>
+__device__ __forceinline__ void column_stats(const float (&m)[E], const float (&lv)[E], float (&v)[E],
+                                             float& kl_out, float& epv_out) {
+  float ls[E], inv[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    v[e] = __expf(lv[e]);                       // bnn.py:898
+    if (EXACT) {
+      // log_std = clip(log(sqrt(var)), -100, 1e8); var is recomputed from it (utils.py:20,48-49)
+      const float l = logf(sqrtf(v[e]));
+      ls[e] = fminf(fmaxf(l, -100.f), 1e8f);
+      if (l != l) ls[e] = l;
+    } else {
+      ls[e] = 0.5f * lv[e];
+    }
+  }
+  float vk[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    vk[e] = EXACT ? expf(2.0f * ls[e]) : v[e];
+    inv[e] = 1.0f / (vk[e] + 1e-10f);
+  }
+  float kl = 0.f;
+#pragma unroll
+  for (int i = 0; i < E; ++i) {
+#pragma unroll
+    for (int j = 0; j < E; ++j) {
+      if (!EXACT && j <= i) continue;
+      const float d = m[j] - m[i];
+      const float d2 = d * d;
+      if (EXACT) {
+        const float pre = 0.5f * ((d2 + vk[i]) / (vk[j] + 1e-10f) - 1.0f) + ls[j] - ls[i];
+        kl += clip_kl_exact(pre);
+      } else {
+        const float c = ls[j] - ls[i];
+        const float kij = fmaf(0.5f * (d2 + vk[i]), inv[j], c - 0.5f);
+        const float kji = fmaf(0.5f * (d2 + vk[j]), inv[i], -c - 0.5f);
+        kl += clip_kl_fast(kij) + clip_kl_fast(kji);
+      }
+    }
+  }
+  // i == j terms are exactly clip(<=0) = 0 on the fast path (finite, normal variances)
+  kl_out = kl / ((float)(E * (E - 1)) + 1e-10f);
+  float mean = 0.f;
+#pragma unroll
+  for (int e = 0; e < E; ++e) mean += m[e];
+  mean *= (1.0f / E);
+  float s2 = 0.f;
+#pragma unroll
+  for (int e = 0; e < E; ++e) { const float t = m[e] - mean; s2 = fmaf(t, t, s2); }
+  epv_out = s2 * (1.0f / E);
+}
+
+template <int E>
+__global__ void __launch_bounds__(128) step_post_kernel(const StepParams p) {
+  __shared__ float tile[kTileRows * 64 + 128];  // obs in / next_obs out staging (obs_dim <= 64)
+  __shared__ float red[4][4];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
+  const int D = p.D, OD = p.obs_dim;
+  const int n_slots_out = p.per_slot ? E : 1;
+  float acc_dkl = 0.f, acc_var = 0.f, acc_rew = 0.f, acc_cost = 0.f;
+
+  for (long long row0 = (long long)blockIdx.x * kTileRows; row0 < n_rows; row0 += (long long)gridDim.x * kTileRows) {
+    const long long g = row0 + tid;
+    const bool live = g < n_rows;
+    const int rows_here = (int)min((long long)kTileRows, n_rows - row0);
+    int eidx = 0;
+    if (!p.per_slot && live) {
+      if (p.elite_idx) {
+        eidx = p.elite_idx[g];
+      } else {  // random elite per row (bnn.py:437-439), counter-based so sharding cannot change it
+        uint32_t rnd[4];
+        const unsigned long long ctr = (unsigned long long)(p.row_offset + (p.row_ids ? (long long)p.row_ids[g] : g));
+        philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), (uint32_t)p.rng_offset, 0u,
+                      (uint32_t)p.seed, (uint32_t)(p.seed >> 32), rnd);
+        eidx = p.elites[__umulhi(rnd[0], (uint32_t)p.n_elites)];
+      }
+    }
+    float kl_row = 0.f, epv_row = 0.f;
+    // ---- pass over output slots (1 in 2-D mode; E in 3-D mode where every member keeps its own row)
+    for (int so = 0; so < n_slots_out; ++so) {
+      // stage obs rows of this tile (slot `so` in 3-D mode) through smem, coalesced
+      __syncthreads();
+      {
+        const float* src = p.obs + (p.per_slot ? (size_t)so * n_rows * OD : 0) + (size_t)row0 * OD;
+        for (int i = tid; i < rows_here * OD; i += kTileRows) tile[i] = src[i];
+      }
+      __syncthreads();
+      RowFeatures f;
+      f.x0 = f.x1 = f.x2 = f.x3 = f.last = 0.f;
+      f.finite_all = true; f.lt100_from1 = true;
+      float rew = 0.f;
+      bool slow = false;
+      if (live) {
+        for (int d = 0; d < D; ++d) {
+          float m[E], lv[E], v[E];
+          const float o = (d < OD) ? tile[tid * OD + d] : 0.f;
+#pragma unroll
+          for (int e = 0; e < E; ++e) {
+            const float* hm = p.heads + ((size_t)e * 2 * D + d) * p.row_stride + g;
+            m[e] = hm[0];
+            lv[e] = hm[(size_t)D * p.row_stride];
+          }
+          if (d < OD) {
+            if (p.per_slot) {
+              // 3-D: member e's mean gets member e's own observation (fake_env.py:156)
+              // obs of the other slots are read straight from global (L2-resident, just loaded)
+#pragma unroll
+              for (int e = 0; e < E; ++e)
+                m[e] += (e == so) ? o : p.obs[((size_t)e * n_rows + g) * OD + d];
+            } else {
+#pragma unroll
+              for (int e = 0; e < E; ++e) m[e] += o;
+            }
+          }
+          float lvmin = lv[0], lvmax = lv[0];
+#pragma unroll
+          for (int e = 1; e < E; ++e) { lvmin = fminf(lvmin, lv[e]); lvmax = fmaxf(lvmax, lv[e]); }
+          bool weird = !(lvmin > -80.f) || !(lvmax < 80.f);
+#pragma unroll
+          for (int e = 0; e < E; ++e) weird = weird || !(fabsf(m[e]) < 1e18f);
+          float kl, epv;
+          if (weird) { column_stats<E, true>(m, lv, v, kl, epv); slow = true; }
+          else column_stats<E, false>(m, lv, v, kl, epv);
+          if (so == 0) {
+            kl_row += kl; epv_row += epv;
+            float sv = 0.f;
+#pragma unroll
+            for (int e = 0; e < E; ++e) sv += v[e];
+            acc_var += sv;
+            if (p.ep_var) p.ep_var[(size_t)g * D + d] = epv;
+          }
+          float x = p.per_slot ? pick<E>(m, so) : pick<E>(m, eidx);
+          if (p.noise) {  // optional north_star mode: mean + noise*std (off in the live reference)
+            const float vs = p.per_slot ? pick<E>(v, so) : pick<E>(v, eidx);
+            const float z = p.noise[(p.per_slot ? (size_t)so * n_rows * D : 0) + (size_t)g * D + d];
+            x = fmaf(z, sqrtf(vs), x);
+          }
+          if (d < OD) {
+            tile[tid * OD + d] = x;  // own row only: safe to overwrite the staged obs
+            f.finite_all = f.finite_all && (fabsf(x) <= 3.402823466e38f);
+            if (d == 0) f.x0 = x;
+            if (d == 1) f.x1 = x;
+            if (d == 2) f.x2 = x;
+            if (d == 3) f.x3 = x;
+            if (d >= 1) f.lt100_from1 = f.lt100_from1 && (x < 100.f);
+            if (d == OD - 1) f.last = x;
+          } else {
+            rew = x;  // reward is the last output column (fake_env.py:180)
+          }
+        }
+        (void)slow;
+        const bool done = termination(p.env_id, f);
+        const float cost = (p.cost_mode == 1) ? static_cost(p.env_id, f, done) : 0.f;
+        const size_t oi = (size_t)so * n_rows + g;
+        p.rew[oi] = rew;
+        p.term[oi] = done ? 1 : 0;
+        if (p.cost) p.cost[oi] = cost;
+        if (so == 0 || p.per_slot) { acc_rew += rew; acc_cost += cost; }
+      }
+      __syncthreads();
+      {
+        float* dst = p.next_obs + (p.per_slot ? (size_t)so * n_rows * OD : 0) + (size_t)row0 * OD;
+        for (int i = tid; i < rows_here * OD; i += kTileRows) dst[i] = tile[i];
+      }
+    }
+    if (live) {
+      const float dkl = kl_row / (float)D;  // np.mean(average_dkl(...), axis=-1), fake_env.py:158
+      p.dkl_path[g] = dkl;
+      if (p.ep_var_mean) p.ep_var_mean[g] = epv_row / (float)D;
+      acc_dkl += dkl;
+    }
+  }
+  // ---- block partial sums of the four scalar diagnostics (fake_env.py:213-220)
+  float vals[4] = {acc_dkl, acc_var, acc_rew, acc_cost};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float x = vals[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) red[k][warp] = x;
+  }
+  __syncthreads();
+  if (tid < 4) p.partials[(size_t)blockIdx.x * 4 + tid] = red[tid][0] + red[tid][1] + red[tid][2] + red[tid][3];
+}
+
+// deterministic final reduction of the per-block partial sums -> 4 means
+__global__ void reduce_scalars_kernel(const float* partials, int n_blocks, const int* n_rows_dev,
+                                      long long n_rows_host, int E, int D, int n_slots_out, float* scalars) {
+  __shared__ double sh[4][32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double s[4] = {0, 0, 0, 0};
+  for (int b = tid; b < n_blocks; b += blockDim.x)
+    for (int k = 0; k < 4; ++k) s[k] += (double)partials[(size_t)b * 4 + k];
+  for (int k = 0; k < 4; ++k) {
+    double x = s[k];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) sh[k][warp] = x;
+  }
+  __syncthreads();
+  if (tid < 4) {
+    double x = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) x += sh[tid][w];
+    const double n = (double)(n_rows_dev ? (long long)(*n_rows_dev) : n_rows_host);
+    double denom = n;                                   // dkl_mean
+    if (tid == 1) denom = n * (double)E * (double)D;    // ensemble_mean_var over [E,B,D]
+    if (tid >= 2) denom = n * (double)n_slots_out;      // rew_mean / cost_mean
+    scalars[tid] = (float)(denom > 0 ? x / denom : 0.0);
+  }
+}
+
+// BNN.predict boundary: [slot][column][row] heads -> mean[E][B][D], var[E][B][D] row-major
+// (bnn.py:713-717); var = exp(logvar) (bnn.py:898).  Non-probabilistic: mean only.
+__global__ void finalize_predict_kernel(const float* __restrict__ heads, long long row_stride, long long n_rows,
+                                        int E, int D, int probabilistic, float* mean, float* var) {
+  const long long total = (long long)E * n_rows * D;
+  const int n_head = probabilistic ? 2 * D : D;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(i % D);
+    const long long g = (i / D) % n_rows;
+    const int e = (int)(i / ((long long)D * n_rows));
+    const float* h = heads + ((size_t)e * n_head + d) * row_stride + g;
+    mean[i] = h[0];
+    if (probabilistic && var) var[i] = __expf(h[(size_t)D * row_stride]);
+  }
+}
+
+
+// non-factored BNN.predict: ensemble mean [B][D]; variance = mean_E(var) + mean_E((mean-mean_E)^2) for
+// probabilistic models (bnn.py:350-352), population var_E(mean) otherwise (bnn.py:736-743)
+__global__ void aggregate_predict_kernel(const float* __restrict__ heads, long long row_stride, long long n_rows,
+                                         int E, int D, int probabilistic, float* mean, float* var) {
+  const long long total = n_rows * D;
+  const int n_head = probabilistic ? 2 * D : D;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(i % D);
+    const long long g = i / D;
+    float m = 0.f;
+    for (int e = 0; e < E; ++e) m += heads[((size_t)e * n_head + d) * row_stride + g];
+    m /= (float)E;
+    mean[i] = m;
+    if (var) {
+      float s2 = 0.f, sv = 0.f;
+      for (int e = 0; e < E; ++e) {
+        const float* h = heads + ((size_t)e * n_head + d) * row_stride + g;
+        const float t = h[0] - m;
+        s2 = fmaf(t, t, s2);
+        if (probabilistic) sv += __expf(h[(size_t)D * row_stride]);
+      }
+      var[i] = (probabilistic ? sv / (float)E : 0.f) + s2 / (float)E;
+    }
+  }
+}
+
+template <int E>
+static cudaError_t launch_step_post_E(const StepParams& p, int n_blocks, cudaStream_t stream) {
+  step_post_kernel<E><<<n_blocks, kTileRows, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+int step_post_blocks(long long n_rows, int num_sms) {
+  long long tiles = (n_rows + kTileRows - 1) / kTileRows;
+  long long cap = (long long)num_sms * 8;
+  if (tiles < 1) tiles = 1;
+  return (int)(tiles < cap ? tiles : cap);
+}
+
+cudaError_t launch_step_post(const StepParams& p, int E, int n_blocks, cudaStream_t stream) {
+  switch (E) {
+    case 1: return launch_step_post_E<1>(p, n_blocks, stream);
+    case 2: return launch_step_post_E<2>(p, n_blocks, stream);
+    case 3: return launch_step_post_E<3>(p, n_blocks, stream);
+    case 4: return launch_step_post_E<4>(p, n_blocks, stream);
+    case 5: return launch_step_post_E<5>(p, n_blocks, stream);
+    case 6: return launch_step_post_E<6>(p, n_blocks, stream);
+    case 7: return launch_step_post_E<7>(p, n_blocks, stream);
+    case 8: return launch_step_post_E<8>(p, n_blocks, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+cudaError_t launch_reduce_scalars(const float* partials, int n_blocks, const int* n_rows_dev, long long n_rows,
+                                  int E, int D, int n_slots_out, float* scalars, cudaStream_t stream) {
+  reduce_scalars_kernel<<<1, 256, 0, stream>>>(partials, n_blocks, n_rows_dev, n_rows, E, D, n_slots_out, scalars);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_aggregate_predict(const float* heads, long long row_stride, long long n_rows, int E, int D,
+                                     int probabilistic, float* mean, float* var, int num_sms, cudaStream_t stream) {
+  const long long total = n_rows * D;
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)num_sms * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  aggregate_predict_kernel<<<(int)blocks, 256, 0, stream>>>(heads, row_stride, n_rows, E, D, probabilistic, mean, var);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_finalize_predict(const float* heads, long long row_stride, long long n_rows, int E, int D,
+                                    int probabilistic, float* mean, float* var, int num_sms, cudaStream_t stream) {
+  const long long total = (long long)E * n_rows * D;
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)num_sms * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  finalize_predict_kernel<<<(int)blocks, 256, 0, stream>>>(heads, row_stride, n_rows, E, D, probabilistic, mean, var);
+  return cudaGetLastError();
+}
+
+}  // namespace cmbpo

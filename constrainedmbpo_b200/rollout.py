@@ -1,0 +1,170 @@
+"""Device-resident batched model rollout.
+
+What ``CMBPO._train`` drives through ``ModelSampler.reset`` / ``sample`` / ``ModelBuffer``
+(mbpo/algorithms/cmbpo.py:335-351; softlearning/samplers/model_sampler.py:220-474;
+softlearning/replay_pools/modelbuffer.py:45-173), restricted to what the hot path owns:
+``env.step``, the rollout-length cutoff ('schedule' length mask, 'uncertainty' accumulated-KL
+limit, ``max_samples`` early termination, terminal mask) and the pool writes.  Critic values,
+log-probs and GAE stay with the reference.
+
+Nothing in the loop synchronises with the host: the live row count is a device scalar that the
+kernels read; shapes stay at capacity.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+
+MODES = {"schedule": 0, "uncertainty": 1}
+
+
+class StubPolicy:
+    """Synthetic benchmark policy ``a = tanh(obs @ P)``, ``P ~ N(0, 1/obs_dim)``; stands
+    in for ``policy.get_action_outs`` (model_sampler.py:275) in throughput runs only."""
+
+    def __init__(self, obs_dim, act_dim, device="cuda:0", seed=4):
+        g = torch.Generator().manual_seed(seed)
+        self.P = (torch.randn(obs_dim, act_dim, generator=g) / np.sqrt(obs_dim)).to(device).contiguous()
+        self.obs_dim, self.act_dim = obs_dim, act_dim
+        self._act = None
+
+    def __call__(self, obs, n_rows_dev=None):
+        lib = _lib.load()
+        B = obs.shape[0]
+        if self._act is None or self._act.shape[0] != B:
+            self._act = torch.empty(B, self.act_dim, dtype=torch.float32, device=obs.device)
+        stream = C.c_void_p(torch.cuda.current_stream(obs.device).cuda_stream)
+        _lib.check(lib.cmbpo_stub_policy(
+            C.c_void_p(obs.data_ptr()), C.c_void_p(self.P.data_ptr()), C.c_void_p(self._act.data_ptr()),
+            C.c_void_p(n_rows_dev.data_ptr()) if n_rows_dev is not None else None,
+            B, self.obs_dim, self.act_dim, stream))
+        return self._act
+
+
+class ModelRollout:
+    """``reset(start_obs)`` then ``run(policy)``; the pool arrays have the reference's logical
+    layout ``[B, max_path_length, dim]`` with row = start-state index (modelbuffer.py:45-114)."""
+
+    def __init__(self, env, max_path_length, rollout_mode="schedule", dkl_lim=None, max_samples=None,
+                 row_offset=0):
+        if rollout_mode not in MODES:
+            raise ValueError("rollout_mode must be 'schedule' or 'uncertainty' on the device path "
+                             "('iv_gae' rolls 3-D states through FakeEnv.step; its GAE weighting is SURVEY §8f N2)")
+        if rollout_mode == "uncertainty" and dkl_lim is None:
+            raise ValueError("'uncertainty' mode needs dkl_lim (model_sampler.py:178-179 set_rollout_dkl)")
+        self.env = env
+        self.T = int(max_path_length)
+        self.mode = rollout_mode
+        self.dkl_lim = float(dkl_lim) if dkl_lim is not None else 0.0
+        self.max_samples = int(max_samples) if max_samples else 0
+        self.row_offset = int(row_offset)
+        self.device = env.device
+        self.B = 0
+        self._lib = _lib.load()
+
+    def reset(self, start_obs):
+        """model_sampler.py:220-263 + modelbuffer.py:45-114."""
+        dev = self.device
+        if not torch.is_tensor(start_obs):
+            start_obs = torch.as_tensor(np.asarray(start_obs, dtype=np.float32))
+        cur = start_obs.to(dev, dtype=torch.float32).contiguous()
+        B, OD = cur.shape
+        AD = self.env.act_dim
+        T = self.T
+        new_shape = B != self.B
+        self.B = B
+        z = lambda *s, dt=torch.float32: torch.zeros(*s, dtype=dt, device=dev)
+        if new_shape:
+            self.pool = {
+                "obs": z(B, T, OD), "act": z(B, T, AD), "next_obs": z(B, T, OD),
+                "rew": z(B, T), "cost": z(B, T), "term": z(B, T, dt=torch.uint8),
+                "dyn_error": z(B, T), "populated": z(B, T, dt=torch.uint8),
+            }
+            self.cur = [torch.empty(B, OD, dtype=torch.float32, device=dev) for _ in range(2)]
+            self.pid = [torch.empty(B, dtype=torch.int32, device=dev) for _ in range(2)]
+            self.dkl_accum = z(B)
+            self.state = torch.zeros(10, dtype=torch.int32, device=dev)
+            self.scratch = torch.empty(int(self._lib.cmbpo_rollout_scratch_bytes(B)) + 64, dtype=torch.uint8, device=dev)
+            self._step_out = {}
+        else:
+            for v in self.pool.values():
+                v.zero_()
+            self.dkl_accum.zero_()
+            self.state.zero_()
+        self.cur[0].copy_(cur)
+        self.pid[0].copy_(torch.arange(B, dtype=torch.int32, device=dev))
+        self.state[0] = B
+        self.flip = 0
+        self.steps_done = 0
+        self._row_ids = torch.empty(B, dtype=torch.int32, device=dev)
+
+    def step(self, policy):
+        """One ``ModelSampler.sample`` (model_sampler.py:265-474) for all alive rows."""
+        env = self.env
+        cur, pid = self.cur[self.flip], self.pid[self.flip]
+        n_dev = self.state[0:1]
+        act = policy(cur, n_dev)
+        row_ids = pid
+        if self.row_offset:
+            torch.add(pid, self.row_offset, out=self._row_ids)
+            row_ids = self._row_ids
+        o = env.step_device(cur, act, n_rows_dev=n_dev, row_ids=row_ids, want_ep_var=False, out=self._step_out)
+        io = _lib.cmbpo_rollout_io()
+        io.n_paths, io.max_path_length, io.mode = self.B, self.T, MODES[self.mode]
+        io.dkl_lim, io.max_samples, io.step_index = self.dkl_lim, self.max_samples, self.steps_done
+        io.obs_dim, io.act_dim = env.obs_dim, env.act_dim
+        io.cur_obs_dev, io.act_dev, io.next_obs_dev = cur.data_ptr(), act.data_ptr(), o["next_obs"].data_ptr()
+        io.rew_dev, io.term_dev, io.cost_dev = o["rew"].data_ptr(), o["term"].data_ptr(), o["cost"].data_ptr()
+        io.dkl_path_dev, io.ep_var_mean_dev = o["dkl_path"].data_ptr(), o["ep_var_mean"].data_ptr()
+        io.path_id_dev, io.state_dev, io.dkl_accum_dev = pid.data_ptr(), self.state.data_ptr(), self.dkl_accum.data_ptr()
+        p = self.pool
+        io.pool_obs_dev, io.pool_act_dev, io.pool_next_obs_dev = p["obs"].data_ptr(), p["act"].data_ptr(), p["next_obs"].data_ptr()
+        io.pool_rew_dev, io.pool_cost_dev, io.pool_term_dev = p["rew"].data_ptr(), p["cost"].data_ptr(), p["term"].data_ptr()
+        io.pool_dyn_error_dev, io.pool_populated_dev = p["dyn_error"].data_ptr(), p["populated"].data_ptr()
+        io.new_obs_dev, io.new_path_id_dev = self.cur[self.flip ^ 1].data_ptr(), self.pid[self.flip ^ 1].data_ptr()
+        io.scratch_dev, io.scratch_bytes = self.scratch.data_ptr(), self.scratch.numel()
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(self._lib.cmbpo_rollout_advance(C.byref(io), stream))
+        self.flip ^= 1
+        self.steps_done += 1
+
+    def run(self, policy, max_steps=None):
+        """Roll until every path has ended.  A path can store at most ``T-1`` transitions
+        (model_sampler.py:437, quirk Q8), so ``T-1`` sampler steps always suffice; no host
+        synchronisation happens inside the loop."""
+        n = self.T - 1 if max_steps is None else min(max_steps, self.T - 1)
+        for _ in range(max(n, 1)):
+            self.step(policy)
+        return self.pool
+
+    # ---- results ----------------------------------------------------------------------------
+    def counters(self):
+        """(n_alive, ptr, total_samples, finished) -- synchronises."""
+        s = self.state.cpu().numpy()
+        total = int(np.frombuffer(s[2:4].tobytes(), dtype=np.int64)[0])
+        return int(s[0]), int(s[1]), total, int(s[5])
+
+    def get(self, numpy=False):
+        out = dict(self.pool)
+        out["dkl_accum"] = self.dkl_accum
+        if numpy:
+            out = {k: v.cpu().numpy() for k, v in out.items()}
+            out["term"] = out["term"].astype(bool)
+            out["populated"] = out["populated"].astype(bool)
+        return out
+
+    def all_gather(self, group=None):
+        """Multi-GPU: concatenate every rank's pool shard along the path axis with one NCCL
+        all-gather per array.  Shards must have equal ``B``."""
+        import torch.distributed as dist
+        ws = dist.get_world_size(group)
+        out = {}
+        for k, v in self.pool.items():
+            full = torch.empty((ws * v.shape[0],) + tuple(v.shape[1:]), dtype=v.dtype, device=v.device)
+            dist.all_gather_into_tensor(full, v.contiguous(), group=group)
+            out[k] = full
+        return out

@@ -1,0 +1,188 @@
+/* cmbpo_b200.h -- C ABI of the B200-native CMBPO model-rollout path (libcmbpo_b200.so).
+ *
+ * The reference (anyboby/ConstrainedMBPO) has no FFI for this path: the boundary is the Python
+ * object surface construct_model / BNN.predict / FakeEnv.step.  Each entry point below cites
+ * the reference interface it stands behind; the Python mirror of that surface
+ * (constrainedmbpo_b200/{constructor,bnn,fake_env,rollout}.py) is a thin ctypes client of
+ * this library.  Citations are relative to the reference repository root.
+ *
+ * Conventions: every `*_dev`/device pointer is a CUDA device pointer owned by the caller
+ * (PyTorch tensors in the Python mirror); `stream` is a cudaStream_t passed as void*; no call
+ * allocates, frees or synchronises except create/destroy/set_*; return value 0 = ok, <0 = error
+ * (text via cmbpo_last_error()).  A handle is reentrant across handles, not thread-safe per
+ * handle.  There is no CPU fallback: every call fails with CMBPO_ERR_CUDA if no sm_100 device
+ * is usable.
+ */
+#ifndef CMBPO_B200_H_
+#define CMBPO_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CMBPO_MAX_LAYERS 8
+#define CMBPO_MAX_SEGMENTS 3
+
+enum {
+  CMBPO_OK = 0,
+  CMBPO_ERR_ARG = -1,         /* invalid argument (mirrors ValueError("Invalid input dimension."), fc.py:111) */
+  CMBPO_ERR_UNSUPPORTED = -2, /* shape outside what the resident-weight kernel supports */
+  CMBPO_ERR_CUDA = -3,        /* CUDA runtime error / no sm_100 device */
+  CMBPO_ERR_STATE = -4,       /* weights/scalers not set (mirrors RuntimeError, bnn.py:135-140,170-173) */
+  CMBPO_ERR_WORKSPACE = -5    /* workspace too small */
+};
+
+/* FC._activations, mbpo/models/fc.py:14-21 (softmax is not supported on this path) */
+enum { CMBPO_ACT_NONE = 0, CMBPO_ACT_SWISH = 1, CMBPO_ACT_RELU = 2, CMBPO_ACT_TANH = 3, CMBPO_ACT_SIGMOID = 4 };
+
+/* mbpo/static/__init__.py:7-24 -- the static_fns modules whose termination_fn / cost_f are fused */
+enum {
+  CMBPO_ENV_NONE = 0, CMBPO_ENV_ANT = 1, CMBPO_ENV_ANTSAFE = 2, CMBPO_ENV_HALFCHEETAH = 3,
+  CMBPO_ENV_HALFCHEETAHSAFE = 4, CMBPO_ENV_HUMANOID = 5, CMBPO_ENV_HUMANOIDSAFE = 6,
+  CMBPO_ENV_HOPPER = 7, CMBPO_ENV_HOPPERSAFE = 8, CMBPO_ENV_WALKER2D = 9
+};
+
+/* Structure of one ensemble: what construct_model(...) fixes (mbpo/models/constructor.py:9-67)
+ * after BNN.finalize doubled the head of a probabilistic model (mbpo/models/bnn.py:190-196). */
+typedef struct cmbpo_cfg {
+  int32_t num_members;                    /* num_networks                     constructor.py:13 */
+  int32_t num_layers;                     /* len(hidden_dims) + 1             constructor.py:57-62 */
+  int32_t in_dim;                         /* in_dim                           constructor.py:9 */
+  int32_t out_dim;                        /* out_dim (per head)               constructor.py:10 */
+  int32_t probabilistic;                  /* loss in {NLL, MSPE}              bnn.py:111-112 */
+  int32_t layer_width[CMBPO_MAX_LAYERS];  /* FC output widths; last = 2*out_dim if probabilistic */
+  int32_t layer_act[CMBPO_MAX_LAYERS];    /* CMBPO_ACT_* per layer; last must be NONE (bnn.py:194-196) */
+} cmbpo_cfg;
+
+/* construct_model -> BNN(params) + FC stack + finalize   (constructor.py:41-67) */
+int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle);
+void cmbpo_destroy(void* handle);
+const char* cmbpo_last_error(void);
+/* 1 if a CUDA device with compute capability 10.x is visible, else 0 (never launches) */
+int cmbpo_device_ok(int device);
+
+/* FC weights [E][in][out] and biases [E][1][out], fp32 (mbpo/models/fc.py:154-185); read after
+ * every BNN.train() (bnn.py:467-666) because training rewrites them.  Device pointers. */
+int cmbpo_set_weights(void* handle, int32_t layer, const float* w_dev, const float* b_dev, void* stream);
+/* TensorStandardScaler state (mbpo/models/utils.py:98-115): mu/var [dim] HOST pointers, NULL =
+ * scaler absent (use_scaler_in/out False, bnn.py:201-207).  `var` is the variance (the TF
+ * variable is only *named* _std); divisor = max(sqrt(var)*sc_factor, 1e-2) (utils.py:161). */
+int cmbpo_set_scalers(void* handle, const float* mu_in, const float* var_in, const float* mu_out,
+                      const float* var_out, float sc_factor, void* stream);
+/* BNN._model_inds (bnn.py:98-102, :428-431): HOST pointer, duplicates allowed */
+int cmbpo_set_elites(void* handle, const int32_t* elites, int32_t k, void* stream);
+
+/* bytes of caller-provided device scratch needed for `max_rows` rows */
+size_t cmbpo_workspace_bytes(void* handle, int64_t max_rows);
+
+/* BNN.predict (mbpo/models/bnn.py:671-776).
+ * Input rows are the concatenation of up to 3 row-major segments (fake_env.py:141-145,:194).
+ * ndim 2: segments are [B][w]; ndim 3: [E][B][w], member e consumes slot e (fc.py:107-108).
+ * agg 0 (factored): mean/var are [E][B][D]; agg 1: ensemble mean [B][D] and, for probabilistic
+ * models, mean_E(var)+mean_E((mean-mean_E)^2) (bnn.py:350-352), else var_E (bnn.py:736-743).
+ * var_dev may be NULL (inc_var=False). */
+typedef struct cmbpo_predict_io {
+  const float* seg_dev[CMBPO_MAX_SEGMENTS];
+  int32_t seg_width[CMBPO_MAX_SEGMENTS];
+  int64_t n_rows;
+  int32_t ndim;
+  int32_t agg;
+  float* mean_dev;
+  float* var_dev;
+  void* workspace_dev;
+  size_t workspace_bytes;
+} cmbpo_predict_io;
+int cmbpo_predict(void* handle, const cmbpo_predict_io* io, void* stream);
+
+/* FakeEnv.step (mbpo/models/fake_env.py:131-222) for the dynamics ensemble of `handle`
+ * (in_dim = obs+act, out_dim = obs+1). */
+typedef struct cmbpo_step_io {
+  const float* obs_dev;        /* [B][obs] or [E][B][obs] */
+  const float* act_dev;        /* [B][act] or [E][B][act] */
+  int64_t n_rows;              /* B (capacity when n_rows_dev is given) */
+  const int32_t* n_rows_dev;   /* optional live row count on the device (rollout loop) */
+  int32_t ndim;                /* 2 or 3 (fake_env.py:133-139, 1-D is broken upstream) */
+  const int32_t* perm;         /* HOST [E]: forward_shuffle permutation (fake_env.py:309-316), NULL = identity */
+  const int32_t* elite_idx_dev;/* [B] injected BNN.random_inds draw (bnn.py:437-439) or NULL => Philox */
+  const int32_t* row_id_dev;   /* optional [B] global path id per row: Philox counter after compaction */
+  const float* noise_dev;      /* optional N(0,1) [B][D] / [E][B][D]; NULL = reference behaviour */
+  uint64_t seed, rng_offset;   /* Philox key / stream when elite_idx_dev == NULL */
+  int64_t row_offset;          /* global index of row 0 (shard-invariant draws) */
+  int32_t env_id;              /* CMBPO_ENV_* : static termination_fn (fake_env.py:182-185) */
+  int32_t cost_mode;           /* 0: zeros (fake_env.py:202); 1: static cost_f (fake_env.py:189) */
+  float* next_obs_dev;         /* [B][obs] or [E][B][obs] */
+  float* rew_dev;              /* [B] or [E][B] */
+  uint8_t* term_dev;           /* [B] or [E][B] */
+  float* cost_dev;             /* [B] or [E][B], may be NULL */
+  float* dkl_path_dev;         /* [B] ensemble_dkl_path (fake_env.py:158) */
+  float* ep_var_mean_dev;      /* [B] mean over D of ensemble_ep_var, may be NULL */
+  float* ep_var_dev;           /* [B][D] ensemble_ep_var (fake_env.py:160), may be NULL */
+  float* scalars_dev;          /* [4]: ensemble_dkl_mean, ensemble_mean_var, rew_mean, cost_mean */
+  void* workspace_dev;
+  size_t workspace_bytes;
+} cmbpo_step_io;
+int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream);
+
+/* ---- device-resident rollout bookkeeping (ModelSampler.sample around env.step,
+ * softlearning/samplers/model_sampler.py:311-332,:386-474; ModelBuffer.store_multiple,
+ * softlearning/replay_pools/modelbuffer.py:130-173) ---- */
+
+/* lives in device memory; initialise n_alive = B and everything else to 0 (model_sampler.py:220-263) */
+typedef struct cmbpo_rollout_state {
+  int32_t n_alive;        /* rows of cur_obs / path_id that are alive */
+  int32_t ptr;            /* pool column of the next store == path length of every alive path (modelbuffer.py:173) */
+  int64_t total_samples;  /* model_sampler.py:386 */
+  int32_t n_stored_last;  /* transitions the last advance wrote */
+  int32_t finished;       /* 1 once no path is alive */
+  int32_t tmp[4];         /* scratch of the advance kernels */
+} cmbpo_rollout_state;
+
+/* One sampler step AFTER cmbpo_step produced next_obs/rew/term/cost/dkl_path/ep_var_mean for the
+ * first state->n_alive rows.  mode 0 = 'schedule' (length mask only), 1 = 'uncertainty'
+ * (accumulated ensemble KL vs dkl_lim, model_sampler.py:311-313).  Pools are [n_paths][T][dim]
+ * (modelbuffer.py:45-114), row = original path id.  Survivors are compacted, order preserved,
+ * into new_obs / new_path_id; state is updated on the device (no host synchronisation). */
+typedef struct cmbpo_rollout_io {
+  int64_t n_paths;             /* B: rows at reset, bounds every grid */
+  int32_t max_path_length;     /* T (modelbuffer.py:19); a path ends when length >= T-1 (model_sampler.py:437) */
+  int32_t mode;
+  float dkl_lim;               /* model_sampler.py:179 set_rollout_dkl */
+  int64_t max_samples;         /* 0 = None (model_sampler.py:327) */
+  int32_t step_index;          /* informational */
+  int32_t obs_dim, act_dim;
+  const float* cur_obs_dev;    /* [n_alive][obs] */
+  const float* act_dev;        /* [n_alive][act] */
+  const float* next_obs_dev;   /* [n_alive][obs] */
+  const float* rew_dev;        /* [n_alive] */
+  const uint8_t* term_dev;     /* [n_alive] */
+  const float* cost_dev;       /* [n_alive] or NULL */
+  const float* dkl_path_dev;   /* [n_alive] */
+  const float* ep_var_mean_dev;/* [n_alive] or NULL */
+  const int32_t* path_id_dev;  /* [n_alive] original path of each alive row */
+  void* state_dev;             /* cmbpo_rollout_state */
+  float* dkl_accum_dev;        /* [B] _dyn_dkl_path (model_sampler.py:240,:415) */
+  float* pool_obs_dev; float* pool_act_dev; float* pool_next_obs_dev;   /* [B][T][dim] */
+  float* pool_rew_dev; float* pool_cost_dev; uint8_t* pool_term_dev;    /* [B][T] */
+  float* pool_dyn_error_dev; uint8_t* pool_populated_dev;               /* [B][T] */
+  float* new_obs_dev;          /* [n_alive'][obs] compacted survivors */
+  int32_t* new_path_id_dev;    /* [n_alive'] */
+  void* scratch_dev; size_t scratch_bytes;   /* >= cmbpo_rollout_scratch_bytes(n_paths) */
+} cmbpo_rollout_io;
+size_t cmbpo_rollout_scratch_bytes(int64_t n_paths);
+int cmbpo_rollout_advance(const cmbpo_rollout_io* io, void* stream);
+
+/* Synthetic benchmark policy a = tanh(obs @ P), P [obs][act] (not part of the reference; stands in
+ * for policy.get_action_outs, model_sampler.py:275, in throughput runs) */
+int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* act_dev, const void* n_rows_dev,
+                      int64_t n_rows, int32_t obs_dim, int32_t act_dim, void* stream);
+
+/* watchdog word of the last launches on this handle (0 = clean), synchronises the stream */
+int cmbpo_status(void* handle, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CMBPO_B200_H_ */

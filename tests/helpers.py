@@ -1,0 +1,77 @@
+"""Shared builders for the parity tests: one random ensemble, mirrored into the oracle
+(NumPy) and -- on a GPU box -- into the CUDA path through BNN.load_state."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from oracle import cmbpo_oracle as orc  # noqa: E402
+
+ENV_DIMS = {  # (obs, act) -- SURVEY §8d "Dims used"
+    "antsafe": (29, 8), "ant": (27, 8), "halfcheetah": (17, 6), "halfcheetahsafe": (18, 6),
+    "humanoid": (45, 17), "humanoidsafe": (45, 17), "hopper": (11, 3), "hoppersafe": (12, 3),
+    "walker2d": (17, 6),
+}
+
+
+def make_params(env="antsafe", hidden=(200, 200, 200, 200), E=7, elites=(0, 1, 2, 3, 4), seed=0,
+                parity_scalers=True, bias=True, dtype=np.float64):
+    """Random dynamics ensemble (fc.py:154-185 init) with non-trivial scalers: mu~U(-1,1),
+    var~U(0.25,4), two input dims forced to var=1e-6 to exercise the 1e-2 floor (quirk Q6)."""
+    obs, act = ENV_DIMS[env]
+    rng = np.random.default_rng(seed)
+    p = orc.init_ensemble(rng, obs + act, obs + 1, hidden, E, probabilistic=True, use_scaler_in=True,
+                          use_scaler_out=True, elites=list(elites), dtype=np.float64)
+    if bias:
+        for b in p.biases:
+            b += rng.normal(0, 0.1, b.shape)
+    if parity_scalers:
+        r3 = np.random.default_rng(3)
+        p.mu_in = r3.uniform(-1, 1, p.mu_in.shape)
+        p.var_in = r3.uniform(0.25, 4, p.var_in.shape)
+        p.var_in[0, 5] = 1e-6
+        p.var_in[0, obs + 1] = 1e-6
+        p.mu_out = r3.uniform(-1, 1, p.mu_out.shape) * 0.1
+        p.var_out = r3.uniform(0.25, 4, p.var_out.shape) * 0.01
+        p.var_out[0, 3] = 1e-6
+    return p.astype(dtype)
+
+
+def make_inputs(env, B, seed=1, E=None):
+    """obs ~ N(0,1) with env overrides so thresholds are crossed; act ~ U(-1,1)."""
+    obs_dim, act_dim = ENV_DIMS[env]
+    rng = np.random.default_rng(seed)
+    shape = (B,) if E is None else (E, B)
+    obs = rng.standard_normal(shape + (obs_dim,))
+    if env in ("antsafe", "ant"):
+        obs[..., 0] = rng.uniform(0.1, 1.1, shape)
+        q = rng.standard_normal(shape + (4,))
+        obs[..., 1:5] = q / np.linalg.norm(q, axis=-1, keepdims=True)
+        obs[..., -1] = rng.uniform(-4, 4, shape)
+    if env.startswith("humanoid"):
+        obs[..., 0] = rng.uniform(0.8, 2.2, shape)
+        obs[..., -1] = rng.uniform(-4, 4, shape)
+    if env.startswith("hopper") or env == "walker2d":
+        obs[..., 0] = rng.uniform(0.5, 1.5, shape)
+        obs[..., 1] = rng.uniform(-0.4, 0.4, shape)
+    act = np.random.default_rng(seed + 1).uniform(-1, 1, shape + (act_dim,))
+    return obs.astype(np.float32), act.astype(np.float32)
+
+
+def build_cuda_env(p, env, hidden, cares_about_cost=False, seed=0):
+    """FakeEnv on cuda:0 carrying exactly the oracle's parameters."""
+    import constrainedmbpo_b200 as cm
+    obs_dim, act_dim = ENV_DIMS[env]
+    fe = cm.FakeEnv(cm.SimpleEnv(obs_dim, act_dim), env, num_networks=p.num_nets, num_elites=len(p.elites),
+                    hidden_dims=tuple(hidden), cares_about_cost=cares_about_cost, seed=seed)
+    fe._model.load_state([w.astype(np.float32) for w in p.weights], [b.astype(np.float32) for b in p.biases],
+                         scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+    return fe
+
+
+def out_scale(p):
+    return orc.scaler_divisor(np.asarray(p.var_out, np.float64), p.sc_factor).reshape(-1)
