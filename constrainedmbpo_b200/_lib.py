@@ -62,7 +62,7 @@ class cmbpo_step_io(C.Structure):
 class cmbpo_rollout_io(C.Structure):
     _fields_ = [
         ("n_paths", C.c_int64), ("max_path_length", C.c_int32), ("mode", C.c_int32),
-        ("dkl_lim", C.c_float), ("max_samples", C.c_int64), ("step_index", C.c_int32),
+        ("dkl_lim", C.c_double), ("max_samples", C.c_int64), ("step_index", C.c_int32),
         ("obs_dim", C.c_int32), ("act_dim", C.c_int32),
         ("cur_obs_dev", C.c_void_p), ("act_dev", C.c_void_p), ("next_obs_dev", C.c_void_p),
         ("rew_dev", C.c_void_p), ("term_dev", C.c_void_p), ("cost_dev", C.c_void_p),
@@ -73,6 +73,7 @@ class cmbpo_rollout_io(C.Structure):
         ("pool_dyn_error_dev", C.c_void_p), ("pool_populated_dev", C.c_void_p),
         ("new_obs_dev", C.c_void_p), ("new_path_id_dev", C.c_void_p),
         ("scratch_dev", C.c_void_p), ("scratch_bytes", C.c_size_t),
+        ("alive_hist_dev", C.c_void_p),
     ]
 
 
@@ -90,6 +91,8 @@ SYMBOLS = {
     "cmbpo_predict": (C.c_int, [C.c_void_p, C.POINTER(cmbpo_predict_io), C.c_void_p]),
     "cmbpo_step": (C.c_int, [C.c_void_p, C.POINTER(cmbpo_step_io), C.c_void_p]),
     "cmbpo_status": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "cmbpo_profile": (C.c_int, [C.c_void_p, C.c_int]),
+    "cmbpo_profile_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cmbpo_rollout_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "cmbpo_rollout_advance": (C.c_int, [C.POINTER(cmbpo_rollout_io), C.c_void_p]),
     "cmbpo_stub_policy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 #include "../../include/cmbpo_b200.h"
 #include "cmbpo_internal.cuh"
@@ -38,6 +39,8 @@ struct Handle {
   uint32_t layers_set = 0;
   int hidden_act = 0;
   bool scalers_set = false;
+  bool profiling = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
 };
 
 static inline int roundup(int x, int m) { return (x + m - 1) / m * m; }
@@ -246,7 +249,17 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   p.row_stride = row_stride_for(n_rows);
   p.heads = heads;
   p.status = h->status_dev;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  if (h->profiling) {
+    CU(cudaEventCreate(&ev0), "cudaEventCreate");
+    CU(cudaEventCreate(&ev1), "cudaEventCreate");
+    CU(cudaEventRecord(ev0, stream), "cudaEventRecord");
+  }
   CU(launch_ensemble_fwd(p, h->hidden_act, h->num_sms, stream), "launch_ensemble_fwd");
+  if (h->profiling) {
+    CU(cudaEventRecord(ev1, stream), "cudaEventRecord");
+    h->prof_events.emplace_back(ev0, ev1);
+  }
   return CMBPO_OK;
 }
 
@@ -323,6 +336,30 @@ extern "C" int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream_) 
   CU(launch_step_post(sp, pl.E, n_blocks, stream), "launch_step_post");
   CU(launch_reduce_scalars(partials, n_blocks, io->n_rows_dev, io->n_rows, pl.E, pl.D, sp.per_slot ? pl.E : 1,
                            io->scalars_dev, stream), "launch_reduce_scalars");
+  return CMBPO_OK;
+}
+
+extern "C" int cmbpo_profile(void* handle, int enable) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h) return fail(CMBPO_ERR_ARG, "cmbpo_profile: null handle");
+  h->profiling = enable != 0;
+  return CMBPO_OK;
+}
+
+extern "C" int cmbpo_profile_read(void* handle, double* fwd_ms_total, int64_t* fwd_launches) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h || !fwd_ms_total || !fwd_launches) return fail(CMBPO_ERR_ARG, "cmbpo_profile_read: null argument");
+  double total = 0.0;
+  for (auto& pr : h->prof_events) {
+    CU(cudaEventSynchronize(pr.second), "cudaEventSynchronize");
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, pr.first, pr.second), "cudaEventElapsedTime");
+    total += ms;
+    cudaEventDestroy(pr.first); cudaEventDestroy(pr.second);
+  }
+  *fwd_ms_total = total;
+  *fwd_launches = (int64_t)h->prof_events.size();
+  h->prof_events.clear();
   return CMBPO_OK;
 }
 

@@ -54,7 +54,8 @@ __global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* ce
     bool unc = false;
     if (io.mode == 1) {  // 'uncertainty': next_dkl = accum[alive] + dkl_path >= dkl_lim
       const int pid = static_cast<const int*>(io.path_id_dev)[i];
-      const float nd = static_cast<const float*>(io.dkl_accum_dev)[pid] + static_cast<const float*>(io.dkl_path_dev)[i];
+      // float64 accumulator + float32 increment, compared with a Python float (model_sampler.py:311-312)
+      const double nd = io.dkl_accum_dev[pid] + (double)static_cast<const float*>(io.dkl_path_dev)[i];
       unc = nd >= io.dkl_lim;
     }
     c = unc ? 0 : 1;
@@ -149,7 +150,7 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
     static_cast<float*>(io.pool_dyn_error_dev)[slot] =
         io.ep_var_mean_dev ? static_cast<const float*>(io.ep_var_mean_dev)[i] : 0.f;
     static_cast<uint8_t*>(io.pool_populated_dev)[slot] = 1;
-    static_cast<float*>(io.dkl_accum_dev)[pid] += static_cast<const float*>(io.dkl_path_dev)[i];
+    io.dkl_accum_dev[pid] += (double)static_cast<const float*>(io.dkl_path_dev)[i];
   }
   const int k = (remaining && !term && !path_end) ? 1 : 0;
   if (i < n) keep[i] = (uint8_t)k;
@@ -208,7 +209,11 @@ extern "C" size_t cmbpo_rollout_scratch_bytes(int64_t n_paths) {
 
 namespace cmbpo {
 // the pre-advance alive count is needed by the compaction after k_scan<2> overwrote it
-__global__ void k_snapshot(const void* state, int* out) { *out = static_cast<const RolloutState*>(state)->n_alive; }
+__global__ void k_snapshot(const void* state, int* out, int* hist) {
+  const int n = static_cast<const RolloutState*>(state)->n_alive;
+  *out = n;
+  if (hist) *hist = n;
+}
 
 // E: stable compaction of the surviving rows: next_obs -> new cur_obs, path ids follow
 __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const uint8_t* keep, const int* blk_off,
@@ -248,7 +253,7 @@ extern "C" int cmbpo_rollout_advance(const cmbpo_rollout_io* io_, void* stream_)
   int* blk_a = reinterpret_cast<int*>(static_cast<uint8_t*>(io.scratch_dev) + off);
   int* blk_b = blk_a + nb + 1;
   int* snap = blk_b + nb;   // last word of blk_b's slack
-  k_snapshot<<<1, 1, 0, stream>>>(io.state_dev, snap);
+  k_snapshot<<<1, 1, 0, stream>>>(io.state_dev, snap, io.alive_hist_dev ? io.alive_hist_dev + io.step_index : nullptr);
   k_decide<<<nb, kRB, 0, stream>>>(io, certain, blk_a);
   k_scan<1><<<1, 1024, 0, stream>>>(io, blk_a, nb);
   k_store<<<nb, kRB, 0, stream>>>(io, certain, blk_a, keep, blk_b);

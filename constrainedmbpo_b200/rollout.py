@@ -45,6 +45,28 @@ class StubPolicy:
         return self._act
 
 
+def compute_dynamics_dkl(env, policy, obs_batch, depth=1):
+    """``ModelSampler.compute_dynamics_dkl`` (model_sampler.py:160-176): roll ``depth`` steps from
+    ``obs_batch``, dropping terminated rows, and return (running mean of ``ensemble_dkl_mean``
+    weighted by rows) * depth -- the value CMBPO hands to ``set_rollout_dkl`` (cmbpo.py:283-285).
+    Calibration only (cold path): synchronises every step."""
+    dev = env.device
+    if not torch.is_tensor(obs_batch):
+        obs_batch = torch.as_tensor(np.asarray(obs_batch, dtype=np.float32))
+    obs = obs_batch.to(dev, dtype=torch.float32).contiguous()
+    total_dkl, total_samples = 0.0, 0
+    for _ in range(depth):
+        if obs.shape[0] == 0:
+            break
+        act = policy(obs).clone()
+        o = env.step_device(obs, act, want_ep_var=False)
+        n_paths = obs.shape[0]
+        total_dkl += float(o["scalars"][0].item()) * n_paths
+        total_samples += n_paths
+        obs = o["next_obs"][~o["term"].reshape(-1).bool()].contiguous()
+    return total_dkl / max(total_samples, 1) * depth
+
+
 class ModelRollout:
     """``reset(start_obs)`` then ``run(policy)``; the pool arrays have the reference's logical
     layout ``[B, max_path_length, dim]`` with row = start-state index (modelbuffer.py:45-114)."""
@@ -66,41 +88,48 @@ class ModelRollout:
         self.B = 0
         self._lib = _lib.load()
 
+    def _allocate(self, B, OD):
+        dev, T, AD = self.device, self.T, self.env.act_dim
+        z = lambda *s, dt=torch.float32: torch.zeros(*s, dtype=dt, device=dev)
+        self.B = B
+        self.pool = {
+            "obs": z(B, T, OD), "act": z(B, T, AD), "next_obs": z(B, T, OD),
+            "rew": z(B, T), "cost": z(B, T), "term": z(B, T, dt=torch.uint8),
+            "dyn_error": z(B, T), "populated": z(B, T, dt=torch.uint8),
+        }
+        self.cur = [torch.empty(B, OD, dtype=torch.float32, device=dev) for _ in range(2)]
+        self.pid = [torch.empty(B, dtype=torch.int32, device=dev) for _ in range(2)]
+        self.dkl_accum = z(B, dt=torch.float64)
+        self.state = torch.zeros(10, dtype=torch.int32, device=dev)
+        self._state_init = torch.zeros(10, dtype=torch.int32, device=dev)
+        self._state_init[0] = B
+        self._arange = torch.arange(B, dtype=torch.int32, device=dev)
+        self.alive_hist = torch.zeros(max(T, 1), dtype=torch.int32, device=dev)
+        self.scratch = torch.empty(int(self._lib.cmbpo_rollout_scratch_bytes(B)) + 64, dtype=torch.uint8, device=dev)
+        self._row_ids = torch.empty(B, dtype=torch.int32, device=dev)
+        self._step_out = {}
+        self._graph = None
+
     def reset(self, start_obs):
-        """model_sampler.py:220-263 + modelbuffer.py:45-114."""
+        """model_sampler.py:220-263 + modelbuffer.py:45-114.  Allocation happens only when the
+        number of start states changes; otherwise the buffers are cleared in place (which is what
+        makes reset + run capturable in one CUDA graph)."""
         dev = self.device
         if not torch.is_tensor(start_obs):
             start_obs = torch.as_tensor(np.asarray(start_obs, dtype=np.float32))
-        cur = start_obs.to(dev, dtype=torch.float32).contiguous()
-        B, OD = cur.shape
-        AD = self.env.act_dim
-        T = self.T
-        new_shape = B != self.B
-        self.B = B
-        z = lambda *s, dt=torch.float32: torch.zeros(*s, dtype=dt, device=dev)
-        if new_shape:
-            self.pool = {
-                "obs": z(B, T, OD), "act": z(B, T, AD), "next_obs": z(B, T, OD),
-                "rew": z(B, T), "cost": z(B, T), "term": z(B, T, dt=torch.uint8),
-                "dyn_error": z(B, T), "populated": z(B, T, dt=torch.uint8),
-            }
-            self.cur = [torch.empty(B, OD, dtype=torch.float32, device=dev) for _ in range(2)]
-            self.pid = [torch.empty(B, dtype=torch.int32, device=dev) for _ in range(2)]
-            self.dkl_accum = z(B)
-            self.state = torch.zeros(10, dtype=torch.int32, device=dev)
-            self.scratch = torch.empty(int(self._lib.cmbpo_rollout_scratch_bytes(B)) + 64, dtype=torch.uint8, device=dev)
-            self._step_out = {}
+        B, OD = start_obs.shape
+        if B != self.B:
+            self._allocate(B, OD)
         else:
             for v in self.pool.values():
                 v.zero_()
             self.dkl_accum.zero_()
-            self.state.zero_()
-        self.cur[0].copy_(cur)
-        self.pid[0].copy_(torch.arange(B, dtype=torch.int32, device=dev))
-        self.state[0] = B
+        self.alive_hist.zero_()
+        self.cur[0].copy_(start_obs, non_blocking=True)
+        self.pid[0].copy_(self._arange)
+        self.state.copy_(self._state_init)
         self.flip = 0
         self.steps_done = 0
-        self._row_ids = torch.empty(B, dtype=torch.int32, device=dev)
 
     def step(self, policy):
         """One ``ModelSampler.sample`` (model_sampler.py:265-474) for all alive rows."""
@@ -127,6 +156,7 @@ class ModelRollout:
         io.pool_dyn_error_dev, io.pool_populated_dev = p["dyn_error"].data_ptr(), p["populated"].data_ptr()
         io.new_obs_dev, io.new_path_id_dev = self.cur[self.flip ^ 1].data_ptr(), self.pid[self.flip ^ 1].data_ptr()
         io.scratch_dev, io.scratch_bytes = self.scratch.data_ptr(), self.scratch.numel()
+        io.alive_hist_dev = self.alive_hist.data_ptr()
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         _lib.check(self._lib.cmbpo_rollout_advance(C.byref(io), stream))
         self.flip ^= 1
@@ -141,12 +171,50 @@ class ModelRollout:
             self.step(policy)
         return self.pool
 
+    def capture(self, start_obs, policy):
+        """Record ``reset(start_obs)`` + ``run(policy)`` into one CUDA graph.  ``start_obs`` must be a
+        CUDA tensor that stays alive (refill it in place before ``replay``); ``policy`` must be a
+        device policy without host synchronisation.  One eager rollout runs first so every lazy
+        allocation (workspace, output buffers, kernel attributes) happens outside the capture."""
+        assert torch.is_tensor(start_obs) and start_obs.is_cuda
+        self.reset(start_obs)
+        self.run(policy)
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.reset(start_obs)
+            self.run(policy)
+        self._graph = g
+        return g
+
+    def replay(self):
+        self._graph.replay()
+
     # ---- results ----------------------------------------------------------------------------
     def counters(self):
         """(n_alive, ptr, total_samples, finished) -- synchronises."""
         s = self.state.cpu().numpy()
         total = int(np.frombuffer(s[2:4].tobytes(), dtype=np.int64)[0])
         return int(s[0]), int(s[1]), total, int(s[5])
+
+    def transitions(self, host_out=None):
+        """``ModelBuffer.get`` minus GAE (modelbuffer.py:348-405): the populated transitions,
+        flattened in [path, t] order.  Returns CUDA tensors, or fills / returns pinned host
+        buffers when ``host_out`` is a dict (device->host copy of exactly the populated rows)."""
+        mask = self.pool["populated"].bool()
+        out = {k: v[mask] for k, v in self.pool.items() if k != "populated"}
+        if host_out is None:
+            return out
+        n = out["rew"].shape[0]
+        for k, v in out.items():
+            h = host_out.get(k)
+            if h is None or h.shape[0] < n:
+                h = torch.empty((max(n, 1),) + tuple(v.shape[1:]), dtype=v.dtype, pin_memory=True)
+                host_out[k] = h
+            h[:n].copy_(v, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        host_out["_n"] = n
+        return host_out
 
     def get(self, numpy=False):
         out = dict(self.pool)

@@ -149,9 +149,9 @@ typedef struct cmbpo_rollout_io {
   int64_t n_paths;             /* B: rows at reset, bounds every grid */
   int32_t max_path_length;     /* T (modelbuffer.py:19); a path ends when length >= T-1 (model_sampler.py:437) */
   int32_t mode;
-  float dkl_lim;               /* model_sampler.py:179 set_rollout_dkl */
+  double dkl_lim;              /* model_sampler.py:179 set_rollout_dkl (a Python float upstream) */
   int64_t max_samples;         /* 0 = None (model_sampler.py:327) */
-  int32_t step_index;          /* informational */
+  int32_t step_index;          /* sampler step t: slot of alive_hist_dev written by this call */
   int32_t obs_dim, act_dim;
   const float* cur_obs_dev;    /* [n_alive][obs] */
   const float* act_dev;        /* [n_alive][act] */
@@ -163,13 +163,14 @@ typedef struct cmbpo_rollout_io {
   const float* ep_var_mean_dev;/* [n_alive] or NULL */
   const int32_t* path_id_dev;  /* [n_alive] original path of each alive row */
   void* state_dev;             /* cmbpo_rollout_state */
-  float* dkl_accum_dev;        /* [B] _dyn_dkl_path (model_sampler.py:240,:415) */
+  double* dkl_accum_dev;       /* [B] _dyn_dkl_path: np.zeros => float64 upstream (model_sampler.py:244,:415) */
   float* pool_obs_dev; float* pool_act_dev; float* pool_next_obs_dev;   /* [B][T][dim] */
   float* pool_rew_dev; float* pool_cost_dev; uint8_t* pool_term_dev;    /* [B][T] */
   float* pool_dyn_error_dev; uint8_t* pool_populated_dev;               /* [B][T] */
   float* new_obs_dev;          /* [n_alive'][obs] compacted survivors */
   int32_t* new_path_id_dev;    /* [n_alive'] */
   void* scratch_dev; size_t scratch_bytes;   /* >= cmbpo_rollout_scratch_bytes(n_paths) */
+  int32_t* alive_hist_dev;     /* optional [T]: rows alive when step `step_index` began (diagnostics / FLOP accounting) */
 } cmbpo_rollout_io;
 size_t cmbpo_rollout_scratch_bytes(int64_t n_paths);
 int cmbpo_rollout_advance(const cmbpo_rollout_io* io, void* stream);
@@ -178,6 +179,12 @@ int cmbpo_rollout_advance(const cmbpo_rollout_io* io, void* stream);
  * for policy.get_action_outs, model_sampler.py:275, in throughput runs) */
 int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* act_dev, const void* n_rows_dev,
                       int64_t n_rows, int32_t obs_dim, int32_t act_dim, void* stream);
+
+/* Measurement aid (no reference counterpart): while enabled, every ensemble-forward launch of this
+ * handle is bracketed by CUDA events on its stream; cmbpo_profile_read waits for them, returns the
+ * summed kernel time and the launch count, and clears the list.  Not usable under graph capture. */
+int cmbpo_profile(void* handle, int enable);
+int cmbpo_profile_read(void* handle, double* fwd_ms_total, int64_t* fwd_launches);
 
 /* watchdog word of the last launches on this handle (0 = clean), synchronises the stream */
 int cmbpo_status(void* handle, void* stream);

@@ -155,7 +155,7 @@ def fc_forward(x, W, b, activation):
     """2-D input: einsum('ij,ajk->aik') (fc.py:105-106); 3-D input with leading E:
     batched matmul (fc.py:107-108); anything else raises (fc.py:110-111)."""
     if x.ndim == 2:
-        raw = np.einsum("ij,ajk->aik", x, W) + b
+        raw = np.matmul(x, W) + b  # == einsum("ij,ajk->aik"), BLAS-backed
     elif x.ndim == 3 and x.shape[0] == W.shape[0]:
         raw = np.matmul(x, W) + b
     else:
@@ -416,7 +416,7 @@ def fake_env_step(p: EnsembleParams, env: str, obs, act, elite_idx=None, perm=No
 # --------------------------------------------------------------------------------------
 def rollout(p: EnsembleParams, env: str, start_obs, policy, max_path_length, rollout_mode,
             dkl_lim=None, max_samples=None, elite_idx_fn=None, cares_about_cost=False,
-            max_steps=None):
+            max_steps=None, step_fn=None, trace=None):
     """Restatement of the loop ``CMBPO._train`` runs (cmbpo.py:335-348): ``sampler.reset`` then
     ``sampler.sample`` until no path is alive, restricted to what the hot path owns: the
     step, the DKL-accumulate cutoff (:311-313), the ``max_samples`` early termination
@@ -425,6 +425,10 @@ def rollout(p: EnsembleParams, env: str, start_obs, policy, max_path_length, rol
     GAE are out of scope and not modelled.
 
     ``policy(obs) -> act`` and ``elite_idx_fn(step, n_alive) -> int[n_alive]`` are injected.
+    ``step_fn(cur, act, step) -> (next_obs, rew, term, info)`` replaces ``fake_env_step`` when
+    given (teacher-forced bookkeeping tests replay recorded step outputs through it; the CPU
+    baseline plugs its BLAS-backed step in).  ``trace``: optional list that receives the number of
+    alive rows at the start of every sampler step.
     2-D modes only ('schedule' / 'uncertainty'); returns the pool arrays.
     """
     assert rollout_mode in ("schedule", "uncertainty")
@@ -456,9 +460,14 @@ def rollout(p: EnsembleParams, env: str, start_obs, policy, max_path_length, rol
         if act_dim is None:
             act_dim = a.shape[-1]
             pool["act"] = np.zeros((B, T, act_dim), np.float32)
-        eidx = elite_idx_fn(step, n_alive)
-        next_obs, rew, term, info = fake_env_step(p, env, cur, a, elite_idx=eidx,
-                                                  cares_about_cost=cares_about_cost)
+        if trace is not None:
+            trace.append(n_alive)
+        if step_fn is not None:
+            next_obs, rew, term, info = step_fn(cur, a, step)
+        else:
+            eidx = elite_idx_fn(step, n_alive)
+            next_obs, rew, term, info = fake_env_step(p, env, cur, a, elite_idx=eidx,
+                                                      cares_about_cost=cares_about_cost)
         rew = np.squeeze(rew, -1)
         c = np.squeeze(info["cost"], -1)
         term = np.squeeze(term, -1)

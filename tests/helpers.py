@@ -75,3 +75,58 @@ def build_cuda_env(p, env, hidden, cares_about_cost=False, seed=0):
 
 def out_scale(p):
     return orc.scaler_divisor(np.asarray(p.var_out, np.float64), p.sc_factor).reshape(-1)
+
+
+# ---- tolerances (BASELINE.json north_star: rtol 1e-2 for bf16 operands) -----------------------
+# The CUDA path feeds bf16 operands to the tensor cores with fp32 accumulation; the oracle is
+# fp64.  An output element y = out*s_out + mu_out is compared as
+#     |y_cuda - y_ref| <= RTOL * |y_ref| + ATOL_SCALE * s_out[d]
+# (s_out = the output scaler's divisor, i.e. the natural unit of head column d).
+RTOL_BF16 = 1e-2
+ATOL_SCALE_BF16 = 2e-2
+VAR_RTOL_BF16 = 5e-2      # variance = exp(logvar): an absolute logvar error e shows up as rel. error e
+
+
+def assert_means_close(got, ref, s_out, rtol=RTOL_BF16, atol_scale=ATOL_SCALE_BF16, what="mean"):
+    got = np.asarray(got, np.float64)
+    ref = np.asarray(ref, np.float64)
+    bound = rtol * np.abs(ref) + atol_scale * s_out
+    bad = np.abs(got - ref) > bound
+    frac = np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-30)
+    assert not bad.any(), (f"{what}: {int(bad.sum())}/{bad.size} elements outside rtol={rtol} atol={atol_scale}*s_out; "
+                           f"worst excess {(np.abs(got - ref) - bound).max():.3e}; relative Frobenius error {frac:.3e}")
+    return frac
+
+
+def near_threshold_rows(env, next_obs_ref, tol_abs):
+    """Rows whose termination / cost decision could flip under a perturbation of ``tol_abs`` (per
+    column, [obs]) of next_obs: distance of every tested quantity to its threshold (mbpo/static/*.py)."""
+    x = np.asarray(next_obs_ref, np.float64)
+    t = np.asarray(tol_abs, np.float64)
+    near = np.zeros(x.shape[:-1], bool)
+
+    t = np.broadcast_to(t, x.shape)
+
+    def band(col, thr, extra=1.0):
+        return np.abs(x[..., col] - thr) <= extra * t[..., col]
+    if env in ("ant", "antsafe"):
+        near |= band(0, 0.2) | band(0, 1.0)
+    if env == "antsafe":
+        zr = 1 - 2 * (x[..., 2] ** 2 + x[..., 3] ** 2)
+        dz = 4 * (np.abs(x[..., 2]) * t[..., 2] + np.abs(x[..., 3]) * t[..., 3]) + 2 * (t[..., 2] ** 2 + t[..., 3] ** 2)
+        near |= np.abs(zr + 0.7) <= dz
+        near |= np.abs(np.abs(x[..., -1]) - 3.2) <= t[..., -1]
+    if env.startswith("humanoid"):
+        near |= band(0, 1.0) | band(0, 2.0)
+        if env == "humanoidsafe":
+            near |= np.abs(np.abs(x[..., -1]) - 3.0) <= t[..., -1]
+    if env.startswith("hopper"):
+        near |= band(0, 0.7) | (np.abs(np.abs(x[..., 1]) - 0.2) <= t[..., 1])
+        near |= (np.abs(x[..., 1:] - 100.0) <= t[..., 1:]).any(-1)
+        if env == "hoppersafe":
+            near |= np.abs(np.abs(x[..., -1]) - 1.0) <= t[..., -1]
+    if env == "walker2d":
+        near |= band(0, 0.8) | band(0, 2.0) | band(1, -1.0) | band(1, 1.0)
+    if env == "halfcheetahsafe":
+        near |= np.abs(np.abs(x[..., -1] * 10) - 2.0) <= 10 * t[..., -1]
+    return near

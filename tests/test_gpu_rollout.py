@@ -1,0 +1,186 @@
+"""Device-resident rollout bookkeeping (model_sampler.py:311-332,:386-474; modelbuffer.py:130-173):
+integer / index work, so the bar is BIT-EXACT against the oracle.
+
+Free-running rollouts diverge between bf16 and fp64 arithmetic (errors compound over the horizon and
+flip cutoff decisions), so the bookkeeping is checked teacher-forced: the step outputs the CUDA path
+produced are recorded per sampler step and replayed through the oracle's sampler loop; every pool
+array, counter and accumulator must then match exactly.  The arithmetic of the step itself is covered
+by test_gpu_step.py."""
+import numpy as np
+import pytest
+
+from tests.helpers import build_cuda_env, make_inputs, make_params, orc
+
+pytestmark = pytest.mark.gpu
+HIDDEN = (200, 200, 200, 200)
+
+
+def _recorded_rollout(env, B, T, mode, dkl_lim=None, max_samples=None, cares_about_cost=True, seed=0):
+    import torch
+    import constrainedmbpo_b200 as cm
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)  # unfitted scalers: states stay O(1)
+    obs, _ = make_inputs(env, B)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=cares_about_cost, seed=seed)
+    pol = cm.StubPolicy(fe.obs_dim, fe.act_dim, device="cuda:0")
+    ro = cm.ModelRollout(fe, T, rollout_mode=mode, dkl_lim=dkl_lim, max_samples=max_samples)
+    ro.reset(obs)
+    rec = []
+    for t in range(T - 1):
+        n = int(ro.state[0].item())
+        if n == 0:
+            break
+        cur = ro.cur[ro.flip][:n].cpu().numpy().copy()
+        ro.step(pol)
+        o = ro._step_out
+        rec.append(dict(cur=cur, act=pol._act[:n].cpu().numpy().copy(),
+                        next_obs=o["next_obs"][:n].cpu().numpy().copy(), rew=o["rew"][:n].cpu().numpy().copy(),
+                        term=o["term"][:n].cpu().numpy().astype(bool), cost=o["cost"][:n].cpu().numpy().copy(),
+                        dkl=o["dkl_path"][:n].cpu().numpy().copy(), epv=o["ep_var_mean"][:n].cpu().numpy().copy()))
+    # a few extra steps after everything finished must be no-ops
+    for _ in range(2):
+        ro.step(pol)
+    return p, obs, ro, rec
+
+
+def _replay_through_oracle(p, env, obs, rec, T, mode, dkl_lim, max_samples):
+    k = {"i": 0}
+
+    def policy(cur):
+        r = rec[k["i"]]
+        assert np.array_equal(cur.astype(np.float32), r["cur"]), "compacted current observations differ"
+        return r["act"]
+
+    def step_fn(cur, a, step):
+        r = rec[k["i"]]
+        k["i"] += 1
+        D = cur.shape[1] + 1
+        info = {"cost": r["cost"], "ensemble_dkl_path": r["dkl"],
+                # the sampler stores mean_d(ep_var) (model_sampler.py:428); replay it as a constant row
+                "ensemble_ep_var": np.repeat(r["epv"][:, None], D, axis=1)}
+        return r["next_obs"], r["rew"], r["term"], info
+    return orc.rollout(p.astype(np.float32), env, obs, policy, T, mode, dkl_lim=dkl_lim, max_samples=max_samples,
+                       step_fn=step_fn)
+
+
+def _assert_pools_equal(ro, ref):
+    got = ro.get(numpy=True)
+    for k in ("obs", "act", "next_obs", "rew", "cost", "term", "populated"):
+        assert np.array_equal(got[k], ref[k]), f"pool[{k}] differs"
+    assert np.allclose(got["dyn_error"], ref["dyn_error"], rtol=1e-6, atol=0)  # mean of a repeated row
+    n_alive, ptr, total, finished = ro.counters()
+    assert total == ref["total_samples"] == int(ref["populated"].sum())
+    assert np.array_equal(got["dkl_accum"], ref["dkl_accum"])  # float64 accumulate, like np.zeros upstream
+    return total
+
+
+def test_schedule_mode_bookkeeping_bit_exact_and_q8_length():
+    """'schedule' mode: every path ends when its length reaches max_path_length-1 (quirk Q8)."""
+    env, B, T = "halfcheetah", 1500, 6
+    p, obs, ro, rec = _recorded_rollout(env, B, T, "schedule", cares_about_cost=False)
+    ref = _replay_through_oracle(p, env, obs, rec, T, "schedule", None, None)
+    total = _assert_pools_equal(ro, ref)
+    assert total == B * (T - 1)                         # halfcheetah never terminates
+    got = ro.get(numpy=True)
+    assert got["populated"][:, : T - 1].all() and not got["populated"][:, T - 1:].any()
+    assert ro.counters()[3] == 1
+
+
+def test_schedule_mode_with_terminals():
+    env, B, T = "antsafe", 2000, 8
+    p, obs, ro, rec = _recorded_rollout(env, B, T, "schedule")
+    ref = _replay_through_oracle(p, env, obs, rec, T, "schedule", None, None)
+    _assert_pools_equal(ro, ref)
+    got = ro.get(numpy=True)
+    # a path is populated on a prefix of columns and stops right after its terminal transition
+    pop = got["populated"]
+    assert (np.diff(pop.astype(int), axis=1) <= 0).all()
+    last = pop.sum(1) - 1
+    rows = np.where((last >= 0) & (last < T - 2))[0]
+    assert got["term"][rows, last[rows]].all()
+    assert len(rec) > 2 and rec[-1]["cur"].shape[0] < B   # some paths did terminate early
+
+
+def test_uncertainty_mode_bookkeeping_bit_exact():
+    """'uncertainty' mode: accumulated ensemble KL vs dkl_lim (model_sampler.py:311-313); the step that
+    crosses the limit is NOT stored."""
+    import constrainedmbpo_b200 as cm
+    env, B, T = "antsafe", 3000, 12
+    p0 = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    obs0, _ = make_inputs(env, 1000, seed=9)
+    fe0 = build_cuda_env(p0, env, HIDDEN)
+    lim = cm.compute_dynamics_dkl(fe0, cm.StubPolicy(29, 8), obs0, depth=3)
+    assert lim > 0
+    p, obs, ro, rec = _recorded_rollout(env, B, T, "uncertainty", dkl_lim=lim)
+    ref = _replay_through_oracle(p, env, obs, rec, T, "uncertainty", lim, None)
+    total = _assert_pools_equal(ro, ref)
+    got = ro.get(numpy=True)
+    assert 0 < total < B * (T - 1)
+    assert (got["dkl_accum"] < lim).all()               # accumulators only absorb stored steps
+    lens = got["populated"].sum(1)
+    assert lens.min() < lens.max()                      # the cutoff is per path
+
+
+def test_max_samples_early_termination():
+    """model_sampler.py:327-332: the first n still-certain rows are cut so total_samples lands on max_samples."""
+    env, B, T = "halfcheetah", 1000, 6
+    cap = 2300
+    p, obs, ro, rec = _recorded_rollout(env, B, T, "schedule", max_samples=cap, cares_about_cost=False)
+    ref = _replay_through_oracle(p, env, obs, rec, T, "schedule", None, cap)
+    total = _assert_pools_equal(ro, ref)
+    assert total == cap
+    got = ro.get(numpy=True)
+    # step 3 (0-based 2) had room for only 300 rows: the FIRST 700 alive rows were cut
+    assert not got["populated"][:700, 2].any() and got["populated"][700:, 2].all()
+
+
+def test_cuda_graph_replay_matches_eager():
+    import torch
+    import constrainedmbpo_b200 as cm
+    env, B, T = "antsafe", 5000, 10
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    obs, _ = make_inputs(env, B)
+    pol = cm.StubPolicy(29, 8)
+    res = []
+    for graph in (False, True):
+        fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True, seed=3)
+        ro = cm.ModelRollout(fe, T, rollout_mode="uncertainty", dkl_lim=0.5)
+        start = torch.from_numpy(obs).cuda()
+        if graph:
+            fe._rng_offset = 0
+            ro.capture(start, pol)   # eager warm-up rollout + capture: offsets 0..T-2 twice
+            ro.replay(); ro.replay()
+        else:
+            ro.reset(start); ro.run(pol)
+        torch.cuda.synchronize()
+        res.append((ro.get(numpy=True), ro.counters()))
+    (a, ca), (b, cb) = res
+    # Philox stream ids differ between the eager run (offsets 0..) and the captured one (offsets T-1..):
+    # compare structure-independent invariants plus exact equality of the draw-independent first step
+    assert np.array_equal(a["obs"][:, 0], b["obs"][:, 0]) and np.array_equal(a["act"][:, 0], b["act"][:, 0])
+    assert ca[3] == cb[3] == 1
+    assert cb[2] == int(b["populated"].sum())
+
+
+def test_full_size_schedule_rollout_properties():
+    """BASELINE configs[2] shape at full size (1M HalfCheetah start states, 'schedule'): size-independent
+    properties -- every path stores exactly T-1 transitions, chained (next_obs[t] == obs[t+1]), pool row b
+    column 0 holds start state b, rewards finite."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    env, B, T = "halfcheetah", 1_000_000, 5
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    fe = build_cuda_env(p, env, HIDDEN)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    start = torch.randn(B, 17, device="cuda", generator=g)
+    ro = cm.ModelRollout(fe, T, rollout_mode="schedule")
+    ro.reset(start)
+    ro.run(cm.StubPolicy(17, 6))
+    n_alive, ptr, total, finished = ro.counters()
+    assert (n_alive, ptr, total, finished) == (0, T - 1, B * (T - 1), 1)
+    pool = ro.pool
+    assert bool(pool["populated"][:, : T - 1].all()) and not bool(pool["populated"][:, T - 1].any())
+    assert torch.equal(pool["obs"][:, 0], start)
+    assert torch.equal(pool["next_obs"][:, : T - 2], pool["obs"][:, 1: T - 1])
+    assert bool(torch.isfinite(pool["rew"]).all())
+    hist = ro.alive_hist.cpu().numpy()
+    assert list(hist[: T - 1]) == [B] * (T - 1)
