@@ -269,7 +269,9 @@ extern "C" int cmbpo_predict(void* handle, const cmbpo_predict_io* io, void* str
   int rc = check_ready(h);
   if (rc) return rc;
   if (io->ndim != 2 && io->ndim != 3) return fail(CMBPO_ERR_ARG, "Invalid input dimension.");
-  if (io->n_rows < 0 || !io->mean_dev) return fail(CMBPO_ERR_ARG, "cmbpo_predict: bad rows/outputs");
+  if (io->n_rows < 0) return fail(CMBPO_ERR_ARG, "cmbpo_predict: negative row count");
+  if (io->n_rows == 0) return CMBPO_OK;   // empty batch: empty outputs, nothing to launch
+  if (!io->mean_dev) return fail(CMBPO_ERR_ARG, "cmbpo_predict: null output pointer");
   if (io->workspace_bytes < cmbpo_workspace_bytes(h, io->n_rows) || !io->workspace_dev)
     return fail(CMBPO_ERR_WORKSPACE, "cmbpo_predict: workspace too small");
   if (io->n_rows == 0) return CMBPO_OK;
@@ -298,6 +300,7 @@ extern "C" int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream_) 
   const ModelPlan& pl = h->plan;
   if (!pl.probabilistic) return fail(CMBPO_ERR_STATE, "cmbpo_step needs a probabilistic dynamics ensemble (fake_env.py:59)");
   if (io->ndim != 2 && io->ndim != 3) return fail(CMBPO_ERR_ARG, "obs/act must be 2-D or 3-D (fake_env.py:132-139)");
+  if (io->n_rows == 0) return CMBPO_OK;
   const int obs_dim = pl.D - 1, act_dim = pl.in_dim - obs_dim;
   if (act_dim < 0) return fail(CMBPO_ERR_ARG, "in_dim smaller than obs_dim");
   if (obs_dim > 64) return fail(CMBPO_ERR_UNSUPPORTED, "obs_dim > 64 not supported by the post-processing tile");

@@ -13,7 +13,12 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 HIDDEN = (200, 200, 200, 200)
 
 
-def _check_step(env, B=3000, cares_about_cost=True, elites=(0, 1, 2, 3, 4)):
+STATIC_COST = {"antsafe", "halfcheetahsafe", "humanoidsafe", "hoppersafe"}
+
+
+def _check_step(env, B=3000, cares_about_cost=None, elites=(0, 1, 2, 3, 4)):
+    if cares_about_cost is None:   # the CostNN branch (no static cost_f) is covered by test_step_costnn_path
+        cares_about_cost = env in STATIC_COST
     p = make_params(env, HIDDEN, elites=elites)
     obs, act = make_inputs(env, B)
     fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=cares_about_cost)
@@ -64,7 +69,8 @@ def test_step_duplicate_elites_injected():
     _check_step("halfcheetah", B=1000, elites=(3, 3, 6, 0, 3))
 
 
-def _zero_weight_env(env, cares_about_cost=True):
+def _zero_weight_env(env):
+    cares_about_cost = env in STATIC_COST
     """Ensemble with zero weights / biases and identity-like output scaler: next_obs == obs exactly, so
     the fused static functions see precisely the golden inputs."""
     p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
