@@ -1,6 +1,7 @@
 // cmbpo_abi.cu -- extern "C" surface of libcmbpo_b200.so (declared in include/cmbpo_b200.h).
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <utility>
@@ -249,6 +250,13 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   p.row_stride = row_stride_for(n_rows);
   p.heads = heads;
   p.status = h->status_dev;
+  static long long* trace_dev = nullptr;
+  const char* trace_path = getenv("CMBPO_TRACE");   // debug timeline of cluster 0 (see tools/trace_dump.py)
+  if (trace_path) {
+    if (!trace_dev) CU(cudaMalloc(&trace_dev, 4 * 2048 * sizeof(long long)), "cudaMalloc(trace)");
+    CU(cudaMemsetAsync(trace_dev, 0, 4 * 2048 * sizeof(long long), stream), "memset(trace)");
+    p.trace = trace_dev;
+  }
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   if (h->profiling) {
     CU(cudaEventCreate(&ev0), "cudaEventCreate");
@@ -259,6 +267,12 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   if (h->profiling) {
     CU(cudaEventRecord(ev1, stream), "cudaEventRecord");
     h->prof_events.emplace_back(ev0, ev1);
+  }
+  if (trace_path) {
+    std::vector<long long> host(4 * 2048);
+    CU(cudaStreamSynchronize(stream), "sync(trace)");
+    CU(cudaMemcpy(host.data(), trace_dev, host.size() * sizeof(long long), cudaMemcpyDeviceToHost), "memcpy(trace)");
+    if (FILE* f = fopen(trace_path, "wb")) { fwrite(host.data(), sizeof(long long), host.size(), f); fclose(f); }
   }
   return CMBPO_OK;
 }

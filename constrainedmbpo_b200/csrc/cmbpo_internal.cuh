@@ -58,6 +58,7 @@ struct FwdParams {
   long long row_stride;         // B stride of the head scratch (>= n_rows)
   float* heads;                 // out: [E][n_head][row_stride] scaled mean | shifted logvar
   int* status;                  // watchdog / error word
+  long long* trace;             // debug timeline (CMBPO_TRACE env), nullptr in production
 };
 
 }  // namespace cmbpo

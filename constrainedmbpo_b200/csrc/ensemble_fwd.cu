@@ -20,12 +20,14 @@
 //     A operand, chunk by chunk (mbarrier per 32 columns) while the epilogue is still running.
 //   * warp roles: 0 = weight loader, 1 = MMA issuer (leader CTA), 2 = TMEM alloc + peer->leader
 //     relay of weight arrivals, 3 = input stager (concat + scaler + bf16 + canonical smem
-//     layout), 4..7 = epilogue (one warp per TMEM lane quadrant).
+//     layout), 4..11 = epilogue (two warps per TMEM lane quadrant, alternating 32-column chunks).
 #include "cmbpo_internal.cuh"
 #include "sm100_ptx.cuh"
 
 namespace cmbpo {
 using namespace sm100;
+
+constexpr int kFwdThreads = 384;   // warps 0-3: loader / MMA issuer / alloc+relay / input stager; 4-11: epilogue
 
 struct SmemLayout {
   uint32_t off_a0, off_const, off_bar, off_tmem, total;
@@ -53,6 +55,15 @@ constexpr int BAR_A_READY = 24;          // [8] one per 32-column chunk
 enum WaitCode : int {
   WC_LOADER_EMPTY = 1, WC_RELAY_FULL = 2, WC_STAGER_EMPTY = 3, WC_MMA_WFULL = 4,
   WC_MMA_A0 = 5, WC_MMA_AREADY = 6, WC_EPI_DFULL = 7
+};
+
+// debug timeline: role r in [0,4) owns trace[r*2048 ..]; entries are (clock64, tag) pairs
+constexpr int kTraceSlots = 1024;
+struct Tracer {
+  long long* base; int n;
+  __device__ __forceinline__ void operator()(int tag) {
+    if (base && n < kTraceSlots) { base[2 * n] = clock64(); base[2 * n + 1] = tag; ++n; }
+  }
 };
 
 template <int ACT>
@@ -96,66 +107,56 @@ __device__ __forceinline__ void signal_chunk(uint32_t bar, int lane) {
   tmem_wait_st();
   tc_fence_before();
   __syncwarp();
-  if (lane == 0) mbar_arrive_cluster(bar, 0);
+  if (lane == 0) mbar_arrive_cluster_light(bar, 0);
 }
 
-// Hidden-layer epilogue for one warp (one TMEM lane quadrant): accumulator -> activation ->
-// bf16 -> same columns, signalling the MMA issuer per 32-column chunk.  Software pipelined:
-// the TMEM load of chunk c+1 is in flight while chunk c is converted, and chunk c-1 is
-// published just before chunk c is stored (its tcgen05.st has long completed by then).
+// Hidden-layer epilogue for one warp: accumulator -> activation -> bf16 -> same columns, signalling
+// the MMA issuer per 32-column chunk.  Two warps share each TMEM lane quadrant (`half` = 0/1 takes the
+// even / odd chunks) so that every SM sub-partition has two instruction streams: the MUFU.TANH ->
+// FFMA dependency stalls of one are filled by the other, and the XU pipe (16 tanh/clk/SM -- the
+// binding unit of this kernel) stays busy.  The TMEM load of the warp's next chunk is in flight while
+// the current one is converted.
 template <int ACT>
 __device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col,
-                                                uint32_t bar_a_ready0, int lane) {
-  const int nfull = npad >> 5;          // 32-wide chunks
-  const bool tail16 = (npad & 31) != 0;  // one 16-wide chunk at the end
-  const int nch = nfull + (tail16 ? 1 : 0);
+                                                uint32_t bar_a_ready0, int lane, int half, Tracer& tr) {
+  const int nfull = npad >> 5;                       // 32-wide chunks
+  const int nch = nfull + ((npad & 31) ? 1 : 0);     // + one 16-wide chunk at the end
   uint32_t ra[32], rb[32], o[16];
-  if (nfull > 0) tmem_ld32(d_addr, ra); else tmem_ld16_lo(d_addr, ra);
-  for (int c = 0; c < nch; c += 2) {
-    // ---- chunk c (registers ra)
+  auto load = [&](int c, uint32_t (&r)[32]) {
+    if (c < nfull) tmem_ld32(d_addr + 32 * c, r); else tmem_ld16_lo(d_addr + 32 * c, r);
+  };
+  auto finish = [&](int c, uint32_t (&r)[32]) {
+    if (c < nfull) { convert_chunk<ACT, 32>(r, o, 32 * c, ones_col); tmem_st16(d_addr + 16 * c, o); }
+    else { convert_chunk<ACT, 16>(r, o, 32 * c, ones_col); tmem_st8_lo(d_addr + 16 * c, o); }
+    signal_chunk(bar_a_ready0 + 8 * c, lane);
+  };
+  int c = half;
+  if (c < nch) load(c, ra);
+  for (; c < nch; c += 4) {
+    tr(300);
     tmem_wait_ld();
-    if (c + 1 < nch) {
-      if (c + 1 < nfull) tmem_ld32(d_addr + 32 * (c + 1), rb);
-      else tmem_ld16_lo(d_addr + 32 * (c + 1), rb);
-    }
-    if (c < nfull) {
-      convert_chunk<ACT, 32>(ra, o, 32 * c, ones_col);
-      if (c > 0) signal_chunk(bar_a_ready0 + 8 * (c - 1), lane);
-      tmem_st16(d_addr + 16 * c, o);
-    } else {
-      convert_chunk<ACT, 16>(ra, o, 32 * c, ones_col);
-      if (c > 0) signal_chunk(bar_a_ready0 + 8 * (c - 1), lane);
-      tmem_st8_lo(d_addr + 16 * c, o);
-    }
-    // ---- chunk c+1 (registers rb)
-    if (c + 1 < nch) {
+    if (c + 2 < nch) load(c + 2, rb);
+    finish(c, ra);
+    tr(302);
+    if (c + 2 < nch) {
       tmem_wait_ld();
-      if (c + 2 < nch) {
-        if (c + 2 < nfull) tmem_ld32(d_addr + 32 * (c + 2), ra);
-        else tmem_ld16_lo(d_addr + 32 * (c + 2), ra);
-      }
-      if (c + 1 < nfull) {
-        convert_chunk<ACT, 32>(rb, o, 32 * (c + 1), ones_col);
-        signal_chunk(bar_a_ready0 + 8 * c, lane);
-        tmem_st16(d_addr + 16 * (c + 1), o);
-      } else {
-        convert_chunk<ACT, 16>(rb, o, 32 * (c + 1), ones_col);
-        signal_chunk(bar_a_ready0 + 8 * c, lane);
-        tmem_st8_lo(d_addr + 16 * (c + 1), o);
-      }
+      if (c + 4 < nch) load(c + 4, ra);
+      finish(c + 2, rb);
     }
   }
-  signal_chunk(bar_a_ready0 + 8 * (nch - 1), lane);
 }
 
 // HACT = activation of every hidden layer (construct_model applies one `activation` to all of
 // them, constructor.py:57-60); a kernel template so each variant gets its own register allocation.
 template <int HACT>
-__global__ void __launch_bounds__(256, 1) ensemble_fwd_kernel(const __grid_constant__ FwdParams p) {
+__global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __grid_constant__ FwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const ModelPlan& pl = p.plan;
   const SmemLayout sl = make_smem_layout(pl);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  // warp index through a shuffle so the compiler knows it is warp-uniform: role branches stay
+  // convergent and the MMA operands live in uniform registers (no per-instruction R2UR waterfall)
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const uint32_t cta = cluster_ctarank();
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
@@ -201,7 +202,7 @@ __global__ void __launch_bounds__(256, 1) ensemble_fwd_kernel(const __grid_const
   __syncthreads();
   cluster_sync();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   // ---------------------------------------------------------------- roles
   if (warp == 0) {
@@ -214,7 +215,7 @@ __global__ void __launch_bounds__(256, 1) ensemble_fwd_kernel(const __grid_const
           const uint8_t* blk = p.wimg + (size_t)(member * 2 + (int)cta) * pl.blk_bytes;
           for (int l = 0; l < L; ++l) {
             const LayerPlan& lp = pl.layer[l];
-            if (unit > 0) mbar_wait(bar(BAR_W_EMPTY + l), (unit - 1) & 1, p.status, WC_LOADER_EMPTY);
+            if (unit > 0) mbar_wait_relaxed(bar(BAR_W_EMPTY + l), (unit - 1) & 1, p.status, WC_LOADER_EMPTY);
             mbar_arrive_expect_tx(bar(BAR_W_FULL + l), lp.bytes);
             bulk_g2s(smem_u32(smem + lp.smem_off), blk + lp.img_off, lp.bytes, bar(BAR_W_FULL + l));
           }
@@ -222,12 +223,15 @@ __global__ void __launch_bounds__(256, 1) ensemble_fwd_kernel(const __grid_const
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (leader CTA, one thread)
-    if (cta == 0 && lane == 0) {
+    // ===== MMA issuer (leader CTA).  The whole warp walks the loop convergently (all lanes wait on the
+    // barriers); only the tcgen05.mma / commit instructions are issued by one elected lane.
+    if (cta == 0) {
       uint32_t unit = 0, n = 0, stage = 0, ar_bits = 0;
+      Tracer tr{(p.trace && cluster_id == 0 && lane == 0) ? p.trace : nullptr, 0};
       for (int tile = cluster_id; tile < n_tiles; tile += n_clusters) {
         for (int e = 0; e < E; ++e, ++unit) {
           for (int l = 0; l < L; ++l, ++n) {
+            tr(100 + l);
             const LayerPlan& lp = pl.layer[l];
             const uint32_t d_col = (n & 1) * kRegionCols;
             const uint32_t a_col = ((n & 1) ^ 1) * kRegionCols;
@@ -236,17 +240,21 @@ __global__ void __launch_bounds__(256, 1) ensemble_fwd_kernel(const __grid_const
             const uint32_t sbo = (uint32_t)(lp.kpad >> 3) * 128u;
             const int ksteps = lp.kpad >> 4;
             mbar_wait_cluster(bar(BAR_W_FULL + l), unit & 1, p.status, WC_MMA_WFULL);
+            tr(110 + l);
             if (l == 0) {
               const uint32_t buf = stage & 1;
               if (p.per_slot_input || e == 0)
                 mbar_wait_cluster(bar(BAR_A0_FULL + buf), (stage >> 1) & 1, p.status, WC_MMA_A0);
               tc_fence_after();
               const uint32_t a_base = smem_u32(smem + sl.off_a0 + buf * pl.a0_bytes);
-              for (int j = 0; j < ksteps; ++j)
-                mma_bf16_ss<2>(tmem_base + d_col, make_smem_desc(a_base + j * 256, 128, sbo),
-                               make_smem_desc(b_base + j * 256, 128, sbo), idesc, j > 0);
+              if (elect_one()) {
+                for (int j = 0; j < ksteps; ++j)
+                  mma_bf16_ss<2>(tmem_base + d_col, make_smem_desc(a_base + j * 256, 128, sbo),
+                                 make_smem_desc(b_base + j * 256, 128, sbo), idesc, j > 0);
+              }
+              __syncwarp();
               if (p.per_slot_input || e == E - 1) {
-                mma_commit_2sm(bar(BAR_A0_EMPTY + buf), 0x3);
+                if (elect_one()) mma_commit_2sm(bar(BAR_A0_EMPTY + buf), 0x3);
                 ++stage;
               }
             } else {
@@ -255,14 +263,22 @@ __global__ void __launch_bounds__(256, 1) ensemble_fwd_kernel(const __grid_const
                 mbar_wait_cluster(bar(BAR_A_READY + c), (ar_bits >> c) & 1, p.status, WC_MMA_AREADY);
                 ar_bits ^= (1u << c);
                 tc_fence_after();
+                tr(120 + c);
                 const int j1 = min(2 * c + 2, ksteps);
-                for (int j = 2 * c; j < j1; ++j)
-                  mma_bf16_ts<2>(tmem_base + d_col, tmem_base + a_col + 8 * j,
-                                 make_smem_desc(b_base + j * 256, 128, sbo), idesc, j > 0);
+                if (elect_one()) {
+                  for (int j = 2 * c; j < j1; ++j)
+                    mma_bf16_ts<2>(tmem_base + d_col, tmem_base + a_col + 8 * j,
+                                   make_smem_desc(b_base + j * 256, 128, sbo), idesc, j > 0);
+                }
+                __syncwarp();
               }
             }
-            mma_commit_2sm(bar(BAR_W_EMPTY + l), 0x3);
-            mma_commit_2sm(bar(BAR_D_FULL), 0x3);
+            if (elect_one()) {
+              mma_commit_2sm(bar(BAR_W_EMPTY + l), 0x3);
+              mma_commit_2sm(bar(BAR_D_FULL), 0x3);
+            }
+            __syncwarp();
+            tr(130 + l);
           }
         }
       }
@@ -274,7 +290,7 @@ __global__ void __launch_bounds__(256, 1) ensemble_fwd_kernel(const __grid_const
       for (int tile = cluster_id; tile < n_tiles; tile += n_clusters)
         for (int e = 0; e < E; ++e, ++unit)
           for (int l = 0; l < L; ++l) {
-            mbar_wait(bar(BAR_W_FULL + l), unit & 1, p.status, WC_RELAY_FULL);
+            mbar_wait_relaxed(bar(BAR_W_FULL + l), unit & 1, p.status, WC_RELAY_FULL);
             mbar_arrive_cluster(bar(BAR_W_FULL + l), 0);
           }
     }
@@ -287,7 +303,7 @@ __global__ void __launch_bounds__(256, 1) ensemble_fwd_kernel(const __grid_const
       const int n_stage = p.per_slot_input ? E : 1;
       for (int e = 0; e < n_stage; ++e, ++stage) {
         const uint32_t buf = stage & 1;
-        if (stage >= 2) mbar_wait(bar(BAR_A0_EMPTY + buf), ((stage >> 1) + 1) & 1, p.status, WC_STAGER_EMPTY);
+        if (stage >= 2) mbar_wait_relaxed(bar(BAR_A0_EMPTY + buf), ((stage >> 1) + 1) & 1, p.status, WC_STAGER_EMPTY);
         uint8_t* a0 = smem + sl.off_a0 + buf * pl.a0_bytes;
         const int in_slot = p.per_slot_input ? p.input_of_slot[e] : 0;
         for (int i = 0; i < 4; ++i) {
@@ -319,28 +335,34 @@ __global__ void __launch_bounds__(256, 1) ensemble_fwd_kernel(const __grid_const
       }
     }
   } else {
-    // ===== epilogue warps 4..7: TMEM lane quadrant q
+    // ===== epilogue warps 4..11: TMEM lane quadrant q (the hardware ties a warp to lanes 32*(warp%4)..),
+    // column half `half`
     const int q = warp & 3;
+    const int half = (warp - 4) >> 2;
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int row_in_tile = q * 32 + lane;
     uint32_t n = 0;
+    Tracer tr{(p.trace && cluster_id == 0 && cta == 0 && warp == 4 && lane == 0) ? p.trace + 2 * kTraceSlots : nullptr, 0};
     for (int tile = cluster_id; tile < n_tiles; tile += n_clusters) {
       const long long grow = (long long)tile * (2 * kTileRows) + (long long)cta * kTileRows + row_in_tile;
       for (int e = 0; e < E; ++e) {
         for (int l = 0; l < L; ++l, ++n) {
           const LayerPlan& lp = pl.layer[l];
           const uint32_t d_addr = tmem_base + lane_base + (n & 1) * kRegionCols;
+          tr(200 + l);
           mbar_wait(bar(BAR_D_FULL), n & 1, p.status, WC_EPI_DFULL);
           tc_fence_after();
+          tr(210 + l);
           if (l < L - 1) {
             const int ones_col = lp.n_real;  // next layer's bias-carrier columns
             const uint32_t ar0 = bar(BAR_A_READY);
-            hidden_epilogue<HACT>(d_addr, lp.npad, ones_col, ar0, lane);
+            hidden_epilogue<HACT>(d_addr, lp.npad, ones_col, ar0, lane, half, tr);
+            tr(220 + l);
           } else {
             // head: inverse output scaler on the mean, 2*log(s) shift on the log-variance
             // (bnn.py:878-893); written as [slot][column][row] so the store is coalesced.
             float* out = p.heads + (size_t)e * pl.n_head * p.row_stride + grow;
-            for (int c0 = 0; c0 < lp.npad; c0 += 16) {
+            for (int c0 = 16 * half; c0 < lp.npad; c0 += 32) {
               uint32_t r[16];
               tmem_ld16(d_addr + c0, r);
               tmem_wait_ld();
@@ -427,7 +449,7 @@ static cudaError_t launch_fwd_variant(const FwdParams& p, int num_sms, cudaStrea
   if (!p.n_rows_dev && n_tiles < clusters) clusters = (int)(n_tiles > 0 ? n_tiles : 1);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(2 * clusters);
-  cfg.blockDim = dim3(256);
+  cfg.blockDim = dim3(kFwdThreads);
   cfg.dynamicSmemBytes = p.plan.smem_total;
   cfg.stream = stream;
   cudaLaunchAttribute at[1];

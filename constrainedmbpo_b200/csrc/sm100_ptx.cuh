@@ -69,6 +69,16 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank)
       "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
       ::"r"(bar), "r"(rank) : "memory");
 }
+// Same, with the default .release.cta semantics (what CUTLASS' ClusterBarrier::arrive(cta_id) emits).
+// Use when the data being published is TMEM / tcgen05 state ordered by tcgen05.fence + the barrier
+// itself: the .release.cluster form above costs a MEMBAR.ALL.GPU + CCTL.IVALL per arrive.
+__device__ __forceinline__ void mbar_arrive_cluster_light(uint32_t bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
+      ::"r"(bar), "r"(rank) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                : "memory");
@@ -105,10 +115,23 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* st
   if (status) { atomicExch(status, code | 0x40000000); __threadfence_system(); }
   __trap();
 }
+// Wait on a barrier whose arrivals may come from the peer CTA.  Deliberately the plain (.acquire.cta)
+// try_wait, as CUTLASS' ClusterBarrier::wait does: the data published through these barriers is TMEM /
+// tcgen05 state (ordered by tcgen05.fence::after_thread_sync) or shared memory consumed by the async
+// proxy, never generic-proxy global data, and the .acquire.cluster form costs a CCTL.IVALL (full L1
+// invalidate, ~300 cycles measured) on every successful wait.
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity, int* status,
                                                   int code) {
-  for (uint32_t it = 0; it < SM100_WAIT_LIMIT; ++it) {
-    if (mbar_try_wait_cluster(bar, parity)) return;
+  mbar_wait(bar, parity, status, code);
+}
+
+// Non-critical waits (producer roles that are a whole work unit ahead): poll with a sleep in between so
+// the polling thread does not take issue / XU slots from the epilogue warp on the same SM sub-partition.
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity, int* status, int code,
+                                                  uint32_t sleep_ns = 256) {
+  for (uint32_t it = 0; it < (SM100_WAIT_LIMIT >> 2); ++it) {
+    if (mbar_try_wait(bar, parity)) return;
+    __nanosleep(sleep_ns);
   }
   if (status) { atomicExch(status, code | 0x40000000); __threadfence_system(); }
   __trap();
