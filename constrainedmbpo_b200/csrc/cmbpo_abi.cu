@@ -11,7 +11,7 @@
 #include "step_post.cuh"
 
 namespace cmbpo {
-uint32_t fwd_smem_bytes(const ModelPlan& pl);
+bool plan_fwd_smem(ModelPlan& pl);
 cudaError_t pack_layer(const float* W, const float* b, uint8_t* img, int E, const LayerPlan& lp,
                        uint32_t blk_bytes, cudaStream_t stream);
 cudaError_t launch_ensemble_fwd(const FwdParams& p, int hidden_act, int num_sms, cudaStream_t stream);
@@ -91,7 +91,7 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
     lp.prescale = (lp.act == CMBPO_ACT_SWISH || lp.act == CMBPO_ACT_SIGMOID) ? 0.5f : 1.0f;
     if (lp.kpad > kRegionCols || lp.npad > kRegionCols) {
       delete h;
-      return fail(CMBPO_ERR_UNSUPPORTED, "layer wider than 254: outside the resident-weight kernel (TMEM ping-pong of 2x256 columns)");
+      return fail(CMBPO_ERR_UNSUPPORTED, "layer wider than 254: outside this kernel (one 256-column TMEM accumulator per row-tile stream)");
     }
     lp.bytes = (uint32_t)(lp.npad / 2) * lp.kpad * 2u;
     lp.smem_off = off;
@@ -104,13 +104,10 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
       delete h;
       return fail(CMBPO_ERR_UNSUPPORTED, "hidden layers must share one activation (constructor.py:57-60)");
     }
-  pl.w_smem_bytes = off;
   pl.blk_bytes = off;
-  pl.a0_bytes = (uint32_t)kTileRows * pl.layer[0].kpad * 2u;
-  pl.smem_total = fwd_smem_bytes(pl);
-  if (pl.smem_total > 227u * 1024u) {
+  if (!plan_fwd_smem(pl)) {
     delete h;
-    return fail(CMBPO_ERR_UNSUPPORTED, "ensemble member does not fit the 227 KB resident-weight budget of a CTA pair");
+    return fail(CMBPO_ERR_UNSUPPORTED, "layer shapes do not fit the 227 KB shared-memory budget (two activation tiles + a two-slot weight ring)");
   }
   CU(cudaSetDevice(device), "cudaSetDevice");
   cudaDeviceProp prop;
@@ -250,13 +247,6 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   p.row_stride = row_stride_for(n_rows);
   p.heads = heads;
   p.status = h->status_dev;
-  static long long* trace_dev = nullptr;
-  const char* trace_path = getenv("CMBPO_TRACE");   // debug timeline of cluster 0 (see tools/trace_dump.py)
-  if (trace_path) {
-    if (!trace_dev) CU(cudaMalloc(&trace_dev, 4 * 2048 * sizeof(long long)), "cudaMalloc(trace)");
-    CU(cudaMemsetAsync(trace_dev, 0, 4 * 2048 * sizeof(long long), stream), "memset(trace)");
-    p.trace = trace_dev;
-  }
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   if (h->profiling) {
     CU(cudaEventCreate(&ev0), "cudaEventCreate");
@@ -267,12 +257,6 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   if (h->profiling) {
     CU(cudaEventRecord(ev1, stream), "cudaEventRecord");
     h->prof_events.emplace_back(ev0, ev1);
-  }
-  if (trace_path) {
-    std::vector<long long> host(4 * 2048);
-    CU(cudaStreamSynchronize(stream), "sync(trace)");
-    CU(cudaMemcpy(host.data(), trace_dev, host.size() * sizeof(long long), cudaMemcpyDeviceToHost), "memcpy(trace)");
-    if (FILE* f = fopen(trace_path, "wb")) { fwrite(host.data(), sizeof(long long), host.size(), f); fclose(f); }
   }
   return CMBPO_OK;
 }

@@ -9,7 +9,8 @@ constexpr int kMaxLayers = 8;
 constexpr int kMaxSeg = 3;     // input row = concat of up to 3 segments (obs | act | next_obs)
 constexpr int kMaxMembers = 16;
 constexpr int kTileRows = 128;  // rows per CTA tile (= TMEM lanes)
-constexpr int kRegionCols = 256;  // two ping-pong accumulator regions of 256 TMEM columns
+constexpr int kRegionCols = 256;  // one 256-column TMEM accumulator region per row-tile stream (2 streams)
+constexpr int kMaxSlots = 8;      // weight ring slots
 
 enum Activation : int { ACT_NONE = 0, ACT_SWISH = 1, ACT_RELU = 2, ACT_TANH = 3, ACT_SIGMOID = 4 };
 
@@ -20,7 +21,7 @@ struct LayerPlan {
   int kpad, npad;       // kpad = roundup(k_real + 2, 16): two extra K rows carry the bias (hi+lo bf16)
   int act;              // Activation
   float prescale;       // 0.5 for swish/sigmoid (tanh form works on x/2), else 1
-  uint32_t smem_off;    // byte offset of the layer's slot inside the weight region of smem
+  uint32_t smem_off;    // (unused by the streaming kernel; layers go through the weight ring)
   uint32_t img_off;     // byte offset inside one (member, half) block of the packed image
   uint32_t bytes;       // (npad/2) * kpad * 2
 };
@@ -33,9 +34,12 @@ struct ModelPlan {
   int D;                // output dim per head
   int probabilistic;    // head split into mean | logvar (bnn.py:111-112, :190-191)
   LayerPlan layer[kMaxLayers];
-  uint32_t w_smem_bytes;  // sum of slot bytes
+  uint32_t w_smem_bytes;  // w_slots * slot_bytes
   uint32_t blk_bytes;     // bytes of one (member, half) image block
-  uint32_t a0_bytes;      // 128 * k0pad * 2
+  uint32_t a0_bytes;      // 128 * k0pad * 2: staged input tile of one stream
+  uint32_t a_bytes;       // 128 * max_l>=1(kpad_l) * 2: activation tile of one stream (0 if L == 1)
+  uint32_t slot_bytes;    // max_l(bytes_l) rounded up to 128: one weight ring slot
+  uint32_t w_slots;       // ring depth (2..kMaxSlots), as many as fit beside the activation tiles
   uint32_t smem_total;    // dynamic smem the forward kernel needs
 };
 
@@ -58,7 +62,6 @@ struct FwdParams {
   long long row_stride;         // B stride of the head scratch (>= n_rows)
   float* heads;                 // out: [E][n_head][row_stride] scaled mean | shifted logvar
   int* status;                  // watchdog / error word
-  long long* trace;             // debug timeline (CMBPO_TRACE env), nullptr in production
 };
 
 }  // namespace cmbpo

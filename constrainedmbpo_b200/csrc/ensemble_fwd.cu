@@ -7,63 +7,80 @@
 // kernels (step_post.cu) which need the log-variance anyway.
 //
 // Shape of the kernel (see DESIGN.md "K1"):
-//   * persistent CTA *pairs* (cluster of 2, tcgen05 cta_group::2).  A pair owns a 256-row
-//     super-tile; each CTA holds its own 128 rows (TMEM lanes) and HALF of every layer's
-//     weight matrix (N split), so one member's whole bf16 weight set (~150 KB per CTA at
-//     4x200) is resident in shared memory and refilled layer by layer by 1-D bulk async
-//     copies (TMA engine) as soon as the tensor pipe releases a slot.
-//   * activations never leave the SM: layer l's fp32 accumulator (TMEM) is read by the
-//     epilogue warps, bias is already in the GEMM (two extra K rows hold bias hi/lo against
-//     two constant-one A columns), swish is evaluated as g + g*tanh(g) on g = x/2 (weights are
-//     pre-scaled by 1/2, exact), and the bf16 result is written back IN PLACE over the
-//     accumulator's own columns, where the next layer's tcgen05.mma reads it as its TMEM
-//     A operand, chunk by chunk (mbarrier per 32 columns) while the epilogue is still running.
+//   * persistent CTA *pairs* (cluster of 2, tcgen05 cta_group::2, M = 256).  A pair works on TWO
+//     256-row tiles at a time ("streams" X and Y); each CTA holds 128 rows of each stream (TMEM
+//     lanes) and HALF of every layer's weight matrix (N split).
+//   * the two streams walk (member, layer) in lock-step and alternate on the two execution
+//     resources: while the epilogue warps turn stream X's accumulator into the next layer's bf16
+//     activations (MUFU.TANH bound), the tensor pipe runs the same layer for stream Y, and vice
+//     versa.  Each stream owns one 256-column fp32 TMEM accumulator and one bf16 activation tile in
+//     shared memory (canonical K-major core-matrix layout, the A operand of the next tcgen05.mma).
+//   * weights stream from L2 through a ring of layer-sized shared-memory slots (1-D bulk async
+//     copies, TMA engine); one fill serves both streams.
+//   * bias rides in the GEMM (two extra K rows hold bias hi/lo against two constant-one A columns);
+//     swish is evaluated as g + g*tanh(g) on g = x/2 (weights are pre-scaled by 1/2, exact).
 //   * warp roles: 0 = weight loader, 1 = MMA issuer (leader CTA), 2 = TMEM alloc + peer->leader
-//     relay of weight arrivals, 3 = input stager (concat + scaler + bf16 + canonical smem
-//     layout), 4..11 = epilogue (two warps per TMEM lane quadrant, alternating 32-column chunks).
+//     relay of weight arrivals, 3 / 12 = input stagers of stream X / Y (concat + scaler + bf16 +
+//     canonical layout), 4..11 = epilogue (two warps per TMEM lane quadrant, alternating chunks).
+//   * every tcgen05.mma of a stream is gated by the epilogue's completion of that stream's previous
+//     pass (A_READY), so no barrier ever has more than one phase outstanding.
 #include "cmbpo_internal.cuh"
 #include "sm100_ptx.cuh"
 
 namespace cmbpo {
 using namespace sm100;
 
-constexpr int kFwdThreads = 384;   // warps 0-3: loader / MMA issuer / alloc+relay / input stager; 4-11: epilogue
+constexpr int kFwdThreads = 416;   // 13 warps
+constexpr int kStagerYWarp = 12;
 
 struct SmemLayout {
-  uint32_t off_a0, off_const, off_bar, off_tmem, total;
+  uint32_t off_a, off_a0, off_const, off_bar, off_tmem, total;
 };
 __host__ __device__ inline SmemLayout make_smem_layout(const ModelPlan& pl) {
   SmemLayout s;
-  s.off_a0 = pl.w_smem_bytes;
+  s.off_a = pl.w_slots * pl.slot_bytes;
+  s.off_a0 = s.off_a + 2 * pl.a_bytes;
   s.off_const = s.off_a0 + 2 * pl.a0_bytes;
-  uint32_t nconst = 2u * pl.in_dim + 2u * pl.n_head;
+  uint32_t nconst = 2u * ((pl.in_dim + 3u) & ~3u) + 2u * ((pl.n_head + 15u) & ~15u);
   s.off_bar = (s.off_const + 4u * nconst + 15u) & ~15u;
-  s.off_tmem = s.off_bar + 40u * 8u;
+  s.off_tmem = s.off_bar + 32u * 8u;
   s.total = s.off_tmem + 16u;
   return s;
+}
+
+// Fills the shared-memory part of the plan (slot size, ring depth, tile sizes); false if even a
+// two-slot ring does not fit the 227 KB of a CTA.
+bool plan_fwd_smem(ModelPlan& pl) {
+  uint32_t slot = 0, kmax = 0;
+  for (int l = 0; l < pl.L; ++l) {
+    slot = pl.layer[l].bytes > slot ? pl.layer[l].bytes : slot;
+    if (l >= 1 && (uint32_t)pl.layer[l].kpad > kmax) kmax = pl.layer[l].kpad;
+  }
+  pl.slot_bytes = (slot + 127u) & ~127u;
+  pl.a_bytes = (uint32_t)kTileRows * kmax * 2u;
+  pl.a0_bytes = (uint32_t)kTileRows * pl.layer[0].kpad * 2u;
+  for (int s = kMaxSlots; s >= 2; --s) {
+    pl.w_slots = s;
+    pl.w_smem_bytes = s * pl.slot_bytes;
+    pl.smem_total = make_smem_layout(pl).total;
+    if (pl.smem_total <= 227u * 1024u) return true;
+  }
+  return false;
 }
 uint32_t fwd_smem_bytes(const ModelPlan& pl) { return make_smem_layout(pl).total; }
 
 // barrier indices inside the barrier block
-constexpr int BAR_W_FULL = 0;            // [kMaxLayers]
-constexpr int BAR_W_EMPTY = 8;           // [kMaxLayers]
-constexpr int BAR_A0_FULL = 16;          // [2]
+constexpr int BAR_W_FULL = 0;            // [kMaxSlots]
+constexpr int BAR_W_EMPTY = 8;           // [kMaxSlots]
+constexpr int BAR_A0_FULL = 16;          // [2 streams]
 constexpr int BAR_A0_EMPTY = 18;         // [2]
-constexpr int BAR_D_FULL = 20;           // [1]
-constexpr int BAR_A_READY = 24;          // [8] one per 32-column chunk
+constexpr int BAR_D_FULL = 20;           // [2]
+constexpr int BAR_A_READY = 22;          // [2]  epilogue finished a pass: D free, next A in smem
+constexpr int kNumBars = 24;
 
 enum WaitCode : int {
   WC_LOADER_EMPTY = 1, WC_RELAY_FULL = 2, WC_STAGER_EMPTY = 3, WC_MMA_WFULL = 4,
   WC_MMA_A0 = 5, WC_MMA_AREADY = 6, WC_EPI_DFULL = 7
-};
-
-// debug timeline: role r in [0,4) owns trace[r*2048 ..]; entries are (clock64, tag) pairs
-constexpr int kTraceSlots = 1024;
-struct Tracer {
-  long long* base; int n;
-  __device__ __forceinline__ void operator()(int tag) {
-    if (base && n < kTraceSlots) { base[2 * n] = clock64(); base[2 * n + 1] = tag; ++n; }
-  }
 };
 
 template <int ACT>
@@ -82,10 +99,15 @@ __device__ __forceinline__ float activate(float g) {
   }
 }
 
-// Convert one accumulator chunk (W fp32 columns starting at col0) to packed bf16 in registers.
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// Convert W (32 or 16) accumulator columns starting at col0 to bf16 and store them into this
+// thread's row of the next layer's A tile (one 16-byte store per 8-column core-matrix row).
 template <int ACT, int W>
-__device__ __forceinline__ void convert_chunk(const uint32_t (&r)[32], uint32_t (&o)[16], int col0,
-                                              int ones_col) {
+__device__ __forceinline__ void convert_store(const uint32_t (&r)[32], int col0, int ones_col, uint32_t a_row) {
+  uint32_t o[W / 2];
   if (ones_col >= col0 - 1 && ones_col < col0 + W) {
     // the chunk that holds the next layer's two bias-carrier columns (warp-uniform, once per layer)
 #pragma unroll
@@ -101,43 +123,34 @@ __device__ __forceinline__ void convert_chunk(const uint32_t (&r)[32], uint32_t 
     for (int i = 0; i < W / 2; ++i)
       o[i] = pack_bf16x2(activate<ACT>(__uint_as_float(r[2 * i])), activate<ACT>(__uint_as_float(r[2 * i + 1])));
   }
+  const uint32_t dst = a_row + (uint32_t)(col0 >> 3) * 128u;
+#pragma unroll
+  for (int g = 0; g < W / 8; ++g) sts128(dst + 128u * g, o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
 }
 
-__device__ __forceinline__ void signal_chunk(uint32_t bar, int lane) {
-  tmem_wait_st();
-  tc_fence_before();
-  __syncwarp();
-  if (lane == 0) mbar_arrive_cluster_light(bar, 0);
-}
-
-// Hidden-layer epilogue for one warp: accumulator -> activation -> bf16 -> same columns, signalling
-// the MMA issuer per 32-column chunk.  Two warps share each TMEM lane quadrant (`half` = 0/1 takes the
-// even / odd chunks) so that every SM sub-partition has two instruction streams: the MUFU.TANH ->
-// FFMA dependency stalls of one are filled by the other, and the XU pipe (16 tanh/clk/SM -- the
-// binding unit of this kernel) stays busy.  The TMEM load of the warp's next chunk is in flight while
-// the current one is converted.
+// Hidden-layer epilogue for one warp: accumulator (TMEM) -> activation -> bf16 -> A tile (smem).
+// Two warps share each TMEM lane quadrant (`half` = 0/1 takes the even / odd 32-column chunks) so
+// that every SM sub-partition has two instruction streams feeding the XU pipe (16 tanh/clk/SM -- the
+// binding unit of this kernel).  The TMEM load of the warp's next chunk is in flight while the current
+// one is converted.
 template <int ACT>
-__device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col,
-                                                uint32_t bar_a_ready0, int lane, int half, Tracer& tr) {
+__device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col, uint32_t a_row, int half) {
   const int nfull = npad >> 5;                       // 32-wide chunks
   const int nch = nfull + ((npad & 31) ? 1 : 0);     // + one 16-wide chunk at the end
-  uint32_t ra[32], rb[32], o[16];
+  uint32_t ra[32], rb[32];
   auto load = [&](int c, uint32_t (&r)[32]) {
     if (c < nfull) tmem_ld32(d_addr + 32 * c, r); else tmem_ld16_lo(d_addr + 32 * c, r);
   };
   auto finish = [&](int c, uint32_t (&r)[32]) {
-    if (c < nfull) { convert_chunk<ACT, 32>(r, o, 32 * c, ones_col); tmem_st16(d_addr + 16 * c, o); }
-    else { convert_chunk<ACT, 16>(r, o, 32 * c, ones_col); tmem_st8_lo(d_addr + 16 * c, o); }
-    signal_chunk(bar_a_ready0 + 8 * c, lane);
+    if (c < nfull) convert_store<ACT, 32>(r, 32 * c, ones_col, a_row);
+    else convert_store<ACT, 16>(r, 32 * c, ones_col, a_row);
   };
   int c = half;
   if (c < nch) load(c, ra);
   for (; c < nch; c += 4) {
-    tr(300);
     tmem_wait_ld();
     if (c + 2 < nch) load(c + 2, rb);
     finish(c, ra);
-    tr(302);
     if (c + 2 < nch) {
       tmem_wait_ld();
       if (c + 4 < nch) load(c + 4, ra);
@@ -145,6 +158,47 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int o
     }
   }
 }
+
+// Head epilogue for one warp: inverse output scaler on the mean, 2*log(s) shift on the log-variance
+// (bnn.py:878-893); written as [slot][column][row] so that a warp's store covers 32 consecutive rows.
+__device__ __forceinline__ void head_epilogue(uint32_t d_addr, int npad, int n_head, const float* s_scale,
+                                              const float* s_shift, float* out, long long row_stride,
+                                              bool live, int half) {
+  for (int c0 = 16 * half; c0 < npad; c0 += 32) {
+    uint32_t r[16];
+    tmem_ld16(d_addr + c0, r);
+    float* colp = out + (size_t)c0 * row_stride;
+    float sc[16], sh[16];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {   // the constant arrays are padded to a multiple of 16 floats
+      const float4 a = *reinterpret_cast<const float4*>(s_scale + c0 + 4 * i);
+      const float4 b = *reinterpret_cast<const float4*>(s_shift + c0 + 4 * i);
+      sc[4 * i] = a.x; sc[4 * i + 1] = a.y; sc[4 * i + 2] = a.z; sc[4 * i + 3] = a.w;
+      sh[4 * i] = b.x; sh[4 * i + 1] = b.y; sh[4 * i + 2] = b.z; sh[4 * i + 3] = b.w;
+    }
+    tmem_wait_ld();
+    if (live) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        if (c0 + i < n_head) *colp = fmaf(__uint_as_float(r[i]), sc[i], sh[i]);
+        colp += row_stride;
+      }
+    }
+  }
+}
+
+// Tile schedule shared by every role: cluster c owns 256-row tiles c, c+C, c+2C, ...; consecutive
+// tiles of that list form a pair (stream X, stream Y); the last pair may have no Y.
+struct PairIter {
+  int tile, step, n_tiles;
+  __device__ __forceinline__ PairIter(int cluster_id, int n_clusters, int n_tiles_)
+      : tile(cluster_id), step(n_clusters), n_tiles(n_tiles_) {}
+  __device__ __forceinline__ bool valid() const { return tile < n_tiles; }
+  __device__ __forceinline__ int x() const { return tile; }
+  __device__ __forceinline__ bool has_y() const { return tile + step < n_tiles; }
+  __device__ __forceinline__ int y() const { return tile + step; }
+  __device__ __forceinline__ void next() { tile += 2 * step; }
+};
 
 // HACT = activation of every hidden layer (construct_model applies one `activation` to all of
 // them, constructor.py:57-60); a kernel template so each variant gets its own register allocation.
@@ -162,37 +216,39 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
   const int n_tiles = (int)((n_rows + 2 * kTileRows - 1) / (2 * kTileRows));
   const int E = pl.E, L = pl.L;
+  const int S = (int)pl.w_slots;
 
+  const int in_pad4 = (pl.in_dim + 3) & ~3, head_pad16 = (pl.n_head + 15) & ~15;
   float* s_const = reinterpret_cast<float*>(smem + sl.off_const);
   float* s_in_mu = s_const;
-  float* s_in_inv = s_const + pl.in_dim;
-  float* s_head_scale = s_const + 2 * pl.in_dim;
-  float* s_head_shift = s_const + 2 * pl.in_dim + pl.n_head;
+  float* s_in_inv = s_const + in_pad4;
+  float* s_head_scale = s_const + 2 * in_pad4;
+  float* s_head_shift = s_const + 2 * in_pad4 + head_pad16;
   const uint32_t bar0 = smem_u32(smem + sl.off_bar);
   auto bar = [bar0](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + sl.off_tmem);
 
   // ---------------------------------------------------------------- setup
   if (tid == 0) {
-    for (int l = 0; l < kMaxLayers; ++l) {
-      mbar_init(bar(BAR_W_FULL + l), cta == 0 ? 2 : 1);
-      mbar_init(bar(BAR_W_EMPTY + l), 1);
-      mbar_init(bar(BAR_A_READY + l), 8);
+    for (int s = 0; s < kMaxSlots; ++s) {
+      mbar_init(bar(BAR_W_FULL + s), cta == 0 ? 2 : 1);   // leader: own fill + relayed peer fill
+      mbar_init(bar(BAR_W_EMPTY + s), 1);                 // tcgen05.commit
     }
-    for (int b = 0; b < 2; ++b) {
-      mbar_init(bar(BAR_A0_FULL + b), 2);
-      mbar_init(bar(BAR_A0_EMPTY + b), 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar(BAR_A0_FULL + s), 2);                 // one stager warp per CTA
+      mbar_init(bar(BAR_A0_EMPTY + s), 1);                // tcgen05.commit
+      mbar_init(bar(BAR_D_FULL + s), 1);                  // tcgen05.commit
+      mbar_init(bar(BAR_A_READY + s), 16);                // 8 epilogue warps x 2 CTAs
     }
-    mbar_init(bar(BAR_D_FULL), 1);
     fence_mbar_init();
   }
-  for (int i = tid; i < pl.in_dim; i += blockDim.x) {
-    s_in_mu[i] = p.in_mu ? p.in_mu[i] : 0.f;
-    s_in_inv[i] = p.in_inv ? p.in_inv[i] : 1.f;
+  for (int i = tid; i < in_pad4; i += blockDim.x) {
+    s_in_mu[i] = (p.in_mu && i < pl.in_dim) ? p.in_mu[i] : 0.f;
+    s_in_inv[i] = (p.in_inv && i < pl.in_dim) ? p.in_inv[i] : 1.f;
   }
-  for (int i = tid; i < pl.n_head; i += blockDim.x) {
-    s_head_scale[i] = p.head_scale ? p.head_scale[i] : 1.f;
-    s_head_shift[i] = p.head_shift ? p.head_shift[i] : 0.f;
+  for (int i = tid; i < head_pad16; i += blockDim.x) {
+    s_head_scale[i] = (p.head_scale && i < pl.n_head) ? p.head_scale[i] : 1.f;
+    s_head_shift[i] = (p.head_shift && i < pl.n_head) ? p.head_shift[i] : 0.f;
   }
   if (warp == 2) {
     tmem_alloc<2>(smem_u32(tmem_slot), 512);
@@ -206,18 +262,19 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
 
   // ---------------------------------------------------------------- roles
   if (warp == 0) {
-    // ===== weight loader: refill layer slot l with the next (tile, member) as soon as free
+    // ===== weight loader: layer n of the (pair, member, layer) walk goes to ring slot n % S
     if (lane == 0) {
-      uint32_t unit = 0;
-      for (int tile = cluster_id; tile < n_tiles; tile += n_clusters) {
-        for (int e = 0; e < E; ++e, ++unit) {
+      int slot = 0; uint32_t use = 0;
+      for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
+        for (int e = 0; e < E; ++e) {
           const int member = p.member_of_slot[e];
           const uint8_t* blk = p.wimg + (size_t)(member * 2 + (int)cta) * pl.blk_bytes;
           for (int l = 0; l < L; ++l) {
             const LayerPlan& lp = pl.layer[l];
-            if (unit > 0) mbar_wait_relaxed(bar(BAR_W_EMPTY + l), (unit - 1) & 1, p.status, WC_LOADER_EMPTY);
-            mbar_arrive_expect_tx(bar(BAR_W_FULL + l), lp.bytes);
-            bulk_g2s(smem_u32(smem + lp.smem_off), blk + lp.img_off, lp.bytes, bar(BAR_W_FULL + l));
+            if (use > 0) mbar_wait_relaxed(bar(BAR_W_EMPTY + slot), (use - 1) & 1, p.status, WC_LOADER_EMPTY, 64);
+            mbar_arrive_expect_tx(bar(BAR_W_FULL + slot), lp.bytes);
+            bulk_g2s(smem_u32(smem + (uint32_t)slot * pl.slot_bytes), blk + lp.img_off, lp.bytes, bar(BAR_W_FULL + slot));
+            if (++slot == S) { slot = 0; ++use; }
           }
         }
       }
@@ -226,85 +283,72 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
     // ===== MMA issuer (leader CTA).  The whole warp walks the loop convergently (all lanes wait on the
     // barriers); only the tcgen05.mma / commit instructions are issued by one elected lane.
     if (cta == 0) {
-      uint32_t unit = 0, n = 0, stage = 0, ar_bits = 0;
-      Tracer tr{(p.trace && cluster_id == 0 && lane == 0) ? p.trace : nullptr, 0};
-      for (int tile = cluster_id; tile < n_tiles; tile += n_clusters) {
-        for (int e = 0; e < E; ++e, ++unit) {
-          for (int l = 0; l < L; ++l, ++n) {
-            tr(100 + l);
+      int slot = 0; uint32_t use = 0;
+      uint32_t passes[2] = {0, 0}, stage[2] = {0, 0};
+      for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
+        const bool has_y = it.has_y();
+        for (int e = 0; e < E; ++e) {
+          const bool new_input = p.per_slot_input || e == 0;
+          const bool last_use = p.per_slot_input || e == E - 1;
+          for (int l = 0; l < L; ++l) {
             const LayerPlan& lp = pl.layer[l];
-            const uint32_t d_col = (n & 1) * kRegionCols;
-            const uint32_t a_col = ((n & 1) ^ 1) * kRegionCols;
             const uint32_t idesc = make_idesc(256, lp.npad, kFmtBF16);
-            const uint32_t b_base = smem_u32(smem + lp.smem_off);
+            const uint32_t b_base = smem_u32(smem + (uint32_t)slot * pl.slot_bytes);
             const uint32_t sbo = (uint32_t)(lp.kpad >> 3) * 128u;
             const int ksteps = lp.kpad >> 4;
-            mbar_wait_cluster(bar(BAR_W_FULL + l), unit & 1, p.status, WC_MMA_WFULL);
-            tr(110 + l);
-            if (l == 0) {
-              const uint32_t buf = stage & 1;
-              if (p.per_slot_input || e == 0)
-                mbar_wait_cluster(bar(BAR_A0_FULL + buf), (stage >> 1) & 1, p.status, WC_MMA_A0);
+            mbar_wait(bar(BAR_W_FULL + slot), use & 1, p.status, WC_MMA_WFULL);
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+              if (s == 1 && !has_y) continue;
+              if (passes[s] > 0) mbar_wait(bar(BAR_A_READY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
+              if (l == 0 && new_input) mbar_wait(bar(BAR_A0_FULL + s), stage[s] & 1, p.status, WC_MMA_A0);
               tc_fence_after();
-              const uint32_t a_base = smem_u32(smem + sl.off_a0 + buf * pl.a0_bytes);
+              const uint32_t a_base = (l == 0) ? smem_u32(smem + sl.off_a0 + s * pl.a0_bytes)
+                                               : smem_u32(smem + sl.off_a + s * pl.a_bytes);
+              const uint32_t d_tmem = tmem_base + s * kRegionCols;
               if (elect_one()) {
                 for (int j = 0; j < ksteps; ++j)
-                  mma_bf16_ss<2>(tmem_base + d_col, make_smem_desc(a_base + j * 256, 128, sbo),
+                  mma_bf16_ss<2>(d_tmem, make_smem_desc(a_base + j * 256, 128, sbo),
                                  make_smem_desc(b_base + j * 256, 128, sbo), idesc, j > 0);
+                mma_commit_2sm(bar(BAR_D_FULL + s), 0x3);
+                if (l == 0 && last_use) mma_commit_2sm(bar(BAR_A0_EMPTY + s), 0x3);
               }
               __syncwarp();
-              if (p.per_slot_input || e == E - 1) {
-                if (elect_one()) mma_commit_2sm(bar(BAR_A0_EMPTY + buf), 0x3);
-                ++stage;
-              }
-            } else {
-              const int nch = (lp.kpad + 31) >> 5;
-              for (int c = 0; c < nch; ++c) {
-                mbar_wait_cluster(bar(BAR_A_READY + c), (ar_bits >> c) & 1, p.status, WC_MMA_AREADY);
-                ar_bits ^= (1u << c);
-                tc_fence_after();
-                tr(120 + c);
-                const int j1 = min(2 * c + 2, ksteps);
-                if (elect_one()) {
-                  for (int j = 2 * c; j < j1; ++j)
-                    mma_bf16_ts<2>(tmem_base + d_col, tmem_base + a_col + 8 * j,
-                                   make_smem_desc(b_base + j * 256, 128, sbo), idesc, j > 0);
-                }
-                __syncwarp();
-              }
+              if (l == 0 && last_use) ++stage[s];
+              ++passes[s];
             }
-            if (elect_one()) {
-              mma_commit_2sm(bar(BAR_W_EMPTY + l), 0x3);
-              mma_commit_2sm(bar(BAR_D_FULL), 0x3);
-            }
+            if (elect_one()) mma_commit_2sm(bar(BAR_W_EMPTY + slot), 0x3);
             __syncwarp();
-            tr(130 + l);
+            if (++slot == S) { slot = 0; ++use; }
           }
         }
       }
     }
   } else if (warp == 2) {
-    // ===== relay (peer CTA): forward "my half of layer l has landed" to the leader's barrier
+    // ===== relay (peer CTA): forward "my half of this slot has landed" to the leader's barrier
     if (cta == 1 && lane == 0) {
-      uint32_t unit = 0;
-      for (int tile = cluster_id; tile < n_tiles; tile += n_clusters)
-        for (int e = 0; e < E; ++e, ++unit)
+      int slot = 0; uint32_t use = 0;
+      for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next())
+        for (int e = 0; e < E; ++e)
           for (int l = 0; l < L; ++l) {
-            mbar_wait_relaxed(bar(BAR_W_FULL + l), unit & 1, p.status, WC_RELAY_FULL);
-            mbar_arrive_cluster(bar(BAR_W_FULL + l), 0);
+            mbar_wait_relaxed(bar(BAR_W_FULL + slot), use & 1, p.status, WC_RELAY_FULL, 32);
+            mbar_arrive_cluster(bar(BAR_W_FULL + slot), 0);
+            if (++slot == S) { slot = 0; ++use; }
           }
     }
-  } else if (warp == 3) {
-    // ===== input stager: concat(segments) -> (x-mu)*inv -> bf16 -> canonical K-major smem tile
+  } else if (warp == 3 || warp == kStagerYWarp) {
+    // ===== input stager of one stream: concat(segments) -> (x-mu)*inv -> bf16 -> canonical K-major tile
+    const int s = (warp == 3) ? 0 : 1;
     const LayerPlan& l0 = pl.layer[0];
     const uint32_t sbo = (uint32_t)(l0.kpad >> 3) * 128u;
-    uint32_t stage = 0;
-    for (int tile = cluster_id; tile < n_tiles; tile += n_clusters) {
+    uint8_t* a0 = smem + sl.off_a0 + s * pl.a0_bytes;
+    uint32_t st = 0;
+    for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
+      if (s == 1 && !it.has_y()) continue;
+      const int tile = s ? it.y() : it.x();
       const int n_stage = p.per_slot_input ? E : 1;
-      for (int e = 0; e < n_stage; ++e, ++stage) {
-        const uint32_t buf = stage & 1;
-        if (stage >= 2) mbar_wait_relaxed(bar(BAR_A0_EMPTY + buf), ((stage >> 1) + 1) & 1, p.status, WC_STAGER_EMPTY);
-        uint8_t* a0 = smem + sl.off_a0 + buf * pl.a0_bytes;
+      for (int e = 0; e < n_stage; ++e, ++st) {
+        if (st > 0) mbar_wait_relaxed(bar(BAR_A0_EMPTY + s), (st - 1) & 1, p.status, WC_STAGER_EMPTY, 64);
         const int in_slot = p.per_slot_input ? p.input_of_slot[e] : 0;
         for (int i = 0; i < 4; ++i) {
           const int r = lane + 32 * i;
@@ -312,10 +356,11 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
           uint8_t* rowp = a0 + (uint32_t)(r >> 3) * sbo + (uint32_t)(r & 7) * 16u;
           const bool live = g < n_rows;
           int k = 0;
-          for (int s = 0; s < kMaxSeg; ++s) {
-            const int w = p.seg_width[s];
+          for (int sg = 0; sg < kMaxSeg; ++sg) {
+            const int w = p.seg_width[sg];
             if (w == 0) continue;
-            const float* src = p.seg_ptr[s] + (size_t)in_slot * p.seg_slot_stride[s] + (size_t)g * w;
+            const float* src = p.seg_ptr[sg] + (size_t)in_slot * p.seg_slot_stride[sg] + (size_t)g * w;
+#pragma unroll 4
             for (int kk = 0; kk < w; ++kk, ++k) {
               float x = live ? __ldg(src + kk) : 0.f;
               float xn = (x - s_in_mu[k]) * s_in_inv[k];
@@ -331,7 +376,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
         }
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(bar(BAR_A0_FULL + buf), 0);
+        if (lane == 0) mbar_arrive_cluster(bar(BAR_A0_FULL + s), 0);
       }
     }
   } else {
@@ -341,40 +386,37 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
     const int half = (warp - 4) >> 2;
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int row_in_tile = q * 32 + lane;
-    uint32_t n = 0;
-    Tracer tr{(p.trace && cluster_id == 0 && cta == 0 && warp == 4 && lane == 0) ? p.trace + 2 * kTraceSlots : nullptr, 0};
-    for (int tile = cluster_id; tile < n_tiles; tile += n_clusters) {
-      const long long grow = (long long)tile * (2 * kTileRows) + (long long)cta * kTileRows + row_in_tile;
+    uint32_t dphase[2] = {0, 0};
+    for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
+      const bool has_y = it.has_y();
+      long long grow[2];
+      grow[0] = (long long)it.x() * (2 * kTileRows) + (long long)cta * kTileRows + row_in_tile;
+      grow[1] = (long long)it.y() * (2 * kTileRows) + (long long)cta * kTileRows + row_in_tile;
       for (int e = 0; e < E; ++e) {
-        for (int l = 0; l < L; ++l, ++n) {
+        for (int l = 0; l < L; ++l) {
           const LayerPlan& lp = pl.layer[l];
-          const uint32_t d_addr = tmem_base + lane_base + (n & 1) * kRegionCols;
-          tr(200 + l);
-          mbar_wait(bar(BAR_D_FULL), n & 1, p.status, WC_EPI_DFULL);
-          tc_fence_after();
-          tr(210 + l);
-          if (l < L - 1) {
-            const int ones_col = lp.n_real;  // next layer's bias-carrier columns
-            const uint32_t ar0 = bar(BAR_A_READY);
-            hidden_epilogue<HACT>(d_addr, lp.npad, ones_col, ar0, lane, half, tr);
-            tr(220 + l);
-          } else {
-            // head: inverse output scaler on the mean, 2*log(s) shift on the log-variance
-            // (bnn.py:878-893); written as [slot][column][row] so the store is coalesced.
-            float* out = p.heads + (size_t)e * pl.n_head * p.row_stride + grow;
-            for (int c0 = 16 * half; c0 < lp.npad; c0 += 32) {
-              uint32_t r[16];
-              tmem_ld16(d_addr + c0, r);
-              tmem_wait_ld();
-              if (grow < n_rows) {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                  const int j = c0 + i;
-                  if (j < pl.n_head)
-                    out[(size_t)j * p.row_stride] = fmaf(__uint_as_float(r[i]), s_head_scale[j], s_head_shift[j]);
-                }
-              }
+          for (int s = 0; s < 2; ++s) {
+            if (s == 1 && !has_y) continue;
+            const uint32_t d_addr = tmem_base + lane_base + s * kRegionCols;
+            mbar_wait(bar(BAR_D_FULL + s), dphase[s] & 1, p.status, WC_EPI_DFULL);
+            ++dphase[s];
+            tc_fence_after();
+            if (l < L - 1) {
+              // next layer's A tile: row stride group = npad (= next kpad) * 16 bytes
+              const uint32_t a_row = smem_u32(smem + sl.off_a + s * pl.a_bytes) +
+                                     (uint32_t)(row_in_tile >> 3) * ((uint32_t)lp.npad * 16u) +
+                                     (uint32_t)(row_in_tile & 7) * 16u;
+              hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, a_row, half);
+              fence_proxy_async_smem();      // generic-proxy smem writes -> visible to tcgen05.mma
+            } else {
+              float* out = p.heads + (size_t)e * pl.n_head * p.row_stride + grow[s];
+              head_epilogue(d_addr, lp.npad, pl.n_head, s_head_scale, s_head_shift, out, p.row_stride,
+                            grow[s] < n_rows, half);
             }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster_light(bar(BAR_A_READY + s), 0);
           }
         }
       }
