@@ -19,5 +19,11 @@ build/umma_probe: tools/umma_probe.cu $(SRC)/sm100_ptx.cuh
 	@mkdir -p build
 	$(NVCC) $(ARCH) -O3 -lineinfo -std=c++17 -o $@ $<
 
+# debug build with the in-kernel timeline (CMBPO_LIB=build/libcmbpo_b200_trace.so CMBPO_TRACE_OUT=file ...)
+trace: build/libcmbpo_b200_trace.so
+build/libcmbpo_b200_trace.so: $(wildcard $(SRC)/*.cu) $(wildcard $(SRC)/*.cuh) include/cmbpo_b200.h
+	@mkdir -p build
+	$(NVCC) $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -DCMBPO_TRACE -shared -o $@ $(SRC)/ensemble_fwd.cu $(SRC)/step_post.cu $(SRC)/cmbpo_abi.cu $(SRC)/rollout_ops.cu -lcudart
+
 clean:
 	rm -rf build $(OUT)

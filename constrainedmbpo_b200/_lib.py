@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcmbpo_b200.so")
+# CMBPO_LIB: debug builds of the same ABI (e.g. build/libcmbpo_b200_trace.so, `make trace`)
+LIB_PATH = os.environ.get("CMBPO_LIB") or os.path.join(_HERE, "libcmbpo_b200.so")
 
 MAX_LAYERS = 8
 MAX_SEGMENTS = 3

@@ -199,7 +199,8 @@ extern "C" int cmbpo_set_elites(void* handle, const int32_t* elites, int32_t k, 
   return CMBPO_OK;
 }
 
-static inline long long row_stride_for(long long n_rows) { return (n_rows + 31) / 32 * 32; }
+// rows of the tile-major head scratch (cmbpo_internal.cuh head_index): whole 128-row blocks
+static inline long long row_stride_for(long long n_rows) { return (n_rows + kTileRows - 1) / kTileRows * kTileRows; }
 
 extern "C" size_t cmbpo_workspace_bytes(void* handle, int64_t max_rows) {
   Handle* h = static_cast<Handle*>(handle);
@@ -244,9 +245,17 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   }
   p.n_rows_dev = n_rows_dev;
   p.n_rows = n_rows;
-  p.row_stride = row_stride_for(n_rows);
   p.heads = heads;
   p.status = h->status_dev;
+#ifdef CMBPO_TRACE
+  static long long* trace_dev = nullptr;
+  const char* trace_path = getenv("CMBPO_TRACE_OUT");   // debug timeline of cluster 0 (tools/trace_report.py)
+  if (trace_path) {
+    if (!trace_dev) CU(cudaMalloc(&trace_dev, 4 * 4096 * sizeof(long long)), "cudaMalloc(trace)");
+    CU(cudaMemsetAsync(trace_dev, 0, 4 * 4096 * sizeof(long long), stream), "memset(trace)");
+    p.trace = trace_dev;
+  }
+#endif
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   if (h->profiling) {
     CU(cudaEventCreate(&ev0), "cudaEventCreate");
@@ -258,6 +267,14 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
     CU(cudaEventRecord(ev1, stream), "cudaEventRecord");
     h->prof_events.emplace_back(ev0, ev1);
   }
+#ifdef CMBPO_TRACE
+  if (trace_path) {
+    std::vector<long long> host(4 * 4096);
+    CU(cudaStreamSynchronize(stream), "sync(trace)");
+    CU(cudaMemcpy(host.data(), trace_dev, host.size() * sizeof(long long), cudaMemcpyDeviceToHost), "memcpy(trace)");
+    if (FILE* f = fopen(trace_path, "wb")) { fwrite(host.data(), sizeof(long long), host.size(), f); fclose(f); }
+  }
+#endif
   return CMBPO_OK;
 }
 

@@ -43,6 +43,13 @@ struct ModelPlan {
   uint32_t smem_total;    // dynamic smem the forward kernel needs
 };
 
+// Head scratch layout ("tile-major"): the rows are cut in blocks of kTileRows (one CTA tile); block b
+// holds [slot e][head column j][128 rows] contiguously, so a CTA's output for one (tile, member) is one
+// contiguous n_head*512-byte region and consumers still read 128 consecutive rows per column.
+__host__ __device__ inline size_t head_index(long long g, int e, int col, int E, int n_head) {
+  return (((size_t)(g >> 7) * E + e) * n_head + col) * (size_t)kTileRows + (size_t)(g & (kTileRows - 1));
+}
+
 // Arguments of one ensemble forward launch.
 struct FwdParams {
   ModelPlan plan;
@@ -59,9 +66,9 @@ struct FwdParams {
   int input_of_slot[kMaxMembers];   // input slot feeding output slot j (3-D only)
   const int* n_rows_dev;        // optional device scalar with the live row count (rollout loop)
   long long n_rows;             // row count if n_rows_dev == nullptr
-  long long row_stride;         // B stride of the head scratch (>= n_rows)
-  float* heads;                 // out: [E][n_head][row_stride] scaled mean | shifted logvar
+  float* heads;                 // out: tile-major head scratch (head_index), scaled mean | shifted logvar
   int* status;                  // watchdog / error word
+  long long* trace;             // debug timeline, only read by -DCMBPO_TRACE builds (tools/trace_fwd.cu)
 };
 
 }  // namespace cmbpo

@@ -10,18 +10,17 @@
 //   * persistent CTA *pairs* (cluster of 2, tcgen05 cta_group::2, M = 256).  A pair works on TWO
 //     256-row tiles at a time ("streams" X and Y); each CTA holds 128 rows of each stream (TMEM
 //     lanes) and HALF of every layer's weight matrix (N split).
-//   * the two streams walk (member, layer) in lock-step and alternate on the two execution
-//     resources: while the epilogue warps turn stream X's accumulator into the next layer's bf16
-//     activations (MUFU.TANH bound), the tensor pipe runs the same layer for stream Y, and vice
-//     versa.  Each stream owns one 256-column fp32 TMEM accumulator and one bf16 activation tile in
+//   * the two streams walk (member, layer) in lock-step, each with its own four epilogue warps: while
+//     stream X's accumulator is turned into the next layer's bf16 activations (MUFU.TANH bound), the
+//     tensor pipe runs the same layer for stream Y, and vice versa.  Each stream owns one 256-column fp32 TMEM accumulator and one bf16 activation tile in
 //     shared memory (canonical K-major core-matrix layout, the A operand of the next tcgen05.mma).
 //   * weights stream from L2 through a ring of layer-sized shared-memory slots (1-D bulk async
 //     copies, TMA engine); one fill serves both streams.
 //   * bias rides in the GEMM (two extra K rows hold bias hi/lo against two constant-one A columns);
 //     swish is evaluated as g + g*tanh(g) on g = x/2 (weights are pre-scaled by 1/2, exact).
-//   * warp roles: 0 = weight loader, 1 = MMA issuer (leader CTA), 2 = TMEM alloc + peer->leader
-//     relay of weight arrivals, 3 / 12 = input stagers of stream X / Y (concat + scaler + bf16 +
-//     canonical layout), 4..11 = epilogue (two warps per TMEM lane quadrant, alternating chunks).
+//   * warp roles: 0 = weight loader (+ peer->leader relay of weight arrivals), 1 = MMA issuer (leader
+//     CTA), 2 = TMEM alloc + input stager of stream Y, 3 = input stager of stream X (concat + scaler +
+//     bf16 + canonical layout), 4..7 / 8..11 = epilogue of stream X / Y (one warp per TMEM lane quadrant).
 //   * every tcgen05.mma of a stream is gated by the epilogue's completion of that stream's previous
 //     pass (A_READY), so no barrier ever has more than one phase outstanding.
 #include "cmbpo_internal.cuh"
@@ -30,8 +29,7 @@
 namespace cmbpo {
 using namespace sm100;
 
-constexpr int kFwdThreads = 416;   // 13 warps
-constexpr int kStagerYWarp = 12;
+constexpr int kFwdThreads = 384;   // 12 warps (a multiple of 4 warps: ptxas sizes registers for it)
 
 struct SmemLayout {
   uint32_t off_a, off_a0, off_const, off_bar, off_tmem, total;
@@ -78,6 +76,17 @@ constexpr int BAR_D_FULL = 20;           // [2]
 constexpr int BAR_A_READY = 22;          // [2]  epilogue finished a pass: D free, next A in smem
 constexpr int kNumBars = 24;
 
+// Debug timeline (compile with -DCMBPO_TRACE): cluster 0's MMA issuer and epilogue warp 4 (leader CTA)
+// append (clock64, tag) pairs to p.trace[role * 2 * kTraceSlots ..]; tools/trace_report.py prints it.
+constexpr int kTraceSlots = 2048;
+#ifdef CMBPO_TRACE
+#define TR_DECL(role, cond) long long* tr_base = ((cond) && p.trace) ? p.trace + (role) * 2 * kTraceSlots : nullptr; int tr_n = 0
+#define TR(tag) do { if (tr_base && tr_n < kTraceSlots) { tr_base[2 * tr_n] = clock64(); tr_base[2 * tr_n + 1] = (tag); ++tr_n; } } while (0)
+#else
+#define TR_DECL(role, cond)
+#define TR(tag)
+#endif
+
 enum WaitCode : int {
   WC_LOADER_EMPTY = 1, WC_RELAY_FULL = 2, WC_STAGER_EMPTY = 3, WC_MMA_WFULL = 4,
   WC_MMA_A0 = 5, WC_MMA_AREADY = 6, WC_EPI_DFULL = 7
@@ -106,35 +115,51 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 // Convert W (32 or 16) accumulator columns starting at col0 to bf16 and store them into this
 // thread's row of the next layer's A tile (one 16-byte store per 8-column core-matrix row).
 template <int ACT, int W>
-__device__ __forceinline__ void convert_store(const uint32_t (&r)[32], int col0, int ones_col, uint32_t a_row) {
+__device__ __forceinline__ void convert_store(const uint32_t (&r)[32], int col0, uint32_t a_row) {
   uint32_t o[W / 2];
-  if (ones_col >= col0 - 1 && ones_col < col0 + W) {
-    // the chunk that holds the next layer's two bias-carrier columns (warp-uniform, once per layer)
 #pragma unroll
-    for (int i = 0; i < W / 2; ++i) {
-      float a = activate<ACT>(__uint_as_float(r[2 * i]));
-      float b = activate<ACT>(__uint_as_float(r[2 * i + 1]));
-      if (col0 + 2 * i == ones_col || col0 + 2 * i == ones_col + 1) a = 1.0f;
-      if (col0 + 2 * i + 1 == ones_col || col0 + 2 * i + 1 == ones_col + 1) b = 1.0f;
-      o[i] = pack_bf16x2(a, b);
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < W / 2; ++i)
-      o[i] = pack_bf16x2(activate<ACT>(__uint_as_float(r[2 * i])), activate<ACT>(__uint_as_float(r[2 * i + 1])));
-  }
+  for (int i = 0; i < W / 2; ++i)
+    o[i] = pack_bf16x2(activate<ACT>(__uint_as_float(r[2 * i])), activate<ACT>(__uint_as_float(r[2 * i + 1])));
   const uint32_t dst = a_row + (uint32_t)(col0 >> 3) * 128u;
 #pragma unroll
   for (int g = 0; g < W / 8; ++g) sts128(dst + 128u * g, o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
 }
 
 // Hidden-layer epilogue for one warp: accumulator (TMEM) -> activation -> bf16 -> A tile (smem).
-// Two warps share each TMEM lane quadrant (`half` = 0/1 takes the even / odd 32-column chunks) so
-// that every SM sub-partition has two instruction streams feeding the XU pipe (16 tanh/clk/SM -- the
-// binding unit of this kernel).  The TMEM load of the warp's next chunk is in flight while the current
-// one is converted.
+// One warp per TMEM lane quadrant and stream converts the whole row (all chunks); the two warps that
+// share an SM sub-partition belong to DIFFERENT streams, so the pass boundary of one stream (arrive ->
+// MMA -> D_FULL -> first TMEM load) sits in the shadow of the other stream's conversion and the XU pipe
+// (16 tanh/clk/SM -- the binding unit of this kernel) stays fed.  NPAD is compile-time for the common
+// layer widths: the whole pass is then one straight-line block in which the TMEM load of the next
+// chunk, the address arithmetic and the shared-memory stores are scheduled between the MUFUs.
+template <int ACT, int NPAD>
+__device__ __forceinline__ void hidden_epilogue_t(uint32_t d_addr, uint32_t a_row) {
+  constexpr int NFULL = NPAD / 32;
+  constexpr int NCH = NFULL + ((NPAD % 32) ? 1 : 0);
+  uint32_t ra[32], rb[32];
+  auto load = [&](int c, uint32_t (&r)[32]) {
+    if (c < NFULL) tmem_ld32(d_addr + 32 * c, r); else tmem_ld16_lo(d_addr + 32 * c, r);
+  };
+  auto finish = [&](int c, uint32_t (&r)[32]) {
+    if (c < NFULL) convert_store<ACT, 32>(r, 32 * c, a_row); else convert_store<ACT, 16>(r, 32 * c, a_row);
+  };
+  load(0, ra);
+#pragma unroll
+  for (int c = 0; c < NCH; c += 2) {
+    tmem_wait_ld();
+    if (c + 1 < NCH) load(c + 1, rb);
+    finish(c, ra);
+    if (c + 1 < NCH) {
+      tmem_wait_ld();
+      if (c + 2 < NCH) load(c + 2, ra);
+      finish(c + 1, rb);
+    }
+  }
+}
+
+// Same for an arbitrary (runtime) layer width.
 template <int ACT>
-__device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col, uint32_t a_row, int half) {
+__device__ __forceinline__ void hidden_epilogue_any(uint32_t d_addr, int npad, uint32_t a_row) {
   const int nfull = npad >> 5;                       // 32-wide chunks
   const int nch = nfull + ((npad & 31) ? 1 : 0);     // + one 16-wide chunk at the end
   uint32_t ra[32], rb[32];
@@ -142,32 +167,49 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int o
     if (c < nfull) tmem_ld32(d_addr + 32 * c, r); else tmem_ld16_lo(d_addr + 32 * c, r);
   };
   auto finish = [&](int c, uint32_t (&r)[32]) {
-    if (c < nfull) convert_store<ACT, 32>(r, 32 * c, ones_col, a_row);
-    else convert_store<ACT, 16>(r, 32 * c, ones_col, a_row);
+    if (c < nfull) convert_store<ACT, 32>(r, 32 * c, a_row); else convert_store<ACT, 16>(r, 32 * c, a_row);
   };
-  int c = half;
-  if (c < nch) load(c, ra);
-  for (; c < nch; c += 4) {
+  load(0, ra);
+  for (int c = 0; c < nch; c += 2) {
     tmem_wait_ld();
-    if (c + 2 < nch) load(c + 2, rb);
+    if (c + 1 < nch) load(c + 1, rb);
     finish(c, ra);
-    if (c + 2 < nch) {
+    if (c + 1 < nch) {
       tmem_wait_ld();
-      if (c + 4 < nch) load(c + 4, ra);
-      finish(c + 2, rb);
+      if (c + 2 < nch) load(c + 2, ra);
+      finish(c + 1, rb);
     }
   }
 }
 
+// ones_col / ones_col+1 of the produced tile are the next layer's bias carriers (constant 1.0):
+// overwritten after the row's own stores.
+template <int ACT>
+__device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col, uint32_t a_row) {
+  switch (npad) {
+    case 208: hidden_epilogue_t<ACT, 208>(d_addr, a_row); break;   // hidden 200 (BASELINE configs)
+    case 224: hidden_epilogue_t<ACT, 224>(d_addr, a_row); break;   // hidden 220 (FakeEnv default)
+    case 144: hidden_epilogue_t<ACT, 144>(d_addr, a_row); break;   // hidden 128 (V / VC critics)
+    case 80:  hidden_epilogue_t<ACT, 80>(d_addr, a_row); break;    // hidden 64 (CostNN)
+    default:  hidden_epilogue_any<ACT>(d_addr, npad, a_row); break;
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int k = ones_col + j;
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(a_row + (uint32_t)(k >> 3) * 128u + (uint32_t)(k & 7) * 2u),
+                 "h"((uint16_t)0x3F80) : "memory");
+  }
+}
+
 // Head epilogue for one warp: inverse output scaler on the mean, 2*log(s) shift on the log-variance
-// (bnn.py:878-893); written as [slot][column][row] so that a warp's store covers 32 consecutive rows.
+// (bnn.py:878-893); `out` points at this thread's row inside the (tile block, member) region of the
+// tile-major scratch, column stride 128 floats: a warp's store covers 32 consecutive rows.
 __device__ __forceinline__ void head_epilogue(uint32_t d_addr, int npad, int n_head, const float* s_scale,
-                                              const float* s_shift, float* out, long long row_stride,
-                                              bool live, int half) {
-  for (int c0 = 16 * half; c0 < npad; c0 += 32) {
+                                              const float* s_shift, float* out, bool live) {
+  for (int c0 = 0; c0 < npad; c0 += 16) {
     uint32_t r[16];
     tmem_ld16(d_addr + c0, r);
-    float* colp = out + (size_t)c0 * row_stride;
+    float* colp = out + (size_t)c0 * kTileRows;
     float sc[16], sh[16];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {   // the constant arrays are padded to a multiple of 16 floats
@@ -179,10 +221,8 @@ __device__ __forceinline__ void head_epilogue(uint32_t d_addr, int npad, int n_h
     tmem_wait_ld();
     if (live) {
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        if (c0 + i < n_head) *colp = fmaf(__uint_as_float(r[i]), sc[i], sh[i]);
-        colp += row_stride;
-      }
+      for (int i = 0; i < 16; ++i)
+        if (c0 + i < n_head) colp[i * kTileRows] = fmaf(__uint_as_float(r[i]), sc[i], sh[i]);
     }
   }
 }
@@ -238,7 +278,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
       mbar_init(bar(BAR_A0_FULL + s), 2);                 // one stager warp per CTA
       mbar_init(bar(BAR_A0_EMPTY + s), 1);                // tcgen05.commit
       mbar_init(bar(BAR_D_FULL + s), 1);                  // tcgen05.commit
-      mbar_init(bar(BAR_A_READY + s), 16);                // 8 epilogue warps x 2 CTAs
+      mbar_init(bar(BAR_A_READY + s), 8);                 // 4 epilogue warps of the stream x 2 CTAs
     }
     fence_mbar_init();
   }
@@ -262,20 +302,37 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
 
   // ---------------------------------------------------------------- roles
   if (warp == 0) {
-    // ===== weight loader: layer n of the (pair, member, layer) walk goes to ring slot n % S
+    // ===== weight loader: layer n of the (pair, member, layer) walk goes to ring slot n % S.  In the
+    // peer CTA the same thread also relays "my half of slot s has landed" to the leader's barrier
+    // (the MMA issuer waits on the leader's W_FULL only), so it polls instead of blocking.
     if (lane == 0) {
-      int slot = 0; uint32_t use = 0;
-      for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
-        for (int e = 0; e < E; ++e) {
-          const int member = p.member_of_slot[e];
-          const uint8_t* blk = p.wimg + (size_t)(member * 2 + (int)cta) * pl.blk_bytes;
-          for (int l = 0; l < L; ++l) {
-            const LayerPlan& lp = pl.layer[l];
-            if (use > 0) mbar_wait_relaxed(bar(BAR_W_EMPTY + slot), (use - 1) & 1, p.status, WC_LOADER_EMPTY, 64);
-            mbar_arrive_expect_tx(bar(BAR_W_FULL + slot), lp.bytes);
-            bulk_g2s(smem_u32(smem + (uint32_t)slot * pl.slot_bytes), blk + lp.img_off, lp.bytes, bar(BAR_W_FULL + slot));
-            if (++slot == S) { slot = 0; ++use; }
-          }
+      long long n_pairs = 0;
+      for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) ++n_pairs;
+      const long long total = n_pairs * E * L;
+      long long fill_n = 0, relay_n = 0;
+      int f_slot = 0, f_e = 0, f_l = 0, r_slot = 0; uint32_t f_use = 0, r_use = 0;
+      uint32_t idle = 0;
+      while (fill_n < total || (cta == 1 && relay_n < total)) {
+        bool progress = false;
+        if (fill_n < total && (f_use == 0 || mbar_try_wait(bar(BAR_W_EMPTY + f_slot), (f_use - 1) & 1))) {
+          const LayerPlan& lp = pl.layer[f_l];
+          const uint8_t* blk = p.wimg + (size_t)(p.member_of_slot[f_e] * 2 + (int)cta) * pl.blk_bytes;
+          mbar_arrive_expect_tx(bar(BAR_W_FULL + f_slot), lp.bytes);
+          bulk_g2s(smem_u32(smem + (uint32_t)f_slot * pl.slot_bytes), blk + lp.img_off, lp.bytes, bar(BAR_W_FULL + f_slot));
+          if (++f_l == L) { f_l = 0; if (++f_e == E) f_e = 0; }
+          if (++f_slot == S) { f_slot = 0; ++f_use; }
+          ++fill_n; progress = true;
+        }
+        if (cta == 1 && relay_n < fill_n && mbar_try_wait(bar(BAR_W_FULL + r_slot), r_use & 1)) {
+          mbar_arrive_cluster(bar(BAR_W_FULL + r_slot), 0);
+          if (++r_slot == S) { r_slot = 0; ++r_use; }
+          ++relay_n; progress = true;
+        }
+        if (progress) { idle = 0; continue; }
+        __nanosleep(32);
+        if (++idle > (SM100_WAIT_LIMIT >> 2)) {
+          if (p.status) { atomicExch(p.status, WC_LOADER_EMPTY | 0x40000000); __threadfence_system(); }
+          __trap();
         }
       }
     }
@@ -285,6 +342,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
     if (cta == 0) {
       int slot = 0; uint32_t use = 0;
       uint32_t passes[2] = {0, 0}, stage[2] = {0, 0};
+      TR_DECL(0, cluster_id == 0 && lane == 0);
       for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
         const bool has_y = it.has_y();
         for (int e = 0; e < E; ++e) {
@@ -296,13 +354,16 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
             const uint32_t b_base = smem_u32(smem + (uint32_t)slot * pl.slot_bytes);
             const uint32_t sbo = (uint32_t)(lp.kpad >> 3) * 128u;
             const int ksteps = lp.kpad >> 4;
+            TR(100 + l);
             mbar_wait(bar(BAR_W_FULL + slot), use & 1, p.status, WC_MMA_WFULL);
 #pragma unroll
             for (int s = 0; s < 2; ++s) {
               if (s == 1 && !has_y) continue;
+              TR(110 + 10 * s + l);
               if (passes[s] > 0) mbar_wait(bar(BAR_A_READY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
               if (l == 0 && new_input) mbar_wait(bar(BAR_A0_FULL + s), stage[s] & 1, p.status, WC_MMA_A0);
               tc_fence_after();
+              TR(130 + 10 * s + l);
               const uint32_t a_base = (l == 0) ? smem_u32(smem + sl.off_a0 + s * pl.a0_bytes)
                                                : smem_u32(smem + sl.off_a + s * pl.a_bytes);
               const uint32_t d_tmem = tmem_base + s * kRegionCols;
@@ -314,6 +375,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
                 if (l == 0 && last_use) mma_commit_2sm(bar(BAR_A0_EMPTY + s), 0x3);
               }
               __syncwarp();
+              TR(150 + 10 * s + l);
               if (l == 0 && last_use) ++stage[s];
               ++passes[s];
             }
@@ -324,19 +386,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
         }
       }
     }
-  } else if (warp == 2) {
-    // ===== relay (peer CTA): forward "my half of this slot has landed" to the leader's barrier
-    if (cta == 1 && lane == 0) {
-      int slot = 0; uint32_t use = 0;
-      for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next())
-        for (int e = 0; e < E; ++e)
-          for (int l = 0; l < L; ++l) {
-            mbar_wait_relaxed(bar(BAR_W_FULL + slot), use & 1, p.status, WC_RELAY_FULL, 32);
-            mbar_arrive_cluster(bar(BAR_W_FULL + slot), 0);
-            if (++slot == S) { slot = 0; ++use; }
-          }
-    }
-  } else if (warp == 3 || warp == kStagerYWarp) {
+  } else if (warp == 2 || warp == 3) {
     // ===== input stager of one stream: concat(segments) -> (x-mu)*inv -> bf16 -> canonical K-major tile
     const int s = (warp == 3) ? 0 : 1;
     const LayerPlan& l0 = pl.layer[0];
@@ -380,44 +430,42 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
       }
     }
   } else {
-    // ===== epilogue warps 4..11: TMEM lane quadrant q (the hardware ties a warp to lanes 32*(warp%4)..),
-    // column half `half`
+    // ===== epilogue warps 4..11: TMEM lane quadrant q (the hardware ties a warp to lanes 32*(warp%4)..);
+    // warps 4..7 serve stream X, warps 8..11 stream Y
     const int q = warp & 3;
-    const int half = (warp - 4) >> 2;
+    const int s = (warp - 4) >> 2;
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int row_in_tile = q * 32 + lane;
-    uint32_t dphase[2] = {0, 0};
+    const uint32_t d_addr = tmem_base + lane_base + s * kRegionCols;
+    const uint32_t a_tile = smem_u32(smem + sl.off_a + s * pl.a_bytes) + (uint32_t)(row_in_tile & 7) * 16u;
+    uint32_t dphase = 0;
+    TR_DECL(1 + s, cluster_id == 0 && cta == 0 && q == 0 && lane == 0);
     for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
-      const bool has_y = it.has_y();
-      long long grow[2];
-      grow[0] = (long long)it.x() * (2 * kTileRows) + (long long)cta * kTileRows + row_in_tile;
-      grow[1] = (long long)it.y() * (2 * kTileRows) + (long long)cta * kTileRows + row_in_tile;
+      if (s == 1 && !it.has_y()) continue;
+      const int tile = s ? it.y() : it.x();
+      const long long blk = (long long)tile * 2 + cta;           // 128-row block of the head scratch
+      const bool live = blk * kTileRows + row_in_tile < n_rows;
       for (int e = 0; e < E; ++e) {
         for (int l = 0; l < L; ++l) {
           const LayerPlan& lp = pl.layer[l];
-#pragma unroll
-          for (int s = 0; s < 2; ++s) {
-            if (s == 1 && !has_y) continue;
-            const uint32_t d_addr = tmem_base + lane_base + s * kRegionCols;
-            mbar_wait(bar(BAR_D_FULL + s), dphase[s] & 1, p.status, WC_EPI_DFULL);
-            ++dphase[s];
-            tc_fence_after();
-            if (l < L - 1) {
-              // next layer's A tile: row stride group = npad (= next kpad) * 16 bytes
-              const uint32_t a_row = smem_u32(smem + sl.off_a + s * pl.a_bytes) +
-                                     (uint32_t)(row_in_tile >> 3) * ((uint32_t)lp.npad * 16u) +
-                                     (uint32_t)(row_in_tile & 7) * 16u;
-              hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, a_row, half);
-              fence_proxy_async_smem();      // generic-proxy smem writes -> visible to tcgen05.mma
-            } else {
-              float* out = p.heads + (size_t)e * pl.n_head * p.row_stride + grow[s];
-              head_epilogue(d_addr, lp.npad, pl.n_head, s_head_scale, s_head_shift, out, p.row_stride,
-                            grow[s] < n_rows, half);
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_cluster_light(bar(BAR_A_READY + s), 0);
+          TR(200 + l);
+          mbar_wait(bar(BAR_D_FULL + s), dphase & 1, p.status, WC_EPI_DFULL);
+          ++dphase;
+          tc_fence_after();
+          TR(220 + l);
+          if (l < L - 1) {
+            // next layer's A tile: 8-row group stride = npad (= next kpad) * 16 bytes
+            const uint32_t a_row = a_tile + (uint32_t)(row_in_tile >> 3) * ((uint32_t)lp.npad * 16u);
+            hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, a_row);
+            fence_proxy_async_smem();      // generic-proxy smem writes -> visible to tcgen05.mma
+          } else {
+            float* out = p.heads + ((size_t)(blk * E + e) * pl.n_head) * kTileRows + row_in_tile;
+            head_epilogue(d_addr, lp.npad, pl.n_head, s_head_scale, s_head_shift, out, live);
           }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster_light(bar(BAR_A_READY + s), 0);
+          TR(240 + l);
         }
       }
     }

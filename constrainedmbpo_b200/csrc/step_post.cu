@@ -2,7 +2,7 @@
 // after BNN.predict returns (mbpo/models/fake_env.py:156-222), plus the transposing
 // "finalize" used by the plain BNN.predict boundary.
 //
-// One thread per rollout row.  The heads arrive as [slot][column][row] (written coalesced by
+// One thread per rollout row.  The heads arrive tile-major (cmbpo_internal.cuh head_index; written coalesced by
 // ensemble_fwd.cu), so every load below is a fully coalesced 128-byte warp access.  Row-major
 // tensors (obs in, next_obs out) go through a shared-memory tile so global traffic stays
 // coalesced too.
@@ -201,9 +201,9 @@ __global__ void __launch_bounds__(128) step_post_kernel(const StepParams p) {
           const float o = (d < OD) ? tile[tid * OD + d] : 0.f;
 #pragma unroll
           for (int e = 0; e < E; ++e) {
-            const float* hm = p.heads + ((size_t)e * 2 * D + d) * p.row_stride + g;
+            const float* hm = p.heads + head_index(g, e, d, E, 2 * D);
             m[e] = hm[0];
-            lv[e] = hm[(size_t)D * p.row_stride];
+            lv[e] = hm[(size_t)D * kTileRows];
           }
           if (d < OD) {
             if (p.per_slot) {
@@ -313,7 +313,7 @@ __global__ void reduce_scalars_kernel(const float* partials, int n_blocks, const
   }
 }
 
-// BNN.predict boundary: [slot][column][row] heads -> mean[E][B][D], var[E][B][D] row-major
+// BNN.predict boundary: tile-major heads -> mean[E][B][D], var[E][B][D] row-major
 // (bnn.py:713-717); var = exp(logvar) (bnn.py:898).  Non-probabilistic: mean only.
 __global__ void finalize_predict_kernel(const float* __restrict__ heads, long long row_stride, long long n_rows,
                                         int E, int D, int probabilistic, float* mean, float* var) {
@@ -323,9 +323,9 @@ __global__ void finalize_predict_kernel(const float* __restrict__ heads, long lo
     const int d = (int)(i % D);
     const long long g = (i / D) % n_rows;
     const int e = (int)(i / ((long long)D * n_rows));
-    const float* h = heads + ((size_t)e * n_head + d) * row_stride + g;
+    const float* h = heads + head_index(g, e, d, E, n_head);
     mean[i] = h[0];
-    if (probabilistic && var) var[i] = __expf(h[(size_t)D * row_stride]);
+    if (probabilistic && var) var[i] = __expf(h[(size_t)D * kTileRows]);
   }
 }
 
@@ -340,16 +340,16 @@ __global__ void aggregate_predict_kernel(const float* __restrict__ heads, long l
     const int d = (int)(i % D);
     const long long g = i / D;
     float m = 0.f;
-    for (int e = 0; e < E; ++e) m += heads[((size_t)e * n_head + d) * row_stride + g];
+    for (int e = 0; e < E; ++e) m += heads[head_index(g, e, d, E, n_head)];
     m /= (float)E;
     mean[i] = m;
     if (var) {
       float s2 = 0.f, sv = 0.f;
       for (int e = 0; e < E; ++e) {
-        const float* h = heads + ((size_t)e * n_head + d) * row_stride + g;
+        const float* h = heads + head_index(g, e, d, E, n_head);
         const float t = h[0] - m;
         s2 = fmaf(t, t, s2);
-        if (probabilistic) sv += __expf(h[(size_t)D * row_stride]);
+        if (probabilistic) sv += __expf(h[(size_t)D * kTileRows]);
       }
       var[i] = (probabilistic ? sv / (float)E : 0.f) + s2 / (float)E;
     }

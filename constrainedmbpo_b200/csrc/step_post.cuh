@@ -12,8 +12,8 @@ enum EnvId : int {
 };
 
 struct StepParams {
-  const float* heads;        // [E][2D][row_stride]: scaled mean | shifted logvar (ensemble_fwd.cu)
-  long long row_stride;
+  const float* heads;        // tile-major [block][E][2D][128] scaled mean | shifted logvar (ensemble_fwd.cu)
+  long long row_stride;      // rows the scratch was sized for (multiple of 128)
   int D;                     // obs_dim + 1 (fake_env.py:58)
   int obs_dim;
   int per_slot;              // 1 = 3-D inputs: every member keeps its own trajectory (fake_env.py:164-165)
