@@ -112,6 +112,16 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
   asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
+// XU token between the two epilogue warps of one SM sub-partition (stream X's and stream Y's): named
+// barrier `id` completes when the waiting warp (bar.sync) and the signalling warp (bar.arrive) are both
+// in; a waiting warp is parked by the hardware and takes no issue slots.  id == 0: no token protocol.
+__device__ __forceinline__ void token_wait(int id) {
+  if (id) asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
+}
+__device__ __forceinline__ void token_pass(int id) {
+  if (id) asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory");
+}
+
 // Convert W (32 or 16) accumulator columns starting at col0 to bf16 and store them into this
 // thread's row of the next layer's A tile (one 16-byte store per 8-column core-matrix row).
 template <int ACT, int W>
@@ -133,7 +143,7 @@ __device__ __forceinline__ void convert_store(const uint32_t (&r)[32], int col0,
 // layer widths: the whole pass is then one straight-line block in which the TMEM load of the next
 // chunk, the address arithmetic and the shared-memory stores are scheduled between the MUFUs.
 template <int ACT, int NPAD>
-__device__ __forceinline__ void hidden_epilogue_t(uint32_t d_addr, uint32_t a_row) {
+__device__ __forceinline__ void hidden_epilogue_t(uint32_t d_addr, uint32_t a_row, int tok_wait, int tok_pass) {
   constexpr int NFULL = NPAD / 32;
   constexpr int NCH = NFULL + ((NPAD % 32) ? 1 : 0);
   uint32_t ra[32], rb[32];
@@ -144,9 +154,11 @@ __device__ __forceinline__ void hidden_epilogue_t(uint32_t d_addr, uint32_t a_ro
     if (c < NFULL) convert_store<ACT, 32>(r, 32 * c, a_row); else convert_store<ACT, 16>(r, 32 * c, a_row);
   };
   load(0, ra);
+  tmem_wait_ld();
+  token_wait(tok_wait);          // first chunk already in registers: the MUFUs start right at the hand-over
 #pragma unroll
   for (int c = 0; c < NCH; c += 2) {
-    tmem_wait_ld();
+    if (c > 0) tmem_wait_ld();
     if (c + 1 < NCH) load(c + 1, rb);
     finish(c, ra);
     if (c + 1 < NCH) {
@@ -155,11 +167,12 @@ __device__ __forceinline__ void hidden_epilogue_t(uint32_t d_addr, uint32_t a_ro
       finish(c + 1, rb);
     }
   }
+  token_pass(tok_pass);
 }
 
 // Same for an arbitrary (runtime) layer width.
 template <int ACT>
-__device__ __forceinline__ void hidden_epilogue_any(uint32_t d_addr, int npad, uint32_t a_row) {
+__device__ __forceinline__ void hidden_epilogue_any(uint32_t d_addr, int npad, uint32_t a_row, int tok_wait, int tok_pass) {
   const int nfull = npad >> 5;                       // 32-wide chunks
   const int nch = nfull + ((npad & 31) ? 1 : 0);     // + one 16-wide chunk at the end
   uint32_t ra[32], rb[32];
@@ -170,8 +183,10 @@ __device__ __forceinline__ void hidden_epilogue_any(uint32_t d_addr, int npad, u
     if (c < nfull) convert_store<ACT, 32>(r, 32 * c, a_row); else convert_store<ACT, 16>(r, 32 * c, a_row);
   };
   load(0, ra);
+  tmem_wait_ld();
+  token_wait(tok_wait);
   for (int c = 0; c < nch; c += 2) {
-    tmem_wait_ld();
+    if (c > 0) tmem_wait_ld();
     if (c + 1 < nch) load(c + 1, rb);
     finish(c, ra);
     if (c + 1 < nch) {
@@ -180,18 +195,20 @@ __device__ __forceinline__ void hidden_epilogue_any(uint32_t d_addr, int npad, u
       finish(c + 1, rb);
     }
   }
+  token_pass(tok_pass);
 }
 
 // ones_col / ones_col+1 of the produced tile are the next layer's bias carriers (constant 1.0):
 // overwritten after the row's own stores.
 template <int ACT>
-__device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col, uint32_t a_row) {
+__device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col, uint32_t a_row,
+                                                int tok_wait, int tok_pass) {
   switch (npad) {
-    case 208: hidden_epilogue_t<ACT, 208>(d_addr, a_row); break;   // hidden 200 (BASELINE configs)
-    case 224: hidden_epilogue_t<ACT, 224>(d_addr, a_row); break;   // hidden 220 (FakeEnv default)
-    case 144: hidden_epilogue_t<ACT, 144>(d_addr, a_row); break;   // hidden 128 (V / VC critics)
-    case 80:  hidden_epilogue_t<ACT, 80>(d_addr, a_row); break;    // hidden 64 (CostNN)
-    default:  hidden_epilogue_any<ACT>(d_addr, npad, a_row); break;
+    case 208: hidden_epilogue_t<ACT, 208>(d_addr, a_row, tok_wait, tok_pass); break;   // hidden 200 (BASELINE configs)
+    case 224: hidden_epilogue_t<ACT, 224>(d_addr, a_row, tok_wait, tok_pass); break;   // hidden 220 (FakeEnv default)
+    case 144: hidden_epilogue_t<ACT, 144>(d_addr, a_row, tok_wait, tok_pass); break;   // hidden 128 (V / VC critics)
+    case 80:  hidden_epilogue_t<ACT, 80>(d_addr, a_row, tok_wait, tok_pass); break;    // hidden 64 (CostNN)
+    default:  hidden_epilogue_any<ACT>(d_addr, npad, a_row, tok_wait, tok_pass); break;
   }
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
@@ -440,8 +457,16 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
     const uint32_t a_tile = smem_u32(smem + sl.off_a + s * pl.a_bytes) + (uint32_t)(row_in_tile & 7) * 16u;
     uint32_t dphase = 0;
     TR_DECL(1 + s, cluster_id == 0 && cta == 0 && q == 0 && lane == 0);
+    // XU token of this sub-partition: X waits on barrier 1+q / passes 5+q, Y the other way round.  Only
+    // pairs that have both streams use it (hidden passes alternate X, Y, X, Y ...); Y opens the game
+    // and keeps the token of its very last pass.
+    const int tok_mine = s ? 5 + q : 1 + q, tok_other = s ? 1 + q : 5 + q;
+    if (s == 1 && L > 1 && PairIter(cluster_id, n_clusters, n_tiles).has_y()) token_pass(tok_other);
     for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
       if (s == 1 && !it.has_y()) continue;
+      const bool use_tok = it.has_y();
+      PairIter nx = it; nx.next();
+      const bool last_tok_pair = !(nx.valid() && nx.has_y());
       const int tile = s ? it.y() : it.x();
       const long long blk = (long long)tile * 2 + cta;           // 128-row block of the head scratch
       const bool live = blk * kTileRows + row_in_tile < n_rows;
@@ -456,7 +481,9 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
           if (l < L - 1) {
             // next layer's A tile: 8-row group stride = npad (= next kpad) * 16 bytes
             const uint32_t a_row = a_tile + (uint32_t)(row_in_tile >> 3) * ((uint32_t)lp.npad * 16u);
-            hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, a_row);
+            const bool keep = s == 1 && last_tok_pair && e == E - 1 && l == L - 2;
+            hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, a_row, use_tok ? tok_mine : 0,
+                                  (use_tok && !keep) ? tok_other : 0);
             fence_proxy_async_smem();      // generic-proxy smem writes -> visible to tcgen05.mma
           } else {
             float* out = p.heads + ((size_t)(blk * E + e) * pl.n_head) * kTileRows + row_in_tile;
