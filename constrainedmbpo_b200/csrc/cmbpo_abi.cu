@@ -15,6 +15,7 @@ bool plan_fwd_smem(ModelPlan& pl);
 cudaError_t pack_layer(const float* W, const float* b, uint8_t* img, int E, const LayerPlan& lp,
                        uint32_t blk_bytes, cudaStream_t stream);
 cudaError_t launch_ensemble_fwd(const FwdParams& p, int hidden_act, int num_sms, cudaStream_t stream);
+cudaError_t launch_stage_inputs(const StageParams& p, int num_sms, cudaStream_t stream);
 }  // namespace cmbpo
 
 using namespace cmbpo;
@@ -202,13 +203,24 @@ extern "C" int cmbpo_set_elites(void* handle, const int32_t* elites, int32_t k, 
 // rows of the tile-major head scratch (cmbpo_internal.cuh head_index): whole 128-row blocks
 static inline long long row_stride_for(long long n_rows) { return (n_rows + kTileRows - 1) / kTileRows * kTileRows; }
 
+// workspace = head scratch | step_post partial sums | staged layer-0 tiles (E input slots)
+static size_t a0_slot_bytes(const Handle* h, long long rows) {
+  const long long rows_pad = (rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
+  return (size_t)rows_pad * h->plan.layer[0].kpad * 2u;
+}
+static size_t ws_partials_offset(const Handle* h, long long rows) {
+  return (size_t)h->plan.E * h->plan.n_head * row_stride_for(rows) * sizeof(float);
+}
+static size_t ws_a0_offset(const Handle* h, long long rows) {
+  const size_t o = ws_partials_offset(h, rows) + (size_t)step_post_blocks(rows, h->num_sms) * 4 * sizeof(float);
+  return (o + 255) & ~(size_t)255;
+}
+
 extern "C" size_t cmbpo_workspace_bytes(void* handle, int64_t max_rows) {
   Handle* h = static_cast<Handle*>(handle);
   if (!h || max_rows < 0) return 0;
   const ModelPlan& pl = h->plan;
-  const size_t heads = (size_t)pl.E * pl.n_head * row_stride_for(max_rows) * sizeof(float);
-  const size_t partials = (size_t)step_post_blocks(max_rows, h->num_sms) * 4 * sizeof(float);
-  return heads + partials + 256;
+  return ws_a0_offset(h, max_rows) + (size_t)pl.E * a0_slot_bytes(h, max_rows) + 256;
 }
 
 static int check_ready(Handle* h) {
@@ -224,18 +236,35 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   memset(&p, 0, sizeof(p));
   p.plan = pl;
   p.wimg = h->wimg;
-  p.in_mu = h->consts;
-  p.in_inv = h->consts + pl.in_dim;
   p.head_scale = h->consts + 2 * pl.in_dim;
   p.head_shift = h->consts + 2 * pl.in_dim + pl.n_head;
+  StageParams sp;
+  memset(&sp, 0, sizeof(sp));
   int wsum = 0;
   for (int s = 0; s < kMaxSeg; ++s) {
-    p.seg_ptr[s] = (s < nseg) ? seg[s] : nullptr;
-    p.seg_width[s] = (s < nseg && seg[s]) ? seg_width[s] : 0;
-    p.seg_slot_stride[s] = (ndim == 3) ? n_rows * (long long)p.seg_width[s] : 0;
-    wsum += p.seg_width[s];
+    sp.seg_ptr[s] = (s < nseg) ? seg[s] : nullptr;
+    sp.seg_width[s] = (s < nseg && seg[s]) ? seg_width[s] : 0;
+    sp.seg_slot_stride[s] = (ndim == 3) ? n_rows * (long long)sp.seg_width[s] : 0;
+    wsum += sp.seg_width[s];
   }
   if (wsum != pl.in_dim) return fail(CMBPO_ERR_ARG, "Invalid input dimension.");  // fc.py:111
+  // compact the segment list (a null middle segment would break the concat walk of the staging kernel)
+  for (int s = 0, d = 0; s < kMaxSeg; ++s)
+    if (sp.seg_width[s] > 0) {
+      if (d != s) {
+        sp.seg_ptr[d] = sp.seg_ptr[s]; sp.seg_width[d] = sp.seg_width[s]; sp.seg_slot_stride[d] = sp.seg_slot_stride[s];
+        sp.seg_ptr[s] = nullptr; sp.seg_width[s] = 0; sp.seg_slot_stride[s] = 0;
+      }
+      ++d;
+    }
+  sp.n_slots = (ndim == 3) ? pl.E : 1;
+  sp.in_dim = pl.in_dim; sp.kpad = pl.layer[0].kpad;
+  sp.in_mu = h->consts; sp.in_inv = h->consts + pl.in_dim;
+  sp.n_rows_dev = n_rows_dev; sp.n_rows = n_rows;
+  sp.slot_stride_bytes = (long long)a0_slot_bytes(h, n_rows);
+  sp.a0img = reinterpret_cast<uint8_t*>(heads) + ws_a0_offset(h, n_rows);
+  p.a0img = sp.a0img;
+  p.a0_slot_stride = sp.slot_stride_bytes;
   p.per_slot_input = (ndim == 3) ? 1 : 0;
   for (int e = 0; e < pl.E; ++e) {
     const int m = (ndim == 3 && perm) ? perm[e] : e;
@@ -256,6 +285,7 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
     p.trace = trace_dev;
   }
 #endif
+  CU(launch_stage_inputs(sp, h->num_sms, stream), "launch_stage_inputs");
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   if (h->profiling) {
     CU(cudaEventCreate(&ev0), "cudaEventCreate");
@@ -331,7 +361,7 @@ extern "C" int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream_) 
   CU(cudaSetDevice(h->device), "cudaSetDevice");
   float* heads = static_cast<float*>(io->workspace_dev);
   const long long stride = row_stride_for(io->n_rows);
-  float* partials = heads + (size_t)pl.E * pl.n_head * stride;
+  float* partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(heads) + ws_partials_offset(h, io->n_rows));
   const float* segs[CMBPO_MAX_SEGMENTS] = {io->obs_dev, io->act_dev, nullptr};
   const int32_t widths[CMBPO_MAX_SEGMENTS] = {obs_dim, act_dim, 0};
   rc = run_forward(h, segs, widths, 2, io->n_rows, io->n_rows_dev, io->ndim, io->perm, heads, stream);

@@ -50,17 +50,30 @@ __host__ __device__ inline size_t head_index(long long g, int e, int col, int E,
   return (((size_t)(g >> 7) * E + e) * n_head + col) * (size_t)kTileRows + (size_t)(g & (kTileRows - 1));
 }
 
+// Arguments of the input staging pass (K0): concat of the row segments -> input scaler -> bf16 ->
+// canonical K-major A tiles of layer 0, one a0_bytes block per (input slot, 128-row block).
+struct StageParams {
+  const float* seg_ptr[kMaxSeg];       // input segments; row-major [slots?][B][width]
+  int seg_width[kMaxSeg];
+  long long seg_slot_stride[kMaxSeg];  // elements between input slots (3-D input), else 0
+  int n_slots;                         // 1 (2-D input shared by all members) or E (3-D, fc.py:107-108)
+  int in_dim, kpad;
+  const float* in_mu;                  // [in_dim] scaler_in mean          (utils.py:161)
+  const float* in_inv;                 // [in_dim] 1 / max(sqrt(var)*sc, 1e-2)
+  const int* n_rows_dev;               // optional device scalar with the live row count
+  long long n_rows;
+  long long slot_stride_bytes;         // bytes between input slots of the image
+  uint8_t* a0img;                      // out
+};
+
 // Arguments of one ensemble forward launch.
 struct FwdParams {
   ModelPlan plan;
   const uint8_t* wimg;          // packed bf16 weight image [E][2][blk_bytes]
-  const float* in_mu;           // [in_dim] scaler_in mean          (utils.py:161)
-  const float* in_inv;          // [in_dim] 1 / max(sqrt(var)*sc, 1e-2)
+  const uint8_t* a0img;         // staged layer-0 A tiles [input slot][128-row block][a0_bytes]
+  long long a0_slot_stride;     // bytes between input slots of a0img
   const float* head_scale;      // [n_head] s_out for mean cols, 1 for logvar cols (utils.py:172,192)
   const float* head_shift;      // [n_head] mu_out for mean cols, 2*log(s_out) for logvar cols
-  const float* seg_ptr[kMaxSeg];   // input segments; row-major [slots?][B][width]
-  int seg_width[kMaxSeg];
-  long long seg_slot_stride[kMaxSeg];  // elements between ensemble slots (0 => shared by all slots)
   int per_slot_input;           // 0: 2-D input shared by all members; 1: 3-D input (fc.py:107-108)
   int member_of_slot[kMaxMembers];  // weights used for output slot j
   int input_of_slot[kMaxMembers];   // input slot feeding output slot j (3-D only)
@@ -68,7 +81,7 @@ struct FwdParams {
   long long n_rows;             // row count if n_rows_dev == nullptr
   float* heads;                 // out: tile-major head scratch (head_index), scaled mean | shifted logvar
   int* status;                  // watchdog / error word
-  long long* trace;             // debug timeline, only read by -DCMBPO_TRACE builds (tools/trace_fwd.cu)
+  long long* trace;             // debug timeline, only read by -DCMBPO_TRACE builds
 };
 
 }  // namespace cmbpo

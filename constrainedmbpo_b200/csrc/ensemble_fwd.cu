@@ -19,8 +19,8 @@
 //   * bias rides in the GEMM (two extra K rows hold bias hi/lo against two constant-one A columns);
 //     swish is evaluated as g + g*tanh(g) on g = x/2 (weights are pre-scaled by 1/2, exact).
 //   * warp roles: 0 = weight loader (+ peer->leader relay of weight arrivals), 1 = MMA issuer (leader
-//     CTA), 2 = TMEM alloc + input stager of stream Y, 3 = input stager of stream X (concat + scaler +
-//     bf16 + canonical layout), 4..7 / 8..11 = epilogue of stream X / Y (one warp per TMEM lane quadrant).
+//     CTA), 2 = TMEM alloc, 3 = layer-0 operand loader (bulk copies of the tiles stage_inputs_kernel
+//     wrote), 4..7 / 8..11 = epilogue of stream X / Y (one warp per TMEM lane quadrant).
 //   * every tcgen05.mma of a stream is gated by the epilogue's completion of that stream's previous
 //     pass (A_READY), so no barrier ever has more than one phase outstanding.
 #include "cmbpo_internal.cuh"
@@ -39,7 +39,7 @@ __host__ __device__ inline SmemLayout make_smem_layout(const ModelPlan& pl) {
   s.off_a = pl.w_slots * pl.slot_bytes;
   s.off_a0 = s.off_a + 2 * pl.a_bytes;
   s.off_const = s.off_a0 + 2 * pl.a0_bytes;
-  uint32_t nconst = 2u * ((pl.in_dim + 3u) & ~3u) + 2u * ((pl.n_head + 15u) & ~15u);
+  uint32_t nconst = 2u * ((pl.n_head + 15u) & ~15u);
   s.off_bar = (s.off_const + 4u * nconst + 15u) & ~15u;
   s.off_tmem = s.off_bar + 32u * 8u;
   s.total = s.off_tmem + 16u;
@@ -274,13 +274,29 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
   const int n_tiles = (int)((n_rows + 2 * kTileRows - 1) / (2 * kTileRows));
   const int E = pl.E, L = pl.L;
   const int S = (int)pl.w_slots;
+  // Work split.  Members are independent (each writes its own head region), so a launch with few
+  // tiles is also cut along the member axis: G member groups x nvc "virtual clusters" of tiles.  G
+  // minimises the modelled makespan (a tile pair costs ~38, a lone tile ~34 time units per member);
+  // ties go to the smaller G, so big batches keep G = 1.
+  int G = 1;
+  {
+    long long best = -1;
+    for (int gg = 1; gg <= E && gg <= n_clusters; ++gg) {
+      const int nv = n_clusters / gg;
+      const long long t = (n_tiles + nv - 1) / nv;
+      const long long cost = (long long)((E + gg - 1) / gg) * ((t >> 1) * 38 + (t & 1) * 34);
+      if (best < 0 || cost < best) { best = cost; G = gg; }
+    }
+  }
+  const int nvc = n_clusters / G;
+  const int vc = cluster_id % nvc, mg = cluster_id / nvc;
+  const int vtiles = (mg < G) ? n_tiles : 0;            // clusters beyond G * nvc have no work
+  const int e_begin = (mg < G) ? (mg * E) / G : 0, e_end = (mg < G) ? ((mg + 1) * E) / G : 0;
 
-  const int in_pad4 = (pl.in_dim + 3) & ~3, head_pad16 = (pl.n_head + 15) & ~15;
+  const int head_pad16 = (pl.n_head + 15) & ~15;
   float* s_const = reinterpret_cast<float*>(smem + sl.off_const);
-  float* s_in_mu = s_const;
-  float* s_in_inv = s_const + in_pad4;
-  float* s_head_scale = s_const + 2 * in_pad4;
-  float* s_head_shift = s_const + 2 * in_pad4 + head_pad16;
+  float* s_head_scale = s_const;
+  float* s_head_shift = s_const + head_pad16;
   const uint32_t bar0 = smem_u32(smem + sl.off_bar);
   auto bar = [bar0](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + sl.off_tmem);
@@ -292,16 +308,12 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
       mbar_init(bar(BAR_W_EMPTY + s), 1);                 // tcgen05.commit
     }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(bar(BAR_A0_FULL + s), 2);                 // one stager warp per CTA
+      mbar_init(bar(BAR_A0_FULL + s), cta == 0 ? 2 : 1);  // leader: own fill + relayed peer fill
       mbar_init(bar(BAR_A0_EMPTY + s), 1);                // tcgen05.commit
       mbar_init(bar(BAR_D_FULL + s), 1);                  // tcgen05.commit
       mbar_init(bar(BAR_A_READY + s), 8);                 // 4 epilogue warps of the stream x 2 CTAs
     }
     fence_mbar_init();
-  }
-  for (int i = tid; i < in_pad4; i += blockDim.x) {
-    s_in_mu[i] = (p.in_mu && i < pl.in_dim) ? p.in_mu[i] : 0.f;
-    s_in_inv[i] = (p.in_inv && i < pl.in_dim) ? p.in_inv[i] : 1.f;
   }
   for (int i = tid; i < head_pad16; i += blockDim.x) {
     s_head_scale[i] = (p.head_scale && i < pl.n_head) ? p.head_scale[i] : 1.f;
@@ -324,10 +336,10 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
     // (the MMA issuer waits on the leader's W_FULL only), so it polls instead of blocking.
     if (lane == 0) {
       long long n_pairs = 0;
-      for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) ++n_pairs;
-      const long long total = n_pairs * E * L;
+      for (PairIter it(vc, nvc, vtiles); it.valid(); it.next()) ++n_pairs;
+      const long long total = n_pairs * (e_end - e_begin) * L;
       long long fill_n = 0, relay_n = 0;
-      int f_slot = 0, f_e = 0, f_l = 0, r_slot = 0; uint32_t f_use = 0, r_use = 0;
+      int f_slot = 0, f_e = e_begin, f_l = 0, r_slot = 0; uint32_t f_use = 0, r_use = 0;
       uint32_t idle = 0;
       while (fill_n < total || (cta == 1 && relay_n < total)) {
         bool progress = false;
@@ -336,7 +348,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
           const uint8_t* blk = p.wimg + (size_t)(p.member_of_slot[f_e] * 2 + (int)cta) * pl.blk_bytes;
           mbar_arrive_expect_tx(bar(BAR_W_FULL + f_slot), lp.bytes);
           bulk_g2s(smem_u32(smem + (uint32_t)f_slot * pl.slot_bytes), blk + lp.img_off, lp.bytes, bar(BAR_W_FULL + f_slot));
-          if (++f_l == L) { f_l = 0; if (++f_e == E) f_e = 0; }
+          if (++f_l == L) { f_l = 0; if (++f_e == e_end) f_e = e_begin; }
           if (++f_slot == S) { f_slot = 0; ++f_use; }
           ++fill_n; progress = true;
         }
@@ -360,11 +372,11 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
       int slot = 0; uint32_t use = 0;
       uint32_t passes[2] = {0, 0}, stage[2] = {0, 0};
       TR_DECL(0, cluster_id == 0 && lane == 0);
-      for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
+      for (PairIter it(vc, nvc, vtiles); it.valid(); it.next()) {
         const bool has_y = it.has_y();
-        for (int e = 0; e < E; ++e) {
-          const bool new_input = p.per_slot_input || e == 0;
-          const bool last_use = p.per_slot_input || e == E - 1;
+        for (int e = e_begin; e < e_end; ++e) {
+          const bool new_input = p.per_slot_input || e == e_begin;
+          const bool last_use = p.per_slot_input || e == e_end - 1;
           for (int l = 0; l < L; ++l) {
             const LayerPlan& lp = pl.layer[l];
             const uint32_t idesc = make_idesc(256, lp.npad, kFmtBF16);
@@ -403,49 +415,46 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
         }
       }
     }
-  } else if (warp == 2 || warp == 3) {
-    // ===== input stager of one stream: concat(segments) -> (x-mu)*inv -> bf16 -> canonical K-major tile
-    const int s = (warp == 3) ? 0 : 1;
-    const LayerPlan& l0 = pl.layer[0];
-    const uint32_t sbo = (uint32_t)(l0.kpad >> 3) * 128u;
-    uint8_t* a0 = smem + sl.off_a0 + s * pl.a0_bytes;
-    uint32_t st = 0;
-    for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
-      if (s == 1 && !it.has_y()) continue;
-      const int tile = s ? it.y() : it.x();
-      const int n_stage = p.per_slot_input ? E : 1;
-      for (int e = 0; e < n_stage; ++e, ++st) {
-        if (st > 0) mbar_wait_relaxed(bar(BAR_A0_EMPTY + s), (st - 1) & 1, p.status, WC_STAGER_EMPTY, 64);
-        const int in_slot = p.per_slot_input ? p.input_of_slot[e] : 0;
-        for (int i = 0; i < 4; ++i) {
-          const int r = lane + 32 * i;
-          const long long g = (long long)tile * (2 * kTileRows) + (long long)cta * kTileRows + r;
-          uint8_t* rowp = a0 + (uint32_t)(r >> 3) * sbo + (uint32_t)(r & 7) * 16u;
-          const bool live = g < n_rows;
-          int k = 0;
-          for (int sg = 0; sg < kMaxSeg; ++sg) {
-            const int w = p.seg_width[sg];
-            if (w == 0) continue;
-            const float* src = p.seg_ptr[sg] + (size_t)in_slot * p.seg_slot_stride[sg] + (size_t)g * w;
-#pragma unroll 4
-            for (int kk = 0; kk < w; ++kk, ++k) {
-              float x = live ? __ldg(src + kk) : 0.f;
-              float xn = (x - s_in_mu[k]) * s_in_inv[k];
-              *reinterpret_cast<__nv_bfloat16*>(rowp + (uint32_t)(k >> 3) * 128u + (uint32_t)(k & 7) * 2u) =
-                  __float2bfloat16_rn(live ? xn : 0.f);
-            }
+  } else if (warp == 3) {
+    // ===== layer-0 operand loader: the staged bf16 input tile of each stream (written by
+    // stage_inputs_kernel) comes in with one bulk copy per (pair, input stage); the peer CTA's
+    // thread also relays its arrivals to the leader's A0_FULL.
+    if (lane == 0) {
+      const int n_stage = p.per_slot_input ? (e_end - e_begin) : 1;
+      long long total[2] = {0, 0}, fill_n[2] = {0, 0}, relay_n[2] = {0, 0};
+      for (PairIter it(vc, nvc, vtiles); it.valid(); it.next()) { total[0] += n_stage; if (it.has_y()) total[1] += n_stage; }
+      uint32_t idle = 0;
+      while (fill_n[0] < total[0] || fill_n[1] < total[1] ||
+             (cta == 1 && (relay_n[0] < total[0] || relay_n[1] < total[1]))) {
+        bool progress = false;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          if (fill_n[s] < total[s] &&
+              (fill_n[s] == 0 || mbar_try_wait(bar(BAR_A0_EMPTY + s), (uint32_t)(fill_n[s] - 1) & 1))) {
+            const long long pair = fill_n[s] / n_stage;
+            const int est = (int)(fill_n[s] - pair * n_stage);
+            const long long tile = vc + (2 * pair + s) * (long long)nvc;
+            const int in_slot = p.per_slot_input ? p.input_of_slot[e_begin + est] : 0;
+            const uint8_t* src = p.a0img + (size_t)in_slot * p.a0_slot_stride + (size_t)(tile * 2 + cta) * pl.a0_bytes;
+            mbar_arrive_expect_tx(bar(BAR_A0_FULL + s), pl.a0_bytes);
+            bulk_g2s(smem_u32(smem + sl.off_a0 + s * pl.a0_bytes), src, pl.a0_bytes, bar(BAR_A0_FULL + s));
+            ++fill_n[s]; progress = true;
           }
-          for (; k < l0.kpad; ++k) {  // bias carrier columns, then zero padding
-            float v = (k < pl.in_dim + 2) ? 1.0f : 0.0f;
-            *reinterpret_cast<__nv_bfloat16*>(rowp + (uint32_t)(k >> 3) * 128u + (uint32_t)(k & 7) * 2u) =
-                __float2bfloat16_rn(v);
+          if (cta == 1 && relay_n[s] < fill_n[s] && mbar_try_wait(bar(BAR_A0_FULL + s), (uint32_t)relay_n[s] & 1)) {
+            mbar_arrive_cluster(bar(BAR_A0_FULL + s), 0);
+            ++relay_n[s]; progress = true;
           }
         }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(bar(BAR_A0_FULL + s), 0);
+        if (progress) { idle = 0; continue; }
+        __nanosleep(64);
+        if (++idle > (SM100_WAIT_LIMIT >> 2)) {
+          if (p.status) { atomicExch(p.status, WC_STAGER_EMPTY | 0x40000000); __threadfence_system(); }
+          __trap();
+        }
       }
     }
+  } else if (warp == 2) {
+    // (TMEM allocation / release only)
   } else {
     // ===== epilogue warps 4..11: TMEM lane quadrant q (the hardware ties a warp to lanes 32*(warp%4)..);
     // warps 4..7 serve stream X, warps 8..11 stream Y
@@ -461,8 +470,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
     // pairs that have both streams use it (hidden passes alternate X, Y, X, Y ...); Y opens the game
     // and keeps the token of its very last pass.
     const int tok_mine = s ? 5 + q : 1 + q, tok_other = s ? 1 + q : 5 + q;
-    if (s == 1 && L > 1 && PairIter(cluster_id, n_clusters, n_tiles).has_y()) token_pass(tok_other);
-    for (PairIter it(cluster_id, n_clusters, n_tiles); it.valid(); it.next()) {
+    if (s == 1 && L > 1 && PairIter(vc, nvc, vtiles).has_y()) token_pass(tok_other);
+    for (PairIter it(vc, nvc, vtiles); it.valid(); it.next()) {
       if (s == 1 && !it.has_y()) continue;
       const bool use_tok = it.has_y();
       PairIter nx = it; nx.next();
@@ -470,7 +479,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
       const int tile = s ? it.y() : it.x();
       const long long blk = (long long)tile * 2 + cta;           // 128-row block of the head scratch
       const bool live = blk * kTileRows + row_in_tile < n_rows;
-      for (int e = 0; e < E; ++e) {
+      for (int e = e_begin; e < e_end; ++e) {
         for (int l = 0; l < L; ++l) {
           const LayerPlan& lp = pl.layer[l];
           TR(200 + l);
@@ -481,7 +490,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
           if (l < L - 1) {
             // next layer's A tile: 8-row group stride = npad (= next kpad) * 16 bytes
             const uint32_t a_row = a_tile + (uint32_t)(row_in_tile >> 3) * ((uint32_t)lp.npad * 16u);
-            const bool keep = s == 1 && last_tok_pair && e == E - 1 && l == L - 2;
+            const bool keep = s == 1 && last_tok_pair && e == e_end - 1 && l == L - 2;
             hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, a_row, use_tok ? tok_mine : 0,
                                   (use_tok && !keep) ? tok_other : 0);
             fence_proxy_async_smem();      // generic-proxy smem writes -> visible to tcgen05.mma
@@ -503,6 +512,69 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
   __syncthreads();
   cluster_sync();
   if (warp == 2) tmem_dealloc<2>(tmem_base, 512);
+}
+
+// ---------------------------------------------------------------------------------------
+// K0 input staging: concat(segments) (fake_env.py:141-145) -> (x - mu) * inv (utils.py:161) -> bf16 ->
+// canonical K-major A tile of layer 0, element (r, k) of a 128-row block at
+//     (r/8)*(kpad/8)*128 + (k/8)*128 + (r%8)*16 + (k%8)*2
+// columns in_dim, in_dim+1 are the constant-one bias carriers, the rest of the padding is zero.
+// One thread per (row, 8-column group): 8 scalar loads, one 16-byte store; consecutive threads take
+// consecutive rows, so a warp writes four whole 128-byte core matrices.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) stage_inputs_kernel(const StageParams p) {
+  const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
+  const long long rows_pad = (n_rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
+  const int kg = p.kpad >> 3;
+  const long long per_slot = rows_pad * kg;
+  const long long total = per_slot * p.n_slots;
+  const uint32_t blk_bytes = (uint32_t)kTileRows * p.kpad * 2u;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int slot = (int)(i / per_slot);
+    const long long j = i - (long long)slot * per_slot;
+    // j -> (128-row block, k-group, row in block): rows fastest, then k-groups, then blocks
+    const long long blk = j / ((long long)kTileRows * kg);
+    const int rem = (int)(j - blk * kTileRows * kg);
+    const int g8 = rem / kTileRows, r = rem - g8 * kTileRows;
+    const long long row = blk * kTileRows + r;
+    uint32_t packed[4];
+#pragma unroll
+    for (int h2 = 0; h2 < 4; ++h2) {
+      float v[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int k = g8 * 8 + h2 * 2 + u;
+        float x = 0.f;
+        if (row < n_rows) {
+          if (k < p.in_dim) {
+            int kk = k, sg = 0;
+            while (sg < kMaxSeg - 1 && kk >= p.seg_width[sg]) { kk -= p.seg_width[sg]; ++sg; }
+            const float raw = __ldg(p.seg_ptr[sg] + (size_t)slot * p.seg_slot_stride[sg] + (size_t)row * p.seg_width[sg] + kk);
+            const float mu = p.in_mu ? p.in_mu[k] : 0.f, inv = p.in_inv ? p.in_inv[k] : 1.f;
+            x = (raw - mu) * inv;
+          } else if (k < p.in_dim + 2) {
+            x = 1.0f;
+          }
+        }
+        v[u] = x;
+      }
+      packed[h2] = pack_bf16x2(v[0], v[1]);
+    }
+    uint8_t* dst = p.a0img + (size_t)slot * p.slot_stride_bytes + (size_t)blk * blk_bytes +
+                   (size_t)(r >> 3) * ((size_t)kg * 128) + (size_t)g8 * 128 + (size_t)(r & 7) * 16;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+  }
+}
+
+cudaError_t launch_stage_inputs(const StageParams& p, int num_sms, cudaStream_t stream) {
+  const long long rows_pad = (p.n_rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
+  const long long total = rows_pad * (p.kpad >> 3) * p.n_slots;
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)num_sms * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  stage_inputs_kernel<<<(int)blocks, 256, 0, stream>>>(p);
+  return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------------------
@@ -562,8 +634,9 @@ static cudaError_t launch_fwd_variant(const FwdParams& p, int num_sms, cudaStrea
     attr_set = true;
   }
   const long long n_tiles = (p.n_rows + 2 * kTileRows - 1) / (2 * kTileRows);
+  // all clusters even for few tiles: the kernel also splits the work along the member axis
   int clusters = num_sms / 2;
-  if (!p.n_rows_dev && n_tiles < clusters) clusters = (int)(n_tiles > 0 ? n_tiles : 1);
+  if (!p.n_rows_dev && n_tiles * p.plan.E < clusters) clusters = (int)(n_tiles > 0 ? n_tiles * p.plan.E : 1);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(2 * clusters);
   cfg.blockDim = dim3(kFwdThreads);

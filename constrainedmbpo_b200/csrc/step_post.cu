@@ -154,18 +154,28 @@ __device__ __forceinline__ void column_stats(const float (&m)[E], const float (&
   epv_out = s2 * (1.0f / E);
 }
 
+// kPostParts threads share one row: thread (r, part) handles output columns d = part, part+4, ...;
+// a warp is 32 consecutive rows of one part, so head loads stay 128-byte coalesced while the serial
+// per-thread chain (the latency floor of small sampler steps) is a quarter as long.
+constexpr int kPostParts = 4;
+constexpr int kPostThreads = kTileRows * kPostParts;
+
 template <int E>
-__global__ void __launch_bounds__(128) step_post_kernel(const StepParams p) {
+__global__ void __launch_bounds__(kPostThreads) step_post_kernel(const StepParams p) {
   __shared__ float tile[kTileRows * 64 + 128];  // obs in / next_obs out staging (obs_dim <= 64)
-  __shared__ float red[4][4];
+  __shared__ float s_kl[kPostParts][kTileRows], s_epv[kPostParts][kTileRows];
+  __shared__ float s_rew[kTileRows];
+  __shared__ uint8_t s_flags[kPostParts][kTileRows];
+  __shared__ float red[4][kPostThreads / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int r = tid & (kTileRows - 1), part = tid / kTileRows;
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
   const int D = p.D, OD = p.obs_dim;
   const int n_slots_out = p.per_slot ? E : 1;
   float acc_dkl = 0.f, acc_var = 0.f, acc_rew = 0.f, acc_cost = 0.f;
 
   for (long long row0 = (long long)blockIdx.x * kTileRows; row0 < n_rows; row0 += (long long)gridDim.x * kTileRows) {
-    const long long g = row0 + tid;
+    const long long g = row0 + r;
     const bool live = g < n_rows;
     const int rows_here = (int)min((long long)kTileRows, n_rows - row0);
     int eidx = 0;
@@ -187,18 +197,14 @@ __global__ void __launch_bounds__(128) step_post_kernel(const StepParams p) {
       __syncthreads();
       {
         const float* src = p.obs + (p.per_slot ? (size_t)so * n_rows * OD : 0) + (size_t)row0 * OD;
-        for (int i = tid; i < rows_here * OD; i += kTileRows) tile[i] = src[i];
+        for (int i = tid; i < rows_here * OD; i += kPostThreads) tile[i] = src[i];
       }
       __syncthreads();
-      RowFeatures f;
-      f.x0 = f.x1 = f.x2 = f.x3 = f.last = 0.f;
-      f.finite_all = true; f.lt100_from1 = true;
-      float rew = 0.f;
-      bool slow = false;
+      bool finite_part = true, lt100_part = true;
       if (live) {
-        for (int d = 0; d < D; ++d) {
+        for (int d = part; d < D; d += kPostParts) {
           float m[E], lv[E], v[E];
-          const float o = (d < OD) ? tile[tid * OD + d] : 0.f;
+          const float o = (d < OD) ? tile[r * OD + d] : 0.f;
 #pragma unroll
           for (int e = 0; e < E; ++e) {
             const float* hm = p.heads + head_index(g, e, d, E, 2 * D);
@@ -224,7 +230,7 @@ __global__ void __launch_bounds__(128) step_post_kernel(const StepParams p) {
 #pragma unroll
           for (int e = 0; e < E; ++e) weird = weird || !(fabsf(m[e]) < 1e18f);
           float kl, epv;
-          if (weird) { column_stats<E, true>(m, lv, v, kl, epv); slow = true; }
+          if (weird) column_stats<E, true>(m, lv, v, kl, epv);
           else column_stats<E, false>(m, lv, v, kl, epv);
           if (so == 0) {
             kl_row += kl; epv_row += epv;
@@ -241,19 +247,30 @@ __global__ void __launch_bounds__(128) step_post_kernel(const StepParams p) {
             x = fmaf(z, sqrtf(vs), x);
           }
           if (d < OD) {
-            tile[tid * OD + d] = x;  // own row only: safe to overwrite the staged obs
-            f.finite_all = f.finite_all && (fabsf(x) <= 3.402823466e38f);
-            if (d == 0) f.x0 = x;
-            if (d == 1) f.x1 = x;
-            if (d == 2) f.x2 = x;
-            if (d == 3) f.x3 = x;
-            if (d >= 1) f.lt100_from1 = f.lt100_from1 && (x < 100.f);
-            if (d == OD - 1) f.last = x;
+            tile[r * OD + d] = x;  // own element only: safe to overwrite the staged obs
+            finite_part = finite_part && (fabsf(x) <= 3.402823466e38f);
+            if (d >= 1) lt100_part = lt100_part && (x < 100.f);
           } else {
-            rew = x;  // reward is the last output column (fake_env.py:180)
+            s_rew[r] = x;  // reward is the last output column (fake_env.py:180)
           }
         }
-        (void)slow;
+      }
+      s_flags[part][r] = (uint8_t)((finite_part ? 1 : 0) | (lt100_part ? 2 : 0));
+      __syncthreads();
+      if (live && part == 0) {
+        RowFeatures f;
+        uint8_t fl = 3;
+#pragma unroll
+        for (int q = 0; q < kPostParts; ++q) fl &= s_flags[q][r];
+        f.finite_all = (fl & 1) != 0;
+        f.lt100_from1 = (fl & 2) != 0;
+        const float* xr = tile + r * OD;
+        f.x0 = xr[0];
+        f.x1 = OD > 1 ? xr[1] : 0.f;
+        f.x2 = OD > 2 ? xr[2] : 0.f;
+        f.x3 = OD > 3 ? xr[3] : 0.f;
+        f.last = xr[OD - 1];
+        const float rew = s_rew[r];
         const bool done = termination(p.env_id, f);
         const float cost = (p.cost_mode == 1) ? static_cost(p.env_id, f, done) : 0.f;
         const size_t oi = (size_t)so * n_rows + g;
@@ -262,16 +279,21 @@ __global__ void __launch_bounds__(128) step_post_kernel(const StepParams p) {
         if (p.cost) p.cost[oi] = cost;
         if (so == 0 || p.per_slot) { acc_rew += rew; acc_cost += cost; }
       }
-      __syncthreads();
       {
         float* dst = p.next_obs + (p.per_slot ? (size_t)so * n_rows * OD : 0) + (size_t)row0 * OD;
-        for (int i = tid; i < rows_here * OD; i += kTileRows) dst[i] = tile[i];
+        for (int i = tid; i < rows_here * OD; i += kPostThreads) dst[i] = tile[i];
       }
     }
-    if (live) {
-      const float dkl = kl_row / (float)D;  // np.mean(average_dkl(...), axis=-1), fake_env.py:158
+    s_kl[part][r] = kl_row;
+    s_epv[part][r] = epv_row;
+    __syncthreads();
+    if (live && part == 0) {
+      float ks = 0.f, es = 0.f;
+#pragma unroll
+      for (int q = 0; q < kPostParts; ++q) { ks += s_kl[q][r]; es += s_epv[q][r]; }
+      const float dkl = ks / (float)D;  // np.mean(average_dkl(...), axis=-1), fake_env.py:158
       p.dkl_path[g] = dkl;
-      if (p.ep_var_mean) p.ep_var_mean[g] = epv_row / (float)D;
+      if (p.ep_var_mean) p.ep_var_mean[g] = es / (float)D;
       acc_dkl += dkl;
     }
   }
@@ -285,7 +307,11 @@ __global__ void __launch_bounds__(128) step_post_kernel(const StepParams p) {
     if (lane == 0) red[k][warp] = x;
   }
   __syncthreads();
-  if (tid < 4) p.partials[(size_t)blockIdx.x * 4 + tid] = red[tid][0] + red[tid][1] + red[tid][2] + red[tid][3];
+  if (tid < 4) {
+    float x = 0.f;
+    for (int w = 0; w < kPostThreads / 32; ++w) x += red[tid][w];
+    p.partials[(size_t)blockIdx.x * 4 + tid] = x;
+  }
 }
 
 // deterministic final reduction of the per-block partial sums -> 4 means
@@ -358,13 +384,13 @@ __global__ void aggregate_predict_kernel(const float* __restrict__ heads, long l
 
 template <int E>
 static cudaError_t launch_step_post_E(const StepParams& p, int n_blocks, cudaStream_t stream) {
-  step_post_kernel<E><<<n_blocks, kTileRows, 0, stream>>>(p);
+  step_post_kernel<E><<<n_blocks, kPostThreads, 0, stream>>>(p);
   return cudaGetLastError();
 }
 
 int step_post_blocks(long long n_rows, int num_sms) {
   long long tiles = (n_rows + kTileRows - 1) / kTileRows;
-  long long cap = (long long)num_sms * 8;
+  long long cap = (long long)num_sms * 4;
   if (tiles < 1) tiles = 1;
   return (int)(tiles < cap ? tiles : cap);
 }
