@@ -339,6 +339,16 @@ __device__ __forceinline__ void tmem_st8_lo(uint32_t taddr, const uint32_t (&r)[
         "r"(r[7]) : "memory");
 }
 
+// 8-column load into r[OFF .. OFF+8) of a 32-register buffer
+template <int OFF>
+__device__ __forceinline__ void tmem_ld8_at(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(r[OFF + 0]), "=r"(r[OFF + 1]), "=r"(r[OFF + 2]), "=r"(r[OFF + 3]), "=r"(r[OFF + 4]),
+        "=r"(r[OFF + 5]), "=r"(r[OFF + 6]), "=r"(r[OFF + 7])
+      : "r"(taddr));
+}
+
 // two fp32 -> packed bf16x2 (lo -> bits [0,16), hi -> bits [16,32)), round-to-nearest-even
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   uint32_t r;
