@@ -121,7 +121,7 @@ __device__ __forceinline__ void column_stats(const float (&m)[E], const float (&
 #pragma unroll
   for (int e = 0; e < E; ++e) {
     vk[e] = EXACT ? expf(2.0f * ls[e]) : v[e];
-    inv[e] = 1.0f / (vk[e] + 1e-10f);
+    inv[e] = EXACT ? 1.0f / (vk[e] + 1e-10f) : __frcp_rn(vk[e] + 1e-10f);
   }
   float kl = 0.f;
 #pragma unroll
@@ -154,30 +154,32 @@ __device__ __forceinline__ void column_stats(const float (&m)[E], const float (&
   epv_out = s2 * (1.0f / E);
 }
 
-// kPostParts threads share one row: thread (r, part) handles output columns d = part, part+4, ...;
-// a warp is 32 consecutive rows of one part, so head loads stay 128-byte coalesced while the serial
-// per-thread chain (the latency floor of small sampler steps) is a quarter as long.
-constexpr int kPostParts = 4;
-constexpr int kPostThreads = kTileRows * kPostParts;
+// kPostParts warps share a block of kPostRows rows: warp `part` handles output columns d = part,
+// part+16, ... of all 32 rows (lane = row), so head loads stay 128-byte coalesced while the serial
+// per-thread chain -- the latency floor of the small sampler steps late in a rollout -- is one or two
+// columns long, and a small batch still spreads over all SMs (32-row blocks).
+constexpr int kPostRows = 32;
+constexpr int kPostParts = 16;
+constexpr int kPostThreads = kPostRows * kPostParts;
 
 template <int E>
-__global__ void __launch_bounds__(kPostThreads) step_post_kernel(const StepParams p) {
-  __shared__ float tile[kTileRows * 64 + 128];  // obs in / next_obs out staging (obs_dim <= 64)
-  __shared__ float s_kl[kPostParts][kTileRows], s_epv[kPostParts][kTileRows];
-  __shared__ float s_rew[kTileRows];
-  __shared__ uint8_t s_flags[kPostParts][kTileRows];
-  __shared__ float red[4][kPostThreads / 32];
+__global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepParams p) {
+  __shared__ float tile[kPostRows * 64 + 32];  // obs in / next_obs out staging (obs_dim <= 64)
+  __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
+  __shared__ float s_rew[kPostRows];
+  __shared__ uint8_t s_flags[kPostParts][kPostRows];
+  __shared__ float red[4][kPostParts];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int r = tid & (kTileRows - 1), part = tid / kTileRows;
+  const int r = lane, part = warp;
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
   const int D = p.D, OD = p.obs_dim;
   const int n_slots_out = p.per_slot ? E : 1;
   float acc_dkl = 0.f, acc_var = 0.f, acc_rew = 0.f, acc_cost = 0.f;
 
-  for (long long row0 = (long long)blockIdx.x * kTileRows; row0 < n_rows; row0 += (long long)gridDim.x * kTileRows) {
+  for (long long row0 = (long long)blockIdx.x * kPostRows; row0 < n_rows; row0 += (long long)gridDim.x * kPostRows) {
     const long long g = row0 + r;
     const bool live = g < n_rows;
-    const int rows_here = (int)min((long long)kTileRows, n_rows - row0);
+    const int rows_here = (int)min((long long)kPostRows, n_rows - row0);
     int eidx = 0;
     if (!p.per_slot && live) {
       if (p.elite_idx) {
@@ -193,7 +195,7 @@ __global__ void __launch_bounds__(kPostThreads) step_post_kernel(const StepParam
     float kl_row = 0.f, epv_row = 0.f;
     // ---- pass over output slots (1 in 2-D mode; E in 3-D mode where every member keeps its own row)
     for (int so = 0; so < n_slots_out; ++so) {
-      // stage obs rows of this tile (slot `so` in 3-D mode) through smem, coalesced
+      // stage obs rows of this block (slot `so` in 3-D mode) through smem, coalesced
       __syncthreads();
       {
         const float* src = p.obs + (p.per_slot ? (size_t)so * n_rows * OD : 0) + (size_t)row0 * OD;
@@ -309,7 +311,7 @@ __global__ void __launch_bounds__(kPostThreads) step_post_kernel(const StepParam
   __syncthreads();
   if (tid < 4) {
     float x = 0.f;
-    for (int w = 0; w < kPostThreads / 32; ++w) x += red[tid][w];
+    for (int w = 0; w < kPostParts; ++w) x += red[tid][w];
     p.partials[(size_t)blockIdx.x * 4 + tid] = x;
   }
 }
@@ -389,8 +391,8 @@ static cudaError_t launch_step_post_E(const StepParams& p, int n_blocks, cudaStr
 }
 
 int step_post_blocks(long long n_rows, int num_sms) {
-  long long tiles = (n_rows + kTileRows - 1) / kTileRows;
-  long long cap = (long long)num_sms * 4;
+  long long tiles = (n_rows + kPostRows - 1) / kPostRows;
+  long long cap = (long long)num_sms * 8;
   if (tiles < 1) tiles = 1;
   return (int)(tiles < cap ? tiles : cap);
 }
