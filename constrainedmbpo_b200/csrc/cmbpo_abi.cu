@@ -38,6 +38,7 @@ struct Handle {
   int* elites_dev = nullptr;
   int n_elites = 0;
   int* status_dev = nullptr;
+  unsigned int* ticket_dev = nullptr;   // step_post's last-block counter
   uint32_t layers_set = 0;
   int hidden_act = 0;
   bool scalers_set = false;
@@ -120,6 +121,8 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
   CU(cudaMalloc(&h->elites_dev, sizeof(int) * 64), "cudaMalloc(elites)");
   CU(cudaMalloc(&h->status_dev, sizeof(int)), "cudaMalloc(status)");
   CU(cudaMemset(h->status_dev, 0, sizeof(int)), "cudaMemset(status)");
+  CU(cudaMalloc(&h->ticket_dev, sizeof(unsigned int)), "cudaMalloc(ticket)");
+  CU(cudaMemset(h->ticket_dev, 0, sizeof(unsigned int)), "cudaMemset(ticket)");
   // defaults: identity scalers (utils.py:108-115), every member elite
   int rc = cmbpo_set_scalers(h, nullptr, nullptr, nullptr, nullptr, 1.0f, nullptr);
   if (rc != 0) { cmbpo_destroy(h); return rc; }
@@ -136,7 +139,7 @@ extern "C" void cmbpo_destroy(void* handle) {
   Handle* h = static_cast<Handle*>(handle);
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->wimg); cudaFree(h->consts); cudaFree(h->elites_dev); cudaFree(h->status_dev);
+  cudaFree(h->wimg); cudaFree(h->consts); cudaFree(h->elites_dev); cudaFree(h->status_dev); cudaFree(h->ticket_dev);
   delete h;
 }
 
@@ -380,10 +383,11 @@ extern "C" int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream_) 
   sp.next_obs = io->next_obs_dev; sp.rew = io->rew_dev; sp.term = io->term_dev; sp.cost = io->cost_dev;
   sp.dkl_path = io->dkl_path_dev; sp.ep_var_mean = io->ep_var_mean_dev; sp.ep_var = io->ep_var_dev;
   sp.partials = partials;
+  sp.ticket = h->ticket_dev;
+  sp.scalars = io->scalars_dev;
   const int n_blocks = step_post_blocks(io->n_rows, h->num_sms);
   CU(launch_step_post(sp, pl.E, n_blocks, stream), "launch_step_post");
-  CU(launch_reduce_scalars(partials, n_blocks, io->n_rows_dev, io->n_rows, pl.E, pl.D, sp.per_slot ? pl.E : 1,
-                           io->scalars_dev, stream), "launch_reduce_scalars");
+
   return CMBPO_OK;
 }
 

@@ -68,9 +68,14 @@ __global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* ce
 
 // B/D: single-block exclusive scan of per-block counts (in place), then a small epilogue
 template <int PHASE>
-__global__ void __launch_bounds__(1024) k_scan(cmbpo_rollout_io io, int* blk_cnt, int n_blocks_max) {
+__global__ void __launch_bounds__(1024) k_scan(cmbpo_rollout_io io, int* blk_cnt, int n_blocks_max, int* snap, int* hist) {
   RolloutState* st = static_cast<RolloutState*>(io.state_dev);
   const int n_blocks = (st->n_alive + kRB - 1) / kRB;
+  if (PHASE == 1 && threadIdx.x == 0) {
+    // the pre-advance alive count is needed by the compaction after k_scan<2> overwrote it
+    *snap = st->n_alive;
+    if (hist) *hist = st->n_alive;
+  }
   __shared__ int sh[1024];
   __shared__ int carry;
   if (threadIdx.x == 0) carry = 0;
@@ -157,22 +162,32 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
   int tot;
   block_exclusive_scan(k, &tot);   // includes the __syncthreads that publishes s_pid / s_rem
   if (threadIdx.x == 0) blk_keep_cnt[blockIdx.x] = tot;
-  // row payloads: one warp per row so each 4*dim-byte row moves as one coalesced segment
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // row payloads: flat element loop over the block's 256 rows (source rows are contiguous, so loads are
+  // fully coalesced; every thread has several independent load->store chains in flight -- a
+  // warp-per-row loop here was a 32-deep serial latency chain, 35 us even for a handful of rows)
   const int OD = io.obs_dim, AD = io.act_dim;
-  for (int r = warp; r < kRB; r += 8) {
-    const int gi = blockIdx.x * kRB + r;
-    if (gi >= n || !s_rem[r]) continue;
-    const size_t slot = (size_t)s_pid[r] * T + ptr;
-    const float* so = static_cast<const float*>(io.cur_obs_dev) + (size_t)gi * OD;
-    const float* sn = static_cast<const float*>(io.next_obs_dev) + (size_t)gi * OD;
-    float* po = static_cast<float*>(io.pool_obs_dev) + slot * OD;
-    float* pn = static_cast<float*>(io.pool_next_obs_dev) + slot * OD;
-    for (int d = lane; d < OD; d += 32) { po[d] = so[d]; pn[d] = sn[d]; }
-    if (AD > 0) {
-      const float* sa = static_cast<const float*>(io.act_dev) + (size_t)gi * AD;
-      float* pa = static_cast<float*>(io.pool_act_dev) + slot * AD;
-      for (int d = lane; d < AD; d += 32) pa[d] = sa[d];
+  const int row_base = blockIdx.x * kRB;
+  const float* so = static_cast<const float*>(io.cur_obs_dev) + (size_t)row_base * OD;
+  const float* sn = static_cast<const float*>(io.next_obs_dev) + (size_t)row_base * OD;
+  float* po = static_cast<float*>(io.pool_obs_dev);
+  float* pn = static_cast<float*>(io.pool_next_obs_dev);
+  const int n_here = min(kRB, n - row_base);
+#pragma unroll 4
+  for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {
+    const int r = idx / OD, d = idx - r * OD;
+    if (s_rem[r]) {
+      const size_t o = ((size_t)s_pid[r] * T + ptr) * OD + d;
+      po[o] = so[idx];
+      pn[o] = sn[idx];
+    }
+  }
+  if (AD > 0) {
+    const float* sa = static_cast<const float*>(io.act_dev) + (size_t)row_base * AD;
+    float* pa = static_cast<float*>(io.pool_act_dev);
+#pragma unroll 4
+    for (int idx = threadIdx.x; idx < n_here * AD; idx += kRB) {
+      const int r = idx / AD, d = idx - r * AD;
+      if (s_rem[r]) pa[((size_t)s_pid[r] * T + ptr) * AD + d] = sa[idx];
     }
   }
 }
@@ -208,13 +223,6 @@ extern "C" size_t cmbpo_rollout_scratch_bytes(int64_t n_paths) {
 }
 
 namespace cmbpo {
-// the pre-advance alive count is needed by the compaction after k_scan<2> overwrote it
-__global__ void k_snapshot(const void* state, int* out, int* hist) {
-  const int n = static_cast<const RolloutState*>(state)->n_alive;
-  *out = n;
-  if (hist) *hist = n;
-}
-
 // E: stable compaction of the surviving rows: next_obs -> new cur_obs, path ids follow
 __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const uint8_t* keep, const int* blk_off,
                                                       const int* n_before_dev) {
@@ -226,14 +234,16 @@ __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const 
   s_dst[threadIdx.x] = k ? dst : -1;
   if (k) static_cast<int*>(io.new_path_id_dev)[dst] = static_cast<const int*>(io.path_id_dev)[i];
   __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int OD = io.obs_dim;
-  for (int r = warp; r < kRB; r += 8) {
+  const int row_base = blockIdx.x * kRB;
+  const int n_here = min(kRB, n_before - row_base);
+  const float* src = static_cast<const float*>(io.next_obs_dev) + (size_t)row_base * OD;
+  float* dstp = static_cast<float*>(io.new_obs_dev);
+#pragma unroll 4
+  for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {   // flat element loop, see k_store
+    const int r = idx / OD, d = idx - r * OD;
     const int d0 = s_dst[r];
-    if (d0 < 0) continue;
-    const float* src = static_cast<const float*>(io.next_obs_dev) + (size_t)(blockIdx.x * kRB + r) * OD;
-    float* dstp = static_cast<float*>(io.new_obs_dev) + (size_t)d0 * OD;
-    for (int d = lane; d < OD; d += 32) dstp[d] = src[d];
+    if (d0 >= 0) dstp[(size_t)d0 * OD + d] = src[idx];
   }
 }
 }  // namespace cmbpo
@@ -253,11 +263,10 @@ extern "C" int cmbpo_rollout_advance(const cmbpo_rollout_io* io_, void* stream_)
   int* blk_a = reinterpret_cast<int*>(static_cast<uint8_t*>(io.scratch_dev) + off);
   int* blk_b = blk_a + nb + 1;
   int* snap = blk_b + nb;   // last word of blk_b's slack
-  k_snapshot<<<1, 1, 0, stream>>>(io.state_dev, snap, io.alive_hist_dev ? io.alive_hist_dev + io.step_index : nullptr);
   k_decide<<<nb, kRB, 0, stream>>>(io, certain, blk_a);
-  k_scan<1><<<1, 1024, 0, stream>>>(io, blk_a, nb);
+  k_scan<1><<<1, 1024, 0, stream>>>(io, blk_a, nb, snap, io.alive_hist_dev ? io.alive_hist_dev + io.step_index : nullptr);
   k_store<<<nb, kRB, 0, stream>>>(io, certain, blk_a, keep, blk_b);
-  k_scan<2><<<1, 1024, 0, stream>>>(io, blk_b, nb);
+  k_scan<2><<<1, 1024, 0, stream>>>(io, blk_b, nb, nullptr, nullptr);
   k_compact_dev<<<nb, kRB, 0, stream>>>(io, keep, blk_b, snap);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(g_roll_err, sizeof(g_roll_err), "rollout_advance: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }

@@ -314,6 +314,34 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
     for (int w = 0; w < kPostParts; ++w) x += red[tid][w];
     p.partials[(size_t)blockIdx.x * 4 + tid] = x;
   }
+  // ---- the last block to finish sums the partials in block order (deterministic) -> 4 means
+  __shared__ bool s_last;
+  __shared__ double sh[4][kPostParts];
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = atomicAdd(p.ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double s[4] = {0, 0, 0, 0};
+  for (int b = tid; b < (int)gridDim.x; b += kPostThreads)
+    for (int k = 0; k < 4; ++k) s[k] += (double)__ldcg(p.partials + (size_t)b * 4 + k);
+  for (int k = 0; k < 4; ++k) {
+    double x = s[k];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) sh[k][warp] = x;
+  }
+  __syncthreads();
+  if (tid < 4) {
+    double x = 0;
+    for (int w = 0; w < kPostParts; ++w) x += sh[tid][w];
+    const double n = (double)n_rows;
+    double denom = n;                                        // dkl_mean
+    if (tid == 1) denom = n * (double)E * (double)D;         // ensemble_mean_var over [E,B,D]
+    if (tid >= 2) denom = n * (double)n_slots_out;           // rew_mean / cost_mean
+    p.scalars[tid] = (float)(denom > 0 ? x / denom : 0.0);
+  }
+  if (tid == 0) *p.ticket = 0;   // ready for the next launch
 }
 
 // deterministic final reduction of the per-block partial sums -> 4 means

@@ -37,6 +37,8 @@ struct StepParams {
   float* ep_var_mean;        // [B]   mean_d(ensemble_ep_var) (model_sampler.py:428) (may be nullptr)
   float* ep_var;             // [B][D] ensemble_ep_var (fake_env.py:160) (may be nullptr)
   float* partials;           // [n_blocks][4] partial sums: dkl, var, rew, cost
+  unsigned int* ticket;      // zero-initialised block counter: the last block to finish reduces the partials
+  float* scalars;            // [4] ensemble_dkl_mean, ensemble_mean_var, rew_mean, cost_mean (fake_env.py:213-220)
 };
 
 int step_post_blocks(long long n_rows, int num_sms);
