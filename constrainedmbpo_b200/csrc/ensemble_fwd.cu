@@ -29,7 +29,8 @@
 namespace cmbpo {
 using namespace sm100;
 
-constexpr int kFwdThreads = 384;   // 12 warps (a multiple of 4 warps: ptxas sizes registers for it)
+constexpr int kFwdThreads = 640;   // 20 warps: 4 service warps + 2 streams x 2 column halves x 4 TMEM lane quadrants
+constexpr int kEpiWarpsPerStream = 8;
 
 struct SmemLayout {
   uint32_t off_a, off_a0, off_const, off_bar, off_tmem, total;
@@ -92,6 +93,18 @@ enum WaitCode : int {
   WC_MMA_A0 = 5, WC_MMA_AREADY = 6, WC_EPI_DFULL = 7
 };
 
+#ifdef CMBPO_TRACE
+#define TR_STAMP(i) do { g_stamp[i] = clock64(); } while (0)
+#define TR_STAMP_DECL long long g_stamp[2] = {0, 0}
+#define TR_STAMP_ARG , long long (&g_stamp)[2]
+#define TR_STAMP_PASS , g_stamp
+#else
+#define TR_STAMP(i)
+#define TR_STAMP_DECL
+#define TR_STAMP_ARG
+#define TR_STAMP_PASS
+#endif
+
 template <int ACT>
 __device__ __forceinline__ float activate(float g) {
   // g is the pre-activation, already halved for ACT_SWISH / ACT_SIGMOID
@@ -116,114 +129,111 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 // barrier `id` completes when the waiting warp (bar.sync) and the signalling warp (bar.arrive) are both
 // in; a waiting warp is parked by the hardware and takes no issue slots.  id == 0: no token protocol.
 __device__ __forceinline__ void token_wait(int id) {
-  if (id) asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
+  if (id) asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory");
 }
 __device__ __forceinline__ void token_pass(int id) {
-  if (id) asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory");
+  if (id) asm volatile("bar.arrive %0, 128;" ::"r"(id) : "memory");
 }
 
-// Convert W (32 or 16) accumulator columns starting at col0 to bf16 and store them into this
-// thread's row of the next layer's A tile (one 16-byte store per 8-column core-matrix row).
-template <int ACT, int W>
-__device__ __forceinline__ void convert_store(const uint32_t (&r)[32], int col0, uint32_t a_row) {
-  uint32_t o[W / 2];
+// Convert 16 accumulator columns starting at col0 to bf16 and store them into this thread's row of the
+// next layer's A tile (one 16-byte store per 8-column core-matrix row).
+template <int ACT>
+__device__ __forceinline__ void convert_store16(const uint32_t (&r)[16], int col0, uint32_t a_row) {
+  uint32_t o[8];
 #pragma unroll
-  for (int i = 0; i < W / 2; ++i)
+  for (int i = 0; i < 8; ++i)
     o[i] = pack_bf16x2(activate<ACT>(__uint_as_float(r[2 * i])), activate<ACT>(__uint_as_float(r[2 * i + 1])));
   const uint32_t dst = a_row + (uint32_t)(col0 >> 3) * 128u;
-#pragma unroll
-  for (int g = 0; g < W / 8; ++g) sts128(dst + 128u * g, o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
+  sts128(dst, o[0], o[1], o[2], o[3]);
+  sts128(dst + 128u, o[4], o[5], o[6], o[7]);
 }
 
-// Hidden-layer epilogue for one warp: accumulator (TMEM) -> activation -> bf16 -> A tile (smem).
-// One warp per TMEM lane quadrant and stream converts the whole row (all chunks); the two warps that
-// share an SM sub-partition belong to DIFFERENT streams, so the pass boundary of one stream (arrive ->
-// MMA -> D_FULL -> first TMEM load) sits in the shadow of the other stream's conversion and the XU pipe
-// (16 tanh/clk/SM -- the binding unit of this kernel) stays fed.  NPAD is compile-time for the common
-// layer widths: the whole pass is then one straight-line block in which the TMEM load of the next
-// chunk, the address arithmetic and the shared-memory stores are scheduled between the MUFUs.
-template <int ACT, int NPAD>
-__device__ __forceinline__ void hidden_epilogue_t(uint32_t d_addr, uint32_t a_row, int tok_wait, int tok_pass) {
-  constexpr int NFULL = NPAD / 32;
-  constexpr int NCH = NFULL + ((NPAD % 32) ? 1 : 0);
-  uint32_t ra[32], rb[32];
-  auto load = [&](int c, uint32_t (&r)[32]) {
-    if (c < NFULL) tmem_ld32(d_addr + 32 * c, r); else tmem_ld16_lo(d_addr + 32 * c, r);
-  };
-  auto finish = [&](int c, uint32_t (&r)[32]) {
-    if (c < NFULL) convert_store<ACT, 32>(r, 32 * c, a_row); else convert_store<ACT, 16>(r, 32 * c, a_row);
-  };
-  load(0, ra);
+// Hidden-layer epilogue for one warp: accumulator (TMEM) -> activation -> bf16 -> A tile (smem), for the
+// 16-column chunks [cb, ce) of this warp's 32 rows.  TWO warps (column halves) serve each TMEM lane
+// quadrant of a stream and run at the same time on one SM sub-partition: a single warp cannot keep the
+// XU pipe busy (measured 11.3-11.7 cycles per warp-wide MUFU.TANH against 8.4-8.9 for two warps,
+// tools/epi_probe2.cu), and the XU pipe (16 tanh/clk/SM) is the binding unit of this kernel.  The four
+// warps of a sub-partition (two per stream) hand an XU token back and forth, so the pass boundary of one
+// stream (arrive -> MMA -> D_FULL -> first TMEM load) sits in the shadow of the other stream's conversion.
+// CB / CE are compile-time for the common layer widths: the pass is then one straight-line block.
+template <int ACT, int CB, int CE>
+__device__ __forceinline__ void hidden_epilogue_t(uint32_t d_addr, uint32_t a_row, int tok_wait, int tok_pass TR_STAMP_ARG) {
+  uint32_t ra[16], rb[16];
+  if (CB < CE) tmem_ld16(d_addr + 16 * CB, ra);
   tmem_wait_ld();
   token_wait(tok_wait);          // first chunk already in registers: the MUFUs start right at the hand-over
+  TR_STAMP(0);
 #pragma unroll
-  for (int c = 0; c < NCH; c += 2) {
-    if (c > 0) tmem_wait_ld();
-    if (c + 1 < NCH) load(c + 1, rb);
-    finish(c, ra);
-    if (c + 1 < NCH) {
+  for (int c = CB; c < CE; c += 2) {
+    if (c > CB) tmem_wait_ld();
+    if (c + 1 < CE) tmem_ld16(d_addr + 16 * (c + 1), rb);
+    convert_store16<ACT>(ra, 16 * c, a_row);
+    if (c + 1 < CE) {
       tmem_wait_ld();
-      if (c + 2 < NCH) load(c + 2, ra);
-      finish(c + 1, rb);
+      if (c + 2 < CE) tmem_ld16(d_addr + 16 * (c + 2), ra);
+      convert_store16<ACT>(rb, 16 * (c + 1), a_row);
+    }
+  }
+  TR_STAMP(1);
+  token_pass(tok_pass);
+}
+
+// Same for an arbitrary (runtime) chunk range.
+template <int ACT>
+__device__ __forceinline__ void hidden_epilogue_any(uint32_t d_addr, int cb, int ce, uint32_t a_row, int tok_wait, int tok_pass) {
+  uint32_t ra[16], rb[16];
+  if (cb < ce) tmem_ld16(d_addr + 16 * cb, ra);
+  tmem_wait_ld();
+  token_wait(tok_wait);
+  for (int c = cb; c < ce; c += 2) {
+    if (c > cb) tmem_wait_ld();
+    if (c + 1 < ce) tmem_ld16(d_addr + 16 * (c + 1), rb);
+    convert_store16<ACT>(ra, 16 * c, a_row);
+    if (c + 1 < ce) {
+      tmem_wait_ld();
+      if (c + 2 < ce) tmem_ld16(d_addr + 16 * (c + 2), ra);
+      convert_store16<ACT>(rb, 16 * (c + 1), a_row);
     }
   }
   token_pass(tok_pass);
 }
 
-// Same for an arbitrary (runtime) layer width.
-template <int ACT>
-__device__ __forceinline__ void hidden_epilogue_any(uint32_t d_addr, int npad, uint32_t a_row, int tok_wait, int tok_pass) {
-  const int nfull = npad >> 5;                       // 32-wide chunks
-  const int nch = nfull + ((npad & 31) ? 1 : 0);     // + one 16-wide chunk at the end
-  uint32_t ra[32], rb[32];
-  auto load = [&](int c, uint32_t (&r)[32]) {
-    if (c < nfull) tmem_ld32(d_addr + 32 * c, r); else tmem_ld16_lo(d_addr + 32 * c, r);
-  };
-  auto finish = [&](int c, uint32_t (&r)[32]) {
-    if (c < nfull) convert_store<ACT, 32>(r, 32 * c, a_row); else convert_store<ACT, 16>(r, 32 * c, a_row);
-  };
-  load(0, ra);
-  tmem_wait_ld();
-  token_wait(tok_wait);
-  for (int c = 0; c < nch; c += 2) {
-    if (c > 0) tmem_wait_ld();
-    if (c + 1 < nch) load(c + 1, rb);
-    finish(c, ra);
-    if (c + 1 < nch) {
-      tmem_wait_ld();
-      if (c + 2 < nch) load(c + 2, ra);
-      finish(c + 1, rb);
-    }
-  }
-  token_pass(tok_pass);
+template <int ACT, int NPAD>
+__device__ __forceinline__ void hidden_epilogue_half(uint32_t d_addr, int half, uint32_t a_row, int tok_wait, int tok_pass TR_STAMP_ARG) {
+  constexpr int NCH = NPAD / 16, H0 = (NCH + 1) / 2;
+  if (half == 0) hidden_epilogue_t<ACT, 0, H0>(d_addr, a_row, tok_wait, tok_pass TR_STAMP_PASS);
+  else           hidden_epilogue_t<ACT, H0, NCH>(d_addr, a_row, tok_wait, tok_pass TR_STAMP_PASS);
 }
 
 // ones_col / ones_col+1 of the produced tile are the next layer's bias carriers (constant 1.0):
-// overwritten after the row's own stores.
+// overwritten, after the row's own stores, by the warp whose column range holds them.
 template <int ACT>
-__device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col, uint32_t a_row,
-                                                int tok_wait, int tok_pass) {
+__device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col, int half, uint32_t a_row,
+                                                int tok_wait, int tok_pass TR_STAMP_ARG) {
+  const int nch = npad >> 4, h0 = (nch + 1) >> 1;
+  const int cb = half ? h0 : 0, ce = half ? nch : h0;
   switch (npad) {
-    case 208: hidden_epilogue_t<ACT, 208>(d_addr, a_row, tok_wait, tok_pass); break;   // hidden 200 (BASELINE configs)
-    case 224: hidden_epilogue_t<ACT, 224>(d_addr, a_row, tok_wait, tok_pass); break;   // hidden 220 (FakeEnv default)
-    case 144: hidden_epilogue_t<ACT, 144>(d_addr, a_row, tok_wait, tok_pass); break;   // hidden 128 (V / VC critics)
-    case 80:  hidden_epilogue_t<ACT, 80>(d_addr, a_row, tok_wait, tok_pass); break;    // hidden 64 (CostNN)
-    default:  hidden_epilogue_any<ACT>(d_addr, npad, a_row, tok_wait, tok_pass); break;
+    case 208: hidden_epilogue_half<ACT, 208>(d_addr, half, a_row, tok_wait, tok_pass TR_STAMP_PASS); break;   // hidden 200 (BASELINE configs)
+    case 224: hidden_epilogue_half<ACT, 224>(d_addr, half, a_row, tok_wait, tok_pass TR_STAMP_PASS); break;   // hidden 220 (FakeEnv default)
+    case 144: hidden_epilogue_half<ACT, 144>(d_addr, half, a_row, tok_wait, tok_pass TR_STAMP_PASS); break;   // hidden 128 (V / VC critics)
+    case 80:  hidden_epilogue_half<ACT, 80>(d_addr, half, a_row, tok_wait, tok_pass TR_STAMP_PASS); break;    // hidden 64 (CostNN)
+    default:  hidden_epilogue_any<ACT>(d_addr, cb, ce, a_row, tok_wait, tok_pass); break;
   }
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
     const int k = ones_col + j;
-    asm volatile("st.shared.u16 [%0], %1;" ::"r"(a_row + (uint32_t)(k >> 3) * 128u + (uint32_t)(k & 7) * 2u),
-                 "h"((uint16_t)0x3F80) : "memory");
+    if ((k >> 4) >= cb && (k >> 4) < ce)
+      asm volatile("st.shared.u16 [%0], %1;" ::"r"(a_row + (uint32_t)(k >> 3) * 128u + (uint32_t)(k & 7) * 2u),
+                   "h"((uint16_t)0x3F80) : "memory");
   }
 }
 
 // Head epilogue for one warp: inverse output scaler on the mean, 2*log(s) shift on the log-variance
 // (bnn.py:878-893); `out` points at this thread's row inside the (tile block, member) region of the
 // tile-major scratch, column stride 128 floats: a warp's store covers 32 consecutive rows.
-__device__ __forceinline__ void head_epilogue(uint32_t d_addr, int npad, int n_head, const float* s_scale,
+__device__ __forceinline__ void head_epilogue(uint32_t d_addr, int c_begin, int c_end, int n_head, const float* s_scale,
                                               const float* s_shift, float* out, bool live) {
-  for (int c0 = 0; c0 < npad; c0 += 16) {
+  for (int c0 = c_begin; c0 < c_end; c0 += 16) {
     uint32_t r[16];
     tmem_ld16(d_addr + c0, r);
     float* colp = out + (size_t)c0 * kTileRows;
@@ -311,7 +321,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
       mbar_init(bar(BAR_A0_FULL + s), cta == 0 ? 2 : 1);  // leader: own fill + relayed peer fill
       mbar_init(bar(BAR_A0_EMPTY + s), 1);                // tcgen05.commit
       mbar_init(bar(BAR_D_FULL + s), 1);                  // tcgen05.commit
-      mbar_init(bar(BAR_A_READY + s), 8);                 // 4 epilogue warps of the stream x 2 CTAs
+      mbar_init(bar(BAR_A_READY + s), 2 * kEpiWarpsPerStream);   // 8 epilogue warps of the stream x 2 CTAs
     }
     fence_mbar_init();
   }
@@ -456,16 +466,17 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
   } else if (warp == 2) {
     // (TMEM allocation / release only)
   } else {
-    // ===== epilogue warps 4..11: TMEM lane quadrant q (the hardware ties a warp to lanes 32*(warp%4)..);
-    // warps 4..7 serve stream X, warps 8..11 stream Y
+    // ===== epilogue warps 4..19: TMEM lane quadrant q (the hardware ties a warp to lanes 32*(warp%4)..);
+    // warps 4..7 / 12..15 serve stream X (column half 0 / 1), warps 8..11 / 16..19 stream Y
     const int q = warp & 3;
-    const int s = (warp - 4) >> 2;
+    const int s = ((warp - 4) >> 2) & 1;
+    const int half = (warp - 4) >> 3;
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int row_in_tile = q * 32 + lane;
     const uint32_t d_addr = tmem_base + lane_base + s * kRegionCols;
     const uint32_t a_tile = smem_u32(smem + sl.off_a + s * pl.a_bytes) + (uint32_t)(row_in_tile & 7) * 16u;
     uint32_t dphase = 0;
-    TR_DECL(1 + s, cluster_id == 0 && cta == 0 && q == 0 && lane == 0);
+    TR_DECL(1 + s, cluster_id == 0 && cta == 0 && q == 0 && half == 0 && lane == 0);
     // XU token of this sub-partition: X waits on barrier 1+q / passes 5+q, Y the other way round.  Only
     // pairs that have both streams use it (hidden passes alternate X, Y, X, Y ...); Y opens the game
     // and keeps the token of its very last pass.
@@ -491,12 +502,20 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
             // next layer's A tile: 8-row group stride = npad (= next kpad) * 16 bytes
             const uint32_t a_row = a_tile + (uint32_t)(row_in_tile >> 3) * ((uint32_t)lp.npad * 16u);
             const bool keep = s == 1 && last_tok_pair && e == e_end - 1 && l == L - 2;
-            hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, a_row, use_tok ? tok_mine : 0,
-                                  (use_tok && !keep) ? tok_other : 0);
+            TR_STAMP_DECL;
+            hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, half, a_row, use_tok ? tok_mine : 0,
+                                  (use_tok && !keep) ? tok_other : 0 TR_STAMP_PASS);
+#ifdef CMBPO_TRACE
+            if (tr_base && tr_n + 2 <= kTraceSlots) {
+              tr_base[2 * tr_n] = g_stamp[0]; tr_base[2 * tr_n + 1] = 260 + l; ++tr_n;
+              tr_base[2 * tr_n] = g_stamp[1]; tr_base[2 * tr_n + 1] = 280 + l; ++tr_n;
+            }
+#endif
             fence_proxy_async_smem();      // generic-proxy smem writes -> visible to tcgen05.mma
           } else {
             float* out = p.heads + ((size_t)(blk * E + e) * pl.n_head) * kTileRows + row_in_tile;
-            head_epilogue(d_addr, lp.npad, pl.n_head, s_head_scale, s_head_shift, out, live);
+            const int hch = lp.npad >> 4, hh0 = (hch + 1) >> 1;   // 16-column chunks of the head, split like the hidden layers
+            head_epilogue(d_addr, 16 * (half ? hh0 : 0), 16 * (half ? hch : hh0), pl.n_head, s_head_scale, s_head_shift, out, live);
           }
           tc_fence_before();
           __syncwarp();
