@@ -16,6 +16,9 @@ cudaError_t pack_layer(const float* W, const float* b, uint8_t* img, int E, cons
                        uint32_t blk_bytes, cudaStream_t stream);
 cudaError_t launch_ensemble_fwd(const FwdParams& p, int hidden_act, int num_sms, cudaStream_t stream);
 cudaError_t launch_stage_inputs(const StageParams& p, int num_sms, cudaStream_t stream);
+cudaError_t pack_wide_layer(const float* W, const float* b, uint8_t* img, float* bias_tab, int E,
+                            const WideLayerPlan& lp, cudaStream_t stream);
+cudaError_t launch_wide_layer(const WideParams& p, int act, int num_sms, cudaStream_t stream);
 }  // namespace cmbpo
 
 using namespace cmbpo;
@@ -43,10 +46,17 @@ struct Handle {
   int hidden_act = 0;
   bool scalers_set = false;
   bool profiling = false;
+  // wide path (wide_fwd.cu): any layer wider than the fused kernel's 254 columns, or CMBPO_FORCE_WIDE=1
+  bool wide = false;
+  WideLayerPlan wl[kMaxLayers];
+  uint8_t* wimg_wide = nullptr;
+  float* bias_wide = nullptr;
+  int wide_max_kc = 0;         // widest hidden activation image, in 64-column chunks
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
 };
 
 static inline int roundup(int x, int m) { return (x + m - 1) / m * m; }
+constexpr long long kWideSlabRows = 131072;   // rows per pass of the wide path (bounds the activation images)
 
 extern "C" const char* cmbpo_last_error(void) { return g_err.c_str(); }
 
@@ -91,9 +101,10 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
     lp.act = cfg->layer_act[l];
     if (lp.act < 0 || lp.act > CMBPO_ACT_SIGMOID) { delete h; return fail(CMBPO_ERR_ARG, "unknown activation id"); }
     lp.prescale = (lp.act == CMBPO_ACT_SWISH || lp.act == CMBPO_ACT_SIGMOID) ? 0.5f : 1.0f;
-    if (lp.kpad > kRegionCols || lp.npad > kRegionCols) {
+    if (lp.kpad > kRegionCols || lp.npad > kRegionCols) h->wide = true;   // beyond one 256-column accumulator per stream
+    if (lp.k_real > kWideMaxWidth || lp.n_real > kWideMaxWidth) {
       delete h;
-      return fail(CMBPO_ERR_UNSUPPORTED, "layer wider than 254: outside this kernel (one 256-column TMEM accumulator per row-tile stream)");
+      return fail(CMBPO_ERR_UNSUPPORTED, "layer wider than 2048 columns");
     }
     lp.bytes = (uint32_t)(lp.npad / 2) * lp.kpad * 2u;
     lp.smem_off = off;
@@ -107,16 +118,41 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
       return fail(CMBPO_ERR_UNSUPPORTED, "hidden layers must share one activation (constructor.py:57-60)");
     }
   pl.blk_bytes = off;
-  if (!plan_fwd_smem(pl)) {
-    delete h;
-    return fail(CMBPO_ERR_UNSUPPORTED, "layer shapes do not fit the 227 KB shared-memory budget (two activation tiles + a two-slot weight ring)");
+  if (const char* fw = getenv("CMBPO_FORCE_WIDE")) if (fw[0] == '1') h->wide = true;   // test hook: same nets on both kernels
+  if (!h->wide && !plan_fwd_smem(pl)) h->wide = true;   // shapes beyond the fused kernel's shared-memory budget
+  size_t wide_img = 0, wide_bias = 0;
+  if (h->wide) {
+    if (roundup(n_head, 16) > kWideNC) {
+      delete h;
+      return fail(CMBPO_ERR_UNSUPPORTED, "head wider than 256 columns");
+    }
+    for (int l = 0; l < L; ++l) {
+      WideLayerPlan& w = h->wl[l];
+      w.k_real = pl.layer[l].k_real; w.n_real = pl.layer[l].n_real;
+      w.kpad = roundup(w.k_real, kWideKC);
+      w.npad = (l < L - 1) ? roundup(w.n_real, kWideKC) : roundup(w.n_real, 16);
+      w.k_chunks = w.kpad / kWideKC;
+      w.n_chunks = (w.npad + kWideNC - 1) / kWideNC;
+      w.act = pl.layer[l].act; w.prescale = pl.layer[l].prescale;
+      w.w_off = wide_img; w.b_off = wide_bias;
+      wide_img += (size_t)E * w.n_chunks * 2 * w.k_chunks * kWideBlk;
+      wide_bias += (size_t)E * w.npad;
+      if (l < L - 1 && w.npad / kWideKC > h->wide_max_kc) h->wide_max_kc = w.npad / kWideKC;
+    }
   }
   CU(cudaSetDevice(device), "cudaSetDevice");
   cudaDeviceProp prop;
   CU(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
   h->num_sms = prop.multiProcessorCount;
-  CU(cudaMalloc(&h->wimg, (size_t)E * 2 * pl.blk_bytes), "cudaMalloc(wimg)");
-  CU(cudaMemset(h->wimg, 0, (size_t)E * 2 * pl.blk_bytes), "cudaMemset(wimg)");
+  if (h->wide) {
+    CU(cudaMalloc(&h->wimg_wide, wide_img), "cudaMalloc(wimg_wide)");
+    CU(cudaMemset(h->wimg_wide, 0, wide_img), "cudaMemset(wimg_wide)");
+    CU(cudaMalloc(&h->bias_wide, wide_bias * sizeof(float)), "cudaMalloc(bias_wide)");
+    CU(cudaMemset(h->bias_wide, 0, wide_bias * sizeof(float)), "cudaMemset(bias_wide)");
+  } else {
+    CU(cudaMalloc(&h->wimg, (size_t)E * 2 * pl.blk_bytes), "cudaMalloc(wimg)");
+    CU(cudaMemset(h->wimg, 0, (size_t)E * 2 * pl.blk_bytes), "cudaMemset(wimg)");
+  }
   CU(cudaMalloc(&h->consts, sizeof(float) * (2 * pl.in_dim + 2 * n_head)), "cudaMalloc(consts)");
   CU(cudaMalloc(&h->elites_dev, sizeof(int) * 64), "cudaMalloc(elites)");
   CU(cudaMalloc(&h->status_dev, sizeof(int)), "cudaMalloc(status)");
@@ -139,7 +175,7 @@ extern "C" void cmbpo_destroy(void* handle) {
   Handle* h = static_cast<Handle*>(handle);
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->wimg); cudaFree(h->consts); cudaFree(h->elites_dev); cudaFree(h->status_dev); cudaFree(h->ticket_dev);
+  cudaFree(h->wimg); cudaFree(h->wimg_wide); cudaFree(h->bias_wide); cudaFree(h->consts); cudaFree(h->elites_dev); cudaFree(h->status_dev); cudaFree(h->ticket_dev);
   delete h;
 }
 
@@ -148,8 +184,13 @@ extern "C" int cmbpo_set_weights(void* handle, int32_t layer, const float* w_dev
   if (!h || !w_dev) return fail(CMBPO_ERR_ARG, "cmbpo_set_weights: null argument");
   if (layer < 0 || layer >= h->plan.L) return fail(CMBPO_ERR_ARG, "cmbpo_set_weights: layer out of range");
   CU(cudaSetDevice(h->device), "cudaSetDevice");
-  CU(pack_layer(w_dev, b_dev, h->wimg, h->plan.E, h->plan.layer[layer], h->plan.blk_bytes, (cudaStream_t)stream),
-     "pack_layer");
+  if (h->wide) {
+    CU(pack_wide_layer(w_dev, b_dev, h->wimg_wide + h->wl[layer].w_off, h->bias_wide + h->wl[layer].b_off, h->plan.E,
+                       h->wl[layer], (cudaStream_t)stream), "pack_wide_layer");
+  } else {
+    CU(pack_layer(w_dev, b_dev, h->wimg, h->plan.E, h->plan.layer[layer], h->plan.blk_bytes, (cudaStream_t)stream),
+       "pack_layer");
+  }
   h->layers_set |= (1u << layer);
   return CMBPO_OK;
 }
@@ -209,7 +250,16 @@ static inline long long row_stride_for(long long n_rows) { return (n_rows + kTil
 // workspace = head scratch | step_post partial sums | staged layer-0 tiles (E input slots)
 static size_t a0_slot_bytes(const Handle* h, long long rows) {
   const long long rows_pad = (rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
-  return (size_t)rows_pad * h->plan.layer[0].kpad * 2u;
+  return (size_t)rows_pad * (h->wide ? h->wl[0].kpad : h->plan.layer[0].kpad) * 2u;
+}
+// wide path: two ping-pong activation images [E slots][slab 128-row blocks][widest hidden K chunks]
+static long long wide_slab_pad(long long rows) {
+  const long long r = rows < kWideSlabRows ? rows : kWideSlabRows;
+  return (r + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
+}
+static size_t wide_act_bytes(const Handle* h, long long rows) {
+  if (!h->wide) return 0;
+  return (size_t)h->plan.E * (size_t)(wide_slab_pad(rows) / kTileRows) * h->wide_max_kc * kWideBlk;
 }
 static size_t ws_partials_offset(const Handle* h, long long rows) {
   return (size_t)h->plan.E * h->plan.n_head * row_stride_for(rows) * sizeof(float);
@@ -223,7 +273,7 @@ extern "C" size_t cmbpo_workspace_bytes(void* handle, int64_t max_rows) {
   Handle* h = static_cast<Handle*>(handle);
   if (!h || max_rows < 0) return 0;
   const ModelPlan& pl = h->plan;
-  return ws_a0_offset(h, max_rows) + (size_t)pl.E * a0_slot_bytes(h, max_rows) + 256;
+  return ws_a0_offset(h, max_rows) + (size_t)pl.E * a0_slot_bytes(h, max_rows) + 256 + 2 * wide_act_bytes(h, max_rows) + 256;
 }
 
 static int check_ready(Handle* h) {
@@ -261,7 +311,8 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
       ++d;
     }
   sp.n_slots = (ndim == 3) ? pl.E : 1;
-  sp.in_dim = pl.in_dim; sp.kpad = pl.layer[0].kpad;
+  sp.in_dim = pl.in_dim; sp.kpad = h->wide ? h->wl[0].kpad : pl.layer[0].kpad;
+  sp.chunked = h->wide ? 1 : 0;
   sp.in_mu = h->consts; sp.in_inv = h->consts + pl.in_dim;
   sp.n_rows_dev = n_rows_dev; sp.n_rows = n_rows;
   sp.slot_stride_bytes = (long long)a0_slot_bytes(h, n_rows);
@@ -295,7 +346,48 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
     CU(cudaEventCreate(&ev1), "cudaEventCreate");
     CU(cudaEventRecord(ev0, stream), "cudaEventRecord");
   }
-  CU(launch_ensemble_fwd(p, h->hidden_act, h->num_sms, stream), "launch_ensemble_fwd");
+  if (!h->wide) {
+    CU(launch_ensemble_fwd(p, h->hidden_act, h->num_sms, stream), "launch_ensemble_fwd");
+  } else {
+    // wide path: per row slab, one launch per FC layer; activations ping-pong between two bf16 images
+    const size_t act_bytes = wide_act_bytes(h, n_rows);
+    uint8_t* act0 = sp.a0img + (((size_t)pl.E * a0_slot_bytes(h, n_rows) + 255) & ~(size_t)255);
+    uint8_t* actbuf[2] = {act0, act0 + ((act_bytes + 255) & ~(size_t)255)};
+    const long long slab_blocks = wide_slab_pad(n_rows) / kTileRows;
+    for (long long row0 = 0; row0 < n_rows; row0 += kWideSlabRows) {
+      const long long slab_rows = (n_rows - row0 < kWideSlabRows) ? n_rows - row0 : kWideSlabRows;
+      for (int l = 0; l < pl.L; ++l) {
+        WideParams wp;
+        memset(&wp, 0, sizeof(wp));
+        wp.lp = h->wl[l];
+        wp.E = pl.E; wp.n_head = pl.n_head; wp.is_head = (l == pl.L - 1) ? 1 : 0;
+        wp.w_img = h->wimg_wide + h->wl[l].w_off;
+        wp.bias = h->bias_wide + h->wl[l].b_off;
+        for (int e = 0; e < pl.E; ++e) {
+          wp.member_of_slot[e] = p.member_of_slot[e];
+          wp.input_of_slot[e] = (l == 0) ? p.input_of_slot[e] : e;
+        }
+        if (l == 0) {
+          wp.a_img = sp.a0img + (size_t)(row0 / kTileRows) * h->wl[0].k_chunks * kWideBlk;
+          wp.a_slot_stride = sp.slot_stride_bytes;
+          wp.per_slot_input = p.per_slot_input;
+        } else {
+          wp.a_img = actbuf[(l - 1) & 1];
+          wp.a_slot_stride = (long long)slab_blocks * h->wl[l].k_chunks * kWideBlk;
+          wp.per_slot_input = 1;
+        }
+        wp.out_img = actbuf[l & 1];
+        wp.out_slot_stride = (long long)slab_blocks * (h->wl[l].npad / kWideKC) * kWideBlk;
+        wp.heads = heads;
+        wp.head_blk0 = row0 / kTileRows;
+        wp.head_scale = p.head_scale; wp.head_shift = p.head_shift;
+        wp.n_rows_dev = n_rows_dev; wp.n_rows = n_rows;
+        wp.row0 = row0; wp.slab_rows = slab_rows;
+        wp.status = h->status_dev;
+        CU(launch_wide_layer(wp, h->wl[l].act, h->num_sms, stream), "launch_wide_layer");
+      }
+    }
+  }
   if (h->profiling) {
     CU(cudaEventRecord(ev1, stream), "cudaEventRecord");
     h->prof_events.emplace_back(ev0, ev1);

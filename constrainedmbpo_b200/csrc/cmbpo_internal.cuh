@@ -58,6 +58,7 @@ struct StageParams {
   long long seg_slot_stride[kMaxSeg];  // elements between input slots (3-D input), else 0
   int n_slots;                         // 1 (2-D input shared by all members) or E (3-D, fc.py:107-108)
   int in_dim, kpad;
+  int chunked;                         // 1: wide-path image (K chunks of 64, no bias-carrier columns)
   const float* in_mu;                  // [in_dim] scaler_in mean          (utils.py:161)
   const float* in_inv;                 // [in_dim] 1 / max(sqrt(var)*sc, 1e-2)
   const int* n_rows_dev;               // optional device scalar with the live row count
@@ -82,6 +83,53 @@ struct FwdParams {
   float* heads;                 // out: tile-major head scratch (head_index), scaled mean | shifted logvar
   int* status;                  // watchdog / error word
   long long* trace;             // debug timeline, only read by -DCMBPO_TRACE builds
+};
+
+// ---------------------------------------------------------------------------------------
+// Wide path (any layer width up to kWideMaxWidth, e.g. the reference's shipped (512, 512) nets,
+// examples/config/antsafe/cmbpo_uc.py:36): one launch per FC layer, activations as bf16 tile images
+// in HBM/L2 between the launches.  Image layout ("chunked canonical"): rows in blocks of 128, K in
+// chunks of kWideKC columns; one (row block, K chunk) is a contiguous 16 KB block holding 8x8 core
+// matrices: element (r, k) at (r/8)*1024 + (k/8)*128 + (r%8)*16 + (k%8)*2 -- the SWIZZLE_NONE K-major
+// operand layout of tcgen05.mma with LBO = 128, SBO = 1024, so a stage is filled by one bulk copy.
+// ---------------------------------------------------------------------------------------
+constexpr int kWideKC = 64;            // K columns per pipeline stage
+constexpr int kWideNC = 256;           // N columns per accumulator (one tcgen05.mma N)
+constexpr int kWideMaxWidth = 2048;
+constexpr uint32_t kWideBlk = 128u * kWideKC * 2u;   // 16 KB: one (128 rows, 64 k) block
+
+struct WideLayerPlan {
+  int k_real, n_real;
+  int kpad;              // roundup(k_real, 64)
+  int npad;              // hidden: roundup(n_real, 64) (= next layer's kpad); head: roundup(n_real, 16)
+  int k_chunks, n_chunks;
+  int act;
+  float prescale;
+  size_t w_off;          // byte offset of this layer in the wide weight image
+  size_t b_off;          // float offset of this layer in the bias table ([E][npad], prescaled)
+};
+
+struct WideParams {
+  WideLayerPlan lp;
+  int E, n_head, is_head;
+  const uint8_t* w_img;        // this layer: [slot e][n chunk][cta half][k chunk] blocks of kWideBlk bytes
+  const float* bias;           // this layer: [E][npad]
+  const uint8_t* a_img;        // input image [input slot][128-row block][k chunk]
+  long long a_slot_stride;     // bytes between input slots (0: one input shared by all members)
+  uint8_t* out_img;            // hidden: next layer's input image [slot e][128-row block][k chunk]
+  long long out_slot_stride;
+  float* heads;                // head: tile-major fp32 scratch (head_index)
+  long long head_blk0;         // first 128-row block of this slab inside the head scratch
+  const float* head_scale;
+  const float* head_shift;
+  int member_of_slot[kMaxMembers];
+  int input_of_slot[kMaxMembers];
+  int per_slot_input;
+  const int* n_rows_dev;       // optional live row count of the WHOLE batch
+  long long n_rows;            // rows of the whole batch if n_rows_dev == nullptr
+  long long row0;              // first row of this slab
+  long long slab_rows;         // rows of this slab (multiple of 256 except for the last slab)
+  int* status;
 };
 
 }  // namespace cmbpo

@@ -571,7 +571,7 @@ __global__ void __launch_bounds__(256) stage_inputs_kernel(const StageParams p) 
             const float raw = __ldg(p.seg_ptr[sg] + (size_t)slot * p.seg_slot_stride[sg] + (size_t)row * p.seg_width[sg] + kk);
             const float mu = p.in_mu ? p.in_mu[k] : 0.f, inv = p.in_inv ? p.in_inv[k] : 1.f;
             x = (raw - mu) * inv;
-          } else if (k < p.in_dim + 2) {
+          } else if (k < p.in_dim + 2 && !p.chunked) {
             x = 1.0f;
           }
         }
@@ -579,8 +579,11 @@ __global__ void __launch_bounds__(256) stage_inputs_kernel(const StageParams p) 
       }
       packed[h2] = pack_bf16x2(v[0], v[1]);
     }
-    uint8_t* dst = p.a0img + (size_t)slot * p.slot_stride_bytes + (size_t)blk * blk_bytes +
-                   (size_t)(r >> 3) * ((size_t)kg * 128) + (size_t)g8 * 128 + (size_t)(r & 7) * 16;
+    uint8_t* dst = p.a0img + (size_t)slot * p.slot_stride_bytes + (size_t)blk * blk_bytes;
+    if (p.chunked)   // [k chunk of 64][8-row group][k group][row][k]: cmbpo_internal.cuh "chunked canonical"
+      dst += (size_t)(g8 >> 3) * kWideBlk + (size_t)(r >> 3) * 1024 + (size_t)(g8 & 7) * 128 + (size_t)(r & 7) * 16;
+    else
+      dst += (size_t)(r >> 3) * ((size_t)kg * 128) + (size_t)g8 * 128 + (size_t)(r & 7) * 16;
     *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
   }
 }
