@@ -363,7 +363,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
           ++fill_n; progress = true;
         }
         if (cta == 1 && relay_n < fill_n && mbar_try_wait(bar(BAR_W_FULL + r_slot), r_use & 1)) {
-          mbar_arrive_cluster(bar(BAR_W_FULL + r_slot), 0);
+          mbar_arrive_cluster_light(bar(BAR_W_FULL + r_slot), 0);
           if (++r_slot == S) { r_slot = 0; ++r_use; }
           ++relay_n; progress = true;
         }
@@ -451,7 +451,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
             ++fill_n[s]; progress = true;
           }
           if (cta == 1 && relay_n[s] < fill_n[s] && mbar_try_wait(bar(BAR_A0_FULL + s), (uint32_t)relay_n[s] & 1)) {
-            mbar_arrive_cluster(bar(BAR_A0_FULL + s), 0);
+            mbar_arrive_cluster_light(bar(BAR_A0_FULL + s), 0);
             ++relay_n[s]; progress = true;
           }
         }

@@ -108,26 +108,33 @@ __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __gri
       long long fill_n = 0, relay_n = 0;
       int f_stage = 0, r_stage = 0, f_j = 0; uint32_t f_use = 0, r_use = 0;
       uint32_t idle = 0;
+      // per-item state, decoded once per item (the 64-bit divisions of the item walk are slow on one thread)
+      const uint8_t* a_src = nullptr; const uint8_t* b_src = nullptr; uint32_t b_bytes = 0;
       while (fill_n < total || (cta == 1 && relay_n < total)) {
         bool progress = false;
         if (fill_n < total && (f_use == 0 || mbar_try_wait(bar(WB_EMPTY + f_stage), (f_use - 1) & 1))) {
-          const int e = it.slot(), tile = it.tile(), c = it.chunk();
-          const int chunk_n = min(kWideNC, lp.npad - c * kWideNC);
-          const uint32_t b_bytes = (uint32_t)(chunk_n >> 1) * 128u;
-          const int in_slot = p.per_slot_input ? p.input_of_slot[e] : 0;
-          const uint8_t* a_src = p.a_img + (size_t)in_slot * p.a_slot_stride +
-                                 ((size_t)(tile * 2 + (int)cta) * KC + f_j) * kWideBlk;
-          const uint8_t* b_src = p.w_img + ((((size_t)p.member_of_slot[e] * NCH + c) * 2 + cta) * KC + f_j) * kWideBlk;
+          if (f_j == 0) {
+            const int e = it.slot(), tile = it.tile(), c = it.chunk();
+            const int chunk_n = min(kWideNC, lp.npad - c * kWideNC);
+            b_bytes = (uint32_t)(chunk_n >> 1) * 128u;
+            const int in_slot = p.per_slot_input ? p.input_of_slot[e] : 0;
+            a_src = p.a_img + (size_t)in_slot * p.a_slot_stride + (size_t)(tile * 2 + (int)cta) * KC * kWideBlk;
+            b_src = p.w_img + (((size_t)p.member_of_slot[e] * NCH + c) * 2 + cta) * KC * kWideBlk;
+          }
           const uint32_t dst = smem_u32(smem + (uint32_t)f_stage * kWideStageBytes);
           mbar_arrive_expect_tx(bar(WB_FULL + f_stage), kWideBlk + b_bytes);
           bulk_g2s(dst, a_src, kWideBlk, bar(WB_FULL + f_stage));
           bulk_g2s(dst + kWideBlk, b_src, b_bytes, bar(WB_FULL + f_stage));
+          a_src += kWideBlk; b_src += kWideBlk;
           if (++f_j == KC) { f_j = 0; it.next(); }
           if (++f_stage == kWideStages) { f_stage = 0; ++f_use; }
           ++fill_n; progress = true;
         }
         if (cta == 1 && relay_n < fill_n && mbar_try_wait(bar(WB_FULL + r_stage), r_use & 1)) {
-          mbar_arrive_cluster(bar(WB_FULL + r_stage), 0);
+          // light (default-semantics) arrive: the data it announces was written by the async proxy and is
+          // read by the async proxy (tcgen05.mma); the .release.cluster form costs a MEMBAR.ALL.GPU + L1
+          // invalidate per K chunk, which alone held this kernel at ~2000 cycles per stage
+          mbar_arrive_cluster_light(bar(WB_FULL + r_stage), 0);
           if (++r_stage == kWideStages) { r_stage = 0; ++r_use; }
           ++relay_n; progress = true;
         }
