@@ -37,6 +37,14 @@ WORKLOADS = {
                                          mode="uncertainty", T=30, rows=100_000, dkl_depth=5, cost=True),
     "halfcheetah_schedule_L10_1M": dict(env="halfcheetah", obs=17, act=6, hidden=(200, 200, 200, 200), E=7, K=5,
                                         mode="schedule", T=10, rows=1_000_000, dkl_depth=0, cost=False),
+    # the shape every shipped CMBPO config uses (examples/config/antsafe/cmbpo_uc.py:36): two 512-wide hidden
+    # layers -> the layer-at-a-time wide kernel (wide_fwd.cu)
+    "antsafe_shipped_2x512_uncertainty_H30_100k": dict(env="antsafe", obs=29, act=8, hidden=(512, 512), E=7, K=5,
+                                                       mode="uncertainty", T=30, rows=100_000, dkl_depth=5, cost=True),
+    "antsafe_step_1M_4x512": dict(env="antsafe", obs=29, act=8, hidden=(512, 512, 512, 512), E=7, K=5,
+                                  mode="schedule", T=2, rows=1_000_000, dkl_depth=0, cost=True),
+    "antsafe_step_256k_4x1024": dict(env="antsafe", obs=29, act=8, hidden=(1024, 1024, 1024, 1024), E=7, K=5,
+                                     mode="schedule", T=2, rows=262_144, dkl_depth=0, cost=True),
     "antsafe_step_1M": dict(env="antsafe", obs=29, act=8, hidden=(200, 200, 200, 200), E=7, K=5,
                             mode="schedule", T=2, rows=1_000_000, dkl_depth=0, cost=True),
 }
@@ -339,7 +347,12 @@ def run_gpu(args, w, wname):
                          f"{r['transitions']} transitions in {r['seconds']:.2f} s; TF 1.14 unavailable -> fp32 op-for-op "
                          f"port (torch BLAS GEMMs + NumPy post-processing, 64k-row chunks)"}
 
-    kernels_per_sampler_step = 10  # stub policy, ensemble fwd, step post, scalar reduce, 6 bookkeeping kernels
+    wide = max(w["hidden"]) > 254
+    fwd_kernel = "wide_layer_kernel" if wide else "ensemble_fwd_kernel"
+    # stub policy, input staging, ensemble forward (fused: 1 launch; wide: one per FC layer and 131072-row slab),
+    # step post, 6 bookkeeping kernels
+    fwd_launches = (len(w["hidden"]) + 1) * ((rows + 131071) // 131072) if wide else 1
+    kernels_per_sampler_step = 9 + fwd_launches
     out = {
         "metric": "rollout transitions/sec (7-member ensemble step)",
         "value": value, "unit": "transitions/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -355,7 +368,7 @@ def run_gpu(args, w, wname):
         "e2e": {"value": e2e_val, "unit": "transitions/s", "h2d_bytes_per_step": int(start_host.numel() * 4),
                 "d2h_bytes_per_step": int(rec * per_rollout), "steps": e2e_steps},
         "gpu_launches": int(kernels_per_sampler_step * (w["T"] - 1) * args.steps),
-        "roofline": {"bound": "tensor", "kernel": "ensemble_fwd_kernel", "achieved": achieved_tf, "peak": peak,
+        "roofline": {"bound": "tensor", "kernel": fwd_kernel, "achieved": achieved_tf, "peak": peak,
                      "unit": "TFLOP/s", "frac": achieved_tf / peak, "traffic": None,
                      "peak_source": f"{peaks['source']} bf16 sustained (burst {peaks['bf16_burst']})",
                      "flops_per_row": F, "launches_per_rollout": launches_fwd,
