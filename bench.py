@@ -45,6 +45,11 @@ WORKLOADS = {
                                   mode="schedule", T=2, rows=1_000_000, dkl_depth=0, cost=True),
     "antsafe_step_256k_4x1024": dict(env="antsafe", obs=29, act=8, hidden=(1024, 1024, 1024, 1024), E=7, K=5,
                                      mode="schedule", T=2, rows=262_144, dkl_depth=0, cost=True),
+    # BASELINE.json configs[3]: Humanoid-shaped ensemble (MBPO-truncated 45-dim obs, 17 act), 'iv_gae' rollouts
+    # (every member rolls its own state, 3-D FakeEnv.step) with the static cost head; 1M start states over 8 GPUs
+    # = 125k per GPU, maxroll 12
+    "humanoidsafe_iv_gae_H12_125k": dict(env="humanoidsafe", obs=45, act=17, hidden=(200, 200, 200, 200), E=7, K=5,
+                                         mode="iv_gae", T=12, rows=125_000, dkl_depth=0, cost=True),
     "antsafe_step_1M": dict(env="antsafe", obs=29, act=8, hidden=(200, 200, 200, 200), E=7, K=5,
                             mode="schedule", T=2, rows=1_000_000, dkl_depth=0, cost=True),
 }
@@ -58,7 +63,10 @@ def flops_per_row(w):
 
 
 def bytes_per_transition(w):
-    """fp32 record that reaches the model pool: obs, act, next_obs, rew, cost, dyn_error + term byte."""
+    """fp32 record that reaches the model pool: obs, act, next_obs, rew, cost, dyn_error + term byte
+    ('iv_gae': one obs/act/next_obs/rew/cost/term per member, modelbuffer.py:48-51)."""
+    if w["mode"] == "iv_gae":
+        return w["E"] * (4 * (2 * w["obs"] + w["act"] + 2) + 1) + 4
     return 4 * (2 * w["obs"] + w["act"] + 3) + 1
 
 

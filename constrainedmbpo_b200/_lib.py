@@ -74,7 +74,19 @@ class cmbpo_rollout_io(C.Structure):
         ("pool_dyn_error_dev", C.c_void_p), ("pool_populated_dev", C.c_void_p),
         ("new_obs_dev", C.c_void_p), ("new_path_id_dev", C.c_void_p),
         ("scratch_dev", C.c_void_p), ("scratch_bytes", C.c_size_t),
-        ("alive_hist_dev", C.c_void_p),
+        ("alive_hist_dev", C.c_void_p), ("n_members", C.c_int32),
+    ]
+
+
+class cmbpo_pack_io(C.Structure):
+    _fields_ = [
+        ("n_paths", C.c_int64), ("max_path_length", C.c_int32), ("obs_dim", C.c_int32), ("act_dim", C.c_int32),
+        ("n_members", C.c_int32), ("row_offset", C.c_int64),
+        ("pool_obs_dev", C.c_void_p), ("pool_act_dev", C.c_void_p), ("pool_next_obs_dev", C.c_void_p),
+        ("pool_rew_dev", C.c_void_p), ("pool_cost_dev", C.c_void_p), ("pool_term_dev", C.c_void_p),
+        ("pool_dyn_error_dev", C.c_void_p), ("pool_populated_dev", C.c_void_p),
+        ("records_dev", C.c_void_p), ("capacity", C.c_int64), ("count_dev", C.c_void_p),
+        ("scratch_dev", C.c_void_p), ("scratch_bytes", C.c_size_t),
     ]
 
 
@@ -96,8 +108,11 @@ SYMBOLS = {
     "cmbpo_profile_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cmbpo_rollout_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "cmbpo_rollout_advance": (C.c_int, [C.POINTER(cmbpo_rollout_io), C.c_void_p]),
+    "cmbpo_record_width": (C.c_int32, [C.c_int32, C.c_int32, C.c_int32]),
+    "cmbpo_pack_scratch_bytes": (C.c_size_t, [C.c_int64]),
+    "cmbpo_pack_records": (C.c_int, [C.POINTER(cmbpo_pack_io), C.c_void_p]),
     "cmbpo_stub_policy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
-                                    C.c_int32, C.c_int32, C.c_void_p]),
+                                    C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
 }
 
 _lib = None

@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* ce
       // float64 accumulator + float32 increment, compared with a Python float (model_sampler.py:311-312)
       const double nd = io.dkl_accum_dev[pid] + (double)static_cast<const float*>(io.dkl_path_dev)[i];
       unc = nd >= io.dkl_lim;
-    }
+    }   // mode 2 ('iv_gae'): no uncertainty cutoff in the sampler (model_sampler.py:315)
     c = unc ? 0 : 1;
     certain[i] = (uint8_t)c;
   }
@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(1024) k_scan(cmbpo_rollout_io io, int* blk_cnt
     if (PHASE == 1) {
       // model_sampler.py:327-332: n = total_samples + alive - too_uncertain - max_samples
       long long n_early = 0;
-      if (io.max_samples > 0) {
+      if (io.max_samples > 0 && io.mode != 2) {   // :327 `max_samples and not rollout_mode=='iv_gae'`
         n_early = st->total_samples + (long long)total - io.max_samples;
         if (n_early < 0) n_early = 0;
         if (n_early > total) n_early = total;
@@ -139,19 +139,26 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
   const bool path_end = (ptr + 1) >= (T - 1);  // path_length after increment >= max_path_length-1
   __shared__ int s_pid[kRB];
   __shared__ uint8_t s_rem[kRB];
+  // 'iv_gae' (mode 2): every per-transition array carries a leading member axis -- step arrays
+  // [E][n_paths (capacity)][.], pools [E][n_paths][T][.] (modelbuffer.py:48-51,:134-150)
+  const int E = (io.mode == 2 && io.n_members > 1) ? io.n_members : 1;
+  const size_t cap = (size_t)io.n_paths;
   int pid = 0;
-  bool term = false;
+  bool term = false;   // 2-D: the row's terminal; iv_gae: np.any(terminal, axis=0) (model_sampler.py:445)
   if (i < n) {
     pid = static_cast<const int*>(io.path_id_dev)[i];
-    term = static_cast<const uint8_t*>(io.term_dev)[i] != 0;
+    for (int e = 0; e < E; ++e) term = term || static_cast<const uint8_t*>(io.term_dev)[e * cap + i] != 0;
   }
   s_pid[threadIdx.x] = pid;
   s_rem[threadIdx.x] = remaining ? 1 : 0;
   if (remaining) {
     const size_t slot = (size_t)pid * T + ptr;
-    static_cast<float*>(io.pool_rew_dev)[slot] = static_cast<const float*>(io.rew_dev)[i];
-    static_cast<float*>(io.pool_cost_dev)[slot] = io.cost_dev ? static_cast<const float*>(io.cost_dev)[i] : 0.f;
-    static_cast<uint8_t*>(io.pool_term_dev)[slot] = term ? 1 : 0;
+    for (int e = 0; e < E; ++e) {
+      const size_t se = e * cap * T + slot, ie = e * cap + i;
+      static_cast<float*>(io.pool_rew_dev)[se] = static_cast<const float*>(io.rew_dev)[ie];
+      static_cast<float*>(io.pool_cost_dev)[se] = io.cost_dev ? static_cast<const float*>(io.cost_dev)[ie] : 0.f;
+      static_cast<uint8_t*>(io.pool_term_dev)[se] = static_cast<const uint8_t*>(io.term_dev)[ie] ? 1 : 0;
+    }
     static_cast<float*>(io.pool_dyn_error_dev)[slot] =
         io.ep_var_mean_dev ? static_cast<const float*>(io.ep_var_mean_dev)[i] : 0.f;
     static_cast<uint8_t*>(io.pool_populated_dev)[slot] = 1;
@@ -167,27 +174,29 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
   // warp-per-row loop here was a 32-deep serial latency chain, 35 us even for a handful of rows)
   const int OD = io.obs_dim, AD = io.act_dim;
   const int row_base = blockIdx.x * kRB;
-  const float* so = static_cast<const float*>(io.cur_obs_dev) + (size_t)row_base * OD;
-  const float* sn = static_cast<const float*>(io.next_obs_dev) + (size_t)row_base * OD;
-  float* po = static_cast<float*>(io.pool_obs_dev);
-  float* pn = static_cast<float*>(io.pool_next_obs_dev);
   const int n_here = min(kRB, n - row_base);
+  for (int e = 0; e < E; ++e) {
+    const float* so = static_cast<const float*>(io.cur_obs_dev) + (e * cap + row_base) * OD;
+    const float* sn = static_cast<const float*>(io.next_obs_dev) + (e * cap + row_base) * OD;
+    float* po = static_cast<float*>(io.pool_obs_dev) + e * cap * T * OD;
+    float* pn = static_cast<float*>(io.pool_next_obs_dev) + e * cap * T * OD;
 #pragma unroll 4
-  for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {
-    const int r = idx / OD, d = idx - r * OD;
-    if (s_rem[r]) {
-      const size_t o = ((size_t)s_pid[r] * T + ptr) * OD + d;
-      po[o] = so[idx];
-      pn[o] = sn[idx];
+    for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {
+      const int r = idx / OD, d = idx - r * OD;
+      if (s_rem[r]) {
+        const size_t o = ((size_t)s_pid[r] * T + ptr) * OD + d;
+        po[o] = so[idx];
+        pn[o] = sn[idx];
+      }
     }
-  }
-  if (AD > 0) {
-    const float* sa = static_cast<const float*>(io.act_dev) + (size_t)row_base * AD;
-    float* pa = static_cast<float*>(io.pool_act_dev);
+    if (AD > 0) {
+      const float* sa = static_cast<const float*>(io.act_dev) + (e * cap + row_base) * AD;
+      float* pa = static_cast<float*>(io.pool_act_dev) + e * cap * T * AD;
 #pragma unroll 4
-    for (int idx = threadIdx.x; idx < n_here * AD; idx += kRB) {
-      const int r = idx / AD, d = idx - r * AD;
-      if (s_rem[r]) pa[((size_t)s_pid[r] * T + ptr) * AD + d] = sa[idx];
+      for (int idx = threadIdx.x; idx < n_here * AD; idx += kRB) {
+        const int r = idx / AD, d = idx - r * AD;
+        if (s_rem[r]) pa[((size_t)s_pid[r] * T + ptr) * AD + d] = sa[idx];
+      }
     }
   }
 }
@@ -195,19 +204,21 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
 // synthetic benchmark policy a = tanh(obs @ P); not part of the reference
 __global__ void __launch_bounds__(256) k_stub_policy(const float* __restrict__ obs, const float* __restrict__ P,
                                                      float* __restrict__ act, const int* n_rows_dev,
-                                                     long long n_rows, int OD, int AD) {
+                                                     long long n_rows, int OD, int AD, int n_slots) {
   extern __shared__ float sP[];
   for (int i = threadIdx.x; i < OD * AD; i += blockDim.x) sP[i] = P[i];
   __syncthreads();
   const long long n = n_rows_dev ? (long long)(*n_rows_dev) : n_rows;
-  const long long total = n * AD;
+  const long long per_slot = n * AD;
+  const long long total = per_slot * n_slots;   // slot e of obs / act starts at row e * n_rows (capacity)
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const long long r = idx / AD;
-    const int a = (int)(idx % AD);
+    const long long slot = idx / per_slot, j = idx - slot * per_slot;
+    const long long r = slot * n_rows + j / AD;
+    const int a = (int)(j % AD);
     float s = 0.f;
     for (int d = 0; d < OD; ++d) s = fmaf(obs[(size_t)r * OD + d], sP[d * AD + a], s);
-    act[idx] = tanhf(s);
+    act[(size_t)r * AD + a] = tanhf(s);
   }
 }
 
@@ -237,13 +248,17 @@ __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const 
   const int OD = io.obs_dim;
   const int row_base = blockIdx.x * kRB;
   const int n_here = min(kRB, n_before - row_base);
-  const float* src = static_cast<const float*>(io.next_obs_dev) + (size_t)row_base * OD;
-  float* dstp = static_cast<float*>(io.new_obs_dev);
+  const int E = (io.mode == 2 && io.n_members > 1) ? io.n_members : 1;
+  const size_t cap = (size_t)io.n_paths;
+  for (int e = 0; e < E; ++e) {   // iv_gae: every member's own state follows (model_sampler.py:444,:463-464)
+    const float* src = static_cast<const float*>(io.next_obs_dev) + (e * cap + row_base) * OD;
+    float* dstp = static_cast<float*>(io.new_obs_dev) + e * cap * OD;
 #pragma unroll 4
-  for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {   // flat element loop, see k_store
-    const int r = idx / OD, d = idx - r * OD;
-    const int d0 = s_dst[r];
-    if (d0 >= 0) dstp[(size_t)d0 * OD + d] = src[idx];
+    for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {   // flat element loop, see k_store
+      const int r = idx / OD, d = idx - r * OD;
+      const int d0 = s_dst[r];
+      if (d0 >= 0) dstp[(size_t)d0 * OD + d] = src[idx];
+    }
   }
 }
 }  // namespace cmbpo
@@ -274,13 +289,148 @@ extern "C" int cmbpo_rollout_advance(const cmbpo_rollout_io* io_, void* stream_)
 }
 
 extern "C" int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* act_dev, const void* n_rows_dev,
-                                 int64_t n_rows, int32_t obs_dim, int32_t act_dim, void* stream_) {
+                                 int64_t n_rows, int32_t obs_dim, int32_t act_dim, int32_t n_slots, void* stream_) {
   if (!obs_dev || !P_dev || !act_dev || n_rows < 0) return CMBPO_ERR_ARG;
   if (n_rows == 0) return CMBPO_OK;
-  long long blocks = (n_rows * act_dim + 255) / 256;
+  if (n_slots < 1) n_slots = 1;
+  long long blocks = (n_rows * act_dim * n_slots + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
   k_stub_policy<<<(int)blocks, 256, obs_dim * act_dim * sizeof(float), (cudaStream_t)stream_>>>(
       static_cast<const float*>(obs_dev), static_cast<const float*>(P_dev), static_cast<float*>(act_dev),
-      static_cast<const int*>(n_rows_dev), n_rows, obs_dim, act_dim);
+      static_cast<const int*>(n_rows_dev), n_rows, obs_dim, act_dim, n_slots);
   return cudaGetLastError() == cudaSuccess ? CMBPO_OK : CMBPO_ERR_CUDA;
+}
+
+// ---------------------------------------------------------------------------------------
+// Packing of the populated transitions of a model pool into one dense record matrix (what
+// ModelBuffer.get selects with populated_mask, softlearning/replay_pools/modelbuffer.py:348-405),
+// in [path, t] order: the send buffer of the multi-GPU all-gather.
+//   record = obs[E*OD] | act[E*AD] | next_obs[E*OD] | rew[E] | cost[E] | dyn_error | term[E] | path | t
+// (E = 1 unless the pool is an 'iv_gae' pool; path = global start-state index and t are int32 bit
+// patterns in the last two fp32 slots).  populated_mask rows are prefixes by construction (a finished
+// path never stores again, modelbuffer.py:110-114), so the k-th record of a path is its column k.
+// ---------------------------------------------------------------------------------------
+namespace cmbpo {
+
+__device__ __forceinline__ int block_exclusive_scan_int(int v, int* total) {
+  __shared__ int ws[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+  if (lane == 31) ws[warp] = incl;
+  __syncthreads();
+  int base = 0, tot = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) { if (w < warp) base += ws[w]; tot += ws[w]; }
+  __syncthreads();
+  if (total) *total = tot;
+  return base + incl - v;
+}
+
+__global__ void __launch_bounds__(kRB) k_pack_count(cmbpo_pack_io io, int* path_off, int* blk_cnt) {
+  const long long b = (long long)blockIdx.x * kRB + threadIdx.x;
+  const int T = io.max_path_length;
+  int len = 0;
+  if (b < io.n_paths) {
+    const uint8_t* m = io.pool_populated_dev + (size_t)b * T;
+    for (int t = 0; t < T; ++t) len += m[t] ? 1 : 0;
+  }
+  int tot;
+  const int off = block_exclusive_scan_int(len, &tot);
+  if (b < io.n_paths) path_off[b] = off;
+  if (threadIdx.x == 0) blk_cnt[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(1024) k_pack_scan(int* blk_cnt, int n_blocks, long long* blk_off, long long* count_out) {
+  __shared__ long long sh[1024];
+  __shared__ long long carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n_blocks; base += 1024) {
+    const int i = base + threadIdx.x;
+    const long long v = (i < n_blocks) ? blk_cnt[i] : 0;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {
+      const long long t = (threadIdx.x >= off) ? sh[threadIdx.x - off] : 0;
+      __syncthreads();
+      sh[threadIdx.x] += t;
+      __syncthreads();
+    }
+    const long long incl = sh[threadIdx.x];
+    if (i < n_blocks) blk_off[i] = carry + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry += incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *count_out = carry;
+}
+
+__global__ void __launch_bounds__(kRB) k_pack_write(cmbpo_pack_io io, const int* path_off, const int* blk_cnt,
+                                                    const long long* blk_off, int W) {
+  __shared__ int s_off[kRB + 1];
+  const long long b0 = (long long)blockIdx.x * kRB;
+  const int n_here = (int)min((long long)kRB, io.n_paths - b0);
+  const int total = blk_cnt[blockIdx.x];
+  s_off[threadIdx.x] = (threadIdx.x < n_here) ? path_off[b0 + threadIdx.x] : total;
+  if (threadIdx.x == 0) s_off[kRB] = total;
+  __syncthreads();
+  const long long out0 = blk_off[blockIdx.x];
+  if (out0 + total > io.capacity) return;   // caller sized the buffer too small: count_dev still reports the need
+  const int E = io.n_members > 1 ? io.n_members : 1;
+  const int OD = io.obs_dim, AD = io.act_dim, T = io.max_path_length;
+  const int c0 = E * OD, c1 = c0 + E * AD, c2 = c1 + E * OD, c3 = c2 + E, c4 = c3 + E, c5 = c4 + 1, c6 = c5 + E;
+  const size_t B = (size_t)io.n_paths;
+  float* out = io.records_dev + (size_t)out0 * W;
+  const long long n_elems = (long long)total * W;
+  for (long long idx = threadIdx.x; idx < n_elems; idx += kRB) {
+    const int rec = (int)(idx / W), col = (int)(idx - (long long)rec * W);
+    int lo = 0, hi = kRB;   // last path with s_off[path] <= rec (paths without records share their successor's offset)
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_off[mid] <= rec) lo = mid; else hi = mid; }
+    const int t = rec - s_off[lo];
+    const size_t b = (size_t)(b0 + lo);
+    float v;
+    if (col < c0) { const int e = col / OD, d = col - e * OD; v = io.pool_obs_dev[((e * B + b) * T + t) * OD + d]; }
+    else if (col < c1) { const int k = col - c0, e = k / AD, d = k - e * AD; v = io.pool_act_dev[((e * B + b) * T + t) * AD + d]; }
+    else if (col < c2) { const int k = col - c1, e = k / OD, d = k - e * OD; v = io.pool_next_obs_dev[((e * B + b) * T + t) * OD + d]; }
+    else if (col < c3) v = io.pool_rew_dev[((col - c2) * B + b) * T + t];
+    else if (col < c4) v = io.pool_cost_dev[((col - c3) * B + b) * T + t];
+    else if (col < c5) v = io.pool_dyn_error_dev[b * T + t];
+    else if (col < c6) v = io.pool_term_dev[((col - c5) * B + b) * T + t] ? 1.0f : 0.0f;
+    else if (col == c6) v = __int_as_float((int)(io.row_offset + (long long)b));
+    else v = __int_as_float(t);
+    out[idx] = v;
+  }
+}
+}  // namespace cmbpo
+
+extern "C" int32_t cmbpo_record_width(int32_t obs_dim, int32_t act_dim, int32_t n_members) {
+  const int E = n_members > 1 ? n_members : 1;
+  return E * (2 * obs_dim + act_dim + 3) + 1 + 2;
+}
+
+extern "C" size_t cmbpo_pack_scratch_bytes(int64_t n_paths) {
+  const size_t nb = (size_t)((n_paths + kRB - 1) / kRB) + 1;
+  return (size_t)n_paths * sizeof(int) + nb * (sizeof(int) + sizeof(long long)) + 256;
+}
+
+extern "C" int cmbpo_pack_records(const cmbpo_pack_io* io_, void* stream_) {
+  if (!io_ || !io_->records_dev || !io_->count_dev || !io_->scratch_dev || !io_->pool_populated_dev) return CMBPO_ERR_ARG;
+  const cmbpo_pack_io io = *io_;
+  if (io.n_paths < 0 || io.max_path_length <= 0) return CMBPO_ERR_ARG;
+  if (io.scratch_bytes < cmbpo_pack_scratch_bytes(io.n_paths)) return CMBPO_ERR_WORKSPACE;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  const int nb = (int)((io.n_paths + kRB - 1) / kRB);
+  // scratch: [nb+1] int64 block offsets | [n_paths] int path offsets | [nb] int block counts
+  long long* blk_off = static_cast<long long*>(io.scratch_dev);
+  int* path_off = reinterpret_cast<int*>(blk_off + nb + 1);
+  int* blk_cnt = path_off + io.n_paths;
+  if (nb > 0) k_pack_count<<<nb, kRB, 0, stream>>>(io, path_off, blk_cnt);
+  k_pack_scan<<<1, 1024, 0, stream>>>(blk_cnt, nb, blk_off, reinterpret_cast<long long*>(io.count_dev));
+  if (nb > 0) k_pack_write<<<nb, kRB, 0, stream>>>(io, path_off, blk_cnt, blk_off,
+                                                   cmbpo_record_width(io.obs_dim, io.act_dim, io.n_members));
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { snprintf(g_roll_err, sizeof(g_roll_err), "pack_records: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }
+  return CMBPO_OK;
 }

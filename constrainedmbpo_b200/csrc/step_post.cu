@@ -172,6 +172,9 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int r = lane, part = warp;
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
+  // 3-D mode: member slot e of obs/act/next_obs/rew/term/cost starts at row e * capacity (the array shapes
+  // stay at capacity while the live row count shrinks during an 'iv_gae' rollout)
+  const long long slot_rows = p.n_rows;
   const int D = p.D, OD = p.obs_dim;
   const int n_slots_out = p.per_slot ? E : 1;
   float acc_dkl = 0.f, acc_var = 0.f, acc_rew = 0.f, acc_cost = 0.f;
@@ -198,7 +201,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
       // stage obs rows of this block (slot `so` in 3-D mode) through smem, coalesced
       __syncthreads();
       {
-        const float* src = p.obs + (p.per_slot ? (size_t)so * n_rows * OD : 0) + (size_t)row0 * OD;
+        const float* src = p.obs + (p.per_slot ? (size_t)so * slot_rows * OD : 0) + (size_t)row0 * OD;
         for (int i = tid; i < rows_here * OD; i += kPostThreads) tile[i] = src[i];
       }
       __syncthreads();
@@ -219,7 +222,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
               // obs of the other slots are read straight from global (L2-resident, just loaded)
 #pragma unroll
               for (int e = 0; e < E; ++e)
-                m[e] += (e == so) ? o : p.obs[((size_t)e * n_rows + g) * OD + d];
+                m[e] += (e == so) ? o : p.obs[((size_t)e * slot_rows + g) * OD + d];
             } else {
 #pragma unroll
               for (int e = 0; e < E; ++e) m[e] += o;
@@ -245,7 +248,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
           float x = p.per_slot ? pick<E>(m, so) : pick<E>(m, eidx);
           if (p.noise) {  // optional north_star mode: mean + noise*std (off in the live reference)
             const float vs = p.per_slot ? pick<E>(v, so) : pick<E>(v, eidx);
-            const float z = p.noise[(p.per_slot ? (size_t)so * n_rows * D : 0) + (size_t)g * D + d];
+            const float z = p.noise[(p.per_slot ? (size_t)so * slot_rows * D : 0) + (size_t)g * D + d];
             x = fmaf(z, sqrtf(vs), x);
           }
           if (d < OD) {
@@ -275,14 +278,14 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
         const float rew = s_rew[r];
         const bool done = termination(p.env_id, f);
         const float cost = (p.cost_mode == 1) ? static_cost(p.env_id, f, done) : 0.f;
-        const size_t oi = (size_t)so * n_rows + g;
+        const size_t oi = (size_t)so * slot_rows + g;
         p.rew[oi] = rew;
         p.term[oi] = done ? 1 : 0;
         if (p.cost) p.cost[oi] = cost;
         if (so == 0 || p.per_slot) { acc_rew += rew; acc_cost += cost; }
       }
       {
-        float* dst = p.next_obs + (p.per_slot ? (size_t)so * n_rows * OD : 0) + (size_t)row0 * OD;
+        float* dst = p.next_obs + (p.per_slot ? (size_t)so * slot_rows * OD : 0) + (size_t)row0 * OD;
         for (int i = tid; i < rows_here * OD; i += kPostThreads) dst[i] = tile[i];
       }
     }

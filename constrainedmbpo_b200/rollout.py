@@ -19,7 +19,7 @@ import torch
 
 from . import _lib
 
-MODES = {"schedule": 0, "uncertainty": 1}
+MODES = {"schedule": 0, "uncertainty": 1, "iv_gae": 2}
 
 
 class StubPolicy:
@@ -34,14 +34,15 @@ class StubPolicy:
 
     def __call__(self, obs, n_rows_dev=None):
         lib = _lib.load()
-        B = obs.shape[0]
-        if self._act is None or self._act.shape[0] != B:
-            self._act = torch.empty(B, self.act_dim, dtype=torch.float32, device=obs.device)
+        B = obs.shape[-2]
+        shape = tuple(obs.shape[:-1]) + (self.act_dim,)   # [B, act] or, for 'iv_gae' states, [E, B, act]
+        if self._act is None or tuple(self._act.shape) != shape:
+            self._act = torch.empty(shape, dtype=torch.float32, device=obs.device)
         stream = C.c_void_p(torch.cuda.current_stream(obs.device).cuda_stream)
         _lib.check(lib.cmbpo_stub_policy(
             C.c_void_p(obs.data_ptr()), C.c_void_p(self.P.data_ptr()), C.c_void_p(self._act.data_ptr()),
             C.c_void_p(n_rows_dev.data_ptr()) if n_rows_dev is not None else None,
-            B, self.obs_dim, self.act_dim, stream))
+            B, self.obs_dim, self.act_dim, obs.shape[0] if obs.dim() == 3 else 1, stream))
         return self._act
 
 
@@ -72,10 +73,9 @@ class ModelRollout:
     layout ``[B, max_path_length, dim]`` with row = start-state index (modelbuffer.py:45-114)."""
 
     def __init__(self, env, max_path_length, rollout_mode="schedule", dkl_lim=None, max_samples=None,
-                 row_offset=0):
+                 row_offset=0, perm_fn=None):
         if rollout_mode not in MODES:
-            raise ValueError("rollout_mode must be 'schedule' or 'uncertainty' on the device path "
-                             "('iv_gae' rolls 3-D states through FakeEnv.step; its GAE weighting is SURVEY §8f N2)")
+            raise ValueError("rollout_mode must be 'schedule', 'uncertainty' or 'iv_gae' (cmbpo.py:89)")
         if rollout_mode == "uncertainty" and dkl_lim is None:
             raise ValueError("'uncertainty' mode needs dkl_lim (model_sampler.py:178-179 set_rollout_dkl)")
         self.env = env
@@ -84,6 +84,10 @@ class ModelRollout:
         self.dkl_lim = float(dkl_lim) if dkl_lim is not None else 0.0
         self.max_samples = int(max_samples) if max_samples else 0
         self.row_offset = int(row_offset)
+        # 'iv_gae' only: perm_fn(step) -> the forward_shuffle permutation FakeEnv.step draws per call
+        # (fake_env.py:309-316, global NumPy RNG upstream).  It is a launch argument, so a captured graph
+        # replays the permutations drawn at capture time.
+        self.perm_fn = perm_fn
         self.device = env.device
         self.B = 0
         self._lib = _lib.load()
@@ -92,12 +96,15 @@ class ModelRollout:
         dev, T, AD = self.device, self.T, self.env.act_dim
         z = lambda *s, dt=torch.float32: torch.zeros(*s, dtype=dt, device=dev)
         self.B = B
+        # 'iv_gae': one trajectory per ensemble member -- leading E on the per-transition arrays
+        # (model_sampler.py:225-226, modelbuffer.py:48-51); dyn_error / populated stay [B, T] (:59,:110)
+        E = (self.env.num_networks,) if self.mode == "iv_gae" else ()
         self.pool = {
-            "obs": z(B, T, OD), "act": z(B, T, AD), "next_obs": z(B, T, OD),
-            "rew": z(B, T), "cost": z(B, T), "term": z(B, T, dt=torch.uint8),
+            "obs": z(*E, B, T, OD), "act": z(*E, B, T, AD), "next_obs": z(*E, B, T, OD),
+            "rew": z(*E, B, T), "cost": z(*E, B, T), "term": z(*E, B, T, dt=torch.uint8),
             "dyn_error": z(B, T), "populated": z(B, T, dt=torch.uint8),
         }
-        self.cur = [torch.empty(B, OD, dtype=torch.float32, device=dev) for _ in range(2)]
+        self.cur = [torch.empty(*E, B, OD, dtype=torch.float32, device=dev) for _ in range(2)]
         self.pid = [torch.empty(B, dtype=torch.int32, device=dev) for _ in range(2)]
         self.dkl_accum = z(B, dt=torch.float64)
         self.state = torch.zeros(10, dtype=torch.int32, device=dev)
@@ -125,7 +132,7 @@ class ModelRollout:
                 v.zero_()
             self.dkl_accum.zero_()
         self.alive_hist.zero_()
-        self.cur[0].copy_(start_obs, non_blocking=True)
+        self.cur[0].copy_(start_obs, non_blocking=True)   # 'iv_gae': broadcast = np.tile(obs[None], (E,1,1))
         self.pid[0].copy_(self._arange)
         self.state.copy_(self._state_init)
         self.flip = 0
@@ -141,7 +148,11 @@ class ModelRollout:
         if self.row_offset:
             torch.add(pid, self.row_offset, out=self._row_ids)
             row_ids = self._row_ids
-        o = env.step_device(cur, act, n_rows_dev=n_dev, row_ids=row_ids, want_ep_var=False, out=self._step_out)
+        perm = None
+        if self.mode == "iv_gae" and self.perm_fn is not None:
+            perm = self.perm_fn(self.steps_done)
+        o = env.step_device(cur, act, n_rows_dev=n_dev, row_ids=row_ids, want_ep_var=False, out=self._step_out,
+                            perm=perm)
         io = _lib.cmbpo_rollout_io()
         io.n_paths, io.max_path_length, io.mode = self.B, self.T, MODES[self.mode]
         io.dkl_lim, io.max_samples, io.step_index = self.dkl_lim, self.max_samples, self.steps_done
@@ -157,6 +168,7 @@ class ModelRollout:
         io.new_obs_dev, io.new_path_id_dev = self.cur[self.flip ^ 1].data_ptr(), self.pid[self.flip ^ 1].data_ptr()
         io.scratch_dev, io.scratch_bytes = self.scratch.data_ptr(), self.scratch.numel()
         io.alive_hist_dev = self.alive_hist.data_ptr()
+        io.n_members = env.num_networks if self.mode == "iv_gae" else 0
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         _lib.check(self._lib.cmbpo_rollout_advance(C.byref(io), stream))
         self.flip ^= 1
@@ -202,7 +214,10 @@ class ModelRollout:
         flattened in [path, t] order.  Returns CUDA tensors, or fills / returns pinned host
         buffers when ``host_out`` is a dict (device->host copy of exactly the populated rows)."""
         mask = self.pool["populated"].bool()
-        out = {k: v[mask] for k, v in self.pool.items() if k != "populated"}
+        # 'iv_gae' pools carry a leading member axis: flatten to [n, E, ...]
+        per_member = () if self.mode != "iv_gae" else ("obs", "act", "next_obs", "rew", "cost", "term")
+        out = {k: (v.movedim(0, 2)[mask] if k in per_member else v[mask])
+               for k, v in self.pool.items() if k != "populated"}
         if host_out is None:
             return out
         n = out["rew"].shape[0]

@@ -142,7 +142,11 @@ typedef struct cmbpo_rollout_state {
 
 /* One sampler step AFTER cmbpo_step produced next_obs/rew/term/cost/dkl_path/ep_var_mean for the
  * first state->n_alive rows.  mode 0 = 'schedule' (length mask only), 1 = 'uncertainty'
- * (accumulated ensemble KL vs dkl_lim, model_sampler.py:311-313).  Pools are [n_paths][T][dim]
+ * (accumulated ensemble KL vs dkl_lim, model_sampler.py:311-313), 2 = 'iv_gae' (every member rolls
+ * its own state, model_sampler.py:225-226: cur_obs/act/next_obs/rew/term/cost are
+ * [n_members][n_paths][.] with member stride n_paths rows, pools obs/act/next_obs/rew/cost/term are
+ * [n_members][n_paths][T][.] (modelbuffer.py:48-51); no uncertainty cutoff and no max_samples cap
+ * (:315,:327); a path ends when ANY member's state terminates (:445)).  Pools are [n_paths][T][dim]
  * (modelbuffer.py:45-114), row = original path id.  Survivors are compacted, order preserved,
  * into new_obs / new_path_id; state is updated on the device (no host synchronisation). */
 typedef struct cmbpo_rollout_io {
@@ -171,14 +175,41 @@ typedef struct cmbpo_rollout_io {
   int32_t* new_path_id_dev;    /* [n_alive'] */
   void* scratch_dev; size_t scratch_bytes;   /* >= cmbpo_rollout_scratch_bytes(n_paths) */
   int32_t* alive_hist_dev;     /* optional [T]: rows alive when step `step_index` began (diagnostics / FLOP accounting) */
+  int32_t n_members;           /* mode 2 only: E (leading axis of the step arrays and pools); 0/1 otherwise */
 } cmbpo_rollout_io;
 size_t cmbpo_rollout_scratch_bytes(int64_t n_paths);
 int cmbpo_rollout_advance(const cmbpo_rollout_io* io, void* stream);
 
+/* Populated transitions of a model pool -> one dense fp32 record matrix in [path, t] order: what
+ * ModelBuffer.get selects with populated_mask (softlearning/replay_pools/modelbuffer.py:348-405), laid out
+ * as the send buffer of the multi-GPU all-gather.  Record (width cmbpo_record_width):
+ *   obs[E*obs] | act[E*act] | next_obs[E*obs] | rew[E] | cost[E] | dyn_error | term[E] | path | t
+ * E = n_members for 'iv_gae' pools ([E][n_paths][T][.]), else 1; path (= row_offset + pool row) and t are
+ * int32 bit patterns.  count_dev receives the number of populated transitions; nothing is written for a
+ * block of paths whose records would not fit `capacity` (compare count with capacity afterwards). */
+typedef struct cmbpo_pack_io {
+  int64_t n_paths;
+  int32_t max_path_length;
+  int32_t obs_dim, act_dim;
+  int32_t n_members;
+  int64_t row_offset;
+  const float* pool_obs_dev; const float* pool_act_dev; const float* pool_next_obs_dev;
+  const float* pool_rew_dev; const float* pool_cost_dev; const uint8_t* pool_term_dev;
+  const float* pool_dyn_error_dev; const uint8_t* pool_populated_dev;
+  float* records_dev;          /* [capacity][cmbpo_record_width] */
+  int64_t capacity;
+  int64_t* count_dev;          /* [1] */
+  void* scratch_dev; size_t scratch_bytes;   /* >= cmbpo_pack_scratch_bytes(n_paths) */
+} cmbpo_pack_io;
+int32_t cmbpo_record_width(int32_t obs_dim, int32_t act_dim, int32_t n_members);
+size_t cmbpo_pack_scratch_bytes(int64_t n_paths);
+int cmbpo_pack_records(const cmbpo_pack_io* io, void* stream);
+
 /* Synthetic benchmark policy a = tanh(obs @ P), P [obs][act] (not part of the reference; stands in
- * for policy.get_action_outs, model_sampler.py:275, in throughput runs) */
+ * for policy.get_action_outs, model_sampler.py:275, in throughput runs).  n_slots > 1: obs / act are
+ * [n_slots][n_rows][.] ('iv_gae' states), the live count applies to every slot. */
 int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* act_dev, const void* n_rows_dev,
-                      int64_t n_rows, int32_t obs_dim, int32_t act_dim, void* stream);
+                      int64_t n_rows, int32_t obs_dim, int32_t act_dim, int32_t n_slots, void* stream);
 
 /* Measurement aid (no reference counterpart): while enabled, every ensemble-forward launch of this
  * handle is bracketed by CUDA events on its stream; cmbpo_profile_read waits for them, returns the

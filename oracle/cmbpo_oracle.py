@@ -529,3 +529,90 @@ def rollout(p: EnsembleParams, env: str, start_obs, policy, max_path_length, rol
     pool["dkl_accum"] = dkl_accum
     pool["path_length"] = path_length
     return pool
+
+
+def rollout_iv_gae(p: EnsembleParams, env: str, start_obs, policy, max_path_length, perm_fn=None,
+                   cares_about_cost=False, max_steps=None, step_fn=None, trace=None):
+    """The same sampler loop in ``rollout_mode == 'iv_gae'`` (model_sampler.py:225-226, :283-288, :348-362,
+    :388-392, :444-445, :463-464; modelbuffer.py:48-51, :134-150): the start states are tiled over the
+    ensemble axis and every member rolls its own trajectory through the 3-D branch of ``FakeEnv.step``
+    (fake_env.py:147-153, :164-165).  No uncertainty cutoff (:315) and no ``max_samples`` cap (:327) in
+    this mode; a path ends at the length mask (:437, Q8) or when ANY member's state terminates (:445).
+    Per-transition pools carry a leading ``E``; ``dyn_error`` / ``populated`` stay ``[B, T]``.
+
+    ``policy(obs[E,n,obs]) -> act[E,n,act]``; ``perm_fn(step) -> permutation of range(E)`` is the injected
+    ``forward_shuffle`` draw.  The inverse-variance GAE that consumes these pools is SURVEY §8f N2.
+    """
+    dt = p.dtype
+    start_obs = np.asarray(start_obs, dtype=dt)
+    B, obs_dim = start_obs.shape
+    E = len(p.weights[0])
+    T = max_path_length
+    pool = {
+        "obs": np.zeros((E, B, T, obs_dim), np.float32),
+        "next_obs": np.zeros((E, B, T, obs_dim), np.float32),
+        "rew": np.zeros((E, B, T), np.float32),
+        "cost": np.zeros((E, B, T), np.float32),
+        "term": np.zeros((E, B, T), bool),
+        "dyn_error": np.zeros((B, T), np.float32),
+        "populated": np.zeros((B, T), bool),
+    }
+    terminated = np.zeros(B, bool)
+    ptr = 0
+    cur = np.tile(start_obs[None], (E, 1, 1))  # :226
+    path_length = np.zeros(B)
+    dkl_accum = np.zeros(B)
+    total_samples = 0
+    step = 0
+    while (~terminated).any() and (max_steps is None or step < max_steps):
+        alive = ~terminated
+        n_alive = int(alive.sum())
+        a = np.asarray(policy(cur), dtype=dt)
+        if "act" not in pool:
+            pool["act"] = np.zeros((E, B, T, a.shape[-1]), np.float32)
+        if trace is not None:
+            trace.append(n_alive)
+        if step_fn is not None:
+            next_obs, rew, term, info = step_fn(cur, a, step)
+        else:
+            next_obs, rew, term, info = fake_env_step(p, env, cur, a, perm=np.asarray(perm_fn(step)),
+                                                      cares_about_cost=cares_about_cost)
+        rew = np.squeeze(rew, -1)            # [E, n]
+        c = np.squeeze(info["cost"], -1)     # [E, n]
+        term = np.squeeze(term, -1)          # [E, n]
+        dkl_path = info["ensemble_dkl_path"]
+        ep_var = info["ensemble_ep_var"]
+        # too_uncertain is all-False (:315), max_samples is skipped (:327) => every alive path is stored
+        total_samples += n_alive  # :386
+        path_length[alive] += 1  # :400
+        dkl_accum[alive] += dkl_path  # :415
+        pool["obs"][:, alive, ptr] = cur  # modelbuffer.py:134-150
+        pool["act"][:, alive, ptr] = a
+        pool["next_obs"][:, alive, ptr] = next_obs
+        pool["rew"][:, alive, ptr] = rew
+        pool["cost"][:, alive, ptr] = c
+        pool["term"][:, alive, ptr] = term
+        pool["dyn_error"][alive, ptr] = np.mean(ep_var, axis=-1)  # :168
+        pool["populated"][alive, ptr] = True
+        ptr += 1
+        cur = next_obs  # :435
+        path_end = (path_length >= max_path_length - 1)[alive]  # :437
+        idx_alive = np.where(alive)[0]
+        terminated[idx_alive[path_end]] = True
+        rem2 = ~path_end
+        if not rem2.any():
+            break
+        cur = cur[:, rem2]  # :444
+        prem_term = np.any(term[:, rem2], axis=0)  # :445
+        idx_alive = np.where(~terminated)[0]
+        terminated[idx_alive[prem_term]] = True
+        if prem_term.all():
+            break
+        cur = cur[:, ~prem_term]  # :464
+        step += 1
+    pool["ptr"] = ptr
+    pool["total_samples"] = total_samples
+    pool["terminated"] = terminated
+    pool["dkl_accum"] = dkl_accum
+    pool["path_length"] = path_length
+    return pool

@@ -89,20 +89,25 @@ class TorchEnsemble:
         return mean, var
 
 
-def fake_env_step(ens: TorchEnsemble, env: str, obs, act, elite_idx, cares_about_cost=False):
-    """FakeEnv.step (fake_env.py:131-222), 2-D path, fp32: GEMMs in torch, the rest in NumPy exactly
-    as ``oracle.cmbpo_oracle.fake_env_step`` does it."""
+def fake_env_step(ens: TorchEnsemble, env: str, obs, act, elite_idx, cares_about_cost=False, perm=None):
+    """FakeEnv.step (fake_env.py:131-222), fp32: GEMMs in torch, the rest in NumPy exactly as
+    ``oracle.cmbpo_oracle.fake_env_step`` does it.  3-D inputs ([E,B,.], 'iv_gae') take ``perm`` (the
+    forward_shuffle draw) and keep every member's own sample (fake_env.py:147-153, :164-165)."""
     obs = np.asarray(obs, dtype=np.float32)
     act = np.asarray(act, dtype=np.float32)
     inputs = np.concatenate((obs, act), axis=-1)
+    if obs.ndim == 3:
+        inputs = inputs[perm]
     means, variances = ens.predict_factored(inputs)
     means = np.array(means)
+    if obs.ndim == 3:
+        means, variances = means[perm], variances[perm]
     means[:, :, :-1] += obs
     stds = np.sqrt(variances)
     dkl_path = np.mean(orc.average_dkl(means, stds), axis=-1)
     ep_var = np.var(means, axis=0)
     B = means.shape[1]
-    samples = means[np.asarray(elite_idx), np.arange(B)]
+    samples = means if obs.ndim == 3 else means[np.asarray(elite_idx), np.arange(B)]
     next_obs, rewards = samples[..., :-1], samples[..., -1:]
     term_fn, cost_fn = orc.STATIC_FNS[env]
     terminals = term_fn(obs, act, next_obs)
@@ -121,6 +126,13 @@ def rollout(ens: TorchEnsemble, env, start_obs, policy_np, max_path_length, roll
     """The sampler loop of ``oracle.cmbpo_oracle.rollout`` with the torch-backed step; returns
     (total transitions stored, seconds)."""
     rng = elite_rng or np.random.default_rng(5)
+    if rollout_mode == "iv_gae":
+        E = ens.p.num_nets
+        step_fn = lambda cur, a, step: fake_env_step(ens, env, cur, a, None, cares_about_cost, perm=rng.permutation(E))
+        t0 = time.perf_counter()
+        pool = orc.rollout_iv_gae(ens.p, env, start_obs, policy_np, max_path_length, step_fn=step_fn,
+                                  cares_about_cost=cares_about_cost)
+        return int(pool["total_samples"]), time.perf_counter() - t0, pool
     step_fn = lambda cur, a, step: _step_tuple(ens, env, cur, a, rng, cares_about_cost)
     t0 = time.perf_counter()
     pool = orc.rollout(ens.p, env, start_obs, policy_np, max_path_length, rollout_mode, dkl_lim=dkl_lim,

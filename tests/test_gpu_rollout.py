@@ -184,3 +184,83 @@ def test_full_size_schedule_rollout_properties():
     assert bool(torch.isfinite(pool["rew"]).all())
     hist = ro.alive_hist.cpu().numpy()
     assert list(hist[: T - 1]) == [B] * (T - 1)
+
+
+def _recorded_rollout_iv(env, B, T, seed=0, cares_about_cost=True):
+    """'iv_gae' mode: [E, n, .] states; records every sampler step's inputs / outputs and permutations."""
+    import constrainedmbpo_b200 as cm
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    obs, _ = make_inputs(env, B)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=cares_about_cost, seed=seed)
+    pol = cm.StubPolicy(fe.obs_dim, fe.act_dim, device="cuda:0")
+    prng = np.random.default_rng(11)
+    perms = [prng.permutation(p.num_nets) for _ in range(T + 2)]
+    ro = cm.ModelRollout(fe, T, rollout_mode="iv_gae", perm_fn=lambda t: perms[t])
+    ro.reset(obs)
+    rec = []
+    for t in range(T - 1):
+        n = int(ro.state[0].item())
+        if n == 0:
+            break
+        cur = ro.cur[ro.flip][:, :n].cpu().numpy().copy()
+        ro.step(pol)
+        o = ro._step_out
+        g = lambda x: x[:, :n].cpu().numpy().copy()
+        rec.append(dict(cur=cur, act=g(pol._act), next_obs=g(o["next_obs"]), rew=g(o["rew"]),
+                        term=g(o["term"]).astype(bool), cost=g(o["cost"]),
+                        dkl=o["dkl_path"][:n].cpu().numpy().copy(), epv=o["ep_var_mean"][:n].cpu().numpy().copy()))
+    for _ in range(2):
+        ro.step(pol)
+    return p, obs, ro, rec, perms
+
+
+def test_iv_gae_mode_bookkeeping_bit_exact():
+    """'iv_gae' (model_sampler.py:225-226,:444-445; modelbuffer.py:48-51,:134-150): every member rolls its own
+    state; pools carry a leading E; a path ends when ANY member terminates.  Teacher-forced, bit-exact."""
+    env, B, T = "antsafe", 1200, 7
+    p, obs, ro, rec, perms = _recorded_rollout_iv(env, B, T)
+    k = {"i": 0}
+
+    def policy(cur):
+        r = rec[k["i"]]
+        assert np.array_equal(cur.astype(np.float32), r["cur"]), "compacted member states differ"
+        return r["act"]
+
+    def step_fn(cur, a, step):
+        r = rec[k["i"]]
+        k["i"] += 1
+        D = cur.shape[-1] + 1
+        info = {"cost": r["cost"], "ensemble_dkl_path": r["dkl"],
+                "ensemble_ep_var": np.repeat(r["epv"][:, None], D, axis=1)}
+        return r["next_obs"], r["rew"], r["term"], info
+    ref = orc.rollout_iv_gae(p.astype(np.float32), env, obs, policy, T, step_fn=step_fn)
+    got = ro.get(numpy=True)
+    for key in ("obs", "act", "next_obs", "rew", "cost", "term", "populated"):
+        assert got[key].shape == ref[key].shape, key
+        assert np.array_equal(got[key], ref[key]), f"pool[{key}] differs"
+    assert np.allclose(got["dyn_error"], ref["dyn_error"], rtol=1e-6, atol=0)
+    assert np.array_equal(got["dkl_accum"], ref["dkl_accum"])
+    n_alive, ptr, total, finished = ro.counters()
+    assert total == ref["total_samples"] == int(ref["populated"].sum()) and finished == 1
+    assert len(rec) > 2 and rec[-1]["cur"].shape[1] < B            # some paths ended through a member's terminal
+    assert np.array_equal(got["obs"][:, :, 0], np.tile(obs[None], (7, 1, 1)))  # np.tile start states (:226)
+    # members diverge after the first step: trajectories are per member
+    assert not np.array_equal(got["next_obs"][0, :, 0], got["next_obs"][1, :, 0])
+    tr = ro.transitions()
+    assert tr["obs"].shape == (total, 7, 29) and tr["dyn_error"].shape == (total,)
+
+
+def test_iv_gae_step_matches_oracle_on_compacted_states():
+    """Arithmetic of the 3-D step inside the rollout (live count < capacity: member stride stays at
+    capacity): step outputs of sampler step 2 against the fp64 oracle on the same member states."""
+    from tests.helpers import assert_means_close, out_scale
+    env, B, T = "antsafe", 900, 5
+    p, obs, ro, rec, perms = _recorded_rollout_iv(env, B, T, cares_about_cost=True)
+    t = 2
+    r = rec[t]
+    assert r["cur"].shape[1] < B
+    nobs, rew, term, info = orc.fake_env_step(p, env, r["cur"], r["act"], perm=perms[t], cares_about_cost=True)
+    s = out_scale(p)
+    assert_means_close(r["next_obs"], nobs, s[:-1], what="iv next_obs")
+    assert_means_close(r["rew"], rew, s[-1:], what="iv reward")
+    assert np.allclose(r["dkl"], info["ensemble_dkl_path"], rtol=0.1, atol=1e-7)

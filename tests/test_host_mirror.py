@@ -61,7 +61,8 @@ def test_rollout_mode_validation():
     class E:  # never touched before validation
         device = "cpu"
     with pytest.raises(ValueError, match="iv_gae"):
-        cm.ModelRollout(E(), 10, rollout_mode="iv_gae")
+        cm.ModelRollout(E(), 10, rollout_mode="bogus")
+    assert cm.ModelRollout(E(), 10, rollout_mode="iv_gae").mode == "iv_gae"   # cmbpo.py:89 third mode
     with pytest.raises(ValueError, match="dkl_lim"):
         cm.ModelRollout(E(), 10, rollout_mode="uncertainty")
 
