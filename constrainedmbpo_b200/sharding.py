@@ -32,7 +32,10 @@ def pack_records(pool: dict, row_offset: int = 0):
     path, t = mask.nonzero(as_tuple=True)
     cols = []
     for k in RECORD_FIELDS:
-        v = pool[k][mask]
+        v = pool[k]
+        if k != "dyn_error" and v.dim() > mask.dim() and tuple(v.shape[1:3]) == tuple(mask.shape):
+            v = v.movedim(0, 2)      # 'iv_gae' pool [E,B,T,.] -> [B,T,E,.]: member-major columns per field
+        v = v[mask]
         cols.append(v.reshape(v.shape[0], -1).to(torch.float32))
     rec = torch.cat(cols, dim=1)
     coords = torch.stack([path + int(row_offset), t], dim=1).to(torch.int64)
@@ -80,16 +83,135 @@ def gather_transitions(pool: dict, row_offset: int = 0, group=None):
     return rec_all, coords_all, counts
 
 
-class PoolGatherer:
-    """Per-rollout all-gather of the transitions a ``ModelRollout`` generated (one NCCL all-gather
-    of the packed records + one of the coordinates)."""
+def record_width(obs_dim, act_dim, n_members=1):
+    """Columns of one packed record (``cmbpo_record_width``): the RECORD_FIELDS payload + (path, t)."""
+    E = max(int(n_members), 1)
+    return E * (2 * obs_dim + act_dim + 3) + 1 + 2
 
-    def __init__(self, rollout, world, group=None):
+
+def pack_records_cuda(pool: dict, row_offset, obs_dim, act_dim, n_members, out, count, scratch, stream=None):
+    """``cmbpo_pack_records``: the CUDA twin of ``pack_records`` + coords in one launch sequence, no host
+    synchronisation.  ``out`` [capacity, W] fp32, ``count`` int64 [1], ``scratch`` uint8 (all CUDA)."""
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    B, T = pool["populated"].shape
+    io = _lib.cmbpo_pack_io()
+    io.n_paths, io.max_path_length, io.obs_dim, io.act_dim = B, T, obs_dim, act_dim
+    io.n_members, io.row_offset = (n_members if n_members > 1 else 0), int(row_offset)
+    io.pool_obs_dev, io.pool_act_dev, io.pool_next_obs_dev = pool["obs"].data_ptr(), pool["act"].data_ptr(), pool["next_obs"].data_ptr()
+    io.pool_rew_dev, io.pool_cost_dev, io.pool_term_dev = pool["rew"].data_ptr(), pool["cost"].data_ptr(), pool["term"].data_ptr()
+    io.pool_dyn_error_dev, io.pool_populated_dev = pool["dyn_error"].data_ptr(), pool["populated"].data_ptr()
+    io.records_dev, io.capacity, io.count_dev = out.data_ptr(), out.shape[0], count.data_ptr()
+    io.scratch_dev, io.scratch_bytes = scratch.data_ptr(), scratch.numel()
+    st = stream if stream is not None else torch.cuda.current_stream(out.device)
+    _lib.check(lib.cmbpo_pack_records(C.byref(io), C.c_void_p(st.cuda_stream)))
+
+
+class PoolGatherer:
+    """Per-rollout all-gather of the transitions a ``ModelRollout`` generated into the replicated model
+    pool -- the only collective on the path.
+
+    ``launch()`` (call it right after a rollout was enqueued) packs that rollout's populated transitions
+    into a staging buffer on the compute stream (``cmbpo_pack_records``, no host sync) and then runs the
+    NCCL collective of the PREVIOUS rollout on a side stream, so the transfer overlaps the rollout now
+    executing.  Shards have different transition counts ('uncertainty' cutoffs, terminals): counts are
+    all-gathered first (8 bytes per rank), then the payload goes straight into a dense
+    ``[sum(counts), W]`` matrix -- ``all_gather_into_tensor`` when the counts are equal, else the
+    uneven-size ``all_gather`` (one broadcast per rank inside one NCCL group).  ``wait()`` drains the
+    pipeline and returns ``(records, counts)`` of the last rollout; ``records[:, -2:]`` viewed as
+    int32 are the (global path, t) coordinates."""
+
+    def __init__(self, rollout, world, group=None, capacity=None):
         self.ro, self.world, self.group = rollout, world, group
+        self.capacity = capacity
         self.last = None
+        self._pending = None
+        self._k = 0
+        self._buf = None
+
+    def _allocate(self):
+        ro = self.ro
+        dev = ro.device
+        B, T = ro.pool["populated"].shape
+        self.E = ro.env.num_networks if ro.mode == "iv_gae" else 1
+        self.W = record_width(ro.env.obs_dim, ro.env.act_dim, self.E)
+        cap = int(self.capacity) if self.capacity else B * max(T - 1, 1)   # a path stores at most T-1 (Q8)
+        from . import _lib
+        nscr = int(_lib.load().cmbpo_pack_scratch_bytes(B)) + 64
+        self._buf = [dict(rec=torch.empty(cap, self.W, dtype=torch.float32, device=dev),
+                          count=torch.zeros(1, dtype=torch.int64, device=dev),
+                          count_host=torch.zeros(1, dtype=torch.int64).pin_memory(),
+                          scratch=torch.empty(nscr, dtype=torch.uint8, device=dev),
+                          packed=torch.cuda.Event(), sent=None) for _ in range(2)]
+        self._side = torch.cuda.Stream(device=dev)
 
     def launch(self):
-        self.last = gather_transitions(self.ro.pool, self.ro.row_offset, self.group)
+        if self._buf is None:
+            self._allocate()
+        ro = self.ro
+        b = self._buf[self._k & 1]
+        main = torch.cuda.current_stream(ro.device)
+        if b["sent"] is not None:
+            main.wait_event(b["sent"])          # the collective two rollouts ago has read this staging buffer
+        pack_records_cuda(ro.pool, ro.row_offset, ro.env.obs_dim, ro.env.act_dim, self.E, b["rec"], b["count"],
+                          b["scratch"], main)
+        b["count_host"].copy_(b["count"], non_blocking=True)
+        b["packed"].record(main)
+        prev, self._pending = self._pending, b
+        self._k += 1
+        if prev is not None:
+            self._collect(prev)
+
+    def _collect(self, b):
+        b["packed"].synchronize()
+        n = int(b["count_host"][0])
+        if n > b["rec"].shape[0]:
+            raise RuntimeError(f"PoolGatherer: {n} transitions exceed the staging capacity {b['rec'].shape[0]}")
+        with torch.cuda.stream(self._side):
+            counts_dev = torch.empty(self.world, dtype=torch.int64, device=b["rec"].device)
+            dist.all_gather_into_tensor(counts_dev, b["count"], group=self.group)
+            counts = [int(c) for c in counts_dev.cpu()]
+            total = sum(counts)
+            full = torch.empty(total, self.W, dtype=torch.float32, device=b["rec"].device)
+            if total > 0:
+                if min(counts) == max(counts):
+                    dist.all_gather_into_tensor(full, b["rec"][:n], group=self.group)
+                else:
+                    outs, o = [], 0
+                    for c in counts:
+                        outs.append(full[o:o + c])
+                        o += c
+                    dist.all_gather(outs, b["rec"][:n], group=self.group)
+            ev = torch.cuda.Event()
+            ev.record(self._side)
+            b["sent"] = ev
+        full.record_stream(self._side)
+        self.last = (full, counts)
 
     def wait(self):
+        if self._pending is not None:
+            b, self._pending = self._pending, None
+            self._collect(b)
+        if self._buf is not None:
+            self._side.synchronize()
         return self.last
+
+
+def unpack_gathered(rec: torch.Tensor, obs_dim: int, act_dim: int, n_members: int = 1):
+    """Split the gathered record matrix back into named arrays (+ int64 ``coords`` [n, 2])."""
+    E = max(int(n_members), 1)
+    o, out = 0, {}
+    for k, wdt in (("obs", E * obs_dim), ("act", E * act_dim), ("next_obs", E * obs_dim), ("rew", E), ("cost", E),
+                   ("dyn_error", 1), ("term", E)):
+        v = rec[:, o:o + wdt]
+        if E > 1 and k != "dyn_error":
+            v = v.reshape(v.shape[0], E, -1)
+            v = v[..., 0] if v.shape[-1] == 1 else v
+        elif wdt == 1:
+            v = v[:, 0]
+        out[k] = v
+        o += wdt
+    out["term"] = out["term"] != 0
+    out["coords"] = rec[:, o:o + 2].contiguous().view(torch.int32).to(torch.int64)
+    return out

@@ -264,3 +264,45 @@ def test_iv_gae_step_matches_oracle_on_compacted_states():
     assert_means_close(r["next_obs"], nobs, s[:-1], what="iv next_obs")
     assert_means_close(r["rew"], rew, s[-1:], what="iv reward")
     assert np.allclose(r["dkl"], info["ensemble_dkl_path"], rtol=0.1, atol=1e-7)
+
+
+@pytest.mark.parametrize("mode", ["uncertainty", "iv_gae"])
+def test_pack_records_kernel_matches_mask_selection(mode):
+    """cmbpo_pack_records == populated-mask selection in [path, t] order (modelbuffer.py:348-405), bit-exact,
+    for a ragged 2-D pool and an 'iv_gae' pool; coordinates carry the global path id."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    from constrainedmbpo_b200 import sharding, _lib
+    env, B, T = "antsafe", 1777, 9
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    obs, _ = make_inputs(env, B)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True, seed=1)
+    ro = cm.ModelRollout(fe, T, rollout_mode=mode, dkl_lim=2e-5 if mode == "uncertainty" else None, row_offset=5000)
+    ro.reset(obs)
+    ro.run(cm.StubPolicy(29, 8))
+    E = 7 if mode == "iv_gae" else 1
+    W = sharding.record_width(29, 8, E)
+    assert W == _lib.load().cmbpo_record_width(29, 8, E)
+    n_ref = int(ro.pool["populated"].sum())
+    assert 0 < n_ref < B * (T - 1)
+    out = torch.full((n_ref + 3, W), -7.0, device="cuda")
+    count = torch.zeros(1, dtype=torch.int64, device="cuda")
+    scratch = torch.empty(int(_lib.load().cmbpo_pack_scratch_bytes(B)) + 64, dtype=torch.uint8, device="cuda")
+    sharding.pack_records_cuda(ro.pool, ro.row_offset, 29, 8, E, out, count, scratch)
+    torch.cuda.synchronize()
+    assert int(count) == n_ref
+    rec, coords = sharding.pack_records(ro.pool, ro.row_offset)
+    assert rec.shape == (n_ref, W - 2)
+    assert torch.equal(out[:n_ref, : W - 2], rec)
+    assert torch.equal(out[:n_ref, W - 2:].contiguous().view(torch.int32).long(), coords)
+    assert bool((out[n_ref:] == -7.0).all())                      # nothing written past the count
+    un = sharding.unpack_gathered(out[:n_ref], 29, 8, E)
+    assert torch.equal(un["coords"], coords) and un["term"].dtype == torch.bool
+    if E > 1:
+        assert un["obs"].shape == (n_ref, 7, 29) and un["rew"].shape == (n_ref, 7)
+        assert torch.equal(un["obs"], ro.transitions()["obs"])
+    # too-small capacity: count still reports the need, the buffer is not overrun
+    small = torch.full((10, W), -7.0, device="cuda")
+    sharding.pack_records_cuda(ro.pool, ro.row_offset, 29, 8, E, small, count, scratch)
+    torch.cuda.synchronize()
+    assert int(count) == n_ref

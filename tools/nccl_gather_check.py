@@ -1,0 +1,68 @@
+#!/usr/bin/env python
+"""N-GPU check of the transition all-gather (run under torchrun, one rank per GPU):
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/nccl_gather_check.py
+Each rank rolls out its row block (global row ids via row_offset); the gathered records must equal, bit for bit,
+the rollout of ALL rows on one GPU (SURVEY §8e parity statement) -- for ragged ('uncertainty') and equal
+('schedule') shard sizes, pipelined over several rollouts."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import constrainedmbpo_b200 as cm  # noqa: E402
+from constrainedmbpo_b200 import sharding  # noqa: E402
+from tests.helpers import build_cuda_env, make_inputs, make_params  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=dev)
+    env, hidden, B = "antsafe", (200, 200, 200, 200), 20_001
+    p = make_params(env, hidden, parity_scalers=False, bias=False)
+    obs_all, _ = make_inputs(env, B)
+    ok = True
+    for mode, T, lim in (("uncertainty", 10, 3e-5), ("schedule", 5, None), ("iv_gae", 5, None)):
+        fe = cm.FakeEnv(cm.SimpleEnv(29, 8), env, num_networks=7, num_elites=5, hidden_dims=hidden,
+                        cares_about_cost=True, device=str(dev), seed=3)
+        fe._model.load_state([w.astype(np.float32) for w in p.weights], [b.astype(np.float32) for b in p.biases],
+                             scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+        lo, hi = sharding.shard_bounds(B, world, rank)
+        obs = torch.from_numpy(obs_all[lo:hi]).to(dev)
+        full, counts = _run(fe, obs, lo, T, mode, lim, world, 3)
+        ref, _ = _run(fe, torch.from_numpy(obs_all).to(dev), 0, T, mode, lim, None, 1)
+        same = full.shape == ref.shape and torch.equal(full.view(torch.int32), ref.view(torch.int32))
+        ok = ok and same
+        if rank == 0:
+            print(f"{mode}: gathered {tuple(full.shape)} counts={counts} equal_to_single_gpu={same}", flush=True)
+    t = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    dist.destroy_process_group()
+    sys.exit(0 if int(t) == 1 else 1)
+
+
+def _run(fe, obs, lo, T, mode, lim, world, n):
+    perms = [np.random.default_rng(100 + t).permutation(7) for t in range(T + 1)]
+    ro = cm.ModelRollout(fe, T, rollout_mode=mode, dkl_lim=lim, row_offset=lo, perm_fn=lambda t: perms[t])
+    pol = cm.StubPolicy(fe.obs_dim, fe.act_dim, device=fe.device)
+    g = sharding.PoolGatherer(ro, world) if world else None
+    for _ in range(n):
+        fe._rng_offset = 0
+        ro.reset(obs)
+        ro.run(pol)
+        if g:
+            g.launch()
+    if g:
+        return g.wait()
+    torch.cuda.synchronize()
+    rec, coords = sharding.pack_records(ro.pool, lo)
+    return torch.cat([rec, coords.to(torch.int32).view(torch.float32)], dim=1), None
+
+
+if __name__ == "__main__":
+    main()
