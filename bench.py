@@ -246,9 +246,16 @@ def run_gpu(args, w, wname):
             ro.reset(start_dev)
             ro.run(policy)
     gather = None
-    if world > 1:
-        from constrainedmbpo_b200.sharding import PoolGatherer
-        gather = PoolGatherer(ro, world)
+    if world > 1 and args.gather != "none":
+        from constrainedmbpo_b200.sharding import P2PPoolGatherer, PoolGatherer
+        if args.transport == "p2p":
+            PoolGatherer = P2PPoolGatherer
+        group = None
+        if args.nccl_max_ctas > 0:   # cap the SMs NCCL takes from the persistent forward kernel
+            opts = dist.ProcessGroupNCCL.Options()
+            opts.config.max_ctas = args.nccl_max_ctas
+            group = dist.new_group(pg_options=opts)
+        gather = PoolGatherer(ro, world, group=group, pack_only=(args.gather == "pack"))
 
     def one_step():
         step_fn()
@@ -371,7 +378,7 @@ def run_gpu(args, w, wname):
                    "dkl_lim": dkl_lim, "transitions_per_rollout_per_gpu": per_rollout,
                    "rows_forwarded_per_rollout": rows_forwarded, "cuda_graph": use_graph,
                    "l2": "no explicit flush: per-rollout working set (model pool + head scratch, > 0.9 GB at the named size) exceeds the 126 MB L2",
-                   "parallelism": f"rows sharded x{args.gpus}, weights replicated" + (", NCCL all-gather of transitions" if world > 1 else "")},
+                   "parallelism": f"rows sharded x{args.gpus}, weights replicated" + (f", NCCL all-gather of transitions (transport={args.transport}, gather={args.gather}, max_ctas={args.nccl_max_ctas or 'default'})" if world > 1 else "")},
         "clocks": clk,
         "e2e": {"value": e2e_val, "unit": "transitions/s", "h2d_bytes_per_step": int(start_host.numel() * 4),
                 "d2h_bytes_per_step": int(rec * per_rollout), "steps": e2e_steps},
@@ -399,6 +406,11 @@ def main():
     ap.add_argument("--rows", type=int, default=0, help="override start states per GPU")
     ap.add_argument("--cpu-rows", type=int, default=0, help="start states of the CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--gather", default="full", choices=["full", "pack", "none"],
+                    help="N>1 diagnosis: full = pack + NCCL all-gather (the measured path), pack = packing only, none")
+    ap.add_argument("--transport", default="nccl", choices=["nccl", "p2p"],
+                    help="N>1: NCCL all-gather kernels, or copy-engine pulls over symmetric-memory peer mappings")
+    ap.add_argument("--nccl-max-ctas", type=int, default=0, help="N>1: NCCL max_ctas of the gather group (0 = default)")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
     w = WORKLOADS[args.workload]

@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
   s_pid[threadIdx.x] = pid;
   s_rem[threadIdx.x] = remaining ? 1 : 0;
   if (remaining) {
-    const size_t slot = (size_t)pid * T + ptr;
+    const size_t slot = (size_t)ptr * cap + pid;   // time-major storage [T][n_paths]: one step's stores are contiguous
     for (int e = 0; e < E; ++e) {
       const size_t se = e * cap * T + slot, ie = e * cap + i;
       static_cast<float*>(io.pool_rew_dev)[se] = static_cast<const float*>(io.rew_dev)[ie];
@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
     for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {
       const int r = idx / OD, d = idx - r * OD;
       if (s_rem[r]) {
-        const size_t o = ((size_t)s_pid[r] * T + ptr) * OD + d;
+        const size_t o = ((size_t)ptr * cap + s_pid[r]) * OD + d;
         po[o] = so[idx];
         pn[o] = sn[idx];
       }
@@ -195,30 +195,41 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
 #pragma unroll 4
       for (int idx = threadIdx.x; idx < n_here * AD; idx += kRB) {
         const int r = idx / AD, d = idx - r * AD;
-        if (s_rem[r]) pa[((size_t)s_pid[r] * T + ptr) * AD + d] = sa[idx];
+        if (s_rem[r]) pa[((size_t)ptr * cap + s_pid[r]) * AD + d] = sa[idx];
       }
     }
   }
 }
 
-// synthetic benchmark policy a = tanh(obs @ P); not part of the reference
+// synthetic benchmark policy a = tanh(obs @ P); not part of the reference.  64-row tiles of
+// obs are staged through shared memory so that global loads and stores are both coalesced.
+constexpr int kPolRows = 64;
 __global__ void __launch_bounds__(256) k_stub_policy(const float* __restrict__ obs, const float* __restrict__ P,
                                                      float* __restrict__ act, const int* n_rows_dev,
                                                      long long n_rows, int OD, int AD, int n_slots) {
-  extern __shared__ float sP[];
+  extern __shared__ float sm[];
+  float* sP = sm;                       // [OD][AD]
+  float* sO = sm + OD * AD;             // [kPolRows][OD + 1]
   for (int i = threadIdx.x; i < OD * AD; i += blockDim.x) sP[i] = P[i];
-  __syncthreads();
   const long long n = n_rows_dev ? (long long)(*n_rows_dev) : n_rows;
-  const long long per_slot = n * AD;
-  const long long total = per_slot * n_slots;   // slot e of obs / act starts at row e * n_rows (capacity)
-  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const long long slot = idx / per_slot, j = idx - slot * per_slot;
-    const long long r = slot * n_rows + j / AD;
-    const int a = (int)(j % AD);
-    float s = 0.f;
-    for (int d = 0; d < OD; ++d) s = fmaf(obs[(size_t)r * OD + d], sP[d * AD + a], s);
-    act[(size_t)r * AD + a] = tanhf(s);
+  const long long tiles_per_slot = (n + kPolRows - 1) / kPolRows;
+  const long long n_tiles = tiles_per_slot * n_slots;   // slot e of obs / act starts at row e * n_rows (capacity)
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long slot = tile / tiles_per_slot, r0 = (tile - slot * tiles_per_slot) * kPolRows;
+    const int rows_here = (int)min((long long)kPolRows, n - r0);
+    const size_t row_base = (size_t)(slot * n_rows + r0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < rows_here * OD; i += blockDim.x) {
+      const int r = i / OD, d = i - r * OD;
+      sO[r * (OD + 1) + d] = obs[row_base * OD + i];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < rows_here * AD; i += blockDim.x) {
+      const int r = i / AD, a = i - r * AD;
+      float s = 0.f;
+      for (int d = 0; d < OD; ++d) s = fmaf(sO[r * (OD + 1) + d], sP[d * AD + a], s);
+      act[row_base * AD + i] = tanhf(s);
+    }
   }
 }
 
@@ -293,9 +304,11 @@ extern "C" int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* a
   if (!obs_dev || !P_dev || !act_dev || n_rows < 0) return CMBPO_ERR_ARG;
   if (n_rows == 0) return CMBPO_OK;
   if (n_slots < 1) n_slots = 1;
-  long long blocks = (n_rows * act_dim * n_slots + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  k_stub_policy<<<(int)blocks, 256, obs_dim * act_dim * sizeof(float), (cudaStream_t)stream_>>>(
+  long long blocks = ((n_rows + kPolRows - 1) / kPolRows) * n_slots;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  const size_t smem = ((size_t)obs_dim * act_dim + (size_t)kPolRows * (obs_dim + 1)) * sizeof(float);
+  if (smem > 48 * 1024) return CMBPO_ERR_UNSUPPORTED;
+  k_stub_policy<<<(int)blocks, 256, smem, (cudaStream_t)stream_>>>(
       static_cast<const float*>(obs_dev), static_cast<const float*>(P_dev), static_cast<float*>(act_dev),
       static_cast<const int*>(n_rows_dev), n_rows, obs_dim, act_dim, n_slots);
   return cudaGetLastError() == cudaSuccess ? CMBPO_OK : CMBPO_ERR_CUDA;
@@ -333,8 +346,8 @@ __global__ void __launch_bounds__(kRB) k_pack_count(cmbpo_pack_io io, int* path_
   const int T = io.max_path_length;
   int len = 0;
   if (b < io.n_paths) {
-    const uint8_t* m = io.pool_populated_dev + (size_t)b * T;
-    for (int t = 0; t < T; ++t) len += m[t] ? 1 : 0;
+    const uint8_t* m = io.pool_populated_dev + (size_t)b;   // storage [T][n_paths]
+    for (int t = 0; t < T; ++t) len += m[(size_t)t * io.n_paths] ? 1 : 0;
   }
   int tot;
   const int off = block_exclusive_scan_int(len, &tot);
@@ -367,40 +380,71 @@ __global__ void __launch_bounds__(1024) k_pack_scan(int* blk_cnt, int n_blocks, 
   if (threadIdx.x == 0) *count_out = carry;
 }
 
+constexpr int kPackSub = 4;              // write blocks per 256-path scan block (more blocks in flight: the
+constexpr int kPackPaths = kRB / kPackSub;   // per-record chain lookup -> loads -> store is latency-bound)
 __global__ void __launch_bounds__(kRB) k_pack_write(cmbpo_pack_io io, const int* path_off, const int* blk_cnt,
                                                     const long long* blk_off, int W) {
-  __shared__ int s_off[kRB + 1];
-  const long long b0 = (long long)blockIdx.x * kRB;
-  const int n_here = (int)min((long long)kRB, io.n_paths - b0);
-  const int total = blk_cnt[blockIdx.x];
-  s_off[threadIdx.x] = (threadIdx.x < n_here) ? path_off[b0 + threadIdx.x] : total;
-  if (threadIdx.x == 0) s_off[kRB] = total;
+  __shared__ int s_off[kPackPaths + 1];
+  const int blk = blockIdx.x / kPackSub, sub = blockIdx.x % kPackSub;
+  const long long b0 = (long long)blk * kRB + (long long)sub * kPackPaths;
+  const int blk_total = blk_cnt[blk];
+  if (threadIdx.x <= kPackPaths) {
+    const long long bp = b0 + threadIdx.x;
+    const bool in_blk = (sub * kPackPaths + (int)threadIdx.x) < kRB && bp < io.n_paths;
+    s_off[threadIdx.x] = in_blk ? path_off[bp] : blk_total;
+  }
   __syncthreads();
-  const long long out0 = blk_off[blockIdx.x];
-  if (out0 + total > io.capacity) return;   // caller sized the buffer too small: count_dev still reports the need
+  const int rec_lo = s_off[0], total = s_off[kPackPaths];
+  const long long out0 = blk_off[blk];
+  if (out0 + blk_total > io.capacity) return;   // caller sized the buffer too small: count_dev still reports the need
   const int E = io.n_members > 1 ? io.n_members : 1;
   const int OD = io.obs_dim, AD = io.act_dim, T = io.max_path_length;
   const int c0 = E * OD, c1 = c0 + E * AD, c2 = c1 + E * OD, c3 = c2 + E, c4 = c3 + E, c5 = c4 + 1, c6 = c5 + E;
   const size_t B = (size_t)io.n_paths;
   float* out = io.records_dev + (size_t)out0 * W;
-  const long long n_elems = (long long)total * W;
-  for (long long idx = threadIdx.x; idx < n_elems; idx += kRB) {
-    const int rec = (int)(idx / W), col = (int)(idx - (long long)rec * W);
-    int lo = 0, hi = kRB;   // last path with s_off[path] <= rec (paths without records share their successor's offset)
-    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_off[mid] <= rec) lo = mid; else hi = mid; }
-    const int t = rec - s_off[lo];
-    const size_t b = (size_t)(b0 + lo);
-    float v;
-    if (col < c0) { const int e = col / OD, d = col - e * OD; v = io.pool_obs_dev[((e * B + b) * T + t) * OD + d]; }
-    else if (col < c1) { const int k = col - c0, e = k / AD, d = k - e * AD; v = io.pool_act_dev[((e * B + b) * T + t) * AD + d]; }
-    else if (col < c2) { const int k = col - c1, e = k / OD, d = k - e * OD; v = io.pool_next_obs_dev[((e * B + b) * T + t) * OD + d]; }
-    else if (col < c3) v = io.pool_rew_dev[((col - c2) * B + b) * T + t];
-    else if (col < c4) v = io.pool_cost_dev[((col - c3) * B + b) * T + t];
-    else if (col < c5) v = io.pool_dyn_error_dev[b * T + t];
-    else if (col < c6) v = io.pool_term_dev[((col - c5) * B + b) * T + t] ? 1.0f : 0.0f;
-    else if (col == c6) v = __int_as_float((int)(io.row_offset + (long long)b));
-    else v = __int_as_float(t);
-    out[idx] = v;
+  // one warp per record (the path lookup is warp-uniform), lanes stride over the record's columns; kU records
+  // are in flight per warp so kU independent global loads overlap (a single chain ran at ~0.9 TB/s)
+  constexpr int kU = 4, kWarps = kRB / 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int rec0 = rec_lo + warp; rec0 < total; rec0 += kWarps * kU) {
+    int tt[kU];
+    size_t bb[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int rec = min(rec0 + u * kWarps, total - 1);
+      int lo = 0, hi = kPackPaths;   // last path with s_off[path] <= rec (paths without records share their successor's offset)
+      while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_off[mid] <= rec) lo = mid; else hi = mid; }
+      tt[u] = rec - s_off[lo];
+      bb[u] = (size_t)(b0 + lo);
+    }
+    for (int col = lane; col < W; col += 32) {
+      // column -> (field base pointer, element stride decode) is the same for all kU records
+      const float* base = nullptr;
+      const uint8_t* tbase = nullptr;
+      int e = 0, d = 0, width = 1, kind = 0;   // kind 0: float field, 1: term byte, 2: path id, 3: t
+      if (col < c0) { e = (E == 1) ? 0 : col / OD; d = col - e * OD; width = OD; base = io.pool_obs_dev; }
+      else if (col < c1) { const int k = col - c0; e = (E == 1) ? 0 : k / AD; d = k - e * AD; width = AD; base = io.pool_act_dev; }
+      else if (col < c2) { const int k = col - c1; e = (E == 1) ? 0 : k / OD; d = k - e * OD; width = OD; base = io.pool_next_obs_dev; }
+      else if (col < c3) { e = col - c2; base = io.pool_rew_dev; }
+      else if (col < c4) { e = col - c3; base = io.pool_cost_dev; }
+      else if (col < c5) { base = io.pool_dyn_error_dev; }
+      else if (col < c6) { e = col - c5; tbase = io.pool_term_dev; kind = 1; }
+      else kind = (col == c6) ? 2 : 3;
+      float v[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const size_t cell = ((size_t)e * T + tt[u]) * B + bb[u];   // storage [E][T][n_paths]
+        if (kind == 0) v[u] = __ldg(base + cell * width + d);
+        else if (kind == 1) v[u] = __ldg(tbase + cell) ? 1.0f : 0.0f;
+        else if (kind == 2) v[u] = __int_as_float((int)(io.row_offset + (long long)bb[u]));
+        else v[u] = __int_as_float(tt[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int rec = rec0 + u * kWarps;
+        if (rec < total) out[(size_t)rec * W + col] = v[u];
+      }
+    }
   }
 }
 }  // namespace cmbpo
@@ -428,7 +472,7 @@ extern "C" int cmbpo_pack_records(const cmbpo_pack_io* io_, void* stream_) {
   int* blk_cnt = path_off + io.n_paths;
   if (nb > 0) k_pack_count<<<nb, kRB, 0, stream>>>(io, path_off, blk_cnt);
   k_pack_scan<<<1, 1024, 0, stream>>>(blk_cnt, nb, blk_off, reinterpret_cast<long long*>(io.count_dev));
-  if (nb > 0) k_pack_write<<<nb, kRB, 0, stream>>>(io, path_off, blk_cnt, blk_off,
+  if (nb > 0) k_pack_write<<<nb * kPackSub, kRB, 0, stream>>>(io, path_off, blk_cnt, blk_off,
                                                    cmbpo_record_width(io.obs_dim, io.act_dim, io.n_members));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(g_roll_err, sizeof(g_roll_err), "pack_records: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }

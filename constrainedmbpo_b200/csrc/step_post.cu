@@ -162,13 +162,62 @@ constexpr int kPostRows = 32;
 constexpr int kPostParts = 16;
 constexpr int kPostThreads = kPostRows * kPostParts;
 
+// Block partial sums of the four scalar diagnostics (fake_env.py:213-220); the last block to finish sums
+// the partials in block order (deterministic) and writes the 4 means.
+template <int E>
+__device__ __forceinline__ void finish_scalars(const StepParams& p, const float (&vals)[4], long long n_rows,
+                                               int n_slots_out) {
+  __shared__ float red[4][kPostParts];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float x = vals[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) red[k][warp] = x;
+  }
+  __syncthreads();
+  if (tid < 4) {
+    float x = 0.f;
+    for (int w = 0; w < kPostParts; ++w) x += red[tid][w];
+    p.partials[(size_t)blockIdx.x * 4 + tid] = x;
+  }
+  // ---- the last block to finish sums the partials in block order (deterministic) -> 4 means
+  __shared__ bool s_last;
+  __shared__ double sh[4][kPostParts];
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = atomicAdd(p.ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double s[4] = {0, 0, 0, 0};
+  for (int b = tid; b < (int)gridDim.x; b += kPostThreads)
+    for (int k = 0; k < 4; ++k) s[k] += (double)__ldcg(p.partials + (size_t)b * 4 + k);
+  for (int k = 0; k < 4; ++k) {
+    double x = s[k];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) sh[k][warp] = x;
+  }
+  __syncthreads();
+  if (tid < 4) {
+    double x = 0;
+    for (int w = 0; w < kPostParts; ++w) x += sh[tid][w];
+    const double n = (double)n_rows;
+    double denom = n;                                        // dkl_mean
+    if (tid == 1) denom = n * (double)E * (double)p.D;       // ensemble_mean_var over [E,B,D]
+    if (tid >= 2) denom = n * (double)n_slots_out;           // rew_mean / cost_mean
+    p.scalars[tid] = (float)(denom > 0 ? x / denom : 0.0);
+  }
+  if (tid == 0) *p.ticket = 0;   // ready for the next launch
+}
+
 template <int E>
 __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepParams p) {
   __shared__ float tile[kPostRows * 64 + 32];  // obs in / next_obs out staging (obs_dim <= 64)
   __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
   __shared__ float s_rew[kPostRows];
   __shared__ uint8_t s_flags[kPostParts][kPostRows];
-  __shared__ float red[4][kPostParts];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int r = lane, part = warp;
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
@@ -302,49 +351,131 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
       acc_dkl += dkl;
     }
   }
-  // ---- block partial sums of the four scalar diagnostics (fake_env.py:213-220)
-  float vals[4] = {acc_dkl, acc_var, acc_rew, acc_cost};
+  const float vals[4] = {acc_dkl, acc_var, acc_rew, acc_cost};
+  finish_scalars<E>(p, vals, n_rows, n_slots_out);
+}
+
+
+// 3-D inputs ('iv_gae' rollouts, fake_env.py:147-153,:164-165): every member keeps its own sample, so a row
+// has E observations in and E next observations out.  The column statistics (KL, var_E) are computed ONCE per
+// (row, column) with member e's mean shifted by member e's own observation; all E member tiles live in
+// (dynamic) shared memory so global traffic stays coalesced.  Warp `part` < E then evaluates the static
+// termination / cost function of member `part`.
+template <int E>
+__global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const StepParams p) {
+  extern __shared__ float tiles[];                 // [E][kPostRows * OD]
+  __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
+  __shared__ float s_rew[E][kPostRows];
+  __shared__ uint8_t s_fin[kPostParts][kPostRows], s_lt[kPostParts][kPostRows];   // bit e = member e
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int r = lane, part = warp;
+  const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
+  const long long slot_rows = p.n_rows;            // member stride = capacity
+  const int D = p.D, OD = p.obs_dim;
+  const int tile_elems = kPostRows * OD;
+  float acc_dkl = 0.f, acc_var = 0.f, acc_rew = 0.f, acc_cost = 0.f;
+
+  for (long long row0 = (long long)blockIdx.x * kPostRows; row0 < n_rows; row0 += (long long)gridDim.x * kPostRows) {
+    const long long g = row0 + r;
+    const bool live = g < n_rows;
+    const int rows_here = (int)min((long long)kPostRows, n_rows - row0);
+    __syncthreads();
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    float x = vals[k];
+    for (int e = 0; e < E; ++e) {
+      const float* src = p.obs + ((size_t)e * slot_rows + row0) * OD;
+      for (int i = tid; i < rows_here * OD; i += kPostThreads) tiles[e * tile_elems + i] = src[i];
+    }
+    __syncthreads();
+    float kl_row = 0.f, epv_row = 0.f;
+    uint32_t fin = (1u << E) - 1u, lt = (1u << E) - 1u;
+    if (live) {
+      for (int d = part; d < D; d += kPostParts) {
+        float m[E], lv[E], v[E];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-    if (lane == 0) red[k][warp] = x;
+        for (int e = 0; e < E; ++e) {
+          const float* hm = p.heads + head_index(g, e, d, E, 2 * D);
+          m[e] = hm[0];
+          lv[e] = hm[(size_t)D * kTileRows];
+        }
+        if (d < OD) {
+#pragma unroll
+          for (int e = 0; e < E; ++e) m[e] += tiles[e * tile_elems + r * OD + d];   // fake_env.py:156
+        }
+        float lvmin = lv[0], lvmax = lv[0];
+#pragma unroll
+        for (int e = 1; e < E; ++e) { lvmin = fminf(lvmin, lv[e]); lvmax = fmaxf(lvmax, lv[e]); }
+        bool weird = !(lvmin > -80.f) || !(lvmax < 80.f);
+#pragma unroll
+        for (int e = 0; e < E; ++e) weird = weird || !(fabsf(m[e]) < 1e18f);
+        float kl, epv;
+        if (weird) column_stats<E, true>(m, lv, v, kl, epv);
+        else column_stats<E, false>(m, lv, v, kl, epv);
+        kl_row += kl; epv_row += epv;
+        float sv = 0.f;
+#pragma unroll
+        for (int e = 0; e < E; ++e) sv += v[e];
+        acc_var += sv;
+        if (p.ep_var) p.ep_var[(size_t)g * D + d] = epv;
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          float x = m[e];
+          if (p.noise) x = fmaf(p.noise[((size_t)e * slot_rows + g) * D + d], sqrtf(v[e]), x);
+          if (d < OD) {
+            tiles[e * tile_elems + r * OD + d] = x;   // own element only
+            if (!(fabsf(x) <= 3.402823466e38f)) fin &= ~(1u << e);
+            if (d >= 1 && !(x < 100.f)) lt &= ~(1u << e);
+          } else {
+            s_rew[e][r] = x;                           // reward = last output column (fake_env.py:180)
+          }
+        }
+      }
+    }
+    s_fin[part][r] = (uint8_t)fin;
+    s_lt[part][r] = (uint8_t)lt;
+    s_kl[part][r] = kl_row;
+    s_epv[part][r] = epv_row;
+    __syncthreads();
+    for (int so = part; so < E; so += kPostParts) {
+      if (live) {
+        RowFeatures f;
+        uint32_t a = 0xffu, b = 0xffu;
+#pragma unroll
+        for (int q = 0; q < kPostParts; ++q) { a &= s_fin[q][r]; b &= s_lt[q][r]; }
+        f.finite_all = ((a >> so) & 1u) != 0;
+        f.lt100_from1 = ((b >> so) & 1u) != 0;
+        const float* xr = tiles + so * tile_elems + r * OD;
+        f.x0 = xr[0];
+        f.x1 = OD > 1 ? xr[1] : 0.f;
+        f.x2 = OD > 2 ? xr[2] : 0.f;
+        f.x3 = OD > 3 ? xr[3] : 0.f;
+        f.last = xr[OD - 1];
+        const float rew = s_rew[so][r];
+        const bool done = termination(p.env_id, f);
+        const float cost = (p.cost_mode == 1) ? static_cost(p.env_id, f, done) : 0.f;
+        const size_t oi = (size_t)so * slot_rows + g;
+        p.rew[oi] = rew;
+        p.term[oi] = done ? 1 : 0;
+        if (p.cost) p.cost[oi] = cost;
+        acc_rew += rew; acc_cost += cost;
+      }
+    }
+    if (live && part == kPostParts - 1) {
+      float ks = 0.f, es = 0.f;
+#pragma unroll
+      for (int q = 0; q < kPostParts; ++q) { ks += s_kl[q][r]; es += s_epv[q][r]; }
+      const float dkl = ks / (float)D;
+      p.dkl_path[g] = dkl;
+      if (p.ep_var_mean) p.ep_var_mean[g] = es / (float)D;
+      acc_dkl += dkl;
+    }
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+      float* dst = p.next_obs + ((size_t)e * slot_rows + row0) * OD;
+      for (int i = tid; i < rows_here * OD; i += kPostThreads) dst[i] = tiles[e * tile_elems + i];
+    }
   }
-  __syncthreads();
-  if (tid < 4) {
-    float x = 0.f;
-    for (int w = 0; w < kPostParts; ++w) x += red[tid][w];
-    p.partials[(size_t)blockIdx.x * 4 + tid] = x;
-  }
-  // ---- the last block to finish sums the partials in block order (deterministic) -> 4 means
-  __shared__ bool s_last;
-  __shared__ double sh[4][kPostParts];
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) s_last = atomicAdd(p.ticket, 1u) == gridDim.x - 1;
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  double s[4] = {0, 0, 0, 0};
-  for (int b = tid; b < (int)gridDim.x; b += kPostThreads)
-    for (int k = 0; k < 4; ++k) s[k] += (double)__ldcg(p.partials + (size_t)b * 4 + k);
-  for (int k = 0; k < 4; ++k) {
-    double x = s[k];
-    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-    if (lane == 0) sh[k][warp] = x;
-  }
-  __syncthreads();
-  if (tid < 4) {
-    double x = 0;
-    for (int w = 0; w < kPostParts; ++w) x += sh[tid][w];
-    const double n = (double)n_rows;
-    double denom = n;                                        // dkl_mean
-    if (tid == 1) denom = n * (double)E * (double)D;         // ensemble_mean_var over [E,B,D]
-    if (tid >= 2) denom = n * (double)n_slots_out;           // rew_mean / cost_mean
-    p.scalars[tid] = (float)(denom > 0 ? x / denom : 0.0);
-  }
-  if (tid == 0) *p.ticket = 0;   // ready for the next launch
+  const float vals[4] = {acc_dkl, acc_var, acc_rew, acc_cost};
+  finish_scalars<E>(p, vals, n_rows, E);
 }
 
 // deterministic final reduction of the per-block partial sums -> 4 means
@@ -417,6 +548,18 @@ __global__ void aggregate_predict_kernel(const float* __restrict__ heads, long l
 
 template <int E>
 static cudaError_t launch_step_post_E(const StepParams& p, int n_blocks, cudaStream_t stream) {
+  if (p.per_slot && E > 1) {
+    const size_t smem = (size_t)E * kPostRows * p.obs_dim * sizeof(float);
+    static bool attr_set = false;   // same value for every launch of this instantiation (obs_dim <= 64)
+    if (!attr_set) {
+      cudaError_t e = cudaFuncSetAttribute(step_post3d_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)((size_t)E * kPostRows * 64 * sizeof(float)));
+      if (e != cudaSuccess) return e;
+      attr_set = true;
+    }
+    step_post3d_kernel<E><<<n_blocks, kPostThreads, smem, stream>>>(p);
+    return cudaGetLastError();
+  }
   step_post_kernel<E><<<n_blocks, kPostThreads, 0, stream>>>(p);
   return cudaGetLastError();
 }

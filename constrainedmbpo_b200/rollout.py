@@ -99,10 +99,15 @@ class ModelRollout:
         # 'iv_gae': one trajectory per ensemble member -- leading E on the per-transition arrays
         # (model_sampler.py:225-226, modelbuffer.py:48-51); dyn_error / populated stay [B, T] (:59,:110)
         E = (self.env.num_networks,) if self.mode == "iv_gae" else ()
+        # The tensors are the reference's logical [B, T, .] arrays (views); their STORAGE is time-major
+        # [T, B, .] so that one sampler step's stores are contiguous (include/cmbpo_b200.h, pool pointers).
+        n = len(E)
+        vec = lambda w: z(*E, T, B, w).transpose(n, n + 1)
+        sca = lambda dt=torch.float32: z(*E, T, B, dt=dt).transpose(n, n + 1)
         self.pool = {
-            "obs": z(*E, B, T, OD), "act": z(*E, B, T, AD), "next_obs": z(*E, B, T, OD),
-            "rew": z(*E, B, T), "cost": z(*E, B, T), "term": z(*E, B, T, dt=torch.uint8),
-            "dyn_error": z(B, T), "populated": z(B, T, dt=torch.uint8),
+            "obs": vec(OD), "act": vec(AD), "next_obs": vec(OD),
+            "rew": sca(), "cost": sca(), "term": sca(torch.uint8),
+            "dyn_error": z(T, B).t(), "populated": z(T, B, dt=torch.uint8).t(),
         }
         self.cur = [torch.empty(*E, B, OD, dtype=torch.float32, device=dev) for _ in range(2)]
         self.pid = [torch.empty(B, dtype=torch.int32, device=dev) for _ in range(2)]

@@ -96,6 +96,8 @@ def pack_records_cuda(pool: dict, row_offset, obs_dim, act_dim, n_members, out, 
     from . import _lib
     lib = _lib.load()
     B, T = pool["populated"].shape
+    if pool["populated"].stride() != (1, B) or pool["obs"].stride()[-3:] != (obs_dim, B * obs_dim, 1):
+        raise ValueError("pack_records_cuda expects ModelRollout pools (logical [B,T,.] views of time-major storage)")
     io = _lib.cmbpo_pack_io()
     io.n_paths, io.max_path_length, io.obs_dim, io.act_dim = B, T, obs_dim, act_dim
     io.n_members, io.row_offset = (n_members if n_members > 1 else 0), int(row_offset)
@@ -122,8 +124,9 @@ class PoolGatherer:
     pipeline and returns ``(records, counts)`` of the last rollout; ``records[:, -2:]`` viewed as
     int32 are the (global path, t) coordinates."""
 
-    def __init__(self, rollout, world, group=None, capacity=None):
+    def __init__(self, rollout, world, group=None, capacity=None, pack_only=False):
         self.ro, self.world, self.group = rollout, world, group
+        self.pack_only = pack_only   # measurement aid: skip the collective
         self.capacity = capacity
         self.last = None
         self._pending = None
@@ -168,6 +171,9 @@ class PoolGatherer:
         n = int(b["count_host"][0])
         if n > b["rec"].shape[0]:
             raise RuntimeError(f"PoolGatherer: {n} transitions exceed the staging capacity {b['rec'].shape[0]}")
+        if self.pack_only:
+            self.last = (b["rec"][:n], [n])
+            return
         with torch.cuda.stream(self._side):
             counts_dev = torch.empty(self.world, dtype=torch.int64, device=b["rec"].device)
             dist.all_gather_into_tensor(counts_dev, b["count"], group=self.group)
@@ -196,6 +202,72 @@ class PoolGatherer:
         if self._buf is not None:
             self._side.synchronize()
         return self.last
+
+
+class P2PPoolGatherer(PoolGatherer):
+    """Same contract as ``PoolGatherer`` with the payload moved by the COPY ENGINES over NVLink peer
+    mappings instead of NCCL kernels: the staging buffers are symmetric memory
+    (``torch.distributed._symmetric_memory``), every rank pulls each peer's packed records straight into
+    its dense ``[sum(counts), W]`` matrix with ``cudaMemcpyAsync`` on a side stream.  No SM is taken from
+    the persistent forward kernel while the transfer overlaps the next rollout (an NCCL all-gather kernel
+    holds 8-32 SMs for the whole transfer, and a forward cluster that cannot become resident delays its
+    statically assigned tiles).  Cross-rank ordering: a symmetric-memory barrier after the pack ("records
+    visible") and one after the pulls ("staging reusable")."""
+
+    def _allocate(self):
+        import torch.distributed._symmetric_memory as symm
+        ro = self.ro
+        dev = ro.device
+        B, T = ro.pool["populated"].shape
+        self.E = ro.env.num_networks if ro.mode == "iv_gae" else 1
+        self.W = record_width(ro.env.obs_dim, ro.env.act_dim, self.E)
+        cap = int(self.capacity) if self.capacity else B * max(T - 1, 1)
+        group = self.group if self.group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(group)
+        capt = torch.tensor([cap], dtype=torch.int64, device=dev)   # symmetric buffers: same size on every rank
+        dist.all_reduce(capt, op=dist.ReduceOp.MAX, group=group)
+        cap = self.cap = int(capt.item())
+        from . import _lib
+        nscr = int(_lib.load().cmbpo_pack_scratch_bytes(B)) + 64
+        stage = symm.empty(2 * cap * self.W, dtype=torch.float32, device=dev)
+        cnt = symm.empty(16, dtype=torch.int64, device=dev)
+        cnt.zero_()
+        self._stage_h = symm.rendezvous(stage, group)
+        self._cnt_h = symm.rendezvous(cnt, group)
+        self._stage, self._cnt = stage, cnt
+        self._peer_stage = [[self._stage_h.get_buffer(r, (cap, self.W), torch.float32, s * cap * self.W)
+                             for r in range(self.world)] for s in range(2)]
+        self._peer_cnt = [self._cnt_h.get_buffer(r, (16,), torch.int64, 0) for r in range(self.world)]
+        self._buf = [dict(rec=self._peer_stage[s][self.rank], count=cnt[s:s + 1], slot=s,
+                          count_host=torch.zeros(1, dtype=torch.int64).pin_memory(),
+                          scratch=torch.empty(nscr, dtype=torch.uint8, device=dev),
+                          packed=torch.cuda.Event(), sent=None) for s in range(2)]
+        self._side = torch.cuda.Stream(device=dev)
+
+    def _collect(self, b):
+        s = b["slot"]
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(b["packed"])
+            self._stage_h.barrier(channel=0)                     # every rank's records of this rollout are visible
+            cnts = torch.stack([self._peer_cnt[r][s] for r in range(self.world)])
+            counts = [int(c) for c in cnts.cpu()]
+            if max(counts) > self.cap:
+                raise RuntimeError(f"PoolGatherer: {max(counts)} transitions exceed the staging capacity {self.cap}")
+            offs = [0]
+            for c in counts:
+                offs.append(offs[-1] + c)
+            full = torch.empty(offs[-1], self.W, dtype=torch.float32, device=b["rec"].device)
+            if not self.pack_only:
+                for i in range(self.world):                      # own shard first, then peers, staggered by rank
+                    r = (self.rank + i) % self.world
+                    if counts[r]:
+                        full[offs[r]:offs[r + 1]].copy_(self._peer_stage[s][r][:counts[r]], non_blocking=True)
+            self._stage_h.barrier(channel=1)                     # every rank has pulled: staging slot reusable
+            ev = torch.cuda.Event()
+            ev.record(self._side)
+            b["sent"] = ev
+        full.record_stream(self._side)
+        self.last = (full, counts)
 
 
 def unpack_gathered(rec: torch.Tensor, obs_dim: int, act_dim: int, n_members: int = 1):

@@ -146,8 +146,8 @@ typedef struct cmbpo_rollout_state {
  * its own state, model_sampler.py:225-226: cur_obs/act/next_obs/rew/term/cost are
  * [n_members][n_paths][.] with member stride n_paths rows, pools obs/act/next_obs/rew/cost/term are
  * [n_members][n_paths][T][.] (modelbuffer.py:48-51); no uncertainty cutoff and no max_samples cap
- * (:315,:327); a path ends when ANY member's state terminates (:445)).  Pools are [n_paths][T][dim]
- * (modelbuffer.py:45-114), row = original path id.  Survivors are compacted, order preserved,
+ * (:315,:327); a path ends when ANY member's state terminates (:445)).  Pools are indexed [path][t]
+ * (modelbuffer.py:45-114), path = original start-state row; see the storage note at the pool pointers.  Survivors are compacted, order preserved,
  * into new_obs / new_path_id; state is updated on the device (no host synchronisation). */
 typedef struct cmbpo_rollout_io {
   int64_t n_paths;             /* B: rows at reset, bounds every grid */
@@ -168,9 +168,12 @@ typedef struct cmbpo_rollout_io {
   const int32_t* path_id_dev;  /* [n_alive] original path of each alive row */
   void* state_dev;             /* cmbpo_rollout_state */
   double* dkl_accum_dev;       /* [B] _dyn_dkl_path: np.zeros => float64 upstream (model_sampler.py:244,:415) */
-  float* pool_obs_dev; float* pool_act_dev; float* pool_next_obs_dev;   /* [B][T][dim] */
-  float* pool_rew_dev; float* pool_cost_dev; uint8_t* pool_term_dev;    /* [B][T] */
-  float* pool_dyn_error_dev; uint8_t* pool_populated_dev;               /* [B][T] */
+  /* Model pools.  LOGICAL index is the reference's [path b][column t] (modelbuffer.py:45-114); the STORAGE is
+   * time-major, element (b, t) at ((t * n_paths) + b) * dim, so that the stores of one sampler step (all alive
+   * paths, one column) are contiguous.  'iv_gae': one such [T][n_paths][dim] block per member. */
+  float* pool_obs_dev; float* pool_act_dev; float* pool_next_obs_dev;   /* [T][B][dim] */
+  float* pool_rew_dev; float* pool_cost_dev; uint8_t* pool_term_dev;    /* [T][B] */
+  float* pool_dyn_error_dev; uint8_t* pool_populated_dev;               /* [T][B] */
   float* new_obs_dev;          /* [n_alive'][obs] compacted survivors */
   int32_t* new_path_id_dev;    /* [n_alive'] */
   void* scratch_dev; size_t scratch_bytes;   /* >= cmbpo_rollout_scratch_bytes(n_paths) */
@@ -184,7 +187,7 @@ int cmbpo_rollout_advance(const cmbpo_rollout_io* io, void* stream);
  * ModelBuffer.get selects with populated_mask (softlearning/replay_pools/modelbuffer.py:348-405), laid out
  * as the send buffer of the multi-GPU all-gather.  Record (width cmbpo_record_width):
  *   obs[E*obs] | act[E*act] | next_obs[E*obs] | rew[E] | cost[E] | dyn_error | term[E] | path | t
- * E = n_members for 'iv_gae' pools ([E][n_paths][T][.]), else 1; path (= row_offset + pool row) and t are
+ * E = n_members for 'iv_gae' pools, else 1 (pool storage as in cmbpo_rollout_io: time-major); path (= row_offset + pool row) and t are
  * int32 bit patterns.  count_dev receives the number of populated transitions; nothing is written for a
  * block of paths whose records would not fit `capacity` (compare count with capacity afterwards). */
 typedef struct cmbpo_pack_io {

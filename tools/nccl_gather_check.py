@@ -50,7 +50,8 @@ def _run(fe, obs, lo, T, mode, lim, world, n):
     perms = [np.random.default_rng(100 + t).permutation(7) for t in range(T + 1)]
     ro = cm.ModelRollout(fe, T, rollout_mode=mode, dkl_lim=lim, row_offset=lo, perm_fn=lambda t: perms[t])
     pol = cm.StubPolicy(fe.obs_dim, fe.act_dim, device=fe.device)
-    g = sharding.PoolGatherer(ro, world) if world else None
+    G = sharding.P2PPoolGatherer if os.environ.get("CMBPO_TRANSPORT") == "p2p" else sharding.PoolGatherer
+    g = G(ro, world) if world else None
     for _ in range(n):
         fe._rng_offset = 0
         ro.reset(obs)
