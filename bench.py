@@ -320,31 +320,40 @@ def run_gpu(args, w, wname):
     peaks = measured_peaks()
     peak = peaks["bf16_sustained"]
 
-    # ---- e2e: host start states in, populated transitions out, every step ------------------------
-    host_out = {}
+    # ---- e2e: host start states in (pinned -> H2D every step), populated transitions out to pinned host memory
+    # (pack kernel + one D2H per rollout on a side stream, overlapping the next rollout), all inside the timed region
+    from constrainedmbpo_b200.sharding import HostDrain
+    drain = HostDrain(ro)
+
     def e2e_step():
         start_dev.copy_(start_host, non_blocking=True)
         step_fn()
-        return ro.transitions(host_out)["_n"]
+        drain.launch()
     for _ in range(2):
         e2e_step()
+    drain.wait()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     e2e_steps = max(1, min(args.steps, 10))
     t0 = time.perf_counter()
     n_tr = 0
-    for _ in range(e2e_steps):
-        n_tr += e2e_step()
+    for k in range(e2e_steps):
+        e2e_step()
+        if k > 0:
+            n_tr += drain.last[1][0]          # rollout k-1: its device->host copy was just enqueued
+    host_rec, cnt = drain.wait()              # the last rollout's records are on the host when this returns
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    n_tr += cnt[0]
+    assert host_rec.shape[0] == cnt[0] > 0 and float(host_rec[:, 0].abs().sum()) > 0
     te = torch.tensor([e2e_s, float(n_tr)], dtype=torch.float64, device=dev)
     if world > 1:
         a = te.clone(); dist.all_reduce(a, op=dist.ReduceOp.MAX)
         b = te.clone(); dist.all_reduce(b, op=dist.ReduceOp.SUM)
         e2e_s, n_tr = float(a[0]), float(b[1])
     e2e_val = n_tr / e2e_s
-    rec = bytes_per_transition(w)
+    rec = drain.W * 4   # packed record: the transition payload + (path, t) coordinates
 
     if rank != 0:
         if world > 1:
@@ -408,7 +417,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--gather", default="full", choices=["full", "pack", "none"],
                     help="N>1 diagnosis: full = pack + NCCL all-gather (the measured path), pack = packing only, none")
-    ap.add_argument("--transport", default="nccl", choices=["nccl", "p2p"],
+    ap.add_argument("--transport", default="p2p", choices=["nccl", "p2p"],
                     help="N>1: NCCL all-gather kernels, or copy-engine pulls over symmetric-memory peer mappings")
     ap.add_argument("--nccl-max-ctas", type=int, default=0, help="N>1: NCCL max_ctas of the gather group (0 = default)")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels eagerly instead of replaying a CUDA graph")

@@ -270,6 +270,34 @@ class P2PPoolGatherer(PoolGatherer):
         self.last = (full, counts)
 
 
+class HostDrain(PoolGatherer):
+    """The same pipeline with the HOST as destination (single rank, no collective): rollout k's packed
+    records go to pinned host memory with one ``cudaMemcpyAsync`` on a side stream while rollout k+1
+    runs.  ``wait()`` returns ``(host_records[:n], [n])``.  This is what ``ModelBuffer.get`` hands to the
+    policy update when the consumer lives on the host (modelbuffer.py:348-405)."""
+
+    def __init__(self, rollout, capacity=None):
+        super().__init__(rollout, 1, None, capacity)
+        self._host = [None, None]
+
+    def _collect(self, b):
+        b["packed"].synchronize()
+        n = int(b["count_host"][0])
+        if n > b["rec"].shape[0]:
+            raise RuntimeError(f"HostDrain: {n} transitions exceed the staging capacity {b['rec'].shape[0]}")
+        s = 0 if b is self._buf[0] else 1
+        h = self._host[s]
+        if h is None or h.shape[0] < n:
+            h = self._host[s] = torch.empty(max(n, 1) + max(n, 1) // 8, self.W, dtype=torch.float32, pin_memory=True)
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(b["packed"])
+            h[:n].copy_(b["rec"][:n], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._side)
+            b["sent"] = ev
+        self.last = (h[:n], [n])
+
+
 def unpack_gathered(rec: torch.Tensor, obs_dim: int, act_dim: int, n_members: int = 1):
     """Split the gathered record matrix back into named arrays (+ int64 ``coords`` [n, 2])."""
     E = max(int(n_members), 1)
