@@ -97,6 +97,19 @@ def stub_policy_matrix(w, seed=4):
     return (torch.randn(w["obs"], w["act"], generator=g) / np.sqrt(w["obs"])).numpy()
 
 
+def committed_traffic(w, rows_per_launch):
+    """dram bytes per forward launch from the committed ncu --set full capture of the same kernel and
+    ensemble shape (profiles/*_fwd_1M_traffic.json: one 1M-row launch), scaled by rows per launch."""
+    import glob
+    if tuple(w["hidden"]) != (200, 200, 200, 200) or w["env"] != "antsafe" or w["mode"] == "iv_gae":
+        return None, None
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_fwd_1M_traffic.json")))
+    if not files:
+        return None, None
+    d = json.load(open(files[-1]))
+    return d["bytes_per_row"] * rows_per_launch, d["source"]
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -371,6 +384,7 @@ def run_gpu(args, w, wname):
                          f"{r['transitions']} transitions in {r['seconds']:.2f} s; TF 1.14 unavailable -> fp32 op-for-op "
                          f"port (torch BLAS GEMMs + NumPy post-processing, 64k-row chunks)"}
 
+    traffic, traffic_src = committed_traffic(w, rows_forwarded / max(launches_fwd, 1))
     wide = max(w["hidden"]) > 254
     fwd_kernel = "wide_layer_kernel" if wide else "ensemble_fwd_kernel"
     # stub policy, input staging, ensemble forward (fused: 1 launch; wide: one per FC layer and 131072-row slab),
@@ -393,7 +407,7 @@ def run_gpu(args, w, wname):
                 "d2h_bytes_per_step": int(rec * per_rollout), "steps": e2e_steps},
         "gpu_launches": int(kernels_per_sampler_step * (w["T"] - 1) * args.steps),
         "roofline": {"bound": "tensor", "kernel": fwd_kernel, "achieved": achieved_tf, "peak": peak,
-                     "unit": "TFLOP/s", "frac": achieved_tf / peak, "traffic": None,
+                     "unit": "TFLOP/s", "frac": achieved_tf / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "peak_source": f"{peaks['source']} bf16 sustained (burst {peaks['bf16_burst']})",
                      "flops_per_row": F, "launches_per_rollout": launches_fwd,
                      "kernel_ms_per_rollout": fwd_ms_per_rollout,

@@ -72,7 +72,12 @@ KEYS = [
 ]
 
 
-def full_capture(stem, title):
+def to_bytes(val, unit):
+    mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    return float(val.replace(",", "")) * mult.get(unit, 1)
+
+
+def full_capture(stem, title, traffic_rows=None):
     rep = os.path.join(G, f"{tag}_{stem}.ncu-rep")
     if not os.path.exists(rep):
         return
@@ -84,6 +89,12 @@ def full_capture(stem, title):
         f.write(f"# {title}\n# ncu --set full --clock-control none --import-source on (one launch); values per launch\n")
         for vals in rows[2:]:
             d = dict(zip(hdr, zip(units, vals)))
+            if traffic_rows and "dram__bytes_read.sum" in d:
+                rd, wr = to_bytes(d["dram__bytes_read.sum"][1], d["dram__bytes_read.sum"][0]), to_bytes(d["dram__bytes_write.sum"][1], d["dram__bytes_write.sum"][0])
+                json.dump({"kernel": short(d.get("Kernel Name", ("", "?"))[1]), "rows": traffic_rows, "dram_bytes_read": rd,
+                           "dram_bytes_write": wr, "bytes_per_row": (rd + wr) / traffic_rows,
+                           "source": f"profiles/{tag}_{stem}_ncu_summary.txt (ncu --set full, one launch)"},
+                          open(os.path.join(P, f"{tag}_{stem}_traffic.json"), "w"))
             f.write(f"kernel: {short(d.get('Kernel Name', ('', '?'))[1])}  grid {d.get('Grid Size', ('', '?'))[1]} block {d.get('Block Size', ('', '?'))[1]}\n")
             for k in KEYS:
                 if k in d:
@@ -98,7 +109,8 @@ def full_capture(stem, title):
 
 
 def bench_lines():
-    for stem in ("bench", "bench_reference", "bench_halfcheetah", "bench_step1M", "bench_wide512"):
+    for stem in ("bench", "bench_reference", "bench_halfcheetah", "bench_step1M", "bench_wide512", "bench_step1M_4x512",
+                 "bench_step256k_4x1024", "bench_iv_gae", "bench_n2", "bench_n2_nccl"):
         src = os.path.join(G, f"{tag}_{stem}.json")
         if os.path.exists(src) and os.path.getsize(src):
             line = open(src).read().strip().splitlines()[-1]
@@ -107,15 +119,17 @@ def bench_lines():
             except ValueError:
                 continue
             open(os.path.join(P, f"{tag}_{stem}.json"), "w").write(line + "\n")
-    for stem in ("fwd_bench.log", "pytest_gpu.log", "sweep.log", "trace_report.txt"):
+    for stem in ("fwd_bench.log", "pytest_gpu.log", "sweep.log", "trace_report.txt", "gather_check.log", "pack_bench.log"):
         src = os.path.join(G, f"{tag}_{stem}")
         if os.path.exists(src):
             open(os.path.join(P, f"{tag}_{stem}"), "w").write(open(src).read())
 
 
 launch_list()
-full_capture("fwd_1M", "ensemble_fwd_kernel, antsafe 4x200, 1,000,000 rows (tools/fwd_bench.py 1000000)")
+full_capture("fwd_1M", "ensemble_fwd_kernel, antsafe 4x200, 1,000,000 rows (tools/fwd_bench.py 1000000)", traffic_rows=1_000_000)
 full_capture("post_1M", "step_post_kernel, antsafe, 1,000,000 rows (tools/fwd_bench.py 1000000)")
-full_capture("wide_512", "wide_layer_kernel, antsafe 2x512, 262,144 rows")
+full_capture("wide_512", "wide_layer_kernel, antsafe 4x512, 262,144 rows (one layer launch)")
+full_capture("post3d", "step_post3d_kernel, humanoidsafe iv_gae, 125,000 rows x 7 members")
+full_capture("pack", "k_pack_write, default workload pool (440k records x 72 columns)")
 bench_lines()
 print(sorted(os.listdir(P)))
