@@ -306,3 +306,94 @@ def test_pack_records_kernel_matches_mask_selection(mode):
     sharding.pack_records_cuda(ro.pool, ro.row_offset, 29, 8, E, small, count, scratch)
     torch.cuda.synchronize()
     assert int(count) == n_ref
+
+
+class _ReplayEnv:
+    """Stands in for FakeEnv inside ModelRollout: step_device hands back the step outputs the REFERENCE's
+    sampler received (tests/golden/sampler_*.npz), so cmbpo_rollout_advance is checked against the pools the
+    reference's real ModelSampler + ModelBuffer produced from exactly those arrays."""
+    def __init__(self, steps, B, E, iv):
+        import torch
+        self.steps, self.B, self.iv = steps, B, iv
+        self.device = torch.device("cuda:0")
+        self.obs_dim, self.act_dim, self.num_networks = 29, 8, E
+        self.i = 0
+        self.seen_cur = []
+
+    def _cap(self, a, dtype):
+        import torch
+        a = np.asarray(a)
+        if a.shape[-1] == 1 and a.ndim == (3 if self.iv else 2):
+            pass
+        lead = (self.num_networks,) if self.iv else ()
+        tail = a.shape[len(lead) + 1:]
+        out = torch.zeros(lead + (self.B,) + tuple(tail), dtype=dtype, device=self.device)
+        n = a.shape[len(lead)]
+        if self.iv:
+            out[:, :n] = torch.from_numpy(np.ascontiguousarray(a)).to(self.device, dtype)
+        else:
+            out[:n] = torch.from_numpy(np.ascontiguousarray(a)).to(self.device, dtype)
+        return out
+
+    def policy(self, cur, n_dev):
+        import torch
+        n = int(n_dev.item())
+        if self.i < len(self.steps):
+            r = self.steps[self.i]
+            got = (cur[:, :n] if self.iv else cur[:n]).cpu().numpy()
+            assert np.array_equal(got, r["cur"]), f"compacted observations differ from the reference's at step {self.i}"
+            return self._cap(r["act"], torch.float32)
+        assert n == 0
+        return self._cap(np.zeros(((self.num_networks,) if self.iv else ()) + (0, 8), np.float32), torch.float32)
+
+    def step_device(self, cur, act, n_rows_dev=None, row_ids=None, want_ep_var=False, out=None, perm=None):
+        import torch
+        if self.i >= len(self.steps):
+            z = self.steps[0]
+            r = {k: np.zeros_like(v[:, :0] if self.iv and v.ndim > 1 and k not in ("dkl", "ep_var") else v[:0]) for k, v in z.items()}
+        else:
+            r = self.steps[self.i]
+        self.i += 1
+        f32 = torch.float32
+        lead = (self.num_networks,) if self.iv else ()
+        d = {"next_obs": self._cap(r["next_obs"], f32), "rew": self._cap(r["rew"], f32),
+             "term": self._cap(r["term"].astype(np.uint8), torch.uint8), "cost": self._cap(r["cost"], f32)}
+        iv, self.iv = self.iv, False          # per-path arrays have no member axis
+        d["dkl_path"] = self._cap(r["dkl"].astype(np.float32), f32)
+        d["ep_var_mean"] = self._cap(np.mean(r["ep_var"], axis=-1).astype(np.float32), f32)   # model_sampler.py:428
+        self.iv = iv
+        out.update(d)
+        return out
+
+
+@pytest.mark.parametrize("name", ["schedule", "uncertainty", "iv_gae"])
+def test_rollout_bookkeeping_matches_reference_modelsampler_golden(name):
+    """cmbpo_rollout_advance (through ModelRollout) teacher-forced with the step outputs the reference's REAL
+    ModelSampler received, against the pools its REAL ModelBuffer ended with: bit-exact (integer / index / copy
+    work), all three rollout modes, max_samples early termination included."""
+    import os
+    import constrainedmbpo_b200 as cm
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", f"sampler_{name}.npz"), allow_pickle=False)
+    steps = [{k: g[f"step{i}_{k}"] for k in ("cur", "act", "next_obs", "rew", "term", "cost", "dkl", "ep_var")}
+             for i in range(int(g["n_steps"]))]
+    B, T, E = g["start_obs"].shape[0], int(g["T"]), int(g["E"])
+    env = _ReplayEnv(steps, B, E, name == "iv_gae")
+    ro = cm.ModelRollout(env, T, rollout_mode=name, dkl_lim=float(g["dkl_lim"]) or None,
+                         max_samples=int(g["max_samples"]) or None)
+    ro.reset(g["start_obs"])
+    for _ in range(T - 1):
+        ro.step(lambda cur, n_dev: env.policy(cur, n_dev))
+    assert env.i >= len(steps)
+    got = ro.get(numpy=True)
+    for ours, ref in (("obs", "obs_buf"), ("act", "act_buf"), ("next_obs", "nextobs_buf"), ("rew", "rew_buf"),
+                      ("cost", "cost_buf"), ("term", "term_buf"), ("dyn_error", "dyn_error_buf")):
+        assert got[ours].shape == g[ref].shape and np.array_equal(got[ours], g[ref]), ours
+    if name == "iv_gae":   # the reference trims populated_mask by the iv horizon afterwards (SURVEY §8f N2)
+        assert np.array_equal(got["populated"], np.arange(T)[None, :] < g["path_length"][:, None])
+    else:
+        assert np.array_equal(got["populated"], g["populated_mask"])
+    n_alive, ptr, total, finished = ro.counters()
+    assert (n_alive, total, finished) == (0, int(g["total_samples"]), 1)
+    assert np.array_equal(got["dkl_accum"], g["dyn_dkl_path"])
+    hist = ro.alive_hist.cpu().numpy()
+    assert list(hist[: len(g["alive_hist"])]) == list(g["alive_hist"])
