@@ -320,49 +320,50 @@ class _ReplayEnv:
         self.i = 0
         self.seen_cur = []
 
-    def _cap(self, a, dtype):
+    def _cap(self, a, dtype, members=None):
+        """Recorded [n, ...] (or [E, n, ...]) array -> capacity-shaped CUDA tensor, live rows first."""
         import torch
-        a = np.asarray(a)
-        if a.shape[-1] == 1 and a.ndim == (3 if self.iv else 2):
-            pass
-        lead = (self.num_networks,) if self.iv else ()
-        tail = a.shape[len(lead) + 1:]
-        out = torch.zeros(lead + (self.B,) + tuple(tail), dtype=dtype, device=self.device)
+        members = self.iv if members is None else members
+        a = np.ascontiguousarray(a)
+        lead = (self.num_networks,) if members else ()
         n = a.shape[len(lead)]
-        if self.iv:
-            out[:, :n] = torch.from_numpy(np.ascontiguousarray(a)).to(self.device, dtype)
+        out = torch.zeros(lead + (self.B,) + tuple(a.shape[len(lead) + 1:]), dtype=dtype, device=self.device)
+        src = torch.from_numpy(a).to(self.device, dtype)
+        if members:
+            out[:, :n] = src
         else:
-            out[:n] = torch.from_numpy(np.ascontiguousarray(a)).to(self.device, dtype)
+            out[:n] = src
         return out
+
+    def _record(self):
+        if self.i < len(self.steps):
+            return self.steps[self.i]
+        lead = (self.num_networks,) if self.iv else ()   # every path has ended: zero live rows
+        z = lambda *tail, dt=np.float32: np.zeros(lead + (0,) + tail, dt)
+        return dict(cur=z(29), act=z(8), next_obs=z(29), rew=z(1), term=z(1, dt=bool), cost=z(1),
+                    dkl=np.zeros(0, np.float32), ep_var=np.zeros((0, 30), np.float32))
 
     def policy(self, cur, n_dev):
         import torch
         n = int(n_dev.item())
-        if self.i < len(self.steps):
-            r = self.steps[self.i]
-            got = (cur[:, :n] if self.iv else cur[:n]).cpu().numpy()
-            assert np.array_equal(got, r["cur"]), f"compacted observations differ from the reference's at step {self.i}"
-            return self._cap(r["act"], torch.float32)
-        assert n == 0
-        return self._cap(np.zeros(((self.num_networks,) if self.iv else ()) + (0, 8), np.float32), torch.float32)
+        r = self._record()
+        got = (cur[:, :n] if self.iv else cur[:n]).cpu().numpy()
+        assert got.shape == r["cur"].shape and np.array_equal(got, r["cur"]), \
+            f"compacted observations differ from the reference's at step {self.i}"
+        return self._cap(r["act"], torch.float32)
 
     def step_device(self, cur, act, n_rows_dev=None, row_ids=None, want_ep_var=False, out=None, perm=None):
         import torch
-        if self.i >= len(self.steps):
-            z = self.steps[0]
-            r = {k: np.zeros_like(v[:, :0] if self.iv and v.ndim > 1 and k not in ("dkl", "ep_var") else v[:0]) for k, v in z.items()}
-        else:
-            r = self.steps[self.i]
+        r = self._record()
         self.i += 1
         f32 = torch.float32
-        lead = (self.num_networks,) if self.iv else ()
-        d = {"next_obs": self._cap(r["next_obs"], f32), "rew": self._cap(r["rew"], f32),
-             "term": self._cap(r["term"].astype(np.uint8), torch.uint8), "cost": self._cap(r["cost"], f32)}
-        iv, self.iv = self.iv, False          # per-path arrays have no member axis
-        d["dkl_path"] = self._cap(r["dkl"].astype(np.float32), f32)
-        d["ep_var_mean"] = self._cap(np.mean(r["ep_var"], axis=-1).astype(np.float32), f32)   # model_sampler.py:428
-        self.iv = iv
-        out.update(d)
+        out.update({
+            "next_obs": self._cap(r["next_obs"], f32), "rew": self._cap(r["rew"], f32),
+            "term": self._cap(r["term"].astype(np.uint8), torch.uint8), "cost": self._cap(r["cost"], f32),
+            "dkl_path": self._cap(r["dkl"].astype(np.float32), f32, members=False),
+            # the sampler stores np.mean(dyn_ep_var, axis=-1) (model_sampler.py:428)
+            "ep_var_mean": self._cap(np.mean(r["ep_var"], axis=-1).astype(np.float32), f32, members=False),
+        })
         return out
 
 
