@@ -242,3 +242,34 @@ def test_step_rejects_1d_like_reference():
     fe = build_cuda_env(p, env, HIDDEN)
     with pytest.raises(NameError):  # quirk Q3: fake_env.py:204-210
         fe.step(np.zeros(17, np.float32), np.zeros(6, np.float32))
+
+
+@pytest.mark.parametrize("tag,env", [("antsafe2d", "antsafe"), ("humanoidsafe3d", "humanoidsafe"), ("hopper2d", "hopper"),
+                                     ("halfcheetahsafe2d", "halfcheetahsafe")])
+def test_step_against_reference_fake_env_golden(tag, env):
+    """The CUDA FakeEnv.step against what the reference's REAL FakeEnv.step returned (tests/golden/fakeenv_step.npz:
+    real fake_env.py + real StaticFns, model outputs from the fp32 restatement of the TF graph) for the same ensemble,
+    inputs and injected draws: means within the bf16 tolerance, decisions equal away from thresholds."""
+    from tests.test_oracle_golden import load_fakeenv_golden
+    g = load_fakeenv_golden(tag)
+    hidden = (24, 24)
+    p = make_params(env, hidden, parity_scalers=True, bias=True, dtype=np.float32)
+    cost = bool(g["cares_about_cost"])
+    fe = build_cuda_env(p, env, hidden, cares_about_cost=cost)
+    three_d = g["obs"].ndim == 3
+    no, rw, tm, info = fe.step(g["obs"], g["act"], elite_idx=None if three_d else g["idx"], perm=g["perm"] if three_d else None)
+    s = out_scale(p)
+    assert no.shape == g["next_obs"].shape and rw.shape == g["rew"].shape and tm.shape == g["term"].shape
+    assert_means_close(no, g["next_obs"], s[:-1], what="next_obs vs reference FakeEnv.step")
+    assert_means_close(rw, g["rew"], s[-1:], what="reward vs reference FakeEnv.step")
+    tol = RTOL_BF16 * np.abs(g["next_obs"].astype(np.float64)) + ATOL_SCALE_BF16 * s[:-1]
+    near = near_threshold_rows(env, g["next_obs"], tol)
+    mism = (tm != g["term"])[..., 0]
+    assert not (mism & ~near).any(), f"{int((mism & ~near).sum())} termination mismatches away from thresholds"
+    if cost:
+        mc = (info["cost"] != g["cost"])[..., 0]
+        assert not (mc & ~near).any()
+    rel = np.abs(info["ensemble_dkl_path"] - g["dkl_path"]) / (np.abs(g["dkl_path"]) + 1e-6)
+    assert np.median(rel) < 2e-2, f"dkl_path median rel err {np.median(rel):.3e}"
+    assert abs(info["ensemble_mean_var"] - g["mean_var"]) < 2e-2 * g["mean_var"]
+    assert abs(info["rew_mean"] - g["rew_mean"]) < 1e-2 * (abs(g["rew_mean"]) + s[-1])
