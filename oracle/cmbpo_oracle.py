@@ -616,3 +616,103 @@ def rollout_iv_gae(p: EnsembleParams, env: str, start_obs, policy, max_path_leng
     pool["dkl_accum"] = dkl_accum
     pool["path_length"] = path_length
     return pool
+
+
+# --------------------------------------------------------------------------------------
+# ModelBuffer.finish_path_multiple: GAE and inverse-variance GAE
+#   softlearning/replay_pools/modelbuffer.py:176-346
+#   softlearning/policies/safe_utils/utils.py:18-188 (discount_cumsum, discount_cumsum_weighted,
+#   disc_cumsum_matrix, triu_indices_t_h)
+# --------------------------------------------------------------------------------------
+GAE_EPS = 1e-8  # EPS of safe_utils/utils.py
+
+
+def _iv_gae_path(x, v_ext, m, gamma_mat, gamma, lam):
+    """One path, one signal (reward or cost).  ``x`` [E, L] per-member signal, ``v_ext`` [E, L+1] per-member
+    values with the bootstrap value appended, ``m`` the member whose trajectory supplies the deltas
+    (modelbuffer.py:210), ``gamma_mat`` the discount of the partial-sum matrix (the reference passes
+    ``self.gamma`` for BOTH signals, modelbuffer.py:225,:286), ``gamma``/``lam`` the signal's own discounts.
+    Returns (adv[L], ret_var[L], roll_lengths[L]) in float64."""
+    E, L = x.shape
+    x = x.astype(np.float64)
+    v_ext = v_ext.astype(np.float64)
+    # deltas of the chosen member, in the buffers' float32 (modelbuffer.py:210: float32 arrays and Python floats)
+    xm, vm = x[m].astype(np.float32), v_ext[m].astype(np.float32)
+    deltas = (xm + np.float32(gamma) * vm[1:] - vm[:-1]).astype(np.float64)
+    var = np.zeros((L, L))
+    for t in range(L):
+        for h in range(L - t):
+            # disc_cumsum_matrix entry (utils.py:128-180) + bootstrapped value (modelbuffer.py:226)
+            s = np.zeros(E)
+            for j in range(h + 1):
+                s += gamma_mat ** j * x[:, t + j]
+            s += v_ext[:, t + h + 1] * gamma ** (h + 1)
+            var[t, h] = np.var(s)                                   # :227 epistemic variance over members
+    w = np.zeros((L, L))
+    for t in range(L):
+        for h in range(L - t):
+            w[t, h] = 1.0 / (var[t, h] + GAE_EPS) * (lam * gamma ** 2) ** h     # :230-233
+        w[t, L - 1 - t] *= 1.0 / (1.0 - lam * gamma ** 2 + GAE_EPS)              # :234 last h of every row
+    adv, ret_var, roll = np.zeros(L), np.zeros(L), np.zeros(L)
+    for t in range(L):
+        dw = np.cumsum(w[t, ::-1])[::-1]                                        # :237 sum from h to the end
+        norm = 1.0 / dw[0]                                                       # :238
+        for h in range(L - t):
+            adv[t] += gamma ** h * deltas[t + h] * dw[h] * norm                  # :249 discount_cumsum_weighted
+            ret_var[t] += w[t, h] * norm * var[t, h]                             # :245,:251-252
+            roll[t] += (t + h) * w[t, h]                                         # :254-255
+        roll[t] = roll[t] * norm - t
+    return adv, ret_var, roll
+
+
+def finish_paths(rew, val, cost, cval, finish_ptr, last_val, last_cval, mode, gamma, lam, cost_gamma, cost_lam,
+                 model_ind=0, cares_about_cost=True, max_uncertainty_r=5.5, max_uncertainty_c=5.5, populated=None):
+    """``ModelBuffer.finish_path_multiple`` for every path at once.  Path ``b`` was finished when the pool column
+    was ``finish_ptr[b]`` (its slice is ``[0:finish_ptr[b]]``, modelbuffer.py:199) with bootstrap values
+    ``last_val[..., b]`` / ``last_cval[..., b]``.  Arrays are ``[B, T]`` ('schedule' / 'uncertainty') or
+    ``[E, B, T]`` ('iv_gae'); outputs are float32 ``[B, T]`` like the reference's buffers.  In 'iv_gae' mode the
+    populated mask is trimmed at the first column whose normalised return variance exceeds the limits
+    (:329-343) -- including the reference's quirk that a path with NO such column gets horizon
+    ``argmax(all False) == 0`` and is dropped entirely."""
+    iv = mode == "iv_gae"
+    B, T = rew.shape[-2:]
+    out = {k: np.zeros((B, T), np.float32) for k in ("adv", "ret", "cadv", "cret", "ret_var", "cret_var",
+                                                      "roll_lengths", "croll_lengths")}
+    pop = None if populated is None else np.array(populated, bool)
+    for b in range(B):
+        L = int(finish_ptr[b])
+        if L <= 0:   # never stored anything (modelbuffer.py:198 `if self.ptr>0`)
+            continue
+        if not iv:
+            for sig, v, lv, g, l, ka, kr in ((rew, val, last_val, gamma, lam, "adv", "ret"),
+                                            (cost, cval, last_cval, cost_gamma, cost_lam, "cadv", "cret")):
+                x_ext = np.append(sig[b, :L], lv[b]).astype(np.float32)     # :201 (rews also gets last_val appended)
+                v_ext = np.append(v[b, :L], lv[b]).astype(np.float32)
+                deltas = x_ext[:-1] + np.float32(g) * v_ext[1:] - v_ext[:-1]   # float32, :264
+                a = np.zeros(L)
+                run = 0.0
+                for t in range(L - 1, -1, -1):                              # discount_cumsum (utils.py:44-47)
+                    run = float(deltas[t]) + g * l * run
+                    a[t] = run
+                out[ka][b, :L] = a
+                out[kr][b, :L] = out[ka][b, :L] + v[b, :L]                   # :268 float32 + float32
+            continue
+        v_ext = np.concatenate((val[:, b, :L], last_val[:, b, None]), axis=-1)
+        a, rv, rl = _iv_gae_path(rew[:, b, :L], v_ext, model_ind, gamma, gamma, lam)
+        out["adv"][b, :L], out["ret_var"][b, :L], out["roll_lengths"][b, :L] = a, rv, rl
+        out["ret"][b, :L] = out["adv"][b, :L] + val[model_ind, b, :L]
+        cv_ext = np.concatenate((cval[:, b, :L], last_cval[:, b, None]), axis=-1)
+        a, rv, rl = _iv_gae_path(cost[:, b, :L], cv_ext, model_ind, gamma, cost_gamma, cost_lam)
+        out["cadv"][b, :L], out["cret_var"][b, :L], out["croll_lengths"][b, :L] = a, rv, rl
+        out["cret"][b, :L] = out["cadv"][b, :L] + cval[model_ind, b, :L]
+        if pop is not None:
+            # :329-343, evaluated on the float32 buffers
+            ncv = out["cret_var"][b, :L] / (out["cret_var"][b, 0:1] + GAE_EPS)
+            nrv = out["ret_var"][b, :L] / (out["ret_var"][b, 0:1] + GAE_EPS)
+            mask = nrv > max_uncertainty_r
+            if cares_about_cost:
+                mask = np.logical_or(ncv > max_uncertainty_c, mask)
+            horizon = int(np.argmax(mask))
+            pop[b, :] &= np.arange(T) < horizon
+    out["populated"] = pop
+    return out

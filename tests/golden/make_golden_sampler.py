@@ -146,13 +146,27 @@ def run(mode, B, T, seed, max_samples=None, dkl_lim=None, max_unc=(5.5, 5.5)):
     env, pol = FakeEnv(seed), FakePolicy(seed + 10)
     pool = ModelBuffer(B, env, T, E, rollout_mode=mode, cares_about_cost=True,
                        max_uncertainty_r=max_unc[0], max_uncertainty_c=max_unc[1])
-    pool.initialize({}, gamma=0.99, lam=0.95, cost_gamma=0.99, cost_lam=0.95)
+    pool.initialize({}, gamma=0.99, lam=0.95, cost_gamma=0.97, cost_lam=0.9)   # distinct cost discounts on purpose
     sampler = ModelSampler(T, batch_size=B, cares_about_cost=True, rollout_mode=mode, logger=object())
     sampler.initialize(env, pol, pool)
     if dkl_lim is not None:
         sampler.set_rollout_dkl(dkl_lim)
     obs, _ = make_inputs(ENV, B, seed=seed)
     sampler.reset(obs)
+    # log what the sampler hands to finish_path_multiple (path ids, bootstrap values, pool column at that moment)
+    fin_ptr = np.full(B, -1, np.int64)
+    lead = (E,) if mode == "iv_gae" else ()
+    last_val, last_cval = np.zeros(lead + (B,), np.float32), np.zeros(lead + (B,), np.float32)
+    orig_finish = pool.finish_path_multiple
+
+    def logged_finish(term_mask, last_val_=0, last_cval_=0):
+        if term_mask.any():
+            fin = np.where(pool.alive_paths)[0][term_mask]
+            fin_ptr[fin] = pool.ptr
+            last_val[..., fin] = last_val_
+            last_cval[..., fin] = last_cval_
+        return orig_finish(term_mask, last_val_, last_cval_)
+    pool.finish_path_multiple = logged_finish
     alive_hist = []
     n_calls = 0
     while pool.alive_paths.any():
@@ -165,7 +179,7 @@ def run(mode, B, T, seed, max_samples=None, dkl_lim=None, max_unc=(5.5, 5.5)):
                model_ind=pool.model_ind, alive_hist=np.array(alive_hist), n_steps=len(env.calls),
                total_samples=sampler._total_samples, path_length=sampler._path_length,
                dyn_dkl_path=sampler._dyn_dkl_path, ptr=pool.ptr, max_uncertainty=np.array(max_unc),
-               gamma=0.99, lam=0.95)
+               gamma=0.99, lam=0.95, cost_gamma=0.97, cost_lam=0.9, finish_ptr=fin_ptr, last_val=last_val, last_cval=last_cval)
     for k in ("obs_buf", "act_buf", "nextobs_buf", "rew_buf", "cost_buf", "term_buf", "dyn_error_buf",
               "populated_mask", "terminated_paths_mask", "val_buf", "cval_buf", "val_var_buf", "cval_var_buf",
               "adv_buf", "ret_buf", "cadv_buf", "cret_buf", "ret_var_buf", "cret_var_buf", "roll_lengths_buf",
