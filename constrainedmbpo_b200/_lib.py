@@ -90,6 +90,20 @@ class cmbpo_pack_io(C.Structure):
     ]
 
 
+class cmbpo_gae_io(C.Structure):
+    _fields_ = [
+        ("n_paths", C.c_int64), ("max_path_length", C.c_int32), ("mode", C.c_int32), ("n_members", C.c_int32),
+        ("model_ind", C.c_int32), ("cares_about_cost", C.c_int32),
+        ("gamma", C.c_double), ("lam", C.c_double), ("cost_gamma", C.c_double), ("cost_lam", C.c_double),
+        ("max_uncertainty_r", C.c_float), ("max_uncertainty_c", C.c_float),
+        ("rew_dev", C.c_void_p), ("val_dev", C.c_void_p), ("cost_dev", C.c_void_p), ("cval_dev", C.c_void_p),
+        ("finish_ptr_dev", C.c_void_p), ("last_val_dev", C.c_void_p), ("last_cval_dev", C.c_void_p),
+        ("adv_dev", C.c_void_p), ("ret_dev", C.c_void_p), ("cadv_dev", C.c_void_p), ("cret_dev", C.c_void_p),
+        ("ret_var_dev", C.c_void_p), ("cret_var_dev", C.c_void_p), ("roll_lengths_dev", C.c_void_p),
+        ("croll_lengths_dev", C.c_void_p), ("populated_dev", C.c_void_p),
+    ]
+
+
 # every symbol include/cmbpo_b200.h declares: (restype, argtypes)
 SYMBOLS = {
     "cmbpo_create": (C.c_int, [C.POINTER(cmbpo_cfg), C.c_int, C.POINTER(C.c_void_p)]),
@@ -111,6 +125,7 @@ SYMBOLS = {
     "cmbpo_record_width": (C.c_int32, [C.c_int32, C.c_int32, C.c_int32]),
     "cmbpo_pack_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "cmbpo_pack_records": (C.c_int, [C.POINTER(cmbpo_pack_io), C.c_void_p]),
+    "cmbpo_finish_paths": (C.c_int, [C.POINTER(cmbpo_gae_io), C.c_void_p]),
     "cmbpo_stub_policy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                     C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
 }

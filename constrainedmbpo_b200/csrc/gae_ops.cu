@@ -1,0 +1,162 @@
+// gae_ops.cu -- ModelBuffer.finish_path_multiple on the device: generalised advantage
+// estimation for the 'schedule' / 'uncertainty' pools and the inverse-variance weighted GAE + horizon trim of
+// the 'iv_gae' pools (softlearning/replay_pools/modelbuffer.py:176-346; softlearning/policies/safe_utils/
+// utils.py:18-188).
+//
+// One thread per path; every array is in the rollout's time-major storage ([E][T][n_paths], see
+// include/cmbpo_b200.h), so a warp's loads of one column are one coalesced 128-byte access.  O(L) per path
+// for plain GAE, O(E L^2) for the iv variant (L <= 64): HBM / latency bound, fp64 like the reference's
+// NumPy (float64 lfilter / np.var on float32 buffers), results rounded to the float32 buffers at the same
+// points as the reference.
+#include <cstdint>
+#include <cstdio>
+#include <cuda_runtime.h>
+#include "../../include/cmbpo_b200.h"
+
+namespace cmbpo {
+
+constexpr int kGaeMaxT = 64;
+constexpr double kGaeEps = 1e-8;   // EPS, safe_utils/utils.py:5
+
+// float32 delta of the reference: rews[:-1] + gamma * vals[1:] - vals[:-1] on float32 arrays (modelbuffer.py:210,:264)
+__device__ __forceinline__ float delta_f32(float x, float g, float v_next, float v) {
+  return __fsub_rn(__fadd_rn(x, __fmul_rn(g, v_next)), v);
+}
+
+// plain GAE of one signal: adv[t] = delta[t] + gamma*lam*adv[t+1] (discount_cumsum, utils.py:44-47)
+__device__ void gae_path(const float* x, const float* v, float last, int L, size_t B, size_t b, double gamma, double lam,
+                         float* adv, float* ret) {
+  double run = 0.0;
+  float v_next = last;
+  const float g = (float)gamma;
+  for (int t = L - 1; t >= 0; --t) {
+    const float xt = x[(size_t)t * B + b], vt = v[(size_t)t * B + b];
+    run = (double)delta_f32(xt, g, v_next, vt) + gamma * lam * run;
+    const float a = (float)run;
+    adv[(size_t)t * B + b] = a;
+    ret[(size_t)t * B + b] = __fadd_rn(a, vt);          // R_t = A_t + V_t (modelbuffer.py:268)
+    v_next = vt;
+  }
+}
+
+// inverse-variance weighted GAE of one signal (modelbuffer.py:204-260 / :272-326)
+template <int E>
+__device__ void iv_gae_path(const float* x, const float* v, const float* last, int L, int T, size_t B, size_t b, int m,
+                            double gamma_mat, double gamma, double lam, float* adv, float* ret, float* ret_var, float* roll) {
+  const size_t es = (size_t)T * B;   // member stride
+  double w[kGaeMaxT], var[kGaeMaxT];
+  const double lg = lam * gamma * gamma;
+  const float g32 = (float)gamma;
+  for (int t = 0; t < L; ++t) {
+    double s[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) s[e] = 0.0;
+    double gm = 1.0, gh1 = gamma, lh = 1.0;   // gamma_mat^h, gamma^(h+1), (lam*gamma^2)^h
+    const int H = L - t;
+    for (int h = 0; h < H; ++h) {
+      double r[E], mean = 0.0;
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        s[e] += gm * (double)x[e * es + (size_t)(t + h) * B + b];                       // disc_cumsum_matrix
+        const double vn = (t + h + 1 < L) ? (double)v[e * es + (size_t)(t + h + 1) * B + b] : (double)last[e * B + b];
+        r[e] = s[e] + vn * gh1;                                                        // + V_{t+h+1} * gamma^(h+1)
+        mean += r[e];
+      }
+      mean /= E;
+      double q = 0.0;
+#pragma unroll
+      for (int e = 0; e < E; ++e) { const double d = r[e] - mean; q += d * d; }
+      var[h] = q / E;                                                                  // np.var(axis=0)
+      w[h] = 1.0 / (var[h] + kGaeEps) * lh;
+      gm *= gamma_mat; gh1 *= gamma; lh *= lg;
+    }
+    w[H - 1] *= 1.0 / (1.0 - lg + kGaeEps);                                            // last h of the row
+    double tot = 0.0;
+    for (int h = 0; h < H; ++h) tot += w[h];
+    const double norm = 1.0 / tot;
+    double a = 0.0, rv = 0.0, rl = 0.0, suffix = tot, gh = 1.0;
+    for (int h = 0; h < H; ++h) {
+      const int k = t + h;
+      const float xk = x[m * es + (size_t)k * B + b], vk = v[m * es + (size_t)k * B + b];
+      const float vn = (k + 1 < L) ? v[m * es + (size_t)(k + 1) * B + b] : last[m * B + b];
+      a += gh * (double)delta_f32(xk, g32, vn, vk) * (suffix * norm);                  // d_weight_mat[t][h]
+      rv += w[h] * norm * var[h];
+      rl += (double)k * w[h];
+      suffix -= w[h];
+      gh *= gamma;
+    }
+    const float af = (float)a;
+    adv[(size_t)t * B + b] = af;
+    ret[(size_t)t * B + b] = __fadd_rn(af, v[m * es + (size_t)t * B + b]);
+    ret_var[(size_t)t * B + b] = (float)rv;
+    roll[(size_t)t * B + b] = (float)(rl * norm - (double)t);
+  }
+}
+
+template <int E>
+__global__ void __launch_bounds__(128) k_finish_paths(cmbpo_gae_io io) {
+  const size_t B = (size_t)io.n_paths;
+  const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const int T = io.max_path_length;
+  int L = io.finish_ptr_dev[b];
+  if (L <= 0) return;                 // modelbuffer.py:198: nothing stored, nothing computed
+  if (L > T) L = T;
+  if (io.mode != 2) {
+    gae_path(io.rew_dev, io.val_dev, io.last_val_dev[b], L, B, b, io.gamma, io.lam, io.adv_dev, io.ret_dev);
+    gae_path(io.cost_dev, io.cval_dev, io.last_cval_dev[b], L, B, b, io.cost_gamma, io.cost_lam, io.cadv_dev, io.cret_dev);
+    return;
+  }
+  const int m = io.model_ind;
+  iv_gae_path<E>(io.rew_dev, io.val_dev, io.last_val_dev, L, T, B, b, m, io.gamma, io.gamma, io.lam,
+                 io.adv_dev, io.ret_dev, io.ret_var_dev, io.roll_lengths_dev);
+  // the cost partial sums are discounted with gamma, the bootstrap with cost_gamma (modelbuffer.py:286-287)
+  iv_gae_path<E>(io.cost_dev, io.cval_dev, io.last_cval_dev, L, T, B, b, m, io.gamma, io.cost_gamma, io.cost_lam,
+                 io.cadv_dev, io.cret_dev, io.cret_var_dev, io.croll_lengths_dev);
+  if (io.populated_dev) {
+    // horizon = first column whose normalised return variance exceeds a limit, evaluated on the float32 buffers;
+    // argmax of an all-False mask is 0, which drops the whole path (modelbuffer.py:329-343)
+    const float r0 = __fadd_rn(io.ret_var_dev[b], 1e-8f), c0 = __fadd_rn(io.cret_var_dev[b], 1e-8f);
+    int horizon = 0;
+    for (int t = 0; t < L; ++t) {
+      const bool ur = __fdiv_rn(io.ret_var_dev[(size_t)t * B + b], r0) > io.max_uncertainty_r;
+      const bool uc = io.cares_about_cost && (__fdiv_rn(io.cret_var_dev[(size_t)t * B + b], c0) > io.max_uncertainty_c);
+      if (ur || uc) { horizon = t; break; }
+    }
+    for (int t = horizon; t < T; ++t) io.populated_dev[(size_t)t * B + b] = 0;
+  }
+}
+
+}  // namespace cmbpo
+
+using namespace cmbpo;
+static thread_local char g_gae_err[160];
+
+extern "C" int cmbpo_finish_paths(const cmbpo_gae_io* io_, void* stream_) {
+  if (!io_) return CMBPO_ERR_ARG;
+  const cmbpo_gae_io io = *io_;
+  if (io.n_paths < 0 || io.max_path_length <= 0) return CMBPO_ERR_ARG;
+  if (!io.rew_dev || !io.val_dev || !io.cost_dev || !io.cval_dev || !io.finish_ptr_dev || !io.last_val_dev ||
+      !io.last_cval_dev || !io.adv_dev || !io.ret_dev || !io.cadv_dev || !io.cret_dev) return CMBPO_ERR_ARG;
+  if (io.mode == 2) {
+    if (!io.ret_var_dev || !io.cret_var_dev || !io.roll_lengths_dev || !io.croll_lengths_dev) return CMBPO_ERR_ARG;
+    if (io.max_path_length > kGaeMaxT || io.n_members < 1 || io.n_members > 8 || io.model_ind < 0 ||
+        io.model_ind >= io.n_members) return CMBPO_ERR_UNSUPPORTED;
+  }
+  if (io.n_paths == 0) return CMBPO_OK;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  const int nb = (int)((io.n_paths + 127) / 128);
+  switch (io.mode == 2 ? io.n_members : 1) {
+    case 1: k_finish_paths<1><<<nb, 128, 0, stream>>>(io); break;
+    case 2: k_finish_paths<2><<<nb, 128, 0, stream>>>(io); break;
+    case 3: k_finish_paths<3><<<nb, 128, 0, stream>>>(io); break;
+    case 4: k_finish_paths<4><<<nb, 128, 0, stream>>>(io); break;
+    case 5: k_finish_paths<5><<<nb, 128, 0, stream>>>(io); break;
+    case 6: k_finish_paths<6><<<nb, 128, 0, stream>>>(io); break;
+    case 7: k_finish_paths<7><<<nb, 128, 0, stream>>>(io); break;
+    default: k_finish_paths<8><<<nb, 128, 0, stream>>>(io); break;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { snprintf(g_gae_err, sizeof(g_gae_err), "finish_paths: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }
+  return CMBPO_OK;
+}

@@ -1,0 +1,62 @@
+"""``ModelBuffer.finish_path_multiple`` on the device (softlearning/replay_pools/modelbuffer.py:176-346): GAE for
+the 'schedule' / 'uncertainty' pools, inverse-variance weighted GAE + horizon trim for the 'iv_gae' pools.
+A thin ctypes client of ``cmbpo_finish_paths``; PyTorch only owns the buffers."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+MODES = {"schedule": 0, "uncertainty": 1, "iv_gae": 2}
+
+
+def _time_major(x, lead):
+    """Logical [(E,) B, T] tensor -> storage [(E,) T, B] (no copy when it already is a ModelRollout pool view)."""
+    s = x.transpose(lead, lead + 1)
+    return s if s.is_contiguous() else s.contiguous()
+
+
+def finish_paths(rew, val, cost, cval, finish_ptr, last_val, last_cval, rollout_mode, gamma=0.99, lam=0.95,
+                 cost_gamma=0.99, cost_lam=0.95, model_ind=0, cares_about_cost=True, max_uncertainty_r=5.5,
+                 max_uncertainty_c=5.5, populated=None):
+    """All arguments are CUDA tensors shaped like the reference's buffers: ``rew/val/cost/cval`` ``[B, T]`` or, for
+    'iv_gae', ``[E, B, T]``; ``finish_ptr`` int ``[B]`` (pool column when the path was finished); ``last_val`` /
+    ``last_cval`` ``[B]`` or ``[E, B]`` (model_sampler.py:497-548); ``populated`` uint8/bool ``[B, T]`` (trimmed copy
+    returned for 'iv_gae').  Returns a dict of float32 ``[B, T]`` tensors: adv, ret, cadv, cret (+ ret_var, cret_var,
+    roll_lengths, croll_lengths, populated for 'iv_gae')."""
+    lib = _lib.load()
+    mode = MODES[rollout_mode]
+    iv = mode == 2
+    lead = 1 if iv else 0
+    dev = rew.device
+    B, T = rew.shape[-2:]
+    f32 = lambda t: t.to(device=dev, dtype=torch.float32)
+    srcs = [_time_major(f32(t), lead) for t in (rew, val, cost, cval)]
+    fp = finish_ptr.to(device=dev, dtype=torch.int32).contiguous()
+    lv, lc = f32(last_val).contiguous(), f32(last_cval).contiguous()
+    names = ["adv", "ret", "cadv", "cret"] + (["ret_var", "cret_var", "roll_lengths", "croll_lengths"] if iv else [])
+    outs = {k: torch.zeros(T, B, dtype=torch.float32, device=dev) for k in names}
+    pop = None
+    if iv and populated is not None:
+        pop = _time_major(populated.to(device=dev, dtype=torch.uint8), 0).clone()
+    io = _lib.cmbpo_gae_io()
+    io.n_paths, io.max_path_length, io.mode = B, T, mode
+    io.n_members = rew.shape[0] if iv else 1
+    io.model_ind, io.cares_about_cost = int(model_ind), int(bool(cares_about_cost))
+    io.gamma, io.lam, io.cost_gamma, io.cost_lam = gamma, lam, cost_gamma, cost_lam
+    io.max_uncertainty_r, io.max_uncertainty_c = max_uncertainty_r, max_uncertainty_c
+    io.rew_dev, io.val_dev, io.cost_dev, io.cval_dev = (t.data_ptr() for t in srcs)
+    io.finish_ptr_dev, io.last_val_dev, io.last_cval_dev = fp.data_ptr(), lv.data_ptr(), lc.data_ptr()
+    io.adv_dev, io.ret_dev, io.cadv_dev, io.cret_dev = (outs[k].data_ptr() for k in names[:4])
+    if iv:
+        io.ret_var_dev, io.cret_var_dev = outs["ret_var"].data_ptr(), outs["cret_var"].data_ptr()
+        io.roll_lengths_dev, io.croll_lengths_dev = outs["roll_lengths"].data_ptr(), outs["croll_lengths"].data_ptr()
+        io.populated_dev = pop.data_ptr() if pop is not None else None
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(lib.cmbpo_finish_paths(C.byref(io), stream))
+    res = {k: v.t() for k, v in outs.items()}     # logical [B, T] views of the time-major storage
+    if pop is not None:
+        res["populated"] = pop.t()
+    return res

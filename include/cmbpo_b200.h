@@ -208,6 +208,33 @@ int32_t cmbpo_record_width(int32_t obs_dim, int32_t act_dim, int32_t n_members);
 size_t cmbpo_pack_scratch_bytes(int64_t n_paths);
 int cmbpo_pack_records(const cmbpo_pack_io* io, void* stream);
 
+/* ModelBuffer.finish_path_multiple for every path of a pool at once (softlearning/replay_pools/modelbuffer.py:
+ * 176-346; softlearning/policies/safe_utils/utils.py:18-188).  Path b was finished when the pool column was
+ * finish_ptr[b] (its slice is [0, finish_ptr[b]), modelbuffer.py:199) with bootstrap values last_val / last_cval
+ * (model_sampler.py:497-548).  mode 0/1: GAE, adv = discount_cumsum(rew + gamma*V' - V, gamma*lam), ret = adv + V,
+ * same for cost with cost_gamma / cost_lam.  mode 2 ('iv_gae'): inverse-variance weighted advantages of member
+ * model_ind's trajectory, weights from the epistemic variance over members of the h-step bootstrapped returns,
+ * plus ret_var / roll_lengths and the horizon trim of populated (first column whose normalised return variance
+ * exceeds max_uncertainty_r / _c; a path with no such column is dropped entirely, as upstream, argmax quirk).
+ * All arrays use the rollout's time-major storage: element (member e, path b, column t) at (e*T + t)*n_paths + b. */
+typedef struct cmbpo_gae_io {
+  int64_t n_paths;
+  int32_t max_path_length;     /* T (<= 64 in mode 2) */
+  int32_t mode;                /* 0 / 1: GAE; 2: 'iv_gae' */
+  int32_t n_members;           /* mode 2: E */
+  int32_t model_ind;           /* mode 2: ModelBuffer.model_ind (modelbuffer.py:26) */
+  int32_t cares_about_cost;
+  double gamma, lam, cost_gamma, cost_lam;            /* ModelBuffer.initialize (modelbuffer.py:33-43) */
+  float max_uncertainty_r, max_uncertainty_c;         /* modelbuffer.py:14-15 */
+  const float* rew_dev; const float* val_dev; const float* cost_dev; const float* cval_dev;   /* [E][T][B] */
+  const int32_t* finish_ptr_dev;                      /* [B] */
+  const float* last_val_dev; const float* last_cval_dev;                                      /* [E][B] */
+  float* adv_dev; float* ret_dev; float* cadv_dev; float* cret_dev;                           /* [T][B] */
+  float* ret_var_dev; float* cret_var_dev; float* roll_lengths_dev; float* croll_lengths_dev; /* [T][B], mode 2 */
+  uint8_t* populated_dev;                             /* [T][B], trimmed in place in mode 2; may be NULL */
+} cmbpo_gae_io;
+int cmbpo_finish_paths(const cmbpo_gae_io* io, void* stream);
+
 /* Synthetic benchmark policy a = tanh(obs @ P), P [obs][act] (not part of the reference; stands in
  * for policy.get_action_outs, model_sampler.py:275, in throughput runs).  n_slots > 1: obs / act are
  * [n_slots][n_rows][.] ('iv_gae' states), the live count applies to every slot. */
