@@ -388,9 +388,9 @@ def run_gpu(args, w, wname):
     wide = max(w["hidden"]) > 254
     fwd_kernel = "wide_layer_kernel" if wide else "ensemble_fwd_kernel"
     # stub policy, input staging, ensemble forward (fused: 1 launch; wide: one per FC layer and 131072-row slab),
-    # step post, 6 bookkeeping kernels
+    # step post, 3 bookkeeping kernels (decide+scan, store+scan, compact); N>1 adds 3 pack kernels per rollout
     fwd_launches = (len(w["hidden"]) + 1) * ((rows + 131071) // 131072) if wide else 1
-    kernels_per_sampler_step = 9 + fwd_launches
+    kernels_per_sampler_step = 6 + fwd_launches
     out = {
         "metric": "rollout transitions/sec (7-member ensemble step)",
         "value": value, "unit": "transitions/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -401,11 +401,12 @@ def run_gpu(args, w, wname):
                    "dkl_lim": dkl_lim, "transitions_per_rollout_per_gpu": per_rollout,
                    "rows_forwarded_per_rollout": rows_forwarded, "cuda_graph": use_graph,
                    "l2": "no explicit flush: per-rollout working set (model pool + head scratch, > 0.9 GB at the named size) exceeds the 126 MB L2",
-                   "parallelism": f"rows sharded x{args.gpus}, weights replicated" + (f", NCCL all-gather of transitions (transport={args.transport}, gather={args.gather}, max_ctas={args.nccl_max_ctas or 'default'})" if world > 1 else "")},
+                   "parallelism": f"rows sharded x{args.gpus}, weights replicated" + (f", all-gather of transitions into the replicated pool (transport={args.transport}: "
+                                    f"{'copy-engine pulls over symmetric-memory peer mappings' if args.transport == 'p2p' else 'NCCL'}, gather={args.gather})" if world > 1 else "")},
         "clocks": clk,
         "e2e": {"value": e2e_val, "unit": "transitions/s", "h2d_bytes_per_step": int(start_host.numel() * 4),
                 "d2h_bytes_per_step": int(rec * per_rollout), "steps": e2e_steps},
-        "gpu_launches": int(kernels_per_sampler_step * (w["T"] - 1) * args.steps),
+        "gpu_launches": int((kernels_per_sampler_step * (w["T"] - 1) + (3 if gather is not None else 0)) * args.steps),
         "roofline": {"bound": "tensor", "kernel": fwd_kernel, "achieved": achieved_tf, "peak": peak,
                      "unit": "TFLOP/s", "frac": achieved_tf / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "peak_source": f"{peaks['source']} bf16 sustained (burst {peaks['bf16_burst']})",

@@ -25,6 +25,7 @@ struct RolloutState {
   int n_stored_last;
   int finished;
   int tmp_total_certain, tmp_n_early, tmp_n_keep, tmp_do_store;
+  unsigned int ticket_a, ticket_b;   // block counters of the two fused scan epilogues (zero between launches)
 };
 static_assert(sizeof(RolloutState) == sizeof(cmbpo_rollout_state), "state layout");
 
@@ -44,9 +45,54 @@ __device__ __forceinline__ int block_exclusive_scan(int flag, int* total) {
   return base + intra;
 }
 
+// exclusive scan of arbitrary non-negative ints over the block's 256 threads
+__device__ __forceinline__ int block_exclusive_scan_int(int v, int* total) {
+  __shared__ int ws[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+  if (lane == 31) ws[warp] = incl;
+  __syncthreads();
+  int base = 0, tot = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) { if (w < warp) base += ws[w]; tot += ws[w]; }
+  __syncthreads();
+  if (total) *total = tot;
+  return base + incl - v;
+}
+
+// "last block done" epilogue shared by k_decide and k_store: every block publishes its count and takes a ticket;
+// the block that takes the last one scans the per-block counts in place (exclusive) and returns true with the
+// total in *total_out (valid on every thread of that block).  Replaces two single-block scan launches per step.
+__device__ __forceinline__ bool last_block_scan(int* blk_cnt, int my_count, int n_blocks, unsigned int* ticket, int* total_out) {
+  __shared__ bool s_last;
+  __shared__ int s_carry;
+  if (threadIdx.x == 0) blk_cnt[blockIdx.x] = my_count;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) { s_last = atomicAdd(ticket, 1u) == gridDim.x - 1; s_carry = 0; }
+  __syncthreads();
+  if (!s_last) return false;
+  __threadfence();
+  for (int base = 0; base < n_blocks; base += kRB) {
+    const int i = base + threadIdx.x;
+    const int v = (i < n_blocks) ? __ldcg(blk_cnt + i) : 0;
+    int tot;
+    const int ex = block_exclusive_scan_int(v, &tot);
+    if (i < n_blocks) blk_cnt[i] = s_carry + ex;
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry += tot;
+    __syncthreads();
+  }
+  *total_out = s_carry;
+  if (threadIdx.x == 0) *ticket = 0;   // ready for the next launch
+  return true;
+}
+
 // A: too_uncertain flags (model_sampler.py:311-315) -> per-block count of still-certain rows
-__global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* certain, int* blk_cnt) {
-  const RolloutState* st = static_cast<const RolloutState*>(io.state_dev);
+__global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* certain, int* blk_cnt, int* snap, int* hist) {
+  RolloutState* st = static_cast<RolloutState*>(io.state_dev);
   const int n = st->n_alive;
   const int i = blockIdx.x * kRB + threadIdx.x;
   int c = 0;
@@ -63,64 +109,23 @@ __global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* ce
   }
   int tot;
   block_exclusive_scan(c, &tot);
-  if (threadIdx.x == 0) blk_cnt[blockIdx.x] = tot;
-}
-
-// B/D: single-block exclusive scan of per-block counts (in place), then a small epilogue
-template <int PHASE>
-__global__ void __launch_bounds__(1024) k_scan(cmbpo_rollout_io io, int* blk_cnt, int n_blocks_max, int* snap, int* hist) {
-  RolloutState* st = static_cast<RolloutState*>(io.state_dev);
-  const int n_blocks = (st->n_alive + kRB - 1) / kRB;
-  if (PHASE == 1 && threadIdx.x == 0) {
-    // the pre-advance alive count is needed by the compaction after k_scan<2> overwrote it
-    *snap = st->n_alive;
-    if (hist) *hist = st->n_alive;
-  }
-  __shared__ int sh[1024];
-  __shared__ int carry;
-  if (threadIdx.x == 0) carry = 0;
-  __syncthreads();
-  for (int base = 0; base < n_blocks; base += 1024) {
-    const int i = base + threadIdx.x;
-    const int v = (i < n_blocks) ? blk_cnt[i] : 0;
-    sh[threadIdx.x] = v;
-    __syncthreads();
-    for (int off = 1; off < 1024; off <<= 1) {  // Hillis-Steele inclusive scan
-      int t = (threadIdx.x >= off) ? sh[threadIdx.x - off] : 0;
-      __syncthreads();
-      sh[threadIdx.x] += t;
-      __syncthreads();
-    }
-    const int incl = sh[threadIdx.x];
-    if (i < n_blocks) blk_cnt[i] = carry + incl - v;
-    __syncthreads();
-    if (threadIdx.x == 1023) carry += incl;
-    __syncthreads();
-  }
+  int total;
+  if (!last_block_scan(blk_cnt, tot, (n + kRB - 1) / kRB, &st->ticket_a, &total)) return;
   if (threadIdx.x == 0) {
-    const int total = carry;
-    if (PHASE == 1) {
-      // model_sampler.py:327-332: n = total_samples + alive - too_uncertain - max_samples
-      long long n_early = 0;
-      if (io.max_samples > 0 && io.mode != 2) {   // :327 `max_samples and not rollout_mode=='iv_gae'`
-        n_early = st->total_samples + (long long)total - io.max_samples;
-        if (n_early < 0) n_early = 0;
-        if (n_early > total) n_early = total;
-      }
-      st->tmp_total_certain = total;
-      st->tmp_n_early = (int)n_early;
-      const int n_remaining = total - (int)n_early;
-      st->tmp_do_store = n_remaining > 0 ? 1 : 0;   // model_sampler.py:339-342: nothing alive -> return
-      st->n_stored_last = n_remaining;
-    } else {
-      st->tmp_n_keep = total;
-      if (st->tmp_do_store) {
-        st->total_samples += st->n_stored_last;      // :386
-        st->ptr += 1;                                // modelbuffer.py:173
-      }
-      st->n_alive = st->tmp_do_store ? total : 0;
-      st->finished = (st->n_alive == 0) ? 1 : 0;
+    *snap = n;                       // the pre-advance alive count, needed by the compaction
+    if (hist) *hist = n;
+    // model_sampler.py:327-332: n = total_samples + alive - too_uncertain - max_samples
+    long long n_early = 0;
+    if (io.max_samples > 0 && io.mode != 2) {   // :327 `max_samples and not rollout_mode=='iv_gae'`
+      n_early = st->total_samples + (long long)total - io.max_samples;
+      if (n_early < 0) n_early = 0;
+      if (n_early > total) n_early = total;
     }
+    st->tmp_total_certain = total;
+    st->tmp_n_early = (int)n_early;
+    const int n_remaining = total - (int)n_early;
+    st->tmp_do_store = n_remaining > 0 ? 1 : 0;   // model_sampler.py:339-342: nothing alive -> return
+    st->n_stored_last = n_remaining;
   }
 }
 
@@ -128,12 +133,13 @@ __global__ void __launch_bounds__(1024) k_scan(cmbpo_rollout_io io, int* blk_cnt
 //    dkl accumulate (:415), length mask (:437, quirk Q8) and terminal mask (:453-456) -> keep flag
 __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_t* certain, const int* blk_off,
                                                 uint8_t* keep, int* blk_keep_cnt) {
-  const RolloutState* st = static_cast<const RolloutState*>(io.state_dev);
+  RolloutState* st = static_cast<RolloutState*>(io.state_dev);
   const int n = st->n_alive;
+  const int n_early = st->tmp_n_early, do_store = st->tmp_do_store;   // read before any block can take the last ticket
   const int i = blockIdx.x * kRB + threadIdx.x;
   const int c = (i < n) ? certain[i] : 0;
   const int rank = blk_off[blockIdx.x] + block_exclusive_scan(c, nullptr);
-  const bool remaining = c && rank >= st->tmp_n_early && st->tmp_do_store;
+  const bool remaining = c && rank >= n_early && do_store;
   const int ptr = st->ptr;
   const int T = io.max_path_length;
   const bool path_end = (ptr + 1) >= (T - 1);  // path_length after increment >= max_path_length-1
@@ -168,7 +174,6 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
   if (i < n) keep[i] = (uint8_t)k;
   int tot;
   block_exclusive_scan(k, &tot);   // includes the __syncthreads that publishes s_pid / s_rem
-  if (threadIdx.x == 0) blk_keep_cnt[blockIdx.x] = tot;
   // row payloads: flat element loop over the block's 256 rows (source rows are contiguous, so loads are
   // fully coalesced; every thread has several independent load->store chains in flight -- a
   // warp-per-row loop here was a 32-deep serial latency chain, 35 us even for a handful of rows)
@@ -198,6 +203,19 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
         if (s_rem[r]) pa[((size_t)ptr * cap + s_pid[r]) * AD + d] = sa[idx];
       }
     }
+  }
+  // fused scan epilogue (was a separate single-block launch): the last block to finish its stores scans the
+  // keep counts and advances the rollout state (every block read the state at its start)
+  int total;
+  if (!last_block_scan(blk_keep_cnt, tot, (n + kRB - 1) / kRB, &st->ticket_b, &total)) return;
+  if (threadIdx.x == 0) {
+    st->tmp_n_keep = total;
+    if (do_store) {
+      st->total_samples += st->n_stored_last;      // model_sampler.py:386
+      st->ptr += 1;                                // modelbuffer.py:173
+    }
+    st->n_alive = do_store ? total : 0;
+    st->finished = (st->n_alive == 0) ? 1 : 0;
   }
 }
 
@@ -289,10 +307,8 @@ extern "C" int cmbpo_rollout_advance(const cmbpo_rollout_io* io_, void* stream_)
   int* blk_a = reinterpret_cast<int*>(static_cast<uint8_t*>(io.scratch_dev) + off);
   int* blk_b = blk_a + nb + 1;
   int* snap = blk_b + nb;   // last word of blk_b's slack
-  k_decide<<<nb, kRB, 0, stream>>>(io, certain, blk_a);
-  k_scan<1><<<1, 1024, 0, stream>>>(io, blk_a, nb, snap, io.alive_hist_dev ? io.alive_hist_dev + io.step_index : nullptr);
+  k_decide<<<nb, kRB, 0, stream>>>(io, certain, blk_a, snap, io.alive_hist_dev ? io.alive_hist_dev + io.step_index : nullptr);
   k_store<<<nb, kRB, 0, stream>>>(io, certain, blk_a, keep, blk_b);
-  k_scan<2><<<1, 1024, 0, stream>>>(io, blk_b, nb, nullptr, nullptr);
   k_compact_dev<<<nb, kRB, 0, stream>>>(io, keep, blk_b, snap);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(g_roll_err, sizeof(g_roll_err), "rollout_advance: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }
@@ -324,22 +340,6 @@ extern "C" int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* a
 // path never stores again, modelbuffer.py:110-114), so the k-th record of a path is its column k.
 // ---------------------------------------------------------------------------------------
 namespace cmbpo {
-
-__device__ __forceinline__ int block_exclusive_scan_int(int v, int* total) {
-  __shared__ int ws[8];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int incl = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-  if (lane == 31) ws[warp] = incl;
-  __syncthreads();
-  int base = 0, tot = 0;
-#pragma unroll
-  for (int w = 0; w < 8; ++w) { if (w < warp) base += ws[w]; tot += ws[w]; }
-  __syncthreads();
-  if (total) *total = tot;
-  return base + incl - v;
-}
 
 __global__ void __launch_bounds__(kRB) k_pack_count(cmbpo_pack_io io, int* path_off, int* blk_cnt) {
   const long long b = (long long)blockIdx.x * kRB + threadIdx.x;

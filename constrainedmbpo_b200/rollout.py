@@ -112,8 +112,8 @@ class ModelRollout:
         self.cur = [torch.empty(*E, B, OD, dtype=torch.float32, device=dev) for _ in range(2)]
         self.pid = [torch.empty(B, dtype=torch.int32, device=dev) for _ in range(2)]
         self.dkl_accum = z(B, dt=torch.float64)
-        self.state = torch.zeros(10, dtype=torch.int32, device=dev)
-        self._state_init = torch.zeros(10, dtype=torch.int32, device=dev)
+        self.state = torch.zeros(12, dtype=torch.int32, device=dev)     # cmbpo_rollout_state (48 bytes)
+        self._state_init = torch.zeros(12, dtype=torch.int32, device=dev)
         self._state_init[0] = B
         self._arange = torch.arange(B, dtype=torch.int32, device=dev)
         self.alive_hist = torch.zeros(max(T, 1), dtype=torch.int32, device=dev)

@@ -137,7 +137,7 @@ typedef struct cmbpo_rollout_state {
   int64_t total_samples;  /* model_sampler.py:386 */
   int32_t n_stored_last;  /* transitions the last advance wrote */
   int32_t finished;       /* 1 once no path is alive */
-  int32_t tmp[4];         /* scratch of the advance kernels */
+  int32_t tmp[6];         /* scratch of the advance kernels (must be zero at reset) */
 } cmbpo_rollout_state;
 
 /* One sampler step AFTER cmbpo_step produced next_obs/rew/term/cost/dkl_path/ep_var_mean for the

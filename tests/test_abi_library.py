@@ -60,7 +60,7 @@ def test_ctypes_struct_layout_matches_header():
         assert int(got[name]) == C.sizeof(st), name
         for f, _ in st._fields_:
             assert int(got[f"{name}.{f}"]) == getattr(st, f).offset, f"{name}.{f}"
-    assert int(got["cmbpo_rollout_state"]) == 40   # 10 int32 words (rollout.py state tensor)
+    assert int(got["cmbpo_rollout_state"]) == 48   # 12 int32 words (rollout.py state tensor)
 
 
 def test_no_gpu_means_loud_failure_not_fallback(lib):
