@@ -398,3 +398,39 @@ def test_rollout_bookkeeping_matches_reference_modelsampler_golden(name):
     assert np.array_equal(got["dkl_accum"], g["dyn_dkl_path"])
     hist = ro.alive_hist.cpu().numpy()
     assert list(hist[: len(g["alive_hist"])]) == list(g["alive_hist"])
+
+
+@pytest.mark.parametrize("B,T", [(1, 2), (1, 5), (257, 3), (256, 2), (511, 4)])
+def test_rollout_edge_sizes_bit_exact(B, T):
+    """Ragged / minimal sizes: one path, one stored column (T=2 -> a path stores exactly T-1 = 1 transition, Q8),
+    row counts around the 256-row block boundary."""
+    env = "antsafe"
+    p, obs, ro, rec = _recorded_rollout(env, B, T, "schedule")
+    ref = _replay_through_oracle(p, env, obs, rec, T, "schedule", None, None)
+    total = _assert_pools_equal(ro, ref)
+    assert 0 < total <= B * (T - 1)
+    from constrainedmbpo_b200 import sharding
+    rec_t, coords = sharding.pack_records(ro.pool, 0)
+    assert rec_t.shape[0] == total
+
+
+def test_pack_records_empty_pool():
+    """A pool nothing was stored in (every path cut at the first step by a zero KL limit) packs to zero records."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    from constrainedmbpo_b200 import sharding, _lib
+    env, B, T = "antsafe", 300, 5
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    obs, _ = make_inputs(env, B)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True)
+    ro = cm.ModelRollout(fe, T, rollout_mode="uncertainty", dkl_lim=0.0)
+    ro.reset(obs)
+    ro.run(cm.StubPolicy(29, 8))
+    assert ro.counters() == (0, 0, 0, 1) and int(ro.pool["populated"].sum()) == 0
+    W = sharding.record_width(29, 8, 1)
+    out = torch.full((4, W), -7.0, device="cuda")
+    count = torch.full((1,), 99, dtype=torch.int64, device="cuda")
+    scratch = torch.empty(int(_lib.load().cmbpo_pack_scratch_bytes(B)) + 64, dtype=torch.uint8, device="cuda")
+    sharding.pack_records_cuda(ro.pool, 0, 29, 8, 1, out, count, scratch)
+    torch.cuda.synchronize()
+    assert int(count) == 0 and bool((out == -7.0).all())
