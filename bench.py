@@ -119,6 +119,26 @@ def measured_peaks():
     return dict(bf16_burst=1590.0, bf16_sustained=1400.0, hbm=6650.0, source="fallback")
 
 
+def bind_to_gpu_numa_node(gpu_index):
+    """Pin this rank's host threads (and so its pinned staging buffers, first-touched locally) to the CPUs NVML
+    reports as local to the GPU, so that 8 ranks streaming records to the host do not cross sockets on a multi-socket
+    box (a no-op on the single-node pool this was measured on).  Best effort: returns the CPU count bound, or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        n_words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        cpus = [64 * w + b for w, word in enumerate(mask) for b in range(64) if (word >> b) & 1]
+        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms DURING the timed region."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -233,6 +253,7 @@ def run_gpu(args, w, wname):
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else None   # N=1: all cores stay free for the cpu_baseline leg
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -405,7 +426,7 @@ def run_gpu(args, w, wname):
                                     f"{'copy-engine pulls over symmetric-memory peer mappings' if args.transport == 'p2p' else 'NCCL'}, gather={args.gather})" if world > 1 else "")},
         "clocks": clk,
         "e2e": {"value": e2e_val, "unit": "transitions/s", "h2d_bytes_per_step": int(start_host.numel() * 4),
-                "d2h_bytes_per_step": int(rec * per_rollout), "steps": e2e_steps},
+                "d2h_bytes_per_step": int(rec * per_rollout), "steps": e2e_steps, "host_cpus_bound": numa},
         "gpu_launches": int((kernels_per_sampler_step * (w["T"] - 1) + (3 if gather is not None else 0)) * args.steps),
         "roofline": {"bound": "tensor", "kernel": fwd_kernel, "achieved": achieved_tf, "peak": peak,
                      "unit": "TFLOP/s", "frac": achieved_tf / peak, "traffic": traffic, "traffic_source": traffic_src,
