@@ -75,6 +75,10 @@ class cmbpo_rollout_io(C.Structure):
         ("new_obs_dev", C.c_void_p), ("new_path_id_dev", C.c_void_p),
         ("scratch_dev", C.c_void_p), ("scratch_bytes", C.c_size_t),
         ("alive_hist_dev", C.c_void_p), ("n_members", C.c_int32),
+        ("val_cur_dev", C.c_void_p), ("cval_cur_dev", C.c_void_p), ("val_next_dev", C.c_void_p),
+        ("cval_next_dev", C.c_void_p), ("new_val_dev", C.c_void_p), ("new_cval_dev", C.c_void_p),
+        ("pool_val_dev", C.c_void_p), ("pool_cval_dev", C.c_void_p), ("finish_ptr_dev", C.c_void_p),
+        ("last_val_dev", C.c_void_p), ("last_cval_dev", C.c_void_p),
     ]
 
 

@@ -165,6 +165,12 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
       static_cast<float*>(io.pool_cost_dev)[se] = io.cost_dev ? static_cast<const float*>(io.cost_dev)[ie] : 0.f;
       static_cast<uint8_t*>(io.pool_term_dev)[se] = static_cast<const uint8_t*>(io.term_dev)[ie] ? 1 : 0;
     }
+    if (io.pool_val_dev) {   // val_buf / cval_buf[alive, ptr] = V(s_t), VC(s_t) (modelbuffer.py:141-146)
+      for (int e = 0; e < E; ++e) {
+        io.pool_val_dev[e * cap * T + slot] = io.val_cur_dev[e * cap + i];
+        io.pool_cval_dev[e * cap * T + slot] = io.cval_cur_dev[e * cap + i];
+      }
+    }
     static_cast<float*>(io.pool_dyn_error_dev)[slot] =
         io.ep_var_mean_dev ? static_cast<const float*>(io.ep_var_mean_dev)[i] : 0.f;
     static_cast<uint8_t*>(io.pool_populated_dev)[slot] = 1;
@@ -172,6 +178,20 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
   }
   const int k = (remaining && !term && !path_end) ? 1 : 0;
   if (i < n) keep[i] = (uint8_t)k;
+  if (io.finish_ptr_dev && i < n && !k) {
+    // this path ends now: what ModelSampler._finish_paths hands to finish_path_multiple (model_sampler.py:497-548)
+    //  - cut before the store (too uncertain / max_samples): column ptr, bootstrap V(s_t), VC(s_t)   (:336, append both)
+    //  - length reached after the store: column ptr+1, bootstrap V(s_t+1), VC(s_t+1)                 (:438, append both)
+    //  - environment terminal: column ptr+1, value bootstrap 0, cost bootstrap VC(s_t+1)             (:456, append_vals=False)
+    io.finish_ptr_dev[pid] = remaining ? ptr + 1 : ptr;
+    for (int e = 0; e < E; ++e) {
+      float lv, lc;
+      if (!remaining) { lv = io.val_cur_dev[e * cap + i]; lc = io.cval_cur_dev[e * cap + i]; }
+      else { lv = path_end ? io.val_next_dev[e * cap + i] : 0.f; lc = io.cval_next_dev[e * cap + i]; }
+      io.last_val_dev[e * cap + pid] = lv;
+      io.last_cval_dev[e * cap + pid] = lc;
+    }
+  }
   int tot;
   block_exclusive_scan(k, &tot);   // includes the __syncthreads that publishes s_pid / s_rem
   // row payloads: flat element loop over the block's 256 rows (source rows are contiguous, so loads are
@@ -273,6 +293,13 @@ __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const 
   __shared__ int s_dst[kRB];
   s_dst[threadIdx.x] = k ? dst : -1;
   if (k) static_cast<int*>(io.new_path_id_dev)[dst] = static_cast<const int*>(io.path_id_dev)[i];
+  if (k && io.new_val_dev) {   // V(s_t+1) of a survivor is V(s_t) of its next step: the critics run once per state
+    const int Ev = (io.mode == 2 && io.n_members > 1) ? io.n_members : 1;
+    for (int e = 0; e < Ev; ++e) {
+      io.new_val_dev[e * (size_t)io.n_paths + dst] = io.val_next_dev[e * (size_t)io.n_paths + i];
+      io.new_cval_dev[e * (size_t)io.n_paths + dst] = io.cval_next_dev[e * (size_t)io.n_paths + i];
+    }
+  }
   __syncthreads();
   const int OD = io.obs_dim;
   const int row_base = blockIdx.x * kRB;

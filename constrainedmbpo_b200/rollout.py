@@ -73,7 +73,7 @@ class ModelRollout:
     layout ``[B, max_path_length, dim]`` with row = start-state index (modelbuffer.py:45-114)."""
 
     def __init__(self, env, max_path_length, rollout_mode="schedule", dkl_lim=None, max_samples=None,
-                 row_offset=0, perm_fn=None):
+                 row_offset=0, perm_fn=None, value_fn=None):
         if rollout_mode not in MODES:
             raise ValueError("rollout_mode must be 'schedule', 'uncertainty' or 'iv_gae' (cmbpo.py:89)")
         if rollout_mode == "uncertainty" and dkl_lim is None:
@@ -88,6 +88,13 @@ class ModelRollout:
         # (fake_env.py:309-316, global NumPy RNG upstream).  It is a launch argument, so a captured graph
         # replays the permutations drawn at capture time.
         self.perm_fn = perm_fn
+        # Optional critics in the loop: value_fn(obs, n_rows_dev, path_ids) -> (v, vc), CUDA float32
+        # tensors shaped [capacity] ('iv_gae': [E, capacity]) holding V(obs), VC(obs) of the live rows -- what
+        # policy.get_action_outs / get_v / get_vc return after the sampler's v_inds gather (model_sampler.py:275-294,
+        # :497-548).  Called once per state: on the start states at reset and on next_obs every step; survivors'
+        # values are compacted along with their observations.  With it the rollout fills val / cval pools and the
+        # finish records (finish_ptr, last_val, last_cval) that ``finish()`` hands to cmbpo_finish_paths.
+        self.value_fn = value_fn
         self.device = env.device
         self.B = 0
         self._lib = _lib.load()
@@ -110,6 +117,11 @@ class ModelRollout:
             "dyn_error": z(T, B).t(), "populated": z(T, B, dt=torch.uint8).t(),
         }
         self.cur = [torch.empty(*E, B, OD, dtype=torch.float32, device=dev) for _ in range(2)]
+        if self.value_fn is not None:
+            self.pool["val"], self.pool["cval"] = sca(), sca()
+            self.vcur = [[torch.zeros(*E, B, dtype=torch.float32, device=dev) for _ in range(2)] for _ in range(2)]
+            self.finish_ptr = torch.zeros(B, dtype=torch.int32, device=dev)
+            self.last_val, self.last_cval = z(*E, B), z(*E, B)
         self.pid = [torch.empty(B, dtype=torch.int32, device=dev) for _ in range(2)]
         self.dkl_accum = z(B, dt=torch.float64)
         self.state = torch.zeros(12, dtype=torch.int32, device=dev)     # cmbpo_rollout_state (48 bytes)
@@ -142,6 +154,11 @@ class ModelRollout:
         self.state.copy_(self._state_init)
         self.flip = 0
         self.steps_done = 0
+        self.gae = None
+        if self.value_fn is not None:
+            self.finish_ptr.zero_(); self.last_val.zero_(); self.last_cval.zero_()
+            v, vc = self.value_fn(self.cur[0], self.state[0:1], self.pid[0])
+            self.vcur[0][0].copy_(v); self.vcur[0][1].copy_(vc)
 
     def step(self, policy):
         """One ``ModelSampler.sample`` (model_sampler.py:265-474) for all alive rows."""
@@ -174,6 +191,16 @@ class ModelRollout:
         io.scratch_dev, io.scratch_bytes = self.scratch.data_ptr(), self.scratch.numel()
         io.alive_hist_dev = self.alive_hist.data_ptr()
         io.n_members = env.num_networks if self.mode == "iv_gae" else 0
+        if self.value_fn is not None:
+            v_next, vc_next = self.value_fn(o["next_obs"], n_dev, pid)
+            self._v_next = (v_next.contiguous(), vc_next.contiguous())   # keep alive until the launch is enqueued
+            vc_, vn_ = self.vcur[self.flip], self.vcur[self.flip ^ 1]
+            io.val_cur_dev, io.cval_cur_dev = vc_[0].data_ptr(), vc_[1].data_ptr()
+            io.val_next_dev, io.cval_next_dev = self._v_next[0].data_ptr(), self._v_next[1].data_ptr()
+            io.new_val_dev, io.new_cval_dev = vn_[0].data_ptr(), vn_[1].data_ptr()
+            io.pool_val_dev, io.pool_cval_dev = p["val"].data_ptr(), p["cval"].data_ptr()
+            io.finish_ptr_dev = self.finish_ptr.data_ptr()
+            io.last_val_dev, io.last_cval_dev = self.last_val.data_ptr(), self.last_cval.data_ptr()
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         _lib.check(self._lib.cmbpo_rollout_advance(C.byref(io), stream))
         self.flip ^= 1
@@ -220,7 +247,7 @@ class ModelRollout:
         buffers when ``host_out`` is a dict (device->host copy of exactly the populated rows)."""
         mask = self.pool["populated"].bool()
         # 'iv_gae' pools carry a leading member axis: flatten to [n, E, ...]
-        per_member = () if self.mode != "iv_gae" else ("obs", "act", "next_obs", "rew", "cost", "term")
+        per_member = () if self.mode != "iv_gae" else ("obs", "act", "next_obs", "rew", "cost", "term", "val", "cval")
         out = {k: (v.movedim(0, 2)[mask] if k in per_member else v[mask])
                for k, v in self.pool.items() if k != "populated"}
         if host_out is None:
@@ -236,13 +263,37 @@ class ModelRollout:
         host_out["_n"] = n
         return host_out
 
+    def finish(self, gamma=0.99, lam=0.95, cost_gamma=0.99, cost_lam=0.95, model_ind=0, cares_about_cost=True,
+               max_uncertainty_r=5.5, max_uncertainty_c=5.5):
+        """``ModelBuffer.finish_path_multiple`` for every path of the finished rollout (modelbuffer.py:176-346):
+        adds adv / ret / cadv / cret (+ ret_var, cret_var, roll_lengths, croll_lengths and the horizon-trimmed
+        ``populated`` in 'iv_gae' mode) to the pool.  Needs ``value_fn``."""
+        if self.value_fn is None:
+            raise RuntimeError("finish() needs the critic values: construct ModelRollout with value_fn=...")
+        from .gae import finish_paths
+        p = self.pool
+        res = finish_paths(p["rew"], p["val"], p["cost"], p["cval"], self.finish_ptr, self.last_val, self.last_cval,
+                           self.mode, gamma=gamma, lam=lam, cost_gamma=cost_gamma, cost_lam=cost_lam,
+                           model_ind=model_ind, cares_about_cost=cares_about_cost,
+                           max_uncertainty_r=max_uncertainty_r, max_uncertainty_c=max_uncertainty_c,
+                           populated=p["populated"])
+        if "populated" in res:                    # pool["populated"] stays what store_multiple populated
+            res["populated_trimmed"] = res.pop("populated")
+        self.gae = res
+        return res
+
     def get(self, numpy=False):
         out = dict(self.pool)
+        out.update(getattr(self, "gae", None) or {})
+        if self.value_fn is not None:
+            out.update(finish_ptr=self.finish_ptr, last_val=self.last_val, last_cval=self.last_cval)
         out["dkl_accum"] = self.dkl_accum
         if numpy:
             out = {k: v.cpu().numpy() for k, v in out.items()}
             out["term"] = out["term"].astype(bool)
             out["populated"] = out["populated"].astype(bool)
+            if "populated_trimmed" in out:
+                out["populated_trimmed"] = out["populated_trimmed"].astype(bool)
         return out
 
     def all_gather(self, group=None):

@@ -179,6 +179,18 @@ typedef struct cmbpo_rollout_io {
   void* scratch_dev; size_t scratch_bytes;   /* >= cmbpo_rollout_scratch_bytes(n_paths) */
   int32_t* alive_hist_dev;     /* optional [T]: rows alive when step `step_index` began (diagnostics / FLOP accounting) */
   int32_t n_members;           /* mode 2 only: E (leading axis of the step arrays and pools); 0/1 otherwise */
+  /* Optional critic values (all NULL = not tracked).  The sampler stores V(s_t), VC(s_t) with every transition
+   * (model_sampler.py:275-294, modelbuffer.py:141-146) and hands bootstrap values to finish_path_multiple when a
+   * path ends (model_sampler.py:497-548).  val_cur/cval_cur: values of the current states, val_next/cval_next: of
+   * next_obs ([n_alive], 2-D modes: already gathered per path with v_inds; mode 2: [E][n_paths]).  Survivors'
+   * next values are compacted into new_val/new_cval (the next step's val_cur).  pool_val/pool_cval use the pool
+   * storage; finish_ptr [n_paths], last_val / last_cval [E][n_paths] are what cmbpo_finish_paths consumes. */
+  const float* val_cur_dev; const float* cval_cur_dev;
+  const float* val_next_dev; const float* cval_next_dev;
+  float* new_val_dev; float* new_cval_dev;
+  float* pool_val_dev; float* pool_cval_dev;
+  int32_t* finish_ptr_dev;
+  float* last_val_dev; float* last_cval_dev;
 } cmbpo_rollout_io;
 size_t cmbpo_rollout_scratch_bytes(int64_t n_paths);
 int cmbpo_rollout_advance(const cmbpo_rollout_io* io, void* stream);

@@ -434,3 +434,73 @@ def test_pack_records_empty_pool():
     sharding.pack_records_cuda(ro.pool, 0, 29, 8, 1, out, count, scratch)
     torch.cuda.synchronize()
     assert int(count) == 0 and bool((out == -7.0).all())
+
+
+def _golden_policy_values(seed_cfg):
+    """The FakePolicy of tests/golden/make_golden_sampler.py (deterministic functions of the observation) and the
+    per-path v_inds / vc_inds the reference sampler drew at reset (same seeded generator, same call order)."""
+    r = np.random.default_rng(seed_cfg + 10)
+    r.standard_normal((29, 8))                          # P (actions come from the recording)
+    wv = (r.standard_normal((7, 29)) / np.sqrt(29)).astype(np.float32)
+    wc = (r.standard_normal((7, 29)) / np.sqrt(29)).astype(np.float32)
+    return wv, wc, np.random.default_rng(seed_cfg + 11)
+
+
+@pytest.mark.parametrize("name,seed", [("schedule", 21), ("uncertainty", 22), ("iv_gae", 23)])
+def test_rollout_values_and_finish_records_match_reference_golden(name, seed):
+    """Critic values in the loop (SURVEY §8f N1 plumbing) + finish_path_multiple (N2), end to end against the
+    reference's real sampler / pool: val_buf / cval_buf, the column and bootstrap values of every finished path
+    (model_sampler.py:497-548), then adv / ret / cadv / cret (and the iv outputs + horizon trim) from finish()."""
+    import os
+    import torch
+    import constrainedmbpo_b200 as cm
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", f"sampler_{name}.npz"), allow_pickle=False)
+    steps = [{k: g[f"step{i}_{k}"] for k in ("cur", "act", "next_obs", "rew", "term", "cost", "dkl", "ep_var")}
+             for i in range(int(g["n_steps"]))]
+    B, T, E = g["start_obs"].shape[0], int(g["T"]), int(g["E"])
+    iv = name == "iv_gae"
+    wv, wc, prng = _golden_policy_values(seed)
+    v_inds, vc_inds = prng.integers(0, 3, B), prng.integers(0, 3, B)       # policy.random_v_inds / random_vc_inds at reset
+    env = _ReplayEnv(steps, B, E, iv)
+
+    def value_fn(obs, n_dev, pid):
+        n = int(n_dev.item())
+        o = (obs[:, :n] if iv else obs[:n]).cpu().numpy()
+        ids = pid[:n].cpu().numpy()
+        lead = (E,) if iv else ()
+        v, vc = np.zeros(lead + (B,), np.float32), np.zeros(lead + (B,), np.float32)
+        if n:
+            if iv:   # get_v on [E, n, obs] -> [E, n]
+                v[:, :n] = np.sin(np.einsum("ebd,ed->eb", o, wv)).astype(np.float32)
+                vc[:, :n] = (0.5 * np.sin(np.einsum("ebd,ed->eb", o, wc)).astype(np.float32) + 0.5)
+            else:    # get_v(...)[v_inds, arange]: 3 critics, one drawn per path at reset
+                allv = np.sin(o @ wv[:3].T).T.astype(np.float32)
+                allc = (0.5 * np.sin(o @ wc[:3].T).T.astype(np.float32) + 0.5)
+                v[:n], vc[:n] = allv[v_inds[ids], np.arange(n)], allc[vc_inds[ids], np.arange(n)]
+        return torch.from_numpy(v).cuda(), torch.from_numpy(vc).cuda()
+
+    ro = cm.ModelRollout(env, T, rollout_mode=name, dkl_lim=float(g["dkl_lim"]) or None,
+                         max_samples=int(g["max_samples"]) or None, value_fn=value_fn)
+    ro.reset(g["start_obs"])
+    for _ in range(T - 1):
+        ro.step(lambda cur, n_dev: env.policy(cur, n_dev))
+    got = ro.get(numpy=True)
+    # the fixture's policy evaluated the bootstrap values on row SUBSETS (get_v(obs[term_mask]), model_sampler.py:521),
+    # this value_fn on all live rows: a float32 BLAS product may round differently for different batch shapes, so
+    # the value arrays are compared to 1 ulp-ish; WHICH value lands where (and the finish column) is exact
+    close = lambda a, b: a.shape == b.shape and np.allclose(a, b, rtol=1e-6, atol=1e-7)
+    assert close(got["val"], g["val_buf"]) and close(got["cval"], g["cval_buf"])
+    assert np.array_equal(got["val"] != 0, g["val_buf"] != 0)
+    assert np.array_equal(got["finish_ptr"], g["finish_ptr"])
+    assert close(got["last_val"], g["last_val"]) and close(got["last_cval"], g["last_cval"])
+    assert np.array_equal(got["last_val"] == 0, g["last_val"] == 0)      # env terminals bootstrap with exactly 0
+    res = ro.finish(gamma=float(g["gamma"]), lam=float(g["lam"]), cost_gamma=float(g["cost_gamma"]), cost_lam=float(g["cost_lam"]),
+                    model_ind=int(g["model_ind"]), cares_about_cost=True,
+                    max_uncertainty_r=float(g["max_uncertainty"][0]), max_uncertainty_c=float(g["max_uncertainty"][1]))
+    keys = [("adv", "adv_buf"), ("ret", "ret_buf"), ("cadv", "cadv_buf"), ("cret", "cret_buf")]
+    if iv:
+        keys += [("ret_var", "ret_var_buf"), ("cret_var", "cret_var_buf"), ("roll_lengths", "roll_lengths_buf")]
+    for ours, ref in keys:
+        assert np.allclose(res[ours].cpu().numpy(), g[ref], rtol=2e-5, atol=2e-6), ours
+    if iv:
+        assert np.array_equal(res["populated_trimmed"].cpu().numpy().astype(bool), g["populated_mask"])
