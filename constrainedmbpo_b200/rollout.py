@@ -46,6 +46,35 @@ class StubPolicy:
         return self._act
 
 
+class CriticValues:
+    """``value_fn`` for ``ModelRollout`` built from the policy's two value ensembles as device models
+    (cpo_policy.py:883-945: V and VC are ``construct_model`` ensembles -- 3 nets, 128x128 swish, MSE, i.e. the
+    non-probabilistic ``BNN.predict`` branch, bnn.py:718-724 -- so the same forward kernel serves them).
+    2-D modes: every path keeps the critic member drawn for it at reset (``policy.random_v_inds`` /
+    ``random_vc_inds``, model_sampler.py:248-249), the value of a row is that member's prediction
+    (``get_action_outs['v'][v_inds, batch_inds]``, :290).  The per-path gather is an index op on the
+    ``[E_v, B]`` predictions; all arithmetic is the ensemble forward."""
+
+    def __init__(self, v_model, vc_model, n_paths, v_inds=None, vc_inds=None, seed=None):
+        self.v, self.vc = v_model, vc_model
+        dev = v_model.device
+        g = torch.Generator().manual_seed(int(seed)) if seed is not None else None
+        draw = lambda m: torch.randint(0, m.num_nets, (n_paths,), generator=g)
+        as_idx = lambda x, m: (draw(m) if x is None else torch.as_tensor(np.asarray(x))).to(dev, torch.int64)
+        self.v_inds, self.vc_inds = as_idx(v_inds, v_model), as_idx(vc_inds, vc_model)
+
+    def __call__(self, obs, n_rows_dev=None, path_ids=None):
+        if obs.dim() != 2:
+            raise NotImplementedError("'iv_gae' states need value ensembles with one member per dynamics member")
+        B = obs.shape[0]
+        pid = (path_ids if path_ids is not None else torch.arange(B, device=obs.device)).long().clamp_(0, self.v_inds.shape[0] - 1)
+        out = []
+        for model, inds in ((self.v, self.v_inds), (self.vc, self.vc_inds)):
+            mean, _ = model.predict_device([obs], 2, 0, want_var=False)          # [E_v, B, 1]
+            out.append(mean[:, :, 0].gather(0, inds[pid][None, :])[0])
+        return out[0], out[1]
+
+
 def compute_dynamics_dkl(env, policy, obs_batch, depth=1):
     """``ModelSampler.compute_dynamics_dkl`` (model_sampler.py:160-176): roll ``depth`` steps from
     ``obs_batch``, dropping terminated rows, and return (running mean of ``ensemble_dkl_mean``

@@ -504,3 +504,45 @@ def test_rollout_values_and_finish_records_match_reference_golden(name, seed):
         assert np.allclose(res[ours].cpu().numpy(), g[ref], rtol=2e-5, atol=2e-6), ours
     if iv:
         assert np.array_equal(res["populated_trimmed"].cpu().numpy().astype(bool), g["populated_mask"])
+
+
+def test_rollout_with_device_critics_end_to_end():
+    """N1 wiring: V / VC as device ensembles (3 nets, 128x128 swish, MSE -> non-probabilistic predict) feeding the
+    rollout through CriticValues; stored values equal BNN.predict of the stored observations with the per-path
+    member, bootstrap rules hold, and finish() equals the oracle's GAE on the same pools."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    env, B, T = "antsafe", 700, 7
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    obs, _ = make_inputs(env, B)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True, seed=2)
+    critics = []
+    for k, name in enumerate(("V", "VC")):
+        pc = orc.init_ensemble(np.random.default_rng(40 + k), 29, 1, (128, 128), 3, probabilistic=False,
+                               use_scaler_in=False, use_scaler_out=False, elites=[0, 1], dtype=np.float32)
+        m = cm.construct_model(in_dim=29, out_dim=1, name=name, hidden_dims=(128, 128), num_networks=3, num_elites=2,
+                               loss="MSE", use_scaler_in=False, use_scaler_out=False, device="cuda:0")
+        m.load_state(pc.weights, pc.biases, elites=pc.elites)
+        critics.append(m)
+    vf = cm.CriticValues(critics[0], critics[1], B, seed=3)
+    ro = cm.ModelRollout(fe, T, rollout_mode="schedule", value_fn=vf)
+    ro.reset(obs)
+    ro.run(cm.StubPolicy(29, 8))
+    got = ro.get(numpy=True)
+    pop = got["populated"]
+    assert pop.sum() > B and got["finish_ptr"].min() >= 1 and (got["finish_ptr"] == pop.sum(1)).all()
+    # stored values = the drawn member's prediction for the stored observation
+    for key, m, inds in (("val", critics[0], vf.v_inds), ("cval", critics[1], vf.vc_inds)):
+        pred = m.predict(got["obs"][pop], factored=True, inc_var=False)[..., 0]          # [3, n]
+        member = inds.cpu().numpy()[np.where(pop)[0]]
+        assert np.allclose(got[key][pop], pred[member, np.arange(pred.shape[1])], rtol=1e-5, atol=1e-6)
+    # environment terminals bootstrap the value with 0, everything else with V(next state)
+    last = pop.sum(1) - 1
+    ended_by_term = got["term"][np.arange(B), last] & (last < T - 2)
+    assert ended_by_term.any() and (got["last_val"][ended_by_term] == 0).all()
+    assert (got["last_val"][~ended_by_term] != 0).all() and (got["last_cval"] != 0).all()
+    res = ro.finish(gamma=0.99, lam=0.95, cost_gamma=0.97, cost_lam=0.9)
+    ref = orc.finish_paths(got["rew"], got["val"], got["cost"], got["cval"], got["finish_ptr"], got["last_val"],
+                           got["last_cval"], "schedule", 0.99, 0.95, 0.97, 0.9)
+    for k in ("adv", "ret", "cadv", "cret"):
+        assert np.allclose(res[k].cpu().numpy(), ref[k], rtol=2e-5, atol=2e-6), k
