@@ -57,6 +57,7 @@ class cmbpo_step_io(C.Structure):
         ("cost_dev", C.c_void_p), ("dkl_path_dev", C.c_void_p), ("ep_var_mean_dev", C.c_void_p),
         ("ep_var_dev", C.c_void_p), ("scalars_dev", C.c_void_p),
         ("workspace_dev", C.c_void_p), ("workspace_bytes", C.c_size_t),
+        ("sample_mode", C.c_int32), ("bound_logvar", C.c_int32), ("max_logvar", C.c_float), ("min_logvar", C.c_float),
     ]
 
 

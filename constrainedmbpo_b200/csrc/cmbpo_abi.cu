@@ -470,6 +470,9 @@ extern "C" int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream_) 
   sp.elites = h->elites_dev; sp.n_elites = h->n_elites;
   sp.seed = io->seed; sp.rng_offset = io->rng_offset; sp.row_offset = io->row_offset;
   sp.noise = io->noise_dev;
+  sp.sample_mode = io->sample_mode; sp.bound_logvar = io->bound_logvar;
+  sp.max_logvar = io->max_logvar; sp.min_logvar = io->min_logvar;
+  sp.head_shift = h->consts + 2 * pl.in_dim + pl.n_head;
   sp.env_id = io->env_id; sp.cost_mode = io->cost_mode;
   sp.n_rows_dev = io->n_rows_dev; sp.n_rows = io->n_rows;
   sp.next_obs = io->next_obs_dev; sp.rew = io->rew_dev; sp.term = io->term_dev; sp.cost = io->cost_dev;

@@ -30,6 +30,17 @@ __device__ __forceinline__ float u32_to_unit(uint32_t x) {  // (0,1]
   return ((float)(x >> 8) + 1.0f) * (1.0f / 16777216.0f);
 }
 
+// standard normal from one Philox draw: Box-Muller on two 32-bit words (u1 in (0,1], u2 in (0,1])
+__device__ __forceinline__ float philox_normal(unsigned long long row, uint32_t col, uint32_t stream, unsigned long long seed) {
+  uint32_t rnd[4];
+  philox4x32_10((uint32_t)row, (uint32_t)(row >> 32), stream, 0x9E3779B9u ^ col, (uint32_t)seed, (uint32_t)(seed >> 32), rnd);
+  const float u1 = u32_to_unit(rnd[0]), u2 = u32_to_unit(rnd[1]);
+  return sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2);
+}
+
+// softplus(x) = log(1 + e^x), stable for large |x| (np.logaddexp(0, x))
+__device__ __forceinline__ float softplusf(float x) { return x > 0.f ? x + log1pf(expf(-x)) : log1pf(expf(x)); }
+
 // np.clip(x, 0, 1e10) including NumPy's NaN propagation (mbpo/models/utils.py:24)
 __device__ __forceinline__ float clip_kl_exact(float x) {
   const float r = fminf(fmaxf(x, 0.f), 1e10f);
@@ -277,6 +288,16 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
               for (int e = 0; e < E; ++e) m[e] += o;
             }
           }
+          if (p.bound_logvar) {   // optional PETS bounding on the raw head (bnn.py:888-889, bnn_chua.py:400-401)
+            const float sh = p.head_shift ? p.head_shift[D + d] : 0.f;
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+              float raw = lv[e] - sh;
+              raw = p.max_logvar - softplusf(p.max_logvar - raw);
+              raw = p.min_logvar + softplusf(raw - p.min_logvar);
+              lv[e] = raw + sh;
+            }
+          }
           float lvmin = lv[0], lvmax = lv[0];
 #pragma unroll
           for (int e = 1; e < E; ++e) { lvmin = fminf(lvmin, lv[e]); lvmax = fmaxf(lvmax, lv[e]); }
@@ -295,9 +316,11 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
             if (p.ep_var) p.ep_var[(size_t)g * D + d] = epv;
           }
           float x = p.per_slot ? pick<E>(m, so) : pick<E>(m, eidx);
-          if (p.noise) {  // optional north_star mode: mean + noise*std (off in the live reference)
+          if (p.noise || p.sample_mode == 1) {  // optional north_star mode: mean + N(0,1)*std (off in the live reference)
             const float vs = p.per_slot ? pick<E>(v, so) : pick<E>(v, eidx);
-            const float z = p.noise[(p.per_slot ? (size_t)so * slot_rows * D : 0) + (size_t)g * D + d];
+            const unsigned long long grow = (unsigned long long)(p.row_offset + (p.row_ids ? (long long)p.row_ids[g] : g));
+            const float z = p.noise ? p.noise[(p.per_slot ? (size_t)so * slot_rows * D : 0) + (size_t)g * D + d]
+                                    : philox_normal(grow, (uint32_t)(so * 4096 + d + 1), (uint32_t)p.rng_offset, p.seed);
             x = fmaf(z, sqrtf(vs), x);
           }
           if (d < OD) {
@@ -401,6 +424,16 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const Step
 #pragma unroll
           for (int e = 0; e < E; ++e) m[e] += tiles[e * tile_elems + r * OD + d];   // fake_env.py:156
         }
+        if (p.bound_logvar) {   // optional PETS bounding on the raw head (bnn.py:888-889, bnn_chua.py:400-401)
+          const float sh = p.head_shift ? p.head_shift[D + d] : 0.f;
+#pragma unroll
+          for (int e = 0; e < E; ++e) {
+            float raw = lv[e] - sh;
+            raw = p.max_logvar - softplusf(p.max_logvar - raw);
+            raw = p.min_logvar + softplusf(raw - p.min_logvar);
+            lv[e] = raw + sh;
+          }
+        }
         float lvmin = lv[0], lvmax = lv[0];
 #pragma unroll
         for (int e = 1; e < E; ++e) { lvmin = fminf(lvmin, lv[e]); lvmax = fmaxf(lvmax, lv[e]); }
@@ -420,6 +453,10 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const Step
         for (int e = 0; e < E; ++e) {
           float x = m[e];
           if (p.noise) x = fmaf(p.noise[((size_t)e * slot_rows + g) * D + d], sqrtf(v[e]), x);
+          else if (p.sample_mode == 1) {
+            const unsigned long long grow = (unsigned long long)(p.row_offset + (p.row_ids ? (long long)p.row_ids[g] : g));
+            x = fmaf(philox_normal(grow, (uint32_t)(e * 4096 + d + 1), (uint32_t)p.rng_offset, p.seed), sqrtf(v[e]), x);
+          }
           if (d < OD) {
             tiles[e * tile_elems + r * OD + d] = x;   // own element only
             if (!(fabsf(x) <= 3.402823466e38f)) fin &= ~(1u << e);

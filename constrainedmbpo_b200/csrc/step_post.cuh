@@ -25,6 +25,10 @@ struct StepParams {
   long long row_offset;      // global index of local row 0 (sharding must not change the draw)
   const int* row_ids;        // optional [B] path id per row (replaces g in row_offset + g)
   const float* noise;        // optional standard normals [B][D] / [E][B][D]; nullptr = reference behaviour
+  int sample_mode;           // 1: in-kernel Philox Gaussian sampling mean + N(0,1)*std (0 = reference: means)
+  int bound_logvar;          // 1: soft-bound the raw log-variance head to [min_logvar, max_logvar]
+  float max_logvar, min_logvar;
+  const float* head_shift;   // [2D] output-scaler shifts (2*log s_out for the logvar columns), for bound_logvar
   int env_id;                // EnvId
   int cost_mode;             // 0 zeros (fake_env.py:202), 1 static cost_f (fake_env.py:189)
   const int* n_rows_dev;     // optional device-resident row count

@@ -27,7 +27,9 @@ class FakeEnv:
                  cares_about_cost=False,
                  session=None,
                  device="cuda:0",
-                 seed=None):
+                 seed=None,
+                 sample_noise=False,
+                 logvar_bound=None):
         # fake_env.py:28-44
         self.domain = true_environment.domain if getattr(true_environment, "domain", None) else ""
         self.env = true_environment
@@ -68,6 +70,11 @@ class FakeEnv:
                                                seed=None if seed is None else seed + 1)
         else:
             self._cost_model = None
+        # options beyond the live reference (both off by default): Gaussian sampling of the next state in the output
+        # kernel (Philox4x32-10, keyed by global row id) and PETS soft-bounding of the log-variance head to
+        # (max_logvar, min_logvar) -- commented out upstream (bnn.py:888-889)
+        self.sample_noise = bool(sample_noise)
+        self.logvar_bound = tuple(float(x) for x in logvar_bound) if logvar_bound is not None else None
         self.dyn_target_var_rm = 1
         self._rng_offset = 0
         self._seed = int(seed) if seed is not None else int(np.random.randint(2 ** 31 - 1))
@@ -143,6 +150,9 @@ class FakeEnv:
             io.noise_dev = noise.data_ptr()
         io.seed, io.rng_offset, io.row_offset = self._seed, self._rng_offset, 0
         self._rng_offset += 1
+        io.sample_mode = 1 if self.sample_noise else 0
+        if self.logvar_bound is not None:
+            io.bound_logvar, io.max_logvar, io.min_logvar = 1, self.logvar_bound[0], self.logvar_bound[1]
         io.env_id = self._static.env_id
         io.cost_mode = 1 if (self.cares_about_cost and self.static_c) else 0
         io.next_obs_dev, io.rew_dev, io.term_dev = next_obs.data_ptr(), rew.data_ptr(), term.data_ptr()

@@ -123,6 +123,16 @@ typedef struct cmbpo_step_io {
   float* scalars_dev;          /* [4]: ensemble_dkl_mean, ensemble_mean_var, rew_mean, cost_mean */
   void* workspace_dev;
   size_t workspace_bytes;
+  /* Options beyond the live reference (both 0 = reference behaviour):
+   * sample_mode 1: Gaussian sampling in the kernel, sample = mean + N(0,1)*std of the selected member (every member in
+   *   3-D mode), normals from Philox4x32-10 (Box-Muller) keyed by (global row id, member, column, rng_offset, seed):
+   *   independent of sharding and batch position.  noise_dev, when given, takes precedence (injected draws).
+   * bound_logvar 1: logvar = max_logvar - softplus(max_logvar - logvar); logvar = min_logvar + softplus(logvar -
+   *   min_logvar) on the raw head, before the inverse output scaler (the PETS bounding that is commented out in
+   *   bnn.py:888-889; bnn_chua.py:400-401). */
+  int32_t sample_mode;
+  int32_t bound_logvar;
+  float max_logvar, min_logvar;
 } cmbpo_step_io;
 int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream);
 

@@ -130,3 +130,26 @@ def near_threshold_rows(env, next_obs_ref, tol_abs):
     if env == "halfcheetahsafe":
         near |= np.abs(np.abs(x[..., -1] * 10) - 2.0) <= 10 * t[..., -1]
     return near
+
+
+# ---- Philox4x32-10 (Salmon et al. 2011) in NumPy: reproduces the normals the output kernel draws in sample_mode 1 ----
+def philox4x32_10(c0, c1, c2, c3, k0, k1):
+    c0, c1, c2, c3 = (np.asarray(c, np.uint64) & 0xFFFFFFFF for c in (c0, c1, c2, c3))
+    k0, k1 = np.uint64(k0 & 0xFFFFFFFF), np.uint64(k1 & 0xFFFFFFFF)
+    M0, M1, MASK = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57), np.uint64(0xFFFFFFFF)
+    for _ in range(10):
+        p0, p1 = M0 * c0, M1 * c2
+        hi0, lo0, hi1, lo1 = p0 >> np.uint64(32), p0 & MASK, p1 >> np.uint64(32), p1 & MASK
+        c0, c1, c2, c3 = (hi1 ^ c1 ^ k0) & MASK, lo1, (hi0 ^ c3 ^ k1) & MASK, lo0
+        k0, k1 = (k0 + np.uint64(0x9E3779B9)) & MASK, (k1 + np.uint64(0xBB67AE85)) & MASK
+    return c0, c1, c2, c3
+
+
+def philox_normals(rows, D, stream, seed, member=0):
+    """[len(rows), D] standard normals exactly as step_post.cu's philox_normal draws them (Box-Muller on words 0, 1)."""
+    rows = np.asarray(rows, np.uint64)[:, None]
+    col = np.uint64(member * 4096 + 1) + np.arange(D, dtype=np.uint64)[None, :]
+    r = philox4x32_10(rows & np.uint64(0xFFFFFFFF), rows >> np.uint64(32), np.uint64(stream),
+                      np.uint64(0x9E3779B9) ^ col, seed & 0xFFFFFFFF, seed >> 32)
+    unit = lambda x: ((x >> np.uint64(8)).astype(np.float64) + 1.0) / 16777216.0
+    return np.sqrt(-2.0 * np.log(unit(r[0]))) * np.cos(2.0 * np.pi * unit(r[1]))

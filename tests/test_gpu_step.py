@@ -277,3 +277,62 @@ def test_step_against_reference_fake_env_golden(tag, env):
     assert np.median(rel) < 2e-2, f"dkl_path median rel err {np.median(rel):.3e}"
     assert abs(info["ensemble_mean_var"] - g["mean_var"]) < 2e-2 * g["mean_var"]
     assert abs(info["rew_mean"] - g["rew_mean"]) < 1e-2 * (abs(g["rew_mean"]) + s[-1])
+
+
+def test_step_philox_gaussian_sampling_mode():
+    """sample_mode 1 (north_star's fused Philox Gaussian sampling; off in the live reference): the kernel's draws are
+    reproduced in NumPy (Philox4x32-10 + Box-Muller keyed by global row id and column) and injected into the oracle;
+    draws do not depend on where a row sits in the batch."""
+    from tests.helpers import philox_normals
+    env, B = "halfcheetah", 4096
+    p = make_params(env, HIDDEN)
+    obs, act = make_inputs(env, B)
+    import constrainedmbpo_b200 as cm
+    fe = cm.FakeEnv(cm.SimpleEnv(17, 6), env, num_networks=7, num_elites=5, hidden_dims=HIDDEN, seed=1234, sample_noise=True)
+    fe._model.load_state([w.astype(np.float32) for w in p.weights], [b.astype(np.float32) for b in p.biases],
+                         scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+    idx = np.random.default_rng(7).choice(p.elites, size=B)
+    stream = fe._rng_offset
+    no, rw, tm, info = fe.step(obs, act, elite_idx=idx)
+    z = philox_normals(np.arange(B), 18, stream, fe._seed)
+    assert abs(z.mean()) < 0.02 and abs(z.std() - 1) < 0.02
+    rno, rrw, _, rinfo = orc.fake_env_step(p, env, obs.astype(np.float64), act.astype(np.float64), elite_idx=idx, noise=z)
+    s = out_scale(p)
+    std_sel = np.sqrt(rinfo["_vars"][idx, np.arange(B)])
+    bound = RTOL_BF16 * np.abs(rno) + ATOL_SCALE_BF16 * s[:-1] + 3e-2 * np.abs(z[:, :-1]) * std_sel[:, :-1]
+    assert (np.abs(no - rno) <= bound).all(), float((np.abs(no - rno) - bound).max())
+    assert np.abs(rw - rrw).max() <= RTOL_BF16 * np.abs(rrw).max() + ATOL_SCALE_BF16 * s[-1] + 3e-2 * np.abs(z[:, -1:] * std_sel[:, -1:]).max()
+    # the noise really is there (the deterministic step differs by about one std)
+    fe2 = build_cuda_env(p, env, HIDDEN)
+    det, *_ = fe2.step(obs, act, elite_idx=idx)
+    ratio = np.abs(no - det) / std_sel[:, :-1]
+    assert 0.6 < np.median(ratio) / 0.6745 < 1.4          # median |N(0,1)| = 0.6745
+    # shard invariance: rows [1000, 2000) stepped alone with their global ids draw the same normals
+    import torch
+    fe._rng_offset = stream
+    o = fe.step_device(torch.from_numpy(obs[1000:2000]).cuda(), torch.from_numpy(act[1000:2000]).cuda(),
+                       elite_idx=torch.from_numpy(idx[1000:2000].astype(np.int32)),
+                       row_ids=torch.arange(1000, 2000, dtype=torch.int32, device="cuda"))
+    assert np.array_equal(o["next_obs"].cpu().numpy(), no[1000:2000])
+
+
+def test_step_logvar_soft_bounding_option():
+    """bound_logvar (PETS soft bounds, commented out upstream at bnn.py:888-889): variances and everything derived from
+    them follow the oracle's bounded form; means are untouched."""
+    env, B = "antsafe", 2000
+    p = make_params(env, HIDDEN)
+    obs, act = make_inputs(env, B)
+    import constrainedmbpo_b200 as cm
+    bounds = (0.5, -10.0)                      # FakeEnv's max_logvar / min_logvar (fake_env.py:61-75)
+    fe = cm.FakeEnv(cm.SimpleEnv(29, 8), env, num_networks=7, num_elites=5, hidden_dims=HIDDEN, seed=0, logvar_bound=bounds)
+    fe._model.load_state([w.astype(np.float32) for w in p.weights], [b.astype(np.float32) for b in p.biases],
+                         scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+    idx = np.random.default_rng(7).choice(p.elites, size=B)
+    no, rw, tm, info = fe.step(obs, act, elite_idx=idx)
+    rno, _, _, rb = orc.fake_env_step(p, env, obs.astype(np.float64), act.astype(np.float64), elite_idx=idx, logvar_bound=bounds)
+    _, _, _, ru = orc.fake_env_step(p, env, obs.astype(np.float64), act.astype(np.float64), elite_idx=idx)
+    assert_means_close(no, rno, out_scale(p)[:-1], what="next_obs (bounded logvar)")
+    assert abs(info["ensemble_mean_var"] - rb["ensemble_mean_var"]) < 2e-2 * rb["ensemble_mean_var"]
+    assert abs(rb["ensemble_mean_var"] - ru["ensemble_mean_var"]) > 0.2 * ru["ensemble_mean_var"]   # the bound bites
+    rel = np.abs(info["ensemble_dkl_path"] - rb["ensemble_dkl_path"]) / (np.abs(rb["ensemble_dkl_path"]) + 1e-6)
+    assert np.median(rel) < 2e-2
