@@ -261,8 +261,8 @@ class BNN:
         ``(mu, var)`` pairs, elite list.  Needed after every ``train()``."""
         assert len(weights) == len(self.layers) and len(biases) == len(self.layers)
         for i, (w, b) in enumerate(zip(weights, biases)):
-            w = torch.as_tensor(np.asarray(w), dtype=torch.float32)
-            b = torch.as_tensor(np.asarray(b), dtype=torch.float32)
+            w = (w if torch.is_tensor(w) else torch.as_tensor(np.asarray(w))).to(torch.float32)
+            b = (b if torch.is_tensor(b) else torch.as_tensor(np.asarray(b))).to(torch.float32)
             if tuple(w.shape) != tuple(self.weights[i].shape) or b.numel() != self.biases[i].numel():
                 raise ValueError(f"layer {i}: expected {tuple(self.weights[i].shape)}, got {tuple(w.shape)}")
             self.weights[i] = w.to(self.device).contiguous()

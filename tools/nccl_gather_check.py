@@ -30,8 +30,10 @@ def main():
     for mode, T, lim in (("uncertainty", 10, 3e-5), ("schedule", 5, None), ("iv_gae", 5, None)):
         fe = cm.FakeEnv(cm.SimpleEnv(29, 8), env, num_networks=7, num_elites=5, hidden_dims=hidden,
                         cares_about_cost=True, device=str(dev), seed=3)
-        fe._model.load_state([w.astype(np.float32) for w in p.weights], [b.astype(np.float32) for b in p.biases],
-                             scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+        if rank == 0:      # only rank 0 holds the "trained" state; the others receive it (weights replicated, §8e)
+            fe._model.load_state([w.astype(np.float32) for w in p.weights], [b.astype(np.float32) for b in p.biases],
+                                 scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+        sharding.broadcast_model_state(fe._model, src=0)
         lo, hi = sharding.shard_bounds(B, world, rank)
         obs = torch.from_numpy(obs_all[lo:hi]).to(dev)
         full, counts = _run(fe, obs, lo, T, mode, lim, world, 3)
