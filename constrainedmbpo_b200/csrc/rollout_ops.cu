@@ -90,6 +90,11 @@ __device__ __forceinline__ bool last_block_scan(int* blk_cnt, int my_count, int 
   return true;
 }
 
+// idx / w for 0 <= idx < 2^20 and small w through a float reciprocal (exact: the quotient's fractional part stays
+// at least 0.5/w away from an integer, far above the float rounding error); replaces a ~20-instruction integer division
+// in the payload copy loops
+__device__ __forceinline__ int fast_div(int idx, float inv_w) { return (int)(((float)idx + 0.5f) * inv_w); }
+
 // A: too_uncertain flags (model_sampler.py:311-315) -> per-block count of still-certain rows
 __global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* certain, int* blk_cnt, int* snap, int* hist) {
   RolloutState* st = static_cast<RolloutState*>(io.state_dev);
@@ -198,6 +203,7 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
   // fully coalesced; every thread has several independent load->store chains in flight -- a
   // warp-per-row loop here was a 32-deep serial latency chain, 35 us even for a handful of rows)
   const int OD = io.obs_dim, AD = io.act_dim;
+  const float inv_od = 1.0f / (float)OD, inv_ad = AD > 0 ? 1.0f / (float)AD : 0.f;
   const int row_base = blockIdx.x * kRB;
   const int n_here = min(kRB, n - row_base);
   for (int e = 0; e < E; ++e) {
@@ -205,9 +211,9 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
     const float* sn = static_cast<const float*>(io.next_obs_dev) + (e * cap + row_base) * OD;
     float* po = static_cast<float*>(io.pool_obs_dev) + e * cap * T * OD;
     float* pn = static_cast<float*>(io.pool_next_obs_dev) + e * cap * T * OD;
-#pragma unroll 4
+#pragma unroll 8
     for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {
-      const int r = idx / OD, d = idx - r * OD;
+      const int r = fast_div(idx, inv_od), d = idx - r * OD;
       if (s_rem[r]) {
         const size_t o = ((size_t)ptr * cap + s_pid[r]) * OD + d;
         po[o] = so[idx];
@@ -219,7 +225,7 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
       float* pa = static_cast<float*>(io.pool_act_dev) + e * cap * T * AD;
 #pragma unroll 4
       for (int idx = threadIdx.x; idx < n_here * AD; idx += kRB) {
-        const int r = idx / AD, d = idx - r * AD;
+        const int r = fast_div(idx, inv_ad), d = idx - r * AD;
         if (s_rem[r]) pa[((size_t)ptr * cap + s_pid[r]) * AD + d] = sa[idx];
       }
     }
@@ -302,6 +308,7 @@ __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const 
   }
   __syncthreads();
   const int OD = io.obs_dim;
+  const float inv_od = 1.0f / (float)OD;
   const int row_base = blockIdx.x * kRB;
   const int n_here = min(kRB, n_before - row_base);
   const int E = (io.mode == 2 && io.n_members > 1) ? io.n_members : 1;
@@ -311,7 +318,7 @@ __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const 
     float* dstp = static_cast<float*>(io.new_obs_dev) + e * cap * OD;
 #pragma unroll 4
     for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {   // flat element loop, see k_store
-      const int r = idx / OD, d = idx - r * OD;
+      const int r = fast_div(idx, inv_od), d = idx - r * OD;
       const int d0 = s_dst[r];
       if (d0 >= 0) dstp[(size_t)d0 * OD + d] = src[idx];
     }

@@ -223,7 +223,7 @@ __device__ __forceinline__ void finish_scalars(const StepParams& p, const float 
   if (tid == 0) *p.ticket = 0;   // ready for the next launch
 }
 
-template <int E>
+template <int E, bool OPT>   // OPT: the beyond-reference options (sample_mode / bound_logvar) are compiled in
 __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepParams p) {
   __shared__ float tile[kPostRows * 64 + 32];  // obs in / next_obs out staging (obs_dim <= 64)
   __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
               for (int e = 0; e < E; ++e) m[e] += o;
             }
           }
-          if (p.bound_logvar) {   // optional PETS bounding on the raw head (bnn.py:888-889, bnn_chua.py:400-401)
+          if (OPT && p.bound_logvar) {   // optional PETS bounding on the raw head (bnn.py:888-889, bnn_chua.py:400-401)
             const float sh = p.head_shift ? p.head_shift[D + d] : 0.f;
 #pragma unroll
             for (int e = 0; e < E; ++e) {
@@ -316,7 +316,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
             if (p.ep_var) p.ep_var[(size_t)g * D + d] = epv;
           }
           float x = p.per_slot ? pick<E>(m, so) : pick<E>(m, eidx);
-          if (p.noise || p.sample_mode == 1) {  // optional north_star mode: mean + N(0,1)*std (off in the live reference)
+          if (p.noise || (OPT && p.sample_mode == 1)) {  // optional north_star mode: mean + N(0,1)*std (off in the live reference)
             const float vs = p.per_slot ? pick<E>(v, so) : pick<E>(v, eidx);
             const unsigned long long grow = (unsigned long long)(p.row_offset + (p.row_ids ? (long long)p.row_ids[g] : g));
             const float z = p.noise ? p.noise[(p.per_slot ? (size_t)so * slot_rows * D : 0) + (size_t)g * D + d]
@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
 // (row, column) with member e's mean shifted by member e's own observation; all E member tiles live in
 // (dynamic) shared memory so global traffic stays coalesced.  Warp `part` < E then evaluates the static
 // termination / cost function of member `part`.
-template <int E>
+template <int E, bool OPT>
 __global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const StepParams p) {
   extern __shared__ float tiles[];                 // [E][kPostRows * OD]
   __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
@@ -424,7 +424,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const Step
 #pragma unroll
           for (int e = 0; e < E; ++e) m[e] += tiles[e * tile_elems + r * OD + d];   // fake_env.py:156
         }
-        if (p.bound_logvar) {   // optional PETS bounding on the raw head (bnn.py:888-889, bnn_chua.py:400-401)
+        if (OPT && p.bound_logvar) {   // optional PETS bounding on the raw head (bnn.py:888-889, bnn_chua.py:400-401)
           const float sh = p.head_shift ? p.head_shift[D + d] : 0.f;
 #pragma unroll
           for (int e = 0; e < E; ++e) {
@@ -453,7 +453,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const Step
         for (int e = 0; e < E; ++e) {
           float x = m[e];
           if (p.noise) x = fmaf(p.noise[((size_t)e * slot_rows + g) * D + d], sqrtf(v[e]), x);
-          else if (p.sample_mode == 1) {
+          else if (OPT && p.sample_mode == 1) {
             const unsigned long long grow = (unsigned long long)(p.row_offset + (p.row_ids ? (long long)p.row_ids[g] : g));
             x = fmaf(philox_normal(grow, (uint32_t)(e * 4096 + d + 1), (uint32_t)p.rng_offset, p.seed), sqrtf(v[e]), x);
           }
@@ -583,22 +583,28 @@ __global__ void aggregate_predict_kernel(const float* __restrict__ heads, long l
   }
 }
 
-template <int E>
-static cudaError_t launch_step_post_E(const StepParams& p, int n_blocks, cudaStream_t stream) {
+template <int E, bool OPT>
+static cudaError_t launch_step_post_EO(const StepParams& p, int n_blocks, cudaStream_t stream) {
   if (p.per_slot && E > 1) {
     const size_t smem = (size_t)E * kPostRows * p.obs_dim * sizeof(float);
     static bool attr_set = false;   // same value for every launch of this instantiation (obs_dim <= 64)
     if (!attr_set) {
-      cudaError_t e = cudaFuncSetAttribute(step_post3d_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      cudaError_t e = cudaFuncSetAttribute(step_post3d_kernel<E, OPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)((size_t)E * kPostRows * 64 * sizeof(float)));
       if (e != cudaSuccess) return e;
       attr_set = true;
     }
-    step_post3d_kernel<E><<<n_blocks, kPostThreads, smem, stream>>>(p);
+    step_post3d_kernel<E, OPT><<<n_blocks, kPostThreads, smem, stream>>>(p);
     return cudaGetLastError();
   }
-  step_post_kernel<E><<<n_blocks, kPostThreads, 0, stream>>>(p);
+  step_post_kernel<E, OPT><<<n_blocks, kPostThreads, 0, stream>>>(p);
   return cudaGetLastError();
+}
+
+template <int E>
+static cudaError_t launch_step_post_E(const StepParams& p, int n_blocks, cudaStream_t stream) {
+  if (p.bound_logvar || p.sample_mode) return launch_step_post_EO<E, true>(p, n_blocks, stream);
+  return launch_step_post_EO<E, false>(p, n_blocks, stream);
 }
 
 int step_post_blocks(long long n_rows, int num_sms) {
