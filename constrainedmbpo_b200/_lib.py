@@ -109,6 +109,14 @@ class cmbpo_gae_io(C.Structure):
     ]
 
 
+class cmbpo_norm_io(C.Structure):
+    _fields_ = [
+        ("n_elems", C.c_int64), ("adv_dev", C.c_void_p), ("cadv_dev", C.c_void_p), ("ret_dev", C.c_void_p),
+        ("cret_dev", C.c_void_p), ("populated_dev", C.c_void_p), ("stats_dev", C.c_void_p),
+        ("scratch_dev", C.c_void_p), ("scratch_bytes", C.c_size_t),
+    ]
+
+
 # every symbol include/cmbpo_b200.h declares: (restype, argtypes)
 SYMBOLS = {
     "cmbpo_create": (C.c_int, [C.POINTER(cmbpo_cfg), C.c_int, C.POINTER(C.c_void_p)]),
@@ -131,6 +139,8 @@ SYMBOLS = {
     "cmbpo_pack_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "cmbpo_pack_records": (C.c_int, [C.POINTER(cmbpo_pack_io), C.c_void_p]),
     "cmbpo_finish_paths": (C.c_int, [C.POINTER(cmbpo_gae_io), C.c_void_p]),
+    "cmbpo_normalize_scratch_bytes": (C.c_size_t, []),
+    "cmbpo_normalize_advantages": (C.c_int, [C.POINTER(cmbpo_norm_io), C.c_void_p]),
     "cmbpo_stub_policy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                     C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
 }

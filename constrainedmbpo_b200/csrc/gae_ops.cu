@@ -160,3 +160,110 @@ extern "C" int cmbpo_finish_paths(const cmbpo_gae_io* io_, void* stream_) {
   if (e != cudaSuccess) { snprintf(g_gae_err, sizeof(g_gae_err), "finish_paths: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }
   return CMBPO_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// ModelBuffer.get's advantage normalisation (modelbuffer.py:358-372): over the populated entries,
+//   adv  <- (adv - mean(adv)) / (std(adv) + EPS)      (mpi_statistics_scalar: float32 mean and population std)
+//   cadv <- cadv - mean(cadv)                         (centred, NOT rescaled)
+// plus the means of ret / cret for the diagnostics.  Three small launches (sums -> squared deviations -> apply);
+// partial sums in fp64, reduced by the last block to finish; the statistics are rounded to float32 where the
+// reference holds them in float32.  stats_dev: [adv_mean, adv_std, cadv_mean, ret_mean, cret_mean, n].
+// ---------------------------------------------------------------------------------------
+namespace cmbpo {
+
+constexpr int kNormThreads = 256;
+
+__device__ __forceinline__ double block_sum(double x, double* sh) {
+  for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = x;
+  __syncthreads();
+  double t = 0.0;
+  for (int w = 0; w < kNormThreads / 32; ++w) t += sh[w];
+  __syncthreads();
+  return t;
+}
+
+template <int PHASE>
+__global__ void __launch_bounds__(kNormThreads) k_adv_stats(cmbpo_norm_io io, double* partials, unsigned int* ticket) {
+  __shared__ double sh[kNormThreads / 32];
+  __shared__ bool s_last;
+  const long long n = io.n_elems;
+  constexpr int NV = PHASE == 1 ? 5 : 1;
+  double acc[NV];
+  for (int k = 0; k < NV; ++k) acc[k] = 0.0;
+  const float mean = PHASE == 2 ? io.stats_dev[0] : 0.f;
+  for (long long i = (long long)blockIdx.x * kNormThreads + threadIdx.x; i < n; i += (long long)gridDim.x * kNormThreads) {
+    if (!io.populated_dev[i]) continue;
+    if (PHASE == 1) {
+      acc[0] += (double)io.adv_dev[i]; acc[1] += (double)io.cadv_dev[i];
+      acc[2] += io.ret_dev ? (double)io.ret_dev[i] : 0.0; acc[3] += io.cret_dev ? (double)io.cret_dev[i] : 0.0;
+      acc[4] += 1.0;
+    } else {
+      const float d = __fsub_rn(io.adv_dev[i], mean);     // (x - mean)**2 on float32 (mpi_tools.py:85)
+      acc[0] += (double)__fmul_rn(d, d);
+    }
+  }
+  for (int k = 0; k < NV; ++k) {
+    const double t = block_sum(acc[k], sh);
+    if (threadIdx.x == 0) partials[(size_t)blockIdx.x * NV + k] = t;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double tot[NV];
+  for (int k = 0; k < NV; ++k) {
+    double x = 0.0;
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += kNormThreads) x += __ldcg(partials + (size_t)b * NV + k);
+    tot[k] = block_sum(x, sh);
+  }
+  if (threadIdx.x == 0) {
+    if (PHASE == 1) {
+      const double cnt = tot[4];
+      io.stats_dev[0] = cnt > 0 ? (float)((float)tot[0] / (float)cnt) : 0.f;   // float32 sum / float32 n (mpi_tools.py:82-83)
+      io.stats_dev[2] = cnt > 0 ? (float)((float)tot[1] / (float)cnt) : 0.f;
+      io.stats_dev[3] = cnt > 0 ? (float)(tot[2] / cnt) : 0.f;
+      io.stats_dev[4] = cnt > 0 ? (float)(tot[3] / cnt) : 0.f;
+      io.stats_dev[5] = (float)cnt;
+    } else {
+      const float cnt = io.stats_dev[5];
+      io.stats_dev[1] = cnt > 0 ? sqrtf((float)tot[0] / cnt) : 0.f;             // :86
+    }
+    *ticket = 0;
+  }
+}
+
+__global__ void __launch_bounds__(kNormThreads) k_adv_apply(cmbpo_norm_io io) {
+  const float mean = io.stats_dev[0], denom = __fadd_rn(io.stats_dev[1], 1e-8f), cmean = io.stats_dev[2];
+  if (io.stats_dev[5] <= 0.f) return;                                           // modelbuffer.py:356 `if self.size>0`
+  for (long long i = (long long)blockIdx.x * kNormThreads + threadIdx.x; i < io.n_elems; i += (long long)gridDim.x * kNormThreads) {
+    if (!io.populated_dev[i]) continue;
+    io.adv_dev[i] = __fdiv_rn(__fsub_rn(io.adv_dev[i], mean), denom);           // :361
+    io.cadv_dev[i] = __fsub_rn(io.cadv_dev[i], cmean);                          // :367
+  }
+}
+}  // namespace cmbpo
+
+extern "C" size_t cmbpo_normalize_scratch_bytes(void) { return 1024 * 5 * sizeof(double) + 64; }
+
+extern "C" int cmbpo_normalize_advantages(const cmbpo_norm_io* io_, void* stream_) {
+  if (!io_ || !io_->adv_dev || !io_->cadv_dev || !io_->populated_dev || !io_->stats_dev || !io_->scratch_dev) return CMBPO_ERR_ARG;
+  const cmbpo_norm_io io = *io_;
+  if (io.n_elems < 0) return CMBPO_ERR_ARG;
+  if (io.scratch_bytes < cmbpo_normalize_scratch_bytes()) return CMBPO_ERR_WORKSPACE;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  long long nb = (io.n_elems + kNormThreads - 1) / kNormThreads;
+  if (nb > 1024) nb = 1024;
+  if (nb < 1) nb = 1;
+  unsigned int* ticket = static_cast<unsigned int*>(io.scratch_dev);            // must be zero (first call: memset below)
+  double* partials = reinterpret_cast<double*>(static_cast<uint8_t*>(io.scratch_dev) + 64);
+  cudaMemsetAsync(ticket, 0, 64, stream);
+  k_adv_stats<1><<<(int)nb, kNormThreads, 0, stream>>>(io, partials, ticket);
+  k_adv_stats<2><<<(int)nb, kNormThreads, 0, stream>>>(io, partials, ticket);
+  k_adv_apply<<<(int)nb, kNormThreads, 0, stream>>>(io);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { snprintf(g_gae_err, sizeof(g_gae_err), "normalize_advantages: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }
+  return CMBPO_OK;
+}

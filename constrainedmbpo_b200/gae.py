@@ -60,3 +60,29 @@ def finish_paths(rew, val, cost, cval, finish_ptr, last_val, last_cval, rollout_
     if pop is not None:
         res["populated"] = pop.t()
     return res
+
+
+def normalize_advantages(adv, cadv, populated, ret=None, cret=None):
+    """``ModelBuffer.get``'s advantage trick (modelbuffer.py:356-372) in place on CUDA tensors of one common layout
+    (e.g. the ``[B, T]`` views ``finish_paths`` returns): ``adv`` standardised with the float32 mean / population std
+    over the populated entries, ``cadv`` centred only.  Returns the statistics as a CUDA float32 tensor
+    ``[adv_mean, adv_std, cadv_mean, ret_mean, cret_mean, n]``."""
+    lib = _lib.load()
+    dev = adv.device
+    base = lambda t: t if t.is_contiguous() else (t.t() if t.dim() == 2 and t.t().is_contiguous() else None)
+    ts = [base(t) for t in (adv, cadv, populated) + ((ret,) if ret is not None else ()) + ((cret,) if cret is not None else ())]
+    if any(t is None for t in ts) or len({(tuple(t.shape), t.stride()) for t in ts}) != 1:
+        raise ValueError("normalize_advantages: all arrays must share one dense layout")
+    pop = ts[2]
+    if pop.dtype != torch.uint8:
+        raise ValueError("populated must be uint8")
+    stats = torch.zeros(6, dtype=torch.float32, device=dev)
+    scratch = torch.empty(int(lib.cmbpo_normalize_scratch_bytes()), dtype=torch.uint8, device=dev)
+    io = _lib.cmbpo_norm_io()
+    io.n_elems = adv.numel()
+    io.adv_dev, io.cadv_dev, io.populated_dev = ts[0].data_ptr(), ts[1].data_ptr(), pop.data_ptr()
+    io.ret_dev = ts[3].data_ptr() if ret is not None else None
+    io.cret_dev = ts[3 + (ret is not None)].data_ptr() if cret is not None else None
+    io.stats_dev, io.scratch_dev, io.scratch_bytes = stats.data_ptr(), scratch.data_ptr(), scratch.numel()
+    _lib.check(lib.cmbpo_normalize_advantages(C.byref(io), C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
+    return stats

@@ -311,6 +311,22 @@ class ModelRollout:
         self.gae = res
         return res
 
+    def get_batch(self, model_ind=0, **finish_kw):
+        """``ModelBuffer.get`` (modelbuffer.py:348-405) for the finished rollout: ``finish()`` (GAE / iv-GAE + horizon
+        trim), the advantage normalisation over the populated entries, then the populated-mask selection in
+        [path, t] order.  'iv_gae': per-member arrays are taken from member ``model_ind`` (:376-381).  Returns
+        ``(batch dict of CUDA tensors, stats)`` with stats = [adv_mean, adv_std, cadv_mean, ret_mean, cret_mean, n]."""
+        from .gae import normalize_advantages
+        res = self.gae if self.gae is not None else self.finish(model_ind=model_ind, **finish_kw)
+        pop = res.get("populated_trimmed", self.pool["populated"])
+        stats = normalize_advantages(res["adv"], res["cadv"], pop, ret=res["ret"], cret=res["cret"])
+        mask = pop.bool()
+        iv = self.mode == "iv_gae"
+        pick = lambda v: (v[model_ind] if iv else v)[mask]
+        batch = {k: pick(self.pool[k]) for k in ("obs", "act", "val", "cval", "cost", "rew")}
+        batch.update({k: res[k][mask] for k in res if k != "populated_trimmed"})
+        return batch, stats
+
     def get(self, numpy=False):
         out = dict(self.pool)
         out.update(getattr(self, "gae", None) or {})

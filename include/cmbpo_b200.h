@@ -257,6 +257,22 @@ typedef struct cmbpo_gae_io {
 } cmbpo_gae_io;
 int cmbpo_finish_paths(const cmbpo_gae_io* io, void* stream);
 
+/* ModelBuffer.get's advantage normalisation over the populated entries (softlearning/replay_pools/modelbuffer.py:
+ * 356-372; mpi_statistics_scalar, softlearning/policies/safe_utils/mpi_tools.py:71-93): adv <- (adv - mean) / (std + 1e-8)
+ * with the float32 mean and population std, cadv <- cadv - mean(cadv) (centred, not rescaled), in place.
+ * stats_dev [6] receives adv_mean, adv_std, cadv_mean, ret_mean, cret_mean, n.  Arrays are flat (any layout, the same
+ * for all of them), n_elems entries; ret_dev / cret_dev may be NULL. */
+typedef struct cmbpo_norm_io {
+  int64_t n_elems;
+  float* adv_dev; float* cadv_dev;
+  const float* ret_dev; const float* cret_dev;
+  const uint8_t* populated_dev;
+  float* stats_dev;
+  void* scratch_dev; size_t scratch_bytes;    /* >= cmbpo_normalize_scratch_bytes() */
+} cmbpo_norm_io;
+size_t cmbpo_normalize_scratch_bytes(void);
+int cmbpo_normalize_advantages(const cmbpo_norm_io* io, void* stream);
+
 /* Synthetic benchmark policy a = tanh(obs @ P), P [obs][act] (not part of the reference; stands in
  * for policy.get_action_outs, model_sampler.py:275, in throughput runs).  n_slots > 1: obs / act are
  * [n_slots][n_rows][.] ('iv_gae' states), the live count applies to every slot. */

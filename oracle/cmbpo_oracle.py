@@ -716,3 +716,25 @@ def finish_paths(rew, val, cost, cval, finish_ptr, last_val, last_cval, mode, ga
             pop[b, :] &= np.arange(T) < horizon
     out["populated"] = pop
     return out
+
+
+def normalize_advantages(adv, cadv, populated):
+    """``ModelBuffer.get``'s advantage trick (modelbuffer.py:356-372) with ``mpi_statistics_scalar`` at world size 1
+    (safe_utils/mpi_tools.py:71-93): float32 mean / population std over the populated entries; ``adv`` standardised,
+    ``cadv`` centred only.  Returns (adv, cadv, adv_mean, adv_std, cadv_mean) without touching the inputs."""
+    adv, cadv = np.array(adv, np.float32), np.array(cadv, np.float32)
+    pop = np.asarray(populated, bool)
+    if pop.sum() == 0:
+        return adv, cadv, 0.0, 0.0, 0.0
+
+    def stats(x):
+        x = np.array(x, dtype=np.float32)
+        s, n = np.asarray([np.sum(x), len(x)], dtype=np.float32)
+        mean = s / n
+        ss = np.asarray(np.sum((x - mean) ** 2), dtype=np.float32)
+        return mean, np.sqrt(ss / n)
+    am, asd = stats(adv[pop].flatten())
+    adv[pop] = (adv[pop] - am) / (asd + GAE_EPS)
+    cm, _ = stats(cadv[pop].flatten())
+    cadv[pop] -= cm
+    return adv, cadv, am, asd, cm

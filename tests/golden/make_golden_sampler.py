@@ -185,6 +185,14 @@ def run(mode, B, T, seed, max_samples=None, dkl_lim=None, max_unc=(5.5, 5.5)):
               "adv_buf", "ret_buf", "cadv_buf", "cret_buf", "ret_var_buf", "cret_var_buf", "roll_lengths_buf",
               "croll_lengths_buf"):
         out[k] = np.array(getattr(pool, k))
+    # ModelBuffer.get (modelbuffer.py:348-405): advantage normalisation + populated-mask selection (resets the pool)
+    res, diag = pool.get()
+    names = ["obs", "act", "adv", "ret_var", "cadv", "cret_var", "ret", "cret", "logp", "val", "val_var", "cval",
+             "cval_var", "cost"]
+    for k, v in zip(names, res):
+        out[f"get_{k}"] = np.array(v)
+    for k, v in diag.items():
+        out[f"diag_{k}"] = np.array(v)
     for i, c in enumerate(env.calls):
         for k, v in c.items():
             out[f"step{i}_{k}"] = v

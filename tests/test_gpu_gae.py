@@ -75,3 +75,43 @@ def test_finish_paths_matches_oracle_on_seeded_pools(mode, E, B, T):
         # the trim compares float32 ratios with a threshold: rows whose ratio sits within float32 rounding of it may flip
         assert (got != want).any(axis=1).sum() <= 1
         assert (out["populated"].astype(bool) <= stored).all()
+
+
+@pytest.mark.parametrize("name", ["schedule", "uncertainty", "iv_gae"])
+def test_normalize_advantages_matches_reference_get(name):
+    """cmbpo_normalize_advantages on the reference's own adv / cadv buffers against what its real ModelBuffer.get
+    returned (float32 statistics: summation order differs, so a few ulp)."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    g = _golden(name)
+    pop = g["populated_mask"]
+    t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a)).to("cuda", dt)
+    adv, cadv = t(g["adv_buf"], torch.float32), t(g["cadv_buf"], torch.float32)
+    stats = cm.normalize_advantages(adv, cadv, t(pop.astype(np.uint8), torch.uint8), ret=t(g["ret_buf"], torch.float32),
+                                    cret=t(g["cret_buf"], torch.float32)).cpu().numpy()
+    a, c = adv.cpu().numpy(), cadv.cpu().numpy()
+    assert np.allclose(a[pop], g["get_adv"], rtol=1e-5, atol=1e-6) and np.allclose(c[pop], g["get_cadv"], rtol=1e-5, atol=1e-6)
+    assert np.array_equal(a[~pop], g["adv_buf"][~pop]) and np.array_equal(c[~pop], g["cadv_buf"][~pop])   # untouched
+    assert int(stats[5]) == int(g["diag_poolm_batch_size"])
+    assert np.isclose(stats[3], float(g["diag_poolm_ret_mean"]), rtol=1e-5, atol=1e-7)
+    assert np.isclose(stats[4], float(g["diag_poolm_cret_mean"]), rtol=1e-5, atol=1e-7)
+    assert abs(a[pop].mean()) < 1e-5 and abs(a[pop].std() - 1) < 1e-4
+
+
+def test_normalize_advantages_large_and_empty():
+    import torch
+    import constrainedmbpo_b200 as cm
+    rng = np.random.default_rng(2)
+    B, T = 200_000, 10
+    adv = (rng.standard_normal((B, T)) * 3 + 5).astype(np.float32)
+    cadv = (rng.standard_normal((B, T)) + 2).astype(np.float32)
+    pop = rng.random((B, T)) < 0.4
+    ra, rc, am, asd, cmn = orc.normalize_advantages(adv, cadv, pop)
+    a, c = torch.from_numpy(adv).cuda().t().contiguous().t(), torch.from_numpy(cadv).cuda().t().contiguous().t()   # time-major views
+    p = torch.from_numpy(pop.astype(np.uint8)).cuda().t().contiguous().t()
+    stats = cm.normalize_advantages(a, c, p).cpu().numpy()
+    assert np.allclose(a.cpu().numpy(), ra, rtol=2e-5, atol=2e-5) and np.allclose(c.cpu().numpy(), rc, rtol=2e-5, atol=2e-5)
+    assert np.isclose(stats[0], am, rtol=1e-5) and np.isclose(stats[1], asd, rtol=1e-5) and np.isclose(stats[2], cmn, rtol=1e-5)
+    z = torch.zeros(4, 3, device="cuda")
+    s0 = cm.normalize_advantages(z.clone(), z.clone(), torch.zeros(4, 3, dtype=torch.uint8, device="cuda")).cpu().numpy()
+    assert s0[5] == 0 and s0[1] == 0

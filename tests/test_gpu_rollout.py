@@ -504,6 +504,14 @@ def test_rollout_values_and_finish_records_match_reference_golden(name, seed):
         assert np.allclose(res[ours].cpu().numpy(), g[ref], rtol=2e-5, atol=2e-6), ours
     if iv:
         assert np.array_equal(res["populated_trimmed"].cpu().numpy().astype(bool), g["populated_mask"])
+    # ModelBuffer.get: normalised advantages + populated-mask selection, against what the reference's get() returned
+    batch, stats = ro.get_batch(model_ind=int(g["model_ind"]))
+    b = {k: v.cpu().numpy() for k, v in batch.items()}
+    assert b["obs"].shape == g["get_obs"].shape and np.array_equal(b["obs"], g["get_obs"]) and np.array_equal(b["act"], g["get_act"])
+    for ours, ref in (("adv", "get_adv"), ("cadv", "get_cadv"), ("ret", "get_ret"), ("cret", "get_cret"), ("val", "get_val"),
+                      ("cost", "get_cost")):
+        assert np.allclose(b[ours], g[ref], rtol=5e-5, atol=5e-6), ours
+    assert int(stats[5].item()) == int(g["diag_poolm_batch_size"])
 
 
 def test_rollout_with_device_critics_end_to_end():
