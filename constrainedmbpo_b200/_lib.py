@@ -117,6 +117,19 @@ class cmbpo_norm_io(C.Structure):
     ]
 
 
+MAX_FIELDS = 4
+
+
+class cmbpo_sample_io(C.Structure):
+    _fields_ = [
+        ("archive_size", C.c_int64), ("batch_size", C.c_int64), ("prob_dev", C.c_void_p), ("epoch_dev", C.c_void_p),
+        ("epoch_prob_dev", C.c_void_p), ("n_epochs", C.c_int32), ("rebuild_cdf", C.c_int32), ("cdf_dev", C.c_void_p),
+        ("uniform_dev", C.c_void_p), ("seed", C.c_uint64), ("rng_offset", C.c_uint64), ("sample_offset", C.c_int64),
+        ("field_dev", C.c_void_p * MAX_FIELDS), ("field_width", C.c_int32 * MAX_FIELDS),
+        ("out_dev", C.c_void_p * MAX_FIELDS), ("index_dev", C.c_void_p),
+    ]
+
+
 # every symbol include/cmbpo_b200.h declares: (restype, argtypes)
 SYMBOLS = {
     "cmbpo_create": (C.c_int, [C.POINTER(cmbpo_cfg), C.c_int, C.POINTER(C.c_void_p)]),
@@ -141,6 +154,7 @@ SYMBOLS = {
     "cmbpo_finish_paths": (C.c_int, [C.POINTER(cmbpo_gae_io), C.c_void_p]),
     "cmbpo_normalize_scratch_bytes": (C.c_size_t, []),
     "cmbpo_normalize_advantages": (C.c_int, [C.POINTER(cmbpo_norm_io), C.c_void_p]),
+    "cmbpo_sample_archive": (C.c_int, [C.POINTER(cmbpo_sample_io), C.c_void_p]),
     "cmbpo_stub_policy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                     C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
 }

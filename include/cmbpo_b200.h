@@ -273,6 +273,33 @@ typedef struct cmbpo_norm_io {
 size_t cmbpo_normalize_scratch_bytes(void);
 int cmbpo_normalize_advantages(const cmbpo_norm_io* io, void* stream);
 
+/* Start-state sampling from the real-data archive (softlearning/replay_pools/cpobuffer.py:531-542 boltz_dist,
+ * :559-610 distributed_batch_from_archive; mbpo/algorithms/cmbpo.py:328-333): weighted draw with replacement
+ * (np.random.choice(archive_size, batch_size, p=dist): idx = searchsorted(cumsum(p)/sum(p), u, side='right')) and the
+ * gather of the drawn rows, on an archive resident in device memory.  The row distribution is either given
+ * (prob_dev, e.g. unif_dist / disc_dist) or built from the per-row epoch id and a per-epoch table
+ * (boltz_dist: epoch_prob[e] = ep_probs[e] / rows_in_epoch[e], 0 for empty slots).  uniform_dev injects the
+ * uniforms (parity); NULL = 53-bit Philox4x32-10 doubles keyed by (sample_offset + b, rng_offset, seed). */
+#define CMBPO_MAX_FIELDS 4
+typedef struct cmbpo_sample_io {
+  int64_t archive_size;
+  int64_t batch_size;
+  const float* prob_dev;          /* [archive_size] or NULL */
+  const int32_t* epoch_dev;       /* [archive_size] epoch id per row, < 0 = empty slot (cpobuffer epoch_archive) */
+  const float* epoch_prob_dev;    /* [n_epochs] float32 like sample_p (cpobuffer.py:537-538) */
+  int32_t n_epochs;
+  int32_t rebuild_cdf;            /* 1: (re)build cdf_dev from the distribution; 0: reuse it */
+  double* cdf_dev;                /* [archive_size] workspace / cache */
+  const double* uniform_dev;      /* [batch_size] or NULL */
+  uint64_t seed, rng_offset;
+  int64_t sample_offset;          /* global index of sample 0 (shard-invariant draws) */
+  const float* field_dev[CMBPO_MAX_FIELDS];   /* archive arrays [archive_size][width] (observations, mu, log_std, ...) */
+  int32_t field_width[CMBPO_MAX_FIELDS];
+  float* out_dev[CMBPO_MAX_FIELDS];           /* [batch_size][width] */
+  int64_t* index_dev;             /* optional [batch_size] drawn row indices */
+} cmbpo_sample_io;
+int cmbpo_sample_archive(const cmbpo_sample_io* io, void* stream);
+
 /* Synthetic benchmark policy a = tanh(obs @ P), P [obs][act] (not part of the reference; stands in
  * for policy.get_action_outs, model_sampler.py:275, in throughput runs).  n_slots > 1: obs / act are
  * [n_slots][n_rows][.] ('iv_gae' states), the live count applies to every slot. */

@@ -738,3 +738,24 @@ def normalize_advantages(adv, cadv, populated):
     cm, _ = stats(cadv[pop].flatten())
     cadv[pop] -= cm
     return adv, cadv, am, asd, cm
+
+
+# --------------------------------------------------------------------------------------
+# Start-state sampling: softlearning/replay_pools/cpobuffer.py:531-542, :559-610
+# --------------------------------------------------------------------------------------
+def boltz_dist(epoch_archive, kls, alpha=1):
+    """``CPOBuffer.boltz_dist``: Boltzmann weights over epochs, spread evenly over each epoch's rows (float32)."""
+    epoch_archive = np.asarray(epoch_archive)
+    ep_probs = np.exp(alpha * np.negative(kls))
+    ep_probs /= np.sum(ep_probs)
+    sample_p = np.bincount(epoch_archive[epoch_archive >= 0]).astype(np.float32)
+    sample_p[sample_p > 0] = ep_probs / sample_p[sample_p > 0]
+    return np.where(epoch_archive >= 0, sample_p[epoch_archive], 0)
+
+
+def choice_indices(dist, uniforms):
+    """What ``np.random.choice(len(dist), size, p=dist)`` does with its uniforms (legacy RandomState.choice):
+    cdf = cumsum(float64 p), normalised by its last entry; index = searchsorted(cdf, u, side='right')."""
+    cdf = np.asarray(dist, dtype=np.float64).cumsum()
+    cdf /= cdf[-1]
+    return cdf.searchsorted(np.asarray(uniforms, np.float64), side="right")
