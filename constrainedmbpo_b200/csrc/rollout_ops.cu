@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* ce
 
 // C: stable rank among certain rows -> remaining mask -> pool write (modelbuffer.py:130-173),
 //    dkl accumulate (:415), length mask (:437, quirk Q8) and terminal mask (:453-456) -> keep flag
-__global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_t* certain, const int* blk_off,
+__global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, uint8_t* certain, const int* blk_off,
                                                 uint8_t* keep, int* blk_keep_cnt) {
   RolloutState* st = static_cast<RolloutState*>(io.state_dev);
   const int n = st->n_alive;
@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
     io.dkl_accum_dev[pid] += (double)static_cast<const float*>(io.dkl_path_dev)[i];
   }
   const int k = (remaining && !term && !path_end) ? 1 : 0;
-  if (i < n) keep[i] = (uint8_t)k;
+  if (i < n) { keep[i] = (uint8_t)k; certain[i] = remaining ? 1 : 0; }   // certain[] now = 'stored' flags (k_store_payload)
   if (io.finish_ptr_dev && i < n && !k) {
     // this path ends now: what ModelSampler._finish_paths hands to finish_path_multiple (model_sampler.py:497-548)
     //  - cut before the store (too uncertain / max_samples): column ptr, bootstrap V(s_t), VC(s_t)   (:336, append both)
@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
   const float inv_od = 1.0f / (float)OD, inv_ad = AD > 0 ? 1.0f / (float)AD : 0.f;
   const int row_base = blockIdx.x * kRB;
   const int n_here = min(kRB, n - row_base);
-  for (int e = 0; e < E; ++e) {
+  for (int e = 0; e < (E == 1 ? 1 : 0); ++e) {   // member-leading pools: payload moved by k_store_payload, one grid row per member
     const float* so = static_cast<const float*>(io.cur_obs_dev) + (e * cap + row_base) * OD;
     const float* sn = static_cast<const float*>(io.next_obs_dev) + (e * cap + row_base) * OD;
     float* po = static_cast<float*>(io.pool_obs_dev) + e * cap * T * OD;
@@ -242,6 +242,51 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, const uint8_
     }
     st->n_alive = do_store ? total : 0;
     st->finished = (st->n_alive == 0) ? 1 : 0;
+  }
+}
+
+// 'iv_gae' payload copy: grid (row blocks, members), so the E member blocks of obs / next_obs / act move in parallel
+// instead of in a per-block loop (k_store at 125k rows x 7 members: 520 us -> see profiles/).  Runs after k_store:
+// `stored` are the flags it published, the column is the pre-increment ptr.
+__global__ void __launch_bounds__(kRB) k_store_payload(cmbpo_rollout_io io, const uint8_t* stored, const int* n_before_dev) {
+  const RolloutState* st = static_cast<const RolloutState*>(io.state_dev);
+  if (!st->tmp_do_store) return;
+  const int n = *n_before_dev;
+  const int ptr = st->ptr - 1;                     // k_store's epilogue already advanced it
+  const int T = io.max_path_length, OD = io.obs_dim, AD = io.act_dim;
+  const size_t cap = (size_t)io.n_paths;
+  const int e = blockIdx.y;
+  const int row_base = blockIdx.x * kRB;
+  const int n_here = min(kRB, n - row_base);
+  if (n_here <= 0) return;
+  __shared__ int s_pid[kRB];
+  __shared__ uint8_t s_rem[kRB];
+  const int i = row_base + threadIdx.x;
+  s_pid[threadIdx.x] = (i < n) ? static_cast<const int*>(io.path_id_dev)[i] : 0;
+  s_rem[threadIdx.x] = (i < n) ? stored[i] : 0;
+  __syncthreads();
+  const float inv_od = 1.0f / (float)OD, inv_ad = AD > 0 ? 1.0f / (float)AD : 0.f;
+  const float* so = static_cast<const float*>(io.cur_obs_dev) + (e * cap + row_base) * OD;
+  const float* sn = static_cast<const float*>(io.next_obs_dev) + (e * cap + row_base) * OD;
+  float* po = static_cast<float*>(io.pool_obs_dev) + e * cap * T * OD;
+  float* pn = static_cast<float*>(io.pool_next_obs_dev) + e * cap * T * OD;
+#pragma unroll 8
+  for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {
+    const int r = fast_div(idx, inv_od), d = idx - r * OD;
+    if (s_rem[r]) {
+      const size_t o = ((size_t)ptr * cap + s_pid[r]) * OD + d;
+      po[o] = so[idx];
+      pn[o] = sn[idx];
+    }
+  }
+  if (AD > 0) {
+    const float* sa = static_cast<const float*>(io.act_dev) + (e * cap + row_base) * AD;
+    float* pa = static_cast<float*>(io.pool_act_dev) + e * cap * T * AD;
+#pragma unroll 4
+    for (int idx = threadIdx.x; idx < n_here * AD; idx += kRB) {
+      const int r = fast_div(idx, inv_ad), d = idx - r * AD;
+      if (s_rem[r]) pa[((size_t)ptr * cap + s_pid[r]) * AD + d] = sa[idx];
+    }
   }
 }
 
@@ -298,25 +343,24 @@ __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const 
   const int dst = blk_off[blockIdx.x] + block_exclusive_scan(k, nullptr);
   __shared__ int s_dst[kRB];
   s_dst[threadIdx.x] = k ? dst : -1;
-  if (k) static_cast<int*>(io.new_path_id_dev)[dst] = static_cast<const int*>(io.path_id_dev)[i];
-  if (k && io.new_val_dev) {   // V(s_t+1) of a survivor is V(s_t) of its next step: the critics run once per state
-    const int Ev = (io.mode == 2 && io.n_members > 1) ? io.n_members : 1;
-    for (int e = 0; e < Ev; ++e) {
-      io.new_val_dev[e * (size_t)io.n_paths + dst] = io.val_next_dev[e * (size_t)io.n_paths + i];
-      io.new_cval_dev[e * (size_t)io.n_paths + dst] = io.cval_next_dev[e * (size_t)io.n_paths + i];
-    }
+  const int E = (io.mode == 2 && io.n_members > 1) ? io.n_members : 1;
+  const size_t cap = (size_t)io.n_paths;
+  const int e0 = blockIdx.y;                        // grid.y = members: every member's block moves in parallel
+  if (k && e0 == 0) static_cast<int*>(io.new_path_id_dev)[dst] = static_cast<const int*>(io.path_id_dev)[i];
+  if (k && io.new_val_dev && e0 < E) {   // V(s_t+1) of a survivor is V(s_t) of its next step: the critics run once per state
+    io.new_val_dev[e0 * cap + dst] = io.val_next_dev[e0 * cap + i];
+    io.new_cval_dev[e0 * cap + dst] = io.cval_next_dev[e0 * cap + i];
   }
   __syncthreads();
   const int OD = io.obs_dim;
   const float inv_od = 1.0f / (float)OD;
   const int row_base = blockIdx.x * kRB;
   const int n_here = min(kRB, n_before - row_base);
-  const int E = (io.mode == 2 && io.n_members > 1) ? io.n_members : 1;
-  const size_t cap = (size_t)io.n_paths;
-  for (int e = 0; e < E; ++e) {   // iv_gae: every member's own state follows (model_sampler.py:444,:463-464)
+  {   // iv_gae: every member's own state follows (model_sampler.py:444,:463-464)
+    const int e = e0;
     const float* src = static_cast<const float*>(io.next_obs_dev) + (e * cap + row_base) * OD;
     float* dstp = static_cast<float*>(io.new_obs_dev) + e * cap * OD;
-#pragma unroll 4
+#pragma unroll 8
     for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {   // flat element loop, see k_store
       const int r = fast_div(idx, inv_od), d = idx - r * OD;
       const int d0 = s_dst[r];
@@ -343,7 +387,8 @@ extern "C" int cmbpo_rollout_advance(const cmbpo_rollout_io* io_, void* stream_)
   int* snap = blk_b + nb;   // last word of blk_b's slack
   k_decide<<<nb, kRB, 0, stream>>>(io, certain, blk_a, snap, io.alive_hist_dev ? io.alive_hist_dev + io.step_index : nullptr);
   k_store<<<nb, kRB, 0, stream>>>(io, certain, blk_a, keep, blk_b);
-  k_compact_dev<<<nb, kRB, 0, stream>>>(io, keep, blk_b, snap);
+  if (io.mode == 2 && io.n_members > 1) k_store_payload<<<dim3(nb, io.n_members), kRB, 0, stream>>>(io, certain, snap);
+  k_compact_dev<<<dim3(nb, (io.mode == 2 && io.n_members > 1) ? io.n_members : 1), kRB, 0, stream>>>(io, keep, blk_b, snap);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(g_roll_err, sizeof(g_roll_err), "rollout_advance: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }
   return CMBPO_OK;
