@@ -554,3 +554,36 @@ def test_rollout_with_device_critics_end_to_end():
                            got["last_cval"], "schedule", 0.99, 0.95, 0.97, 0.9)
     for k in ("adv", "ret", "cadv", "cret"):
         assert np.allclose(res[k].cpu().numpy(), ref[k], rtol=2e-5, atol=2e-6), k
+
+
+def test_host_drain_pipeline_delivers_every_rollout():
+    """HostDrain (pack kernel + one pinned D2H per rollout on a side stream, one rollout behind): each rollout's records
+    arrive on the host complete and in [path, t] order, also when consecutive rollouts differ in size."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    from constrainedmbpo_b200 import sharding
+    env, T = "antsafe", 8
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True, seed=4)
+    pol = cm.StubPolicy(29, 8)
+    B = 3000
+    ro = cm.ModelRollout(fe, T, rollout_mode="uncertainty", dkl_lim=3e-5)
+    drain = sharding.HostDrain(ro)
+    want = []
+    got = []
+    for k in range(4):
+        obs, _ = make_inputs(env, B, seed=20 + k)
+        ro.reset(obs)
+        ro.run(pol)
+        rec, coords = sharding.pack_records(ro.pool, 0)
+        want.append(torch.cat([rec, coords.to(torch.int32).view(torch.float32)], dim=1).cpu())
+        drain.launch()
+        if k > 0:
+            h, cnt = drain.last                      # rollout k-1: its copy was just enqueued on the side stream
+            drain._side.synchronize()
+            got.append(h.clone())
+    h, cnt = drain.wait()
+    got.append(h.clone())
+    assert len({w.shape[0] for w in want}) > 1       # the rollouts really differ in size
+    for w, g_ in zip(want, got):
+        assert w.shape == g_.shape and torch.equal(w.view(torch.int32), g_.view(torch.int32))
