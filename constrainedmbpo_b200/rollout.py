@@ -253,10 +253,20 @@ class ModelRollout:
         self.reset(start_obs)
         self.run(policy)
         torch.cuda.synchronize(self.device)
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            self.reset(start_obs)
-            self.run(policy)
+        # No garbage collection while the stream is capturing: collecting an unreferenced model (BNN.__del__ ->
+        # cmbpo_destroy -> cudaFree) from the cyclic GC in the middle of the capture would invalidate it.
+        import gc
+        gc.collect()
+        was_enabled = gc.isenabled()
+        gc.disable()
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.reset(start_obs)
+                self.run(policy)
+        finally:
+            if was_enabled:
+                gc.enable()
         self._graph = g
         return g
 

@@ -63,7 +63,10 @@ class _Model:
         self.last = {}
 
     def predict(self, inputs, factored=True, inc_var=True):
-        m, v = orc.predict(self.p, inputs, factored=factored, inc_var=inc_var)
+        out = orc.predict(self.p, inputs, factored=factored, inc_var=inc_var)
+        if not inc_var:                       # the cost head: a single array (bnn.py:744-748, :772-776)
+            return np.array(out)
+        m, v = out
         self.last["means"], self.last["vars"] = np.array(m), np.array(v)
         return np.array(m), np.array(v)
 
@@ -77,7 +80,8 @@ def main():
     FakeEnv = load_fake_env()
     out = {}
     for tag, env, B, ndim, cost in (("antsafe2d", "antsafe", 96, 2, True), ("humanoidsafe3d", "humanoidsafe", 64, 3, True),
-                                    ("hopper2d", "hopper", 80, 2, False), ("halfcheetahsafe2d", "halfcheetahsafe", 50, 2, True)):
+                                    ("hopper2d", "hopper", 80, 2, False), ("halfcheetahsafe2d", "halfcheetahsafe", 50, 2, True),
+                                    ("ant2d_costnn", "ant", 72, 2, True), ("humanoid3d_costnn", "humanoid", 40, 3, True)):
         obs_dim, act_dim = ENV_DIMS[env]
         p = make_params(env, (24, 24), parity_scalers=True, bias=True, dtype=np.float32)
         static = _load(f"mbpo.static.{env}", f"mbpo/static/{env}.py").StaticFns
@@ -87,6 +91,12 @@ def main():
         fe.static_c = hasattr(static, "cost_f")
         fe.cares_about_cost = cost
         fe._model = _Model(p, np.random.default_rng(31))
+        if cost and not fe.static_c:
+            # the learned cost head (fake_env.py:76-94, :191-196): MSE ensemble on concat(obs, act, next_obs), 64x64
+            pc = orc.init_ensemble(np.random.default_rng(17), 2 * obs_dim + act_dim, 1, (64, 64), 7, probabilistic=False,
+                                   use_scaler_in=False, use_scaler_out=False, elites=list(range(5)), dtype=np.float32)
+            fe._cost_model = _Model(pc, np.random.default_rng(32))
+            fe.cost_m_loss = "MSE"
         obs, act = make_inputs(env, B, seed=13, E=7 if ndim == 3 else None)
         np.random.seed(77)                       # forward_shuffle draws np.random.permutation(E) (fake_env.py:314)
         next_obs, rew, term, info = fe.step(obs, act)

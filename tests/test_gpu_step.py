@@ -245,7 +245,8 @@ def test_step_rejects_1d_like_reference():
 
 
 @pytest.mark.parametrize("tag,env", [("antsafe2d", "antsafe"), ("humanoidsafe3d", "humanoidsafe"), ("hopper2d", "hopper"),
-                                     ("halfcheetahsafe2d", "halfcheetahsafe")])
+                                     ("halfcheetahsafe2d", "halfcheetahsafe"), ("ant2d_costnn", "ant"),
+                                     ("humanoid3d_costnn", "humanoid")])
 def test_step_against_reference_fake_env_golden(tag, env):
     """The CUDA FakeEnv.step against what the reference's REAL FakeEnv.step returned (tests/golden/fakeenv_step.npz:
     real fake_env.py + real StaticFns, model outputs from the fp32 restatement of the TF graph) for the same ensemble,
@@ -257,6 +258,12 @@ def test_step_against_reference_fake_env_golden(tag, env):
     cost = bool(g["cares_about_cost"])
     fe = build_cuda_env(p, env, hidden, cares_about_cost=cost)
     three_d = g["obs"].ndim == 3
+    costnn = tag.endswith("costnn")
+    if costnn:   # the learned cost head of the fixture (fake_env.py:76-94): same seeded 64x64 MSE ensemble
+        od, ad = g["obs"].shape[-1], g["act"].shape[-1]
+        pc = orc.init_ensemble(np.random.default_rng(17), 2 * od + ad, 1, (64, 64), 7, probabilistic=False,
+                               use_scaler_in=False, use_scaler_out=False, elites=list(range(5)), dtype=np.float32)
+        fe._cost_model.load_state(pc.weights, pc.biases, elites=pc.elites)
     no, rw, tm, info = fe.step(g["obs"], g["act"], elite_idx=None if three_d else g["idx"], perm=g["perm"] if three_d else None)
     s = out_scale(p)
     assert no.shape == g["next_obs"].shape and rw.shape == g["rew"].shape and tm.shape == g["term"].shape
@@ -270,7 +277,10 @@ def test_step_against_reference_fake_env_golden(tag, env):
     near = near_threshold_rows(env, g["next_obs"], tol)
     mism = (tm != g["term"])[..., 0]
     assert not (mism & ~near).any(), f"{int((mism & ~near).sum())} termination mismatches away from thresholds"
-    if cost:
+    if cost and costnn:    # continuous output of the cost ensemble's mean (fake_env.py:196), unit scale
+        assert info["cost"].shape == g["cost"].shape
+        assert (np.abs(info["cost"] - g["cost"]) <= 1e-2 * np.abs(g["cost"]) + 2e-2).all()
+    elif cost:
         mc = (info["cost"] != g["cost"])[..., 0]
         assert not (mc & ~near).any()
     rel = np.abs(info["ensemble_dkl_path"] - g["dkl_path"]) / (np.abs(g["dkl_path"]) + 1e-6)
