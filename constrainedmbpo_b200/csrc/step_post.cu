@@ -46,7 +46,6 @@ __device__ __forceinline__ float clip_kl_exact(float x) {
   const float r = fminf(fmaxf(x, 0.f), 1e10f);
   return (x != x) ? x : r;
 }
-__device__ __forceinline__ float clip_kl_fast(float x) { return fminf(fmaxf(x, 0.f), 1e10f); }
 
 // static termination / cost functions, mbpo/static/<env>.py.  `x` = next_obs features the
 // functions look at; comparisons are done in fp32 exactly as NumPy does on fp32 arrays.
@@ -111,49 +110,39 @@ __device__ __forceinline__ float pick(const float (&m)[E], int idx) {
   return r;
 }
 
-// One column d of one row: all-pairs KL (utils.py:30-57, quirk Q5), var_E(mean) (fake_env.py:160)
-template <int E, bool EXACT>
-__device__ __forceinline__ void column_stats(const float (&m)[E], const float (&lv)[E], float (&v)[E],
-                                             float& kl_out, float& epv_out) {
-  float ls[E], inv[E];
+__device__ __forceinline__ float rcp_approx(float x) {   // one MUFU.RCP, no range fix-up branch
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// One column d of one row, reference order of operations: all-pairs KL with the per-pair clip to [0, 1e10]
+// (utils.py:14-57, quirk Q5), var_E(mean) (fake_env.py:160).  Taken by columns with non-finite / extreme
+// heads and by columns where a pair could reach the upper clip; everything else goes through
+// column_stats_fast below.
+template <int E>
+__device__ __noinline__ void column_stats_exact(const float (&m)[E], const float (&lv)[E], float (&v)[E],
+                                                float& kl_out, float& epv_out) {
+  float ls[E], vk[E];
 #pragma unroll
   for (int e = 0; e < E; ++e) {
     v[e] = __expf(lv[e]);                       // bnn.py:898
-    if (EXACT) {
-      // log_std = clip(log(sqrt(var)), -100, 1e8); var is recomputed from it (utils.py:20,48-49)
-      const float l = logf(sqrtf(v[e]));
-      ls[e] = fminf(fmaxf(l, -100.f), 1e8f);
-      if (l != l) ls[e] = l;
-    } else {
-      ls[e] = 0.5f * lv[e];
-    }
-  }
-  float vk[E];
-#pragma unroll
-  for (int e = 0; e < E; ++e) {
-    vk[e] = EXACT ? expf(2.0f * ls[e]) : v[e];
-    inv[e] = EXACT ? 1.0f / (vk[e] + 1e-10f) : __frcp_rn(vk[e] + 1e-10f);
+    // log_std = clip(log(sqrt(var)), -100, 1e8); var is recomputed from it (utils.py:20,48-49)
+    const float l = logf(sqrtf(v[e]));
+    ls[e] = fminf(fmaxf(l, -100.f), 1e8f);
+    if (l != l) ls[e] = l;
+    vk[e] = expf(2.0f * ls[e]);
   }
   float kl = 0.f;
 #pragma unroll
   for (int i = 0; i < E; ++i) {
 #pragma unroll
     for (int j = 0; j < E; ++j) {
-      if (!EXACT && j <= i) continue;
       const float d = m[j] - m[i];
-      const float d2 = d * d;
-      if (EXACT) {
-        const float pre = 0.5f * ((d2 + vk[i]) / (vk[j] + 1e-10f) - 1.0f) + ls[j] - ls[i];
-        kl += clip_kl_exact(pre);
-      } else {
-        const float c = ls[j] - ls[i];
-        const float kij = fmaf(0.5f * (d2 + vk[i]), inv[j], c - 0.5f);
-        const float kji = fmaf(0.5f * (d2 + vk[j]), inv[i], -c - 0.5f);
-        kl += clip_kl_fast(kij) + clip_kl_fast(kji);
-      }
+      const float pre = 0.5f * ((d * d + vk[i]) / (vk[j] + 1e-10f) - 1.0f) + ls[j] - ls[i];
+      kl += clip_kl_exact(pre);
     }
   }
-  // i == j terms are exactly clip(<=0) = 0 on the fast path (finite, normal variances)
   kl_out = kl / ((float)(E * (E - 1)) + 1e-10f);
   float mean = 0.f;
 #pragma unroll
@@ -163,6 +152,63 @@ __device__ __forceinline__ void column_stats(const float (&m)[E], const float (&
 #pragma unroll
   for (int e = 0; e < E; ++e) { const float t = m[e] - mean; s2 = fmaf(t, t, s2); }
   epv_out = s2 * (1.0f / E);
+}
+
+// Call site of the exact path: it works on copies, so only this (rare) branch puts the arrays on the stack.
+template <int E>
+__device__ __forceinline__ void column_stats_rare(const float (&m)[E], const float (&lv)[E], float (&v)[E],
+                                                  float& kl_out, float& epv_out) {
+  float mc[E], lc[E], vc[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) { mc[e] = m[e]; lc[e] = lv[e]; }
+  column_stats_exact<E>(mc, lc, vc, kl_out, epv_out);
+#pragma unroll
+  for (int e = 0; e < E; ++e) v[e] = vc[e];
+}
+
+// The same statistics in O(E) for finite, moderate heads.  Summed over all ordered pairs i != j the
+// log-std terms of KL(i||j) cancel, and with dl_i = mu_i - mean, S_c = sum dl_i^2, S_v = sum var_i:
+//     sum_{i != j} (var_i + (mu_i - mu_j)^2) = S_v - var_j + S_c + E * dl_j^2          for each j
+// so  sum_{i != j} KL(i||j) = sum_j (S_v - var_j + S_c + E dl_j^2) / (2 (var_j + EPS)) - E (E - 1) / 2.
+// The differences are taken around the mean, so nearly identical members do not cancel catastrophically
+// (same fp32 error class as the pairwise form, whose terms are "ratio/2 - 1/2" as well).  The per-pair clip
+// of the reference cannot be applied here: the lower one only ever removes rounding noise (KL >= 0), and the
+// function returns false -- the caller then takes column_stats_exact -- when some pair could come within a
+// factor 10 of the upper one.
+template <int E>
+__device__ __forceinline__ bool column_stats_fast(const float (&m)[E], const float (&lv)[E], float (&v)[E],
+                                                  float& kl_out, float& epv_out) {
+  float inv[E], dl[E];
+  float sv = 0.f, mean = 0.f;
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    v[e] = __expf(lv[e]);                       // bnn.py:898
+    inv[e] = rcp_approx(v[e] + 1e-10f);
+    sv += v[e];
+    mean += m[e];
+  }
+  mean *= (1.0f / E);
+  float s2 = 0.f, d2max = 0.f, vmax = v[0], invmax = inv[0];
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    dl[e] = m[e] - mean;
+    const float q = dl[e] * dl[e];
+    s2 += q;
+    d2max = fmaxf(d2max, q);
+    vmax = fmaxf(vmax, v[e]);
+    invmax = fmaxf(invmax, inv[e]);
+  }
+  const float base = sv + s2;
+  float acc = -0.5f * (float)(E * (E - 1));
+#pragma unroll
+  for (int j = 0; j < E; ++j) {
+    const float t = fmaf((float)E * dl[j], dl[j], base - v[j]);
+    acc = fmaf(0.5f * inv[j], t, acc);
+  }
+  kl_out = fmaxf(acc, 0.f) * (1.0f / ((float)(E * (E - 1)) + 1e-10f));   // within 1 ulp of the division
+  epv_out = s2 * (1.0f / E);
+  // largest possible pair term: ((mu_i - mu_j)^2 + var_i) / (2 var_j) <= (4 d2max + vmax) * invmax / 2
+  return (4.f * d2max + vmax) * invmax < 1e9f;
 }
 
 // kPostParts warps share a block of kPostRows rows: warp `part` handles output columns d = part,
@@ -242,6 +288,9 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
   for (long long row0 = (long long)blockIdx.x * kPostRows; row0 < n_rows; row0 += (long long)gridDim.x * kPostRows) {
     const long long g = row0 + r;
     const bool live = g < n_rows;
+    // this row's entries of the tile-major head scratch (cmbpo_internal.cuh head_index): member e, column j at
+    // hrow[(e * 2D + j) * kTileRows] -- 32-bit offsets, E * 2D * 128 elements per 128-row block
+    const float* hrow = p.heads + (size_t)(g >> 7) * (size_t)(E * 2 * D * kTileRows) + (size_t)(g & (kTileRows - 1));
     const int rows_here = (int)min((long long)kPostRows, n_rows - row0);
     int eidx = 0;
     if (!p.per_slot && live) {
@@ -272,9 +321,8 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
           const float o = (d < OD) ? tile[r * OD + d] : 0.f;
 #pragma unroll
           for (int e = 0; e < E; ++e) {
-            const float* hm = p.heads + head_index(g, e, d, E, 2 * D);
-            m[e] = hm[0];
-            lv[e] = hm[(size_t)D * kTileRows];
+            m[e] = hrow[(e * 2 * D + d) * kTileRows];
+            lv[e] = hrow[(e * 2 * D + D + d) * kTileRows];
           }
           if (d < OD) {
             if (p.per_slot) {
@@ -305,8 +353,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
 #pragma unroll
           for (int e = 0; e < E; ++e) weird = weird || !(fabsf(m[e]) < 1e18f);
           float kl, epv;
-          if (weird) column_stats<E, true>(m, lv, v, kl, epv);
-          else column_stats<E, false>(m, lv, v, kl, epv);
+          if (weird || !column_stats_fast<E>(m, lv, v, kl, epv)) column_stats_rare<E>(m, lv, v, kl, epv);
           if (so == 0) {
             kl_row += kl; epv_row += epv;
             float sv = 0.f;
@@ -401,6 +448,9 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const Step
   for (long long row0 = (long long)blockIdx.x * kPostRows; row0 < n_rows; row0 += (long long)gridDim.x * kPostRows) {
     const long long g = row0 + r;
     const bool live = g < n_rows;
+    // this row's entries of the tile-major head scratch (cmbpo_internal.cuh head_index): member e, column j at
+    // hrow[(e * 2D + j) * kTileRows] -- 32-bit offsets, E * 2D * 128 elements per 128-row block
+    const float* hrow = p.heads + (size_t)(g >> 7) * (size_t)(E * 2 * D * kTileRows) + (size_t)(g & (kTileRows - 1));
     const int rows_here = (int)min((long long)kPostRows, n_rows - row0);
     __syncthreads();
 #pragma unroll
@@ -416,9 +466,8 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const Step
         float m[E], lv[E], v[E];
 #pragma unroll
         for (int e = 0; e < E; ++e) {
-          const float* hm = p.heads + head_index(g, e, d, E, 2 * D);
-          m[e] = hm[0];
-          lv[e] = hm[(size_t)D * kTileRows];
+          m[e] = hrow[(e * 2 * D + d) * kTileRows];
+          lv[e] = hrow[(e * 2 * D + D + d) * kTileRows];
         }
         if (d < OD) {
 #pragma unroll
@@ -441,8 +490,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const Step
 #pragma unroll
         for (int e = 0; e < E; ++e) weird = weird || !(fabsf(m[e]) < 1e18f);
         float kl, epv;
-        if (weird) column_stats<E, true>(m, lv, v, kl, epv);
-        else column_stats<E, false>(m, lv, v, kl, epv);
+        if (weird || !column_stats_fast<E>(m, lv, v, kl, epv)) column_stats_rare<E>(m, lv, v, kl, epv);
         kl_row += kl; epv_row += epv;
         float sv = 0.f;
 #pragma unroll
