@@ -274,6 +274,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
   __shared__ float tile[kPostRows * 64 + 32];  // obs in / next_obs out staging (obs_dim <= 64)
   __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
   __shared__ float s_rew[kPostRows];
+  __shared__ int s_eidx[kPostRows];
   __shared__ uint8_t s_flags[kPostParts][kPostRows];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int r = lane, part = warp;
@@ -293,7 +294,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
     const float* hrow = p.heads + (size_t)(g >> 7) * (size_t)(E * 2 * D * kTileRows) + (size_t)(g & (kTileRows - 1));
     const int rows_here = (int)min((long long)kPostRows, n_rows - row0);
     int eidx = 0;
-    if (!p.per_slot && live) {
+    if (!p.per_slot && live && part == 0) {   // one warp draws the members; the others pick them up from smem below
       if (p.elite_idx) {
         eidx = p.elite_idx[g];
       } else {  // random elite per row (bnn.py:437-439), counter-based so sharding cannot change it
@@ -303,6 +304,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
                       (uint32_t)p.seed, (uint32_t)(p.seed >> 32), rnd);
         eidx = p.elites[__umulhi(rnd[0], (uint32_t)p.n_elites)];
       }
+      s_eidx[r] = eidx;
     }
     float kl_row = 0.f, epv_row = 0.f;
     // ---- pass over output slots (1 in 2-D mode; E in 3-D mode where every member keeps its own row)
@@ -314,6 +316,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
         for (int i = tid; i < rows_here * OD; i += kPostThreads) tile[i] = src[i];
       }
       __syncthreads();
+      if (!p.per_slot && live) eidx = s_eidx[r];
       bool finite_part = true, lt100_part = true;
       if (live) {
         for (int d = part; d < D; d += kPostParts) {
