@@ -127,6 +127,30 @@ def test_step_nonfinite_rows():
     assert np.isnan(info["ensemble_dkl_path"][3]) == np.isnan(rinfo["ensemble_dkl_path"][3])
 
 
+def test_step_kl_pair_clip_takes_the_exact_path():
+    """The post kernel sums the pair KLs in O(E) form, which cannot apply the reference's per-pair clip to
+    [0, 1e10] (utils.py:24); columns where a pair can reach the clip must fall back to the exact E x E path.
+    One column gets log-variances of about +26 (member 0) and -64 (member 1): finite, inside the kernel's
+    'moderate' range, and several pairs clip -- the unclipped sum would be ~1e21 instead of ~7e10."""
+    env = "antsafe"
+    p = make_params(env, HIDDEN)
+    D = ENV_DIMS[env][0] + 1
+    p.biases[-1][0, ..., D + 4] += 30
+    p.biases[-1][1, ..., D + 4] -= 60
+    obs, act = make_inputs(env, 300)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True)
+    idx = np.random.default_rng(2).choice(p.elites, size=300)
+    no, rw, tm, info = fe.step(obs, act, elite_idx=idx)
+    with np.errstate(all="ignore"):
+        rno, rrw, rtm, rinfo = orc.fake_env_step(p, env, obs.astype(np.float64), act.astype(np.float64),
+                                                 elite_idx=idx, cares_about_cost=True)
+    ref = rinfo["ensemble_dkl_path"]
+    assert ref.min() > 1e7   # the clipped pairs dominate
+    rel = np.abs(info["ensemble_dkl_path"] - ref) / ref
+    assert rel.max() < 2e-2, rel.max()
+    assert_means_close(no, rno, out_scale(p)[:-1])
+
+
 def test_step_3d_with_injected_permutation_quirk_q4():
     """3-D inputs (iv_gae rollouts): forward shuffle, and the 'inverse' shuffle that re-applies the same
     permutation (fake_env.py:309-324): slot j holds f_{p[j]}(x[p[p[j]]])."""
