@@ -236,7 +236,7 @@ __device__ __forceinline__ void finish_scalars(const StepParams& p, const float 
   __syncthreads();
   if (tid < 4) {
     float x = 0.f;
-    for (int w = 0; w < kPostParts; ++w) x += red[tid][w];
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) x += red[tid][w];
     p.partials[(size_t)blockIdx.x * 4 + tid] = x;
   }
   // ---- the last block to finish sums the partials in block order (deterministic) -> 4 means
@@ -249,7 +249,7 @@ __device__ __forceinline__ void finish_scalars(const StepParams& p, const float 
   if (!s_last) return;
   __threadfence();
   double s[4] = {0, 0, 0, 0};
-  for (int b = tid; b < (int)gridDim.x; b += kPostThreads)
+  for (int b = tid; b < (int)gridDim.x; b += (int)blockDim.x)
     for (int k = 0; k < 4; ++k) s[k] += (double)__ldcg(p.partials + (size_t)b * 4 + k);
   for (int k = 0; k < 4; ++k) {
     double x = s[k];
@@ -259,7 +259,7 @@ __device__ __forceinline__ void finish_scalars(const StepParams& p, const float 
   __syncthreads();
   if (tid < 4) {
     double x = 0;
-    for (int w = 0; w < kPostParts; ++w) x += sh[tid][w];
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) x += sh[tid][w];
     const double n = (double)n_rows;
     double denom = n;                                        // dkl_mean
     if (tid == 1) denom = n * (double)E * (double)p.D;       // ensemble_mean_var over [E,B,D]
@@ -278,6 +278,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
   __shared__ uint8_t s_flags[kPostParts][kPostRows];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int r = lane, part = warp;
+  const int n_parts = (int)(blockDim.x >> 5), n_threads = (int)blockDim.x;   // launch_step_post_EO sizes the block to D
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
   // 3-D mode: member slot e of obs/act/next_obs/rew/term/cost starts at row e * capacity (the array shapes
   // stay at capacity while the live row count shrinks during an 'iv_gae' rollout)
@@ -313,13 +314,13 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
       __syncthreads();
       {
         const float* src = p.obs + (p.per_slot ? (size_t)so * slot_rows * OD : 0) + (size_t)row0 * OD;
-        for (int i = tid; i < rows_here * OD; i += kPostThreads) tile[i] = src[i];
+        for (int i = tid; i < rows_here * OD; i += n_threads) tile[i] = src[i];
       }
       __syncthreads();
       if (!p.per_slot && live) eidx = s_eidx[r];
       bool finite_part = true, lt100_part = true;
       if (live) {
-        for (int d = part; d < D; d += kPostParts) {
+        for (int d = part; d < D; d += n_parts) {
           float m[E], lv[E], v[E];
           const float o = (d < OD) ? tile[r * OD + d] : 0.f;
 #pragma unroll
@@ -388,7 +389,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
         RowFeatures f;
         uint8_t fl = 3;
 #pragma unroll
-        for (int q = 0; q < kPostParts; ++q) fl &= s_flags[q][r];
+        for (int q = 0; q < n_parts; ++q) fl &= s_flags[q][r];
         f.finite_all = (fl & 1) != 0;
         f.lt100_from1 = (fl & 2) != 0;
         const float* xr = tile + r * OD;
@@ -408,7 +409,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
       }
       {
         float* dst = p.next_obs + (p.per_slot ? (size_t)so * slot_rows * OD : 0) + (size_t)row0 * OD;
-        for (int i = tid; i < rows_here * OD; i += kPostThreads) dst[i] = tile[i];
+        for (int i = tid; i < rows_here * OD; i += n_threads) dst[i] = tile[i];
       }
     }
     s_kl[part][r] = kl_row;
@@ -417,7 +418,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
     if (live && part == 0) {
       float ks = 0.f, es = 0.f;
 #pragma unroll
-      for (int q = 0; q < kPostParts; ++q) { ks += s_kl[q][r]; es += s_epv[q][r]; }
+      for (int q = 0; q < n_parts; ++q) { ks += s_kl[q][r]; es += s_epv[q][r]; }
       const float dkl = ks / (float)D;  // np.mean(average_dkl(...), axis=-1), fake_env.py:158
       p.dkl_path[g] = dkl;
       if (p.ep_var_mean) p.ep_var_mean[g] = es / (float)D;
@@ -648,7 +649,12 @@ static cudaError_t launch_step_post_EO(const StepParams& p, int n_blocks, cudaSt
     step_post3d_kernel<E, OPT><<<n_blocks, kPostThreads, smem, stream>>>(p);
     return cudaGetLastError();
   }
-  step_post_kernel<E, OPT><<<n_blocks, kPostThreads, 0, stream>>>(p);
+  // 16 column parts per block unless that leaves the last round mostly idle: D = 18 (HalfCheetah) on 16 warps is 2
+  // rounds at 56 % use -> 9 warps x 2 columns (rollout +4 %, same-box A/B).  D = 30 stays at 16: 15 x 2 measured 2 %
+  // slower (fewer threads in flight per SM outweigh the two idle warps).
+  const int rounds = (p.D + kPostParts - 1) / kPostParts;
+  const int parts = (p.D * 5 >= rounds * kPostParts * 4) ? kPostParts : (p.D + rounds - 1) / rounds;
+  step_post_kernel<E, OPT><<<n_blocks, parts * kPostRows, 0, stream>>>(p);
   return cudaGetLastError();
 }
 
