@@ -216,7 +216,10 @@ __device__ __forceinline__ bool column_stats_fast(const float (&m)[E], const flo
 // per-thread chain -- the latency floor of the small sampler steps late in a rollout -- is one or two
 // columns long, and a small batch still spreads over all SMs (32-row blocks).
 constexpr int kPostRows = 32;
-constexpr int kPostParts = 16;
+#ifndef CMBPO_POST_PARTS
+#define CMBPO_POST_PARTS 8
+#endif
+constexpr int kPostParts = CMBPO_POST_PARTS;
 constexpr int kPostThreads = kPostRows * kPostParts;
 
 // Block partial sums of the four scalar diagnostics (fake_env.py:213-220); the last block to finish sums
@@ -270,7 +273,7 @@ __device__ __forceinline__ void finish_scalars(const StepParams& p, const float 
 }
 
 template <int E, bool OPT>   // OPT: the beyond-reference options (sample_mode / bound_logvar) are compiled in
-__global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepParams p) {
+__global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post_kernel(const StepParams p) {
   __shared__ float tile[kPostRows * 64 + 32];  // obs in / next_obs out staging (obs_dim <= 64)
   __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
   __shared__ float s_rew[kPostRows];
@@ -436,7 +439,7 @@ __global__ void __launch_bounds__(kPostThreads, 2) step_post_kernel(const StepPa
 // (dynamic) shared memory so global traffic stays coalesced.  Warp `part` < E then evaluates the static
 // termination / cost function of member `part`.
 template <int E, bool OPT>
-__global__ void __launch_bounds__(kPostThreads, 2) step_post3d_kernel(const StepParams p) {
+__global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post3d_kernel(const StepParams p) {
   extern __shared__ float tiles[];                 // [E][kPostRows * OD]
   __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
   __shared__ float s_rew[E][kPostRows];
@@ -649,9 +652,8 @@ static cudaError_t launch_step_post_EO(const StepParams& p, int n_blocks, cudaSt
     step_post3d_kernel<E, OPT><<<n_blocks, kPostThreads, smem, stream>>>(p);
     return cudaGetLastError();
   }
-  // 16 column parts per block unless that leaves the last round mostly idle: D = 18 (HalfCheetah) on 16 warps is 2
-  // rounds at 56 % use -> 9 warps x 2 columns (rollout +4 %, same-box A/B).  D = 30 stays at 16: 15 x 2 measured 2 %
-  // slower (fewer threads in flight per SM outweigh the two idle warps).
+  // kPostParts column parts per block unless that leaves the last round mostly idle (HalfCheetah, D = 18: 3 rounds
+  // of 8 at 75 % use -> 6 warps x 3 columns); a narrower block that only saves one idle warp measured slower.
   const int rounds = (p.D + kPostParts - 1) / kPostParts;
   const int parts = (p.D * 5 >= rounds * kPostParts * 4) ? kPostParts : (p.D + rounds - 1) / rounds;
   step_post_kernel<E, OPT><<<n_blocks, parts * kPostRows, 0, stream>>>(p);
