@@ -49,6 +49,29 @@ class FC:
     def set_ensemble_size(self, n): self.ensemble_size = n
 
 
+def parse_nns(path):
+    """Layer list of a ``.nns`` structure file (one ``repr(FC)`` per line, written by ``BNN.save``, bnn.py:811-819;
+    read upstream by ``BNN._load_structure``, bnn.py:829-846).  The last line describes the head BEFORE
+    ``finalize`` (single-width output for a probabilistic model, its activation restored)."""
+    layers = []
+    with open(path, "r") as f:
+        for line in f:
+            line = line.strip()
+            if not line:
+                continue
+            if not (line.startswith("FC(") and line.endswith(")")):
+                raise ValueError(f"{path}: not an FC(...) structure line: {line!r}")
+            kw = dict(av.split("=", 1) for av in line[3:-1].split(", "))
+            act = kw["activation"]
+            layers.append(FC(int(kw["output_dim"]), input_dim=int(kw["input_dim"]),
+                             activation=None if act == "None" else act.strip("'\""),
+                             weight_decay=None if kw["weight_decay"] == "None" else float(kw["weight_decay"]),
+                             ensemble_size=int(kw["ensemble_size"])))
+    if not layers:
+        raise ValueError(f"{path}: empty structure file")
+    return layers
+
+
 class TensorStandardScaler:
     """State holder with the attributes of mbpo/models/utils.py:90-239 callers read
     (``cached_mu``, ``cached_var`` at cmbpo.py:378-379).  ``var`` is a variance although the
@@ -120,6 +143,13 @@ class BNN:
         self._handle = None
         self._ws = None
         self.weights, self.biases = [], []
+        self.max_logvar = self.min_logvar = None      # NLL models carry them as trained variables (bnn.py:208-212)
+        if params.get("load_model", False):           # bnn.py:90-94
+            if self.model_dir is None:
+                raise ValueError("Cannot load model without providing model directory.")
+            self.layers = parse_nns(os.path.join(self.model_dir, "%s.nns" % self.name))
+            self.num_nets, self.model_loaded = self.layers[0].get_ensemble_size(), True
+            self._model_inds = np.random.randint(self.num_nets, size=self.num_elites)   # bnn.py:96-97
 
     # ---- properties of the reference ------------------------------------------------------
     @property
@@ -214,10 +244,15 @@ class BNN:
         for s in (self.scaler_in, self.scaler_out):
             if s is not None:
                 s._on_change = self._push_scalers
+        if self.loss_type == "NLL":    # bnn.py:208-212
+            self.max_logvar = np.ones([1, self.out_dim], np.float32) * self.max_logvar_param
+            self.min_logvar = np.ones([1, self.out_dim], np.float32) * self.min_logvar_param
         self.finalized = True
         self._push_weights()
         self._push_scalers()
         self._push_elites()
+        if self.model_loaded:          # bnn.py:374-379
+            self.load_mat(os.path.join(self.model_dir, "%s.mat" % self.name))
 
     # ---- state hand-over (after the reference trained, bnn.py:467-666) ----------------------
     def _stream(self):
@@ -276,24 +311,37 @@ class BNN:
             self.set_elites(elites)
 
     def load_mat(self, path):
-        """Ingest the ``.mat`` written by the reference's ``BNN.save`` (bnn.py:821-827): keys
-        '0'..'N' in the order nonoptvars + optvars = [mu_in, var_in, mu_out, var_out, W0, b0, ...]
-        (bnn.py:222-227), scaler entries present only for the scalers in use."""
+        """Ingest the ``.mat`` written by the reference's ``BNN.save`` (bnn.py:821-827): keys '0'..'N' in the order
+        nonoptvars + optvars = [mu_in, var_in, mu_out, var_out, W0, b0, ..., W_L, b_L, (max_logvar, min_logvar)]
+        (bnn.py:214-227): scaler entries only for the scalers in use, the two log-variance bounds only for 'NLL'."""
         from scipy.io import loadmat
         d = loadmat(path)
-        vals = [d[str(i)] for i in range(len([k for k in d if k.isdigit()]))]
+        n = len([k for k in d if k.isdigit()])
+        vals = [d[str(i)] for i in range(n)]
+        L = len(self.layers)
+        want = 2 * L + 2 * bool(self.use_scaler_in) + 2 * bool(self.use_scaler_out) + 2 * (self.loss_type == "NLL")
+        if n != want:
+            raise ValueError(f"{path}: {n} variables, this structure needs {want} "
+                             f"(scalers in/out: {self.use_scaler_in}/{self.use_scaler_out}, loss {self.loss_type})")
         i = 0
         sin = sout = None
         if self.use_scaler_in:
             sin = (vals[i], vals[i + 1]); i += 2
         if self.use_scaler_out:
             sout = (vals[i], vals[i + 1]); i += 2
-        ws = vals[i:i + 2 * len(self.layers):2]
-        bs = vals[i + 1:i + 2 * len(self.layers):2]
+        ws = vals[i:i + 2 * L:2]
+        bs = vals[i + 1:i + 2 * L:2]
+        for k, b in enumerate(bs):     # savemat squeezes nothing, but tolerate [E, out] biases
+            bs[k] = np.asarray(b).reshape(self.num_nets, 1, -1)
+        i += 2 * L
         self.load_state(ws, bs, sin, sout)
+        if self.loss_type == "NLL":
+            self.max_logvar = np.asarray(vals[i], np.float32).reshape(1, -1)
+            self.min_logvar = np.asarray(vals[i + 1], np.float32).reshape(1, -1)
 
     def save(self, savedir, timestep):
-        """Same two files as bnn.py:799-827: ``{name}_{timestep}.nns`` + ``.mat``."""
+        """Same two files as bnn.py:799-827: ``{name}_{timestep}.nns`` + ``.mat``; a reference ``BNN`` constructed
+        with ``load_model=True, name='{name}_{timestep}'`` reads them back (and so does this class)."""
         from scipy.io import savemat
         if not self.finalized:
             raise RuntimeError()
@@ -312,6 +360,8 @@ class BNN:
                 vals += [np.asarray(s.cached_mu, np.float32), np.asarray(s.cached_var, np.float32)]
         for w, b in zip(self.weights, self.biases):
             vals += [w.cpu().numpy(), b.cpu().numpy()]
+        if self.loss_type == "NLL":
+            vals += [np.asarray(self.max_logvar, np.float32), np.asarray(self.min_logvar, np.float32)]
         savemat(os.path.join(model_dir, "{}_{}.mat".format(self.name, timestep)),
                 {str(i): v for i, v in enumerate(vals)})
 
@@ -392,6 +442,10 @@ class BNN:
             v3d = m2d.var(dim=0, unbiased=False).reshape(x.shape[0], x.shape[1], -1)
             return out(mean), out(v3d)
         return out(mean)
+
+    def check_status(self):
+        """Synchronise this model's stream and raise if a device watchdog tripped (include/cmbpo_b200.h cmbpo_status)."""
+        _lib.check(self._lib.cmbpo_status(self._handle, self._stream()))
 
     def close(self):
         if self._handle is not None:

@@ -40,7 +40,8 @@ struct Handle {
   float* consts = nullptr;     // in_mu | in_inv | head_scale | head_shift
   int* elites_dev = nullptr;
   int n_elites = 0;
-  int* status_dev = nullptr;
+  int* status_dev = nullptr;   // device alias of status_host (mapped pinned memory: readable after a trap)
+  volatile int* status_host = nullptr;
   unsigned int* ticket_dev = nullptr;   // step_post's last-block counter
   uint32_t layers_set = 0;
   int hidden_act = 0;
@@ -155,8 +156,15 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
   }
   CU(cudaMalloc(&h->consts, sizeof(float) * (2 * pl.in_dim + 2 * n_head)), "cudaMalloc(consts)");
   CU(cudaMalloc(&h->elites_dev, sizeof(int) * 64), "cudaMalloc(elites)");
-  CU(cudaMalloc(&h->status_dev, sizeof(int)), "cudaMalloc(status)");
-  CU(cudaMemset(h->status_dev, 0, sizeof(int)), "cudaMemset(status)");
+  // watchdog word in mapped host memory: the kernels write the wait code and __trap(), which poisons the context --
+  // a device-memory word could not be copied back afterwards, the host mapping can still be read
+  {
+    int* hp = nullptr;
+    CU(cudaHostAlloc(&hp, sizeof(int), cudaHostAllocMapped), "cudaHostAlloc(status)");
+    *hp = 0;
+    h->status_host = hp;
+    CU(cudaHostGetDevicePointer(&h->status_dev, hp, 0), "cudaHostGetDevicePointer(status)");
+  }
   CU(cudaMalloc(&h->ticket_dev, sizeof(unsigned int)), "cudaMalloc(ticket)");
   CU(cudaMemset(h->ticket_dev, 0, sizeof(unsigned int)), "cudaMemset(ticket)");
   // defaults: identity scalers (utils.py:108-115), every member elite
@@ -175,7 +183,7 @@ extern "C" void cmbpo_destroy(void* handle) {
   Handle* h = static_cast<Handle*>(handle);
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->wimg); cudaFree(h->wimg_wide); cudaFree(h->bias_wide); cudaFree(h->consts); cudaFree(h->elites_dev); cudaFree(h->status_dev); cudaFree(h->ticket_dev);
+  cudaFree(h->wimg); cudaFree(h->wimg_wide); cudaFree(h->bias_wide); cudaFree(h->consts); cudaFree(h->elites_dev); cudaFreeHost((void*)h->status_host); cudaFree(h->ticket_dev);
   delete h;
 }
 
@@ -513,15 +521,14 @@ extern "C" int cmbpo_profile_read(void* handle, double* fwd_ms_total, int64_t* f
 extern "C" int cmbpo_status(void* handle, void* stream) {
   Handle* h = static_cast<Handle*>(handle);
   if (!h) return fail(CMBPO_ERR_ARG, "cmbpo_status: null handle");
-  int st = 0;
-  cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
-  if (e != cudaSuccess) return fail_cuda(e, "cmbpo_status: stream");
-  e = cudaMemcpy(&st, h->status_dev, sizeof(int), cudaMemcpyDeviceToHost);
-  if (e != cudaSuccess) return fail_cuda(e, "cmbpo_status: memcpy");
+  const cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+  const int st = h->status_host ? *h->status_host : 0;   // mapped host word: valid even if the context is poisoned
   if (st != 0) {
-    char buf[96];
-    snprintf(buf, sizeof(buf), "device watchdog tripped: wait code %d", st & 0xFFFF);
+    char buf[160];
+    snprintf(buf, sizeof(buf), "device watchdog tripped: wait code %d%s%s", st & 0xFFFF,
+             e != cudaSuccess ? "; stream: " : "", e != cudaSuccess ? cudaGetErrorString(e) : "");
     return fail(CMBPO_ERR_CUDA, buf);
   }
+  if (e != cudaSuccess) return fail_cuda(e, "cmbpo_status: stream");
   return CMBPO_OK;
 }

@@ -370,7 +370,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
         if (progress) { idle = 0; continue; }
         __nanosleep(32);
         if (++idle > (SM100_WAIT_LIMIT >> 2)) {
-          if (p.status) { atomicExch(p.status, WC_LOADER_EMPTY | 0x40000000); __threadfence_system(); }
+          if (p.status) { *reinterpret_cast<volatile int*>(p.status) = (WC_LOADER_EMPTY | 0x40000000); __threadfence_system(); }
           __trap();
         }
       }
@@ -458,7 +458,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
         if (progress) { idle = 0; continue; }
         __nanosleep(64);
         if (++idle > (SM100_WAIT_LIMIT >> 2)) {
-          if (p.status) { atomicExch(p.status, WC_STAGER_EMPTY | 0x40000000); __threadfence_system(); }
+          if (p.status) { *reinterpret_cast<volatile int*>(p.status) = (WC_STAGER_EMPTY | 0x40000000); __threadfence_system(); }
           __trap();
         }
       }

@@ -112,7 +112,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* st
   for (uint32_t it = 0; it < SM100_WAIT_LIMIT; ++it) {
     if (mbar_try_wait(bar, parity)) return;
   }
-  if (status) { atomicExch(status, code | 0x40000000); __threadfence_system(); }
+  if (status) { *reinterpret_cast<volatile int*>(status) = (code | 0x40000000); __threadfence_system(); }
   __trap();
 }
 // Wait on a barrier whose arrivals may come from the peer CTA.  Deliberately the plain (.acquire.cta)
@@ -133,7 +133,7 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity,
     if (mbar_try_wait(bar, parity)) return;
     __nanosleep(sleep_ns);
   }
-  if (status) { atomicExch(status, code | 0x40000000); __threadfence_system(); }
+  if (status) { *reinterpret_cast<volatile int*>(status) = (code | 0x40000000); __threadfence_system(); }
   __trap();
 }
 

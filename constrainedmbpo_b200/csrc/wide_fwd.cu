@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __gri
         if (progress) { idle = 0; continue; }
         __nanosleep(32);
         if (++idle > (SM100_WAIT_LIMIT >> 2)) {
-          if (p.status) { atomicExch(p.status, WWC_LOADER | 0x40000000); __threadfence_system(); }
+          if (p.status) { *reinterpret_cast<volatile int*>(p.status) = (WWC_LOADER | 0x40000000); __threadfence_system(); }
           __trap();
         }
       }

@@ -75,26 +75,51 @@ class CriticValues:
         return out[0], out[1]
 
 
-def compute_dynamics_dkl(env, policy, obs_batch, depth=1):
+EPS = 1e-8   # model_sampler.py:17
+
+
+class DklAccumulators:
+    """The two sampler accumulators ``compute_dynamics_dkl`` adds to (``_total_dkl`` / ``_total_samples``,
+    model_sampler.py:51,61; zeroed by ``ModelSampler.reset``, :251,:260).  They persist across calls upstream, so
+    the value returned by a second calibration call is the running mean over BOTH calls (and over whatever
+    ``sample`` added in between, :386); pass one object to successive calls to reproduce that."""
+
+    def __init__(self):
+        self.reset()
+
+    def reset(self):
+        self.total_dkl, self.total_samples = 0.0, 0
+
+    @property
+    def dyn_dkl(self):   # model_sampler.py:192-194
+        return self.total_dkl / (self.total_samples + EPS)
+
+
+def compute_dynamics_dkl(env, policy, obs_batch, depth=1, accum=None, elite_fn=None):
     """``ModelSampler.compute_dynamics_dkl`` (model_sampler.py:160-176): roll ``depth`` steps from
     ``obs_batch``, dropping terminated rows, and return (running mean of ``ensemble_dkl_mean``
     weighted by rows) * depth -- the value CMBPO hands to ``set_rollout_dkl`` (cmbpo.py:283-285).
-    Calibration only (cold path): synchronises every step."""
+    ``accum``: a ``DklAccumulators`` carried across calls (default: fresh, i.e. right after ``reset``).
+    ``elite_fn(step, n_rows) -> int array``: injects the ``BNN.random_inds`` draw of each ``env.step``
+    (parity tests); None = the in-kernel Philox draw.  Calibration only (cold path): synchronises every step."""
     dev = env.device
     if not torch.is_tensor(obs_batch):
         obs_batch = torch.as_tensor(np.asarray(obs_batch, dtype=np.float32))
     obs = obs_batch.to(dev, dtype=torch.float32).contiguous()
-    total_dkl, total_samples = 0.0, 0
-    for _ in range(depth):
-        if obs.shape[0] == 0:
+    acc = accum if accum is not None else DklAccumulators()
+    for k in range(depth):
+        n_paths = obs.shape[0]
+        if n_paths == 0:     # upstream would step an empty batch; its contribution is 0 * 0
             break
         act = policy(obs).clone()
-        o = env.step_device(obs, act, want_ep_var=False)
-        n_paths = obs.shape[0]
-        total_dkl += float(o["scalars"][0].item()) * n_paths
-        total_samples += n_paths
+        idx = None
+        if elite_fn is not None:
+            idx = torch.as_tensor(np.asarray(elite_fn(k, n_paths), dtype=np.int32)).to(dev)
+        o = env.step_device(obs, act, elite_idx=idx, want_ep_var=False)
+        acc.total_dkl += float(o["scalars"][0].item()) * n_paths
+        acc.total_samples += n_paths
         obs = o["next_obs"][~o["term"].reshape(-1).bool()].contiguous()
-    return total_dkl / max(total_samples, 1) * depth
+    return acc.dyn_dkl * depth
 
 
 class ModelRollout:
@@ -349,16 +374,4 @@ class ModelRollout:
             out["populated"] = out["populated"].astype(bool)
             if "populated_trimmed" in out:
                 out["populated_trimmed"] = out["populated_trimmed"].astype(bool)
-        return out
-
-    def all_gather(self, group=None):
-        """Multi-GPU: concatenate every rank's pool shard along the path axis with one NCCL
-        all-gather per array.  Shards must have equal ``B``."""
-        import torch.distributed as dist
-        ws = dist.get_world_size(group)
-        out = {}
-        for k, v in self.pool.items():
-            full = torch.empty((ws * v.shape[0],) + tuple(v.shape[1:]), dtype=v.dtype, device=v.device)
-            dist.all_gather_into_tensor(full, v.contiguous(), group=group)
-            out[k] = full
         return out

@@ -146,18 +146,20 @@ def _step_tuple(ens, env, cur, a, rng, cares_about_cost):
     return no, rw, tm, info
 
 
-def compute_dynamics_dkl(ens: TorchEnsemble, env, obs_batch, policy_np, depth, rng=None):
-    """model_sampler.py:160-176 on the CPU port."""
+def compute_dynamics_dkl(ens: TorchEnsemble, env, obs_batch, policy_np, depth, rng=None, elite_fn=None, totals=None):
+    """model_sampler.py:160-176 on the CPU port.  ``totals`` = [total_dkl, total_samples] carried across calls like the
+    sampler's ``_total_dkl`` / ``_total_samples`` (:51,:61); ``elite_fn(step, n)`` injects the ``random_inds`` draws."""
     rng = rng or np.random.default_rng(6)
     obs = np.asarray(obs_batch, dtype=np.float32)
-    total_dkl, total_n = 0.0, 0
-    for _ in range(depth):
+    tot = totals if totals is not None else [0.0, 0]
+    for k in range(depth):
         if obs.shape[0] == 0:
             break
         a = policy_np(obs)
-        idx = rng.choice(ens.p.elites, size=obs.shape[0])
+        idx = elite_fn(k, obs.shape[0]) if elite_fn is not None else rng.choice(ens.p.elites, size=obs.shape[0])
         no, _, tm, info = fake_env_step(ens, env, obs, a, idx)
-        total_dkl += float(info["ensemble_dkl_mean"]) * obs.shape[0]
-        total_n += obs.shape[0]
-        obs = no[~np.squeeze(tm, -1)]
-    return total_dkl / max(total_n, 1) * depth
+        n_paths = no.shape[0]                                       # :167
+        tot[0] += float(info["ensemble_dkl_mean"]) * n_paths        # :168
+        tot[1] += n_paths                                           # :169
+        obs = no[~np.squeeze(tm, -1)]                               # :171
+    return tot[0] / (tot[1] + 1e-8) * depth                         # :173-174, dyn_dkl :192-194 (EPS = 1e-8, :17)

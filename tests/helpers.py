@@ -82,9 +82,11 @@ def out_scale(p):
 # fp64.  An output element y = out*s_out + mu_out is compared as
 #     |y_cuda - y_ref| <= RTOL * |y_ref| + ATOL_SCALE * s_out[d]
 # (s_out = the output scaler's divisor, i.e. the natural unit of head column d).
+# Observed on B200 (profiles/r02_tolerance_report.txt): max |err| = 4.3e-3 * s_out, max |dlogvar| = 4.8e-3 for the 4-layer
+# nets, inputs at the scaler floor included -- the absolute companion of rtol 1e-2 is 1e-2 * s_out.
 RTOL_BF16 = 1e-2
-ATOL_SCALE_BF16 = 2e-2
-VAR_RTOL_BF16 = 5e-2      # variance = exp(logvar): an absolute logvar error e shows up as rel. error e
+ATOL_SCALE_BF16 = 1e-2
+VAR_RTOL_BF16 = 2e-2      # variance = exp(logvar): an absolute logvar error e shows up as rel. error e
 
 
 def assert_means_close(got, ref, s_out, rtol=RTOL_BF16, atol_scale=ATOL_SCALE_BF16, what="mean"):

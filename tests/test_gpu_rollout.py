@@ -587,3 +587,42 @@ def test_host_drain_pipeline_delivers_every_rollout():
     assert len({w.shape[0] for w in want}) > 1       # the rollouts really differ in size
     for w, g_ in zip(want, got):
         assert w.shape == g_.shape and torch.equal(w.view(torch.int32), g_.view(torch.int32))
+
+
+def test_compute_dynamics_dkl_matches_cpu_port():
+    """A13, ``ModelSampler.compute_dynamics_dkl`` (model_sampler.py:160-176): same 5 000 calibration states, same
+    stub policy matrix, the ``random_inds`` draws of every ``env.step`` injected into both sides.  The value sets
+    ``dkl_lim`` -- every 'uncertainty' cutoff downstream -- so it is compared with the CPU port of the reference
+    (fp32 GEMMs + the NumPy post-processing) and with the fp64 oracle loop; the accumulators persist across calls
+    like the sampler's ``_total_dkl`` / ``_total_samples``."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    from oracle import cpu_baseline as cb
+    env, B, depth = "antsafe", 5000, 3
+    p = make_params(env, HIDDEN)
+    obs, _ = make_inputs(env, B, seed=21)
+    obs[:, 0] = np.random.default_rng(4).uniform(0.3, 0.9, B)     # most rows survive the first step
+    fe = build_cuda_env(p, env, HIDDEN)
+    pol = cm.StubPolicy(29, 8, seed=4)
+    P = pol.P.cpu().numpy()
+    policy_np = lambda o: np.tanh(np.asarray(o, np.float32) @ P)
+    draws = [np.random.default_rng(100 + k).choice(p.elites, size=B) for k in range(2 * depth)]
+    acc = cm.DklAccumulators()
+    got = cm.compute_dynamics_dkl(fe, pol, obs, depth=depth, accum=acc, elite_fn=lambda k, n: draws[k][:n])
+    ens = cb.TorchEnsemble(p)
+    totals = [0.0, 0]
+    ref = cb.compute_dynamics_dkl(ens, env, obs, policy_np, depth, elite_fn=lambda k, n: draws[k][:n], totals=totals)
+    # rows near a termination threshold may drop out on one side only: the row counts must agree to within those
+    assert abs(acc.total_samples - totals[1]) <= 0.01 * totals[1], (acc.total_samples, totals[1])
+    assert acc.total_samples > 2 * B            # the calibration really rolled `depth` steps
+    assert abs(got - ref) <= 2e-2 * ref, (got, ref)
+    # a second call keeps accumulating (model_sampler.py:168-169): running mean over both calls
+    obs2, _ = make_inputs(env, 1000, seed=22)
+    got2 = cm.compute_dynamics_dkl(fe, pol, obs2, depth=1, accum=acc, elite_fn=lambda k, n: draws[depth + k][:n])
+    ref2 = cb.compute_dynamics_dkl(ens, env, obs2, policy_np, 1, elite_fn=lambda k, n: draws[depth + k][:n], totals=totals)
+    assert acc.total_samples == pytest.approx(totals[1], rel=0.01)
+    assert abs(got2 - ref2) <= 2e-2 * ref2
+    assert got2 == pytest.approx(acc.total_dkl / (acc.total_samples + 1e-8))     # depth 1: the running mean itself
+    # a fresh accumulator (= right after ModelSampler.reset) gives the per-call mean
+    fresh = cm.compute_dynamics_dkl(fe, pol, obs2, depth=1, elite_fn=lambda k, n: draws[depth + k][:n])
+    assert fresh != pytest.approx(got2, rel=1e-6)

@@ -294,7 +294,7 @@ def test_step_against_reference_fake_env_golden(tag, env):
     # 24-wide nets fed inputs at the scaler floor (two input dims have var 1e-6 => normalised magnitudes ~1e2, whose
     # bf16 rounding is ~0.5 absolute) see less averaging than the 200-wide nets of test_step_parity: the absolute
     # companion of rtol 1e-2 is 4e-2 * s_out here (observed worst 3.5e-2, 1 element in 20160 above 2e-2)
-    atol = 2 * ATOL_SCALE_BF16
+    atol = 4e-2
     assert_means_close(no, g["next_obs"], s[:-1], atol_scale=atol, what="next_obs vs reference FakeEnv.step")
     assert_means_close(rw, g["rew"], s[-1:], atol_scale=atol, what="reward vs reference FakeEnv.step")
     tol = RTOL_BF16 * np.abs(g["next_obs"].astype(np.float64)) + atol * s[:-1]

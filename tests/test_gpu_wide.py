@@ -18,12 +18,14 @@ pytestmark = pytest.mark.gpu
 
 # Same rtol as the narrow tests (north_star: 1e-2 for bf16 operands).  The absolute companion scales with the
 # square root of the accumulation length: every product carries two bf16 roundings (2^-9 relative), so the
-# error of a K-term dot product grows like sqrt(K): 2e-2 * s_out at K = 200  ->  2e-2 * sqrt(K_max / 200).
-# Floor 3e-2: the two-hidden-layer nets of the shipped configs hand the bf16 rounding of the floor-scaled
-# inputs (|x| ~ 100 where var_in hits the 1e-2 floor, quirk Q6: absolute rounding error up to 0.25) to the
-# heads more directly than the 4-layer BASELINE nets do (observed: <= 9 of 1.3e5 elements between 2e-2 and 3e-2).
+# error of a K-term dot product grows like sqrt(K): 1e-2 * s_out at K = 200  ->  1e-2 * sqrt(K_max / 200)
+# (observed for 4-layer nets: <= 4.1e-3 * s_out up to width 1024, profiles/r02_tolerance_report.txt).
+# Nets with TWO hidden layers (the shipped (512, 512) configs) get 3e-2: they hand the bf16 rounding of the
+# floor-scaled inputs (|x| ~ 100 where var_in hits the 1e-2 floor, quirk Q6: absolute rounding error up to 0.25) to
+# the heads more directly than the 4-layer BASELINE nets do (observed: <= 9 of 1.3e5 elements between 2e-2 and 3e-2).
 def _atol(hidden):
-    return max(3e-2, 2e-2 * float(np.sqrt(max(hidden) / 200.0)))
+    base = 1e-2 * float(np.sqrt(max(hidden) / 200.0))
+    return max(3e-2, base) if len(hidden) < 3 else max(1e-2, base)
 
 
 @pytest.mark.parametrize("hidden", [(512, 512), (1024, 1024, 1024), (300, 260), (512, 200, 384)])

@@ -72,3 +72,32 @@ def test_bench_flop_accounting_matches_survey():
     assert bench.flops_per_row(bench.WORKLOADS["antsafe_uncertainty_H30_100k"]) == 1_951_600
     assert bench.flops_per_row(bench.WORKLOADS["halfcheetah_schedule_L10_1M"]) == 1_845_200
     assert bench.bytes_per_transition(bench.WORKLOADS["antsafe_uncertainty_H30_100k"]) == 4 * (29 + 8 + 29 + 3) + 1
+
+
+def test_nns_structure_reader_round_trip(tmp_path):
+    """``BNN._load_structure`` (bnn.py:829-846) on a file in the exact line format ``BNN.save`` writes (:811-819):
+    the literal lines below are what the reference's ``FC.__repr__`` (fc.py:47-51) prints for the antsafe dynamics
+    ensemble of ``FakeEnv`` (fake_env.py:61-75, decay 1e-6)."""
+    from constrainedmbpo_b200.bnn import parse_nns
+    lines = [
+        "FC(output_dim=200, input_dim=37, activation='swish', weight_decay=2.5e-07, ensemble_size=7)",
+        "FC(output_dim=200, input_dim=200, activation='swish', weight_decay=5e-07, ensemble_size=7)",
+        "FC(output_dim=30, input_dim=200, activation=None, weight_decay=1e-06, ensemble_size=7)",
+    ]
+    path = tmp_path / "BNN_12.nns"
+    path.write_text("\n".join(lines) + "\n")
+    layers = parse_nns(str(path))
+    assert [repr(l) for l in layers] == lines
+    assert layers[0].get_activation() == "swish" and layers[-1].get_activation() is None
+    assert layers[1].weight_decay == 5e-07 and layers[0].get_ensemble_size() == 7
+    # load_model=True takes structure and ensemble size from the file (bnn.py:90-97); no GPU until finalize()
+    m = BNN({"name": "BNN_12", "model_dir": str(tmp_path), "load_model": True, "num_elites": 5, "loss": "MSPE",
+             "num_networks": 3})
+    assert m.model_loaded and m.num_nets == 7 and len(m.layers) == 3 and len(m.elite_inds) == 5
+    with pytest.raises(RuntimeError, match="loaded"):       # bnn.py:139-140
+        m.add(FC(4))
+    with pytest.raises(ValueError, match="model directory"):
+        BNN({"name": "BNN_12", "load_model": True, "num_elites": 5})
+    (tmp_path / "bad.nns").write_text("Dense(3)\n")
+    with pytest.raises(ValueError, match="structure line"):
+        parse_nns(str(tmp_path / "bad.nns"))
