@@ -38,4 +38,20 @@ def test_reference_arm_prints_contract_line():
     line = json.loads(out.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["unit"] == "transitions/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
-    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["config"]["workload"] == "antsafe_uncertainty_H30_100k"
+    # the default workload is BASELINE configs[2] (1 M HalfCheetah start states, strong scaling); both arms print the
+    # same `config` for it
+    import bench
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["config"]["workload"] == "halfcheetah_schedule_L10_1M"
+    assert line["config"] == bench.config_of("halfcheetah_schedule_L10_1M", bench.WORKLOADS["halfcheetah_schedule_L10_1M"], 1)
+    assert line["scaling"] == "strong" and line["config"]["start_states_total"] == 1_000_000
+
+
+def test_reference_arm_predict_workload_and_other_ranks_stay_silent():
+    """configs[0] (one BNN.predict on 10 k rows) on the CPU port; under torchrun only rank 0 runs the reference arm."""
+    cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+           "--workload", "antsafe_predict_10k", "--cpu-rows", "2000"]
+    out = subprocess.run(cmd, check=True, capture_output=True, text=True, cwd=ROOT)
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["config"]["kind"] == "predict" and line["value"] > 0
+    out = subprocess.run(cmd, check=True, capture_output=True, text=True, cwd=ROOT, env=dict(os.environ, RANK="1", WORLD_SIZE="2"))
+    assert out.stdout.strip() == ""

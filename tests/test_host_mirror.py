@@ -74,6 +74,30 @@ def test_bench_flop_accounting_matches_survey():
     assert bench.bytes_per_transition(bench.WORKLOADS["antsafe_uncertainty_H30_100k"]) == 4 * (29 + 8 + 29 + 3) + 1
 
 
+def test_bench_sharding_and_workload_table():
+    """Strong scaling cuts the SAME global batch into contiguous blocks; weak scaling gives every rank its own rows;
+    every BASELINE config has a workload."""
+    import bench
+    w = bench.WORKLOADS[bench.DEFAULT_WORKLOAD]
+    assert bench.DEFAULT_WORKLOAD == "halfcheetah_schedule_L10_1M" and w["scaling"] == "strong"
+    for world in (1, 2, 3, 8):
+        cuts = [bench.shard_rows(w, world, r) for r in range(world)]
+        assert cuts[0][0] == 0 and sum(n for _, n in cuts) == w["rows"]
+        assert all(cuts[i][0] + cuts[i][1] == cuts[i + 1][0] for i in range(world - 1))
+    small = dict(w, rows=10)
+    full = bench.synth_start_states(small, 10, 1)
+    lo, n = bench.shard_rows(small, 3, 1)
+    assert np.array_equal(bench.synth_start_states(small, n, 1, lo=lo), full[lo:lo + n])
+    wk = bench.WORKLOADS["antsafe_uncertainty_H30_100k"]
+    assert bench.shard_rows(wk, 4, 2) == (200_000, 100_000)
+    for name in ("antsafe_predict_10k", "antsafe_uncertainty_H30_100k", "halfcheetah_schedule_L10_1M",
+                 "humanoidsafe_iv_gae_H12_1M", "antsafe_step_4M", "antsafe_step_256k_4x1024"):
+        assert name in bench.WORKLOADS
+    W, B = bench.draw_weights(dict(w, E=2))
+    assert [x.shape for x in W] == [(2, 23, 200), (2, 200, 200), (2, 200, 200), (2, 200, 200), (2, 200, 36)]
+    assert all(np.abs(x).max() <= 2 * (1 / (2 * np.sqrt(x.shape[1]))) + 1e-7 for x in W) and not B[0].any()
+
+
 def test_nns_structure_reader_round_trip(tmp_path):
     """``BNN._load_structure`` (bnn.py:829-846) on a file in the exact line format ``BNN.save`` writes (:811-819):
     the literal lines below are what the reference's ``FC.__repr__`` (fc.py:47-51) prints for the antsafe dynamics

@@ -13,12 +13,9 @@ import constrainedmbpo_b200 as cm
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 10
-wname = sys.argv[3] if len(sys.argv) > 3 else "antsafe_uncertainty_H30_100k"
+wname = sys.argv[3] if len(sys.argv) > 3 else "antsafe_step_1M"
 w = bench.WORKLOADS[wname]
-p = bench.synth_params(w)
-fe = cm.FakeEnv(cm.SimpleEnv(w["obs"], w["act"]), w["env"], num_networks=w["E"], num_elites=w["K"],
-                hidden_dims=w["hidden"], cares_about_cost=w["cost"], seed=5)
-fe._model.load_state(p.weights, p.biases, scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+fe = bench.build_env(w, 0)
 obs = torch.from_numpy(bench.synth_start_states(w, B, 1)).cuda()
 pol = cm.StubPolicy(w["obs"], w["act"])
 act = pol(obs)
@@ -39,5 +36,7 @@ lib.cmbpo_profile_read(h, C.byref(ms), C.byref(n))
 F = bench.flops_per_row(w)
 fwd = ms.value / n.value
 step = e0.elapsed_time(e1) / reps
-print(f"B={B} fwd {fwd*1e3:.1f} us -> {F*B/fwd/1e9:.1f} TFLOP/s ({F*B/fwd/1e9/1372.7*100:.1f}% of 1372.7); "
-      f"whole step {step*1e3:.1f} us -> {B/step/1e3:.2f} M rows/s")
+pk = bench.measured_peaks()
+tf = F * B / fwd / 1e9
+print(f"{wname} B={B} fwd {fwd*1e3:.1f} us -> {tf:.1f} TFLOP/s ({tf/pk['bf16_burst']*100:.1f}% of burst {pk['bf16_burst']:.0f}, "
+      f"{tf/pk['bf16_sustained']*100:.1f}% of sustained {pk['bf16_sustained']:.0f}); whole step {step*1e3:.1f} us -> {B/step/1e3:.2f} M rows/s")

@@ -9,10 +9,7 @@ from constrainedmbpo_b200 import sharding, _lib
 
 wname = sys.argv[1] if len(sys.argv) > 1 else bench.DEFAULT_WORKLOAD
 w = bench.WORKLOADS[wname]
-p = bench.synth_params(w)
-fe = cm.FakeEnv(cm.SimpleEnv(w["obs"], w["act"]), w["env"], num_networks=w["E"], num_elites=w["K"], hidden_dims=w["hidden"],
-                cares_about_cost=w["cost"], device="cuda:0", seed=5)
-fe._model.load_state(p.weights, p.biases, scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+fe = bench.build_env(w, 0)
 pol = cm.StubPolicy(w["obs"], w["act"], device="cuda:0")
 lim = None
 if w["mode"] == "uncertainty":

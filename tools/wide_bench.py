@@ -24,10 +24,7 @@ args = ap.parse_args()
 peak = bench.measured_peaks()["bf16_sustained"]
 for H in [int(x) for x in args.widths.split(",")]:
     w = dict(bench.WORKLOADS["antsafe_step_1M"], hidden=(H,) * args.layers)
-    p = bench.synth_params(w)
-    fe = cm.FakeEnv(cm.SimpleEnv(w["obs"], w["act"]), w["env"], num_networks=w["E"], num_elites=w["K"],
-                    hidden_dims=w["hidden"], cares_about_cost=True, seed=5)
-    fe._model.load_state(p.weights, p.biases, scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+    fe = bench.build_env(w, 0)
     lib, h = fe._model._lib, fe._model._handle
     pol = cm.StubPolicy(w["obs"], w["act"])
     F = bench.flops_per_row(w)
