@@ -193,7 +193,9 @@ def test_predict_wide_beyond_one_slab(hidden, B):
     assert_means_close(full["mean"][:, ridx].cpu().numpy(), rm, out_scale(p), atol_scale=_atol(hidden),
                        what=f"wide {hidden} mean @ {B} rows")
     rel = np.abs(full["var"][:, ridx].cpu().numpy() - rv) / rv
-    assert rel.max() < VAR_RTOL_BF16
+    # two-hidden-layer nets pass the rounding of the floor-scaled inputs almost directly to the log-variance head
+    # (see tests/test_gpu_wide.py _atol): 5e-2 there, the standard bound for the 4-layer nets
+    assert rel.max() < (5e-2 if len(hidden) < 3 else VAR_RTOL_BF16), f"variance rel err max {rel.max():.3e}"
 
 
 def test_full_rollout_at_benchmark_size_matches_chunked_rollouts():
