@@ -95,6 +95,42 @@ __device__ __forceinline__ bool last_block_scan(int* blk_cnt, int my_count, int 
 // in the payload copy loops
 __device__ __forceinline__ int fast_div(int idx, float inv_w) { return (int)(((float)idx + 0.5f) * inv_w); }
 
+
+// Row payload scatter shared by k_store / k_store_payload / k_compact_dev: element idx of the block's contiguous source
+// rows goes to dst[dst_row(r) * W + d] when dst_row(r) >= 0.  The loads of kPayU iterations are issued before the first
+// store (explicit register batch): source and destination are plain pointers, so without the batch the compiler keeps
+// every load behind the previous iteration's store and the loop becomes a chain of serial DRAM round trips
+// (k_store: 178 us for 330 MB at 1 M rows, ~30 long-scoreboard stalls per issue, profiles/r02_small_kernels_ncu_summary.txt).
+constexpr int kPayU = 8;
+template <int NSRC, typename RowFn>
+__device__ __forceinline__ void scatter_rows(const float* const (&src)[NSRC], float* const (&dst)[NSRC], int n_elems, int W,
+                                             float inv_w, RowFn dst_row) {
+  for (int base = threadIdx.x; base < n_elems; base += kRB * kPayU) {
+    float v[NSRC][kPayU];
+    long long o[kPayU];
+#pragma unroll
+    for (int u = 0; u < kPayU; ++u) {
+      const int idx = base + u * kRB;
+      o[u] = -1;
+      if (idx < n_elems) {
+        const int r = fast_div(idx, inv_w), d = idx - r * W;
+        const long long row = dst_row(r);
+        if (row >= 0) {
+          o[u] = row * W + d;
+#pragma unroll
+          for (int k = 0; k < NSRC; ++k) v[k][u] = __ldg(src[k] + idx);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kPayU; ++u)
+      if (o[u] >= 0) {
+#pragma unroll
+        for (int k = 0; k < NSRC; ++k) dst[k][o[u]] = v[k][u];
+      }
+  }
+}
+
 // A: too_uncertain flags (model_sampler.py:311-315) -> per-block count of still-certain rows
 __global__ void __launch_bounds__(kRB) k_decide(cmbpo_rollout_io io, uint8_t* certain, int* blk_cnt, int* snap, int* hist) {
   RolloutState* st = static_cast<RolloutState*>(io.state_dev);
@@ -211,23 +247,16 @@ __global__ void __launch_bounds__(kRB) k_store(cmbpo_rollout_io io, uint8_t* cer
     const float* sn = static_cast<const float*>(io.next_obs_dev) + (e * cap + row_base) * OD;
     float* po = static_cast<float*>(io.pool_obs_dev) + e * cap * T * OD;
     float* pn = static_cast<float*>(io.pool_next_obs_dev) + e * cap * T * OD;
-#pragma unroll 8
-    for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {
-      const int r = fast_div(idx, inv_od), d = idx - r * OD;
-      if (s_rem[r]) {
-        const size_t o = ((size_t)ptr * cap + s_pid[r]) * OD + d;
-        po[o] = so[idx];
-        pn[o] = sn[idx];
-      }
+    auto pool_row = [&](int r) -> long long { return s_rem[r] ? (long long)ptr * (long long)cap + s_pid[r] : -1; };
+    {
+      const float* const src2[2] = {so, sn};
+      float* const dst2[2] = {po, pn};
+      scatter_rows<2>(src2, dst2, n_here * OD, OD, inv_od, pool_row);
     }
     if (AD > 0) {
-      const float* sa = static_cast<const float*>(io.act_dev) + (e * cap + row_base) * AD;
-      float* pa = static_cast<float*>(io.pool_act_dev) + e * cap * T * AD;
-#pragma unroll 4
-      for (int idx = threadIdx.x; idx < n_here * AD; idx += kRB) {
-        const int r = fast_div(idx, inv_ad), d = idx - r * AD;
-        if (s_rem[r]) pa[((size_t)ptr * cap + s_pid[r]) * AD + d] = sa[idx];
-      }
+      const float* const src1[1] = {static_cast<const float*>(io.act_dev) + (e * cap + row_base) * AD};
+      float* const dst1[1] = {static_cast<float*>(io.pool_act_dev) + e * cap * T * AD};
+      scatter_rows<1>(src1, dst1, n_here * AD, AD, inv_ad, pool_row);
     }
   }
   // fused scan epilogue (was a separate single-block launch): the last block to finish its stores scans the
@@ -270,55 +299,66 @@ __global__ void __launch_bounds__(kRB) k_store_payload(cmbpo_rollout_io io, cons
   const float* sn = static_cast<const float*>(io.next_obs_dev) + (e * cap + row_base) * OD;
   float* po = static_cast<float*>(io.pool_obs_dev) + e * cap * T * OD;
   float* pn = static_cast<float*>(io.pool_next_obs_dev) + e * cap * T * OD;
-#pragma unroll 8
-  for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {
-    const int r = fast_div(idx, inv_od), d = idx - r * OD;
-    if (s_rem[r]) {
-      const size_t o = ((size_t)ptr * cap + s_pid[r]) * OD + d;
-      po[o] = so[idx];
-      pn[o] = sn[idx];
-    }
+  auto pool_row = [&](int r) -> long long { return s_rem[r] ? (long long)ptr * (long long)cap + s_pid[r] : -1; };
+  {
+    const float* const src2[2] = {so, sn};
+    float* const dst2[2] = {po, pn};
+    scatter_rows<2>(src2, dst2, n_here * OD, OD, inv_od, pool_row);
   }
   if (AD > 0) {
-    const float* sa = static_cast<const float*>(io.act_dev) + (e * cap + row_base) * AD;
-    float* pa = static_cast<float*>(io.pool_act_dev) + e * cap * T * AD;
-#pragma unroll 4
-    for (int idx = threadIdx.x; idx < n_here * AD; idx += kRB) {
-      const int r = fast_div(idx, inv_ad), d = idx - r * AD;
-      if (s_rem[r]) pa[((size_t)ptr * cap + s_pid[r]) * AD + d] = sa[idx];
-    }
+    const float* const src1[1] = {static_cast<const float*>(io.act_dev) + (e * cap + row_base) * AD};
+    float* const dst1[1] = {static_cast<float*>(io.pool_act_dev) + e * cap * T * AD};
+    scatter_rows<1>(src1, dst1, n_here * AD, AD, inv_ad, pool_row);
   }
 }
 
-// synthetic benchmark policy a = tanh(obs @ P); not part of the reference.  64-row tiles of
-// obs are staged through shared memory so that global loads and stores are both coalesced.
-constexpr int kPolRows = 64;
-__global__ void __launch_bounds__(256) k_stub_policy(const float* __restrict__ obs, const float* __restrict__ P,
-                                                     float* __restrict__ act, const int* n_rows_dev,
-                                                     long long n_rows, int OD, int AD, int n_slots) {
+// synthetic benchmark policy a = tanh(obs @ P); not part of the reference.  One thread per row: the
+// block's 256 obs rows come in through a coalesced flat copy into shared memory (row stride OD + 1: conflict-free row
+// reads), P is read as shared-memory broadcasts, 8 action columns are accumulated in registers per pass, and the
+// actions leave through shared memory as a coalesced flat copy.  (The first version computed one output element per
+// thread from a 64-row tile: 59 M warp instructions per 1 M rows, 84 us; this one is bound by its 92 MB of traffic.)
+constexpr int kPolRows = 256;
+__global__ void __launch_bounds__(kPolRows) k_stub_policy(const float* __restrict__ obs, const float* __restrict__ P,
+                                                          float* __restrict__ act, const int* n_rows_dev,
+                                                          long long n_rows, int OD, int AD, int n_slots) {
   extern __shared__ float sm[];
-  float* sP = sm;                       // [OD][AD]
-  float* sO = sm + OD * AD;             // [kPolRows][OD + 1]
+  float* sP = sm;                         // [OD][AD]
+  float* sO = sm + OD * AD;               // [kPolRows][OD + 1]
+  float* sA = sO + kPolRows * (OD + 1);   // [kPolRows][AD]
   for (int i = threadIdx.x; i < OD * AD; i += blockDim.x) sP[i] = P[i];
   const long long n = n_rows_dev ? (long long)(*n_rows_dev) : n_rows;
   const long long tiles_per_slot = (n + kPolRows - 1) / kPolRows;
   const long long n_tiles = tiles_per_slot * n_slots;   // slot e of obs / act starts at row e * n_rows (capacity)
+  const float inv_od = 1.0f / (float)OD;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long slot = tile / tiles_per_slot, r0 = (tile - slot * tiles_per_slot) * kPolRows;
     const int rows_here = (int)min((long long)kPolRows, n - r0);
     const size_t row_base = (size_t)(slot * n_rows + r0);
     __syncthreads();
-    for (int i = threadIdx.x; i < rows_here * OD; i += blockDim.x) {
-      const int r = i / OD, d = i - r * OD;
+    for (int i = threadIdx.x; i < rows_here * OD; i += kPolRows) {
+      const int r = fast_div(i, inv_od), d = i - r * OD;
       sO[r * (OD + 1) + d] = obs[row_base * OD + i];
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < rows_here * AD; i += blockDim.x) {
-      const int r = i / AD, a = i - r * AD;
-      float s = 0.f;
-      for (int d = 0; d < OD; ++d) s = fmaf(sO[r * (OD + 1) + d], sP[d * AD + a], s);
-      act[row_base * AD + i] = tanhf(s);
+    const int r = threadIdx.x;
+    if (r < rows_here) {
+      const float* xo = sO + r * (OD + 1);
+      for (int a0 = 0; a0 < AD; a0 += 8) {
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int d = 0; d < OD; ++d) {
+          const float x = xo[d];
+          const float* pr = sP + d * AD + a0;
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            if (a0 + u < AD) acc[u] = fmaf(x, pr[u], acc[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          if (a0 + u < AD) sA[r * AD + a0 + u] = tanhf(acc[u]);
+      }
     }
+    __syncthreads();
+    for (int i = threadIdx.x; i < rows_here * AD; i += kPolRows) act[row_base * AD + i] = sA[i];
   }
 }
 
@@ -360,12 +400,9 @@ __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const 
     const int e = e0;
     const float* src = static_cast<const float*>(io.next_obs_dev) + (e * cap + row_base) * OD;
     float* dstp = static_cast<float*>(io.new_obs_dev) + e * cap * OD;
-#pragma unroll 8
-    for (int idx = threadIdx.x; idx < n_here * OD; idx += kRB) {   // flat element loop, see k_store
-      const int r = fast_div(idx, inv_od), d = idx - r * OD;
-      const int d0 = s_dst[r];
-      if (d0 >= 0) dstp[(size_t)d0 * OD + d] = src[idx];
-    }
+    const float* const src1[1] = {src};
+    float* const dst1[1] = {dstp};
+    scatter_rows<1>(src1, dst1, n_here * OD, OD, inv_od, [&](int r) -> long long { return s_dst[r]; });
   }
 }
 }  // namespace cmbpo
@@ -400,10 +437,15 @@ extern "C" int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* a
   if (n_rows == 0) return CMBPO_OK;
   if (n_slots < 1) n_slots = 1;
   long long blocks = ((n_rows + kPolRows - 1) / kPolRows) * n_slots;
-  if (blocks > 148 * 8) blocks = 148 * 8;
-  const size_t smem = ((size_t)obs_dim * act_dim + (size_t)kPolRows * (obs_dim + 1)) * sizeof(float);
-  if (smem > 48 * 1024) return CMBPO_ERR_UNSUPPORTED;
-  k_stub_policy<<<(int)blocks, 256, smem, (cudaStream_t)stream_>>>(
+  if (blocks > 148 * 6) blocks = 148 * 6;
+  const size_t smem = ((size_t)obs_dim * act_dim + (size_t)kPolRows * (obs_dim + 1 + act_dim)) * sizeof(float);
+  if (smem > 200 * 1024) return CMBPO_ERR_UNSUPPORTED;
+  static size_t smem_set = 48 * 1024;
+  if (smem > smem_set) {
+    if (cudaFuncSetAttribute(k_stub_policy, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return CMBPO_ERR_CUDA;
+    smem_set = smem;
+  }
+  k_stub_policy<<<(int)blocks, kPolRows, smem, (cudaStream_t)stream_>>>(
       static_cast<const float*>(obs_dev), static_cast<const float*>(P_dev), static_cast<float*>(act_dev),
       static_cast<const int*>(n_rows_dev), n_rows, obs_dim, act_dim, n_slots);
   return cudaGetLastError() == cudaSuccess ? CMBPO_OK : CMBPO_ERR_CUDA;

@@ -6,6 +6,7 @@
 // ensemble_fwd.cu), so every load below is a fully coalesced 128-byte warp access.  Row-major
 // tensors (obs in, next_obs out) go through a shared-memory tile so global traffic stays
 // coalesced too.
+#include <cstdlib>
 #include "cmbpo_internal.cuh"
 #include "step_post.cuh"
 
@@ -110,6 +111,13 @@ __device__ __forceinline__ float pick(const float (&m)[E], int idx) {
   return r;
 }
 
+// e^x as one FMUL + MUFU.EX2: the .ftz form skips the denormal-input scaling (two FMULs and a compare per call) that
+// __expf emits in a non-fast-math build; results below 2^-126 flush to zero, where var + 1e-10 is 1e-10 either way
+__device__ __forceinline__ float exp_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+  return y;
+}
 __device__ __forceinline__ float rcp_approx(float x) {   // one MUFU.RCP, no range fix-up branch
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -179,25 +187,25 @@ template <int E>
 __device__ __forceinline__ bool column_stats_fast(const float (&m)[E], const float (&lv)[E], float (&v)[E],
                                                   float& kl_out, float& epv_out) {
   float inv[E], dl[E];
-  float sv = 0.f, mean = 0.f;
+  float sv = 0.f, mean = 0.f, lvmin = lv[0], lvmax = lv[0];
 #pragma unroll
   for (int e = 0; e < E; ++e) {
-    v[e] = __expf(lv[e]);                       // bnn.py:898
+    v[e] = exp_fast(lv[e]);                     // bnn.py:898
     inv[e] = rcp_approx(v[e] + 1e-10f);
     sv += v[e];
     mean += m[e];
+    lvmin = fminf(lvmin, lv[e]);
+    lvmax = fmaxf(lvmax, lv[e]);
   }
   mean *= (1.0f / E);
-  float s2 = 0.f, d2max = 0.f, vmax = v[0], invmax = inv[0];
+  float s2 = 0.f, amax = 0.f;
 #pragma unroll
   for (int e = 0; e < E; ++e) {
     dl[e] = m[e] - mean;
-    const float q = dl[e] * dl[e];
-    s2 += q;
-    d2max = fmaxf(d2max, q);
-    vmax = fmaxf(vmax, v[e]);
-    invmax = fmaxf(invmax, inv[e]);
+    s2 = fmaf(dl[e], dl[e], s2);
+    amax = fmaxf(amax, fabsf(dl[e]));
   }
+  const float d2max = amax * amax;
   const float base = sv + s2;
   float acc = -0.5f * (float)(E * (E - 1));
 #pragma unroll
@@ -207,8 +215,15 @@ __device__ __forceinline__ bool column_stats_fast(const float (&m)[E], const flo
   }
   kl_out = fmaxf(acc, 0.f) * (1.0f / ((float)(E * (E - 1)) + 1e-10f));   // within 1 ulp of the division
   epv_out = s2 * (1.0f / E);
-  // largest possible pair term: ((mu_i - mu_j)^2 + var_i) / (2 var_j) <= (4 d2max + vmax) * invmax / 2
-  return (4.f * d2max + vmax) * invmax < 1e9f;
+  // Guard (the caller takes the exact path when it fails): log-variances inside (-80, 80) -- fminf / fmaxf drop NaNs, the
+  // comparisons below do not pass them; means finite and moderate (a NaN / Inf / > ~1e15 mean makes s2 NaN or huge); and
+  // the largest possible pair term ((mu_i - mu_j)^2 + var_i) / (2 var_j) <= (4 d2max + vmax) * invmax / 2 below 1e9,
+  // with vmax / invmax taken from the extreme log-variances (exp is monotone).
+  const float vmax = exp_fast(lvmax), invmax = rcp_approx(exp_fast(lvmin) + 1e-10f);
+  bool ok = (lvmin > -80.f) && (lvmax < 80.f) && (s2 < 1e30f);
+#pragma unroll
+  for (int e = 0; e < E; ++e) ok = ok && (lv[e] == lv[e]);     // a NaN log-variance would slip through fminf / fmaxf
+  return ok && (4.f * d2max + vmax) * invmax < 1e9f;
 }
 
 // kPostParts warps share a block of kPostRows rows: warp `part` handles output columns d = part,
@@ -220,15 +235,16 @@ constexpr int kPostRows = 32;
 #ifndef CMBPO_POST_PARTS
 #define CMBPO_POST_PARTS 8
 #endif
-constexpr int kPostParts = CMBPO_POST_PARTS;
+constexpr int kPostParts = CMBPO_POST_PARTS;            // column parts of the 3-D kernel
 constexpr int kPostThreads = kPostRows * kPostParts;
+constexpr int kPostMaxParts = 10;                       // 2-D kernel: the launcher picks 6..10 parts so that D splits evenly
 
 // Block partial sums of the four scalar diagnostics (fake_env.py:213-220); the last block to finish sums
 // the partials in block order (deterministic) and writes the 4 means.
 template <int E>
 __device__ __forceinline__ void finish_scalars(const StepParams& p, const float (&vals)[4], long long n_rows,
                                                int n_slots_out) {
-  __shared__ float red[4][kPostParts];
+  __shared__ float red[4][kPostMaxParts];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -245,7 +261,7 @@ __device__ __forceinline__ void finish_scalars(const StepParams& p, const float 
   }
   // ---- the last block to finish sums the partials in block order (deterministic) -> 4 means
   __shared__ bool s_last;
-  __shared__ double sh[4][kPostParts];
+  __shared__ double sh[4][kPostMaxParts];
   __threadfence();
   __syncthreads();
   if (tid == 0) s_last = atomicAdd(p.ticket, 1u) == gridDim.x - 1;
@@ -273,13 +289,27 @@ __device__ __forceinline__ void finish_scalars(const StepParams& p, const float 
   if (tid == 0) *p.ticket = 0;   // ready for the next launch
 }
 
+// 16-byte asynchronous global -> shared copy (LDGSTS, L1 bypass); completion through commit / wait groups
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Head staging: the E * 2D head lines of a 32-row block (128 bytes each, one per (member, column), inside one 128-row
+// tile of the tile-major scratch) come in with 16-byte asynchronous copies, issued for row block k+1 as soon as the
+// column arithmetic of block k has finished -- the loads are all in flight at once (no registers held) and overlap the
+// block's termination / store tail and the other resident blocks' arithmetic.  The direct-from-global version of this
+// kernel ran at 2.3-2.6 TB/s with load latency and the block barriers as its top stalls (profiles/r01_post_1M_*).
 template <int E, bool OPT>   // OPT: the beyond-reference options (sample_mode / bound_logvar) are compiled in
-__global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post_kernel(const StepParams p) {
-  __shared__ float tile[kPostRows * 64 + 32];  // obs in / next_obs out staging (obs_dim <= 64)
-  __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
+__global__ void __launch_bounds__(kPostMaxParts * kPostRows, 3) step_post_kernel(const StepParams p) {
+  extern __shared__ __align__(16) float dyn_smem[];
+  float* sH = dyn_smem;                                   // [E * 2D][kPostRows] head lines of the current row block
+  float* tile = dyn_smem + (size_t)E * 2 * p.D * kPostRows;   // [kPostRows * obs_dim + 32] obs in / next_obs out staging
+  __shared__ float s_kl[kPostMaxParts][kPostRows], s_epv[kPostMaxParts][kPostRows];
   __shared__ float s_rew[kPostRows];
   __shared__ int s_eidx[kPostRows];
-  __shared__ uint8_t s_flags[kPostParts][kPostRows];
+  __shared__ uint8_t s_flags[kPostMaxParts][kPostRows];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int r = lane, part = warp;
   const int n_parts = (int)(blockDim.x >> 5), n_threads = (int)blockDim.x;   // launch_step_post_EO sizes the block to D
@@ -291,12 +321,22 @@ __global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post_k
   const int n_slots_out = p.per_slot ? E : 1;
   float acc_dkl = 0.f, acc_var = 0.f, acc_rew = 0.f, acc_cost = 0.f;
 
-  for (long long row0 = (long long)blockIdx.x * kPostRows; row0 < n_rows; row0 += (long long)gridDim.x * kPostRows) {
+  const int n_lines = E * 2 * D;
+  // head line L of the row block at row0: scratch element (row0 >> 7) * E*2D*128 + L * 128 + (row0 & 127), 32 floats
+  auto issue_heads = [&](long long row0) {
+    const float* src = p.heads + (size_t)(row0 >> 7) * (size_t)(n_lines * kTileRows) + (size_t)(row0 & (kTileRows - 1));
+    for (int i = tid; i < n_lines * 8; i += n_threads) {
+      const int L = i >> 3, q = i & 7;
+      cp_async16(sH + L * kPostRows + q * 4, src + (size_t)L * kTileRows + q * 4);
+    }
+    cp_async_commit();
+  };
+  const long long row_step = (long long)gridDim.x * kPostRows;
+  if ((long long)blockIdx.x * kPostRows < n_rows) issue_heads((long long)blockIdx.x * kPostRows);
+  for (long long row0 = (long long)blockIdx.x * kPostRows; row0 < n_rows; row0 += row_step) {
     const long long g = row0 + r;
     const bool live = g < n_rows;
-    // this row's entries of the tile-major head scratch (cmbpo_internal.cuh head_index): member e, column j at
-    // hrow[(e * 2D + j) * kTileRows] -- 32-bit offsets, E * 2D * 128 elements per 128-row block
-    const float* hrow = p.heads + (size_t)(g >> 7) * (size_t)(E * 2 * D * kTileRows) + (size_t)(g & (kTileRows - 1));
+    const float* hrow = sH + r;   // member e, column j of this row at hrow[(e * 2D + j) * kPostRows]
     const int rows_here = (int)min((long long)kPostRows, n_rows - row0);
     int eidx = 0;
     if (!p.per_slot && live && part == 0) {   // one warp draws the members; the others pick them up from smem below
@@ -320,6 +360,7 @@ __global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post_k
         const float* src = p.obs + (p.per_slot ? (size_t)so * slot_rows * OD : 0) + (size_t)row0 * OD;
         for (int i = tid; i < rows_here * OD; i += n_threads) tile[i] = src[i];
       }
+      cp_async_wait_all();     // this thread's share of the head lines has landed; the barrier publishes everybody's
       __syncthreads();
       if (!p.per_slot && live) eidx = s_eidx[r];
       bool finite_part = true, lt100_part = true;
@@ -329,8 +370,8 @@ __global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post_k
           const float o = (d < OD) ? tile[r * OD + d] : 0.f;
 #pragma unroll
           for (int e = 0; e < E; ++e) {
-            m[e] = hrow[(e * 2 * D + d) * kTileRows];
-            lv[e] = hrow[(e * 2 * D + D + d) * kTileRows];
+            m[e] = hrow[(e * 2 * D + d) * kPostRows];
+            lv[e] = hrow[(e * 2 * D + D + d) * kPostRows];
           }
           if (d < OD) {
             if (p.per_slot) {
@@ -354,14 +395,8 @@ __global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post_k
               lv[e] = raw + sh;
             }
           }
-          float lvmin = lv[0], lvmax = lv[0];
-#pragma unroll
-          for (int e = 1; e < E; ++e) { lvmin = fminf(lvmin, lv[e]); lvmax = fmaxf(lvmax, lv[e]); }
-          bool weird = !(lvmin > -80.f) || !(lvmax < 80.f);
-#pragma unroll
-          for (int e = 0; e < E; ++e) weird = weird || !(fabsf(m[e]) < 1e18f);
           float kl, epv;
-          if (weird || !column_stats_fast<E>(m, lv, v, kl, epv)) column_stats_rare<E>(m, lv, v, kl, epv);
+          if (!column_stats_fast<E>(m, lv, v, kl, epv)) column_stats_rare<E>(m, lv, v, kl, epv);
           if (so == 0) {
             kl_row += kl; epv_row += epv;
             float sv = 0.f;
@@ -389,6 +424,8 @@ __global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post_k
       }
       s_flags[part][r] = (uint8_t)((finite_part ? 1 : 0) | (lt100_part ? 2 : 0));
       __syncthreads();
+      // every warp is done with the head lines of this block: start fetching the next block's
+      if (so == n_slots_out - 1 && row0 + row_step < n_rows) issue_heads(row0 + row_step);
       if (live && part == 0) {
         RowFeatures f;
         uint8_t fl = 3;
@@ -491,14 +528,8 @@ __global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post3d
             lv[e] = raw + sh;
           }
         }
-        float lvmin = lv[0], lvmax = lv[0];
-#pragma unroll
-        for (int e = 1; e < E; ++e) { lvmin = fminf(lvmin, lv[e]); lvmax = fmaxf(lvmax, lv[e]); }
-        bool weird = !(lvmin > -80.f) || !(lvmax < 80.f);
-#pragma unroll
-        for (int e = 0; e < E; ++e) weird = weird || !(fabsf(m[e]) < 1e18f);
         float kl, epv;
-        if (weird || !column_stats_fast<E>(m, lv, v, kl, epv)) column_stats_rare<E>(m, lv, v, kl, epv);
+        if (!column_stats_fast<E>(m, lv, v, kl, epv)) column_stats_rare<E>(m, lv, v, kl, epv);
         kl_row += kl; epv_row += epv;
         float sv = 0.f;
 #pragma unroll
@@ -653,11 +684,34 @@ static cudaError_t launch_step_post_EO(const StepParams& p, int n_blocks, cudaSt
     step_post3d_kernel<E, OPT><<<n_blocks, kPostThreads, smem, stream>>>(p);
     return cudaGetLastError();
   }
-  // kPostParts column parts per block unless that leaves the last round mostly idle (HalfCheetah, D = 18: 3 rounds
-  // of 8 at 75 % use -> 6 warps x 3 columns); a narrower block that only saves one idle warp measured slower.
-  const int rounds = (p.D + kPostParts - 1) / kPostParts;
-  const int parts = (p.D * 5 >= rounds * kPostParts * 4) ? kPostParts : (p.D + rounds - 1) / rounds;
-  step_post_kernel<E, OPT><<<n_blocks, parts * kPostRows, 0, stream>>>(p);
+  // 6..10 column parts (warps) per 32-row block, chosen so that the D columns split evenly over the warps (every warp
+  // waits at the block's barriers for the slowest one: D = 30 over 8 warps is 4 | 3 columns, 25 % of the arithmetic
+  // phase idle); ties go to more warps (shorter per-thread column chain).  D = 30 -> 10 x 3, D = 18 -> 9 x 2, D = 46 -> 8 x 6.
+  int parts = kPostMaxParts, best = 1 << 30;
+  for (int c = kPostMaxParts; c >= 6; --c) {
+    const int waste = (p.D + c - 1) / c * c - p.D;
+    if (waste < best) { best = waste; parts = c; }
+  }
+  if (const char* ev = getenv("CMBPO_POST_PARTS_RT")) { const int c = atoi(ev); if (c >= 1 && c <= kPostMaxParts) parts = c; }
+  const size_t smem = ((size_t)E * 2 * p.D * kPostRows + (size_t)kPostRows * p.obs_dim + 32) * sizeof(float);
+  static bool attr_set = false;
+  static int num_sms = 0;
+  if (!attr_set) {   // obs_dim <= 64, D <= 65: at most E * 130 head lines + the obs tile
+    cudaError_t e = cudaFuncSetAttribute(step_post_kernel<E, OPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)(((size_t)E * 2 * 65 * kPostRows + kPostRows * 64 + 32) * sizeof(float)));
+    if (e != cudaSuccess) return e;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    attr_set = true;
+  }
+  // persistent grid: one wave of resident blocks (each block prefetches its next row block while it finishes the current)
+  int per_sm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_post_kernel<E, OPT>, parts * kPostRows, smem);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) return cudaErrorInvalidConfiguration;
+  const int cap = per_sm * (num_sms > 0 ? num_sms : 148);
+  step_post_kernel<E, OPT><<<n_blocks < cap ? n_blocks : cap, parts * kPostRows, smem, stream>>>(p);
   return cudaGetLastError();
 }
 
