@@ -74,8 +74,9 @@ constexpr int BAR_W_EMPTY = 8;           // [kMaxSlots]
 constexpr int BAR_A0_FULL = 16;          // [2 streams]
 constexpr int BAR_A0_EMPTY = 18;         // [2]
 constexpr int BAR_D_FULL = 20;           // [2]
-constexpr int BAR_A_READY = 22;          // [2]  epilogue finished a pass: D free, next A in smem
-constexpr int kNumBars = 24;
+constexpr int BAR_A_READY = 22;          // [2]  epilogue finished a pass: every column of the next A tile is in smem
+constexpr int BAR_A_EARLY = 24;          // [2]  accumulator consumed (all tcgen05.ld done) and all but each warp's LAST chunk of the next A tile in smem
+constexpr int kNumBars = 26;
 
 // Debug timeline (compile with -DCMBPO_TRACE): cluster 0's MMA issuer and epilogue warp 4 (leader CTA)
 // append (clock64, tag) pairs to p.trace[role * 2 * kTraceSlots ..]; tools/trace_report.py prints it.
@@ -156,21 +157,42 @@ __device__ __forceinline__ void convert_store16(const uint32_t (&r)[16], int col
 // warps of a sub-partition (two per stream) hand an XU token back and forth, so the pass boundary of one
 // stream (arrive -> MMA -> D_FULL -> first TMEM load) sits in the shadow of the other stream's conversion.
 // CB / CE are compile-time for the common layer widths: the pass is then one straight-line block.
-template <int ACT, int CB, int CE>
-__device__ __forceinline__ void hidden_epilogue_t(uint32_t d_addr, uint32_t a_row, int tok_wait, int tok_pass TR_STAMP_ARG) {
+// "Early" arrival of one epilogue warp (leader CTA's BAR_A_EARLY of the stream): every tcgen05.ld of this warp for the
+// pass has completed -- the accumulator may be overwritten -- and all of its A-tile stores issued so far are visible to
+// the async proxy.  The MMA issuer starts the next layer's k-steps over the finished columns on this signal and keeps
+// the k-steps over each warp's last chunk for BAR_A_READY, so ~11 of 13 k-steps run under the tail of the conversion.
+__device__ __forceinline__ void early_arrive(uint32_t early_bar) {
+  if (!(early_bar & 0x80000000u)) fence_proxy_async_smem();   // (bit 31: timing experiment without the fence)
+  early_bar &= 0x7fffffffu;
+  tc_fence_before();
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive_cluster_light(early_bar, 0);
+}
+
+// The chunk loop is deliberately NOT unrolled beyond its two-chunk body, and there is ONE copy of it for every layer
+// width: the fully unrolled per-width variants of the first version made the kernel 86-105 KB of SASS, far beyond the
+// instruction caches (L0 ~6 KB per sub-partition, L1.5 32 KB), and the rarely executed roles -- above all the MMA
+// issuer -- spent most of their time on instruction-cache misses (200-400 cycles between consecutive trace stamps of
+// straight-line code, profiles/r02_k1_trace_notes.txt).
+template <int ACT>
+__device__ __forceinline__ void hidden_epilogue_range(uint32_t d_addr, int cb, int ce, uint32_t a_row, int tok_wait, int tok_pass,
+                                                      uint32_t early_bar TR_STAMP_ARG) {
   uint32_t ra[16], rb[16];
-  if (CB < CE) tmem_ld16(d_addr + 16 * CB, ra);
+  if (cb < ce) tmem_ld16(d_addr + 16 * cb, ra);
   tmem_wait_ld();
   token_wait(tok_wait);          // first chunk already in registers: the MUFUs start right at the hand-over
   TR_STAMP(0);
-#pragma unroll
-  for (int c = CB; c < CE; c += 2) {
-    if (c > CB) tmem_wait_ld();
-    if (c + 1 < CE) tmem_ld16(d_addr + 16 * (c + 1), rb);
+  if (ce - cb <= 1) early_arrive(early_bar);
+#pragma unroll 1
+  for (int c = cb; c < ce; c += 2) {
+    if (c > cb) tmem_wait_ld();
+    if (c + 1 < ce) tmem_ld16(d_addr + 16 * (c + 1), rb);
+    if (c == ce - 1 && c > cb) early_arrive(early_bar);        // chunk c is the last one: its load has completed
     convert_store16<ACT>(ra, 16 * c, a_row);
-    if (c + 1 < CE) {
+    if (c + 1 < ce) {
       tmem_wait_ld();
-      if (c + 2 < CE) tmem_ld16(d_addr + 16 * (c + 2), ra);
+      if (c + 2 < ce) tmem_ld16(d_addr + 16 * (c + 2), ra);
+      if (c + 1 == ce - 1) early_arrive(early_bar);
       convert_store16<ACT>(rb, 16 * (c + 1), a_row);
     }
   }
@@ -178,47 +200,52 @@ __device__ __forceinline__ void hidden_epilogue_t(uint32_t d_addr, uint32_t a_ro
   token_pass(tok_pass);
 }
 
-// Same for an arbitrary (runtime) chunk range.
-template <int ACT>
-__device__ __forceinline__ void hidden_epilogue_any(uint32_t d_addr, int cb, int ce, uint32_t a_row, int tok_wait, int tok_pass) {
+// Straight-line version for compile-time chunk ranges: the two widths the BASELINE configs and FakeEnv's default use
+// (hidden 200 -> npad 208, hidden 220 -> npad 224).  The rolled loop above measured 19 % slower per pass (the loop
+// back-edge serialises the TMEM-load / MUFU / store interleaving the scheduler finds in straight-line code).
+template <int ACT, int CB, int CE>
+__device__ __forceinline__ void hidden_epilogue_fixed(uint32_t d_addr, uint32_t a_row, int tok_wait, int tok_pass,
+                                                      uint32_t early_bar TR_STAMP_ARG) {
   uint32_t ra[16], rb[16];
-  if (cb < ce) tmem_ld16(d_addr + 16 * cb, ra);
+  tmem_ld16(d_addr + 16 * CB, ra);
   tmem_wait_ld();
   token_wait(tok_wait);
-  for (int c = cb; c < ce; c += 2) {
-    if (c > cb) tmem_wait_ld();
-    if (c + 1 < ce) tmem_ld16(d_addr + 16 * (c + 1), rb);
+  TR_STAMP(0);
+#pragma unroll
+  for (int c = CB; c < CE; c += 2) {
+    if (c > CB) tmem_wait_ld();
+    if (c + 1 < CE) tmem_ld16(d_addr + 16 * (c + 1), rb);
+    if (c == CE - 1) early_arrive(early_bar);
     convert_store16<ACT>(ra, 16 * c, a_row);
-    if (c + 1 < ce) {
+    if (c + 1 < CE) {
       tmem_wait_ld();
-      if (c + 2 < ce) tmem_ld16(d_addr + 16 * (c + 2), ra);
+      if (c + 2 < CE) tmem_ld16(d_addr + 16 * (c + 2), ra);
+      if (c + 1 == CE - 1) early_arrive(early_bar);
       convert_store16<ACT>(rb, 16 * (c + 1), a_row);
     }
   }
+  TR_STAMP(1);
   token_pass(tok_pass);
 }
-
 template <int ACT, int NPAD>
-__device__ __forceinline__ void hidden_epilogue_half(uint32_t d_addr, int half, uint32_t a_row, int tok_wait, int tok_pass TR_STAMP_ARG) {
+__device__ __forceinline__ void hidden_epilogue_width(uint32_t d_addr, int half, uint32_t a_row, int tok_wait, int tok_pass,
+                                                      uint32_t early_bar TR_STAMP_ARG) {
   constexpr int NCH = NPAD / 16, H0 = (NCH + 1) / 2;
-  if (half == 0) hidden_epilogue_t<ACT, 0, H0>(d_addr, a_row, tok_wait, tok_pass TR_STAMP_PASS);
-  else           hidden_epilogue_t<ACT, H0, NCH>(d_addr, a_row, tok_wait, tok_pass TR_STAMP_PASS);
+  static_assert(H0 >= 2 && NCH - H0 >= 2, "every warp needs at least two chunks here");
+  if (half == 0) hidden_epilogue_fixed<ACT, 0, H0>(d_addr, a_row, tok_wait, tok_pass, early_bar TR_STAMP_PASS);
+  else           hidden_epilogue_fixed<ACT, H0, NCH>(d_addr, a_row, tok_wait, tok_pass, early_bar TR_STAMP_PASS);
 }
 
 // ones_col / ones_col+1 of the produced tile are the next layer's bias carriers (constant 1.0):
 // overwritten, after the row's own stores, by the warp whose column range holds them.
 template <int ACT>
 __device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int ones_col, int half, uint32_t a_row,
-                                                int tok_wait, int tok_pass TR_STAMP_ARG) {
+                                                int tok_wait, int tok_pass, uint32_t early_bar TR_STAMP_ARG) {
   const int nch = npad >> 4, h0 = (nch + 1) >> 1;
   const int cb = half ? h0 : 0, ce = half ? nch : h0;
-  switch (npad) {
-    case 208: hidden_epilogue_half<ACT, 208>(d_addr, half, a_row, tok_wait, tok_pass TR_STAMP_PASS); break;   // hidden 200 (BASELINE configs)
-    case 224: hidden_epilogue_half<ACT, 224>(d_addr, half, a_row, tok_wait, tok_pass TR_STAMP_PASS); break;   // hidden 220 (FakeEnv default)
-    case 144: hidden_epilogue_half<ACT, 144>(d_addr, half, a_row, tok_wait, tok_pass TR_STAMP_PASS); break;   // hidden 128 (V / VC critics)
-    case 80:  hidden_epilogue_half<ACT, 80>(d_addr, half, a_row, tok_wait, tok_pass TR_STAMP_PASS); break;    // hidden 64 (CostNN)
-    default:  hidden_epilogue_any<ACT>(d_addr, cb, ce, a_row, tok_wait, tok_pass); break;
-  }
+  if (npad == 208)      hidden_epilogue_width<ACT, 208>(d_addr, half, a_row, tok_wait, tok_pass, early_bar TR_STAMP_PASS);
+  else if (npad == 224) hidden_epilogue_width<ACT, 224>(d_addr, half, a_row, tok_wait, tok_pass, early_bar TR_STAMP_PASS);
+  else                  hidden_epilogue_range<ACT>(d_addr, cb, ce, a_row, tok_wait, tok_pass, early_bar TR_STAMP_PASS);
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
     const int k = ones_col + j;
@@ -231,26 +258,43 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int o
 // Head epilogue for one warp: inverse output scaler on the mean, 2*log(s) shift on the log-variance
 // (bnn.py:878-893); `out` points at this thread's row inside the (tile block, member) region of the
 // tile-major scratch, column stride 128 floats: a warp's store covers 32 consecutive rows.
-__device__ __forceinline__ void head_epilogue(uint32_t d_addr, int c_begin, int c_end, int n_head, const float* s_scale,
-                                              const float* s_shift, float* out, bool live) {
-  for (int c0 = c_begin; c0 < c_end; c0 += 16) {
-    uint32_t r[16];
-    tmem_ld16(d_addr + c0, r);
-    float* colp = out + (size_t)c0 * kTileRows;
-    float sc[16], sh[16];
+// The pass writes no A tile, so both barriers of the stream (BAR_A_EARLY, BAR_A_READY) get this warp's arrival as soon
+// as its last tcgen05.ld has completed: the next pass's MMAs (layer 0 of the next member) do not wait for the global stores.
+__device__ __forceinline__ void head_store16(const uint32_t (&r)[16], int c0, int n_head, const float* s_scale,
+                                             const float* s_shift, float* out, bool live) {
+  float* colp = out + (size_t)c0 * kTileRows;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {   // the constant arrays are padded to a multiple of 16 floats
-      const float4 a = *reinterpret_cast<const float4*>(s_scale + c0 + 4 * i);
-      const float4 b = *reinterpret_cast<const float4*>(s_shift + c0 + 4 * i);
-      sc[4 * i] = a.x; sc[4 * i + 1] = a.y; sc[4 * i + 2] = a.z; sc[4 * i + 3] = a.w;
-      sh[4 * i] = b.x; sh[4 * i + 1] = b.y; sh[4 * i + 2] = b.z; sh[4 * i + 3] = b.w;
-    }
-    tmem_wait_ld();
+  for (int i = 0; i < 4; ++i) {   // the constant arrays are padded to a multiple of 16 floats
+    const float4 a = *reinterpret_cast<const float4*>(s_scale + c0 + 4 * i);
+    const float4 b = *reinterpret_cast<const float4*>(s_shift + c0 + 4 * i);
     if (live) {
-#pragma unroll
-      for (int i = 0; i < 16; ++i)
-        if (c0 + i < n_head) colp[i * kTileRows] = fmaf(__uint_as_float(r[i]), sc[i], sh[i]);
+      if (c0 + 4 * i + 0 < n_head) colp[(4 * i + 0) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 0]), a.x, b.x);
+      if (c0 + 4 * i + 1 < n_head) colp[(4 * i + 1) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 1]), a.y, b.y);
+      if (c0 + 4 * i + 2 < n_head) colp[(4 * i + 2) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 2]), a.z, b.z);
+      if (c0 + 4 * i + 3 < n_head) colp[(4 * i + 3) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 3]), a.w, b.w);
     }
+  }
+}
+__device__ __forceinline__ void head_arrive(uint32_t early_bar, uint32_t ready_bar) {
+  tc_fence_before();
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) {
+    mbar_arrive_cluster_light(early_bar, 0);
+    mbar_arrive_cluster_light(ready_bar, 0);
+  }
+}
+__device__ __forceinline__ void head_epilogue(uint32_t d_addr, int c_begin, int c_end, int n_head, const float* s_scale,
+                                              const float* s_shift, float* out, bool live, uint32_t early_bar, uint32_t ready_bar) {
+  if (c_begin >= c_end) head_arrive(early_bar, ready_bar);
+  for (int c0 = c_begin; c0 < c_end; c0 += 32) {
+    uint32_t ra[16], rb[16];
+    const bool two = c0 + 16 < c_end;
+    tmem_ld16(d_addr + c0, ra);
+    if (two) tmem_ld16(d_addr + c0 + 16, rb);
+    tmem_wait_ld();
+    if (c0 + 32 >= c_end) head_arrive(early_bar, ready_bar);   // the accumulator is in registers: free it before the stores
+    head_store16(ra, c0, n_head, s_scale, s_shift, out, live);
+    if (two) head_store16(rb, c0 + 16, n_head, s_scale, s_shift, out, live);
   }
 }
 
@@ -322,6 +366,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
       mbar_init(bar(BAR_A0_EMPTY + s), 1);                // tcgen05.commit
       mbar_init(bar(BAR_D_FULL + s), 1);                  // tcgen05.commit
       mbar_init(bar(BAR_A_READY + s), 2 * kEpiWarpsPerStream);   // 8 epilogue warps of the stream x 2 CTAs
+      mbar_init(bar(BAR_A_EARLY + s), 2 * kEpiWarpsPerStream);
     }
     fence_mbar_init();
   }
@@ -399,17 +444,44 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
             for (int s = 0; s < 2; ++s) {
               if (s == 1 && !has_y) continue;
               TR(110 + 10 * s + l);
-              if (passes[s] > 0) mbar_wait(bar(BAR_A_READY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
+              if (passes[s] > 0) mbar_wait(bar(BAR_A_EARLY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
               if (l == 0 && new_input) mbar_wait(bar(BAR_A0_FULL + s), stage[s] & 1, p.status, WC_MMA_A0);
               tc_fence_after();
               TR(130 + 10 * s + l);
               const uint32_t a_base = (l == 0) ? smem_u32(smem + sl.off_a0 + s * pl.a0_bytes)
                                                : smem_u32(smem + sl.off_a + s * pl.a_bytes);
               const uint32_t d_tmem = tmem_base + s * kRegionCols;
+              // descriptors of k-step j = descriptor of k-step 0 + j * (256 bytes >> 4) in the address field
+              const uint64_t a_desc0 = make_smem_desc(a_base, 128, sbo), b_desc0 = make_smem_desc(b_base, 128, sbo);
+              // early k-steps: everything but the last chunk of each column half (h0 - 1 and ksteps - 1); layer 0 reads the
+              // staged input tile, which no epilogue writes: all of it is early
+              const int h0 = (ksteps + 1) >> 1;
+              const int e0_end = (l == 0 || p.dbg == 1) ? (p.dbg == 1 && l > 0 ? 0 : ksteps) : h0 - 1;     // [0, e0_end)
+              const int e1_beg = (l == 0 || p.dbg == 1) ? ksteps : h0, e1_end = (l == 0 || p.dbg == 1) ? ksteps : ksteps - 1;   // [e1_beg, e1_end)
               if (elect_one()) {
-                for (int j = 0; j < ksteps; ++j)
-                  mma_bf16_ss<2>(d_tmem, make_smem_desc(a_base + j * 256, 128, sbo),
-                                 make_smem_desc(b_base + j * 256, 128, sbo), idesc, j > 0);
+                for (int j = 0; j < e0_end; ++j)
+                  mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, j > 0);
+                for (int j = e1_beg; j < e1_end; ++j)
+                  mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, (e0_end > 0 || j > e1_beg) ? 1u : 0u);
+              }
+              const uint32_t acc = (e0_end > 0 || e1_end > e1_beg) ? 1u : 0u;   // did the early batch write the accumulator?
+              __syncwarp();
+              TR(170 + 10 * s + l);
+              if (passes[s] > 0) mbar_wait(bar(BAR_A_READY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
+              tc_fence_after();
+              TR(190 + 10 * s + l);
+              if (elect_one()) {
+                if (l > 0) {
+                  if (p.dbg == 1) {
+                    for (int j = 0; j < ksteps; ++j)
+                      mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, j > 0);
+                  } else {
+                    if (h0 - 1 != ksteps - 1)
+                      mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((h0 - 1) * 16), b_desc0 + (uint64_t)((h0 - 1) * 16), idesc, acc);
+                    mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((ksteps - 1) * 16), b_desc0 + (uint64_t)((ksteps - 1) * 16), idesc,
+                                   (acc || h0 - 1 != ksteps - 1) ? 1u : 0u);
+                  }
+                }
                 mma_commit_2sm(bar(BAR_D_FULL + s), 0x3);
                 if (l == 0 && last_use) mma_commit_2sm(bar(BAR_A0_EMPTY + s), 0x3);
               }
@@ -504,7 +576,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
             const bool keep = s == 1 && last_tok_pair && e == e_end - 1 && l == L - 2;
             TR_STAMP_DECL;
             hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, half, a_row, use_tok ? tok_mine : 0,
-                                  (use_tok && !keep) ? tok_other : 0 TR_STAMP_PASS);
+                                  (use_tok && !keep) ? tok_other : 0, bar(BAR_A_EARLY + s) | (p.dbg == 2 ? 0x80000000u : 0u) TR_STAMP_PASS);
 #ifdef CMBPO_TRACE
             if (tr_base && tr_n + 2 <= kTraceSlots) {
               tr_base[2 * tr_n] = g_stamp[0]; tr_base[2 * tr_n + 1] = 260 + l; ++tr_n;
@@ -512,14 +584,15 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
             }
 #endif
             fence_proxy_async_smem();      // generic-proxy smem writes -> visible to tcgen05.mma
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster_light(bar(BAR_A_READY + s), 0);
           } else {
             float* out = p.heads + ((size_t)(blk * E + e) * pl.n_head) * kTileRows + row_in_tile;
             const int hch = lp.npad >> 4, hh0 = (hch + 1) >> 1;   // 16-column chunks of the head, split like the hidden layers
-            head_epilogue(d_addr, 16 * (half ? hh0 : 0), 16 * (half ? hch : hh0), pl.n_head, s_head_scale, s_head_shift, out, live);
+            head_epilogue(d_addr, 16 * (half ? hh0 : 0), 16 * (half ? hch : hh0), pl.n_head, s_head_scale, s_head_shift, out, live,
+                          bar(BAR_A_EARLY + s), bar(BAR_A_READY + s));
           }
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive_cluster_light(bar(BAR_A_READY + s), 0);
           TR(240 + l);
         }
       }

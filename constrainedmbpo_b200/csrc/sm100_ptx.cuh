@@ -109,6 +109,7 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t par
 // Bounded wait.  On expiry: write (code | 0x80000000) to *status and trap, so a protocol
 // bug becomes a launch failure, never a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* status, int code) {
+#pragma unroll 1   // keep the spin loop one instruction-cache line long (it was unrolled 32x at every call site)
   for (uint32_t it = 0; it < SM100_WAIT_LIMIT; ++it) {
     if (mbar_try_wait(bar, parity)) return;
   }
@@ -129,6 +130,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity,
 // the polling thread does not take issue / XU slots from the epilogue warp on the same SM sub-partition.
 __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity, int* status, int code,
                                                   uint32_t sleep_ns = 256) {
+#pragma unroll 1
   for (uint32_t it = 0; it < (SM100_WAIT_LIMIT >> 2); ++it) {
     if (mbar_try_wait(bar, parity)) return;
     __nanosleep(sleep_ns);

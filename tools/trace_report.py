@@ -43,7 +43,8 @@ for name in ("epiX", "epiY"):
             dur[tag - 240].append(t - td); tdone = t
     print(f"{name}: layer: median loop gap | D_FULL wait | epilogue duration (cycles)")
     for k in sorted(dur):
-        print(f"  {k:3d}: gap {int(np.median(gap[k])) if gap[k] else 0:6d}  wait {int(np.median(wait[k])):6d}   epi {int(np.median(dur[k])):6d}   n={len(dur[k])}")
+        med = lambda a: int(np.median(a)) if len(a) else 0
+        print(f"  {k:3d}: gap {med(gap[k]):6d}  wait {med(wait[k]):6d}   epi {med(dur[k]):6d}   n={len(dur[k])}")
 m = roles["mma"]
 if len(m):
     w, iss = collections.defaultdict(list), collections.defaultdict(list)
