@@ -509,7 +509,8 @@ def run_gpu(args, w, wname):
         e2e_s = time.perf_counter() - t0
         n_units += cnt[0]
         assert host_rec.shape[0] == cnt[0] > 0 and float(host_rec[:, 0].abs().sum()) > 0
-        h2d, d2h = int(start_host.numel() * 4), int(drain.W * 4 * per_step_units)
+        assert drain.last_next is not None and float(drain.last_next.abs().sum()) > 0   # compact records + last next_obs
+        h2d, d2h = int(start_host.numel() * 4), drain.bytes_per_rollout(per_step_units)
     te = torch.tensor([e2e_s, float(n_units)], dtype=torch.float64, device=dev)
     if world > 1:
         a = te.clone(); dist.all_reduce(a, op=dist.ReduceOp.MAX)

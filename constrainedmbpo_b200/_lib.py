@@ -92,6 +92,7 @@ class cmbpo_pack_io(C.Structure):
         ("pool_dyn_error_dev", C.c_void_p), ("pool_populated_dev", C.c_void_p),
         ("records_dev", C.c_void_p), ("capacity", C.c_int64), ("count_dev", C.c_void_p),
         ("scratch_dev", C.c_void_p), ("scratch_bytes", C.c_size_t),
+        ("compact", C.c_int32), ("last_next_obs_dev", C.c_void_p),
     ]
 
 
@@ -149,6 +150,7 @@ SYMBOLS = {
     "cmbpo_rollout_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "cmbpo_rollout_advance": (C.c_int, [C.POINTER(cmbpo_rollout_io), C.c_void_p]),
     "cmbpo_record_width": (C.c_int32, [C.c_int32, C.c_int32, C.c_int32]),
+    "cmbpo_record_width_compact": (C.c_int32, [C.c_int32, C.c_int32, C.c_int32]),
     "cmbpo_pack_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "cmbpo_pack_records": (C.c_int, [C.POINTER(cmbpo_pack_io), C.c_void_p]),
     "cmbpo_finish_paths": (C.c_int, [C.POINTER(cmbpo_gae_io), C.c_void_p]),

@@ -462,7 +462,7 @@ extern "C" int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* a
 // ---------------------------------------------------------------------------------------
 namespace cmbpo {
 
-__global__ void __launch_bounds__(kRB) k_pack_count(cmbpo_pack_io io, int* path_off, int* blk_cnt) {
+__global__ void __launch_bounds__(kRB) k_pack_count(cmbpo_pack_io io, int* path_off, int* blk_cnt, int* path_len) {
   const long long b = (long long)blockIdx.x * kRB + threadIdx.x;
   const int T = io.max_path_length;
   int len = 0;
@@ -472,7 +472,7 @@ __global__ void __launch_bounds__(kRB) k_pack_count(cmbpo_pack_io io, int* path_
   }
   int tot;
   const int off = block_exclusive_scan_int(len, &tot);
-  if (b < io.n_paths) path_off[b] = off;
+  if (b < io.n_paths) { path_off[b] = off; path_len[b] = len; }
   if (threadIdx.x == 0) blk_cnt[blockIdx.x] = tot;
 }
 
@@ -520,7 +520,8 @@ __global__ void __launch_bounds__(kRB) k_pack_write(cmbpo_pack_io io, const int*
   if (out0 + blk_total > io.capacity) return;   // caller sized the buffer too small: count_dev still reports the need
   const int E = io.n_members > 1 ? io.n_members : 1;
   const int OD = io.obs_dim, AD = io.act_dim, T = io.max_path_length;
-  const int c0 = E * OD, c1 = c0 + E * AD, c2 = c1 + E * OD, c3 = c2 + E, c4 = c3 + E, c5 = c4 + 1, c6 = c5 + E;
+  // column boundaries of the record; compact records have an empty next_obs block (c1 == c2)
+  const int c0 = E * OD, c1 = c0 + E * AD, c2 = c1 + (io.compact ? 0 : E * OD), c3 = c2 + E, c4 = c3 + E, c5 = c4 + 1, c6 = c5 + E;
   const size_t B = (size_t)io.n_paths;
   float* out = io.records_dev + (size_t)out0 * W;
   // one warp per record (the path lookup is warp-uniform), lanes stride over the record's columns; kU records
@@ -570,6 +571,26 @@ __global__ void __launch_bounds__(kRB) k_pack_write(cmbpo_pack_io io, const int*
 }
 }  // namespace cmbpo
 
+namespace cmbpo {
+// compact records: next_obs of every path's last stored transition, [n_paths][E * OD] (zeros for empty paths)
+__global__ void __launch_bounds__(256) k_pack_last(cmbpo_pack_io io, const int* path_len) {
+  const int E = io.n_members > 1 ? io.n_members : 1, OD = io.obs_dim, T = io.max_path_length;
+  const long long per = (long long)E * OD, total = io.n_paths * per;
+  const size_t B = (size_t)io.n_paths;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long b = i / per;
+    const int j = (int)(i - b * per), e = j / OD, d = j - e * OD;
+    const int L = path_len[b];
+    io.last_next_obs_dev[i] = L > 0 ? __ldg(io.pool_next_obs_dev + (((size_t)e * T + (L - 1)) * B + (size_t)b) * OD + d) : 0.f;
+  }
+}
+}  // namespace cmbpo
+
+extern "C" int32_t cmbpo_record_width_compact(int32_t obs_dim, int32_t act_dim, int32_t n_members) {
+  const int E = n_members > 1 ? n_members : 1;
+  return E * (obs_dim + act_dim + 3) + 1 + 2;
+}
+
 extern "C" int32_t cmbpo_record_width(int32_t obs_dim, int32_t act_dim, int32_t n_members) {
   const int E = n_members > 1 ? n_members : 1;
   return E * (2 * obs_dim + act_dim + 3) + 1 + 2;
@@ -577,7 +598,7 @@ extern "C" int32_t cmbpo_record_width(int32_t obs_dim, int32_t act_dim, int32_t 
 
 extern "C" size_t cmbpo_pack_scratch_bytes(int64_t n_paths) {
   const size_t nb = (size_t)((n_paths + kRB - 1) / kRB) + 1;
-  return (size_t)n_paths * sizeof(int) + nb * (sizeof(int) + sizeof(long long)) + 256;
+  return (size_t)n_paths * 2 * sizeof(int) + nb * (sizeof(int) + sizeof(long long)) + 256;
 }
 
 extern "C" int cmbpo_pack_records(const cmbpo_pack_io* io_, void* stream_) {
@@ -590,11 +611,20 @@ extern "C" int cmbpo_pack_records(const cmbpo_pack_io* io_, void* stream_) {
   // scratch: [nb+1] int64 block offsets | [n_paths] int path offsets | [nb] int block counts
   long long* blk_off = static_cast<long long*>(io.scratch_dev);
   int* path_off = reinterpret_cast<int*>(blk_off + nb + 1);
-  int* blk_cnt = path_off + io.n_paths;
-  if (nb > 0) k_pack_count<<<nb, kRB, 0, stream>>>(io, path_off, blk_cnt);
+  int* path_len = path_off + io.n_paths;
+  int* blk_cnt = path_len + io.n_paths;
+  if (io.compact && !io.last_next_obs_dev) return CMBPO_ERR_ARG;
+  const int W = io.compact ? cmbpo_record_width_compact(io.obs_dim, io.act_dim, io.n_members)
+                           : cmbpo_record_width(io.obs_dim, io.act_dim, io.n_members);
+  if (nb > 0) k_pack_count<<<nb, kRB, 0, stream>>>(io, path_off, blk_cnt, path_len);
   k_pack_scan<<<1, 1024, 0, stream>>>(blk_cnt, nb, blk_off, reinterpret_cast<long long*>(io.count_dev));
-  if (nb > 0) k_pack_write<<<nb * kPackSub, kRB, 0, stream>>>(io, path_off, blk_cnt, blk_off,
-                                                   cmbpo_record_width(io.obs_dim, io.act_dim, io.n_members));
+  if (nb > 0) k_pack_write<<<nb * kPackSub, kRB, 0, stream>>>(io, path_off, blk_cnt, blk_off, W);
+  if (nb > 0 && io.compact) {
+    const long long tot = io.n_paths * (long long)(io.n_members > 1 ? io.n_members : 1) * io.obs_dim;
+    long long gb = (tot + 255) / 256;
+    if (gb > 148 * 16) gb = 148 * 16;
+    k_pack_last<<<(int)gb, 256, 0, stream>>>(io, path_len);
+  }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(g_roll_err, sizeof(g_roll_err), "pack_records: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }
   return CMBPO_OK;

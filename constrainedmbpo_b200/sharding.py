@@ -101,15 +101,19 @@ def broadcast_model_state(model, src=0, group=None):
                      elites=m["elites"])
 
 
-def record_width(obs_dim, act_dim, n_members=1):
-    """Columns of one packed record (``cmbpo_record_width``): the RECORD_FIELDS payload + (path, t)."""
+def record_width(obs_dim, act_dim, n_members=1, compact=False):
+    """Columns of one packed record (``cmbpo_record_width`` / ``_compact``): the RECORD_FIELDS payload + (path, t);
+    compact records carry no next_obs block (see ``reconstruct_next_obs``)."""
     E = max(int(n_members), 1)
-    return E * (2 * obs_dim + act_dim + 3) + 1 + 2
+    return E * ((1 if compact else 2) * obs_dim + act_dim + 3) + 1 + 2
 
 
-def pack_records_cuda(pool: dict, row_offset, obs_dim, act_dim, n_members, out, count, scratch, stream=None):
+def pack_records_cuda(pool: dict, row_offset, obs_dim, act_dim, n_members, out, count, scratch, stream=None,
+                      last_next_obs=None):
     """``cmbpo_pack_records``: the CUDA twin of ``pack_records`` + coords in one launch sequence, no host
-    synchronisation.  ``out`` [capacity, W] fp32, ``count`` int64 [1], ``scratch`` uint8 (all CUDA)."""
+    synchronisation.  ``out`` [capacity, W] fp32, ``count`` int64 [1], ``scratch`` uint8 (all CUDA).
+    ``last_next_obs`` ([n_paths, E*obs] CUDA fp32): write COMPACT records (no next_obs block) plus the next_obs of every
+    path's last transition into it."""
     import ctypes as C
     from . import _lib
     lib = _lib.load()
@@ -124,6 +128,8 @@ def pack_records_cuda(pool: dict, row_offset, obs_dim, act_dim, n_members, out, 
     io.pool_dyn_error_dev, io.pool_populated_dev = pool["dyn_error"].data_ptr(), pool["populated"].data_ptr()
     io.records_dev, io.capacity, io.count_dev = out.data_ptr(), out.shape[0], count.data_ptr()
     io.scratch_dev, io.scratch_bytes = scratch.data_ptr(), scratch.numel()
+    if last_next_obs is not None:
+        io.compact, io.last_next_obs_dev = 1, last_next_obs.data_ptr()
     st = stream if stream is not None else torch.cuda.current_stream(out.device)
     _lib.check(lib.cmbpo_pack_records(C.byref(io), C.c_void_p(st.cuda_stream)))
 
@@ -292,11 +298,46 @@ class HostDrain(PoolGatherer):
     """The same pipeline with the HOST as destination (single rank, no collective): rollout k's packed
     records go to pinned host memory with one ``cudaMemcpyAsync`` on a side stream while rollout k+1
     runs.  ``wait()`` returns ``(host_records[:n], [n])``.  This is what ``ModelBuffer.get`` hands to the
-    policy update when the consumer lives on the host (modelbuffer.py:348-405)."""
+    policy update when the consumer lives on the host (modelbuffer.py:348-405).
+    ``compact=True`` (default): records without the next_obs block + ``last_next_obs`` [B, E*obs] per rollout
+    (``self.last_next`` after ``wait()``; ``unpack_gathered(..., last_next_obs=...)`` rebuilds next_obs) -- 40 % fewer bytes
+    over PCIe, which is what bounds the end-to-end rate of a 1 M-row rollout."""
 
-    def __init__(self, rollout, capacity=None):
+    def __init__(self, rollout, capacity=None, compact=True):
         super().__init__(rollout, 1, None, capacity)
+        self.compact = bool(compact)
         self._host = [None, None]
+        self._host_last = [None, None]
+        self.last_next = None
+
+    def _allocate(self):
+        super()._allocate()
+        if self.compact:
+            ro = self.ro
+            B = ro.pool["populated"].shape[0]
+            self.W = record_width(ro.env.obs_dim, ro.env.act_dim, self.E, compact=True)
+            for b in self._buf:
+                b["rec"] = b["rec"].view(-1)[: b["rec"].shape[0] * self.W].view(b["rec"].shape[0], self.W)
+                b["last"] = torch.empty(B, self.E * ro.env.obs_dim, dtype=torch.float32, device=ro.device)
+
+    def launch(self):
+        if self._buf is None:
+            self._allocate()
+        if not self.compact:
+            return super().launch()
+        ro = self.ro
+        b = self._buf[self._k & 1]
+        main = torch.cuda.current_stream(ro.device)
+        if b["sent"] is not None:
+            main.wait_event(b["sent"])
+        pack_records_cuda(ro.pool, ro.row_offset, ro.env.obs_dim, ro.env.act_dim, self.E, b["rec"], b["count"],
+                          b["scratch"], main, last_next_obs=b["last"])
+        b["count_host"].copy_(b["count"], non_blocking=True)
+        b["packed"].record(main)
+        prev, self._pending = self._pending, b
+        self._k += 1
+        if prev is not None:
+            self._collect(prev)
 
     def _collect(self, b):
         b["packed"].synchronize()
@@ -307,21 +348,61 @@ class HostDrain(PoolGatherer):
         h = self._host[s]
         if h is None or h.shape[0] < n:
             h = self._host[s] = torch.empty(max(n, 1) + max(n, 1) // 8, self.W, dtype=torch.float32, pin_memory=True)
+        if self.compact and self._host_last[s] is None:
+            self._host_last[s] = torch.empty(tuple(b["last"].shape), dtype=torch.float32, pin_memory=True)
         with torch.cuda.stream(self._side):
             self._side.wait_event(b["packed"])
             h[:n].copy_(b["rec"][:n], non_blocking=True)
+            if self.compact:
+                self._host_last[s].copy_(b["last"], non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(self._side)
             b["sent"] = ev
         self.last = (h[:n], [n])
+        self.last_next = self._host_last[s] if self.compact else None
+
+    def bytes_per_rollout(self, n):
+        """device -> host bytes of a rollout with n transitions"""
+        extra = self._buf[0]["last"].numel() * 4 if self.compact else 0
+        return int(n) * self.W * 4 + extra
 
 
-def unpack_gathered(rec: torch.Tensor, obs_dim: int, act_dim: int, n_members: int = 1):
-    """Split the gathered record matrix back into named arrays (+ int64 ``coords`` [n, 2])."""
+def reconstruct_next_obs(obs, path, last_next_obs, row_offset=0):
+    """next_obs of compact records in [path, t] order: inside a path next_obs[t] is obs[t+1] (the sampler feeds
+    next_obs back as the current observation, model_sampler.py:463-467); the last record of a path takes
+    ``last_next_obs[path - row_offset]``.  ``obs`` [n, (E,) obs], ``path`` int [n] (global ids), torch or NumPy."""
+    if isinstance(obs, torch.Tensor):
+        n = obs.shape[0]
+        nxt = torch.empty_like(obs)
+        if n == 0:
+            return nxt
+        same = torch.zeros(n, dtype=torch.bool, device=obs.device)
+        same[:-1] = path[1:] == path[:-1]
+        nxt[:-1] = obs[1:]
+        ends = ~same
+        nxt[ends] = last_next_obs.reshape((last_next_obs.shape[0],) + tuple(obs.shape[1:]))[(path[ends] - row_offset).long()]
+        return nxt
+    import numpy as np
+    n = obs.shape[0]
+    nxt = np.empty_like(obs)
+    if n == 0:
+        return nxt
+    same = np.zeros(n, bool)
+    same[:-1] = path[1:] == path[:-1]
+    nxt[:-1] = obs[1:]
+    nxt[~same] = last_next_obs.reshape((last_next_obs.shape[0],) + obs.shape[1:])[path[~same] - row_offset]
+    return nxt
+
+
+def unpack_gathered(rec: torch.Tensor, obs_dim: int, act_dim: int, n_members: int = 1, last_next_obs=None, row_offset=0):
+    """Split the gathered record matrix back into named arrays (+ int64 ``coords`` [n, 2]).  Compact records
+    (``last_next_obs`` given): next_obs is rebuilt by ``reconstruct_next_obs``."""
     E = max(int(n_members), 1)
+    compact = last_next_obs is not None
     o, out = 0, {}
-    for k, wdt in (("obs", E * obs_dim), ("act", E * act_dim), ("next_obs", E * obs_dim), ("rew", E), ("cost", E),
-                   ("dyn_error", 1), ("term", E)):
+    fields = [("obs", E * obs_dim), ("act", E * act_dim)] + ([] if compact else [("next_obs", E * obs_dim)]) + \
+             [("rew", E), ("cost", E), ("dyn_error", 1), ("term", E)]
+    for k, wdt in fields:
         v = rec[:, o:o + wdt]
         if E > 1 and k != "dyn_error":
             v = v.reshape(v.shape[0], E, -1)
@@ -332,4 +413,6 @@ def unpack_gathered(rec: torch.Tensor, obs_dim: int, act_dim: int, n_members: in
         o += wdt
     out["term"] = out["term"] != 0
     out["coords"] = rec[:, o:o + 2].contiguous().view(torch.int32).to(torch.int64)
+    if compact:
+        out["next_obs"] = reconstruct_next_obs(out["obs"], out["coords"][:, 0], last_next_obs, row_offset)
     return out

@@ -568,7 +568,7 @@ def test_host_drain_pipeline_delivers_every_rollout():
     pol = cm.StubPolicy(29, 8)
     B = 3000
     ro = cm.ModelRollout(fe, T, rollout_mode="uncertainty", dkl_lim=3e-5)
-    drain = sharding.HostDrain(ro)
+    drain = sharding.HostDrain(ro, compact=False)
     want = []
     got = []
     for k in range(4):
@@ -626,3 +626,51 @@ def test_compute_dynamics_dkl_matches_cpu_port():
     # a fresh accumulator (= right after ModelSampler.reset) gives the per-call mean
     fresh = cm.compute_dynamics_dkl(fe, pol, obs2, depth=1, elite_fn=lambda k, n: draws[depth + k][:n])
     assert fresh != pytest.approx(got2, rel=1e-6)
+
+
+@pytest.mark.parametrize("mode", ["uncertainty", "schedule", "iv_gae"])
+def test_compact_records_rebuild_the_full_records(mode):
+    """Compact records (no next_obs block; next_obs[t] = obs[t+1] inside a path, model_sampler.py:463-467, plus the
+    next_obs of every path's last transition): rebuilt on the host they equal the full records bit for bit, through
+    the pack kernel directly and through the HostDrain pipeline (what bench.py's e2e leg times)."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    from constrainedmbpo_b200 import sharding, _lib
+    env, B, T = "antsafe", 2100, 7
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    obs, _ = make_inputs(env, B)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True, seed=2)
+    off = 7000
+    ro = cm.ModelRollout(fe, T, rollout_mode=mode, dkl_lim=2e-5 if mode == "uncertainty" else None, row_offset=off)
+    ro.reset(obs)
+    ro.run(cm.StubPolicy(29, 8))
+    E = 7 if mode == "iv_gae" else 1
+    W, Wc = sharding.record_width(29, 8, E), sharding.record_width(29, 8, E, compact=True)
+    assert Wc == _lib.load().cmbpo_record_width_compact(29, 8, E) == W - E * 29
+    n = int(ro.pool["populated"].sum())
+    assert 0 < n
+    count = torch.zeros(1, dtype=torch.int64, device="cuda")
+    scratch = torch.empty(int(_lib.load().cmbpo_pack_scratch_bytes(B)) + 64, dtype=torch.uint8, device="cuda")
+    full = torch.empty(n, W, device="cuda")
+    sharding.pack_records_cuda(ro.pool, off, 29, 8, E, full, count, scratch)
+    comp = torch.full((n + 2, Wc), -7.0, device="cuda")
+    last = torch.full((B, E * 29), -3.0, device="cuda")
+    sharding.pack_records_cuda(ro.pool, off, 29, 8, E, comp, count, scratch, last_next_obs=last)
+    torch.cuda.synchronize()
+    assert int(count) == n and bool((comp[n:] == -7.0).all())
+    a = sharding.unpack_gathered(full, 29, 8, E)
+    b = sharding.unpack_gathered(comp[:n], 29, 8, E, last_next_obs=last, row_offset=off)
+    for k in a:
+        assert torch.equal(a[k], b[k]), k
+    lens = ro.pool["populated"].sum(1)
+    assert bool((last[lens == 0] == 0).all())        # paths without a stored transition
+    # NumPy twin of the reconstruction (host consumers)
+    nx = sharding.reconstruct_next_obs(b["obs"].cpu().numpy(), b["coords"][:, 0].cpu().numpy(), last.cpu().numpy(), off)
+    assert np.array_equal(nx, a["next_obs"].cpu().numpy())
+    # through the drain pipeline
+    drain = sharding.HostDrain(ro)
+    drain.launch()
+    h, cnt = drain.wait()
+    assert cnt == [n] and h.shape == (n, Wc) and torch.equal(h, comp[:n].cpu())
+    assert torch.equal(drain.last_next, last.cpu())
+    assert drain.bytes_per_rollout(n) == n * Wc * 4 + B * E * 29 * 4
