@@ -378,7 +378,7 @@ def run_gpu(args, w, wname):
     F = flops_per_row(w)
     peaks = measured_peaks()
     steps, warm = args.steps, max(args.warmup, 3)
-    gather = None
+    gather = dgather = None
     dkl_lim = None
 
     if w["kind"] == "predict":
@@ -396,17 +396,33 @@ def run_gpu(args, w, wname):
         if w["mode"] == "uncertainty":  # cmbpo.py:283-285: 5000 archive states, depth = rollout_schedule[2]
             cal = torch.from_numpy(synth_start_states(w, 5000, 99)).to(dev)
             dkl_lim = cm.compute_dynamics_dkl(fe, policy, cal, depth=w["dkl_depth"])
-        ro = cm.ModelRollout(fe, w["T"], rollout_mode=w["mode"], dkl_lim=dkl_lim, row_offset=row0)
+        # N > 1: 'schedule' pools are dense (every path stores every step), so the pool arenas themselves are all-gathered
+        # by copy engines (sharding.DensePoolGatherer, two rollouts alternating so the pulls overlap the next rollout);
+        # ragged pools ('uncertainty', 'iv_gae' terminals) go as packed records (P2PPoolGatherer / PoolGatherer)
+        fmt = args.gather_format if args.gather_format != "auto" else ("dense" if w["mode"] == "schedule" else "records")
+        dense = world > 1 and args.gather != "none" and fmt == "dense"
+        alloc = None
+        if dense:
+            from constrainedmbpo_b200.sharding import DensePoolGatherer, symmetric_pool_alloc
+            alloc = symmetric_pool_alloc()
+        ros = [cm.ModelRollout(fe, w["T"], rollout_mode=w["mode"], dkl_lim=dkl_lim, row_offset=row0, pool_alloc=alloc)
+               for _ in range(2 if dense else 1)]
+        ro = ros[0]
 
         def step_eager():
             ro.reset(start_dev)
             ro.run(policy)
         if args.no_graph:
-            step_fn = step_eager
+            step_fns = [(lambda r=r: (r.reset(start_dev), r.run(policy))) for r in ros]
         else:
-            ro.capture(start_dev, policy)
-            step_fn = ro.replay
-        if world > 1 and args.gather != "none":
+            for r in ros:
+                r.capture(start_dev, policy)
+            step_fns = [r.replay for r in ros]
+        step_fn = step_fns[0]
+        dgather = None
+        if dense:
+            dgather = DensePoolGatherer(ros, world, pack_only=(args.gather == "pack"))
+        elif world > 1 and args.gather != "none":
             from constrainedmbpo_b200.sharding import P2PPoolGatherer, PoolGatherer
             G = P2PPoolGatherer if args.transport == "p2p" else PoolGatherer
             group = None
@@ -415,16 +431,25 @@ def run_gpu(args, w, wname):
                 opts.config.max_ctas = args.nccl_max_ctas
                 group = dist.new_group(pg_options=opts)
             gather = G(ro, world, group=group, pack_only=(args.gather == "pack"))
+        tick = [0]
 
         def one_step():
+            if dgather is not None:
+                i = tick[0] & 1
+                tick[0] += 1
+                dgather.before_rollout(i)
+                step_fns[i]()
+                dgather.launch(i)
+                return
             step_fn()
             if gather is not None:
                 gather.launch()
 
     for _ in range(warm):
         one_step()
-    if gather is not None:
-        gather.wait()
+    for g_ in (gather, dgather):
+        if g_ is not None:
+            g_.wait()
     torch.cuda.synchronize()
     model.check_status()
     if w["kind"] == "rollout":
@@ -436,7 +461,7 @@ def run_gpu(args, w, wname):
         fwd_launches = (len(w["hidden"]) + 1) * ((rows + 131071) // 131072) if wide else 1
         # per sampler step: stub policy, input staging, ensemble forward (fused: 1 launch; wide: one per FC layer and
         # 131072-row slab), step post, 3 bookkeeping kernels (decide+scan, store+scan, compact)
-        kernels_per_step = (6 + fwd_launches) * (w["T"] - 1) + (3 if gather is not None else 0)
+        kernels_per_step = (6 + fwd_launches) * (w["T"] - 1) + (3 if gather is not None else 0)   # dense gather: copy engines only
 
     # ---- timed region: K steps, device-resident inputs ------------------------------------------------------------
     clocks = ClockSampler(local_rank)
@@ -449,8 +474,9 @@ def run_gpu(args, w, wname):
     ev0.record()
     for _ in range(steps):
         one_step()
-    if gather is not None:
-        gather.wait()
+    for g_ in (gather, dgather):
+        if g_ is not None:
+            g_.wait()
     ev1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -551,8 +577,10 @@ def run_gpu(args, w, wname):
                     "rows_forwarded_per_step": rows_forwarded, "cuda_graph": w["kind"] == "rollout" and not args.no_graph,
                     "timed_region_s": ms * 1e-3,
                     "parallelism": f"rows sharded x{args.gpus} ({w['scaling']} scaling), weights replicated" +
-                                   (f", all-gather of transitions into the replicated pool (transport={args.transport}, "
-                                    f"gather={args.gather})" if gather is not None else "")},
+                                   (f", all-gather of transitions into the replicated pool (records, transport={args.transport}, "
+                                    f"gather={args.gather})" if gather is not None else "") +
+                                   (f", all-gather of the pool arenas into the replicated pool (dense: one copy-engine pull per "
+                                    f"peer over NVLink peer mappings, double-buffered rollouts, gather={args.gather})" if dgather is not None else "")},
         "clocks": clk,
         "e2e": {"value": e2e_val, "unit": "transitions/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "host_cpus_bound": numa},
@@ -584,6 +612,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--gather", default="full", choices=["full", "pack", "none"],
                     help="N>1 diagnosis: full = pack + all-gather (the measured path), pack = packing only, none")
+    ap.add_argument("--gather-format", default="auto", choices=["auto", "dense", "records"],
+                    help="N>1: dense = pull whole pool arenas (default for 'schedule'), records = packed populated transitions")
     ap.add_argument("--transport", default="p2p", choices=["nccl", "p2p"],
                     help="N>1: NCCL all-gather kernels, or copy-engine pulls over symmetric-memory peer mappings")
     ap.add_argument("--nccl-max-ctas", type=int, default=0, help="N>1: NCCL max_ctas of the gather group (0 = default)")

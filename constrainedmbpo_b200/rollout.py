@@ -127,7 +127,7 @@ class ModelRollout:
     layout ``[B, max_path_length, dim]`` with row = start-state index (modelbuffer.py:45-114)."""
 
     def __init__(self, env, max_path_length, rollout_mode="schedule", dkl_lim=None, max_samples=None,
-                 row_offset=0, perm_fn=None, value_fn=None):
+                 row_offset=0, perm_fn=None, value_fn=None, pool_alloc=None):
         if rollout_mode not in MODES:
             raise ValueError("rollout_mode must be 'schedule', 'uncertainty' or 'iv_gae' (cmbpo.py:89)")
         if rollout_mode == "uncertainty" and dkl_lim is None:
@@ -149,6 +149,9 @@ class ModelRollout:
         # values are compacted along with their observations.  With it the rollout fills val / cval pools and the
         # finish records (finish_ptr, last_val, last_cval) that ``finish()`` hands to cmbpo_finish_paths.
         self.value_fn = value_fn
+        # pool_alloc(nbytes) -> uint8 CUDA tensor: where the pool arena lives (default: torch.zeros).  The multi-GPU
+        # gather passes a symmetric-memory allocator so that peers can pull the pool over NVLink.
+        self.pool_alloc = pool_alloc
         self.device = env.device
         self.B = 0
         self._lib = _lib.load()
@@ -163,16 +166,32 @@ class ModelRollout:
         # The tensors are the reference's logical [B, T, .] arrays (views); their STORAGE is time-major
         # [T, B, .] so that one sampler step's stores are contiguous (include/cmbpo_b200.h, pool pointers).
         n = len(E)
-        vec = lambda w: z(*E, T, B, w).transpose(n, n + 1)
-        sca = lambda dt=torch.float32: z(*E, T, B, dt=dt).transpose(n, n + 1)
-        self.pool = {
-            "obs": vec(OD), "act": vec(AD), "next_obs": vec(OD),
-            "rew": sca(), "cost": sca(), "term": sca(torch.uint8),
-            "dyn_error": z(T, B).t(), "populated": z(T, B, dt=torch.uint8).t(),
-        }
+        spec = [("obs", E + (T, B, OD), torch.float32), ("act", E + (T, B, AD), torch.float32),
+                ("next_obs", E + (T, B, OD), torch.float32), ("rew", E + (T, B), torch.float32),
+                ("cost", E + (T, B), torch.float32), ("term", E + (T, B), torch.uint8),
+                ("dyn_error", (T, B), torch.float32), ("populated", (T, B), torch.uint8)]
+        if self.value_fn is not None:
+            spec += [("val", E + (T, B), torch.float32), ("cval", E + (T, B), torch.float32)]
+        # one arena for all pool arrays (256-byte aligned fields): a single fill clears it, and the multi-GPU gather moves
+        # a rank's whole pool with one peer copy (sharding.DensePoolGatherer; ``pool_alloc`` then hands out symmetric memory)
+        self.pool_layout, off = {}, 0
+        for name, shape, dt in spec:
+            nbytes = int(np.prod(shape)) * (4 if dt == torch.float32 else 1)
+            self.pool_layout[name] = (off, shape, dt)
+            off += (nbytes + 255) // 256 * 256
+        if self.pool_alloc is not None:
+            self.pool_arena = self.pool_alloc(off)
+            self.pool_arena.zero_()
+        else:
+            self.pool_arena = torch.zeros(off, dtype=torch.uint8, device=dev)
+        self.pool = {}
+        for name, (o, shape, dt) in self.pool_layout.items():
+            nbytes = int(np.prod(shape)) * (4 if dt == torch.float32 else 1)
+            st = self.pool_arena[o:o + nbytes].view(dt).view(shape)
+            m = len(shape) - 2 - (1 if name in ("obs", "act", "next_obs") else 0)     # index of the T axis
+            self.pool[name] = st.transpose(m, m + 1)
         self.cur = [torch.empty(*E, B, OD, dtype=torch.float32, device=dev) for _ in range(2)]
         if self.value_fn is not None:
-            self.pool["val"], self.pool["cval"] = sca(), sca()
             self.vcur = [[torch.zeros(*E, B, dtype=torch.float32, device=dev) for _ in range(2)] for _ in range(2)]
             self.finish_ptr = torch.zeros(B, dtype=torch.int32, device=dev)
             self.last_val, self.last_cval = z(*E, B), z(*E, B)
@@ -199,8 +218,7 @@ class ModelRollout:
         if B != self.B:
             self._allocate(B, OD)
         else:
-            for v in self.pool.values():
-                v.zero_()
+            self.pool_arena.zero_()
             self.dkl_accum.zero_()
         self.alive_hist.zero_()
         self.cur[0].copy_(start_obs, non_blocking=True)   # 'iv_gae': broadcast = np.tile(obs[None], (E,1,1))

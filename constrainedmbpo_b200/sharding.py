@@ -9,6 +9,7 @@ CPU tensors in the tests); no arithmetic of the path happens in this file.
 """
 from __future__ import annotations
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -416,3 +417,103 @@ def unpack_gathered(rec: torch.Tensor, obs_dim: int, act_dim: int, n_members: in
     if compact:
         out["next_obs"] = reconstruct_next_obs(out["obs"], out["coords"][:, 0], last_next_obs, row_offset)
     return out
+
+
+def symmetric_pool_alloc(group=None):
+    """``pool_alloc`` for ``ModelRollout``: the pool arena in symmetric memory (``torch.distributed._symmetric_memory``)
+    so that every rank of ``group`` can read it through its NVLink peer mapping.  Returns the allocator; the arenas it
+    handed out are rendezvoused by ``DensePoolGatherer``."""
+    import torch.distributed._symmetric_memory as symm
+
+    def alloc(nbytes):
+        dev = torch.device("cuda", torch.cuda.current_device())
+        n = torch.tensor([int(nbytes)], dtype=torch.int64, device=dev)      # symmetric buffers: same size on every rank
+        dist.all_reduce(n, op=dist.ReduceOp.MAX, group=group)
+        return symm.empty(int(n.item()), dtype=torch.uint8, device=dev)
+    return alloc
+
+
+class DensePoolGatherer:
+    """All-gather of the model pool ITSELF, for rollouts whose pools are dense ('schedule' mode: every
+    path stores every step): each rank's pool arena -- all fields, time-major, one contiguous block
+    (``ModelRollout.pool_arena``) -- is pulled by every other rank with ONE copy-engine transfer per peer over the NVLink
+    peer mapping.  No pack kernel, no count exchange, no host synchronisation, no SM taken from the rollout kernels.
+
+    ``rollouts``: two ``ModelRollout`` objects (same shape, ``pool_alloc=symmetric_pool_alloc(group)``) used alternately,
+    so the pulls of rollout k overlap rollout k+1, which writes the other arena.  ``launch(i)`` right after rollout i was
+    enqueued; ``wait()`` drains.  ``pools(i)`` -> ``{field: [one logical [B_shard, T, ...] view per rank]}`` of the gathered
+    pool of buffer i (modelbuffer.py:45-114): their concatenation over the ranks is the single-device pool when the shards
+    are contiguous row blocks.  Only the peers' arenas are copied (the own shard is already resident), and only the first
+    T-1 time blocks of each field (column T-1 is never populated, quirk Q8).  ``pack_only`` (measurement aid): no copies."""
+
+    def __init__(self, rollouts, world, group=None, pack_only=False):
+        import torch.distributed._symmetric_memory as symm
+        assert len(rollouts) == 2
+        self.ros, self.world, self.pack_only = rollouts, world, pack_only
+        group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(group)
+        ro = rollouts[0]
+        dev = ro.device
+        self.nbytes = ro.pool_arena.numel()
+        assert rollouts[1].pool_arena.numel() == self.nbytes and ro.pool_layout == rollouts[1].pool_layout
+        self._h = [symm.rendezvous(r.pool_arena, group) for r in rollouts]
+        self._peer = [[h.get_buffer(r, (self.nbytes,), torch.uint8, 0) for r in range(world)] for h in self._h]
+        self.full = [torch.zeros(world, self.nbytes, dtype=torch.uint8, device=dev) for _ in range(2)]   # column T-1 stays zero
+        self._side = torch.cuda.Stream(device=dev)
+        self._done = [None, None]      # rollout i's arena may be overwritten again after this event
+        self._ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self._launched = [False, False]
+
+    def before_rollout(self, i):
+        """Call before enqueueing rollout i: its arena must not be overwritten while peers still pull the previous one."""
+        if self._done[i] is not None:
+            torch.cuda.current_stream(self.ros[i].device).wait_event(self._done[i])
+
+    def _segments(self, ro):
+        """Byte ranges of the arena worth moving: a path stores at most T-1 transitions (model_sampler.py:437, quirk Q8),
+        so column T-1 of every time-major [T][B][.] field is never populated -- only the first T-1 time blocks travel
+        (fields with a leading member axis are moved whole)."""
+        segs = []
+        for name, (o, shape, dt) in ro.pool_layout.items():
+            nb = int(np.prod(shape)) * (4 if dt == torch.float32 else 1)
+            lead = len(shape) - 2 - (1 if name in ("obs", "act", "next_obs") else 0)     # axes before T
+            if lead == 0 and shape[0] > 1:
+                nb = nb // shape[0] * (shape[0] - 1)
+            segs.append((o, nb))
+        return segs
+
+    def launch(self, i):
+        main = torch.cuda.current_stream(self.ros[i].device)
+        self._ready[i].record(main)
+        segs = self._segments(self.ros[i])
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(self._ready[i])
+            self._h[i].barrier(channel=0)                 # every rank's rollout i is complete
+            if not self.pack_only:
+                for k in range(1, self.world):            # the peers, staggered by rank; the own shard stays where it is
+                    r = (self.rank + k) % self.world
+                    for o, nb in segs:
+                        self.full[i][r, o:o + nb].copy_(self._peer[i][r][o:o + nb], non_blocking=True)
+            self._h[i].barrier(channel=1)                 # every rank has pulled: the arenas may be reused
+            ev = torch.cuda.Event()
+            ev.record(self._side)
+            self._done[i] = ev
+        self._launched[i] = True
+
+    def wait(self):
+        self._side.synchronize()
+
+    def pools(self, i):
+        """``{field: [per-rank logical pool views]}``: entry r is rank r's ``[B_shard, T, ...]`` pool (the own rank's entry
+        is the rollout's own arena -- it is not copied); valid until rollout i runs again."""
+        ro = self.ros[i]
+        out = {}
+        for name, (o, shape, dt) in ro.pool_layout.items():
+            nb = int(np.prod(shape)) * (4 if dt == torch.float32 else 1)
+            m = len(shape) - 2 - (1 if name in ("obs", "act", "next_obs") else 0)
+            views = []
+            for r in range(self.world):
+                src = ro.pool_arena if r == self.rank else self.full[i][r]
+                views.append(src[o:o + nb].view(dt).view(tuple(shape)).transpose(m, m + 1))
+            out[name] = views
+        return out

@@ -22,3 +22,4 @@ def test_two_gpu_gather_equals_single_gpu():
                         os.path.join(ROOT, "tools", "nccl_gather_check.py")], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("equal_to_single_gpu=True") == 3, r.stdout
+    assert r.stdout.count("dense_equal=True") == 3, r.stdout          # DensePoolGatherer, all three modes

@@ -42,6 +42,19 @@ def main():
         ok = ok and same
         if rank == 0:
             print(f"{mode}: gathered {tuple(full.shape)} counts={counts} equal_to_single_gpu={same}", flush=True)
+    # dense gather of the pool arenas themselves (sharding.DensePoolGatherer): equal shards, double-buffered rollouts
+    Bd = 20_000 // world * world
+    for mode, T, lim in (("schedule", 6, None), ("uncertainty", 8, 3e-5), ("iv_gae", 4, None)):
+        fe = cm.FakeEnv(cm.SimpleEnv(29, 8), env, num_networks=7, num_elites=5, hidden_dims=hidden,
+                        cares_about_cost=True, device=str(dev), seed=3)
+        if rank == 0:
+            fe._model.load_state([w.astype(np.float32) for w in p.weights], [b.astype(np.float32) for b in p.biases],
+                                 scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
+        sharding.broadcast_model_state(fe._model, src=0)
+        same = _run_dense(fe, obs_all[:Bd], T, mode, lim, rank, world, dev)
+        ok = ok and same
+        if rank == 0:
+            print(f"{mode}: dense pool gather dense_equal={same}", flush=True)
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()
@@ -65,6 +78,42 @@ def _run(fe, obs, lo, T, mode, lim, world, n):
     torch.cuda.synchronize()
     rec, coords = sharding.pack_records(ro.pool, lo)
     return torch.cat([rec, coords.to(torch.int32).view(torch.float32)], dim=1), None
+
+
+def _run_dense(fe, obs_all, T, mode, lim, rank, world, dev):
+    perms = [np.random.default_rng(100 + t).permutation(7) for t in range(T + 1)]
+    pol = cm.StubPolicy(fe.obs_dim, fe.act_dim, device=fe.device)
+    Bs = obs_all.shape[0] // world
+    lo = rank * Bs
+    alloc = sharding.symmetric_pool_alloc()
+    ros = [cm.ModelRollout(fe, T, rollout_mode=mode, dkl_lim=lim, row_offset=lo, perm_fn=lambda t: perms[t], pool_alloc=alloc)
+           for _ in range(2)]
+    obs = torch.from_numpy(obs_all[lo:lo + Bs]).to(dev)
+    for r in ros:                       # first reset allocates (collective: same order on every rank)
+        fe._rng_offset = 0
+        r.reset(obs)
+    g = sharding.DensePoolGatherer(ros, world)
+    for k in range(4):                  # pipelined: the pulls of rollout k overlap rollout k+1 in the other arena
+        i = k & 1
+        g.before_rollout(i)
+        fe._rng_offset = 0
+        ros[i].reset(obs)
+        ros[i].run(pol)
+        g.launch(i)
+    g.wait()
+    ref = cm.ModelRollout(fe, T, rollout_mode=mode, dkl_lim=lim, row_offset=0, perm_fn=lambda t: perms[t])
+    fe._rng_offset = 0
+    ref.reset(torch.from_numpy(obs_all).to(dev))
+    ref.run(pol)
+    torch.cuda.synchronize()
+    same = True
+    for i in (0, 1):
+        got = g.pools(i)
+        for name, v in ref.pool.items():
+            per_member = mode == "iv_gae" and name not in ("dyn_error", "populated")     # [E, B, T, ...]: B is axis 1
+            x = torch.cat(got[name], dim=1 if per_member else 0)
+            same = same and x.shape == v.shape and bool(torch.equal(x, v))
+    return same
 
 
 if __name__ == "__main__":
