@@ -58,6 +58,7 @@ class cmbpo_step_io(C.Structure):
         ("ep_var_dev", C.c_void_p), ("scalars_dev", C.c_void_p),
         ("workspace_dev", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("sample_mode", C.c_int32), ("bound_logvar", C.c_int32), ("max_logvar", C.c_float), ("min_logvar", C.c_float),
+        ("rng_offset_dev", C.c_void_p),
     ]
 
 
@@ -149,6 +150,7 @@ SYMBOLS = {
     "cmbpo_profile_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cmbpo_rollout_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "cmbpo_rollout_advance": (C.c_int, [C.POINTER(cmbpo_rollout_io), C.c_void_p]),
+    "cmbpo_rollout_finish_all": (C.c_int, [C.POINTER(cmbpo_rollout_io), C.c_void_p]),
     "cmbpo_record_width": (C.c_int32, [C.c_int32, C.c_int32, C.c_int32]),
     "cmbpo_record_width_compact": (C.c_int32, [C.c_int32, C.c_int32, C.c_int32]),
     "cmbpo_pack_scratch_bytes": (C.c_size_t, [C.c_int64]),

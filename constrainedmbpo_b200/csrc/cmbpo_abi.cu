@@ -478,6 +478,7 @@ extern "C" int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream_) 
   sp.elite_idx = io->elite_idx_dev; sp.row_ids = io->row_id_dev;
   sp.elites = h->elites_dev; sp.n_elites = h->n_elites;
   sp.seed = io->seed; sp.rng_offset = io->rng_offset; sp.row_offset = io->row_offset;
+  sp.rng_offset_dev = reinterpret_cast<const unsigned long long*>(io->rng_offset_dev);
   sp.noise = io->noise_dev;
   sp.sample_mode = io->sample_mode; sp.bound_logvar = io->bound_logvar;
   sp.max_logvar = io->max_logvar; sp.min_logvar = io->min_logvar;

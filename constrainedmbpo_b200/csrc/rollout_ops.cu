@@ -407,6 +407,42 @@ __global__ void __launch_bounds__(kRB) k_compact_dev(cmbpo_rollout_io io, const 
 }
 }  // namespace cmbpo
 
+namespace cmbpo {
+// finish_all_paths (model_sampler.py:550-570): one thread per live row; the last thread block clears the alive count
+__global__ void __launch_bounds__(kRB) k_finish_all(cmbpo_rollout_io io) {
+  RolloutState* st = static_cast<RolloutState*>(io.state_dev);
+  const int n = st->n_alive, ptr = st->ptr;
+  const int E = (io.mode == 2 && io.n_members > 1) ? io.n_members : 1;
+  const size_t cap = (size_t)io.n_paths;
+  for (int i = blockIdx.x * kRB + threadIdx.x; i < n; i += gridDim.x * kRB) {
+    const int pid = static_cast<const int*>(io.path_id_dev)[i];
+    io.finish_ptr_dev[pid] = ptr;
+    for (int e = 0; e < E; ++e) {
+      io.last_val_dev[e * cap + pid] = io.val_cur_dev[e * cap + i];
+      io.last_cval_dev[e * cap + pid] = io.cval_cur_dev[e * cap + i];
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  __shared__ bool s_last;
+  if (threadIdx.x == 0) s_last = atomicAdd(&st->ticket_a, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) { st->n_alive = 0; st->finished = 1; st->ticket_a = 0; }
+}
+}  // namespace cmbpo
+
+extern "C" int cmbpo_rollout_finish_all(const cmbpo_rollout_io* io_, void* stream_) {
+  if (!io_ || !io_->state_dev || !io_->path_id_dev || !io_->finish_ptr_dev || !io_->val_cur_dev || !io_->cval_cur_dev ||
+      !io_->last_val_dev || !io_->last_cval_dev) return CMBPO_ERR_ARG;
+  const cmbpo_rollout_io io = *io_;
+  if (io.n_paths <= 0) return CMBPO_OK;
+  long long nb = (io.n_paths + kRB - 1) / kRB;
+  if (nb > 148 * 8) nb = 148 * 8;
+  // every block reads n_alive before the last one clears it: blocks only pass the ticket after their loop
+  k_finish_all<<<(int)nb, kRB, 0, (cudaStream_t)stream_>>>(io);
+  return cudaGetLastError() == cudaSuccess ? CMBPO_OK : CMBPO_ERR_CUDA;
+}
+
 // One sampler step after env.step: see the file header.  `n_paths` bounds the grid; the live row
 // count is read from state_dev on the device, so the host never synchronises inside a rollout.
 extern "C" int cmbpo_rollout_advance(const cmbpo_rollout_io* io_, void* stream_) {

@@ -314,6 +314,7 @@ __global__ void __launch_bounds__(kPostMaxParts * kPostRows, 3) step_post_kernel
   const int r = lane, part = warp;
   const int n_parts = (int)(blockDim.x >> 5), n_threads = (int)blockDim.x;   // launch_step_post_EO sizes the block to D
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
+  const unsigned long long rng_off = p.rng_offset + (p.rng_offset_dev ? *p.rng_offset_dev : 0ull);
   // 3-D mode: member slot e of obs/act/next_obs/rew/term/cost starts at row e * capacity (the array shapes
   // stay at capacity while the live row count shrinks during an 'iv_gae' rollout)
   const long long slot_rows = p.n_rows;
@@ -345,7 +346,7 @@ __global__ void __launch_bounds__(kPostMaxParts * kPostRows, 3) step_post_kernel
       } else {  // random elite per row (bnn.py:437-439), counter-based so sharding cannot change it
         uint32_t rnd[4];
         const unsigned long long ctr = (unsigned long long)(p.row_offset + (p.row_ids ? (long long)p.row_ids[g] : g));
-        philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), (uint32_t)p.rng_offset, 0u,
+        philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), (uint32_t)rng_off, 0u,
                       (uint32_t)p.seed, (uint32_t)(p.seed >> 32), rnd);
         eidx = p.elites[__umulhi(rnd[0], (uint32_t)p.n_elites)];
       }
@@ -410,7 +411,7 @@ __global__ void __launch_bounds__(kPostMaxParts * kPostRows, 3) step_post_kernel
             const float vs = p.per_slot ? pick<E>(v, so) : pick<E>(v, eidx);
             const unsigned long long grow = (unsigned long long)(p.row_offset + (p.row_ids ? (long long)p.row_ids[g] : g));
             const float z = p.noise ? p.noise[(p.per_slot ? (size_t)so * slot_rows * D : 0) + (size_t)g * D + d]
-                                    : philox_normal(grow, (uint32_t)(so * 4096 + d + 1), (uint32_t)p.rng_offset, p.seed);
+                                    : philox_normal(grow, (uint32_t)(so * 4096 + d + 1), (uint32_t)rng_off, p.seed);
             x = fmaf(z, sqrtf(vs), x);
           }
           if (d < OD) {
@@ -485,6 +486,7 @@ __global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post3d
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int r = lane, part = warp;
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
+  const unsigned long long rng_off = p.rng_offset + (p.rng_offset_dev ? *p.rng_offset_dev : 0ull);
   const long long slot_rows = p.n_rows;            // member stride = capacity
   const int D = p.D, OD = p.obs_dim;
   const int tile_elems = kPostRows * OD;
@@ -542,7 +544,7 @@ __global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post3d
           if (p.noise) x = fmaf(p.noise[((size_t)e * slot_rows + g) * D + d], sqrtf(v[e]), x);
           else if (OPT && p.sample_mode == 1) {
             const unsigned long long grow = (unsigned long long)(p.row_offset + (p.row_ids ? (long long)p.row_ids[g] : g));
-            x = fmaf(philox_normal(grow, (uint32_t)(e * 4096 + d + 1), (uint32_t)p.rng_offset, p.seed), sqrtf(v[e]), x);
+            x = fmaf(philox_normal(grow, (uint32_t)(e * 4096 + d + 1), (uint32_t)rng_off, p.seed), sqrtf(v[e]), x);
           }
           if (d < OD) {
             tiles[e * tile_elems + r * OD + d] = x;   // own element only

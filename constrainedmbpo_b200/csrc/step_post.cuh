@@ -22,6 +22,7 @@ struct StepParams {
   const int* elites;         // elite list (bnn.py:428-431), used when elite_idx == nullptr
   int n_elites;
   unsigned long long seed, rng_offset;
+  const unsigned long long* rng_offset_dev;   // optional device word added to rng_offset (graph replays advance it)
   long long row_offset;      // global index of local row 0 (sharding must not change the draw)
   const int* row_ids;        // optional [B] path id per row (replaces g in row_offset + g)
   const float* noise;        // optional standard normals [B][D] / [E][B][D]; nullptr = reference behaviour

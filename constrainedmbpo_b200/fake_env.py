@@ -18,6 +18,7 @@ from .static import resolve as _resolve_static
 
 
 class FakeEnv:
+    supports_rng_offset_dev = True   # step_device takes the device Philox-stream word of ModelRollout
 
     def __init__(self, true_environment,
                  static_fns, num_networks=7,
@@ -96,11 +97,12 @@ class FakeEnv:
 
     # ---- device-level step ------------------------------------------------------------------
     def step_device(self, obs, act, elite_idx=None, perm=None, noise=None, n_rows_dev=None,
-                    row_ids=None, want_ep_var=True, out=None):
+                    row_ids=None, want_ep_var=True, out=None, rng_offset_dev=None):
         """CUDA tensors in, dict of CUDA tensors out.  ``elite_idx`` (int32 [B]) injects the
         ``random_inds`` draw; None -> in-kernel Philox over the elite list.  ``perm`` injects the
         ``forward_shuffle`` permutation of the 3-D path.  ``n_rows_dev``: optional int32 device
-        scalar with the live row count (rollout loop; shapes stay at capacity)."""
+        scalar with the live row count (rollout loop; shapes stay at capacity).  ``rng_offset_dev``: optional uint64 /
+        int64 device word the kernel adds to the Philox stream id (a captured rollout advances it per replay)."""
         m = self._model
         assert obs.dim() == act.dim()  # fake_env.py:132
         ndim = obs.dim()
@@ -150,6 +152,8 @@ class FakeEnv:
             io.noise_dev = noise.data_ptr()
         io.seed, io.rng_offset, io.row_offset = self._seed, self._rng_offset, 0
         self._rng_offset += 1
+        if rng_offset_dev is not None:
+            io.rng_offset_dev = rng_offset_dev.data_ptr()
         io.sample_mode = 1 if self.sample_noise else 0
         if self.logvar_bound is not None:
             io.bound_logvar, io.max_logvar, io.min_logvar = 1, self.logvar_bound[0], self.logvar_bound[1]

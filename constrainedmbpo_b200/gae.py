@@ -62,11 +62,43 @@ def finish_paths(rew, val, cost, cval, finish_ptr, last_val, last_cval, rollout_
     return res
 
 
-def normalize_advantages(adv, cadv, populated, ret=None, cret=None):
+def normalize_advantages_sharded(adv, cadv, populated, ret=None, cret=None, group=None):
+    """The same normalisation when the pool is row-sharded over the ranks of ``group``: the reference's statistics are
+    GLOBAL (``mpi_statistics_scalar`` all-reduces sum / count, then the squared deviations,
+    softlearning/policies/safe_utils/mpi_tools.py:71-93), so the five partial sums and the count are all-reduced (fp64,
+    6 + 1 numbers) and every rank standardises its shard with the global float32 mean / population std.  Plain torch ops
+    on the tensors' device (NCCL for CUDA shards, gloo for the CPU tests): this runs once per rollout, not per step."""
+    import torch.distributed as dist
+    m = populated.bool()
+    f64 = torch.float64
+    zero = torch.zeros((), dtype=f64, device=adv.device)
+    s = torch.stack([adv[m].to(f64).sum(), cadv[m].to(f64).sum(),
+                     ret[m].to(f64).sum() if ret is not None else zero, cret[m].to(f64).sum() if cret is not None else zero,
+                     m.sum().to(f64)])
+    dist.all_reduce(s, group=group)
+    n = s[4]
+    if float(n) <= 0:
+        return torch.zeros(6, dtype=torch.float32, device=adv.device)
+    mean = (s[0] / n).to(torch.float32)
+    cmean = (s[1] / n).to(torch.float32)
+    sq = ((adv[m] - mean).to(f64) ** 2).sum().reshape(1)
+    dist.all_reduce(sq, group=group)
+    std = torch.sqrt(sq[0] / n).to(torch.float32)
+    adv[m] = (adv[m] - mean) / (std + 1e-8)      # modelbuffer.py:361
+    cadv[m] = cadv[m] - cmean                    # :367
+    return torch.stack([mean, std, cmean, (s[2] / n).to(torch.float32), (s[3] / n).to(torch.float32), n.to(torch.float32)])
+
+
+def normalize_advantages(adv, cadv, populated, ret=None, cret=None, group=None):
     """``ModelBuffer.get``'s advantage trick (modelbuffer.py:356-372) in place on CUDA tensors of one common layout
     (e.g. the ``[B, T]`` views ``finish_paths`` returns): ``adv`` standardised with the float32 mean / population std
     over the populated entries, ``cadv`` centred only.  Returns the statistics as a CUDA float32 tensor
-    ``[adv_mean, adv_std, cadv_mean, ret_mean, cret_mean, n]``."""
+    ``[adv_mean, adv_std, cadv_mean, ret_mean, cret_mean, n]``.  ``group``: the process group the rows are sharded
+    over -- statistics then are global (``normalize_advantages_sharded``)."""
+    if group is not None:
+        import torch.distributed as dist
+        if dist.get_world_size(group) > 1:
+            return normalize_advantages_sharded(adv, cadv, populated, ret, cret, group)
     lib = _lib.load()
     dev = adv.device
     base = lambda t: t if t.is_contiguous() else (t.t() if t.dim() == 2 and t.t().is_contiguous() else None)

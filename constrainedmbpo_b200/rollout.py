@@ -127,7 +127,7 @@ class ModelRollout:
     layout ``[B, max_path_length, dim]`` with row = start-state index (modelbuffer.py:45-114)."""
 
     def __init__(self, env, max_path_length, rollout_mode="schedule", dkl_lim=None, max_samples=None,
-                 row_offset=0, perm_fn=None, value_fn=None, pool_alloc=None):
+                 row_offset=0, perm_fn=None, value_fn=None, pool_alloc=None, sharded=False):
         if rollout_mode not in MODES:
             raise ValueError("rollout_mode must be 'schedule', 'uncertainty' or 'iv_gae' (cmbpo.py:89)")
         if rollout_mode == "uncertainty" and dkl_lim is None:
@@ -138,6 +138,13 @@ class ModelRollout:
         self.dkl_lim = float(dkl_lim) if dkl_lim is not None else 0.0
         self.max_samples = int(max_samples) if max_samples else 0
         self.row_offset = int(row_offset)
+        # `sharded`: this rollout holds one row block of a batch that is split over several ranks.  The max_samples cap cuts
+        # "the first n still-certain rows" in GLOBAL row order against the GLOBAL sample count (model_sampler.py:327-332);
+        # a rank-local cap would admit up to world x the budget and cut different rows than the single-device run, so the
+        # combination is refused (the cap needs an exclusive prefix of the per-step certain counts over the ranks).
+        if (sharded or self.row_offset) and self.max_samples:
+            raise NotImplementedError("max_samples with a row-sharded rollout: the cap is defined on the global row order "
+                                      "(model_sampler.py:327-332); run the capped rollout on one device")
         # 'iv_gae' only: perm_fn(step) -> the forward_shuffle permutation FakeEnv.step draws per call
         # (fake_env.py:309-316, global NumPy RNG upstream).  It is a launch argument, so a captured graph
         # replays the permutations drawn at capture time.
@@ -154,6 +161,11 @@ class ModelRollout:
         self.pool_alloc = pool_alloc
         self.device = env.device
         self.B = 0
+        # Philox stream base of this rollout, on the device: every reset() advances it by T, so a captured graph draws
+        # fresh elite members (and Gaussian noise in sample_mode 1) on every replay instead of the counters baked in at
+        # capture time (the per-step host counter FakeEnv._rng_offset is a launch argument and stays frozen in a graph).
+        # Reproducible runs / shard-vs-single comparisons: ``rng_base.zero_()`` before ``reset``.
+        self.rng_base = torch.zeros(1, dtype=torch.int64, device=self.device)
         self._lib = _lib.load()
 
     def _allocate(self, B, OD):
@@ -224,6 +236,7 @@ class ModelRollout:
         self.cur[0].copy_(start_obs, non_blocking=True)   # 'iv_gae': broadcast = np.tile(obs[None], (E,1,1))
         self.pid[0].copy_(self._arange)
         self.state.copy_(self._state_init)
+        self.rng_base.add_(self.T)
         self.flip = 0
         self.steps_done = 0
         self.gae = None
@@ -245,8 +258,9 @@ class ModelRollout:
         perm = None
         if self.mode == "iv_gae" and self.perm_fn is not None:
             perm = self.perm_fn(self.steps_done)
+        kw = {"rng_offset_dev": self.rng_base} if getattr(env, "supports_rng_offset_dev", False) else {}
         o = env.step_device(cur, act, n_rows_dev=n_dev, row_ids=row_ids, want_ep_var=False, out=self._step_out,
-                            perm=perm)
+                            perm=perm, **kw)
         io = _lib.cmbpo_rollout_io()
         io.n_paths, io.max_path_length, io.mode = self.B, self.T, MODES[self.mode]
         io.dkl_lim, io.max_samples, io.step_index = self.dkl_lim, self.max_samples, self.steps_done
@@ -286,6 +300,48 @@ class ModelRollout:
         for _ in range(max(n, 1)):
             self.step(policy)
         return self.pool
+
+    def run_until(self, policy, min_alive_ratio=0.1, sample_budget=None, samples_added=0, max_steps=None):
+        """The rollout loop as ``CMBPO._train`` runs it (mbpo/algorithms/cmbpo.py:339-348): ``sample`` until the stored
+        transitions reach 99 % of ``sample_budget`` (``approx_model_batch``; returns ``keep_rolling = False`` then), or
+        ``alive_ratio <= min_alive_ratio``, or nothing is alive.  One host read of the device counters per sampler step
+        (the reference reads ``info['alive_ratio']`` every step as well); paths still alive afterwards are bootstrapped by
+        ``finish_all_paths`` / ``finish``.  Returns ``(steps_run, keep_rolling)``."""
+        n = self.T - 1 if max_steps is None else min(max_steps, self.T - 1)
+        keep_rolling = True
+        steps = 0
+        for _ in range(max(n, 1)):
+            self.step(policy)
+            steps += 1
+            n_alive, _, total, finished = self.counters()
+            if sample_budget is not None and total + samples_added >= 0.99 * sample_budget:
+                keep_rolling = False
+                break
+            if finished or n_alive / max(self.B, 1) <= min_alive_ratio:
+                break
+        return steps, keep_rolling
+
+    @property
+    def alive_ratio(self):
+        """``info['alive_ratio']`` of the last ``sample`` (model_sampler.py:471) -- synchronises."""
+        return self.counters()[0] / max(self.B, 1)
+
+    def finish_all_paths(self):
+        """``ModelSampler.finish_all_paths`` (model_sampler.py:550-570): every path still alive is finished at the
+        current pool column with V / VC of its current state as bootstrap values.  No host synchronisation; a no-op when
+        nothing is alive (which is the case after a full ``run``)."""
+        if self.value_fn is None:
+            raise RuntimeError("finish_all_paths() needs the critic values: construct ModelRollout with value_fn=...")
+        io = _lib.cmbpo_rollout_io()
+        io.n_paths, io.max_path_length, io.mode = self.B, self.T, MODES[self.mode]
+        io.n_members = self.env.num_networks if self.mode == "iv_gae" else 0
+        io.state_dev, io.path_id_dev = self.state.data_ptr(), self.pid[self.flip].data_ptr()
+        vc_ = self.vcur[self.flip]
+        io.val_cur_dev, io.cval_cur_dev = vc_[0].data_ptr(), vc_[1].data_ptr()
+        io.finish_ptr_dev = self.finish_ptr.data_ptr()
+        io.last_val_dev, io.last_cval_dev = self.last_val.data_ptr(), self.last_cval.data_ptr()
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(self._lib.cmbpo_rollout_finish_all(C.byref(io), stream))
 
     def capture(self, start_obs, policy):
         """Record ``reset(start_obs)`` + ``run(policy)`` into one CUDA graph.  ``start_obs`` must be a
@@ -353,6 +409,7 @@ class ModelRollout:
         if self.value_fn is None:
             raise RuntimeError("finish() needs the critic values: construct ModelRollout with value_fn=...")
         from .gae import finish_paths
+        self.finish_all_paths()      # paths the rollout loop left alive (early exit): bootstrap them first
         p = self.pool
         res = finish_paths(p["rew"], p["val"], p["cost"], p["cval"], self.finish_ptr, self.last_val, self.last_cval,
                            self.mode, gamma=gamma, lam=lam, cost_gamma=cost_gamma, cost_lam=cost_lam,
@@ -364,7 +421,7 @@ class ModelRollout:
         self.gae = res
         return res
 
-    def get_batch(self, model_ind=0, **finish_kw):
+    def get_batch(self, model_ind=0, group=None, **finish_kw):
         """``ModelBuffer.get`` (modelbuffer.py:348-405) for the finished rollout: ``finish()`` (GAE / iv-GAE + horizon
         trim), the advantage normalisation over the populated entries, then the populated-mask selection in
         [path, t] order.  'iv_gae': per-member arrays are taken from member ``model_ind`` (:376-381).  Returns
@@ -372,7 +429,7 @@ class ModelRollout:
         from .gae import normalize_advantages
         res = self.gae if self.gae is not None else self.finish(model_ind=model_ind, **finish_kw)
         pop = res.get("populated_trimmed", self.pool["populated"])
-        stats = normalize_advantages(res["adv"], res["cadv"], pop, ret=res["ret"], cret=res["cret"])
+        stats = normalize_advantages(res["adv"], res["cadv"], pop, ret=res["ret"], cret=res["cret"], group=group)
         mask = pop.bool()
         iv = self.mode == "iv_gae"
         pick = lambda v: (v[model_ind] if iv else v)[mask]

@@ -133,6 +133,9 @@ typedef struct cmbpo_step_io {
   int32_t sample_mode;
   int32_t bound_logvar;
   float max_logvar, min_logvar;
+  /* Optional device word added to rng_offset by the kernel (NULL = 0): a launch captured in a CUDA graph draws from a
+   * fresh Philox stream on every replay when the graph also advances this word (ModelRollout.reset does). */
+  const uint64_t* rng_offset_dev;
 } cmbpo_step_io;
 int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream);
 
@@ -204,6 +207,13 @@ typedef struct cmbpo_rollout_io {
 } cmbpo_rollout_io;
 size_t cmbpo_rollout_scratch_bytes(int64_t n_paths);
 int cmbpo_rollout_advance(const cmbpo_rollout_io* io, void* stream);
+/* ModelSampler.finish_all_paths (softlearning/samplers/model_sampler.py:550-570): the rollout loop was left with
+ * paths still alive (CMBPO._train breaks on alive_ratio <= 0.1 or on the sample budget, mbpo/algorithms/cmbpo.py:339-348);
+ * every live path is finished at the current pool column with V(current state), VC(current state) as bootstrap values
+ * (it did not terminate by the environment).  Uses state_dev, path_id_dev, val_cur_dev / cval_cur_dev (values of the
+ * current states of the live rows), finish_ptr_dev, last_val_dev / last_cval_dev, n_paths, mode, n_members of `io`;
+ * afterwards no path is alive (state: n_alive = 0, finished = 1).  A no-op when nothing is alive. */
+int cmbpo_rollout_finish_all(const cmbpo_rollout_io* io, void* stream);
 
 /* Populated transitions of a model pool -> one dense fp32 record matrix in [path, t] order: what
  * ModelBuffer.get selects with populated_mask (softlearning/replay_pools/modelbuffer.py:348-405), laid out

@@ -140,7 +140,7 @@ class FakePolicy:
     def random_vc_inds(self, n): return self.rng.integers(0, N_V, n)
 
 
-def run(mode, B, T, seed, max_samples=None, dkl_lim=None, max_unc=(5.5, 5.5)):
+def run(mode, B, T, seed, max_samples=None, dkl_lim=None, max_unc=(5.5, 5.5), max_calls=None):
     ModelSampler, ModelBuffer = load_reference()
     np.random.seed(seed)   # ModelBuffer.model_ind / sampler.model_inds use the global RNG
     env, pol = FakeEnv(seed), FakePolicy(seed + 10)
@@ -170,12 +170,16 @@ def run(mode, B, T, seed, max_samples=None, dkl_lim=None, max_unc=(5.5, 5.5)):
     alive_hist = []
     n_calls = 0
     while pool.alive_paths.any():
+        if max_calls is not None and n_calls >= max_calls:
+            break      # CMBPO._train leaves the loop early on alive_ratio / the sample budget (cmbpo.py:339-348):
+                       # finish_all_paths then bootstraps every still-alive path (model_sampler.py:550-570)
         alive_hist.append(int(pool.alive_paths.sum()))
         sampler.sample(max_samples=max_samples)
         n_calls += 1
         assert n_calls <= T + 2
+    alive_at_break = np.array(pool.alive_paths)
     sampler.finish_all_paths()
-    out = dict(start_obs=obs, mode=mode, T=T, E=E, max_samples=max_samples or 0, dkl_lim=dkl_lim or 0.0,
+    out = dict(alive_at_break=alive_at_break, start_obs=obs, mode=mode, T=T, E=E, max_samples=max_samples or 0, dkl_lim=dkl_lim or 0.0,
                model_ind=pool.model_ind, alive_hist=np.array(alive_hist), n_steps=len(env.calls),
                total_samples=sampler._total_samples, path_length=sampler._path_length,
                dyn_dkl_path=sampler._dyn_dkl_path, ptr=pool.ptr, max_uncertainty=np.array(max_unc),
@@ -204,10 +208,13 @@ def main():
         "schedule": dict(mode="schedule", B=48, T=7, seed=21, max_samples=200),
         "uncertainty": dict(mode="uncertainty", B=64, T=9, seed=22, dkl_lim=None),
         "iv_gae": dict(mode="iv_gae", B=40, T=7, seed=23, max_unc=(1.6, 1.6)),
+        # the rollout loop left after 3 sampler steps with paths still alive: finish_all_paths does real work
+        "earlybreak": dict(mode="uncertainty", B=56, T=10, seed=24, dkl_lim=None, max_calls=3),
     }
     # calibrate a dkl limit that cuts paths at different lengths: mean first-step path KL x 3
     probe = run("schedule", 64, 3, 22)
     cfgs["uncertainty"]["dkl_lim"] = float(np.mean(probe["step0_dkl"]) * 3.0)
+    cfgs["earlybreak"]["dkl_lim"] = float(np.mean(probe["step0_dkl"]) * 6.0)
     for name, kw in cfgs.items():
         out = run(**kw)
         path = os.path.join(HERE, f"sampler_{name}.npz")

@@ -674,3 +674,88 @@ def test_compact_records_rebuild_the_full_records(mode):
     assert cnt == [n] and h.shape == (n, Wc) and torch.equal(h, comp[:n].cpu())
     assert torch.equal(drain.last_next, last.cpu())
     assert drain.bytes_per_rollout(n) == n * Wc * 4 + B * E * 29 * 4
+
+
+def test_early_exit_then_finish_all_paths_matches_reference_golden():
+    """The rollout loop left after 3 of 9 sampler steps with 48 of 56 paths alive (CMBPO._train breaks on alive_ratio or
+    the sample budget, cmbpo.py:339-348), then ``finish_all_paths`` (model_sampler.py:550-570): finish columns, bootstrap
+    values V / VC(current state), GAE outputs and ``get()`` against the reference's REAL sampler + pool
+    (tests/golden/sampler_earlybreak.npz)."""
+    import os
+    import torch
+    import constrainedmbpo_b200 as cm
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "sampler_earlybreak.npz"), allow_pickle=False)
+    n_steps = int(g["n_steps"])
+    steps = [{k: g[f"step{i}_{k}"] for k in ("cur", "act", "next_obs", "rew", "term", "cost", "dkl", "ep_var")}
+             for i in range(n_steps)]
+    B, T, E = g["start_obs"].shape[0], int(g["T"]), int(g["E"])
+    assert n_steps == 3 and g["alive_at_break"].sum() > 0.8 * B
+    wv, wc, prng = _golden_policy_values(24)
+    v_inds, vc_inds = prng.integers(0, 3, B), prng.integers(0, 3, B)
+    env = _ReplayEnv(steps, B, E, False)
+
+    def value_fn(obs, n_dev, pid):
+        n = int(n_dev.item())
+        o, ids = obs[:n].cpu().numpy(), pid[:n].cpu().numpy()
+        v, vc = np.zeros(B, np.float32), np.zeros(B, np.float32)
+        if n:
+            allv = np.sin(o @ wv[:3].T).T.astype(np.float32)
+            allc = (0.5 * np.sin(o @ wc[:3].T).T.astype(np.float32) + 0.5)
+            v[:n], vc[:n] = allv[v_inds[ids], np.arange(n)], allc[vc_inds[ids], np.arange(n)]
+        return torch.from_numpy(v).cuda(), torch.from_numpy(vc).cuda()
+
+    ro = cm.ModelRollout(env, T, rollout_mode="uncertainty", dkl_lim=float(g["dkl_lim"]), value_fn=value_fn)
+    ro.reset(g["start_obs"])
+    done, keep = ro.run_until(lambda cur, n_dev: env.policy(cur, n_dev), min_alive_ratio=0.0, max_steps=n_steps)
+    assert done == n_steps and keep
+    n_alive, ptr, total, finished = ro.counters()
+    assert n_alive == int(g["alive_at_break"].sum()) and not finished and total == int(g["total_samples"])
+    assert abs(ro.alive_ratio - n_alive / B) < 1e-12
+    res = ro.finish(gamma=float(g["gamma"]), lam=float(g["lam"]), cost_gamma=float(g["cost_gamma"]), cost_lam=float(g["cost_lam"]),
+                    cares_about_cost=True)
+    assert ro.counters()[0] == 0 and ro.counters()[3] == 1          # finish_all_paths left nothing alive
+    got = ro.get(numpy=True)
+    close = lambda a, b: a.shape == b.shape and np.allclose(a, b, rtol=1e-6, atol=1e-7)
+    assert np.array_equal(got["finish_ptr"], g["finish_ptr"])
+    assert close(got["last_val"], g["last_val"]) and close(got["last_cval"], g["last_cval"])
+    alive = g["alive_at_break"]
+    assert (got["finish_ptr"][alive] == n_steps).all() and (got["last_val"][alive] != 0).all()
+    assert np.array_equal(got["populated"], g["populated_mask"])
+    for ours, ref in (("adv", "adv_buf"), ("ret", "ret_buf"), ("cadv", "cadv_buf"), ("cret", "cret_buf")):
+        assert np.allclose(res[ours].cpu().numpy(), g[ref], rtol=2e-5, atol=2e-6), ours
+    batch, stats = ro.get_batch()
+    b = {k: v.cpu().numpy() for k, v in batch.items()}
+    assert np.array_equal(b["obs"], g["get_obs"])
+    for ours, ref in (("adv", "get_adv"), ("cadv", "get_cadv"), ("ret", "get_ret"), ("cret", "get_cret")):
+        assert np.allclose(b[ours], g[ref], rtol=5e-5, atol=5e-6), ours
+    # finish_all_paths on a rollout that ran to the end changes nothing
+    fp = ro.finish_ptr.clone()
+    ro.finish_all_paths()
+    assert torch.equal(fp, ro.finish_ptr)
+
+
+def test_graph_replays_draw_fresh_philox_streams():
+    """The Philox stream base lives in a device word that every reset() advances (ModelRollout.rng_base): replays of one
+    captured graph draw different elite members per (row, step) -- the host-side launch counters are frozen at capture
+    time -- and restoring the word reproduces a replay bit for bit."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    env, B, T = "halfcheetah", 4000, 5
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    obs, _ = make_inputs(env, B)
+    fe = build_cuda_env(p, env, HIDDEN, seed=3)
+    ro = cm.ModelRollout(fe, T, rollout_mode="schedule")
+    start = torch.from_numpy(obs).cuda()
+    ro.capture(start, cm.StubPolicy(17, 6))
+    ro.replay(); torch.cuda.synchronize()
+    a = ro.pool["next_obs"].clone()
+    base = ro.rng_base.clone()
+    ro.replay(); torch.cuda.synchronize()
+    b = ro.pool["next_obs"].clone()
+    assert int(ro.rng_base) == int(base) + T
+    changed = (a[:, 0] != b[:, 0]).any(dim=-1).float().mean().item()
+    assert 0.6 < changed < 0.95, changed          # 5 elites: a row keeps its member with probability 1/5
+    assert torch.equal(ro.pool["obs"][:, 0], torch.from_numpy(obs).cuda())      # same start states
+    ro.rng_base.copy_(base)
+    ro.replay(); torch.cuda.synchronize()
+    assert torch.equal(ro.pool["next_obs"], b)

@@ -95,3 +95,65 @@ def test_two_rank_gather_equals_single_process():
     assert np.array_equal(rec, ref_rec.numpy())
     un = sharding.unpack_records(torch.from_numpy(rec), 29, 8)
     assert un["obs"].shape == (rec.shape[0], 29) and un["term"].dtype == torch.bool
+
+
+def _norm_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from constrainedmbpo_b200.gae import normalize_advantages
+    from constrainedmbpo_b200.sharding import shard_bounds
+    adv, cadv, ret, cret, pop = _norm_data()
+    lo, hi = shard_bounds(adv.shape[0], world, rank)
+    a, c = torch.from_numpy(adv[lo:hi].copy()), torch.from_numpy(cadv[lo:hi].copy())
+    stats = normalize_advantages(a, c, torch.from_numpy(pop[lo:hi].astype(np.uint8)), ret=torch.from_numpy(ret[lo:hi]),
+                                 cret=torch.from_numpy(cret[lo:hi]), group=dist.group.WORLD)
+    q.put((rank, a.numpy(), c.numpy(), stats.numpy()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _norm_data():
+    r = np.random.default_rng(5)
+    B, T = 90, 7
+    lens = r.integers(0, T, B)
+    pop = np.arange(T)[None, :] < lens[:, None]
+    f = lambda s: (r.standard_normal((B, T)) * s + 0.3).astype(np.float32)
+    return f(2.0), f(0.5), f(1.0), f(1.0), pop
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_advantage_normalisation_is_global():
+    """ModelBuffer.get normalises with GLOBAL statistics (mpi_statistics_scalar, mpi_tools.py:71-93): two ranks holding
+    row shards must produce what one process produces on the whole pool (oracle.normalize_advantages)."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_norm_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = sorted([q.get(timeout=240) for _ in range(world)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    adv, cadv, ret, cret, pop = _norm_data()
+    ra, rc, am, asd, cm_ = orc.normalize_advantages(adv, cadv, pop)
+    a = np.concatenate([g[1] for g in got]); c = np.concatenate([g[2] for g in got])
+    assert np.allclose(a[pop], ra[pop], rtol=2e-6, atol=2e-6) and np.allclose(c[pop], rc[pop], rtol=2e-6, atol=2e-6)
+    assert np.array_equal(a[~pop], adv[~pop])                     # unpopulated entries untouched
+    for g in got:                                                 # every rank reports the same global statistics
+        assert np.allclose(g[3][:3], [am, asd, cm_], rtol=1e-6) and g[3][5] == pop.sum()
+        assert np.isclose(g[3][3], ret[pop].mean(), rtol=1e-6)
+
+
+def test_sharded_rollout_refuses_max_samples():
+    import constrainedmbpo_b200 as cm
+
+    class E:
+        device = "cpu"
+    with pytest.raises(NotImplementedError, match="global row order"):
+        cm.ModelRollout(E(), 10, rollout_mode="schedule", max_samples=100, sharded=True)
+    with pytest.raises(NotImplementedError):
+        cm.ModelRollout(E(), 10, rollout_mode="schedule", max_samples=100, row_offset=500)
+    assert cm.ModelRollout(E(), 10, rollout_mode="schedule", max_samples=100).max_samples == 100

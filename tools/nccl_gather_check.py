@@ -69,6 +69,7 @@ def _run(fe, obs, lo, T, mode, lim, world, n):
     g = G(ro, world) if world else None
     for _ in range(n):
         fe._rng_offset = 0
+        ro.rng_base.zero_()             # same Philox streams in every repetition and in the single-GPU reference
         ro.reset(obs)
         ro.run(pol)
         if g:
@@ -97,12 +98,14 @@ def _run_dense(fe, obs_all, T, mode, lim, rank, world, dev):
         i = k & 1
         g.before_rollout(i)
         fe._rng_offset = 0
+        ros[i].rng_base.zero_()
         ros[i].reset(obs)
         ros[i].run(pol)
         g.launch(i)
     g.wait()
     ref = cm.ModelRollout(fe, T, rollout_mode=mode, dkl_lim=lim, row_offset=0, perm_fn=lambda t: perms[t])
     fe._rng_offset = 0
+    ref.rng_base.zero_()
     ref.reset(torch.from_numpy(obs_all).to(dev))
     ref.run(pol)
     torch.cuda.synchronize()
