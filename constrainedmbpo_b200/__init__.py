@@ -16,6 +16,7 @@ from .static import STATIC, StaticFns  # noqa: F401
 from .spaces import SimpleEnv  # noqa: F401
 from .rollout import CriticValues, DklAccumulators, ModelRollout, StubPolicy, compute_dynamics_dkl  # noqa: F401
 from .gae import finish_paths, normalize_advantages  # noqa: F401
+from .policy import GaussianActor  # noqa: F401
 
 __all__ = ["construct_model", "BNN", "FC", "FakeEnv", "ModelRollout", "STATIC", "StaticFns",
-           "SimpleEnv", "StubPolicy", "compute_dynamics_dkl", "DklAccumulators", "TensorStandardScaler", "CmbpoError", "load_library"]
+           "SimpleEnv", "StubPolicy", "GaussianActor", "compute_dynamics_dkl", "DklAccumulators", "TensorStandardScaler", "CmbpoError", "load_library"]

@@ -43,6 +43,7 @@ class cmbpo_predict_io(C.Structure):
         ("n_rows", C.c_int64), ("ndim", C.c_int32), ("agg", C.c_int32),
         ("mean_dev", C.c_void_p), ("var_dev", C.c_void_p),
         ("workspace_dev", C.c_void_p), ("workspace_bytes", C.c_size_t),
+        ("n_rows_dev", C.c_void_p),
     ]
 
 
@@ -94,6 +95,16 @@ class cmbpo_pack_io(C.Structure):
         ("records_dev", C.c_void_p), ("capacity", C.c_int64), ("count_dev", C.c_void_p),
         ("scratch_dev", C.c_void_p), ("scratch_bytes", C.c_size_t),
         ("compact", C.c_int32), ("last_next_obs_dev", C.c_void_p),
+    ]
+
+
+class cmbpo_actor_io(C.Structure):
+    _fields_ = [
+        ("mu_dev", C.c_void_p), ("log_std_dev", C.c_void_p), ("noise_dev", C.c_void_p),
+        ("n_rows", C.c_int64), ("n_rows_dev", C.c_void_p), ("act_dim", C.c_int32), ("n_slots", C.c_int32),
+        ("deterministic", C.c_int32), ("row_id_dev", C.c_void_p), ("row_offset", C.c_int64),
+        ("seed", C.c_uint64), ("rng_offset", C.c_uint64), ("rng_offset_dev", C.c_void_p),
+        ("pi_dev", C.c_void_p), ("logp_pi_dev", C.c_void_p),
     ]
 
 
@@ -150,6 +161,7 @@ SYMBOLS = {
     "cmbpo_profile_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cmbpo_rollout_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "cmbpo_rollout_advance": (C.c_int, [C.POINTER(cmbpo_rollout_io), C.c_void_p]),
+    "cmbpo_actor_head": (C.c_int, [C.POINTER(cmbpo_actor_io), C.c_void_p]),
     "cmbpo_rollout_finish_all": (C.c_int, [C.POINTER(cmbpo_rollout_io), C.c_void_p]),
     "cmbpo_record_width": (C.c_int32, [C.c_int32, C.c_int32, C.c_int32]),
     "cmbpo_record_width_compact": (C.c_int32, [C.c_int32, C.c_int32, C.c_int32]),

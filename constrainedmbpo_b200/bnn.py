@@ -380,9 +380,10 @@ class BNN:
             self._ws = torch.empty(int(need * 1.25) + 1024, dtype=torch.uint8, device=self.device)
         return self._ws
 
-    def predict_device(self, segments, ndim, agg, want_var=True):
+    def predict_device(self, segments, ndim, agg, want_var=True, n_rows_dev=None):
         """Device-level predict on a list of CUDA fp32 segments whose concatenation along the
-        last axis is the input (no concat copy is made).  Returns CUDA tensors."""
+        last axis is the input (no concat copy is made).  Returns CUDA tensors.  ``n_rows_dev``: optional int32 device
+        scalar with the live row count (rollout loop: shapes stay at capacity, rows beyond it are not computed)."""
         if not self.finalized:
             raise RuntimeError("finalize() the model first")
         segs = [s.contiguous() for s in segments]
@@ -404,6 +405,8 @@ class BNN:
         ws = self._workspace(n_rows)
         io.mean_dev, io.var_dev = mean.data_ptr(), (var.data_ptr() if var is not None else None)
         io.workspace_dev, io.workspace_bytes = ws.data_ptr(), ws.numel()
+        if n_rows_dev is not None:
+            io.n_rows_dev = n_rows_dev.data_ptr()
         _lib.check(self._lib.cmbpo_predict(self._handle, C.byref(io), self._stream()))
         return mean, var
 

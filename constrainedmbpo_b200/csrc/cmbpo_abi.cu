@@ -428,7 +428,7 @@ extern "C" int cmbpo_predict(void* handle, const cmbpo_predict_io* io, void* str
   CU(cudaSetDevice(h->device), "cudaSetDevice");
   const ModelPlan& pl = h->plan;
   float* heads = static_cast<float*>(io->workspace_dev);
-  rc = run_forward(h, io->seg_dev, io->seg_width, CMBPO_MAX_SEGMENTS, io->n_rows, nullptr, io->ndim, nullptr, heads, stream);
+  rc = run_forward(h, io->seg_dev, io->seg_width, CMBPO_MAX_SEGMENTS, io->n_rows, io->n_rows_dev, io->ndim, nullptr, heads, stream);
   if (rc) return rc;
   const long long stride = row_stride_for(io->n_rows);
   if (io->agg == 0 || io->ndim == 3) {

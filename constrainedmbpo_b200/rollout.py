@@ -64,13 +64,19 @@ class CriticValues:
         self.v_inds, self.vc_inds = as_idx(v_inds, v_model), as_idx(vc_inds, vc_model)
 
     def __call__(self, obs, n_rows_dev=None, path_ids=None):
-        if obs.dim() != 2:
-            raise NotImplementedError("'iv_gae' states need value ensembles with one member per dynamics member")
+        if obs.dim() == 3:
+            # 'iv_gae' states [E, B, obs]: get_v feeds them to BNN.predict as 3-D input (cpo_policy.py:927-945), so value
+            # member e scores dynamics member e's state -- the value ensembles must have E members (bnn.py:749-754)
+            if self.v.num_nets != obs.shape[0] or self.vc.num_nets != obs.shape[0]:
+                raise ValueError(f"'iv_gae' states need value ensembles with one member per dynamics member "
+                                 f"({obs.shape[0]}), got {self.v.num_nets} / {self.vc.num_nets}")
+            out = [m.predict_device([obs], 3, 0, want_var=False)[0][:, :, 0] for m in (self.v, self.vc)]
+            return out[0], out[1]
         B = obs.shape[0]
         pid = (path_ids if path_ids is not None else torch.arange(B, device=obs.device)).long().clamp_(0, self.v_inds.shape[0] - 1)
         out = []
         for model, inds in ((self.v, self.v_inds), (self.vc, self.vc_inds)):
-            mean, _ = model.predict_device([obs], 2, 0, want_var=False)          # [E_v, B, 1]
+            mean, _ = model.predict_device([obs], 2, 0, want_var=False, n_rows_dev=n_rows_dev)          # [E_v, B, 1]
             out.append(mean[:, :, 0].gather(0, inds[pid][None, :])[0])
         return out[0], out[1]
 
@@ -250,11 +256,14 @@ class ModelRollout:
         env = self.env
         cur, pid = self.cur[self.flip], self.pid[self.flip]
         n_dev = self.state[0:1]
-        act = policy(cur, n_dev)
         row_ids = pid
         if self.row_offset:
             torch.add(pid, self.row_offset, out=self._row_ids)
             row_ids = self._row_ids
+        if getattr(policy, "takes_rollout_context", False):     # device actor: noise keyed by global row id + stream word
+            act = policy(cur, n_dev, row_ids=row_ids, rng_offset_dev=self.rng_base)
+        else:
+            act = policy(cur, n_dev)
         perm = None
         if self.mode == "iv_gae" and self.perm_fn is not None:
             perm = self.perm_fn(self.steps_done)

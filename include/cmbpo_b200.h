@@ -94,8 +94,35 @@ typedef struct cmbpo_predict_io {
   float* var_dev;
   void* workspace_dev;
   size_t workspace_bytes;
+  const int32_t* n_rows_dev;   /* optional live row count on the device (rollout loop: n_rows is then the capacity; rows
+                                * beyond the live count are not computed, their outputs are unspecified) */
 } cmbpo_predict_io;
 int cmbpo_predict(void* handle, const cmbpo_predict_io* io, void* stream);
+
+/* Gaussian policy head (softlearning/models/ac_network.py:105-117, the actor CPOPolicy.get_action_outs runs every sampler
+ * step, softlearning/policies/cpo_policy.py:883-925): given mu = the actor MLP's output (cmbpo_predict of a 1-member
+ * tanh ensemble) and the state-independent log_std, pi = mu + N(0,1) * exp(log_std) and
+ * logp_pi = sum_a -0.5 * (((pi - mu) / (exp(log_std) + 1e-8))^2 + 2 log_std + log(2 pi))  (gaussian_likelihood, :50-52).
+ * noise_dev injects the normals ([n_rows][act]); NULL = Philox4x32-10 + Box-Muller keyed by (global row id, column,
+ * rng_offset, seed).  n_slots > 1 ('iv_gae' states, [n_slots][n_rows][.] arrays): the SAME normals for every slot of a
+ * row (ac_network.py:129-146 tiles one draw over the ensemble axis).  deterministic 1: pi = mu. */
+typedef struct cmbpo_actor_io {
+  const float* mu_dev;         /* [n_slots][n_rows][act] */
+  const float* log_std_dev;    /* [act] */
+  const float* noise_dev;      /* [n_rows][act] or NULL */
+  int64_t n_rows;              /* rows per slot (capacity when n_rows_dev is given) */
+  const int32_t* n_rows_dev;
+  int32_t act_dim;
+  int32_t n_slots;
+  int32_t deterministic;
+  const int32_t* row_id_dev;   /* optional [n_rows] global path id per row (Philox counter after compaction) */
+  int64_t row_offset;
+  uint64_t seed, rng_offset;
+  const uint64_t* rng_offset_dev;
+  float* pi_dev;               /* [n_slots][n_rows][act] */
+  float* logp_pi_dev;          /* [n_slots][n_rows] */
+} cmbpo_actor_io;
+int cmbpo_actor_head(const cmbpo_actor_io* io, void* stream);
 
 /* FakeEnv.step (mbpo/models/fake_env.py:131-222) for the dynamics ensemble of `handle`
  * (in_dim = obs+act, out_dim = obs+1). */

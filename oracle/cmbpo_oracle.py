@@ -759,3 +759,24 @@ def choice_indices(dist, uniforms):
     cdf = np.asarray(dist, dtype=np.float64).cumsum()
     cdf /= cdf[-1]
     return cdf.searchsorted(np.asarray(uniforms, np.float64), side="right")
+
+
+# --------------------------------------------------------------------------------------
+# Gaussian actor head: softlearning/models/ac_network.py:27-35 (mlp = tf.layers.dense stack),
+# :50-52 (gaussian_likelihood, EPS = 1e-8 at :8), :105-117 (mlp_gaussian_policy), :129-146 (3-D: one draw tiled over E)
+# --------------------------------------------------------------------------------------
+def actor_outs(weights, biases, log_std, obs, noise, activation="tanh"):
+    """``pi``, ``logp_pi``, ``mu`` of ``mlp_gaussian_policy`` for ``obs`` [B, obs] or [E, B, obs]; ``weights`` [in, out] and
+    ``biases`` [out] per dense layer, ``noise`` [B, act] standard normals (the same row of it for every slot of a 3-D obs)."""
+    x = np.asarray(obs)
+    act = ACTIVATIONS[activation]
+    for i, (W, b) in enumerate(zip(weights, biases)):
+        x = x @ np.asarray(W, x.dtype) + np.asarray(b, x.dtype)
+        if i < len(weights) - 1:
+            x = act(x)
+    mu = x
+    ls = np.asarray(log_std, x.dtype)
+    std = np.exp(ls)
+    pi = mu + np.asarray(noise, x.dtype) * std                    # broadcasts [B, act] over a leading E
+    pre = -0.5 * (((pi - mu) / (std + 1e-8)) ** 2 + 2 * ls + np.log(2 * np.pi))
+    return pi, pre.sum(-1), mu
