@@ -328,10 +328,11 @@ def run_reference(args, w, wname):
 # ----------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------
-def build_env(w, local_rank):
+def build_env(w, local_rank, operand_dtype="bf16"):
     import constrainedmbpo_b200 as cm
     fe = cm.FakeEnv(cm.SimpleEnv(w["obs"], w["act"]), w["env"], num_networks=w["E"], num_elites=w["K"],
-                    hidden_dims=w["hidden"], cares_about_cost=w["cost"], device=f"cuda:{local_rank}", seed=MODEL_SEED)
+                    hidden_dims=w["hidden"], cares_about_cost=w["cost"], device=f"cuda:{local_rank}", seed=MODEL_SEED,
+                    operand_dtype=operand_dtype)
     fe._model.set_elites(list(range(w["K"])))      # fitted-model stand-in: the first K members are the elites
     return fe
 
@@ -370,7 +371,7 @@ def run_gpu(args, w, wname):
     row0, rows = shard_rows(w, world, rank)
     if args.rows:
         row0, rows = rank * args.rows, args.rows
-    fe = build_env(w, local_rank)
+    fe = build_env(w, local_rank, args.operand_dtype)
     model = fe._model
     policy = cm.StubPolicy(w["obs"], w["act"], device=dev, seed=4)
     start_host = torch.from_numpy(synth_start_states(w, rows, 1, lo=row0)).pin_memory()
@@ -564,14 +565,14 @@ def run_gpu(args, w, wname):
                          f"port (torch BLAS GEMMs + NumPy post-processing, 64k-row chunks)"}
 
     traffic, traffic_src = committed_traffic(wname, rows_forwarded / max(launches_fwd, 1))
-    wide = max(w["hidden"]) > 254
+    wide = max(w["hidden"]) > 254 or args.operand_dtype == "tf32"
     which, peak = pick_peak(peaks, clk)
     cfg = config_of(wname, w, args.gpus)
     out = {
         "metric": METRIC,
         "value": value, "unit": "transitions/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm,
         "ms_per_step": ms / steps, "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None,
-        "dtype": "bf16", "data": "synthetic",
+        "dtype": args.operand_dtype, "data": "synthetic",
         "config": cfg,
         "details": {"start_states_per_gpu": rows, "dkl_lim": dkl_lim, "units_per_step_per_gpu": per_step_units,
                     "rows_forwarded_per_step": rows_forwarded, "cuda_graph": w["kind"] == "rollout" and not args.no_graph,
@@ -617,6 +618,8 @@ def main():
     ap.add_argument("--transport", default="p2p", choices=["nccl", "p2p"],
                     help="N>1: NCCL all-gather kernels, or copy-engine pulls over symmetric-memory peer mappings")
     ap.add_argument("--nccl-max-ctas", type=int, default=0, help="N>1: NCCL max_ctas of the gather group (0 = default)")
+    ap.add_argument("--operand-dtype", default="bf16", choices=["bf16", "tf32"],
+                    help="tensor-core operand type of the ensemble GEMMs (tf32: layer-at-a-time kernel, rtol 1e-3)")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
     w = WORKLOADS[args.workload]

@@ -29,11 +29,15 @@ class CmbpoError(RuntimeError):
     pass
 
 
+DTYPE_IDS = {"bf16": 0, "tf32": 1}   # CMBPO_DTYPE_*: tensor-core operand type
+
+
 class cmbpo_cfg(C.Structure):
     _fields_ = [
         ("num_members", C.c_int32), ("num_layers", C.c_int32), ("in_dim", C.c_int32),
         ("out_dim", C.c_int32), ("probabilistic", C.c_int32),
         ("layer_width", C.c_int32 * MAX_LAYERS), ("layer_act", C.c_int32 * MAX_LAYERS),
+        ("operand_dtype", C.c_int32),
     ]
 
 

@@ -140,6 +140,11 @@ class BNN:
         self.model_loaded = False
         self.device = torch.device(params.get("device", "cuda:0"))
         self.seed = params.get("seed", None)
+        # tensor-core operand type of the forward kernels: 'bf16' (default; rtol 1e-2 vs the reference's fp32) or 'tf32'
+        # (fp32 operand images, kind::tf32 MMAs, exact activations; rtol 1e-3, about half the throughput)
+        self.operand_dtype = params.get("operand_dtype", "bf16")
+        if self.operand_dtype not in _lib.DTYPE_IDS:
+            raise ValueError(f"operand_dtype must be 'bf16' or 'tf32', got {self.operand_dtype!r}")
         self._handle = None
         self._ws = None
         self.weights, self.biases = [], []
@@ -225,6 +230,7 @@ class BNN:
             if layer.get_activation() == "softmax":
                 raise _lib.CmbpoError("softmax layers are not supported on the B200 rollout path")
             cfg.layer_act[i] = _lib.ACT_IDS[layer.get_activation()]
+        cfg.operand_dtype = _lib.DTYPE_IDS[self.operand_dtype]
         h = C.c_void_p()
         _lib.check(lib.cmbpo_create(C.byref(cfg), self.device.index or 0, C.byref(h)))
         self._handle = h

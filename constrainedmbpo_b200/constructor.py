@@ -29,12 +29,14 @@ def construct_model(in_dim,
                     logit_bias_std=1.0,
                     session=None,
                     device="cuda:0",
-                    seed=None):
+                    seed=None,
+                    operand_dtype="bf16"):
     """Builds the ensemble the way constructor.py:41-67 does: ``BNN(params)``, one ``FC`` per
     hidden dim (weight decays ``decay/4``, ``decay/2``, ``decay``), ``finalize``.  Optimiser
     arguments (``lr``, ``lr_decay``, ``decay_steps``, ``weighted``, ``clip_loss``, ...) are
     accepted and recorded but unused: training stays with the reference.  ``device`` / ``seed``
-    are additions (CUDA device of the handle; seed of the random initial weights)."""
+    are additions (CUDA device of the handle; seed of the random initial weights), and so is ``operand_dtype``
+    ('bf16' | 'tf32': the tensor-core operand type, include/cmbpo_b200.h cmbpo_cfg.operand_dtype)."""
     params = {'name': name,
               'loss': loss,
               'num_networks': num_networks,
@@ -51,6 +53,7 @@ def construct_model(in_dim,
               'logit_bias_std': logit_bias_std,
               'device': device,
               'seed': seed,
+              'operand_dtype': operand_dtype,
               }
     model = BNN(params)
     model.add(FC(hidden_dims[0], input_dim=in_dim, activation=activation, weight_decay=decay / 4))

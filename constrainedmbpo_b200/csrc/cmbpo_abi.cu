@@ -17,7 +17,7 @@ cudaError_t pack_layer(const float* W, const float* b, uint8_t* img, int E, cons
 cudaError_t launch_ensemble_fwd(const FwdParams& p, int hidden_act, int num_sms, cudaStream_t stream);
 cudaError_t launch_stage_inputs(const StageParams& p, int num_sms, cudaStream_t stream);
 cudaError_t pack_wide_layer(const float* W, const float* b, uint8_t* img, float* bias_tab, int E,
-                            const WideLayerPlan& lp, cudaStream_t stream);
+                            const WideLayerPlan& lp, int tf32, cudaStream_t stream);
 cudaError_t launch_wide_layer(const WideParams& p, int act, int num_sms, cudaStream_t stream);
 }  // namespace cmbpo
 
@@ -49,6 +49,7 @@ struct Handle {
   bool profiling = false;
   // wide path (wide_fwd.cu): any layer wider than the fused kernel's 254 columns, or CMBPO_FORCE_WIDE=1
   bool wide = false;
+  bool tf32 = false;           // cfg.operand_dtype == CMBPO_DTYPE_TF32: wide path with fp32 operand images
   WideLayerPlan wl[kMaxLayers];
   uint8_t* wimg_wide = nullptr;
   float* bias_wide = nullptr;
@@ -119,6 +120,11 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
       return fail(CMBPO_ERR_UNSUPPORTED, "hidden layers must share one activation (constructor.py:57-60)");
     }
   pl.blk_bytes = off;
+  if (cfg->operand_dtype != CMBPO_DTYPE_BF16 && cfg->operand_dtype != CMBPO_DTYPE_TF32) {
+    delete h;
+    return fail(CMBPO_ERR_ARG, "operand_dtype must be CMBPO_DTYPE_BF16 or CMBPO_DTYPE_TF32");
+  }
+  if (cfg->operand_dtype == CMBPO_DTYPE_TF32) { h->tf32 = true; h->wide = true; }
   if (const char* fw = getenv("CMBPO_FORCE_WIDE")) if (fw[0] == '1') h->wide = true;   // test hook: same nets on both kernels
   if (!h->wide && !plan_fwd_smem(pl)) h->wide = true;   // shapes beyond the fused kernel's shared-memory budget
   size_t wide_img = 0, wide_bias = 0;
@@ -130,15 +136,21 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
     for (int l = 0; l < L; ++l) {
       WideLayerPlan& w = h->wl[l];
       w.k_real = pl.layer[l].k_real; w.n_real = pl.layer[l].n_real;
-      w.kpad = roundup(w.k_real, kWideKC);
-      w.npad = (l < L - 1) ? roundup(w.n_real, kWideKC) : roundup(w.n_real, 16);
-      w.k_chunks = w.kpad / kWideKC;
+      w.kc = h->tf32 ? kWideKC / 2 : kWideKC;
+      // tf32 layer 0: the scaled inputs reach |x| ~ 1e2 where the input scaler hits its 1e-2 floor (utils.py:161), and a
+      // 10-bit mantissa cannot hold them (nor their products with rounded weights) to 1e-3 of the output scale: the first
+      // GEMM runs as x_hi W_hi + x_lo W_hi + x_hi W_lo (3xTF32), laid out as one GEMM over a K axis three times as long
+      w.split3 = (h->tf32 && l == 0) ? 1 : 0;
+      w.kpad = roundup((w.split3 ? 3 : 1) * w.k_real, w.kc);
+      w.npad = (l < L - 1) ? roundup(w.n_real, w.kc) : roundup(w.n_real, 16);
+      w.k_chunks = w.kpad / w.kc;
       w.n_chunks = (w.npad + kWideNC - 1) / kWideNC;
-      w.act = pl.layer[l].act; w.prescale = pl.layer[l].prescale;
+      w.act = pl.layer[l].act;
+      w.prescale = h->tf32 ? 1.0f : pl.layer[l].prescale;   // tf32 path: exact sigmoid / tanh, no x/2 form
       w.w_off = wide_img; w.b_off = wide_bias;
       wide_img += (size_t)E * w.n_chunks * 2 * w.k_chunks * kWideBlk;
       wide_bias += (size_t)E * w.npad;
-      if (l < L - 1 && w.npad / kWideKC > h->wide_max_kc) h->wide_max_kc = w.npad / kWideKC;
+      if (l < L - 1 && w.npad / w.kc > h->wide_max_kc) h->wide_max_kc = w.npad / w.kc;
     }
   }
   CU(cudaSetDevice(device), "cudaSetDevice");
@@ -194,7 +206,7 @@ extern "C" int cmbpo_set_weights(void* handle, int32_t layer, const float* w_dev
   CU(cudaSetDevice(h->device), "cudaSetDevice");
   if (h->wide) {
     CU(pack_wide_layer(w_dev, b_dev, h->wimg_wide + h->wl[layer].w_off, h->bias_wide + h->wl[layer].b_off, h->plan.E,
-                       h->wl[layer], (cudaStream_t)stream), "pack_wide_layer");
+                       h->wl[layer], h->tf32 ? 1 : 0, (cudaStream_t)stream), "pack_wide_layer");
   } else {
     CU(pack_layer(w_dev, b_dev, h->wimg, h->plan.E, h->plan.layer[layer], h->plan.blk_bytes, (cudaStream_t)stream),
        "pack_layer");
@@ -258,7 +270,7 @@ static inline long long row_stride_for(long long n_rows) { return (n_rows + kTil
 // workspace = head scratch | step_post partial sums | staged layer-0 tiles (E input slots)
 static size_t a0_slot_bytes(const Handle* h, long long rows) {
   const long long rows_pad = (rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
-  return (size_t)rows_pad * (h->wide ? h->wl[0].kpad : h->plan.layer[0].kpad) * 2u;
+  return (size_t)rows_pad * (h->wide ? h->wl[0].kpad : h->plan.layer[0].kpad) * (h->tf32 ? 4u : 2u);
 }
 // wide path: two ping-pong activation images [E slots][slab 128-row blocks][widest hidden K chunks]
 static long long wide_slab_pad(long long rows) {
@@ -321,6 +333,9 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   sp.n_slots = (ndim == 3) ? pl.E : 1;
   sp.in_dim = pl.in_dim; sp.kpad = h->wide ? h->wl[0].kpad : pl.layer[0].kpad;
   sp.chunked = h->wide ? 1 : 0;
+  sp.tf32 = h->tf32 ? 1 : 0;
+  sp.split3 = h->tf32 ? 1 : 0;
+  if (h->tf32 && sp.kpad > 384) return fail(CMBPO_ERR_UNSUPPORTED, "tf32 operands: input width above 128 columns");
   sp.in_mu = h->consts; sp.in_inv = h->consts + pl.in_dim;
   sp.n_rows_dev = n_rows_dev; sp.n_rows = n_rows;
   sp.slot_stride_bytes = (long long)a0_slot_bytes(h, n_rows);
@@ -370,6 +385,7 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
         memset(&wp, 0, sizeof(wp));
         wp.lp = h->wl[l];
         wp.E = pl.E; wp.n_head = pl.n_head; wp.is_head = (l == pl.L - 1) ? 1 : 0;
+        wp.tf32 = h->tf32 ? 1 : 0;
         wp.w_img = h->wimg_wide + h->wl[l].w_off;
         wp.bias = h->bias_wide + h->wl[l].b_off;
         for (int e = 0; e < pl.E; ++e) {
@@ -386,7 +402,7 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
           wp.per_slot_input = 1;
         }
         wp.out_img = actbuf[l & 1];
-        wp.out_slot_stride = (long long)slab_blocks * (h->wl[l].npad / kWideKC) * kWideBlk;
+        wp.out_slot_stride = (long long)slab_blocks * (h->wl[l].npad / h->wl[l].kc) * kWideBlk;
         wp.heads = heads;
         wp.head_blk0 = row0 / kTileRows;
         wp.head_scale = p.head_scale; wp.head_shift = p.head_shift;

@@ -59,6 +59,8 @@ struct StageParams {
   int n_slots;                         // 1 (2-D input shared by all members) or E (3-D, fc.py:107-108)
   int in_dim, kpad;
   int chunked;                         // 1: wide-path image (K chunks of 64, no bias-carrier columns)
+  int tf32;                            // 1 (with chunked): fp32 elements for kind::tf32, K chunks of 32 (same 16 KB blocks)
+  int split3;                          // 1 (with tf32): columns [x_hi | x_lo | x_hi] against weight rows [W_hi ; W_hi ; W_lo]
   const float* in_mu;                  // [in_dim] scaler_in mean          (utils.py:161)
   const float* in_inv;                 // [in_dim] 1 / max(sqrt(var)*sc, 1e-2)
   const int* n_rows_dev;               // optional device scalar with the live row count
@@ -101,8 +103,10 @@ constexpr uint32_t kWideBlk = 128u * kWideKC * 2u;   // 16 KB: one (128 rows, 64
 
 struct WideLayerPlan {
   int k_real, n_real;
-  int kpad;              // roundup(k_real, 64)
-  int npad;              // hidden: roundup(n_real, 64) (= next layer's kpad); head: roundup(n_real, 16)
+  int kc;                // K columns per 16 KB operand block: 64 (bf16) or 32 (tf32: fp32 elements, kind::tf32)
+  int split3;            // tf32 layer 0: K axis = [x_hi | x_lo | x_hi] . [W_hi ; W_hi ; W_lo] (3xTF32 split, kpad = roundup(3 k_real, kc))
+  int kpad;              // roundup(k_real, kc)
+  int npad;              // hidden: roundup(n_real, kc) (= next layer's kpad); head: roundup(n_real, 16)
   int k_chunks, n_chunks;
   int act;
   float prescale;
@@ -113,6 +117,7 @@ struct WideLayerPlan {
 struct WideParams {
   WideLayerPlan lp;
   int E, n_head, is_head;
+  int tf32;                    // operands are fp32 images consumed by tcgen05.mma kind::tf32
   const uint8_t* w_img;        // this layer: [slot e][n chunk][cta half][k chunk] blocks of kWideBlk bytes
   const float* bias;           // this layer: [E][npad]
   const uint8_t* a_img;        // input image [input slot][128-row block][k chunk]

@@ -666,27 +666,43 @@ __global__ void __launch_bounds__(256) stage_inputs_kernel(const StageParams p) 
 // leaves as one contiguous run of 16-byte stores.  stage_inputs_kernel above does 8 scalar loads with a segment search
 // per element and is instruction-bound (58 M warp instructions, 84 us per 1 M HalfCheetah rows); it remains the path
 // for inputs wider than kStageMaxK columns.
-constexpr int kStageMaxK = 256;
+constexpr int kStageMaxK = 384;
 __device__ __forceinline__ int stage_fast_div(int idx, float inv_w) { return (int)(((float)idx + 0.5f) * inv_w); }
 __global__ void __launch_bounds__(256) stage_inputs_block_kernel(const StageParams p) {
-  extern __shared__ __align__(16) uint8_t s_img[];            // [128 rows x kpad] bf16, block-image layout
+  extern __shared__ __align__(16) uint8_t s_img[];            // [128 rows x kpad] bf16 (tf32 path: fp32), block-image layout
   __shared__ float s_mu[kStageMaxK], s_inv[kStageMaxK];
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
   const long long rows_pad = (n_rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
   const int kg = p.kpad >> 3;
   const long long blks_per_slot = rows_pad / kTileRows;
   const long long n_blks = blks_per_slot * p.n_slots;
-  const uint32_t blk_bytes = (uint32_t)kTileRows * p.kpad * 2u;
+  const uint32_t esz = p.tf32 ? 4u : 2u;
+  const uint32_t blk_bytes = (uint32_t)kTileRows * p.kpad * esz;
   for (int k = threadIdx.x; k < p.in_dim; k += blockDim.x) {
     s_mu[k] = p.in_mu ? p.in_mu[k] : 0.f;
     s_inv[k] = p.in_inv ? p.in_inv[k] : 1.f;
   }
   auto off = [&](int r, int k) -> uint32_t {      // byte offset of element (r, k) inside the block image
     const int g8 = k >> 3;
+    if (p.tf32)   // fp32 elements, K chunks of 32: 8x4 core matrices of 128 bytes, LBO 128 / SBO 1024 like the bf16 image
+      return (uint32_t)(k >> 5) * kWideBlk + (uint32_t)(r >> 3) * 1024u + (uint32_t)((k & 31) >> 2) * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(k & 3) * 4u;
     return p.chunked ? (uint32_t)(g8 >> 3) * kWideBlk + (uint32_t)(r >> 3) * 1024u + (uint32_t)(g8 & 7) * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(k & 7) * 2u
                      : (uint32_t)(r >> 3) * ((uint32_t)kg * 128u) + (uint32_t)g8 * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(k & 7) * 2u;
   };
-  const int n_pad = p.kpad - p.in_dim;
+  auto put = [&](int r, int k, float x) {
+    if (p.tf32) {
+      const float hi = round_tf32(x);
+      *reinterpret_cast<float*>(s_img + off(r, k)) = hi;
+      if (p.split3 && k < p.in_dim) {   // [x_hi | x_lo | x_hi] (cmbpo_internal.cuh WideLayerPlan::split3)
+        *reinterpret_cast<float*>(s_img + off(r, k + p.in_dim)) = round_tf32(x - hi);
+        *reinterpret_cast<float*>(s_img + off(r, k + 2 * p.in_dim)) = hi;
+      }
+    } else {
+      *reinterpret_cast<__nv_bfloat16*>(s_img + off(r, k)) = __float2bfloat16_rn(x);
+    }
+  };
+  const int k_used = (p.tf32 && p.split3) ? 3 * p.in_dim : p.in_dim;     // first padding column
+  const int n_pad = p.kpad - k_used;
   const float inv_pad = n_pad > 0 ? 1.0f / (float)n_pad : 0.f;
   for (long long b = blockIdx.x; b < n_blks; b += gridDim.x) {
     const int slot = (int)(b / blks_per_slot);
@@ -696,9 +712,9 @@ __global__ void __launch_bounds__(256) stage_inputs_block_kernel(const StagePara
     __syncthreads();                                           // previous image fully written out (and s_mu / s_inv visible)
     // padding columns: in_dim, in_dim + 1 carry the constant one of the bias rows (fused path), the rest is zero
     for (int i = threadIdx.x; i < kTileRows * n_pad; i += blockDim.x) {
-      const int r = stage_fast_div(i, inv_pad), k = p.in_dim + (i - r * n_pad);
+      const int r = stage_fast_div(i, inv_pad), k = k_used + (i - r * n_pad);
       const bool one = r < rows_here && k < p.in_dim + 2 && !p.chunked;
-      *reinterpret_cast<uint16_t*>(s_img + off(r, k)) = one ? (uint16_t)0x3F80 : (uint16_t)0;
+      put(r, k, one ? 1.0f : 0.0f);
     }
     int k0 = 0;
     for (int sg = 0; sg < kMaxSeg; ++sg) {
@@ -710,7 +726,7 @@ __global__ void __launch_bounds__(256) stage_inputs_block_kernel(const StagePara
       for (int i = threadIdx.x; i < kTileRows * w; i += blockDim.x) {
         const int r = stage_fast_div(i, inv_w), k = k0 + (i - r * w);
         const float x = (i < n_live) ? (__ldg(src + i) - s_mu[k]) * s_inv[k] : 0.f;
-        *reinterpret_cast<__nv_bfloat16*>(s_img + off(r, k)) = __float2bfloat16_rn(x);
+        put(r, k, x);
       }
       k0 += w;
     }
@@ -722,10 +738,10 @@ __global__ void __launch_bounds__(256) stage_inputs_block_kernel(const StagePara
 }
 
 cudaError_t launch_stage_inputs(const StageParams& p, int num_sms, cudaStream_t stream) {
-  if (p.kpad <= kStageMaxK) {
+  if (p.kpad <= (p.tf32 ? kStageMaxK : 256)) {
     const long long rows_pad0 = (p.n_rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
     long long nb = rows_pad0 / kTileRows * p.n_slots;
-    const size_t smem = (size_t)kTileRows * p.kpad * 2u;
+    const size_t smem = (size_t)kTileRows * p.kpad * (p.tf32 ? 4u : 2u);
     static size_t smem_set = 48 * 1024;
     if (smem > smem_set) {
       cudaError_t e = cudaFuncSetAttribute(stage_inputs_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -357,6 +357,13 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
   return r;
 }
+// fp32 -> tf32 (10-bit mantissa) with round-to-nearest, returned as an fp32 bit pattern: tcgen05.mma kind::tf32 reads
+// fp32 words and ignores the low 13 mantissa bits, i.e. truncates whatever was not rounded beforehand
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
 __device__ __forceinline__ float tanh_approx(float x) {
   float y;
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));

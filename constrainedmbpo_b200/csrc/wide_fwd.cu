@@ -35,8 +35,23 @@ constexpr int WB_ACC_EMPTY = 18;   // [2]
 
 enum WideWaitCode : int { WWC_LOADER = 11, WWC_MMA_FULL = 12, WWC_MMA_ACC = 13, WWC_EPI_ACC = 14 };
 
-template <int ACT>
+// 1 / (1 + e^-x) to fp32 accuracy: ex2.approx (2 ulp) + rcp.approx (1 ulp)
+__device__ __forceinline__ float sigmoid_precise(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+  return r;
+}
+
+template <int ACT, bool PRECISE>
 __device__ __forceinline__ float wide_activate(float g) {
+  if constexpr (PRECISE) {   // tf32 path (rtol 1e-3): tanh.approx's ~2^-11 relative error would eat the whole budget
+    if constexpr (ACT == ACT_SWISH) return g * sigmoid_precise(g);              // fc.py:20, g = x (no pre-scaling)
+    else if constexpr (ACT == ACT_RELU) return fmaxf(g, 0.f);
+    else if constexpr (ACT == ACT_TANH) return fmaf(2.0f, sigmoid_precise(2.0f * g), -1.0f);
+    else if constexpr (ACT == ACT_SIGMOID) return sigmoid_precise(g);
+    else return g;
+  }
   // g is the pre-activation, already halved for ACT_SWISH / ACT_SIGMOID (weights and bias pre-scaled)
   if constexpr (ACT == ACT_SWISH) return fmaf(g, tanh_approx(g), g);          // x*sigmoid(x), fc.py:20
   else if constexpr (ACT == ACT_RELU) return fmaxf(g, 0.f);
@@ -60,7 +75,11 @@ struct WideItems {
   __device__ __forceinline__ long long count() const { return i < total ? (total - i + step - 1) / step : 0; }
 };
 
-template <int HACT>
+// TF32: the operand images hold fp32 words (tf32-rounded) in 16 KB blocks of 32 K columns -- the same byte geometry as
+// the bf16 blocks of 64 (8 core matrices of 128 bytes along K, LBO 128, SBO 1024) -- so the loader, the ring and the
+// descriptor stepping (4 MMAs per stage, 256 bytes apart) are unchanged; tcgen05.mma kind::tf32 consumes K = 8 per
+// instruction at half the bf16 rate, and the epilogue evaluates the activation to fp32 accuracy.
+template <int HACT, bool TF32>
 __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __grid_constant__ WideParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const WideLayerPlan& lp = p.lp;
@@ -154,7 +173,7 @@ __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __gri
         const int acc = n_item & 1;
         const uint32_t acc_use = n_item >> 1;
         const int chunk_n = min(kWideNC, lp.npad - it.chunk() * kWideNC);
-        const uint32_t idesc = make_idesc(256, chunk_n, kFmtBF16);
+        const uint32_t idesc = make_idesc(256, chunk_n, TF32 ? kFmtTF32 : kFmtBF16);
         if (acc_use > 0) mbar_wait(bar(WB_ACC_EMPTY + acc), (acc_use - 1) & 1, p.status, WWC_MMA_ACC);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kWideNC;
@@ -165,9 +184,14 @@ __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __gri
           const uint32_t b_base = a_base + kWideBlk;
           if (elect_one()) {
 #pragma unroll
-            for (int ks = 0; ks < kWideKC / 16; ++ks)
-              mma_bf16_ss<2>(d_tmem, make_smem_desc(a_base + ks * 256, 128, 1024),
-                             make_smem_desc(b_base + ks * 256, 128, 1024), idesc, (j > 0 || ks > 0) ? 1u : 0u);
+            for (int ks = 0; ks < kWideKC / 16; ++ks) {
+              if constexpr (TF32)
+                mma_tf32_ss<2>(d_tmem, make_smem_desc(a_base + ks * 256, 128, 1024),
+                               make_smem_desc(b_base + ks * 256, 128, 1024), idesc, (j > 0 || ks > 0) ? 1u : 0u);
+              else
+                mma_bf16_ss<2>(d_tmem, make_smem_desc(a_base + ks * 256, 128, 1024),
+                               make_smem_desc(b_base + ks * 256, 128, 1024), idesc, (j > 0 || ks > 0) ? 1u : 0u);
+            }
             mma_commit_2sm(bar(WB_EMPTY + stage), 0x3);
             if (j == KC - 1) mma_commit_2sm(bar(WB_ACC_FULL + acc), 0x3);
           }
@@ -182,7 +206,7 @@ __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __gri
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int row_in_tile = q * 32 + lane;
     const uint32_t row_off = (uint32_t)(row_in_tile >> 3) * 1024u + (uint32_t)(row_in_tile & 7) * 16u;
-    const int kc_next = lp.npad / kWideKC;     // K chunks of the image this layer writes (hidden layers)
+    const int kc_next = lp.npad / lp.kc;       // K chunks of the image this layer writes (hidden layers)
     uint32_t n_item = 0;
     for (WideItems it(cluster_id, n_clusters, p.E, n_tiles, NCH); it.valid(); it.next(), ++n_item) {
       const int acc = n_item & 1;
@@ -207,14 +231,27 @@ __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __gri
             const float4 v = __ldg(reinterpret_cast<const float4*>(bias + 16 * c16) + i);
             b[4 * i] = v.x; b[4 * i + 1] = v.y; b[4 * i + 2] = v.z; b[4 * i + 3] = v.w;
           }
-          uint32_t o[8];
+          if constexpr (TF32) {   // 16 fp32 words = four 16-byte core-matrix rows, 128 bytes apart, inside one 32-column chunk
+            uint8_t* dst = out_blk + (size_t)(n0 >> 5) * kWideBlk + (size_t)((n0 & 31) >> 2) * 128;
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            o[i] = pack_bf16x2(wide_activate<HACT>(__uint_as_float(r[2 * i]) + b[2 * i]),
-                               wide_activate<HACT>(__uint_as_float(r[2 * i + 1]) + b[2 * i + 1]));
-          uint8_t* dst = out_blk + (size_t)(n0 >> 6) * kWideBlk + (size_t)((n0 & 63) >> 3) * 128;
-          *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
-          *reinterpret_cast<uint4*>(dst + 128) = make_uint4(o[4], o[5], o[6], o[7]);
+            for (int i = 0; i < 4; ++i) {
+              float4 v;
+              v.x = round_tf32(wide_activate<HACT, true>(__uint_as_float(r[4 * i]) + b[4 * i]));
+              v.y = round_tf32(wide_activate<HACT, true>(__uint_as_float(r[4 * i + 1]) + b[4 * i + 1]));
+              v.z = round_tf32(wide_activate<HACT, true>(__uint_as_float(r[4 * i + 2]) + b[4 * i + 2]));
+              v.w = round_tf32(wide_activate<HACT, true>(__uint_as_float(r[4 * i + 3]) + b[4 * i + 3]));
+              *reinterpret_cast<float4*>(dst + 128 * i) = v;
+            }
+          } else {
+            uint32_t o[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              o[i] = pack_bf16x2(wide_activate<HACT, false>(__uint_as_float(r[2 * i]) + b[2 * i]),
+                                 wide_activate<HACT, false>(__uint_as_float(r[2 * i + 1]) + b[2 * i + 1]));
+            uint8_t* dst = out_blk + (size_t)(n0 >> 6) * kWideBlk + (size_t)((n0 & 63) >> 3) * 128;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<uint4*>(dst + 128) = make_uint4(o[4], o[5], o[6], o[7]);
+          }
         };
         for (int c16 = cb; c16 < ce; c16 += 2) {
           tmem_wait_ld();
@@ -269,7 +306,7 @@ __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __gri
 // both pre-scaled by `prescale` (0.5 for swish / sigmoid: the epilogue works on x/2).
 // ---------------------------------------------------------------------------------------
 __global__ void pack_wide_layer_kernel(const float* __restrict__ W, const float* __restrict__ b, uint8_t* img,
-                                       float* bias_tab, int E, WideLayerPlan lp) {
+                                       float* bias_tab, int E, WideLayerPlan lp, int tf32) {
   const long long per_e = (long long)lp.npad * lp.kpad;
   const long long total = (long long)E * per_e;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
@@ -280,30 +317,44 @@ __global__ void pack_wide_layer_kernel(const float* __restrict__ W, const float*
     const int c = n / kWideNC, n_in = n - c * kWideNC;
     const int chunk_n = min(kWideNC, lp.npad - c * kWideNC), nh = chunk_n >> 1;
     const int h = n_in / nh, nl = n_in - h * nh;
-    const int j = k / kWideKC, kk = k - j * kWideKC;
+    const int j = k / lp.kc, kk = k - j * lp.kc;
     float v = 0.f;
-    if (n < lp.n_real && k < lp.k_real) v = W[((size_t)e * lp.k_real + k) * lp.n_real + n] * lp.prescale;
-    const size_t off = ((((size_t)e * lp.n_chunks + c) * 2 + h) * lp.k_chunks + j) * kWideBlk +
-                       (size_t)(nl >> 3) * 1024 + (size_t)(kk >> 3) * 128 + (size_t)(nl & 7) * 16 + (size_t)(kk & 7) * 2;
-    *reinterpret_cast<__nv_bfloat16*>(img + off) = __float2bfloat16_rn(v);
+    if (lp.split3) {   // rows [W_hi ; W_hi ; W_lo] against the staged columns [x_hi | x_lo | x_hi]
+      const int part = k / lp.k_real, ks = k - part * lp.k_real;
+      if (n < lp.n_real && part < 3) {
+        const float w = W[((size_t)e * lp.k_real + ks) * lp.n_real + n] * lp.prescale;
+        const float hi = sm100::round_tf32(w);
+        v = part < 2 ? hi : w - hi;
+      }
+    } else if (n < lp.n_real && k < lp.k_real) {
+      v = W[((size_t)e * lp.k_real + k) * lp.n_real + n] * lp.prescale;
+    }
+    const size_t blk = ((((size_t)e * lp.n_chunks + c) * 2 + h) * lp.k_chunks + j) * kWideBlk;
+    if (tf32) {   // fp32 words, 8x4 core matrices (tcgen05.mma kind::tf32)
+      const size_t off = blk + (size_t)(nl >> 3) * 1024 + (size_t)(kk >> 2) * 128 + (size_t)(nl & 7) * 16 + (size_t)(kk & 3) * 4;
+      *reinterpret_cast<float*>(img + off) = sm100::round_tf32(v);
+    } else {
+      const size_t off = blk + (size_t)(nl >> 3) * 1024 + (size_t)(kk >> 3) * 128 + (size_t)(nl & 7) * 16 + (size_t)(kk & 7) * 2;
+      *reinterpret_cast<__nv_bfloat16*>(img + off) = __float2bfloat16_rn(v);
+    }
     if (k == 0) bias_tab[(size_t)e * lp.npad + n] = (n < lp.n_real && b) ? b[(size_t)e * lp.n_real + n] * lp.prescale : 0.f;
   }
 }
 
 cudaError_t pack_wide_layer(const float* W, const float* b, uint8_t* img, float* bias_tab, int E,
-                            const WideLayerPlan& lp, cudaStream_t stream) {
+                            const WideLayerPlan& lp, int tf32, cudaStream_t stream) {
   const long long total = (long long)E * lp.npad * lp.kpad;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 8192) blocks = 8192;
-  pack_wide_layer_kernel<<<blocks, 256, 0, stream>>>(W, b, img, bias_tab, E, lp);
+  pack_wide_layer_kernel<<<blocks, 256, 0, stream>>>(W, b, img, bias_tab, E, lp, tf32);
   return cudaGetLastError();
 }
 
-template <int HACT>
-static cudaError_t launch_wide_variant(const WideParams& p, int num_sms, cudaStream_t stream) {
+template <int HACT, bool TF32>
+static cudaError_t launch_wide_variant2(const WideParams& p, int num_sms, cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(wide_layer_kernel<HACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(wide_layer_kernel<HACT, TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)kWideSmemBytes);
     if (e != cudaSuccess) return e;
     attr_set = true;
@@ -323,7 +374,11 @@ static cudaError_t launch_wide_variant(const WideParams& p, int num_sms, cudaStr
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, wide_layer_kernel<HACT>, p);
+  return cudaLaunchKernelEx(&cfg, wide_layer_kernel<HACT, TF32>, p);
+}
+template <int HACT>
+static cudaError_t launch_wide_variant(const WideParams& p, int num_sms, cudaStream_t stream) {
+  return p.tf32 ? launch_wide_variant2<HACT, true>(p, num_sms, stream) : launch_wide_variant2<HACT, false>(p, num_sms, stream);
 }
 
 // act: activation of THIS layer (ACT_NONE for the head)

@@ -30,7 +30,8 @@ class FakeEnv:
                  device="cuda:0",
                  seed=None,
                  sample_noise=False,
-                 logvar_bound=None):
+                 logvar_bound=None,
+                 operand_dtype="bf16"):
         # fake_env.py:28-44
         self.domain = true_environment.domain if getattr(true_environment, "domain", None) else ""
         self.env = true_environment
@@ -58,7 +59,7 @@ class FakeEnv:
                                       num_networks=num_networks, num_elites=num_elites,
                                       weighted=dyn_discount < 1, use_scaler_in=True, use_scaler_out=True,
                                       decay=1e-6, max_logvar=.5, min_logvar=-10, session=session,
-                                      device=device, seed=seed)
+                                      device=device, seed=seed, operand_dtype=operand_dtype)
         if self.cares_about_cost and not self.static_c:
             # fake_env.py:76-94: separate CostNN ensemble, MSE (non-probabilistic), 64x64
             self.cost_m_loss = 'MSE'
@@ -68,7 +69,7 @@ class FakeEnv:
                                                num_elites=num_elites, weighted=cost_m_discount < 1,
                                                use_scaler_in=False, use_scaler_out=False, decay=1e-6,
                                                session=session, device=device,
-                                               seed=None if seed is None else seed + 1)
+                                               seed=None if seed is None else seed + 1, operand_dtype=operand_dtype)
         else:
             self._cost_model = None
         # options beyond the live reference (both off by default): Gaussian sampling of the next state in the output

@@ -55,7 +55,12 @@ typedef struct cmbpo_cfg {
   int32_t probabilistic;                  /* loss in {NLL, MSPE}              bnn.py:111-112 */
   int32_t layer_width[CMBPO_MAX_LAYERS];  /* FC output widths; last = 2*out_dim if probabilistic */
   int32_t layer_act[CMBPO_MAX_LAYERS];    /* CMBPO_ACT_* per layer; last must be NONE (bnn.py:194-196) */
+  /* Tensor-core operand type (north_star: "tf32 or bf16 in, fp32 accumulate").  0 = bf16 (default, rtol 1e-2 vs the
+   * reference's fp32 arithmetic), 1 = tf32: fp32 operand images read by tcgen05.mma kind::tf32 (10-bit mantissa, rtol
+   * 1e-3), exact sigmoid / tanh in the epilogue instead of tanh.approx; half the tensor throughput, layer-at-a-time kernel. */
+  int32_t operand_dtype;
 } cmbpo_cfg;
+enum { CMBPO_DTYPE_BF16 = 0, CMBPO_DTYPE_TF32 = 1 };
 
 /* construct_model -> BNN(params) + FC stack + finalize   (constructor.py:41-67) */
 int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle);

