@@ -668,6 +668,7 @@ __global__ void __launch_bounds__(256) stage_inputs_kernel(const StageParams p) 
 // for inputs wider than kStageMaxK columns.
 constexpr int kStageMaxK = 384;
 __device__ __forceinline__ int stage_fast_div(int idx, float inv_w) { return (int)(((float)idx + 0.5f) * inv_w); }
+template <bool TF32>
 __global__ void __launch_bounds__(256) stage_inputs_block_kernel(const StageParams p) {
   extern __shared__ __align__(16) uint8_t s_img[];            // [128 rows x kpad] bf16 (tf32 path: fp32), block-image layout
   __shared__ float s_mu[kStageMaxK], s_inv[kStageMaxK];
@@ -676,7 +677,7 @@ __global__ void __launch_bounds__(256) stage_inputs_block_kernel(const StagePara
   const int kg = p.kpad >> 3;
   const long long blks_per_slot = rows_pad / kTileRows;
   const long long n_blks = blks_per_slot * p.n_slots;
-  const uint32_t esz = p.tf32 ? 4u : 2u;
+  constexpr uint32_t esz = TF32 ? 4u : 2u;
   const uint32_t blk_bytes = (uint32_t)kTileRows * p.kpad * esz;
   for (int k = threadIdx.x; k < p.in_dim; k += blockDim.x) {
     s_mu[k] = p.in_mu ? p.in_mu[k] : 0.f;
@@ -684,13 +685,13 @@ __global__ void __launch_bounds__(256) stage_inputs_block_kernel(const StagePara
   }
   auto off = [&](int r, int k) -> uint32_t {      // byte offset of element (r, k) inside the block image
     const int g8 = k >> 3;
-    if (p.tf32)   // fp32 elements, K chunks of 32: 8x4 core matrices of 128 bytes, LBO 128 / SBO 1024 like the bf16 image
+    if constexpr (TF32)   // fp32 elements, K chunks of 32: 8x4 core matrices of 128 bytes, LBO 128 / SBO 1024 like the bf16 image
       return (uint32_t)(k >> 5) * kWideBlk + (uint32_t)(r >> 3) * 1024u + (uint32_t)((k & 31) >> 2) * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(k & 3) * 4u;
     return p.chunked ? (uint32_t)(g8 >> 3) * kWideBlk + (uint32_t)(r >> 3) * 1024u + (uint32_t)(g8 & 7) * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(k & 7) * 2u
                      : (uint32_t)(r >> 3) * ((uint32_t)kg * 128u) + (uint32_t)g8 * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(k & 7) * 2u;
   };
   auto put = [&](int r, int k, float x) {
-    if (p.tf32) {
+    if constexpr (TF32) {
       const float hi = round_tf32(x);
       *reinterpret_cast<float*>(s_img + off(r, k)) = hi;
       if (p.split3 && k < p.in_dim) {   // [x_hi | x_lo | x_hi] (cmbpo_internal.cuh WideLayerPlan::split3)
@@ -701,7 +702,7 @@ __global__ void __launch_bounds__(256) stage_inputs_block_kernel(const StagePara
       *reinterpret_cast<__nv_bfloat16*>(s_img + off(r, k)) = __float2bfloat16_rn(x);
     }
   };
-  const int k_used = (p.tf32 && p.split3) ? 3 * p.in_dim : p.in_dim;     // first padding column
+  const int k_used = (TF32 && p.split3) ? 3 * p.in_dim : p.in_dim;     // first padding column
   const int n_pad = p.kpad - k_used;
   const float inv_pad = n_pad > 0 ? 1.0f / (float)n_pad : 0.f;
   for (long long b = blockIdx.x; b < n_blks; b += gridDim.x) {
@@ -742,16 +743,18 @@ cudaError_t launch_stage_inputs(const StageParams& p, int num_sms, cudaStream_t 
     const long long rows_pad0 = (p.n_rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
     long long nb = rows_pad0 / kTileRows * p.n_slots;
     const size_t smem = (size_t)kTileRows * p.kpad * (p.tf32 ? 4u : 2u);
-    static size_t smem_set = 48 * 1024;
-    if (smem > smem_set) {
-      cudaError_t e = cudaFuncSetAttribute(stage_inputs_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static size_t smem_set[2] = {48 * 1024, 48 * 1024};
+    if (smem > smem_set[p.tf32 ? 1 : 0]) {
+      cudaError_t e = p.tf32 ? cudaFuncSetAttribute(stage_inputs_block_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                             : cudaFuncSetAttribute(stage_inputs_block_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
-      smem_set = smem;
+      smem_set[p.tf32 ? 1 : 0] = smem;
     }
     const long long cap = (long long)num_sms * 8;
     if (nb > cap) nb = cap;
     if (nb < 1) nb = 1;
-    stage_inputs_block_kernel<<<(int)nb, 256, smem, stream>>>(p);
+    if (p.tf32) stage_inputs_block_kernel<true><<<(int)nb, 256, smem, stream>>>(p);
+    else stage_inputs_block_kernel<false><<<(int)nb, 256, smem, stream>>>(p);
     return cudaGetLastError();
   }
   const long long rows_pad = (p.n_rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);

@@ -686,14 +686,12 @@ static cudaError_t launch_step_post_EO(const StepParams& p, int n_blocks, cudaSt
     step_post3d_kernel<E, OPT><<<n_blocks, kPostThreads, smem, stream>>>(p);
     return cudaGetLastError();
   }
-  // 6..10 column parts (warps) per 32-row block, chosen so that the D columns split evenly over the warps (every warp
-  // waits at the block's barriers for the slowest one: D = 30 over 8 warps is 4 | 3 columns, 25 % of the arithmetic
-  // phase idle); ties go to more warps (shorter per-thread column chain).  D = 30 -> 10 x 3, D = 18 -> 9 x 2, D = 46 -> 8 x 6.
-  int parts = kPostMaxParts, best = 1 << 30;
-  for (int c = kPostMaxParts; c >= 6; --c) {
-    const int waste = (p.D + c - 1) / c * c - p.D;
-    if (waste < best) { best = waste; parts = c; }
-  }
+  // 8 column parts (warps) per 32-row block unless that leaves the last column round mostly idle (HalfCheetah, D = 18:
+  // 3 rounds of 8 at 75 % use -> 6 warps x 3 columns).  Measured at 1 M rows (tools/parts.sh, whole step): antsafe D = 30:
+  // 6 / 8 / 10 parts = 2912 / 2863 / 2875 us; HalfCheetah: 6 / 9 = 2524 / 2573 us -- balanced columns (10 x 3, 9 x 2) do
+  // not pay for the extra per-warp overhead per row block.
+  const int rounds = (p.D + kPostParts - 1) / kPostParts;
+  int parts = (p.D * 5 >= rounds * kPostParts * 4) ? kPostParts : (p.D + rounds - 1) / rounds;
   if (const char* ev = getenv("CMBPO_POST_PARTS_RT")) { const int c = atoi(ev); if (c >= 1 && c <= kPostMaxParts) parts = c; }
   const size_t smem = ((size_t)E * 2 * p.D * kPostRows + (size_t)kPostRows * p.obs_dim + 32) * sizeof(float);
   static bool attr_set = false;

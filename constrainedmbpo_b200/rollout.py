@@ -376,6 +376,9 @@ class ModelRollout:
             if was_enabled:
                 gc.enable()
         self._graph = g
+        # the graph holds raw pointers into the start-state tensor and into whatever the policy owns (its action buffer,
+        # its networks' workspaces): keep both alive as long as the graph can be replayed
+        self._captured_refs = (start_obs, policy)
         return g
 
     def replay(self):

@@ -759,3 +759,5 @@ def test_graph_replays_draw_fresh_philox_streams():
     ro.rng_base.copy_(base)
     ro.replay(); torch.cuda.synchronize()
     assert torch.equal(ro.pool["next_obs"], b)
+    # (the policy above is a temporary: capture() must keep it -- and its action buffer -- alive for the replays)
+    assert ro._captured_refs[1] is not None
