@@ -405,7 +405,23 @@ def run_gpu(args, w, wname):
         alloc = None
         if dense:
             from constrainedmbpo_b200.sharding import DensePoolGatherer, symmetric_pool_alloc
-            alloc = symmetric_pool_alloc()
+            # symmetric memory needs peer access between all ranks' GPUs; if the box cannot provide it, every rank falls
+            # back (collectively) to packed records over NCCL rather than failing the run
+            ok = torch.ones(1, device=dev)
+            try:
+                import torch.distributed._symmetric_memory as _symm
+                probe = _symm.empty(1024, dtype=torch.uint8, device=dev)
+                _symm.rendezvous(probe, dist.group.WORLD)
+            except Exception as exc:    # noqa: BLE001
+                ok.zero_()
+                if rank == 0:
+                    print(f"[bench] symmetric memory unavailable ({type(exc).__name__}: {exc}); using NCCL records", file=sys.stderr)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if float(ok) < 1:
+                dense, fmt = False, "records"
+                args.transport = "nccl"
+            else:
+                alloc = symmetric_pool_alloc()
         ros = [cm.ModelRollout(fe, w["T"], rollout_mode=w["mode"], dkl_lim=dkl_lim, row_offset=row0, pool_alloc=alloc)
                for _ in range(2 if dense else 1)]
         ro = ros[0]

@@ -63,7 +63,7 @@ class cmbpo_step_io(C.Structure):
         ("ep_var_dev", C.c_void_p), ("scalars_dev", C.c_void_p),
         ("workspace_dev", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("sample_mode", C.c_int32), ("bound_logvar", C.c_int32), ("max_logvar", C.c_float), ("min_logvar", C.c_float),
-        ("rng_offset_dev", C.c_void_p),
+        ("rng_offset_dev", C.c_void_p), ("perm_dev", C.c_void_p),
     ]
 
 
@@ -160,6 +160,7 @@ SYMBOLS = {
     "cmbpo_workspace_bytes": (C.c_size_t, [C.c_void_p, C.c_int64]),
     "cmbpo_predict": (C.c_int, [C.c_void_p, C.POINTER(cmbpo_predict_io), C.c_void_p]),
     "cmbpo_step": (C.c_int, [C.c_void_p, C.POINTER(cmbpo_step_io), C.c_void_p]),
+    "cmbpo_draw_permutation": (C.c_int, [C.c_int32, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "cmbpo_status": (C.c_int, [C.c_void_p, C.c_void_p]),
     "cmbpo_profile": (C.c_int, [C.c_void_p, C.c_int]),
     "cmbpo_profile_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),

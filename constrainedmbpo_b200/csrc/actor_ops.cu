@@ -60,7 +60,33 @@ __global__ void __launch_bounds__(256) k_actor_head(cmbpo_actor_io io) {
   }
 }
 
+// np.random.permutation(num_networks) of FakeEnv.forward_shuffle (mbpo/models/fake_env.py:309-316) drawn on the device:
+// one thread, Fisher-Yates from the front; stream id 0x50 ("P") in counter word 3, counter word 0 = step.
+__global__ void k_draw_permutation(int n, unsigned long long seed, unsigned long long rng_offset,
+                                   const unsigned long long* rng_offset_dev, unsigned long long step, int* perm) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const unsigned long long rng = rng_offset + (rng_offset_dev ? *rng_offset_dev : 0ull);
+  int v[CMBPO_MAX_MEMBERS];
+  for (int i = 0; i < n; ++i) v[i] = i;
+  for (int i = 0; i + 1 < n; ++i) {
+    uint32_t rnd[4];
+    philox4x32_10_a((uint32_t)step, (uint32_t)(step >> 32), (uint32_t)rng, 0x50000000u ^ (uint32_t)i,
+                    (uint32_t)seed, (uint32_t)(seed >> 32), rnd);
+    const int j = i + (int)(((unsigned long long)rnd[0] * (unsigned long long)(n - i)) >> 32);
+    const int t = v[i]; v[i] = v[j]; v[j] = t;
+  }
+  for (int i = 0; i < n; ++i) perm[i] = v[i];
+}
+
 }  // namespace cmbpo
+
+extern "C" int cmbpo_draw_permutation(int32_t n, uint64_t seed, uint64_t rng_offset, const uint64_t* rng_offset_dev,
+                                      uint64_t step, int32_t* perm_dev, void* stream_) {
+  if (n < 1 || n > CMBPO_MAX_MEMBERS || !perm_dev) return CMBPO_ERR_ARG;
+  cmbpo::k_draw_permutation<<<1, 32, 0, (cudaStream_t)stream_>>>(n, seed, rng_offset,
+      reinterpret_cast<const unsigned long long*>(rng_offset_dev), step, perm_dev);
+  return cudaGetLastError() == cudaSuccess ? CMBPO_OK : CMBPO_ERR_CUDA;
+}
 
 extern "C" int cmbpo_actor_head(const cmbpo_actor_io* io_, void* stream_) {
   if (!io_ || !io_->mu_dev || !io_->log_std_dev || !io_->pi_dev) return CMBPO_ERR_ARG;

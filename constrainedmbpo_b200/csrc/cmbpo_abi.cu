@@ -22,6 +22,7 @@ cudaError_t launch_wide_layer(const WideParams& p, int act, int num_sms, cudaStr
 }  // namespace cmbpo
 
 using namespace cmbpo;
+static_assert(kMaxMembers == CMBPO_MAX_MEMBERS && kMaxSeg == CMBPO_MAX_SEGMENTS, "include/cmbpo_b200.h and cmbpo_internal.cuh disagree");
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
@@ -303,7 +304,8 @@ static int check_ready(Handle* h) {
 }
 
 static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_width, int nseg, long long n_rows,
-                       const int* n_rows_dev, int ndim, const int32_t* perm, float* heads, cudaStream_t stream) {
+                       const int* n_rows_dev, int ndim, const int32_t* perm, const int32_t* perm_dev, float* heads,
+                       cudaStream_t stream) {
   const ModelPlan& pl = h->plan;
   FwdParams p;
   memset(&p, 0, sizeof(p));
@@ -349,6 +351,7 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
     p.member_of_slot[e] = m;
     p.input_of_slot[e] = (ndim == 3 && perm) ? perm[m] : e;
   }
+  p.perm_dev = (ndim == 3) ? perm_dev : nullptr;
   p.n_rows_dev = n_rows_dev;
   p.n_rows = n_rows;
   p.heads = heads;
@@ -392,6 +395,8 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
           wp.member_of_slot[e] = p.member_of_slot[e];
           wp.input_of_slot[e] = (l == 0) ? p.input_of_slot[e] : e;
         }
+        wp.perm_dev = p.perm_dev;
+        wp.perm_input = (l == 0) ? 1 : 0;
         if (l == 0) {
           wp.a_img = sp.a0img + (size_t)(row0 / kTileRows) * h->wl[0].k_chunks * kWideBlk;
           wp.a_slot_stride = sp.slot_stride_bytes;
@@ -444,7 +449,7 @@ extern "C" int cmbpo_predict(void* handle, const cmbpo_predict_io* io, void* str
   CU(cudaSetDevice(h->device), "cudaSetDevice");
   const ModelPlan& pl = h->plan;
   float* heads = static_cast<float*>(io->workspace_dev);
-  rc = run_forward(h, io->seg_dev, io->seg_width, CMBPO_MAX_SEGMENTS, io->n_rows, io->n_rows_dev, io->ndim, nullptr, heads, stream);
+  rc = run_forward(h, io->seg_dev, io->seg_width, CMBPO_MAX_SEGMENTS, io->n_rows, io->n_rows_dev, io->ndim, nullptr, nullptr, heads, stream);
   if (rc) return rc;
   const long long stride = row_stride_for(io->n_rows);
   if (io->agg == 0 || io->ndim == 3) {
@@ -484,7 +489,7 @@ extern "C" int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream_) 
   float* partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(heads) + ws_partials_offset(h, io->n_rows));
   const float* segs[CMBPO_MAX_SEGMENTS] = {io->obs_dev, io->act_dev, nullptr};
   const int32_t widths[CMBPO_MAX_SEGMENTS] = {obs_dim, act_dim, 0};
-  rc = run_forward(h, segs, widths, 2, io->n_rows, io->n_rows_dev, io->ndim, io->perm, heads, stream);
+  rc = run_forward(h, segs, widths, 2, io->n_rows, io->n_rows_dev, io->ndim, io->perm, io->perm_dev, heads, stream);
   if (rc) return rc;
   StepParams sp;
   memset(&sp, 0, sizeof(sp));

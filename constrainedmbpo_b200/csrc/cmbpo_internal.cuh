@@ -80,6 +80,7 @@ struct FwdParams {
   int per_slot_input;           // 0: 2-D input shared by all members; 1: 3-D input (fc.py:107-108)
   int member_of_slot[kMaxMembers];  // weights used for output slot j
   int input_of_slot[kMaxMembers];   // input slot feeding output slot j (3-D only)
+  const int* perm_dev;          // optional device [E] permutation overriding both maps (member = perm[j], input = perm[perm[j]])
   const int* n_rows_dev;        // optional device scalar with the live row count (rollout loop)
   long long n_rows;             // row count if n_rows_dev == nullptr
   float* heads;                 // out: tile-major head scratch (head_index), scaled mean | shifted logvar
@@ -130,6 +131,8 @@ struct WideParams {
   const float* head_shift;
   int member_of_slot[kMaxMembers];
   int input_of_slot[kMaxMembers];
+  const int* perm_dev;         // optional device [E] permutation: member = perm[j]; layer 0 (perm_input) input = perm[perm[j]]
+  int perm_input;
   int per_slot_input;
   const int* n_rows_dev;       // optional live row count of the WHOLE batch
   long long n_rows;            // rows of the whole batch if n_rows_dev == nullptr
@@ -137,5 +140,27 @@ struct WideParams {
   long long slab_rows;         // rows of this slab (multiple of 256 except for the last slab)
   int* status;
 };
+
+// Slot maps of the 3-D ('iv_gae') path: host arrays by default, a device permutation when the caller drew it on the GPU
+// (cmbpo_draw_permutation) so that a captured rollout replays with a fresh forward_shuffle every time.
+#ifdef __CUDACC__
+__device__ __forceinline__ int perm_at(const int* perm, int j, int E) {
+  const int m = __ldg(perm + j);
+  return m < 0 ? 0 : (m >= E ? E - 1 : m);
+}
+__device__ __forceinline__ int fwd_member_of(const FwdParams& p, int j) {
+  return p.perm_dev ? perm_at(p.perm_dev, j, p.plan.E) : p.member_of_slot[j];
+}
+__device__ __forceinline__ int fwd_input_of(const FwdParams& p, int j) {
+  return p.perm_dev ? perm_at(p.perm_dev, perm_at(p.perm_dev, j, p.plan.E), p.plan.E) : p.input_of_slot[j];
+}
+__device__ __forceinline__ int wide_member_of(const WideParams& p, int j) {
+  return p.perm_dev ? perm_at(p.perm_dev, j, p.E) : p.member_of_slot[j];
+}
+__device__ __forceinline__ int wide_input_of(const WideParams& p, int j) {
+  return (p.perm_dev && p.perm_input) ? perm_at(p.perm_dev, perm_at(p.perm_dev, j, p.E), p.E) : p.input_of_slot[j];
+}
+#endif
+
 
 }  // namespace cmbpo

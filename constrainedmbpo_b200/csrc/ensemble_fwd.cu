@@ -400,7 +400,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
         bool progress = false;
         if (fill_n < total && (f_use == 0 || mbar_try_wait(bar(BAR_W_EMPTY + f_slot), (f_use - 1) & 1))) {
           const LayerPlan& lp = pl.layer[f_l];
-          const uint8_t* blk = p.wimg + (size_t)(p.member_of_slot[f_e] * 2 + (int)cta) * pl.blk_bytes;
+          const uint8_t* blk = p.wimg + (size_t)(fwd_member_of(p, f_e) * 2 + (int)cta) * pl.blk_bytes;
           mbar_arrive_expect_tx(bar(BAR_W_FULL + f_slot), lp.bytes);
           bulk_g2s(smem_u32(smem + (uint32_t)f_slot * pl.slot_bytes), blk + lp.img_off, lp.bytes, bar(BAR_W_FULL + f_slot));
           if (++f_l == L) { f_l = 0; if (++f_e == e_end) f_e = e_begin; }
@@ -516,7 +516,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
             const long long pair = fill_n[s] / n_stage;
             const int est = (int)(fill_n[s] - pair * n_stage);
             const long long tile = vc + (2 * pair + s) * (long long)nvc;
-            const int in_slot = p.per_slot_input ? p.input_of_slot[e_begin + est] : 0;
+            const int in_slot = p.per_slot_input ? fwd_input_of(p, e_begin + est) : 0;
             const uint8_t* src = p.a0img + (size_t)in_slot * p.a0_slot_stride + (size_t)(tile * 2 + cta) * pl.a0_bytes;
             mbar_arrive_expect_tx(bar(BAR_A0_FULL + s), pl.a0_bytes);
             bulk_g2s(smem_u32(smem + sl.off_a0 + s * pl.a0_bytes), src, pl.a0_bytes, bar(BAR_A0_FULL + s));
@@ -738,7 +738,113 @@ __global__ void __launch_bounds__(256) stage_inputs_block_kernel(const StagePara
   }
 }
 
+// bf16 images, third version: the raw fp32 rows of the block come in with 16-byte cp.async copies (a 128-row block of a
+// segment is one contiguous run in global memory, so there is no per-element index arithmetic on the way in); then each
+// thread produces whole 16-byte chunks of the image -- 8 consecutive K columns of one row: 8 shared-memory reads, the
+// scaler, four cvt.rn.bf16x2 -- and stores them straight to global memory, consecutive lanes writing consecutive chunks.
+// A thread keeps its K group for the whole launch (the stride over chunks is a multiple of 8 * kg), so segment base,
+// width, scaler mean / inverse and the padding constants of its 8 columns live in registers.  The block version above
+// spends ~25 instructions and a 4-way bank-conflicted 2-byte shared store per ELEMENT (2.2 TB/s); it stays for tf32.
+__device__ __forceinline__ void stage_cp_async16(void* dst_smem, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__global__ void __launch_bounds__(256) stage_rows_kernel(const StageParams p) {
+  extern __shared__ __align__(16) float s_x[];                // raw rows, segment after segment: [seg][128][w]
+  const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
+  const long long rows_pad = (n_rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
+  const int kg = p.kpad >> 3;
+  const long long blks_per_slot = rows_pad / kTileRows;
+  const long long n_blks = blks_per_slot * p.n_slots;
+  const uint32_t blk_bytes = (uint32_t)kTileRows * p.kpad * 2u;
+  const int span = 8 * kg;                                    // chunks per 8-row group
+  const int stride = (256 / span) * span;                     // active threads: a multiple of span (kg <= 32)
+  const int tid = threadIdx.x;
+  const bool active = tid < stride;
+  const int g8 = (tid >> 3) % kg, rl = tid & 7;
+  const int r8_first = tid / span, r8_step = stride / span;
+  int seg_base[kMaxSeg], sb = 0;
+#pragma unroll
+  for (int sg = 0; sg < kMaxSeg; ++sg) { seg_base[sg] = sb; sb += (kTileRows * p.seg_width[sg] + 3) & ~3; }
+  // the thread's 8 columns
+  int c_base[8], c_w[8];
+  float c_mu[8], c_inv[8], c_pad[8];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int k = g8 * 8 + u;
+    c_base[u] = -1; c_w[u] = 0; c_mu[u] = 0.f; c_inv[u] = 1.f;
+    c_pad[u] = (k >= p.in_dim && k < p.in_dim + 2 && !p.chunked) ? 1.0f : 0.0f;   // constant-one carriers of the bias rows
+    if (k < p.in_dim) {
+      int kk = k, sg = 0;
+      while (sg < kMaxSeg - 1 && kk >= p.seg_width[sg]) { kk -= p.seg_width[sg]; ++sg; }
+      c_base[u] = seg_base[sg] + kk; c_w[u] = p.seg_width[sg];
+      c_mu[u] = p.in_mu ? p.in_mu[k] : 0.f;
+      c_inv[u] = p.in_inv ? p.in_inv[k] : 1.f;
+    }
+  }
+  for (long long b = blockIdx.x; b < n_blks; b += gridDim.x) {
+    const int slot = (int)(b / blks_per_slot);
+    const long long blk = b - (long long)slot * blks_per_slot;
+    const long long row0 = blk * kTileRows;
+    const int rows_here = (int)max(0LL, min((long long)kTileRows, n_rows - row0));
+    __syncthreads();                                           // the previous block's rows have been consumed
+#pragma unroll
+    for (int sg = 0; sg < kMaxSeg; ++sg) {
+      const int w = p.seg_width[sg];
+      if (w <= 0) continue;
+      const float* src = p.seg_ptr[sg] + (size_t)slot * p.seg_slot_stride[sg] + (size_t)row0 * w;
+      float* dst = s_x + seg_base[sg];
+      const int n_live = rows_here * w;
+      if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        const int n4 = n_live >> 2;
+        for (int i = tid; i < n4; i += 256) stage_cp_async16(dst + 4 * i, src + 4 * i);
+        for (int i = 4 * n4 + tid; i < n_live; i += 256) dst[i] = __ldg(src + i);
+      } else {
+        for (int i = tid; i < n_live; i += 256) dst[i] = __ldg(src + i);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    if (active) {
+      uint4* out = reinterpret_cast<uint4*>(p.a0img + (size_t)slot * p.slot_stride_bytes + (size_t)blk * blk_bytes);
+      for (int r8 = r8_first; r8 < kTileRows / 8; r8 += r8_step) {
+        const int r = r8 * 8 + rl;
+        const bool live = r < rows_here;
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          float x = c_pad[u];
+          if (c_base[u] >= 0) x = live ? (s_x[c_base[u] + r * c_w[u]] - c_mu[u]) * c_inv[u] : 0.f;
+          v[u] = live ? x : 0.f;
+        }
+        const uint4 q = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+        const uint32_t idx = p.chunked ? (uint32_t)(g8 >> 3) * (kWideBlk / 16) + (uint32_t)r8 * 64u + (uint32_t)(g8 & 7) * 8u + (uint32_t)rl
+                                       : ((uint32_t)r8 * kg + (uint32_t)g8) * 8u + (uint32_t)rl;
+        out[idx] = q;
+      }
+    }
+  }
+}
+
 cudaError_t launch_stage_inputs(const StageParams& p, int num_sms, cudaStream_t stream) {
+  size_t raw_bytes = 0;
+  for (int sg = 0; sg < kMaxSeg; ++sg) raw_bytes += (((size_t)kTileRows * p.seg_width[sg] + 3) & ~(size_t)3) * sizeof(float);
+  if (!p.tf32 && p.kpad <= 256 && raw_bytes <= 200 * 1024) {
+    const long long rows_pad0 = (p.n_rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
+    long long nb = rows_pad0 / kTileRows * p.n_slots;
+    static size_t raw_set = 48 * 1024;
+    if (raw_bytes > raw_set) {
+      cudaError_t e = cudaFuncSetAttribute(stage_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)raw_bytes);
+      if (e != cudaSuccess) return e;
+      raw_set = raw_bytes;
+    }
+    const long long per_sm = (long long)(200 * 1024 / (raw_bytes + 1024));
+    const long long cap = (long long)num_sms * (per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm));
+    if (nb > cap) nb = cap;
+    if (nb < 1) nb = 1;
+    stage_rows_kernel<<<(int)nb, 256, raw_bytes, stream>>>(p);
+    return cudaGetLastError();
+  }
   if (p.kpad <= (p.tf32 ? kStageMaxK : 256)) {
     const long long rows_pad0 = (p.n_rows + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
     long long nb = rows_pad0 / kTileRows * p.n_slots;

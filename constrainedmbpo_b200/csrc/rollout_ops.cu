@@ -314,18 +314,48 @@ __global__ void __launch_bounds__(kRB) k_store_payload(cmbpo_rollout_io io, cons
 
 // synthetic benchmark policy a = tanh(obs @ P); not part of the reference.  One thread per row: the
 // block's 256 obs rows come in through a coalesced flat copy into shared memory (row stride OD + 1: conflict-free row
-// reads), P is read as shared-memory broadcasts, 8 action columns are accumulated in registers per pass, and the
-// actions leave through shared memory as a coalesced flat copy.  (The first version computed one output element per
-// thread from a 64-row tile: 59 M warp instructions per 1 M rows, 84 us; this one is bound by its 92 MB of traffic.)
+// reads); P sits in shared memory with its rows padded to a multiple of 4 columns and is read as 16-byte broadcasts, up to
+// 24 action columns accumulated in registers per pass (one pass for every environment of the spec), and the actions leave
+// through shared memory as a coalesced flat copy.  (Version 1 computed one output element per thread from a 64-row tile:
+// 59 M warp instructions per 1 M rows; version 2 read P with scalar broadcasts, 9 shared loads per 8 FMAs, and was bound
+// by the shared-memory pipe -- 198 us for 875 k Humanoid rows; this one is bound by its traffic.)
 constexpr int kPolRows = 256;
+template <int NG>
+__device__ __forceinline__ void stub_policy_row(const float* __restrict__ xo, const float* __restrict__ sP, int AP, int OD,
+                                                int a0, int AD, float* __restrict__ out) {
+  float acc[NG * 4];
+#pragma unroll
+  for (int u = 0; u < NG * 4; ++u) acc[u] = 0.f;
+  for (int d = 0; d < OD; ++d) {
+    const float x = xo[d];
+    const float4* pr = reinterpret_cast<const float4*>(sP + d * AP + a0);
+#pragma unroll
+    for (int g = 0; g < NG; ++g) {
+      const float4 w = pr[g];
+      acc[4 * g + 0] = fmaf(x, w.x, acc[4 * g + 0]);
+      acc[4 * g + 1] = fmaf(x, w.y, acc[4 * g + 1]);
+      acc[4 * g + 2] = fmaf(x, w.z, acc[4 * g + 2]);
+      acc[4 * g + 3] = fmaf(x, w.w, acc[4 * g + 3]);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < NG * 4; ++u)
+    if (a0 + u < AD) out[a0 + u] = tanhf(acc[u]);
+}
+
 __global__ void __launch_bounds__(kPolRows) k_stub_policy(const float* __restrict__ obs, const float* __restrict__ P,
                                                           float* __restrict__ act, const int* n_rows_dev,
                                                           long long n_rows, int OD, int AD, int n_slots) {
-  extern __shared__ float sm[];
-  float* sP = sm;                         // [OD][AD]
-  float* sO = sm + OD * AD;               // [kPolRows][OD + 1]
+  extern __shared__ __align__(16) float sm[];
+  const int AP = (AD + 3) & ~3;
+  float* sP = sm;                         // [OD][AP], columns AD..AP-1 zero
+  float* sO = sm + OD * AP;               // [kPolRows][OD + 1]
   float* sA = sO + kPolRows * (OD + 1);   // [kPolRows][AD]
-  for (int i = threadIdx.x; i < OD * AD; i += blockDim.x) sP[i] = P[i];
+  const float inv_ap = 1.0f / (float)AP;
+  for (int i = threadIdx.x; i < OD * AP; i += blockDim.x) {
+    const int d = fast_div(i, inv_ap), a = i - d * AP;
+    sP[i] = a < AD ? P[d * AD + a] : 0.f;
+  }
   const long long n = n_rows_dev ? (long long)(*n_rows_dev) : n_rows;
   const long long tiles_per_slot = (n + kPolRows - 1) / kPolRows;
   const long long n_tiles = tiles_per_slot * n_slots;   // slot e of obs / act starts at row e * n_rows (capacity)
@@ -343,18 +373,16 @@ __global__ void __launch_bounds__(kPolRows) k_stub_policy(const float* __restric
     const int r = threadIdx.x;
     if (r < rows_here) {
       const float* xo = sO + r * (OD + 1);
-      for (int a0 = 0; a0 < AD; a0 += 8) {
-        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        for (int d = 0; d < OD; ++d) {
-          const float x = xo[d];
-          const float* pr = sP + d * AD + a0;
-#pragma unroll
-          for (int u = 0; u < 8; ++u)
-            if (a0 + u < AD) acc[u] = fmaf(x, pr[u], acc[u]);
+      float* out = sA + r * AD;
+      for (int a0 = 0; a0 < AP; a0 += 24) {
+        switch (min(6, (AP - a0) >> 2)) {
+          case 1: stub_policy_row<1>(xo, sP, AP, OD, a0, AD, out); break;
+          case 2: stub_policy_row<2>(xo, sP, AP, OD, a0, AD, out); break;
+          case 3: stub_policy_row<3>(xo, sP, AP, OD, a0, AD, out); break;
+          case 4: stub_policy_row<4>(xo, sP, AP, OD, a0, AD, out); break;
+          case 5: stub_policy_row<5>(xo, sP, AP, OD, a0, AD, out); break;
+          default: stub_policy_row<6>(xo, sP, AP, OD, a0, AD, out); break;
         }
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-          if (a0 + u < AD) sA[r * AD + a0 + u] = tanhf(acc[u]);
       }
     }
     __syncthreads();
@@ -474,7 +502,7 @@ extern "C" int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* a
   if (n_slots < 1) n_slots = 1;
   long long blocks = ((n_rows + kPolRows - 1) / kPolRows) * n_slots;
   if (blocks > 148 * 6) blocks = 148 * 6;
-  const size_t smem = ((size_t)obs_dim * act_dim + (size_t)kPolRows * (obs_dim + 1 + act_dim)) * sizeof(float);
+  const size_t smem = ((size_t)obs_dim * ((act_dim + 3) & ~3) + (size_t)kPolRows * (obs_dim + 1 + act_dim)) * sizeof(float);
   if (smem > 200 * 1024) return CMBPO_ERR_UNSUPPORTED;
   static size_t smem_set = 48 * 1024;
   if (smem > smem_set) {

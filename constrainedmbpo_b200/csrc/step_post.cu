@@ -478,7 +478,7 @@ __global__ void __launch_bounds__(kPostMaxParts * kPostRows, 3) step_post_kernel
 // (dynamic) shared memory so global traffic stays coalesced.  Warp `part` < E then evaluates the static
 // termination / cost function of member `part`.
 template <int E, bool OPT>
-__global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post3d_kernel(const StepParams p) {
+__global__ void __launch_bounds__(kPostThreads, 768 / kPostThreads) step_post3d_kernel(const StepParams p) {
   extern __shared__ float tiles[];                 // [E][kPostRows * OD]
   __shared__ float s_kl[kPostParts][kPostRows], s_epv[kPostParts][kPostRows];
   __shared__ float s_rew[E][kPostRows];
@@ -509,12 +509,27 @@ __global__ void __launch_bounds__(kPostThreads, 1024 / kPostThreads) step_post3d
     float kl_row = 0.f, epv_row = 0.f;
     uint32_t fin = (1u << E) - 1u, lt = (1u << E) - 1u;
     if (live) {
+      // the 2E head values of the NEXT column of this warp are loaded before the current column is evaluated (register
+      // double buffer): twice the loads in flight per thread, the kernel is bound by the latency of these strided reads
+      float mn[E], lvn[E];
+      if (part < D) {
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          mn[e] = hrow[(e * 2 * D + part) * kTileRows];
+          lvn[e] = hrow[(e * 2 * D + D + part) * kTileRows];
+        }
+      }
       for (int d = part; d < D; d += kPostParts) {
         float m[E], lv[E], v[E];
 #pragma unroll
-        for (int e = 0; e < E; ++e) {
-          m[e] = hrow[(e * 2 * D + d) * kTileRows];
-          lv[e] = hrow[(e * 2 * D + D + d) * kTileRows];
+        for (int e = 0; e < E; ++e) { m[e] = mn[e]; lv[e] = lvn[e]; }
+        const int dn = d + kPostParts;
+        if (dn < D) {
+#pragma unroll
+          for (int e = 0; e < E; ++e) {
+            mn[e] = hrow[(e * 2 * D + dn) * kTileRows];
+            lvn[e] = hrow[(e * 2 * D + D + dn) * kTileRows];
+          }
         }
         if (d < OD) {
 #pragma unroll

@@ -136,9 +136,9 @@ __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __gri
             const int e = it.slot(), tile = it.tile(), c = it.chunk();
             const int chunk_n = min(kWideNC, lp.npad - c * kWideNC);
             b_bytes = (uint32_t)(chunk_n >> 1) * 128u;
-            const int in_slot = p.per_slot_input ? p.input_of_slot[e] : 0;
+            const int in_slot = p.per_slot_input ? wide_input_of(p, e) : 0;
             a_src = p.a_img + (size_t)in_slot * p.a_slot_stride + (size_t)(tile * 2 + (int)cta) * KC * kWideBlk;
-            b_src = p.w_img + (((size_t)p.member_of_slot[e] * NCH + c) * 2 + cta) * KC * kWideBlk;
+            b_src = p.w_img + (((size_t)wide_member_of(p, e) * NCH + c) * 2 + cta) * KC * kWideBlk;
           }
           const uint32_t dst = smem_u32(smem + (uint32_t)f_stage * kWideStageBytes);
           mbar_arrive_expect_tx(bar(WB_FULL + f_stage), kWideBlk + b_bytes);
@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(kWideThreads, 1) wide_layer_kernel(const __gri
       const int chunk_n = min(kWideNC, lp.npad - c * kWideNC);
       const int nch = chunk_n >> 4, h0 = (nch + 1) >> 1;
       const int cb = half ? h0 : 0, ce = half ? nch : h0;
-      const float* bias = p.bias + (size_t)p.member_of_slot[e] * lp.npad + c * kWideNC;
+      const float* bias = p.bias + (size_t)wide_member_of(p, e) * lp.npad + c * kWideNC;
       mbar_wait(bar(WB_ACC_FULL + acc), (n_item >> 1) & 1, p.status, WWC_EPI_ACC);
       tc_fence_after();
       const uint32_t d_addr = tmem_base + lane_base + acc * kWideNC;

@@ -101,7 +101,9 @@ class FakeEnv:
                     row_ids=None, want_ep_var=True, out=None, rng_offset_dev=None):
         """CUDA tensors in, dict of CUDA tensors out.  ``elite_idx`` (int32 [B]) injects the
         ``random_inds`` draw; None -> in-kernel Philox over the elite list.  ``perm`` injects the
-        ``forward_shuffle`` permutation of the 3-D path.  ``n_rows_dev``: optional int32 device
+        ``forward_shuffle`` permutation of the 3-D path; ``perm="device"`` draws it on the GPU (cmbpo_draw_permutation,
+        Philox keyed like the elite draws: fresh on every replay of a captured rollout); an int32 CUDA tensor [E] is used
+        as is.  ``n_rows_dev``: optional int32 device
         scalar with the live row count (rollout loop; shapes stay at capacity).  ``rng_offset_dev``: optional uint64 /
         int64 device word the kernel adds to the Philox stream id (a captured rollout advances it per replay)."""
         m = self._model
@@ -137,11 +139,22 @@ class FakeEnv:
         io.n_rows_dev = n_rows_dev.data_ptr() if n_rows_dev is not None else None
         io.ndim = ndim
         perm_arr = None
+        draw_perm = False
         if ndim == 3:
-            if perm is None:
-                perm = np.random.permutation(E)  # fake_env.py:314
-            perm_arr = np.ascontiguousarray(np.asarray(perm, dtype=np.int32))
-            io.perm = perm_arr.ctypes.data_as(C.POINTER(C.c_int32))
+            if isinstance(perm, str):
+                if perm != "device":
+                    raise ValueError("perm must be an array, a CUDA int32 tensor, None or 'device'")
+                if getattr(self, "_perm_dev", None) is None:
+                    self._perm_dev = torch.empty(E, dtype=torch.int32, device=dev)
+                io.perm_dev, draw_perm = self._perm_dev.data_ptr(), True
+            elif torch.is_tensor(perm):
+                perm_arr = perm.to(device=dev, dtype=torch.int32).contiguous()
+                io.perm_dev = perm_arr.data_ptr()
+            else:
+                if perm is None:
+                    perm = np.random.permutation(E)  # fake_env.py:314
+                perm_arr = np.ascontiguousarray(np.asarray(perm, dtype=np.int32))
+                io.perm = perm_arr.ctypes.data_as(C.POINTER(C.c_int32))
         keep = [perm_arr]
         if elite_idx is not None:
             elite_idx = elite_idx.to(device=dev, dtype=torch.int32).contiguous()
@@ -155,6 +168,8 @@ class FakeEnv:
         self._rng_offset += 1
         if rng_offset_dev is not None:
             io.rng_offset_dev = rng_offset_dev.data_ptr()
+        if draw_perm:
+            _lib.check(m._lib.cmbpo_draw_permutation(E, io.seed, io.rng_offset, io.rng_offset_dev, 0, io.perm_dev, m._stream()))
         io.sample_mode = 1 if self.sample_noise else 0
         if self.logvar_bound is not None:
             io.bound_logvar, io.max_logvar, io.min_logvar = 1, self.logvar_bound[0], self.logvar_bound[1]

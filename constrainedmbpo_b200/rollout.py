@@ -152,8 +152,9 @@ class ModelRollout:
             raise NotImplementedError("max_samples with a row-sharded rollout: the cap is defined on the global row order "
                                       "(model_sampler.py:327-332); run the capped rollout on one device")
         # 'iv_gae' only: perm_fn(step) -> the forward_shuffle permutation FakeEnv.step draws per call
-        # (fake_env.py:309-316, global NumPy RNG upstream).  It is a launch argument, so a captured graph
-        # replays the permutations drawn at capture time.
+        # (fake_env.py:309-316, global NumPy RNG upstream), injected as a host launch argument (a captured graph then
+        # replays the permutations given at capture time).  None: the env draws it on the device, keyed by rng_base, so
+        # every replay of a captured rollout shuffles afresh.
         self.perm_fn = perm_fn
         # Optional critics in the loop: value_fn(obs, n_rows_dev, path_ids) -> (v, vc), CUDA float32
         # tensors shaped [capacity] ('iv_gae': [E, capacity]) holding V(obs), VC(obs) of the live rows -- what
@@ -265,8 +266,9 @@ class ModelRollout:
         else:
             act = policy(cur, n_dev)
         perm = None
-        if self.mode == "iv_gae" and self.perm_fn is not None:
-            perm = self.perm_fn(self.steps_done)
+        if self.mode == "iv_gae":       # no perm_fn: drawn on the device per step, fresh on every replay of a capture
+            perm = self.perm_fn(self.steps_done) if self.perm_fn is not None else \
+                ("device" if getattr(env, "supports_rng_offset_dev", False) else None)
         kw = {"rng_offset_dev": self.rng_base} if getattr(env, "supports_rng_offset_dev", False) else {}
         o = env.step_device(cur, act, n_rows_dev=n_dev, row_ids=row_ids, want_ep_var=False, out=self._step_out,
                             perm=perm, **kw)

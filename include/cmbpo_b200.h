@@ -25,6 +25,7 @@ extern "C" {
 
 #define CMBPO_MAX_LAYERS 8
 #define CMBPO_MAX_SEGMENTS 3
+#define CMBPO_MAX_MEMBERS 16     /* ensemble members a handle can hold */
 
 enum {
   CMBPO_OK = 0,
@@ -168,8 +169,18 @@ typedef struct cmbpo_step_io {
   /* Optional device word added to rng_offset by the kernel (NULL = 0): a launch captured in a CUDA graph draws from a
    * fresh Philox stream on every replay when the graph also advances this word (ModelRollout.reset does). */
   const uint64_t* rng_offset_dev;
+  /* Optional DEVICE [E] forward_shuffle permutation (3-D only); takes precedence over the host `perm`.  Filled by
+   * cmbpo_draw_permutation inside the same stream / CUDA graph, it gives every replay of a captured 'iv_gae' rollout a
+   * fresh permutation per step, like the reference's np.random.permutation per FakeEnv.step call (fake_env.py:314). */
+  const int32_t* perm_dev;
 } cmbpo_step_io;
 int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream);
+
+/* Uniform random permutation of 0..n-1 on the device (np.random.permutation(num_networks), fake_env.py:314): Fisher-Yates
+ * driven by Philox4x32-10 words keyed by (seed, rng_offset + *rng_offset_dev, step); element i is swapped with
+ * j = i + floor(u * (n - i)), u the 32-bit word / 2^32.  n <= CMBPO_MAX_MEMBERS.  perm_dev: int32[n]. */
+int cmbpo_draw_permutation(int32_t n, uint64_t seed, uint64_t rng_offset, const uint64_t* rng_offset_dev, uint64_t step,
+                           int32_t* perm_dev, void* stream);
 
 /* ---- device-resident rollout bookkeeping (ModelSampler.sample around env.step,
  * softlearning/samplers/model_sampler.py:311-332,:386-474; ModelBuffer.store_multiple,

@@ -93,14 +93,19 @@ ATOL_SCALE_TF32 = 1e-3
 VAR_RTOL_TF32 = 2e-3
 
 
-def assert_means_close(got, ref, s_out, rtol=RTOL_BF16, atol_scale=ATOL_SCALE_BF16, what="mean"):
+def assert_means_close(got, ref, s_out, rtol=RTOL_BF16, atol_scale=ATOL_SCALE_BF16, what="mean", outlier_frac=0.0):
+    """|got - ref| <= rtol * |ref| + atol_scale * s_out element-wise.  ``outlier_frac`` > 0 (only the shallow-net tf32 cases
+    use it): at most that fraction of the elements may exceed the bound, and none by more than a factor of two."""
     got = np.asarray(got, np.float64)
     ref = np.asarray(ref, np.float64)
     bound = rtol * np.abs(ref) + atol_scale * s_out
-    bad = np.abs(got - ref) > bound
+    err = np.abs(got - ref)
+    bad = err > bound
     frac = np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-30)
-    assert not bad.any(), (f"{what}: {int(bad.sum())}/{bad.size} elements outside rtol={rtol} atol={atol_scale}*s_out; "
-                           f"worst excess {(np.abs(got - ref) - bound).max():.3e}; relative Frobenius error {frac:.3e}")
+    msg = (f"{what}: {int(bad.sum())}/{bad.size} elements outside rtol={rtol} atol={atol_scale}*s_out; "
+           f"worst excess {(err - bound).max():.3e}; relative Frobenius error {frac:.3e}")
+    assert bad.sum() <= outlier_frac * bad.size, msg
+    assert not (err > 2 * bound).any(), msg
     return frac
 
 
@@ -159,3 +164,14 @@ def philox_normals(rows, D, stream, seed, member=0):
                       np.uint64(0x9E3779B9) ^ col, seed & 0xFFFFFFFF, seed >> 32)
     unit = lambda x: ((x >> np.uint64(8)).astype(np.float64) + 1.0) / 16777216.0
     return np.sqrt(-2.0 * np.log(unit(r[0]))) * np.cos(2.0 * np.pi * unit(r[1]))
+
+
+def philox_permutation(n, seed, stream, step=0):
+    """The permutation actor_ops.cu's k_draw_permutation produces: Fisher-Yates from the front, swap partner
+    j = i + floor(word0 * (n - i) / 2^32) with Philox counter (step, stream, 0x50000000 ^ i)."""
+    v = list(range(n))
+    for i in range(n - 1):
+        w = philox4x32_10(step & 0xFFFFFFFF, step >> 32, stream & 0xFFFFFFFF, 0x50000000 ^ i, seed & 0xFFFFFFFF, seed >> 32)
+        j = i + ((int(w[0]) * (n - i)) >> 32)
+        v[i], v[j] = v[j], v[i]
+    return np.asarray(v, np.int32)

@@ -761,3 +761,28 @@ def test_graph_replays_draw_fresh_philox_streams():
     assert torch.equal(ro.pool["next_obs"], b)
     # (the policy above is a temporary: capture() must keep it -- and its action buffer -- alive for the replays)
     assert ro._captured_refs[1] is not None
+
+
+def test_iv_gae_graph_replays_shuffle_afresh():
+    """'iv_gae' without an injected perm_fn: the forward_shuffle permutation is drawn on the device per step (keyed by
+    the rollout's rng_base word), so replays of ONE captured graph use different permutations -- upstream draws
+    np.random.permutation on every FakeEnv.step call (fake_env.py:314) -- and restoring the word reproduces a replay."""
+    import torch
+    import constrainedmbpo_b200 as cm
+    env, B, T = "humanoidsafe", 1500, 4
+    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
+    obs, _ = make_inputs(env, B)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True, seed=5)
+    ro = cm.ModelRollout(fe, T, rollout_mode="iv_gae")
+    pol = cm.StubPolicy(fe.obs_dim, fe.act_dim, device="cuda:0")
+    ro.capture(torch.from_numpy(obs).cuda(), pol)
+    ro.replay(); torch.cuda.synchronize()
+    a = ro.pool["next_obs"].clone()
+    base = ro.rng_base.clone()
+    ro.replay(); torch.cuda.synchronize()
+    b = ro.pool["next_obs"].clone()
+    # slot j holds f_{p[j]}(x[p[p[j]]]): with another permutation (almost) every slot's first transition changes
+    assert not torch.equal(a[:, :, 0], b[:, :, 0])
+    ro.rng_base.copy_(base)
+    ro.replay(); torch.cuda.synchronize()
+    assert torch.equal(ro.pool["next_obs"], b)

@@ -370,3 +370,58 @@ def test_step_logvar_soft_bounding_option():
     assert abs(rb["ensemble_mean_var"] - ru["ensemble_mean_var"]) > 0.2 * ru["ensemble_mean_var"]   # the bound bites
     rel = np.abs(info["ensemble_dkl_path"] - rb["ensemble_dkl_path"]) / (np.abs(rb["ensemble_dkl_path"]) + 1e-6)
     assert np.median(rel) < 2e-2
+
+
+def test_step_3d_device_drawn_permutation():
+    """perm="device": np.random.permutation(E) of forward_shuffle (fake_env.py:314) drawn by cmbpo_draw_permutation --
+    the kernel's Fisher-Yates over Philox words restated in tests/helpers.philox_permutation -- and consumed by the
+    forward kernels from device memory; the step then equals the one with the same permutation injected from the host."""
+    import torch
+    from tests.helpers import philox_permutation
+    env = "humanoidsafe"
+    p = make_params(env, HIDDEN)
+    E, B = 7, 700
+    obs, act = make_inputs(env, B, E=E)
+    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True, seed=11)
+    o_d, a_d = torch.from_numpy(obs).cuda(), torch.from_numpy(act).cuda()
+    seen = set()
+    for call in range(6):
+        stream = fe._rng_offset
+        out = fe.step_device(o_d, a_d, perm="device", want_ep_var=False)
+        got = {k: v.clone() for k, v in out.items() if v is not None}
+        perm = fe._perm_dev.cpu().numpy()
+        assert sorted(perm.tolist()) == list(range(E))
+        assert np.array_equal(perm, philox_permutation(E, fe._seed, stream))
+        seen.add(tuple(perm.tolist()))
+        ref = fe.step_device(o_d, a_d, perm=perm, want_ep_var=False)
+        for k in ("next_obs", "rew", "term", "cost", "dkl_path"):
+            assert torch.equal(got[k], ref[k]), (call, k)
+        # a CUDA tensor permutation takes the same path
+        ref2 = fe.step_device(o_d, a_d, perm=torch.from_numpy(perm).cuda(), want_ep_var=False)
+        assert torch.equal(got["next_obs"], ref2["next_obs"])
+    assert len(seen) >= 5                                    # 7! = 5040 permutations: six draws practically never collide
+    # the device word is added to the stream id (what a captured rollout advances per replay)
+    base = torch.tensor([1000], dtype=torch.int64, device="cuda")
+    stream = fe._rng_offset
+    fe.step_device(o_d, a_d, perm="device", want_ep_var=False, rng_offset_dev=base)
+    assert np.array_equal(fe._perm_dev.cpu().numpy(), philox_permutation(E, fe._seed, stream + 1000))
+
+
+def test_draw_permutation_is_uniform():
+    import ctypes as C
+    import torch
+    from constrainedmbpo_b200 import _lib
+    lib = _lib.load()
+    n, draws = 4, 6000
+    buf = torch.empty((draws, n), dtype=torch.int32, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+    for i in range(draws):
+        _lib.check(lib.cmbpo_draw_permutation(n, 99, i, None, 0, buf[i].data_ptr(), s))
+    perms = buf.cpu().numpy()
+    assert (np.sort(perms, 1) == np.arange(n)).all()
+    codes = (perms * (n ** np.arange(n))).sum(1)
+    _, counts = np.unique(codes, return_counts=True)
+    assert counts.size == 24
+    expect = draws / 24
+    chi2 = ((counts - expect) ** 2 / expect).sum()
+    assert chi2 < 60, chi2                                   # 23 dof: P(chi2 > 60) ~ 3e-5
