@@ -360,19 +360,32 @@ __global__ void __launch_bounds__(kPolRows) k_stub_policy(const float* __restric
   const long long tiles_per_slot = (n + kPolRows - 1) / kPolRows;
   const long long n_tiles = tiles_per_slot * n_slots;   // slot e of obs / act starts at row e * n_rows (capacity)
   const float inv_od = 1.0f / (float)OD;
+  const bool dense = (OD & 1) && (reinterpret_cast<uintptr_t>(obs) & 15) == 0 && (((size_t)n_rows * OD) & 3) == 0 &&
+                     ((OD * AP) & 3) == 0;
+  const int ld_o = dense ? OD : OD + 1;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long slot = tile / tiles_per_slot, r0 = (tile - slot * tiles_per_slot) * kPolRows;
     const int rows_here = (int)min((long long)kPolRows, n - r0);
     const size_t row_base = (size_t)(slot * n_rows + r0);
     __syncthreads();
-    for (int i = threadIdx.x; i < rows_here * OD; i += kPolRows) {
-      const int r = fast_div(i, inv_od), d = i - r * OD;
-      sO[r * (OD + 1) + d] = obs[row_base * OD + i];
+    if (dense) {       // odd OD: rows at stride OD are conflict-free as they are, the tile is one flat 16-byte cp.async copy
+      const float* src = obs + row_base * OD;
+      const int n_el = rows_here * OD, n4 = n_el >> 2;
+      for (int q = threadIdx.x; q < n4; q += kPolRows)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(sO + 4 * q)), "l"(src + 4 * q) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      for (int i = 4 * n4 + threadIdx.x; i < n_el; i += kPolRows) sO[i] = src[i];
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    } else {
+      for (int i = threadIdx.x; i < rows_here * OD; i += kPolRows) {
+        const int r = fast_div(i, inv_od), d = i - r * OD;
+        sO[r * (OD + 1) + d] = obs[row_base * OD + i];
+      }
     }
     __syncthreads();
     const int r = threadIdx.x;
     if (r < rows_here) {
-      const float* xo = sO + r * (OD + 1);
+      const float* xo = sO + r * ld_o;
       float* out = sA + r * AD;
       for (int a0 = 0; a0 < AP; a0 += 24) {
         switch (min(6, (AP - a0) >> 2)) {

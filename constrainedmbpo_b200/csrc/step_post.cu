@@ -491,6 +491,10 @@ __global__ void __launch_bounds__(kPostThreads, 768 / kPostThreads) step_post3d_
   const int D = p.D, OD = p.obs_dim;
   const int tile_elems = kPostRows * OD;
   float acc_dkl = 0.f, acc_var = 0.f, acc_rew = 0.f, acc_cost = 0.f;
+  // 16-byte copies of the obs / next_obs tiles need every member slab 16-byte aligned (row0 * OD * 4 always is: 32 rows)
+  const bool vec_ok = ((reinterpret_cast<uintptr_t>(p.obs) | reinterpret_cast<uintptr_t>(p.next_obs)) & 15) == 0 &&
+                      (((size_t)slot_rows * OD) & 3) == 0;
+  const bool need_row_flags = p.env_id == ENV_ANT || p.env_id == ENV_ANTSAFE || p.env_id == ENV_HOPPER || p.env_id == ENV_HOPPERSAFE;
 
   for (long long row0 = (long long)blockIdx.x * kPostRows; row0 < n_rows; row0 += (long long)gridDim.x * kPostRows) {
     const long long g = row0 + r;
@@ -500,10 +504,27 @@ __global__ void __launch_bounds__(kPostThreads, 768 / kPostThreads) step_post3d_
     const float* hrow = p.heads + (size_t)(g >> 7) * (size_t)(E * 2 * D * kTileRows) + (size_t)(g & (kTileRows - 1));
     const int rows_here = (int)min((long long)kPostRows, n_rows - row0);
     __syncthreads();
+    const int n_el = rows_here * OD;
+    if (vec_ok) {        // 16-byte cp.async straight into the tiles (the scalar loop below costs ~10 instructions per element)
+      const int n4 = n_el >> 2;
 #pragma unroll
-    for (int e = 0; e < E; ++e) {
-      const float* src = p.obs + ((size_t)e * slot_rows + row0) * OD;
-      for (int i = tid; i < rows_here * OD; i += kPostThreads) tiles[e * tile_elems + i] = src[i];
+      for (int e = 0; e < E; ++e) {
+        const float* src = p.obs + ((size_t)e * slot_rows + row0) * OD;
+        for (int q = tid; q < n4; q += kPostThreads) cp_async16(tiles + e * tile_elems + 4 * q, src + 4 * q);
+      }
+      cp_async_commit();
+      const int tail = n_el & 3;
+      if (tid < E * tail) {
+        const int e = tid / tail, i = 4 * n4 + (tid - e * tail);
+        tiles[e * tile_elems + i] = p.obs[((size_t)e * slot_rows + row0) * OD + i];
+      }
+      cp_async_wait_all();
+    } else {
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        const float* src = p.obs + ((size_t)e * slot_rows + row0) * OD;
+        for (int i = tid; i < n_el; i += kPostThreads) tiles[e * tile_elems + i] = src[i];
+      }
     }
     __syncthreads();
     float kl_row = 0.f, epv_row = 0.f;
@@ -563,8 +584,10 @@ __global__ void __launch_bounds__(kPostThreads, 768 / kPostThreads) step_post3d_
           }
           if (d < OD) {
             tiles[e * tile_elems + r * OD + d] = x;   // own element only
-            if (!(fabsf(x) <= 3.402823466e38f)) fin &= ~(1u << e);
-            if (d >= 1 && !(x < 100.f)) lt &= ~(1u << e);
+            if (need_row_flags) {                     // only the Ant / Hopper termination functions look at these
+              if (!(fabsf(x) <= 3.402823466e38f)) fin &= ~(1u << e);
+              if (d >= 1 && !(x < 100.f)) lt &= ~(1u << e);
+            }
           } else {
             s_rew[e][r] = x;                           // reward = last output column (fake_env.py:180)
           }
@@ -609,10 +632,25 @@ __global__ void __launch_bounds__(kPostThreads, 768 / kPostThreads) step_post3d_
       if (p.ep_var_mean) p.ep_var_mean[g] = es / (float)D;
       acc_dkl += dkl;
     }
+    if (vec_ok) {
+      const int n4 = n_el >> 2;
 #pragma unroll
-    for (int e = 0; e < E; ++e) {
-      float* dst = p.next_obs + ((size_t)e * slot_rows + row0) * OD;
-      for (int i = tid; i < rows_here * OD; i += kPostThreads) dst[i] = tiles[e * tile_elems + i];
+      for (int e = 0; e < E; ++e) {
+        float* dst = p.next_obs + ((size_t)e * slot_rows + row0) * OD;
+        for (int q = tid; q < n4; q += kPostThreads)
+          *reinterpret_cast<float4*>(dst + 4 * q) = *reinterpret_cast<const float4*>(tiles + e * tile_elems + 4 * q);
+      }
+      const int tail = n_el & 3;
+      if (tid < E * tail) {
+        const int e = tid / tail, i = 4 * n4 + (tid - e * tail);
+        p.next_obs[((size_t)e * slot_rows + row0) * OD + i] = tiles[e * tile_elems + i];
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        float* dst = p.next_obs + ((size_t)e * slot_rows + row0) * OD;
+        for (int i = tid; i < n_el; i += kPostThreads) dst[i] = tiles[e * tile_elems + i];
+      }
     }
   }
   const float vals[4] = {acc_dkl, acc_var, acc_rew, acc_cost};

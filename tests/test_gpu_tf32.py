@@ -20,7 +20,7 @@ def test_predict_tf32_within_1e3(env, hidden):
     mean, var = m.predict(x, factored=True)
     rm, rv = orc.predict(p, x.astype(np.float64), factored=True)
     # two-hidden-layer nets: the floor-scaled inputs (|x| ~ 1e2, quirk Q6) make first-layer activations of order 10, whose
-    # tf32 rounding (2^-12 relative) reaches the head through a single further layer: 5e-3 * s_out and 5e-3 on the variance
+    # tf32 rounding (2^-12 relative) reaches the head through a single further layer: 5e-3 * s_out and 1e-2 on the variance (twice the mean bound, like the bf16 pair 1e-2 / 2e-2)
     # there (observed worst 4.4e-3 on hopper, whose 14-wide input has two floor dims, and 3.9e-3 on the (512, 512) variance;
     # relative Frobenius error 3.9e-4 in both), the north_star 1e-3 for the 3- and 4-layer nets (the bf16 tests make the
     # same split: 3e-2 vs 1e-2)
@@ -30,7 +30,7 @@ def test_predict_tf32_within_1e3(env, hidden):
                               outlier_frac=1e-4 if shallow else 0.0)   # hopper (64, 64): 1..6 of 252000 elements at 5e-3..5.4e-3
     assert frac < 1e-3
     rel = np.abs(var - rv) / rv
-    assert rel.max() < (5e-3 if shallow else VAR_RTOL_TF32), f"variance rel err max {rel.max():.3e}"
+    assert rel.max() < (1e-2 if shallow else VAR_RTOL_TF32), f"variance rel err max {rel.max():.3e}"
     # and it really is more accurate than the bf16 path on the same net
     mb, _ = _cuda_model(p, hidden, "MSPE").predict(x, factored=True)
     err_t, err_b = np.abs(mean - rm).mean(), np.abs(mb - rm).mean()
