@@ -356,7 +356,6 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   p.n_rows = n_rows;
   p.heads = heads;
   p.status = h->status_dev;
-  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("CMBPO_K1_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
 #ifdef CMBPO_TRACE
   static long long* trace_dev = nullptr;
   const char* trace_path = getenv("CMBPO_TRACE_OUT");   // debug timeline of cluster 0 (tools/trace_report.py)

@@ -86,7 +86,6 @@ struct FwdParams {
   float* heads;                 // out: tile-major head scratch (head_index), scaled mean | shifted logvar
   int* status;                  // watchdog / error word
   long long* trace;             // debug timeline, only read by -DCMBPO_TRACE builds
-  int dbg;                      // experiment switch (CMBPO_K1_DBG), 0 = product behaviour
 };
 
 // ---------------------------------------------------------------------------------------

@@ -162,8 +162,7 @@ __device__ __forceinline__ void convert_store16(const uint32_t (&r)[16], int col
 // the async proxy.  The MMA issuer starts the next layer's k-steps over the finished columns on this signal and keeps
 // the k-steps over each warp's last chunk for BAR_A_READY, so ~11 of 13 k-steps run under the tail of the conversion.
 __device__ __forceinline__ void early_arrive(uint32_t early_bar) {
-  if (!(early_bar & 0x80000000u)) fence_proxy_async_smem();   // (bit 31: timing experiment without the fence)
-  early_bar &= 0x7fffffffu;
+  fence_proxy_async_smem();
   tc_fence_before();
   __syncwarp();
   if ((threadIdx.x & 31) == 0) mbar_arrive_cluster_light(early_bar, 0);
@@ -359,7 +358,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
   if (tid == 0) {
     for (int s = 0; s < kMaxSlots; ++s) {
       mbar_init(bar(BAR_W_FULL + s), cta == 0 ? 2 : 1);   // leader: own fill + relayed peer fill
-      mbar_init(bar(BAR_W_EMPTY + s), 1);                 // tcgen05.commit
+      mbar_init(bar(BAR_W_EMPTY + s), 2);                 // tcgen05.commit of each stream's issuer
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar(BAR_A0_FULL + s), cta == 0 ? 2 : 1);  // leader: own fill + relayed peer fill
@@ -420,81 +419,93 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
         }
       }
     }
-  } else if (warp == 1) {
-    // ===== MMA issuer (leader CTA).  The whole warp walks the loop convergently (all lanes wait on the
-    // barriers); only the tcgen05.mma / commit instructions are issued by one elected lane.
+  } else if (warp == 1 || warp == 2) {
+    // ===== MMA issuers (leader CTA): warp 1 issues stream X, warp 2 stream Y.  Each warp walks its loop convergently
+    // (all lanes wait on the barriers); only the tcgen05.mma / commit instructions are issued by one elected lane.
+    // One issuer per stream: a single warp serving both in a fixed order made X's next layer 0 queue behind Y's head
+    // at every member boundary (and costs ~60-150 cycles per small MMA it issues, next to 16 busy epilogue warps):
+    // neither stream converted for ~3300 of the ~20700 cycles of a member (profiles/r02_k1_trace_notes.txt).  A weight slot
+    // is released by two commits, one per stream (both from warp 1 where the pair has no Y tile).
     if (cta == 0) {
-      int slot = 0; uint32_t use = 0;
+      const int my_s = warp - 1;
       uint32_t passes[2] = {0, 0}, stage[2] = {0, 0};
-      TR_DECL(0, cluster_id == 0 && lane == 0);
-      for (PairIter it(vc, nvc, vtiles); it.valid(); it.next()) {
-        const bool has_y = it.has_y();
-        for (int e = e_begin; e < e_end; ++e) {
-          const bool new_input = p.per_slot_input || e == e_begin;
-          const bool last_use = p.per_slot_input || e == e_end - 1;
-          for (int l = 0; l < L; ++l) {
-            const LayerPlan& lp = pl.layer[l];
-            const uint32_t idesc = make_idesc(256, lp.npad, kFmtBF16);
-            const uint32_t b_base = smem_u32(smem + (uint32_t)slot * pl.slot_bytes);
-            const uint32_t sbo = (uint32_t)(lp.kpad >> 3) * 128u;
-            const int ksteps = lp.kpad >> 4;
-            TR(100 + l);
-            mbar_wait(bar(BAR_W_FULL + slot), use & 1, p.status, WC_MMA_WFULL);
-#pragma unroll
-            for (int s = 0; s < 2; ++s) {
-              if (s == 1 && !has_y) continue;
-              TR(110 + 10 * s + l);
-              if (passes[s] > 0) mbar_wait(bar(BAR_A_EARLY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
-              if (l == 0 && new_input) mbar_wait(bar(BAR_A0_FULL + s), stage[s] & 1, p.status, WC_MMA_A0);
-              tc_fence_after();
-              TR(130 + 10 * s + l);
-              const uint32_t a_base = (l == 0) ? smem_u32(smem + sl.off_a0 + s * pl.a0_bytes)
-                                               : smem_u32(smem + sl.off_a + s * pl.a_bytes);
-              const uint32_t d_tmem = tmem_base + s * kRegionCols;
-              // descriptors of k-step j = descriptor of k-step 0 + j * (256 bytes >> 4) in the address field
-              const uint64_t a_desc0 = make_smem_desc(a_base, 128, sbo), b_desc0 = make_smem_desc(b_base, 128, sbo);
-              // early k-steps: everything but the last chunk of each column half (h0 - 1 and ksteps - 1); layer 0 reads the
-              // staged input tile, which no epilogue writes: all of it is early
-              const int h0 = (ksteps + 1) >> 1;
-              const int e0_end = (l == 0 || p.dbg == 1) ? (p.dbg == 1 && l > 0 ? 0 : ksteps) : h0 - 1;     // [0, e0_end)
-              const int e1_beg = (l == 0 || p.dbg == 1) ? ksteps : h0, e1_end = (l == 0 || p.dbg == 1) ? ksteps : ksteps - 1;   // [e1_beg, e1_end)
-              if (elect_one()) {
-                for (int j = 0; j < e0_end; ++j)
-                  mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, j > 0);
-                for (int j = e1_beg; j < e1_end; ++j)
-                  mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, (e0_end > 0 || j > e1_beg) ? 1u : 0u);
-              }
-              const uint32_t acc = (e0_end > 0 || e1_end > e1_beg) ? 1u : 0u;   // did the early batch write the accumulator?
-              __syncwarp();
-              TR(170 + 10 * s + l);
-              if (passes[s] > 0) mbar_wait(bar(BAR_A_READY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
-              tc_fence_after();
-              TR(190 + 10 * s + l);
-              if (elect_one()) {
-                if (l > 0) {
-                  if (p.dbg == 1) {
-                    for (int j = 0; j < ksteps; ++j)
-                      mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, j > 0);
-                  } else {
-                    if (h0 - 1 != ksteps - 1)
-                      mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((h0 - 1) * 16), b_desc0 + (uint64_t)((h0 - 1) * 16), idesc, acc);
-                    mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((ksteps - 1) * 16), b_desc0 + (uint64_t)((ksteps - 1) * 16), idesc,
-                                   (acc || h0 - 1 != ksteps - 1) ? 1u : 0u);
-                  }
-                }
-                mma_commit_2sm(bar(BAR_D_FULL + s), 0x3);
-                if (l == 0 && last_use) mma_commit_2sm(bar(BAR_A0_EMPTY + s), 0x3);
-              }
-              __syncwarp();
-              TR(150 + 10 * s + l);
-              if (l == 0 && last_use) ++stage[s];
-              ++passes[s];
-            }
-            if (elect_one()) mma_commit_2sm(bar(BAR_W_EMPTY + slot), 0x3);
-            __syncwarp();
-            if (++slot == S) { slot = 0; ++use; }
-          }
+      TR_DECL(my_s == 0 ? 0 : 3, cluster_id == 0 && lane == 0);
+      // One step = layer l of member e on one pair of row tiles; the steps of a CTA pair form one flat sequence that
+      // the weight ring follows (slot, use).
+      struct IssueStep { PairIter it; int e, l, slot; uint32_t use; };
+      auto step_next = [&](IssueStep st) {
+        if (++st.slot == S) { st.slot = 0; ++st.use; }
+        if (++st.l == L) {
+          st.l = 0;
+          if (++st.e == e_end) { st.e = e_begin; st.it.next(); }
         }
+        return st;
+      };
+      auto issue_one = [&](const IssueStep& st, const int s) {
+        const int l = st.l, e = st.e;
+        const bool new_input = p.per_slot_input || e == e_begin;
+        const bool last_use = p.per_slot_input || e == e_end - 1;
+        const LayerPlan& lp = pl.layer[l];
+        const uint32_t idesc = make_idesc(256, lp.npad, kFmtBF16);
+        const uint32_t b_base = smem_u32(smem + (uint32_t)st.slot * pl.slot_bytes);
+        const uint32_t sbo = (uint32_t)(lp.kpad >> 3) * 128u;
+        const int ksteps = lp.kpad >> 4;
+        TR(110 + 10 * s + l);
+        if (passes[s] > 0) mbar_wait(bar(BAR_A_EARLY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
+        if (l == 0 && new_input) mbar_wait(bar(BAR_A0_FULL + s), stage[s] & 1, p.status, WC_MMA_A0);
+        tc_fence_after();
+        TR(130 + 10 * s + l);
+        const uint32_t a_base = (l == 0) ? smem_u32(smem + sl.off_a0 + s * pl.a0_bytes)
+                                         : smem_u32(smem + sl.off_a + s * pl.a_bytes);
+        const uint32_t d_tmem = tmem_base + s * kRegionCols;
+        // descriptors of k-step j = descriptor of k-step 0 + j * (256 bytes >> 4) in the address field
+        const uint64_t a_desc0 = make_smem_desc(a_base, 128, sbo), b_desc0 = make_smem_desc(b_base, 128, sbo);
+        // early k-steps: everything but the last chunk of each column half (h0 - 1 and ksteps - 1); layer 0 reads the
+        // staged input tile, which no epilogue writes: all of it is early
+        const int h0 = (ksteps + 1) >> 1;
+        const int e0_end = (l == 0) ? ksteps : h0 - 1;                                   // [0, e0_end)
+        const int e1_beg = (l == 0) ? ksteps : h0, e1_end = (l == 0) ? ksteps : ksteps - 1;   // [e1_beg, e1_end)
+        if (elect_one()) {
+          for (int j = 0; j < e0_end; ++j)
+            mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, j > 0);
+          for (int j = e1_beg; j < e1_end; ++j)
+            mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, (e0_end > 0 || j > e1_beg) ? 1u : 0u);
+        }
+        const uint32_t acc = (e0_end > 0 || e1_end > e1_beg) ? 1u : 0u;   // did the early batch write the accumulator?
+        __syncwarp();
+        TR(170 + 10 * s + l);
+        if (passes[s] > 0) mbar_wait(bar(BAR_A_READY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
+        tc_fence_after();
+        TR(190 + 10 * s + l);
+        if (elect_one()) {
+          if (l > 0) {
+            if (h0 - 1 != ksteps - 1)
+              mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((h0 - 1) * 16), b_desc0 + (uint64_t)((h0 - 1) * 16), idesc, acc);
+            mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((ksteps - 1) * 16), b_desc0 + (uint64_t)((ksteps - 1) * 16), idesc,
+                           (acc || h0 - 1 != ksteps - 1) ? 1u : 0u);
+          }
+          mma_commit_2sm(bar(BAR_D_FULL + s), 0x3);
+          if (l == 0 && last_use) mma_commit_2sm(bar(BAR_A0_EMPTY + s), 0x3);
+        }
+        __syncwarp();
+        TR(150 + 10 * s + l);
+        if (l == 0 && last_use) ++stage[s];
+        ++passes[s];
+      };
+      IssueStep cur{PairIter(vc, nvc, vtiles), e_begin, 0, 0, 0u};
+      while (cur.it.valid()) {
+        const bool has_y = cur.it.has_y();
+        if (my_s == 0 || has_y) {
+          TR(100 + cur.l);
+          mbar_wait(bar(BAR_W_FULL + cur.slot), cur.use & 1, p.status, WC_MMA_WFULL);
+          issue_one(cur, my_s);
+          if (elect_one()) {
+            mma_commit_2sm(bar(BAR_W_EMPTY + cur.slot), 0x3);
+            if (!has_y) mma_commit_2sm(bar(BAR_W_EMPTY + cur.slot), 0x3);     // stands in for the absent Y stream
+          }
+          __syncwarp();
+        }
+        cur = step_next(cur);
       }
     }
   } else if (warp == 3) {
@@ -535,8 +546,6 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
         }
       }
     }
-  } else if (warp == 2) {
-    // (TMEM allocation / release only)
   } else {
     // ===== epilogue warps 4..19: TMEM lane quadrant q (the hardware ties a warp to lanes 32*(warp%4)..);
     // warps 4..7 / 12..15 serve stream X (column half 0 / 1), warps 8..11 / 16..19 stream Y
@@ -576,7 +585,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
             const bool keep = s == 1 && last_tok_pair && e == e_end - 1 && l == L - 2;
             TR_STAMP_DECL;
             hidden_epilogue<HACT>(d_addr, lp.npad, lp.n_real, half, a_row, use_tok ? tok_mine : 0,
-                                  (use_tok && !keep) ? tok_other : 0, bar(BAR_A_EARLY + s) | (p.dbg == 2 ? 0x80000000u : 0u) TR_STAMP_PASS);
+                                  (use_tok && !keep) ? tok_other : 0, bar(BAR_A_EARLY + s) TR_STAMP_PASS);
 #ifdef CMBPO_TRACE
             if (tr_base && tr_n + 2 <= kTraceSlots) {
               tr_base[2 * tr_n] = g_stamp[0]; tr_base[2 * tr_n + 1] = 260 + l; ++tr_n;

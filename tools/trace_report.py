@@ -14,7 +14,7 @@ raw = np.fromfile(sys.argv[1], dtype=np.int64)
 lo = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 hi = int(sys.argv[3]) if len(sys.argv) > 3 else 400
 roles = {}
-for r, name in enumerate(["mma", "epiX", "epiY"]):
+for r, name in enumerate(["mma", "epiX", "epiY", "mmaY"]):
     a = raw[r * 2 * SLOTS:(r + 1) * 2 * SLOTS].reshape(-1, 2)
     a = a[a[:, 0] != 0]
     roles[name] = a
@@ -45,15 +45,15 @@ for name in ("epiX", "epiY"):
     for k in sorted(dur):
         med = lambda a: int(np.median(a)) if len(a) else 0
         print(f"  {k:3d}: gap {med(gap[k]):6d}  wait {med(wait[k]):6d}   epi {med(dur[k]):6d}   n={len(dur[k])}")
-m = roles["mma"]
-if len(m):
-    w, iss = collections.defaultdict(list), collections.defaultdict(list)
-    last = {}
-    for t, tag in m:
-        tag = int(tag)
-        if 110 <= tag < 130: last[tag - 110] = t
-        elif 130 <= tag < 150: w[tag - 130].append(t - last.get(tag - 130, t)); last[("r", tag - 130)] = t
-        elif tag >= 150: iss[tag - 150].append(t - last.get(("r", tag - 150), t))
-    print("MMA issuer (key = 10*stream + layer): median wait for operands (A_READY/A0) | issue time")
-    for k in sorted(w):
-        print(f"  {k:3d}: wait {int(np.median(w[k])):6d}   issue {int(np.median(iss[k])):6d}")
+for m in (roles["mma"], roles["mmaY"]):
+  if len(m):
+      w, iss = collections.defaultdict(list), collections.defaultdict(list)
+      last = {}
+      for t, tag in m:
+          tag = int(tag)
+          if 110 <= tag < 130: last[tag - 110] = t
+          elif 130 <= tag < 150: w[tag - 130].append(t - last.get(tag - 130, t)); last[("r", tag - 130)] = t
+          elif tag >= 150: iss[tag - 150].append(t - last.get(("r", tag - 150), t))
+      print("MMA issuer (key = 10*stream + layer): median wait for operands (A_READY/A0) | issue time")
+      for k in sorted(w):
+          print(f"  {k:3d}: wait {int(np.median(w[k])):6d}   issue {int(np.median(iss[k])):6d}")
