@@ -41,6 +41,9 @@ struct ModelPlan {
   uint32_t slot_bytes;    // max_l(bytes_l) rounded up to 128: one weight ring slot
   uint32_t w_slots;       // ring depth (2..kMaxSlots), as many as fit beside the activation tiles
   uint32_t smem_total;    // dynamic smem the forward kernel needs
+  uint32_t acc_cols;      // TMEM columns of one stream's hidden-layer accumulator = max hidden npad (streams at 0, acc_cols)
+  uint32_t head_col;      // first TMEM column of the head accumulator shared by both streams (= 2 * acc_cols)
+  uint32_t combo_off;     // byte offset of the NEXT member's layer-0 weights inside a "head + next layer 0" ring slot
 };
 
 // Head scratch layout ("tile-major"): the rows are cut in blocks of kTileRows (one CTA tile); block b

@@ -47,14 +47,24 @@ __host__ __device__ inline SmemLayout make_smem_layout(const ModelPlan& pl) {
   return s;
 }
 
-// Fills the shared-memory part of the plan (slot size, ring depth, tile sizes); false if even a
-// two-slot ring does not fit the 227 KB of a CTA.
+// Fills the shared-memory / TMEM part of the plan (slot size, ring depth, tile sizes, accumulator columns); false if the
+// model does not fit the fused kernel: fewer than two layers, a two-slot ring beyond the 227 KB of a CTA, or no room in
+// the 512 TMEM columns for two hidden accumulators plus the head accumulator.  The caller then takes the layer-at-a-time path.
 bool plan_fwd_smem(ModelPlan& pl) {
-  uint32_t slot = 0, kmax = 0;
+  if (pl.L < 2) return false;
+  uint32_t slot = 0, kmax = 0, acc = 0;
   for (int l = 0; l < pl.L; ++l) {
     slot = pl.layer[l].bytes > slot ? pl.layer[l].bytes : slot;
     if (l >= 1 && (uint32_t)pl.layer[l].kpad > kmax) kmax = pl.layer[l].kpad;
+    if (l < pl.L - 1 && (uint32_t)pl.layer[l].npad > acc) acc = pl.layer[l].npad;
   }
+  pl.acc_cols = acc;
+  pl.head_col = 2u * acc;
+  if (pl.head_col + (uint32_t)pl.layer[pl.L - 1].npad > 512u) return false;
+  // the head of member m and layer 0 of the next member travel in ONE ring slot (see the kernel's step sequence)
+  pl.combo_off = (pl.layer[pl.L - 1].bytes + 127u) & ~127u;
+  const uint32_t combo = pl.combo_off + pl.layer[0].bytes;
+  slot = combo > slot ? combo : slot;
   pl.slot_bytes = (slot + 127u) & ~127u;
   pl.a_bytes = (uint32_t)kTileRows * kmax * 2u;
   pl.a0_bytes = (uint32_t)kTileRows * pl.layer[0].kpad * 2u;
@@ -76,7 +86,9 @@ constexpr int BAR_A0_EMPTY = 18;         // [2]
 constexpr int BAR_D_FULL = 20;           // [2]
 constexpr int BAR_A_READY = 22;          // [2]  epilogue finished a pass: every column of the next A tile is in smem
 constexpr int BAR_A_EARLY = 24;          // [2]  accumulator consumed (all tcgen05.ld done) and all but each warp's LAST chunk of the next A tile in smem
-constexpr int kNumBars = 26;
+constexpr int BAR_H_FULL = 26;           // [2]  head accumulator (shared TMEM region) written for this stream
+constexpr int BAR_H_DRAINED = 28;        // [2]  this stream's epilogue warps have the head accumulator in registers
+constexpr int kNumBars = 30;
 
 // Debug timeline (compile with -DCMBPO_TRACE): cluster 0's MMA issuer and epilogue warp 4 (leader CTA)
 // append (clock64, tag) pairs to p.trace[role * 2 * kTraceSlots ..]; tools/trace_report.py prints it.
@@ -257,8 +269,9 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t d_addr, int npad, int o
 // Head epilogue for one warp: inverse output scaler on the mean, 2*log(s) shift on the log-variance
 // (bnn.py:878-893); `out` points at this thread's row inside the (tile block, member) region of the
 // tile-major scratch, column stride 128 floats: a warp's store covers 32 consecutive rows.
-// The pass writes no A tile, so both barriers of the stream (BAR_A_EARLY, BAR_A_READY) get this warp's arrival as soon
-// as its last tcgen05.ld has completed: the next pass's MMAs (layer 0 of the next member) do not wait for the global stores.
+// The head accumulator is a TMEM region of its own, shared by both streams: the warp arrives on BAR_H_DRAINED of its stream as
+// soon as its last tcgen05.ld has completed, before the global stores.
+template <bool FULL>   // FULL: all 16 columns are real head columns (no per-column predicate: 10 instead of 26 instructions per 4 columns)
 __device__ __forceinline__ void head_store16(const uint32_t (&r)[16], int c0, int n_head, const float* s_scale,
                                              const float* s_shift, float* out, bool live) {
   float* colp = out + (size_t)c0 * kTileRows;
@@ -267,33 +280,38 @@ __device__ __forceinline__ void head_store16(const uint32_t (&r)[16], int c0, in
     const float4 a = *reinterpret_cast<const float4*>(s_scale + c0 + 4 * i);
     const float4 b = *reinterpret_cast<const float4*>(s_shift + c0 + 4 * i);
     if (live) {
-      if (c0 + 4 * i + 0 < n_head) colp[(4 * i + 0) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 0]), a.x, b.x);
-      if (c0 + 4 * i + 1 < n_head) colp[(4 * i + 1) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 1]), a.y, b.y);
-      if (c0 + 4 * i + 2 < n_head) colp[(4 * i + 2) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 2]), a.z, b.z);
-      if (c0 + 4 * i + 3 < n_head) colp[(4 * i + 3) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 3]), a.w, b.w);
+      if (FULL || c0 + 4 * i + 0 < n_head) colp[(4 * i + 0) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 0]), a.x, b.x);
+      if (FULL || c0 + 4 * i + 1 < n_head) colp[(4 * i + 1) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 1]), a.y, b.y);
+      if (FULL || c0 + 4 * i + 2 < n_head) colp[(4 * i + 2) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 2]), a.z, b.z);
+      if (FULL || c0 + 4 * i + 3 < n_head) colp[(4 * i + 3) * kTileRows] = fmaf(__uint_as_float(r[4 * i + 3]), a.w, b.w);
     }
   }
 }
-__device__ __forceinline__ void head_arrive(uint32_t early_bar, uint32_t ready_bar) {
+__device__ __forceinline__ void head_store16_any(const uint32_t (&r)[16], int c0, int n_head, const float* s_scale,
+                                                 const float* s_shift, float* out, bool live) {
+  if (c0 + 16 <= n_head) head_store16<true>(r, c0, n_head, s_scale, s_shift, out, live);
+  else                   head_store16<false>(r, c0, n_head, s_scale, s_shift, out, live);
+}
+__device__ __forceinline__ void head_arrive(uint32_t drained_bar) {
   tc_fence_before();
   __syncwarp();
-  if ((threadIdx.x & 31) == 0) {
-    mbar_arrive_cluster_light(early_bar, 0);
-    mbar_arrive_cluster_light(ready_bar, 0);
-  }
+  if ((threadIdx.x & 31) == 0) mbar_arrive_cluster_light(drained_bar, 0);
 }
 __device__ __forceinline__ void head_epilogue(uint32_t d_addr, int c_begin, int c_end, int n_head, const float* s_scale,
-                                              const float* s_shift, float* out, bool live, uint32_t early_bar, uint32_t ready_bar) {
-  if (c_begin >= c_end) head_arrive(early_bar, ready_bar);
+                                              const float* s_shift, float* out, bool live, uint32_t drained_bar
+                                              TR_STAMP_ARG) {
+  if (c_begin >= c_end) head_arrive(drained_bar);
   for (int c0 = c_begin; c0 < c_end; c0 += 32) {
     uint32_t ra[16], rb[16];
     const bool two = c0 + 16 < c_end;
     tmem_ld16(d_addr + c0, ra);
     if (two) tmem_ld16(d_addr + c0 + 16, rb);
     tmem_wait_ld();
-    if (c0 + 32 >= c_end) head_arrive(early_bar, ready_bar);   // the accumulator is in registers: free it before the stores
-    head_store16(ra, c0, n_head, s_scale, s_shift, out, live);
-    if (two) head_store16(rb, c0 + 16, n_head, s_scale, s_shift, out, live);
+    TR_STAMP(0);
+    if (c0 + 32 >= c_end) head_arrive(drained_bar);   // the accumulator is in registers: the other stream's head may overwrite it
+    TR_STAMP(1);
+    head_store16_any(ra, c0, n_head, s_scale, s_shift, out, live);
+    if (two) head_store16_any(rb, c0 + 16, n_head, s_scale, s_shift, out, live);
   }
 }
 
@@ -366,6 +384,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
       mbar_init(bar(BAR_D_FULL + s), 1);                  // tcgen05.commit
       mbar_init(bar(BAR_A_READY + s), 2 * kEpiWarpsPerStream);   // 8 epilogue warps of the stream x 2 CTAs
       mbar_init(bar(BAR_A_EARLY + s), 2 * kEpiWarpsPerStream);
+      mbar_init(bar(BAR_H_FULL + s), 1);                  // tcgen05.commit
+      mbar_init(bar(BAR_H_DRAINED + s), 2 * kEpiWarpsPerStream);
     }
     fence_mbar_init();
   }
@@ -384,25 +404,54 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   // ---------------------------------------------------------------- roles
+  // The work of a CTA pair is a flat sequence of MEMBER INSTANCES (pair of row tiles, member e); stream Y takes part in
+  // the instances whose pair has a second tile (a prefix of the sequence).  Ring entries, one slot each, in order:
+  //   entry 0:                  layer 0 of the first instance
+  //   then per instance m:      layers 1 .. L-2 (one entry each), and a COMBO entry = head of m at offset 0 plus layer 0 of
+  //                             instance m + 1 at offset combo_off (absent after the last instance)
+  // Layer 0 of the next instance needs nothing from the current one but the accumulator, which is free as soon as the
+  // last hidden conversion has loaded it (BAR_A_EARLY); the head goes to its own TMEM region (head_col) shared by both
+  // streams.  So at a member boundary a stream's MMAs run  L0(m+1) | head(m)  and its epilogue  head(m) | conv0(m+1):
+  // the head pass (TMEM -> scale/shift -> global stores, no XU work) hides under the other stream's last conversion and
+  // the next conversion's operand is ready before the XU token comes back.  (With the head in the stream's accumulator
+  // and layer 0 behind it, neither stream converted for ~3300 of the ~19700 cycles of a member; r02_k1_trace_notes.txt.)
+  struct MemberIter {
+    PairIter it; int e, e_begin, e_end;
+    __device__ __forceinline__ bool valid() const { return it.valid() && e_begin < e_end; }
+    __device__ __forceinline__ void next() { if (++e == e_end) { e = e_begin; it.next(); } }
+  };
+  const MemberIter first_member{PairIter(vc, nvc, vtiles), e_begin, e_begin, e_end};
   if (warp == 0) {
-    // ===== weight loader: layer n of the (pair, member, layer) walk goes to ring slot n % S.  In the
-    // peer CTA the same thread also relays "my half of slot s has landed" to the leader's barrier
-    // (the MMA issuer waits on the leader's W_FULL only), so it polls instead of blocking.
+    // ===== weight loader: ring entry n goes to slot n % S.  In the peer CTA the same thread also relays "my half of slot s
+    // has landed" to the leader's barrier (the MMA issuers wait on the leader's W_FULL only), so it polls instead of blocking.
     if (lane == 0) {
-      long long n_pairs = 0;
-      for (PairIter it(vc, nvc, vtiles); it.valid(); it.next()) ++n_pairs;
-      const long long total = n_pairs * (e_end - e_begin) * L;
+      long long n_members = 0;
+      for (MemberIter mi = first_member; mi.valid(); mi.next()) ++n_members;
+      const long long total = n_members > 0 ? 1 + n_members * (L - 1) : 0;
       long long fill_n = 0, relay_n = 0;
-      int f_slot = 0, f_e = e_begin, f_l = 0, r_slot = 0; uint32_t f_use = 0, r_use = 0;
+      MemberIter cur = first_member;
+      int f_slot = 0, f_l = 0, r_slot = 0; uint32_t f_use = 0, r_use = 0;     // f_l == 0: entry 0 (lone layer 0)
       uint32_t idle = 0;
+      auto member_blk = [&](int e) { return p.wimg + (size_t)(fwd_member_of(p, e) * 2 + (int)cta) * pl.blk_bytes; };
       while (fill_n < total || (cta == 1 && relay_n < total)) {
         bool progress = false;
         if (fill_n < total && (f_use == 0 || mbar_try_wait(bar(BAR_W_EMPTY + f_slot), (f_use - 1) & 1))) {
-          const LayerPlan& lp = pl.layer[f_l];
-          const uint8_t* blk = p.wimg + (size_t)(fwd_member_of(p, f_e) * 2 + (int)cta) * pl.blk_bytes;
-          mbar_arrive_expect_tx(bar(BAR_W_FULL + f_slot), lp.bytes);
-          bulk_g2s(smem_u32(smem + (uint32_t)f_slot * pl.slot_bytes), blk + lp.img_off, lp.bytes, bar(BAR_W_FULL + f_slot));
-          if (++f_l == L) { f_l = 0; if (++f_e == e_end) f_e = e_begin; }
+          const uint32_t dst = smem_u32(smem + (uint32_t)f_slot * pl.slot_bytes);
+          const uint32_t full = bar(BAR_W_FULL + f_slot);
+          if (f_l < L - 1) {               // a single layer: 0 (first entry only) or a hidden layer 1 .. L-2
+            const LayerPlan& lp = pl.layer[f_l];
+            mbar_arrive_expect_tx(full, lp.bytes);
+            bulk_g2s(dst, member_blk(cur.e) + lp.img_off, lp.bytes, full);
+            ++f_l;
+          } else {                         // combo: head of `cur`, layer 0 of the next instance
+            const LayerPlan& hp = pl.layer[L - 1];
+            MemberIter nx = cur; nx.next();
+            const LayerPlan& l0 = pl.layer[0];
+            mbar_arrive_expect_tx(full, hp.bytes + (nx.valid() ? l0.bytes : 0u));
+            bulk_g2s(dst, member_blk(cur.e) + hp.img_off, hp.bytes, full);
+            if (nx.valid()) bulk_g2s(dst + pl.combo_off, member_blk(nx.e) + l0.img_off, l0.bytes, full);
+            cur = nx; f_l = 1;
+          }
           if (++f_slot == S) { f_slot = 0; ++f_use; }
           ++fill_n; progress = true;
         }
@@ -422,90 +471,126 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
   } else if (warp == 1 || warp == 2) {
     // ===== MMA issuers (leader CTA): warp 1 issues stream X, warp 2 stream Y.  Each warp walks its loop convergently
     // (all lanes wait on the barriers); only the tcgen05.mma / commit instructions are issued by one elected lane.
-    // One issuer per stream: a single warp serving both in a fixed order made X's next layer 0 queue behind Y's head
-    // at every member boundary (and costs ~60-150 cycles per small MMA it issues, next to 16 busy epilogue warps):
-    // neither stream converted for ~3300 of the ~20700 cycles of a member (profiles/r02_k1_trace_notes.txt).  A weight slot
-    // is released by two commits, one per stream (both from warp 1 where the pair has no Y tile).
+    // (One warp serving both streams in a fixed order made X's MMAs queue behind Y's at every member boundary, and a
+    // lone warp next to 16 busy epilogue warps needs 60-150 cycles per small MMA it issues.)  A ring slot is released by
+    // two commits, one per stream; warp 1 issues both where stream Y takes no part in the entry.
     if (cta == 0) {
-      const int my_s = warp - 1;
-      uint32_t passes[2] = {0, 0}, stage[2] = {0, 0};
-      TR_DECL(my_s == 0 ? 0 : 3, cluster_id == 0 && lane == 0);
-      // One step = layer l of member e on one pair of row tiles; the steps of a CTA pair form one flat sequence that
-      // the weight ring follows (slot, use).
-      struct IssueStep { PairIter it; int e, l, slot; uint32_t use; };
-      auto step_next = [&](IssueStep st) {
-        if (++st.slot == S) { st.slot = 0; ++st.use; }
-        if (++st.l == L) {
-          st.l = 0;
-          if (++st.e == e_end) { st.e = e_begin; st.it.next(); }
+      const int s = warp - 1;
+      TR_DECL(s == 0 ? 0 : 3, cluster_id == 0 && lane == 0);
+      const uint32_t d_acc = tmem_base + (uint32_t)s * pl.acc_cols, d_head = tmem_base + pl.head_col;
+      const uint32_t a0_base = smem_u32(smem + sl.off_a0 + s * pl.a0_bytes), a_base = smem_u32(smem + sl.off_a + s * pl.a_bytes);
+      uint32_t cp = 0, stage = 0, hm = 0;       // conversion passes consumed, input stages consumed, heads issued
+      int slot = 0; uint32_t use = 0;
+      auto wait_entry = [&]() { mbar_wait(bar(BAR_W_FULL + slot), use & 1, p.status, WC_MMA_WFULL); };
+      auto release_entry = [&](bool y_takes_part) {
+        if (elect_one()) {
+          mma_commit_2sm(bar(BAR_W_EMPTY + slot), 0x3);
+          if (s == 0 && !y_takes_part) mma_commit_2sm(bar(BAR_W_EMPTY + slot), 0x3);     // stands in for the absent Y stream
         }
-        return st;
+        __syncwarp();
+        if (++slot == S) { slot = 0; ++use; }
       };
-      auto issue_one = [&](const IssueStep& st, const int s) {
-        const int l = st.l, e = st.e;
-        const bool new_input = p.per_slot_input || e == e_begin;
-        const bool last_use = p.per_slot_input || e == e_end - 1;
-        const LayerPlan& lp = pl.layer[l];
+      // layer 0 of instance `mi` from the staged input tile; weights at byte `w_off` of the current slot
+      auto issue_l0 = [&](const MemberIter& mi, uint32_t w_off) {
+        const bool new_input = p.per_slot_input || mi.e == e_begin;
+        const bool last_use = p.per_slot_input || mi.e == e_end - 1;
+        const LayerPlan& lp = pl.layer[0];
         const uint32_t idesc = make_idesc(256, lp.npad, kFmtBF16);
-        const uint32_t b_base = smem_u32(smem + (uint32_t)st.slot * pl.slot_bytes);
         const uint32_t sbo = (uint32_t)(lp.kpad >> 3) * 128u;
         const int ksteps = lp.kpad >> 4;
+        TR(110 + 10 * s);
+        if (new_input) mbar_wait(bar(BAR_A0_FULL + s), stage & 1, p.status, WC_MMA_A0);
+        tc_fence_after();
+        TR(130 + 10 * s);
+        const uint64_t a_desc0 = make_smem_desc(a0_base, 128, sbo);
+        const uint64_t b_desc0 = make_smem_desc(smem_u32(smem + (uint32_t)slot * pl.slot_bytes + w_off), 128, sbo);
+        if (elect_one()) {
+#pragma unroll 4
+          for (int j = 0; j < ksteps; ++j)
+            mma_bf16_ss<2>(d_acc, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, j > 0);
+          mma_commit_2sm(bar(BAR_D_FULL + s), 0x3);
+          if (last_use) mma_commit_2sm(bar(BAR_A0_EMPTY + s), 0x3);
+        }
+        __syncwarp();
+        TR(150 + 10 * s);
+        if (last_use) ++stage;
+      };
+      // layer l >= 1 (a hidden layer into the stream's accumulator, or the head into the shared head region) from the A tile
+      // the conversion pass `cp` writes: everything but the last 16-column chunk of each column half on BAR_A_EARLY, the
+      // two k-steps over those chunks on BAR_A_READY
+      auto issue_from_a = [&](int l, uint32_t d_tmem, uint32_t done_bar) {
+        const LayerPlan& lp = pl.layer[l];
+        const uint32_t idesc = make_idesc(256, lp.npad, kFmtBF16);
+        const uint32_t sbo = (uint32_t)(lp.kpad >> 3) * 128u;
+        const int ksteps = lp.kpad >> 4, h0 = (ksteps + 1) >> 1;
         TR(110 + 10 * s + l);
-        if (passes[s] > 0) mbar_wait(bar(BAR_A_EARLY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
-        if (l == 0 && new_input) mbar_wait(bar(BAR_A0_FULL + s), stage[s] & 1, p.status, WC_MMA_A0);
+        mbar_wait(bar(BAR_A_EARLY + s), cp & 1, p.status, WC_MMA_AREADY);
         tc_fence_after();
         TR(130 + 10 * s + l);
-        const uint32_t a_base = (l == 0) ? smem_u32(smem + sl.off_a0 + s * pl.a0_bytes)
-                                         : smem_u32(smem + sl.off_a + s * pl.a_bytes);
-        const uint32_t d_tmem = tmem_base + s * kRegionCols;
-        // descriptors of k-step j = descriptor of k-step 0 + j * (256 bytes >> 4) in the address field
-        const uint64_t a_desc0 = make_smem_desc(a_base, 128, sbo), b_desc0 = make_smem_desc(b_base, 128, sbo);
-        // early k-steps: everything but the last chunk of each column half (h0 - 1 and ksteps - 1); layer 0 reads the
-        // staged input tile, which no epilogue writes: all of it is early
-        const int h0 = (ksteps + 1) >> 1;
-        const int e0_end = (l == 0) ? ksteps : h0 - 1;                                   // [0, e0_end)
-        const int e1_beg = (l == 0) ? ksteps : h0, e1_end = (l == 0) ? ksteps : ksteps - 1;   // [e1_beg, e1_end)
+        const uint64_t a_desc0 = make_smem_desc(a_base, 128, sbo);
+        const uint64_t b_desc0 = make_smem_desc(smem_u32(smem + (uint32_t)slot * pl.slot_bytes), 128, sbo);
         if (elect_one()) {
-          for (int j = 0; j < e0_end; ++j)
+#pragma unroll 2
+          for (int j = 0; j < h0 - 1; ++j)
             mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, j > 0);
-          for (int j = e1_beg; j < e1_end; ++j)
-            mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, (e0_end > 0 || j > e1_beg) ? 1u : 0u);
+#pragma unroll 2
+          for (int j = h0; j < ksteps - 1; ++j)
+            mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)(j * 16), b_desc0 + (uint64_t)(j * 16), idesc, (h0 > 1 || j > h0) ? 1u : 0u);
         }
-        const uint32_t acc = (e0_end > 0 || e1_end > e1_beg) ? 1u : 0u;   // did the early batch write the accumulator?
+        const uint32_t acc = (h0 > 1 || ksteps - 1 > h0) ? 1u : 0u;    // did the early batch write the accumulator?
         __syncwarp();
         TR(170 + 10 * s + l);
-        if (passes[s] > 0) mbar_wait(bar(BAR_A_READY + s), (passes[s] - 1) & 1, p.status, WC_MMA_AREADY);
+        mbar_wait(bar(BAR_A_READY + s), cp & 1, p.status, WC_MMA_AREADY);
         tc_fence_after();
         TR(190 + 10 * s + l);
         if (elect_one()) {
-          if (l > 0) {
-            if (h0 - 1 != ksteps - 1)
-              mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((h0 - 1) * 16), b_desc0 + (uint64_t)((h0 - 1) * 16), idesc, acc);
-            mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((ksteps - 1) * 16), b_desc0 + (uint64_t)((ksteps - 1) * 16), idesc,
-                           (acc || h0 - 1 != ksteps - 1) ? 1u : 0u);
-          }
-          mma_commit_2sm(bar(BAR_D_FULL + s), 0x3);
-          if (l == 0 && last_use) mma_commit_2sm(bar(BAR_A0_EMPTY + s), 0x3);
+          if (h0 - 1 != ksteps - 1)
+            mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((h0 - 1) * 16), b_desc0 + (uint64_t)((h0 - 1) * 16), idesc, acc);
+          mma_bf16_ss<2>(d_tmem, a_desc0 + (uint64_t)((ksteps - 1) * 16), b_desc0 + (uint64_t)((ksteps - 1) * 16), idesc,
+                         (acc || h0 - 1 != ksteps - 1) ? 1u : 0u);
+          mma_commit_2sm(done_bar, 0x3);
         }
         __syncwarp();
         TR(150 + 10 * s + l);
-        if (l == 0 && last_use) ++stage[s];
-        ++passes[s];
+        ++cp;
       };
-      IssueStep cur{PairIter(vc, nvc, vtiles), e_begin, 0, 0, 0u};
-      while (cur.it.valid()) {
+      MemberIter cur = first_member;
+      const bool takes_part = cur.valid() && (s == 0 || cur.it.has_y());
+      bool prev_had_y = false;
+      if (takes_part) {
+        TR(100);
+        wait_entry();
+        issue_l0(cur, 0);
+        release_entry(cur.it.has_y());
+      }
+      while (takes_part && cur.valid() && (s == 0 || cur.it.has_y())) {
         const bool has_y = cur.it.has_y();
-        if (my_s == 0 || has_y) {
-          TR(100 + cur.l);
-          mbar_wait(bar(BAR_W_FULL + cur.slot), cur.use & 1, p.status, WC_MMA_WFULL);
-          issue_one(cur, my_s);
-          if (elect_one()) {
-            mma_commit_2sm(bar(BAR_W_EMPTY + cur.slot), 0x3);
-            if (!has_y) mma_commit_2sm(bar(BAR_W_EMPTY + cur.slot), 0x3);     // stands in for the absent Y stream
-          }
-          __syncwarp();
+        for (int l = 1; l < L - 1; ++l) {
+          TR(100 + l);
+          wait_entry();
+          issue_from_a(l, d_acc, bar(BAR_D_FULL + s));
+          release_entry(has_y);
         }
-        cur = step_next(cur);
+        // combo entry: layer 0 of the next instance as soon as the accumulator is free, then this instance's head
+        MemberIter nx = cur; nx.next();
+        const bool has_next = nx.valid() && (s == 0 || nx.it.has_y());
+        TR(100 + L - 1);
+        wait_entry();
+        // the shared head region: heads alternate X(m), Y(m), X(m+1), ... while the pairs have a Y tile
+        if (s == 0) {
+          if (hm > 0) mbar_wait(bar(BAR_H_DRAINED + (prev_had_y ? 1 : 0)), (hm - 1) & 1, p.status, WC_MMA_AREADY);
+        } else {
+          mbar_wait(bar(BAR_H_DRAINED + 0), hm & 1, p.status, WC_MMA_AREADY);
+        }
+        // head first: its epilogue pass (no XU work) then runs under the other stream's last conversion, and layer 0 of the
+        // next instance -- issued right behind it into the accumulator the last conversion has just drained -- is complete
+        // before that pass ends
+        issue_from_a(L - 1, d_head, bar(BAR_H_FULL + s));
+        ++hm;
+        if (has_next) issue_l0(nx, pl.combo_off);
+        release_entry(has_y);
+        prev_had_y = has_y;
+        cur = nx;
       }
     }
   } else if (warp == 3) {
@@ -554,9 +639,10 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
     const int half = (warp - 4) >> 3;
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int row_in_tile = q * 32 + lane;
-    const uint32_t d_addr = tmem_base + lane_base + s * kRegionCols;
+    const uint32_t d_addr = tmem_base + lane_base + (uint32_t)s * pl.acc_cols;      // this stream's hidden accumulator
+    const uint32_t h_addr = tmem_base + lane_base + pl.head_col;                    // head accumulator shared by the streams
     const uint32_t a_tile = smem_u32(smem + sl.off_a + s * pl.a_bytes) + (uint32_t)(row_in_tile & 7) * 16u;
-    uint32_t dphase = 0;
+    uint32_t dphase = 0, hphase = 0;
     TR_DECL(1 + s, cluster_id == 0 && cta == 0 && q == 0 && half == 0 && lane == 0);
     // XU token of this sub-partition: X waits on barrier 1+q / passes 5+q, Y the other way round.  Only
     // pairs that have both streams use it (hidden passes alternate X, Y, X, Y ...); Y opens the game
@@ -575,8 +661,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
         for (int l = 0; l < L; ++l) {
           const LayerPlan& lp = pl.layer[l];
           TR(200 + l);
-          mbar_wait(bar(BAR_D_FULL + s), dphase & 1, p.status, WC_EPI_DFULL);
-          ++dphase;
+          if (l < L - 1) { mbar_wait(bar(BAR_D_FULL + s), dphase & 1, p.status, WC_EPI_DFULL); ++dphase; }
+          else           { mbar_wait(bar(BAR_H_FULL + s), hphase & 1, p.status, WC_EPI_DFULL); ++hphase; }
           tc_fence_after();
           TR(220 + l);
           if (l < L - 1) {
@@ -599,8 +685,15 @@ __global__ void __launch_bounds__(kFwdThreads, 1) ensemble_fwd_kernel(const __gr
           } else {
             float* out = p.heads + ((size_t)(blk * E + e) * pl.n_head) * kTileRows + row_in_tile;
             const int hch = lp.npad >> 4, hh0 = (hch + 1) >> 1;   // 16-column chunks of the head, split like the hidden layers
-            head_epilogue(d_addr, 16 * (half ? hh0 : 0), 16 * (half ? hch : hh0), pl.n_head, s_head_scale, s_head_shift, out, live,
-                          bar(BAR_A_EARLY + s), bar(BAR_A_READY + s));
+            TR_STAMP_DECL;
+            head_epilogue(h_addr, 16 * (half ? hh0 : 0), 16 * (half ? hch : hh0), pl.n_head, s_head_scale, s_head_shift, out, live,
+                          bar(BAR_H_DRAINED + s) TR_STAMP_PASS);
+#ifdef CMBPO_TRACE
+            if (tr_base && tr_n + 2 <= kTraceSlots) {
+              tr_base[2 * tr_n] = g_stamp[0]; tr_base[2 * tr_n + 1] = 260 + l; ++tr_n;
+              tr_base[2 * tr_n] = g_stamp[1]; tr_base[2 * tr_n + 1] = 280 + l; ++tr_n;
+            }
+#endif
           }
           TR(240 + l);
         }
