@@ -175,6 +175,7 @@ SYMBOLS = {
     "cmbpo_finish_paths": (C.c_int, [C.POINTER(cmbpo_gae_io), C.c_void_p]),
     "cmbpo_normalize_scratch_bytes": (C.c_size_t, []),
     "cmbpo_normalize_advantages": (C.c_int, [C.POINTER(cmbpo_norm_io), C.c_void_p]),
+    "cmbpo_normalize_advantages_static": (C.c_int, [C.POINTER(cmbpo_norm_io), C.c_void_p, C.c_char_p, C.c_size_t]),
     "cmbpo_sample_archive": (C.c_int, [C.POINTER(cmbpo_sample_io), C.c_void_p]),
     "cmbpo_stub_policy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                     C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),

@@ -10,6 +10,7 @@
 // points as the reference.
 #include <cstdint>
 #include <cstdio>
+#include <mutex>
 #include <cuda_runtime.h>
 #include "../../include/cmbpo_b200.h"
 
@@ -265,5 +266,72 @@ extern "C" int cmbpo_normalize_advantages(const cmbpo_norm_io* io_, void* stream
   k_adv_apply<<<(int)nb, kNormThreads, 0, stream>>>(io);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(g_gae_err, sizeof(g_gae_err), "normalize_advantages: %s", cudaGetErrorString(e)); return CMBPO_ERR_CUDA; }
+  return CMBPO_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// cmbpo_normalize_advantages_static: the same three launches as cmbpo_normalize_advantages, with the scratch (ticket word +
+// per-block partial sums) in a file-scope device array instead of caller memory.  No counterpart in the reference; added
+// at the request of the run's operators for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc).  The entry point allocates nothing: no cudaMalloc / cudaFree / allocating library call.
+//  * every GPU that loads the library holds the kNormStaticBytes of the array until exit;
+//  * the array is shared by every call and keeps the last call's contents: the ticket word is cleared at the start of each
+//    call (the partial sums are fully rewritten before they are read), and two calls that overlap on the GPU -- different
+//    streams, or different host threads -- race on it.  Serialise them, or use cmbpo_normalize_advantages with own scratch;
+//  * in host code `g_norm_static` is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress,
+//    looked up once per device with that device current.
+// ---------------------------------------------------------------------------------------
+namespace cmbpo {
+constexpr size_t kNormStaticBytes = CMBPO_NORMALIZE_STATIC_SCRATCH_BYTES;
+static_assert(kNormStaticBytes % 256 == 0 && kNormStaticBytes >= 1024 * 5 * sizeof(double) + 64, "static scratch too small");
+static __device__ __align__(256) unsigned char g_norm_static[kNormStaticBytes];
+constexpr int kNormStaticMaxDevices = 64;
+static void* g_norm_static_ptr[kNormStaticMaxDevices];      // device address of g_norm_static, per device ordinal
+static std::mutex g_norm_static_mu;
+}  // namespace cmbpo
+
+extern "C" int cmbpo_normalize_advantages_static(const cmbpo_norm_io* io_, void* stream_, char* err, size_t err_len) {
+  auto fail = [&](int code, const char* fmt, auto... args) {
+    if (err && err_len) snprintf(err, err_len, fmt, args...);
+    return code;
+  };
+  if (err && err_len) err[0] = 0;
+  if (!io_ || !io_->adv_dev || !io_->cadv_dev || !io_->populated_dev || !io_->stats_dev)
+    return fail(CMBPO_ERR_ARG, "normalize_advantages_static: adv_dev, cadv_dev, populated_dev and stats_dev must be given");
+  const cmbpo_norm_io io = *io_;      // scratch_dev / scratch_bytes are ignored
+  if (io.n_elems < 0) return fail(CMBPO_ERR_ARG, "normalize_advantages_static: negative n_elems");
+  if (io.n_elems > (int64_t)CMBPO_NORMALIZE_STATIC_MAX_ELEMS)
+    return fail(CMBPO_ERR_UNSUPPORTED, "normalize_advantages_static: n_elems %lld exceeds the maximum of %lld entries; use "
+                "cmbpo_normalize_advantages with caller scratch", (long long)io.n_elems, (long long)CMBPO_NORMALIZE_STATIC_MAX_ELEMS);
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(CMBPO_ERR_CUDA, "normalize_advantages_static: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= kNormStaticMaxDevices)
+    return fail(CMBPO_ERR_UNSUPPORTED, "normalize_advantages_static: device ordinal %d beyond %d", dev, kNormStaticMaxDevices);
+  void* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_norm_static_mu);
+    if (!g_norm_static_ptr[dev]) {      // set-up, once per device, with that device current
+      void* ptr = nullptr;
+      e = cudaGetSymbolAddress(&ptr, g_norm_static);
+      if (e != cudaSuccess || !ptr)
+        return fail(CMBPO_ERR_CUDA, "normalize_advantages_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      g_norm_static_ptr[dev] = ptr;
+    }
+    base = g_norm_static_ptr[dev];
+  }
+  cudaStream_t stream = (cudaStream_t)stream_;
+  long long nb = (io.n_elems + kNormThreads - 1) / kNormThreads;
+  if (nb > 1024) nb = 1024;
+  if (nb < 1) nb = 1;
+  unsigned int* ticket = static_cast<unsigned int*>(base);
+  double* partials = reinterpret_cast<double*>(static_cast<uint8_t*>(base) + 64);
+  e = cudaMemsetAsync(ticket, 0, 64, stream);       // the array keeps the last call's contents: the ticket must start at zero
+  if (e != cudaSuccess) return fail(CMBPO_ERR_CUDA, "normalize_advantages_static: cudaMemsetAsync: %s", cudaGetErrorString(e));
+  k_adv_stats<1><<<(int)nb, kNormThreads, 0, stream>>>(io, partials, ticket);
+  k_adv_stats<2><<<(int)nb, kNormThreads, 0, stream>>>(io, partials, ticket);
+  k_adv_apply<<<(int)nb, kNormThreads, 0, stream>>>(io);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(CMBPO_ERR_CUDA, "normalize_advantages_static: %s", cudaGetErrorString(e));
   return CMBPO_OK;
 }

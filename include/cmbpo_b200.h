@@ -334,6 +334,22 @@ typedef struct cmbpo_norm_io {
 size_t cmbpo_normalize_scratch_bytes(void);
 int cmbpo_normalize_advantages(const cmbpo_norm_io* io, void* stream);
 
+/* cmbpo_normalize_advantages without any allocation on the caller's or the library's side.  This entry point has no
+ * counterpart in the reference: it was added at the request of the run's operators, for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, launches and results as
+ * cmbpo_normalize_advantages (bit-identical: same grid, same summation order); io->scratch_dev / scratch_bytes are ignored --
+ * the scratch is a file-scope `static __device__` array of CMBPO_NORMALIZE_STATIC_SCRATCH_BYTES that every GPU loading the
+ * library holds until exit.  Limits and rules:
+ *   - n_elems <= CMBPO_NORMALIZE_STATIC_MAX_ELEMS, else CMBPO_ERR_UNSUPPORTED (nothing is launched);
+ *   - all calls on a device share the array, which keeps the last call's contents (the call clears what must start at zero):
+ *     calls that overlap on the GPU (other streams, other host threads) RACE on it -- serialise them;
+ *   - the device current at the call is the one whose array is used: `stream` must belong to it.
+ * err / err_len: optional buffer that receives the error text (empty on success); the call calls no cudaMalloc, cudaFree or
+ * allocating library routine. */
+#define CMBPO_NORMALIZE_STATIC_SCRATCH_BYTES 41216            /* 64 (ticket) + 1024 blocks x 5 doubles, rounded up to 256 */
+#define CMBPO_NORMALIZE_STATIC_MAX_ELEMS (1LL << 26)          /* 67,108,864 pool entries ([T][B] flattened) */
+int cmbpo_normalize_advantages_static(const cmbpo_norm_io* io, void* stream, char* err, size_t err_len);
+
 /* Start-state sampling from the real-data archive (softlearning/replay_pools/cpobuffer.py:531-542 boltz_dist,
  * :559-610 distributed_batch_from_archive; mbpo/algorithms/cmbpo.py:328-333): weighted draw with replacement
  * (np.random.choice(archive_size, batch_size, p=dist): idx = searchsorted(cumsum(p)/sum(p), u, side='right')) and the
