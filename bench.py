@@ -474,8 +474,8 @@ def run_gpu(args, w, wname):
         hist = ro.alive_hist.cpu().numpy().astype(np.int64)
         rows_forwarded = int(hist.sum())
         launches_fwd = int((hist > 0).sum())
-        wide = max(w["hidden"]) > 254
-        fwd_launches = (len(w["hidden"]) + 1) * ((rows + 131071) // 131072) if wide else 1
+        # forward launches per sampler step: 1 for the fused kernels, one per FC layer and 131072-row slab for wide_layer_kernel
+        fwd_launches = (len(w["hidden"]) + 1) * ((rows + 131071) // 131072) if model._lib.cmbpo_forward_path(model._handle) == 1 else 1
         # per sampler step: stub policy, input staging, ensemble forward (fused: 1 launch; wide: one per FC layer and
         # 131072-row slab), step post, 3 bookkeeping kernels (decide+scan, store+scan, compact)
         kernels_per_step = (6 + fwd_launches) * (w["T"] - 1) + (3 if gather is not None else 0)   # dense gather: copy engines only
@@ -598,7 +598,7 @@ def run_gpu(args, w, wname):
                          f"port (torch BLAS GEMMs + NumPy post-processing, 64k-row chunks)"}
 
     traffic, traffic_src = committed_traffic(wname, rows_forwarded / max(launches_fwd, 1))
-    wide = max(w["hidden"]) > 254 or args.operand_dtype == "tf32"
+    fwd_kernel = ("ensemble_fwd_kernel", "wide_layer_kernel", "fused_wide_kernel")[model._lib.cmbpo_forward_path(model._handle)]
     which, peak = pick_peak(peaks, clk)
     cfg = config_of(wname, w, args.gpus)
     out = {
@@ -619,7 +619,7 @@ def run_gpu(args, w, wname):
         "e2e": {"value": e2e_val, "unit": "transitions/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "host_cpus_bound": numa},
         "gpu_launches": int(kernels_per_step * steps),
-        "roofline": {"bound": "tensor", "kernel": "wide_layer_kernel" if wide else "ensemble_fwd_kernel",
+        "roofline": {"bound": "tensor", "kernel": fwd_kernel,
                      "achieved": achieved_tf, "peak": peak, "unit": "TFLOP/s", "frac": achieved_tf / peak,
                      "peak_source": f"{peaks['source']} bf16 {which} (chosen from the clocks record)",
                      "frac_of_burst": achieved_tf / peaks["bf16_burst"], "frac_of_sustained": achieved_tf / peaks["bf16_sustained"],

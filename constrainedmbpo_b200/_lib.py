@@ -162,6 +162,7 @@ SYMBOLS = {
     "cmbpo_step": (C.c_int, [C.c_void_p, C.POINTER(cmbpo_step_io), C.c_void_p]),
     "cmbpo_draw_permutation": (C.c_int, [C.c_int32, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "cmbpo_status": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "cmbpo_forward_path": (C.c_int, [C.c_void_p]),
     "cmbpo_profile": (C.c_int, [C.c_void_p, C.c_int]),
     "cmbpo_profile_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cmbpo_rollout_scratch_bytes": (C.c_size_t, [C.c_int64]),

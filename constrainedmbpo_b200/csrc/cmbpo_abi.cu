@@ -19,6 +19,7 @@ cudaError_t launch_stage_inputs(const StageParams& p, int num_sms, cudaStream_t 
 cudaError_t pack_wide_layer(const float* W, const float* b, uint8_t* img, float* bias_tab, int E,
                             const WideLayerPlan& lp, int tf32, cudaStream_t stream);
 cudaError_t launch_wide_layer(const WideParams& p, int act, int num_sms, cudaStream_t stream);
+cudaError_t launch_fused_wide(const FusedWideParams& p, int act, int num_sms, cudaStream_t stream);
 }  // namespace cmbpo
 
 using namespace cmbpo;
@@ -55,6 +56,9 @@ struct Handle {
   uint8_t* wimg_wide = nullptr;
   float* bias_wide = nullptr;
   int wide_max_kc = 0;         // widest hidden activation image, in 64-column chunks
+  // fused wide path (fused_wide.cu): hidden layers up to 8 operand blocks wide run the whole stack in one launch
+  bool fused_wide = false;
+  int fw_a_blocks = 0, fw_a0_blocks = 0, fw_stages = 0;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
 };
 
@@ -153,6 +157,14 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
       wide_bias += (size_t)E * w.npad;
       if (l < L - 1 && w.npad / w.kc > h->wide_max_kc) h->wide_max_kc = w.npad / w.kc;
     }
+    // whole-stack kernel when one activation tile (+ the staged input tile + a weight ring) fits in shared memory;
+    // CMBPO_WIDE_FUSED=0 keeps the layer-at-a-time kernel (test hook: the two agree bit for bit)
+    h->fw_a_blocks = h->wide_max_kc;
+    h->fw_a0_blocks = h->wl[0].k_chunks;
+    h->fw_stages = kFusedWideBudgetBlocks - h->fw_a_blocks - h->fw_a0_blocks;
+    if (h->fw_stages > kFusedWideMaxStages) h->fw_stages = kFusedWideMaxStages;
+    h->fused_wide = L >= 2 && h->fw_a_blocks >= 1 && h->fw_a_blocks <= kFusedWideMaxABlocks && h->fw_stages >= kFusedWideMinStages;
+    if (const char* ff = getenv("CMBPO_WIDE_FUSED")) if (ff[0] == '0') h->fused_wide = false;
   }
   CU(cudaSetDevice(device), "cudaSetDevice");
   cudaDeviceProp prop;
@@ -279,7 +291,7 @@ static long long wide_slab_pad(long long rows) {
   return (r + 2 * kTileRows - 1) / (2 * kTileRows) * (2 * kTileRows);
 }
 static size_t wide_act_bytes(const Handle* h, long long rows) {
-  if (!h->wide) return 0;
+  if (!h->wide || h->fused_wide) return 0;   // the fused wide kernel keeps the activations in shared memory
   return (size_t)h->plan.E * (size_t)(wide_slab_pad(rows) / kTileRows) * h->wide_max_kc * kWideBlk;
 }
 static size_t ws_partials_offset(const Handle* h, long long rows) {
@@ -374,6 +386,22 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
   }
   if (!h->wide) {
     CU(launch_ensemble_fwd(p, h->hidden_act, h->num_sms, stream), "launch_ensemble_fwd");
+  } else if (h->fused_wide) {
+    // fused wide path: the whole stack in one launch, activations in shared memory
+    FusedWideParams fp;
+    memset(&fp, 0, sizeof(fp));
+    for (int l = 0; l < pl.L; ++l) fp.lp[l] = h->wl[l];
+    fp.L = pl.L; fp.E = pl.E; fp.n_head = pl.n_head; fp.tf32 = h->tf32 ? 1 : 0;
+    fp.a_blocks = h->fw_a_blocks; fp.a0_blocks = h->fw_a0_blocks; fp.stages = h->fw_stages;
+    fp.w_img = h->wimg_wide; fp.bias = h->bias_wide;
+    fp.a0_img = sp.a0img; fp.a0_slot_stride = sp.slot_stride_bytes;
+    fp.heads = heads; fp.head_scale = p.head_scale; fp.head_shift = p.head_shift;
+    for (int e = 0; e < pl.E; ++e) { fp.member_of_slot[e] = p.member_of_slot[e]; fp.input_of_slot[e] = p.input_of_slot[e]; }
+    fp.perm_dev = p.perm_dev;
+    fp.per_slot_input = p.per_slot_input;
+    fp.n_rows_dev = n_rows_dev; fp.n_rows = n_rows;
+    fp.status = h->status_dev;
+    CU(launch_fused_wide(fp, h->hidden_act, h->num_sms, stream), "launch_fused_wide");
   } else {
     // wide path: per row slab, one launch per FC layer; activations ping-pong between two bf16 images
     const size_t act_bytes = wide_act_bytes(h, n_rows);
@@ -514,6 +542,12 @@ extern "C" int cmbpo_step(void* handle, const cmbpo_step_io* io, void* stream_) 
   CU(launch_step_post(sp, pl.E, n_blocks, stream), "launch_step_post");
 
   return CMBPO_OK;
+}
+
+extern "C" int cmbpo_forward_path(void* handle) {
+  Handle* h = static_cast<Handle*>(handle);
+  if (!h) return fail(CMBPO_ERR_ARG, "cmbpo_forward_path: null handle");
+  return !h->wide ? 0 : (h->fused_wide ? 2 : 1);
 }
 
 extern "C" int cmbpo_profile(void* handle, int enable) {

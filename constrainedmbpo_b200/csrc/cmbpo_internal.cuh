@@ -143,6 +143,35 @@ struct WideParams {
   int* status;
 };
 
+// Fused wide path (fused_wide.cu): the whole FC stack of a wide ensemble in one launch, activations kept in one
+// shared-memory tile per CTA (a_blocks 16 KB blocks), weights streamed from the wide image through `stages` ring slots.
+constexpr int kFusedWideMaxStages = 8;
+constexpr int kFusedWideMaxABlocks = 8;      // widest hidden layer: 8 x 64 bf16 columns (or 8 x 32 tf32 columns)
+constexpr int kFusedWideBudgetBlocks = 14;   // 14 x 16 KB = 224 KB of the 227 KB a CTA may use
+constexpr int kFusedWideMinStages = 3;
+
+struct FusedWideParams {
+  WideLayerPlan lp[kMaxLayers];  // the wide path's layer plans (w_off / b_off relative to w_img / bias)
+  int L, E, n_head, tf32;
+  int a_blocks;                  // 16 KB blocks of the activation tile = max over hidden layers of npad / kc
+  int a0_blocks;                 // 16 KB blocks of the staged input tile = layer 0's k_chunks
+  int stages;                    // weight ring depth
+  const uint8_t* w_img;          // wide weight image (all layers)
+  const float* bias;             // wide bias table (all layers)
+  const uint8_t* a0_img;         // K0's chunked image [input slot][128-row block][k chunk]
+  long long a0_slot_stride;
+  float* heads;                  // out: tile-major fp32 head scratch (head_index)
+  const float* head_scale;
+  const float* head_shift;
+  int member_of_slot[kMaxMembers];
+  int input_of_slot[kMaxMembers];
+  const int* perm_dev;           // optional device [E] permutation: member = perm[j], input = perm[perm[j]]
+  int per_slot_input;
+  const int* n_rows_dev;
+  long long n_rows;
+  int* status;
+};
+
 // Slot maps of the 3-D ('iv_gae') path: host arrays by default, a device permutation when the caller drew it on the GPU
 // (cmbpo_draw_permutation) so that a captured rollout replays with a fresh forward_shuffle every time.
 #ifdef __CUDACC__

@@ -1,0 +1,448 @@
+// fused_wide.cu -- whole-stack PETS-ensemble forward for nets whose hidden layers are too wide for the two-stream
+// fused kernel (ensemble_fwd.cu, <= 254 columns) but still fit ONE shared-memory activation tile: widths up to 512
+// columns in bf16 -- the (512, 512) nets every shipped CMBPO config uses (examples/config/antsafe/cmbpo_uc.py:36,
+// mbpo/models/constructor.py:9-67) -- and up to 256 columns with tf32 operands.
+//
+// Why: the layer-at-a-time kernel (wide_fwd.cu) streams BOTH operands of every (tile, N chunk) item through shared
+// memory (64 B per clock and SM at full tensor rate, above what L2 delivers) and round-trips the bf16 activations of
+// E members through HBM between layers.  Here the activations of a 256-row tile never leave the SM pair:
+//
+//   * A: one activation tile per CTA (128 rows x up to 512 columns, "chunked canonical" 16 KB blocks of
+//     cmbpo_internal.cuh), written by the epilogue of layer l and read by the MMAs of layer l + 1; the staged input
+//     tile of layer 0 (K0's image) has a buffer of its own and is reused by all members of the tile.
+//   * B: the same packed weight image as wide_fwd.cu, streamed in 16 KB blocks (this CTA's N half x 64 k) through a
+//     ring of bulk async copies -- the only operand traffic left: 32 B per clock and SM.
+//   * D: the layer's fp32 accumulator in TMEM, up to two 256-column N chunks (columns 0..511); the head uses chunk 0.
+//
+// Schedule of one (tile, member) instance, tcgen05 cta_group::2, M = 256 rows per CTA pair:
+//   MMAs of layer l (N chunk 0, then 1; K blocks in order) -> commit LAYER_DONE -> the 8 epilogue warps convert the
+//   accumulator 64 columns (one K block of the next layer) at a time: bias + activation + bf16 pack + 16-byte
+//   shared-memory stores, then fence.proxy.async and an arrival on A_RDY[block].  The issuer starts N chunk 0 of layer
+//   l + 1 as soon as the epilogue has left the chunk's accumulator columns (A_RDY of the chunk's last block) and then
+//   follows the epilogue block by block, so the second half of a conversion runs under the next layer's first chunk.
+//   The accumulation order per output element (K blocks in order, 4 k-steps each) and the epilogue arithmetic are
+//   those of wide_fwd.cu: the two kernels agree bit for bit (tests/test_gpu_wide.py).
+//
+// Warp roles: 0 = weight loader (+ relay of the peer CTA's arrivals to the leader's barrier), 1 = MMA issuer (leader
+// CTA), 2 = TMEM alloc, 3 = input-tile loader, 4..11 = epilogue (TMEM lane quadrant = warp % 4, half of every block =
+// (warp - 4) / 4).  Work split: the flat list of (tile, member) instances, member fastest, is cut into one contiguous
+// range per CTA pair.
+#include "cmbpo_internal.cuh"
+#include "sm100_ptx.cuh"
+
+namespace cmbpo {
+using namespace sm100;
+
+constexpr int kFwThreads = 640;
+constexpr int kFwEpiWarps = 16;
+
+constexpr int FB_W_FULL = 0;         // [kFusedWideMaxStages]
+constexpr int FB_W_EMPTY = 8;        // [kFusedWideMaxStages]
+constexpr int FB_A_RDY = 16;         // [kFusedWideMaxABlocks / kFwGroup] blocks of group g of the activation tile written (and every accumulator column below their end read)
+constexpr int kFwGroup = 2;          // K blocks per A_RDY signal: one fence.proxy.async (300-400 cycles) per 128 bf16 columns and warp
+constexpr int FB_A0_FULL = 24;
+constexpr int FB_A0_EMPTY = 25;
+constexpr int FB_LAYER_DONE = 26;    // all MMAs of a layer complete (accumulator full, A tile no longer read)
+constexpr int FB_HEAD_DRAINED = 27;  // the head accumulator is in registers
+constexpr int kFwBars = 28;
+
+enum FusedWideWaitCode : int { FWC_LOADER = 21, FWC_A0 = 22, FWC_MMA_W = 23, FWC_MMA_A = 24, FWC_MMA_A0 = 25, FWC_MMA_HEAD = 26, FWC_EPI = 27 };
+
+__device__ __forceinline__ float fw_sigmoid_precise(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+  return r;
+}
+// same arithmetic as wide_fwd.cu's wide_activate (bit-identical results are tested)
+template <int ACT, bool PRECISE>
+__device__ __forceinline__ float fw_activate(float g) {
+  if constexpr (PRECISE) {
+    if constexpr (ACT == ACT_SWISH) return g * fw_sigmoid_precise(g);
+    else if constexpr (ACT == ACT_RELU) return fmaxf(g, 0.f);
+    else if constexpr (ACT == ACT_TANH) return fmaf(2.0f, fw_sigmoid_precise(2.0f * g), -1.0f);
+    else if constexpr (ACT == ACT_SIGMOID) return fw_sigmoid_precise(g);
+    else return g;
+  }
+  if constexpr (ACT == ACT_SWISH) return fmaf(g, tanh_approx(g), g);
+  else if constexpr (ACT == ACT_RELU) return fmaxf(g, 0.f);
+  else if constexpr (ACT == ACT_TANH) return tanh_approx(g);
+  else if constexpr (ACT == ACT_SIGMOID) return fmaf(0.5f, tanh_approx(g), 0.5f);
+  else return g;
+}
+
+__device__ __forceinline__ int fw_member_of(const FusedWideParams& p, int j) {
+  return p.perm_dev ? perm_at(p.perm_dev, j, p.E) : p.member_of_slot[j];
+}
+__device__ __forceinline__ int fw_input_of(const FusedWideParams& p, int j) {
+  return p.perm_dev ? perm_at(p.perm_dev, perm_at(p.perm_dev, j, p.E), p.E) : p.input_of_slot[j];
+}
+
+// the instances [begin, end) of one CTA pair: i -> (tile = i / E, slot e = i % E)
+struct FwInst {
+  long long i, begin, end, tile;
+  int e, E, per_slot;
+  __device__ __forceinline__ FwInst(long long b, long long en, int E_, int per_slot_)
+      : i(b), begin(b), end(en), tile(b / E_), e((int)(b % E_)), E(E_), per_slot(per_slot_) {}
+  __device__ __forceinline__ bool valid() const { return i < end; }
+  __device__ __forceinline__ void next() { ++i; if (++e == E) { e = 0; ++tile; } }
+  __device__ __forceinline__ bool new_input() const { return per_slot || i == begin || e == 0; }       // the input tile changes
+  __device__ __forceinline__ bool last_use() const { return per_slot || i == end - 1 || e == E - 1; }  // last instance on this input tile
+};
+
+template <int HACT, bool TF32>
+__global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_constant__ FusedWideParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const uint32_t cta = cluster_ctarank();
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
+  const long long n_tiles = (n_rows + 2 * kTileRows - 1) / (2 * kTileRows);
+  const int E = p.E, L = p.L, S = p.stages;
+  const long long total = n_tiles * E;
+  const long long i_begin = total * cluster_id / n_clusters, i_end = total * (cluster_id + 1) / n_clusters;
+
+  const uint32_t off_a0 = (uint32_t)p.a_blocks * kWideBlk;
+  const uint32_t off_ring = off_a0 + (uint32_t)p.a0_blocks * kWideBlk;
+  const uint32_t off_bar = off_ring + (uint32_t)S * kWideBlk;
+  const uint32_t bar0 = smem_u32(smem + off_bar);
+  auto bar = [bar0](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + off_bar + kFwBars * 8u);
+
+  if (tid == 0) {
+    for (int s = 0; s < kFusedWideMaxStages; ++s) {
+      mbar_init(bar(FB_W_FULL + s), cta == 0 ? 2 : 1);    // leader: own fill + relayed peer fill
+      mbar_init(bar(FB_W_EMPTY + s), 1);                  // tcgen05.commit
+    }
+    for (int j = 0; j < kFusedWideMaxABlocks; ++j) mbar_init(bar(FB_A_RDY + j), 2 * kFwEpiWarps);
+    mbar_init(bar(FB_A0_FULL), cta == 0 ? 2 : 1);
+    mbar_init(bar(FB_A0_EMPTY), 1);                       // tcgen05.commit
+    mbar_init(bar(FB_LAYER_DONE), 1);                     // tcgen05.commit
+    mbar_init(bar(FB_HEAD_DRAINED), 2 * kFwEpiWarps);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc<2>(smem_u32(tmem_slot), 512);
+    tmem_relinquish<2>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync();
+  tc_fence_after();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+
+  if (warp == 0) {
+    // ===== weight loader: fill n of the (instance, layer, N chunk, K block) walk goes to ring stage n % S
+    if (lane == 0) {
+      long long per_inst = 0;
+      for (int l = 0; l < L; ++l) per_inst += (long long)p.lp[l].n_chunks * p.lp[l].k_chunks;
+      const long long n_fill = (i_end - i_begin) * per_inst;
+      long long fill_n = 0, relay_n = 0;
+      int f_stage = 0, r_stage = 0; uint32_t f_use = 0, r_use = 0, idle = 0;
+      FwInst it(i_begin, i_end, E, p.per_slot_input);
+      int l = 0, c = 0, j = 0;
+      const uint8_t* b_src = nullptr; uint32_t b_bytes = 0;
+      while (fill_n < n_fill || (cta == 1 && relay_n < n_fill)) {
+        bool progress = false;
+        if (fill_n < n_fill && (f_use == 0 || mbar_try_wait(bar(FB_W_EMPTY + f_stage), (f_use - 1) & 1))) {
+          const WideLayerPlan& lp = p.lp[l];
+          if (j == 0) {
+            const int chunk_n = min(kWideNC, lp.npad - c * kWideNC);
+            b_bytes = (uint32_t)(chunk_n >> 1) * 128u;
+            b_src = p.w_img + lp.w_off + ((((size_t)fw_member_of(p, it.e) * lp.n_chunks + c) * 2 + cta) * lp.k_chunks) * kWideBlk;
+          }
+          mbar_arrive_expect_tx(bar(FB_W_FULL + f_stage), b_bytes);
+          bulk_g2s(smem_u32(smem + off_ring + (uint32_t)f_stage * kWideBlk), b_src, b_bytes, bar(FB_W_FULL + f_stage));
+          b_src += kWideBlk;
+          if (++j == lp.k_chunks) { j = 0; if (++c == lp.n_chunks) { c = 0; if (++l == L) { l = 0; it.next(); } } }
+          if (++f_stage == S) { f_stage = 0; ++f_use; }
+          ++fill_n; progress = true;
+        }
+        if (cta == 1 && relay_n < fill_n && mbar_try_wait(bar(FB_W_FULL + r_stage), r_use & 1)) {
+          mbar_arrive_cluster_light(bar(FB_W_FULL + r_stage), 0);   // async-proxy data consumed by the async proxy: light arrive
+          if (++r_stage == S) { r_stage = 0; ++r_use; }
+          ++relay_n; progress = true;
+        }
+        if (progress) { idle = 0; continue; }
+        __nanosleep(32);
+        if (++idle > (SM100_WAIT_LIMIT >> 2)) {
+          if (p.status) { *reinterpret_cast<volatile int*>(p.status) = (FWC_LOADER | 0x40000000); __threadfence_system(); }
+          __trap();
+        }
+      }
+    }
+  } else if (warp == 3) {
+    // ===== input-tile loader: K0's staged layer-0 operand blocks of this CTA's 128 rows, one fill per input tile
+    if (lane == 0) {
+      long long n_fill = 0;
+      for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next()) if (it.new_input()) ++n_fill;
+      long long fill_n = 0, relay_n = 0; uint32_t idle = 0;
+      FwInst it(i_begin, i_end, E, p.per_slot_input);
+      const uint32_t a0_bytes = (uint32_t)p.a0_blocks * kWideBlk;
+      while (fill_n < n_fill || (cta == 1 && relay_n < n_fill)) {
+        bool progress = false;
+        if (fill_n < n_fill && (fill_n == 0 || mbar_try_wait(bar(FB_A0_EMPTY), (uint32_t)(fill_n - 1) & 1))) {
+          while (!it.new_input()) it.next();
+          const int in_slot = p.per_slot_input ? fw_input_of(p, it.e) : 0;
+          const uint8_t* src = p.a0_img + (size_t)in_slot * p.a0_slot_stride + (size_t)(it.tile * 2 + cta) * a0_bytes;
+          mbar_arrive_expect_tx(bar(FB_A0_FULL), a0_bytes);
+          bulk_g2s(smem_u32(smem + off_a0), src, a0_bytes, bar(FB_A0_FULL));
+          it.next();
+          ++fill_n; progress = true;
+        }
+        if (cta == 1 && relay_n < fill_n && mbar_try_wait(bar(FB_A0_FULL), (uint32_t)relay_n & 1)) {
+          mbar_arrive_cluster_light(bar(FB_A0_FULL), 0);
+          ++relay_n; progress = true;
+        }
+        if (progress) { idle = 0; continue; }
+        __nanosleep(64);
+        if (++idle > (SM100_WAIT_LIMIT >> 2)) {
+          if (p.status) { *reinterpret_cast<volatile int*>(p.status) = (FWC_A0 | 0x40000000); __threadfence_system(); }
+          __trap();
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA): the whole warp walks the loop, one elected lane issues
+    if (cta == 0) {
+      int stage = 0; uint32_t use = 0;
+      uint32_t a_par = 0;          // bit j: parity of the completion of A_RDY[j] the next consuming layer waits for
+      uint32_t a0_n = 0, n_inst = 0;
+      const uint32_t a_tile = smem_u32(smem), a0_tile = smem_u32(smem + off_a0), ring = smem_u32(smem + off_ring);
+      for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next(), ++n_inst) {
+        for (int l = 0; l < L; ++l) {
+          const WideLayerPlan& lp = p.lp[l];
+          const int KC = lp.k_chunks, NCH = lp.n_chunks;
+          uint32_t seen = 0;
+          auto wait_a = [&](int j) {     // K block j of the activation tile (signalled per group of kFwGroup blocks)
+            const int g = j / kFwGroup;
+            if (!((seen >> g) & 1u)) {
+              mbar_wait(bar(FB_A_RDY + g), (a_par >> g) & 1u, p.status, FWC_MMA_A);
+              seen |= 1u << g;
+            }
+          };
+          for (int c = 0; c < NCH; ++c) {
+            const int chunk_n = min(kWideNC, lp.npad - c * kWideNC);
+            const uint32_t idesc = make_idesc(256, chunk_n, TF32 ? kFmtTF32 : kFmtBF16);
+            const uint32_t d_tmem = tmem_base + (uint32_t)(c * kWideNC);
+            if (l == 0) {
+              if (c == 0) {
+                if (it.new_input()) { mbar_wait(bar(FB_A0_FULL), a0_n & 1, p.status, FWC_MMA_A0); ++a0_n; }
+                // the previous instance's head sits in accumulator columns 0..; everything above was drained by its last
+                // hidden conversion, which completed before the head MMAs were issued
+                if (n_inst > 0) mbar_wait(bar(FB_HEAD_DRAINED), (n_inst - 1) & 1, p.status, FWC_MMA_HEAD);
+              }
+            } else {
+              // accumulator columns [256 c, 256 c + chunk_n) must have been read by the conversion of layer l - 1, which
+              // walks the columns in order: wait for the block that ends at or beyond them
+              int drain = (c * kWideNC + chunk_n + lp.kc - 1) / lp.kc;
+              if (drain > KC) drain = KC;
+              wait_a(drain - 1);
+            }
+            for (int j = 0; j < KC; ++j) {
+              if (l > 0) wait_a(j);
+              mbar_wait(bar(FB_W_FULL + stage), use & 1, p.status, FWC_MMA_W);
+              tc_fence_after();
+              const uint32_t a_base = (l == 0 ? a0_tile : a_tile) + (uint32_t)j * kWideBlk;
+              const uint32_t b_base = ring + (uint32_t)stage * kWideBlk;
+              const bool layer_end = (c == NCH - 1 && j == KC - 1);
+              if (elect_one()) {
+#pragma unroll
+                for (int ks = 0; ks < kWideKC / 16; ++ks) {
+                  if constexpr (TF32)
+                    mma_tf32_ss<2>(d_tmem, make_smem_desc(a_base + ks * 256, 128, 1024),
+                                   make_smem_desc(b_base + ks * 256, 128, 1024), idesc, (j > 0 || ks > 0) ? 1u : 0u);
+                  else
+                    mma_bf16_ss<2>(d_tmem, make_smem_desc(a_base + ks * 256, 128, 1024),
+                                   make_smem_desc(b_base + ks * 256, 128, 1024), idesc, (j > 0 || ks > 0) ? 1u : 0u);
+                }
+                mma_commit_2sm(bar(FB_W_EMPTY + stage), 0x3);
+                if (layer_end) {
+                  mma_commit_2sm(bar(FB_LAYER_DONE), 0x3);
+                  if (l == 0 && it.last_use()) mma_commit_2sm(bar(FB_A0_EMPTY), 0x3);
+                }
+              }
+              __syncwarp();
+              if (++stage == S) { stage = 0; ++use; }
+            }
+          }
+          if (l > 0) a_par ^= (1u << ((KC + kFwGroup - 1) / kFwGroup)) - 1u;     // one completion of every group's A_RDY consumed
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue warps 4..19: TMEM lane quadrant q (the hardware ties a warp to lanes 32 * (warp % 4) ..), column part
+    // `part` of every block group: four warps per SM sub-partition hide each other's TMEM / bias-load / fence latencies
+    const int q = warp & 3, part = (warp - 4) >> 2;
+    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    const int row_in_tile = q * 32 + lane;
+    const uint32_t row_off = (uint32_t)(row_in_tile >> 3) * 1024u + (uint32_t)(row_in_tile & 7) * 16u;
+    const uint32_t d_addr = tmem_base + lane_base;
+    uint8_t* a_row = smem + row_off;
+    uint32_t ld_n = 0;
+    for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next()) {
+      const int e = it.e;
+      const int member = fw_member_of(p, e);
+      const long long blk = it.tile * 2 + cta;           // 128-row block of the batch
+      for (int l = 0; l < L; ++l) {
+        const WideLayerPlan& lp = p.lp[l];
+        const float* bias = p.bias + lp.b_off + (size_t)member * lp.npad;
+        mbar_wait(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
+        ++ld_n;
+        tc_fence_after();
+        uint32_t ra[16], rb[16];
+        if (l < L - 1) {
+          // A block group = kFwGroup blocks = GC columns; this warp converts columns [part * GC/4, (part + 1) * GC/4) of every
+          // group in PPG 16-column pieces: piece t -> group t / PPG.  Groups beyond npad (a partial last group) have no
+          // columns for the higher parts: those warps only arrive.
+          constexpr int KCOLS = TF32 ? kWideKC / 2 : kWideKC;   // columns per 16 KB block
+          constexpr int GC = kFwGroup * KCOLS;                 // 128 (bf16) / 64 (tf32)
+          constexpr int PPG = GC / 64;                         // 2 / 1
+          const int n_grp = (lp.npad + GC - 1) / GC;
+          auto col_of = [&](int t) { return (t / PPG) * GC + part * (GC / 4) + (t % PPG) * 16; };
+          int n_t = n_grp * PPG;                               // this warp's pieces with columns below npad (a prefix)
+          while (n_t > 0 && col_of(n_t - 1) >= lp.npad) --n_t;
+          auto arrive_group = [&](int g, bool wrote) {
+            if (wrote) fence_proxy_async_smem();         // generic-proxy smem writes -> visible to tcgen05.mma
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster_light(bar(FB_A_RDY + g), 0);
+          };
+          auto finish = [&](int t, const uint32_t (&r)[16], const float (&b)[16]) {
+            const int n0 = col_of(t);
+            if constexpr (TF32) {
+              uint8_t* dst = a_row + (size_t)(n0 >> 5) * kWideBlk + (size_t)((n0 & 31) >> 2) * 128;
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                float4 v;
+                v.x = round_tf32(fw_activate<HACT, true>(__uint_as_float(r[4 * i]) + b[4 * i]));
+                v.y = round_tf32(fw_activate<HACT, true>(__uint_as_float(r[4 * i + 1]) + b[4 * i + 1]));
+                v.z = round_tf32(fw_activate<HACT, true>(__uint_as_float(r[4 * i + 2]) + b[4 * i + 2]));
+                v.w = round_tf32(fw_activate<HACT, true>(__uint_as_float(r[4 * i + 3]) + b[4 * i + 3]));
+                *reinterpret_cast<float4*>(dst + 128 * i) = v;
+              }
+            } else {
+              uint32_t o[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                o[i] = pack_bf16x2(fw_activate<HACT, false>(__uint_as_float(r[2 * i]) + b[2 * i]),
+                                   fw_activate<HACT, false>(__uint_as_float(r[2 * i + 1]) + b[2 * i + 1]));
+              uint8_t* dst = a_row + (size_t)(n0 >> 6) * kWideBlk + (size_t)((n0 & 63) >> 3) * 128;
+              *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+              *reinterpret_cast<uint4*>(dst + 128) = make_uint4(o[4], o[5], o[6], o[7]);
+            }
+            if ((t + 1) % PPG == 0) arrive_group(t / PPG, true);   // this warp's share of the group is written
+          };
+          auto step = [&](int t, const uint32_t (&r)[16], uint32_t (&r_next)[16]) {
+            float b[16];                                       // warp-uniform addresses, issued before the TMEM wait
+            const float4* src = reinterpret_cast<const float4*>(bias + col_of(t));
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float4 v = __ldg(src + i);
+              b[4 * i] = v.x; b[4 * i + 1] = v.y; b[4 * i + 2] = v.z; b[4 * i + 3] = v.w;
+            }
+            tmem_wait_ld();
+            if (t + 1 < n_t) tmem_ld16(d_addr + col_of(t + 1), r_next);
+            finish(t, r, b);
+          };
+          if (n_t > 0) tmem_ld16(d_addr + col_of(0), ra);
+          for (int t = 0; t < n_t; t += 2) {
+            step(t, ra, rb);
+            if (t + 1 < n_t) step(t + 1, rb, ra);
+          }
+          for (int g = n_t / PPG; g < n_grp; ++g) arrive_group(g, false);   // groups this warp has no columns in
+        } else {
+          // head: (acc + b) * s + shift into the tile-major fp32 scratch (bnn.py:878-893); the accumulator is released
+          // (HEAD_DRAINED) as soon as the warp's columns are in registers, before the global stores
+          const int nch = lp.npad >> 4;
+          const int c_begin = 16 * ((part * nch) >> 2), c_end = 16 * (((part + 1) * nch) >> 2);
+          const bool live_row = blk * kTileRows + row_in_tile < n_rows;
+          float* out = p.heads + ((size_t)(blk * E + e) * p.n_head) * kTileRows + row_in_tile;
+          auto drained = [&]() {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster_light(bar(FB_HEAD_DRAINED), 0);
+          };
+          auto store16 = [&](int c0, const uint32_t (&r)[16]) {
+            if (live_row) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const int col = c0 + i;
+                if (col < p.n_head) {
+                  const float sc = p.head_scale ? __ldg(p.head_scale + col) : 1.f;
+                  const float sh = p.head_shift ? __ldg(p.head_shift + col) : 0.f;
+                  out[(size_t)col * kTileRows] = fmaf(__uint_as_float(r[i]) + __ldg(bias + col), sc, sh);
+                }
+              }
+            }
+          };
+          if (c_begin >= c_end) drained();
+          for (int c0 = c_begin; c0 < c_end; c0 += 32) {
+            const bool two = c0 + 16 < c_end;
+            tmem_ld16(d_addr + c0, ra);
+            if (two) tmem_ld16(d_addr + c0 + 16, rb);
+            tmem_wait_ld();
+            if (c0 + 32 >= c_end) drained();
+            store16(c0, ra);
+            if (two) store16(c0 + 16, rb);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync();
+  if (warp == 2) tmem_dealloc<2>(tmem_base, 512);
+}
+
+size_t fused_wide_smem_bytes(const FusedWideParams& p) {
+  return (size_t)(p.a_blocks + p.a0_blocks + p.stages) * kWideBlk + kFwBars * 8u + 16u;
+}
+
+template <int HACT, bool TF32>
+static cudaError_t launch_fused_wide_variant2(const FusedWideParams& p, int num_sms, cudaStream_t stream) {
+  const size_t smem = fused_wide_smem_bytes(p);
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    cudaError_t e = cudaFuncSetAttribute(fused_wide_kernel<HACT, TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    smem_set = smem;
+  }
+  int clusters = num_sms / 2;
+  if (!p.n_rows_dev) {
+    const long long n_tiles = (p.n_rows + 2 * kTileRows - 1) / (2 * kTileRows);
+    const long long inst = n_tiles * p.E;
+    if (inst < clusters) clusters = (int)(inst > 0 ? inst : 1);
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * clusters);
+  cfg.blockDim = dim3(kFwThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, fused_wide_kernel<HACT, TF32>, p);
+}
+template <int HACT>
+static cudaError_t launch_fused_wide_variant(const FusedWideParams& p, int num_sms, cudaStream_t stream) {
+  return p.tf32 ? launch_fused_wide_variant2<HACT, true>(p, num_sms, stream) : launch_fused_wide_variant2<HACT, false>(p, num_sms, stream);
+}
+
+// act: the activation every hidden layer shares (constructor.py:57-60)
+cudaError_t launch_fused_wide(const FusedWideParams& p, int act, int num_sms, cudaStream_t stream) {
+  switch (act) {
+    case ACT_SWISH:   return launch_fused_wide_variant<ACT_SWISH>(p, num_sms, stream);
+    case ACT_RELU:    return launch_fused_wide_variant<ACT_RELU>(p, num_sms, stream);
+    case ACT_TANH:    return launch_fused_wide_variant<ACT_TANH>(p, num_sms, stream);
+    case ACT_SIGMOID: return launch_fused_wide_variant<ACT_SIGMOID>(p, num_sms, stream);
+    case ACT_NONE:    return launch_fused_wide_variant<ACT_NONE>(p, num_sms, stream);
+    default:          return cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace cmbpo

@@ -389,6 +389,11 @@ int cmbpo_stub_policy(const void* obs_dev, const void* P_dev, void* act_dev, con
 int cmbpo_profile(void* handle, int enable);
 int cmbpo_profile_read(void* handle, double* fwd_ms_total, int64_t* fwd_launches);
 
+/* Which forward kernel this handle's net runs on (measurement aid, no reference counterpart):
+ * 0 = ensemble_fwd_kernel (hidden layers <= 254 wide, two row-tile streams), 1 = wide_layer_kernel (one launch per
+ * FC layer), 2 = fused_wide_kernel (hidden layers up to 512 bf16 / 256 tf32 columns, whole stack in one launch). */
+int cmbpo_forward_path(void* handle);
+
 /* watchdog word of the last launches on this handle (0 = clean), synchronises the stream */
 int cmbpo_status(void* handle, void* stream);
 

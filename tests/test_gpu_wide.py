@@ -145,3 +145,70 @@ np.save(sys.argv[1], np.stack([mean, var]))
     p = make_params("antsafe", (200, 200, 200, 200))
     s = out_scale(p)
     assert_means_close(outs[1][0], outs[0][0], s, what="wide vs fused mean")
+
+
+# ---- fused wide kernel (fused_wide.cu): the whole stack of a <= 512-wide ensemble in one launch -------------------
+def _wide_model(p, hidden, fused, **kw):
+    """CMBPO_WIDE_FUSED is read by cmbpo_create: '0' keeps the layer-at-a-time kernel for this handle."""
+    old = os.environ.get("CMBPO_WIDE_FUSED")
+    os.environ["CMBPO_WIDE_FUSED"] = "1" if fused else "0"
+    try:
+        return _cuda_model(p, hidden, kw.pop("loss", "MSPE"), **kw)
+    finally:
+        if old is None:
+            del os.environ["CMBPO_WIDE_FUSED"]
+        else:
+            os.environ["CMBPO_WIDE_FUSED"] = old
+
+
+@pytest.mark.parametrize("env,hidden,B,dtype", [
+    ("antsafe", (512, 512), 3000, "bf16"),                 # the shipped shape: two N chunks, 8 K blocks
+    ("antsafe", (512, 512, 512, 512), 40_000, "bf16"),     # ~15 (tile, member) instances per CTA pair: ring / phase wrap
+    ("halfcheetah", (256, 256, 256, 256), 2500, "bf16"),   # one N chunk
+    ("antsafe", (512, 200, 384), 1500, "bf16"),            # widths change from layer to layer (chunk 1 of 128 columns)
+    ("antsafe", (300, 260), 777, "bf16"),                  # ragged widths
+    ("antsafe", (200, 200, 200, 200), 5000, "tf32"),       # tf32 operands: 32-column blocks, 3xTF32 layer 0 (4 input blocks)
+    ("hopper", (64, 64), 1000, "tf32"),
+])
+def test_fused_wide_matches_layer_at_a_time_bit_for_bit(env, hidden, B, dtype):
+    """Same weight image, same accumulation order (K blocks in order), same epilogue arithmetic: the fused kernel and
+    wide_fwd.cu must agree to the last bit; the layer-at-a-time kernel is the one the rest of this file pins to the oracle."""
+    p = make_params(env, hidden)
+    obs, act = make_inputs(env, B)
+    x = np.concatenate([obs, act], -1)
+    mf, vf = _wide_model(p, hidden, True, operand_dtype=dtype).predict(x, factored=True)
+    ml, vl = _wide_model(p, hidden, False, operand_dtype=dtype).predict(x, factored=True)
+    assert np.isfinite(mf).all()
+    np.testing.assert_array_equal(mf, ml)
+    np.testing.assert_array_equal(vf, vl)
+
+
+def test_fused_wide_3d_input_and_activations():
+    """3-D inputs (every member its own rows, fc.py:107-108) and the non-swish activations through the fused kernel."""
+    for activation in ("ReLU", "tanh", "sigmoid", "swish"):
+        p = _generic(40, 3, (320, 288), 4, prob=True, activation=activation, seed=11)
+        x = np.random.default_rng(12).standard_normal((4, 900, 40)).astype(np.float32)
+        mf, vf = _wide_model(p, (320, 288), True, loss="NLL", activation=activation).predict(x, factored=True)
+        ml, vl = _wide_model(p, (320, 288), False, loss="NLL", activation=activation).predict(x, factored=True)
+        np.testing.assert_array_equal(mf, ml)
+        np.testing.assert_array_equal(vf, vl)
+        rm, rv = orc.predict(p, x.astype(np.float64), factored=True)
+        assert_means_close(mf, rm, out_scale(p), atol_scale=_atol((320, 288)))
+
+
+def test_fused_wide_at_size_shipped_shape():
+    """200 000 rows of the shipped (512, 512) shape: every CTA pair walks ~75 instances (weight ring and barrier phases
+    wrap many times, input tiles change every 7 instances); all rows bit for bit against the layer-at-a-time kernel, and
+    sampled rows against the fp64 oracle."""
+    hidden = (512, 512)
+    p = make_params("antsafe", hidden)
+    B = 200_000
+    obs, act = make_inputs("antsafe", B)
+    x = np.concatenate([obs, act], -1)
+    mf, vf = _wide_model(p, hidden, True).predict(x, factored=True)
+    ml, vl = _wide_model(p, hidden, False).predict(x, factored=True)
+    np.testing.assert_array_equal(mf, ml)
+    np.testing.assert_array_equal(vf, vl)
+    rows = np.unique(np.concatenate([np.arange(300), np.arange(B - 300, B), np.random.default_rng(3).integers(0, B, 2000)]))
+    rm, _ = orc.predict(p, x[rows].astype(np.float64), factored=True)
+    assert_means_close(mf[:, rows], rm, out_scale(p), atol_scale=_atol(hidden))
