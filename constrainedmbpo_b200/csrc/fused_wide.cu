@@ -44,7 +44,13 @@ constexpr int FB_A0_FULL = 24;
 constexpr int FB_A0_EMPTY = 25;
 constexpr int FB_LAYER_DONE = 26;    // all MMAs of a layer complete (accumulator full, A tile no longer read)
 constexpr int FB_HEAD_DRAINED = 27;  // the head accumulator is in registers
-constexpr int kFwBars = 28;
+constexpr int FB_ACC0_FULL = 28;     // two-chunk layers: N chunk 0 complete (its conversion starts under the MMAs of chunk 1)
+constexpr int FB_A_FREE = 29;        // [2] two-chunk layers: chunk 1's MMAs have read block group g of the activation tile
+constexpr int kFwEarlyGroups = 2;    // block groups under N chunk 0 (256 bf16 columns)
+constexpr int kFwBars = 31;
+static_assert(kFwBars * 8 + 16 <= 512, "barrier area");
+constexpr uint32_t kFwBarBytes = 512;   // barriers + TMEM slot, padded so the bias words behind them are 16-byte aligned
+constexpr int kFwBiasFloats = 512;   // widest hidden layer (8 blocks x 64 bf16 columns)
 
 enum FusedWideWaitCode : int { FWC_LOADER = 21, FWC_A0 = 22, FWC_MMA_W = 23, FWC_MMA_A = 24, FWC_MMA_A0 = 25, FWC_MMA_HEAD = 26, FWC_EPI = 27 };
 
@@ -109,6 +115,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
   const uint32_t bar0 = smem_u32(smem + off_bar);
   auto bar = [bar0](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + off_bar + kFwBars * 8u);
+  float* bias_s = reinterpret_cast<float*>(smem + off_bar + kFwBarBytes);   // [kFwBiasFloats] bias of the pass being converted
 
   if (tid == 0) {
     for (int s = 0; s < kFusedWideMaxStages; ++s) {
@@ -120,6 +127,8 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
     mbar_init(bar(FB_A0_EMPTY), 1);                       // tcgen05.commit
     mbar_init(bar(FB_LAYER_DONE), 1);                     // tcgen05.commit
     mbar_init(bar(FB_HEAD_DRAINED), 2 * kFwEpiWarps);
+    mbar_init(bar(FB_ACC0_FULL), 1);                      // tcgen05.commit
+    for (int g = 0; g < kFwEarlyGroups; ++g) mbar_init(bar(FB_A_FREE + g), 1);   // tcgen05.commit
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -258,6 +267,16 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
                                    make_smem_desc(b_base + ks * 256, 128, 1024), idesc, (j > 0 || ks > 0) ? 1u : 0u);
                 }
                 mma_commit_2sm(bar(FB_W_EMPTY + stage), 0x3);
+                if (NCH == 2) {
+                  // chunk 0 is complete: its conversion starts now; it may overwrite block group g of the activation tile once
+                  // chunk 1 has read it (layer 0 reads the input tile instead: every group is free at once)
+                  if (c == 0 && j == KC - 1) mma_commit_2sm(bar(FB_ACC0_FULL), 0x3);
+                  if (c == 1) {
+#pragma unroll
+                    for (int g = 0; g < kFwEarlyGroups; ++g)
+                      if (j == min((g + 1) * kFwGroup - 1, KC - 1)) mma_commit_2sm(bar(FB_A_FREE + g), 0x3);
+                  }
+                }
                 if (layer_end) {
                   mma_commit_2sm(bar(FB_LAYER_DONE), 0x3);
                   if (l == 0 && it.last_use()) mma_commit_2sm(bar(FB_A0_EMPTY), 0x3);
@@ -280,7 +299,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
     const uint32_t row_off = (uint32_t)(row_in_tile >> 3) * 1024u + (uint32_t)(row_in_tile & 7) * 16u;
     const uint32_t d_addr = tmem_base + lane_base;
     uint8_t* a_row = smem + row_off;
-    uint32_t ld_n = 0;
+    uint32_t ld_n = 0, two_n = 0;     // completions of LAYER_DONE / of the two-chunk barriers consumed
     for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next()) {
       const int e = it.e;
       const int member = fw_member_of(p, e);
@@ -288,9 +307,6 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
       for (int l = 0; l < L; ++l) {
         const WideLayerPlan& lp = p.lp[l];
         const float* bias = p.bias + lp.b_off + (size_t)member * lp.npad;
-        mbar_wait(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
-        ++ld_n;
-        tc_fence_after();
         uint32_t ra[16], rb[16];
         if (l < L - 1) {
           // A block group = kFwGroup blocks = GC columns; this warp converts columns [part * GC/4, (part + 1) * GC/4) of every
@@ -303,6 +319,25 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
           auto col_of = [&](int t) { return (t / PPG) * GC + part * (GC / 4) + (t % PPG) * 16; };
           int n_t = n_grp * PPG;                               // this warp's pieces with columns below npad (a prefix)
           while (n_t > 0 && col_of(n_t - 1) >= lp.npad) --n_t;
+          // The bias of this warp's columns goes through shared memory: one 16-byte global load per lane and pass, issued
+          // while the MMAs still run, instead of four L2-latency loads in front of every piece (a new member every instance
+          // makes them cold misses, on all four warps of a sub-partition at once: ~270 cycles per piece in the ncu samples).
+          // The four quadrant warps of a part write the same values to the same words; a warp reads them after its own
+          // store, and the named barrier keeps the words of the previous pass alive until all four warps are done with it.
+          {
+            constexpr int FPG = GC / 4;                        // floats per group and warp: 32 (bf16) / 16 (tf32)
+            const int g = lane / (FPG / 4), c4 = lane % (FPG / 4);
+            const int col = g * GC + part * FPG + c4 * 4;
+            const bool act = g < n_grp && col < lp.npad;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (act) v = __ldg(reinterpret_cast<const float4*>(bias + col));
+            asm volatile("bar.sync %0, 128;" ::"r"(1 + part) : "memory");
+            if (act) *reinterpret_cast<float4*>(bias_s + col) = v;
+            __syncwarp();
+          }
+          // two-chunk layers: the columns under N chunk 0 (groups 0 .. kFwEarlyGroups) are converted while chunk 1's MMAs run
+          const bool two = lp.n_chunks == 2;
+          const int n_early = two ? min(n_t, kFwEarlyGroups * PPG) : 0;
           auto arrive_group = [&](int g, bool wrote) {
             if (wrote) fence_proxy_async_smem();         // generic-proxy smem writes -> visible to tcgen05.mma
             tc_fence_before();
@@ -311,50 +346,65 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
           };
           auto finish = [&](int t, const uint32_t (&r)[16], const float (&b)[16]) {
             const int n0 = col_of(t);
+            uint32_t o[TF32 ? 16 : 8];
             if constexpr (TF32) {
-              uint8_t* dst = a_row + (size_t)(n0 >> 5) * kWideBlk + (size_t)((n0 & 31) >> 2) * 128;
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                float4 v;
-                v.x = round_tf32(fw_activate<HACT, true>(__uint_as_float(r[4 * i]) + b[4 * i]));
-                v.y = round_tf32(fw_activate<HACT, true>(__uint_as_float(r[4 * i + 1]) + b[4 * i + 1]));
-                v.z = round_tf32(fw_activate<HACT, true>(__uint_as_float(r[4 * i + 2]) + b[4 * i + 2]));
-                v.w = round_tf32(fw_activate<HACT, true>(__uint_as_float(r[4 * i + 3]) + b[4 * i + 3]));
-                *reinterpret_cast<float4*>(dst + 128 * i) = v;
-              }
+              for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(round_tf32(fw_activate<HACT, true>(__uint_as_float(r[i]) + b[i])));
             } else {
-              uint32_t o[8];
 #pragma unroll
               for (int i = 0; i < 8; ++i)
                 o[i] = pack_bf16x2(fw_activate<HACT, false>(__uint_as_float(r[2 * i]) + b[2 * i]),
                                    fw_activate<HACT, false>(__uint_as_float(r[2 * i + 1]) + b[2 * i + 1]));
+            }
+            // early groups: chunk 1's MMAs must have read the group's blocks before they are overwritten
+            if (t < n_early && t % PPG == 0) mbar_wait(bar(FB_A_FREE + t / PPG), two_n & 1, p.status, FWC_EPI);
+            if constexpr (TF32) {
+              uint8_t* dst = a_row + (size_t)(n0 >> 5) * kWideBlk + (size_t)((n0 & 31) >> 2) * 128;
+#pragma unroll
+              for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(dst + 128 * i) = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+            } else {
               uint8_t* dst = a_row + (size_t)(n0 >> 6) * kWideBlk + (size_t)((n0 & 63) >> 3) * 128;
               *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
               *reinterpret_cast<uint4*>(dst + 128) = make_uint4(o[4], o[5], o[6], o[7]);
             }
             if ((t + 1) % PPG == 0) arrive_group(t / PPG, true);   // this warp's share of the group is written
           };
-          auto step = [&](int t, const uint32_t (&r)[16], uint32_t (&r_next)[16]) {
-            float b[16];                                       // warp-uniform addresses, issued before the TMEM wait
-            const float4* src = reinterpret_cast<const float4*>(bias + col_of(t));
+          auto step = [&](int t, int t_end, const uint32_t (&r)[16], uint32_t (&r_next)[16]) {
+            float b[16];                                       // warp-uniform shared-memory addresses (broadcast reads)
+            const float4* src = reinterpret_cast<const float4*>(bias_s + col_of(t));
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-              const float4 v = __ldg(src + i);
+              const float4 v = src[i];
               b[4 * i] = v.x; b[4 * i + 1] = v.y; b[4 * i + 2] = v.z; b[4 * i + 3] = v.w;
             }
             tmem_wait_ld();
-            if (t + 1 < n_t) tmem_ld16(d_addr + col_of(t + 1), r_next);
+            if (t + 1 < t_end) tmem_ld16(d_addr + col_of(t + 1), r_next);
             finish(t, r, b);
           };
-          if (n_t > 0) tmem_ld16(d_addr + col_of(0), ra);
-          for (int t = 0; t < n_t; t += 2) {
-            step(t, ra, rb);
-            if (t + 1 < n_t) step(t + 1, rb, ra);
+          auto run = [&](int t0, int t1) {                     // pieces [t0, t1), TMEM loads one piece ahead
+            if (t0 < t1) tmem_ld16(d_addr + col_of(t0), ra);
+            for (int t = t0; t < t1; t += 2) {
+              step(t, t1, ra, rb);
+              if (t + 1 < t1) step(t + 1, t1, rb, ra);
+            }
+          };
+          if (two) {
+            mbar_wait(bar(FB_ACC0_FULL), two_n & 1, p.status, FWC_EPI);
+            tc_fence_after();
+            run(0, n_early);
           }
+          mbar_wait(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
+          ++ld_n;
+          tc_fence_after();
+          run(n_early, n_t);
+          if (two) ++two_n;
           for (int g = n_t / PPG; g < n_grp; ++g) arrive_group(g, false);   // groups this warp has no columns in
         } else {
           // head: (acc + b) * s + shift into the tile-major fp32 scratch (bnn.py:878-893); the accumulator is released
           // (HEAD_DRAINED) as soon as the warp's columns are in registers, before the global stores
+          mbar_wait(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
+          ++ld_n;
+          tc_fence_after();
           const int nch = lp.npad >> 4;
           const int c_begin = 16 * ((part * nch) >> 2), c_end = 16 * (((part + 1) * nch) >> 2);
           const bool live_row = blk * kTileRows + row_in_tile < n_rows;
@@ -399,7 +449,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
 }
 
 size_t fused_wide_smem_bytes(const FusedWideParams& p) {
-  return (size_t)(p.a_blocks + p.a0_blocks + p.stages) * kWideBlk + kFwBars * 8u + 16u;
+  return (size_t)(p.a_blocks + p.a0_blocks + p.stages) * kWideBlk + kFwBarBytes + kFwBiasFloats * sizeof(float);
 }
 
 template <int HACT, bool TF32>
