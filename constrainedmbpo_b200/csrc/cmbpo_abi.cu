@@ -163,6 +163,10 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
     h->fw_a0_blocks = h->wl[0].k_chunks;
     h->fw_stages = kFusedWideBudgetBlocks - h->fw_a_blocks - h->fw_a0_blocks;
     if (h->fw_stages > kFusedWideMaxStages) h->fw_stages = kFusedWideMaxStages;
+    if (const char* fs = getenv("CMBPO_FW_STAGES")) {   // measurement hook: a shallower weight ring
+      const int v = atoi(fs);
+      if (v >= 2 && v < h->fw_stages) h->fw_stages = v;
+    }
     h->fused_wide = L >= 2 && h->fw_a_blocks >= 1 && h->fw_a_blocks <= kFusedWideMaxABlocks && h->fw_stages >= kFusedWideMinStages;
     if (const char* ff = getenv("CMBPO_WIDE_FUSED")) if (ff[0] == '0') h->fused_wide = false;
   }
@@ -401,6 +405,7 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
     fp.per_slot_input = p.per_slot_input;
     fp.n_rows_dev = n_rows_dev; fp.n_rows = n_rows;
     fp.status = h->status_dev;
+    fp.trace = p.trace;
     CU(launch_fused_wide(fp, h->hidden_act, h->num_sms, stream), "launch_fused_wide");
   } else {
     // wide path: per row slab, one launch per FC layer; activations ping-pong between two bf16 images

@@ -170,6 +170,7 @@ struct FusedWideParams {
   const int* n_rows_dev;
   long long n_rows;
   int* status;
+  long long* trace;              // debug timeline, only read by -DCMBPO_TRACE builds
 };
 
 // Slot maps of the 3-D ('iv_gae') path: host arrays by default, a device permutation when the caller drew it on the GPU

@@ -15,20 +15,28 @@
 //   * D: the layer's fp32 accumulator in TMEM, up to two 256-column N chunks (columns 0..511); the head uses chunk 0.
 //
 // Schedule of one (tile, member) instance, tcgen05 cta_group::2, M = 256 rows per CTA pair:
-//   MMAs of layer l (N chunk 0, then 1; K blocks in order) -> commit LAYER_DONE -> the 8 epilogue warps convert the
-//   accumulator 64 columns (one K block of the next layer) at a time: bias + activation + bf16 pack + 16-byte
-//   shared-memory stores, then fence.proxy.async and an arrival on A_RDY[block].  The issuer starts N chunk 0 of layer
-//   l + 1 as soon as the epilogue has left the chunk's accumulator columns (A_RDY of the chunk's last block) and then
-//   follows the epilogue block by block, so the second half of a conversion runs under the next layer's first chunk.
+//   MMAs of layer l (N chunk 0, then 1; K blocks in order) -> commit LAYER_DONE -> the 16 epilogue warps convert the
+//   accumulator in block groups of 128 columns (two K blocks of the next layer): bias + activation + bf16 pack + 16-byte
+//   shared-memory stores, then fence.proxy.async and an arrival on A_RDY[group].  The issuer starts N chunk 0 of layer
+//   l + 1 as soon as the conversion has left the chunk's accumulator columns and then follows it group by group.  In a
+//   two-chunk layer the conversion of chunk 0 does not wait for the layer: it starts on ACC0_FULL and overwrites block
+//   group g of the activation tile once chunk 1's MMAs have read it (A_FREE[g]), so half of every conversion runs under
+//   MMAs of the same layer and the other half under the first chunk of the next one.
 //   The accumulation order per output element (K blocks in order, 4 k-steps each) and the epilogue arithmetic are
 //   those of wide_fwd.cu: the two kernels agree bit for bit (tests/test_gpu_wide.py).
 //
 // Warp roles: 0 = weight loader (+ relay of the peer CTA's arrivals to the leader's barrier), 1 = MMA issuer (leader
-// CTA), 2 = TMEM alloc, 3 = input-tile loader, 4..11 = epilogue (TMEM lane quadrant = warp % 4, half of every block =
-// (warp - 4) / 4).  Work split: the flat list of (tile, member) instances, member fastest, is cut into one contiguous
-// range per CTA pair.
+// CTA), 2 = TMEM alloc, 3 = input-tile loader, 4..19 = epilogue (TMEM lane quadrant = warp % 4, column quarter of every
+// block group = (warp - 4) / 4).  Work split: the flat list of (tile, member) instances, member fastest, is cut into one
+// contiguous range per CTA pair.  Measurements and what bounds the kernel: profiles/r02_fused_wide_trace_notes.txt.
 #include "cmbpo_internal.cuh"
 #include "sm100_ptx.cuh"
+
+#ifdef FW_EXP_PLAINWAIT   // timing experiment: spin-waiting epilogue warps
+#define FW_EPI_WAIT mbar_wait
+#else
+#define FW_EPI_WAIT mbar_wait_parked
+#endif
 
 namespace cmbpo {
 using namespace sm100;
@@ -39,18 +47,33 @@ constexpr int kFwEpiWarps = 16;
 constexpr int FB_W_FULL = 0;         // [kFusedWideMaxStages]
 constexpr int FB_W_EMPTY = 8;        // [kFusedWideMaxStages]
 constexpr int FB_A_RDY = 16;         // [kFusedWideMaxABlocks / kFwGroup] blocks of group g of the activation tile written (and every accumulator column below their end read)
-constexpr int kFwGroup = 2;          // K blocks per A_RDY signal: one fence.proxy.async (300-400 cycles) per 128 bf16 columns and warp
+#ifndef FW_GROUP
+#define FW_GROUP 2
+#endif
+constexpr int kFwGroup = FW_GROUP;          // K blocks per A_RDY signal: one fence.proxy.async (300-400 cycles) per 128 bf16 columns and warp
 constexpr int FB_A0_FULL = 24;
 constexpr int FB_A0_EMPTY = 25;
 constexpr int FB_LAYER_DONE = 26;    // all MMAs of a layer complete (accumulator full, A tile no longer read)
 constexpr int FB_HEAD_DRAINED = 27;  // the head accumulator is in registers
 constexpr int FB_ACC0_FULL = 28;     // two-chunk layers: N chunk 0 complete (its conversion starts under the MMAs of chunk 1)
-constexpr int FB_A_FREE = 29;        // [2] two-chunk layers: chunk 1's MMAs have read block group g of the activation tile
-constexpr int kFwEarlyGroups = 2;    // block groups under N chunk 0 (256 bf16 columns)
+constexpr int FB_A_FREE = 29;        // [kFwEarlyGroups] two-chunk layers: chunk 1's MMAs have read block group g of the activation tile
+constexpr int kFwEarlyGroups = (kWideNC / kWideKC) / kFwGroup;    // block groups under N chunk 0 (256 bf16 columns)
+static_assert(kFwGroup == 2 || kFwGroup == 4, "block groups of 2 or 4 K blocks");
 constexpr int kFwBars = 31;
 static_assert(kFwBars * 8 + 16 <= 512, "barrier area");
 constexpr uint32_t kFwBarBytes = 512;   // barriers + TMEM slot, padded so the bias words behind them are 16-byte aligned
 constexpr int kFwBiasFloats = 512;   // widest hidden layer (8 blocks x 64 bf16 columns)
+
+// Debug timeline (-DCMBPO_TRACE, `make trace`): cluster 0's MMA issuer (role 0) and two epilogue warps of the leader CTA
+// (role 1: quadrant 0 part 0, role 2: quadrant 0 part 3) append (clock64, tag) pairs; tools/fw_trace_report.py prints them.
+constexpr int kFwTraceSlots = 2048;
+#ifdef CMBPO_TRACE
+#define FTR_DECL(role, cond) long long* tr_base = ((cond) && p.trace) ? p.trace + (role) * 2 * kFwTraceSlots : nullptr; int tr_n = 0
+#define FTR(tag) do { if (tr_base && tr_n < kFwTraceSlots) { tr_base[2 * tr_n] = clock64(); tr_base[2 * tr_n + 1] = (tag); ++tr_n; } } while (0)
+#else
+#define FTR_DECL(role, cond)
+#define FTR(tag)
+#endif
 
 enum FusedWideWaitCode : int { FWC_LOADER = 21, FWC_A0 = 22, FWC_MMA_W = 23, FWC_MMA_A = 24, FWC_MMA_A0 = 25, FWC_MMA_HEAD = 26, FWC_EPI = 27 };
 
@@ -70,6 +93,9 @@ __device__ __forceinline__ float fw_activate(float g) {
     else if constexpr (ACT == ACT_SIGMOID) return fw_sigmoid_precise(g);
     else return g;
   }
+#ifdef FW_EXP_NOTANH   // timing experiment: no MUFU work (results are wrong)
+  return fmaf(g, g, g);
+#endif
   if constexpr (ACT == ACT_SWISH) return fmaf(g, tanh_approx(g), g);
   else if constexpr (ACT == ACT_RELU) return fmaxf(g, 0.f);
   else if constexpr (ACT == ACT_TANH) return tanh_approx(g);
@@ -213,19 +239,31 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (leader CTA): the whole warp walks the loop, one elected lane issues
+    // ===== MMA issuer (leader CTA): the whole warp walks the loop, one lane issues.  A lone warp runs its dependent
+    // instructions 4-6 cycles apart, so everything per K block that is not a wait, an MMA or a commit is kept out of the
+    // inner loop (the first version spent ~650 cycles per 512-cycle K block and bounded the kernel: trace in
+    // profiles/r02_fused_wide_trace_notes.txt): descriptors are running 32-bit words, the A_RDY waits sit at block-group
+    // boundaries and the rare commits behind the loops.
     if (cta == 0) {
-      int stage = 0; uint32_t use = 0;
-      uint32_t a_par = 0;          // bit j: parity of the completion of A_RDY[j] the next consuming layer waits for
+      FTR_DECL(0, cluster_id == 0 && lane == 0);
+      const bool leader = elect_one();
+      uint32_t stage = 0, use = 0;
+      uint32_t a_par = 0;          // bit g: parity of the completion of A_RDY[g] the next consuming layer waits for
       uint32_t a0_n = 0, n_inst = 0;
-      const uint32_t a_tile = smem_u32(smem), a0_tile = smem_u32(smem + off_a0), ring = smem_u32(smem + off_ring);
+      // operand descriptors as (lo, hi) words: the 14-bit address field of lo counts 16-byte units, so a K block is
+      // +kWideBlk/16 and a k-step +16; hi (SBO, version) never changes
+      const uint64_t d0 = make_smem_desc(0, 128, 1024);
+      const uint32_t desc_hi = (uint32_t)(d0 >> 32), desc_lo0 = (uint32_t)d0;
+      const uint32_t a_lo_tile = desc_lo0 | (smem_u32(smem) >> 4), a0_lo_tile = desc_lo0 | (smem_u32(smem + off_a0) >> 4);
+      const uint32_t b_lo_ring = desc_lo0 | (smem_u32(smem + off_ring) >> 4);
+      const uint32_t w_full0 = bar(FB_W_FULL), w_empty0 = bar(FB_W_EMPTY);
       for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next(), ++n_inst) {
         for (int l = 0; l < L; ++l) {
           const WideLayerPlan& lp = p.lp[l];
           const int KC = lp.k_chunks, NCH = lp.n_chunks;
+          const int n_kgrp = (KC + kFwGroup - 1) / kFwGroup;     // block groups of this layer's K axis
           uint32_t seen = 0;
-          auto wait_a = [&](int j) {     // K block j of the activation tile (signalled per group of kFwGroup blocks)
-            const int g = j / kFwGroup;
+          auto wait_group = [&](int g) {     // group g of the activation tile written by the previous layer's conversion
             if (!((seen >> g) & 1u)) {
               mbar_wait(bar(FB_A_RDY + g), (a_par >> g) & 1u, p.status, FWC_MMA_A);
               seen |= 1u << g;
@@ -235,6 +273,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
             const int chunk_n = min(kWideNC, lp.npad - c * kWideNC);
             const uint32_t idesc = make_idesc(256, chunk_n, TF32 ? kFmtTF32 : kFmtBF16);
             const uint32_t d_tmem = tmem_base + (uint32_t)(c * kWideNC);
+            FTR(10000 + l * 1000 + c * 100);
             if (l == 0) {
               if (c == 0) {
                 if (it.new_input()) { mbar_wait(bar(FB_A0_FULL), a0_n & 1, p.status, FWC_MMA_A0); ++a0_n; }
@@ -244,49 +283,49 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
               }
             } else {
               // accumulator columns [256 c, 256 c + chunk_n) must have been read by the conversion of layer l - 1, which
-              // walks the columns in order: wait for the block that ends at or beyond them
+              // walks the columns in order: wait for the group whose last block ends at or beyond them
               int drain = (c * kWideNC + chunk_n + lp.kc - 1) / lp.kc;
               if (drain > KC) drain = KC;
-              wait_a(drain - 1);
+              wait_group((drain - 1) / kFwGroup);
             }
-            for (int j = 0; j < KC; ++j) {
-              if (l > 0) wait_a(j);
-              mbar_wait(bar(FB_W_FULL + stage), use & 1, p.status, FWC_MMA_W);
-              tc_fence_after();
-              const uint32_t a_base = (l == 0 ? a0_tile : a_tile) + (uint32_t)j * kWideBlk;
-              const uint32_t b_base = ring + (uint32_t)stage * kWideBlk;
-              const bool layer_end = (c == NCH - 1 && j == KC - 1);
-              if (elect_one()) {
-#pragma unroll
-                for (int ks = 0; ks < kWideKC / 16; ++ks) {
-                  if constexpr (TF32)
-                    mma_tf32_ss<2>(d_tmem, make_smem_desc(a_base + ks * 256, 128, 1024),
-                                   make_smem_desc(b_base + ks * 256, 128, 1024), idesc, (j > 0 || ks > 0) ? 1u : 0u);
-                  else
-                    mma_bf16_ss<2>(d_tmem, make_smem_desc(a_base + ks * 256, 128, 1024),
-                                   make_smem_desc(b_base + ks * 256, 128, 1024), idesc, (j > 0 || ks > 0) ? 1u : 0u);
+            uint32_t a_lo = (l == 0) ? a0_lo_tile : a_lo_tile;
+            uint32_t acc = 0;
+            for (int g = 0; g < n_kgrp; ++g) {
+              if (l > 0) wait_group(g);
+              FTR(15000 + l * 1000 + c * 100 + g);
+              const int j_end = min((g + 1) * kFwGroup, KC);
+              for (int j = g * kFwGroup; j < j_end; ++j) {
+                mbar_wait(w_full0 + 8u * stage, use & 1, p.status, FWC_MMA_W);
+                tc_fence_after();
+                if (leader) {
+                  const uint32_t b_lo = b_lo_ring + stage * (kWideBlk >> 4);
+                  mma_ss_lohi<2, TF32>(d_tmem, a_lo, b_lo, desc_hi, idesc, acc);
+                  mma_ss_lohi<2, TF32>(d_tmem, a_lo + 16, b_lo + 16, desc_hi, idesc, 1u);
+                  mma_ss_lohi<2, TF32>(d_tmem, a_lo + 32, b_lo + 32, desc_hi, idesc, 1u);
+                  mma_ss_lohi<2, TF32>(d_tmem, a_lo + 48, b_lo + 48, desc_hi, idesc, 1u);
+                  mma_commit_2sm(w_empty0 + 8u * stage, 0x3);
                 }
-                mma_commit_2sm(bar(FB_W_EMPTY + stage), 0x3);
-                if (NCH == 2) {
-                  // chunk 0 is complete: its conversion starts now; it may overwrite block group g of the activation tile once
-                  // chunk 1 has read it (layer 0 reads the input tile instead: every group is free at once)
-                  if (c == 0 && j == KC - 1) mma_commit_2sm(bar(FB_ACC0_FULL), 0x3);
-                  if (c == 1) {
-#pragma unroll
-                    for (int g = 0; g < kFwEarlyGroups; ++g)
-                      if (j == min((g + 1) * kFwGroup - 1, KC - 1)) mma_commit_2sm(bar(FB_A_FREE + g), 0x3);
-                  }
-                }
-                if (layer_end) {
-                  mma_commit_2sm(bar(FB_LAYER_DONE), 0x3);
-                  if (l == 0 && it.last_use()) mma_commit_2sm(bar(FB_A0_EMPTY), 0x3);
-                }
+                acc = 1u;
+                a_lo += kWideBlk >> 4;
+                if (++stage == (uint32_t)S) { stage = 0; ++use; }
               }
-              __syncwarp();
-              if (++stage == S) { stage = 0; ++use; }
+              // two-chunk layers: chunk 1 has read block group g of the activation tile: the conversion of chunk 0 (running
+              // under these MMAs) may overwrite it
+              if (NCH == 2 && c == 1 && g < kFwEarlyGroups && leader) mma_commit_2sm(bar(FB_A_FREE + g), 0x3);
             }
+            FTR(20000 + l * 1000 + c * 100);
+            if (leader) {
+              if (NCH == 2 && c == 0) mma_commit_2sm(bar(FB_ACC0_FULL), 0x3);    // chunk 0 complete: its conversion starts now
+              if (NCH == 2 && c == 1)                                             // groups this layer's K axis does not reach
+                for (int g = n_kgrp; g < kFwEarlyGroups; ++g) mma_commit_2sm(bar(FB_A_FREE + g), 0x3);
+              if (c == NCH - 1) {
+                mma_commit_2sm(bar(FB_LAYER_DONE), 0x3);
+                if (l == 0 && it.last_use()) mma_commit_2sm(bar(FB_A0_EMPTY), 0x3);
+              }
+            }
+            __syncwarp();
           }
-          if (l > 0) a_par ^= (1u << ((KC + kFwGroup - 1) / kFwGroup)) - 1u;     // one completion of every group's A_RDY consumed
+          if (l > 0) a_par ^= (1u << n_kgrp) - 1u;     // one completion of every group's A_RDY consumed
         }
       }
     }
@@ -300,6 +339,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
     const uint32_t d_addr = tmem_base + lane_base;
     uint8_t* a_row = smem + row_off;
     uint32_t ld_n = 0, two_n = 0;     // completions of LAYER_DONE / of the two-chunk barriers consumed
+    FTR_DECL(part == 0 ? 1 : 2, cluster_id == 0 && cta == 0 && q == 0 && (part == 0 || part == 3) && lane == 0);
     for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next()) {
       const int e = it.e;
       const int member = fw_member_of(p, e);
@@ -339,7 +379,9 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
           const bool two = lp.n_chunks == 2;
           const int n_early = two ? min(n_t, kFwEarlyGroups * PPG) : 0;
           auto arrive_group = [&](int g, bool wrote) {
+#ifndef FW_EXP_NOFENCE   // timing experiment: without the proxy fence (racy)
             if (wrote) fence_proxy_async_smem();         // generic-proxy smem writes -> visible to tcgen05.mma
+#endif
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster_light(bar(FB_A_RDY + g), 0);
@@ -357,7 +399,10 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
                                    fw_activate<HACT, false>(__uint_as_float(r[2 * i + 1]) + b[2 * i + 1]));
             }
             // early groups: chunk 1's MMAs must have read the group's blocks before they are overwritten
-            if (t < n_early && t % PPG == 0) mbar_wait(bar(FB_A_FREE + t / PPG), two_n & 1, p.status, FWC_EPI);
+            if (t < n_early && t % PPG == 0) { FW_EPI_WAIT(bar(FB_A_FREE + t / PPG), two_n & 1, p.status, FWC_EPI); FTR(35000 + l * 10 + t / PPG); }
+#ifdef FW_EXP_NOSTS   // timing experiment: no activation stores (results are wrong)
+            if (n0 < 0)
+#endif
             if constexpr (TF32) {
               uint8_t* dst = a_row + (size_t)(n0 >> 5) * kWideBlk + (size_t)((n0 & 31) >> 2) * 128;
 #pragma unroll
@@ -367,7 +412,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
               *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
               *reinterpret_cast<uint4*>(dst + 128) = make_uint4(o[4], o[5], o[6], o[7]);
             }
-            if ((t + 1) % PPG == 0) arrive_group(t / PPG, true);   // this warp's share of the group is written
+            if ((t + 1) % PPG == 0) { arrive_group(t / PPG, true); FTR(36000 + l * 10 + t / PPG); }   // this warp's share of the group is written
           };
           auto step = [&](int t, int t_end, const uint32_t (&r)[16], uint32_t (&r_next)[16]) {
             float b[16];                                       // warp-uniform shared-memory addresses (broadcast reads)
@@ -382,29 +427,40 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
             finish(t, r, b);
           };
           auto run = [&](int t0, int t1) {                     // pieces [t0, t1), TMEM loads one piece ahead
+#ifdef FW_EXP_NOEPI   // timing experiment: arrivals only (results are wrong)
+            for (int t = t0; t < t1; ++t) if ((t + 1) % PPG == 0) arrive_group(t / PPG, false);
+            return;
+#endif
             if (t0 < t1) tmem_ld16(d_addr + col_of(t0), ra);
             for (int t = t0; t < t1; t += 2) {
               step(t, t1, ra, rb);
               if (t + 1 < t1) step(t + 1, t1, rb, ra);
             }
           };
+          FTR(30000 + l);
           if (two) {
-            mbar_wait(bar(FB_ACC0_FULL), two_n & 1, p.status, FWC_EPI);
+            FW_EPI_WAIT(bar(FB_ACC0_FULL), two_n & 1, p.status, FWC_EPI);
             tc_fence_after();
+            FTR(31000 + l);
             run(0, n_early);
+            FTR(32000 + l);
           }
-          mbar_wait(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
+          FW_EPI_WAIT(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
           ++ld_n;
           tc_fence_after();
+          FTR(33000 + l);
           run(n_early, n_t);
+          FTR(34000 + l);
           if (two) ++two_n;
           for (int g = n_t / PPG; g < n_grp; ++g) arrive_group(g, false);   // groups this warp has no columns in
         } else {
           // head: (acc + b) * s + shift into the tile-major fp32 scratch (bnn.py:878-893); the accumulator is released
           // (HEAD_DRAINED) as soon as the warp's columns are in registers, before the global stores
-          mbar_wait(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
+          FTR(30000 + l);
+          FW_EPI_WAIT(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
           ++ld_n;
           tc_fence_after();
+          FTR(33000 + l);
           const int nch = lp.npad >> 4;
           const int c_begin = 16 * ((part * nch) >> 2), c_end = 16 * (((part + 1) * nch) >> 2);
           const bool live_row = blk * kTileRows + row_in_tile < n_rows;
@@ -433,10 +489,11 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
             tmem_ld16(d_addr + c0, ra);
             if (two) tmem_ld16(d_addr + c0 + 16, rb);
             tmem_wait_ld();
-            if (c0 + 32 >= c_end) drained();
+            if (c0 + 32 >= c_end) { drained(); FTR(34000 + l); }
             store16(c0, ra);
             if (two) store16(c0 + 16, rb);
           }
+          FTR(37000 + l);
         }
       }
     }

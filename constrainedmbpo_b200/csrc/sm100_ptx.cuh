@@ -126,6 +126,27 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity,
   mbar_wait(bar, parity, status, code);
 }
 
+// Wait of a warp that has nothing else to do for a long time (an epilogue warp while a whole layer of MMAs runs): the
+// try_wait carries a suspend-time hint, so the hardware parks the warp until the phase completes (or the hint expires)
+// instead of returning to a spin loop that takes issue slots from the MMA issuer on the same SM sub-partition.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint32_t bar, uint32_t parity, uint32_t ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity), "r"(ns) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_parked(uint32_t bar, uint32_t parity, int* status, int code) {
+#pragma unroll 1
+  for (uint32_t it = 0; it < (SM100_WAIT_LIMIT >> 4); ++it) {
+    if (mbar_try_wait_hint(bar, parity, 100000u)) return;
+  }
+  if (status) { *reinterpret_cast<volatile int*>(status) = (code | 0x40000000); __threadfence_system(); }
+  __trap();
+}
+
 // Non-critical waits (producer roles that are a whole work unit ahead): poll with a sleep in between so
 // the polling thread does not take issue / XU slots from the epilogue warp on the same SM sub-partition.
 __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity, int* status, int code,
@@ -267,6 +288,24 @@ __device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, ui
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// Same instruction with the two shared-memory descriptors given as their low words plus the common high word (SBO, version):
+// an issue loop then advances 32-bit words instead of rebuilding 64-bit descriptors.
+template <int CG, bool TF32>
+__device__ __forceinline__ void mma_ss_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                            uint32_t accumulate) {
+  static_assert(CG == 2, "cta_group::2 only");
+  if constexpr (TF32)
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], da, db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+  else
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
 }
 
 // commit: the mbarrier gets one arrival when all previously issued tcgen05.mma of this
