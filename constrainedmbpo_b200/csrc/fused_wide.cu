@@ -32,6 +32,11 @@
 #include "cmbpo_internal.cuh"
 #include "sm100_ptx.cuh"
 
+#ifdef FW_EXP_TESTPOLL   // timing experiment: non-blocking probes (mbarrier.test_wait) in the loader / relay loops -- no difference measured
+#define FW_POLL mbar_test_wait
+#else
+#define FW_POLL mbar_try_wait
+#endif
 #ifdef FW_EXP_PLAINWAIT   // timing experiment: spin-waiting epilogue warps
 #define FW_EPI_WAIT mbar_wait
 #else
@@ -180,11 +185,14 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
       const uint8_t* b_src = nullptr; uint32_t b_bytes = 0;
       while (fill_n < n_fill || (cta == 1 && relay_n < n_fill)) {
         bool progress = false;
-        if (fill_n < n_fill && (f_use == 0 || mbar_try_wait(bar(FB_W_EMPTY + f_stage), (f_use - 1) & 1))) {
+        if (fill_n < n_fill && (f_use == 0 || FW_POLL(bar(FB_W_EMPTY + f_stage), (f_use - 1) & 1))) {
           const WideLayerPlan& lp = p.lp[l];
           if (j == 0) {
             const int chunk_n = min(kWideNC, lp.npad - c * kWideNC);
             b_bytes = (uint32_t)(chunk_n >> 1) * 128u;
+#ifdef FW_EXP_HALFW   // timing experiment: half of every weight block (results are wrong)
+            b_bytes >>= 1;
+#endif
             b_src = p.w_img + lp.w_off + ((((size_t)fw_member_of(p, it.e) * lp.n_chunks + c) * 2 + cta) * lp.k_chunks) * kWideBlk;
           }
           mbar_arrive_expect_tx(bar(FB_W_FULL + f_stage), b_bytes);
@@ -194,7 +202,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
           if (++f_stage == S) { f_stage = 0; ++f_use; }
           ++fill_n; progress = true;
         }
-        if (cta == 1 && relay_n < fill_n && mbar_try_wait(bar(FB_W_FULL + r_stage), r_use & 1)) {
+        if (cta == 1 && relay_n < fill_n && FW_POLL(bar(FB_W_FULL + r_stage), r_use & 1)) {
           mbar_arrive_cluster_light(bar(FB_W_FULL + r_stage), 0);   // async-proxy data consumed by the async proxy: light arrive
           if (++r_stage == S) { r_stage = 0; ++r_use; }
           ++relay_n; progress = true;
@@ -217,7 +225,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
       const uint32_t a0_bytes = (uint32_t)p.a0_blocks * kWideBlk;
       while (fill_n < n_fill || (cta == 1 && relay_n < n_fill)) {
         bool progress = false;
-        if (fill_n < n_fill && (fill_n == 0 || mbar_try_wait(bar(FB_A0_EMPTY), (uint32_t)(fill_n - 1) & 1))) {
+        if (fill_n < n_fill && (fill_n == 0 || FW_POLL(bar(FB_A0_EMPTY), (uint32_t)(fill_n - 1) & 1))) {
           while (!it.new_input()) it.next();
           const int in_slot = p.per_slot_input ? fw_input_of(p, it.e) : 0;
           const uint8_t* src = p.a0_img + (size_t)in_slot * p.a0_slot_stride + (size_t)(it.tile * 2 + cta) * a0_bytes;
@@ -226,7 +234,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
           it.next();
           ++fill_n; progress = true;
         }
-        if (cta == 1 && relay_n < fill_n && mbar_try_wait(bar(FB_A0_FULL), (uint32_t)relay_n & 1)) {
+        if (cta == 1 && relay_n < fill_n && FW_POLL(bar(FB_A0_FULL), (uint32_t)relay_n & 1)) {
           mbar_arrive_cluster_light(bar(FB_A0_FULL), 0);
           ++relay_n; progress = true;
         }

@@ -92,6 +92,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   return ok != 0;
 }
+// Non-blocking probe: mbarrier.try_wait may park the thread for a system-dependent time before it reports "not yet", which
+// a thread that polls SEVERAL barriers in turn (a loader that also relays the peer CTA's arrivals) cannot afford -- the
+// relay would sit behind every unsuccessful probe of the other barrier.
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
 // cluster-scope acquire variant (needed when the arrive came from the peer CTA)
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
   uint32_t ok;

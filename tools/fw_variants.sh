@@ -2,12 +2,12 @@
 # timing experiments on the fused wide kernel: builds of the same library with one switch each (results of the NO* builds are wrong)
 # usage (here, CPU): bash tools/fw_variants.sh build   |  (GPU box): bash tools/fw_variants.sh run
 SRC=constrainedmbpo_b200/csrc
-VARS="base:-DFW_GROUP=2 nosts:-DFW_EXP_NOSTS noepi:-DFW_EXP_NOEPI $FW_EXTRA_VARS"
+VARS="base:-DFW_GROUP=2 trypoll:-DFW_EXP_TRYPOLL $FW_EXTRA_VARS"
 if [ "$1" = build ]; then
   mkdir -p build/fwv
   for v in $VARS; do
     name=${v%%:*}; flag=${v#*:}
-    nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC $flag -c $SRC/fused_wide.cu -o build/fwv/fused_wide_$name.o &
+    nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC ${flag//,/ } -c $SRC/fused_wide.cu -o build/fwv/fused_wide_$name.o &
   done; wait
   for v in $VARS; do
     name=${v%%:*}
