@@ -58,7 +58,7 @@ struct Handle {
   int wide_max_kc = 0;         // widest hidden activation image, in 64-column chunks
   // fused wide path (fused_wide.cu): hidden layers up to 8 operand blocks wide run the whole stack in one launch
   bool fused_wide = false;
-  int fw_a_blocks = 0, fw_a0_blocks = 0, fw_stages = 0;
+  int fw_a_blocks = 0, fw_a0_blocks = 0, fw_stages = 0, fw_streams = 1;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
 };
 
@@ -161,7 +161,12 @@ extern "C" int cmbpo_create(const cmbpo_cfg* cfg, int device, void** handle) {
     // CMBPO_WIDE_FUSED=0 keeps the layer-at-a-time kernel (test hook: the two agree bit for bit)
     h->fw_a_blocks = h->wide_max_kc;
     h->fw_a0_blocks = h->wl[0].k_chunks;
-    h->fw_stages = kFusedWideBudgetBlocks - h->fw_a_blocks - h->fw_a0_blocks;
+    // two row tiles per instance when every layer is one N chunk (<= 256 columns) and both tiles' buffers fit
+    bool one_chunk = true;
+    for (int l = 0; l < L; ++l) if (h->wl[l].n_chunks != 1) one_chunk = false;
+    h->fw_streams = (one_chunk && 2 * (h->fw_a_blocks + h->fw_a0_blocks) + kFusedWideMinStages <= kFusedWideBudgetBlocks) ? 2 : 1;
+    if (const char* fs = getenv("CMBPO_FW_STREAMS")) if (fs[0] == '1') h->fw_streams = 1;   // measurement / test hook
+    h->fw_stages = kFusedWideBudgetBlocks - h->fw_streams * (h->fw_a_blocks + h->fw_a0_blocks);
     if (h->fw_stages > kFusedWideMaxStages) h->fw_stages = kFusedWideMaxStages;
     if (const char* fs = getenv("CMBPO_FW_STAGES")) {   // measurement hook: a shallower weight ring
       const int v = atoi(fs);
@@ -396,7 +401,7 @@ static int run_forward(Handle* h, const float* const* seg, const int32_t* seg_wi
     memset(&fp, 0, sizeof(fp));
     for (int l = 0; l < pl.L; ++l) fp.lp[l] = h->wl[l];
     fp.L = pl.L; fp.E = pl.E; fp.n_head = pl.n_head; fp.tf32 = h->tf32 ? 1 : 0;
-    fp.a_blocks = h->fw_a_blocks; fp.a0_blocks = h->fw_a0_blocks; fp.stages = h->fw_stages;
+    fp.a_blocks = h->fw_a_blocks; fp.a0_blocks = h->fw_a0_blocks; fp.stages = h->fw_stages; fp.streams = h->fw_streams;
     fp.w_img = h->wimg_wide; fp.bias = h->bias_wide;
     fp.a0_img = sp.a0img; fp.a0_slot_stride = sp.slot_stride_bytes;
     fp.heads = heads; fp.head_scale = p.head_scale; fp.head_shift = p.head_shift;

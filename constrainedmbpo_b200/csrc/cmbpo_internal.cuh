@@ -156,6 +156,7 @@ struct FusedWideParams {
   int a_blocks;                  // 16 KB blocks of the activation tile = max over hidden layers of npad / kc
   int a0_blocks;                 // 16 KB blocks of the staged input tile = layer 0's k_chunks
   int stages;                    // weight ring depth
+  int streams;                   // row tiles per instance: 2 when every layer is one N chunk and two activation tiles fit, else 1
   const uint8_t* w_img;          // wide weight image (all layers)
   const float* bias;             // wide bias table (all layers)
   const uint8_t* a0_img;         // K0's chunked image [input slot][128-row block][k chunk]

@@ -64,7 +64,8 @@ constexpr int FB_ACC0_FULL = 28;     // two-chunk layers: N chunk 0 complete (it
 constexpr int FB_A_FREE = 29;        // [kFwEarlyGroups] two-chunk layers: chunk 1's MMAs have read block group g of the activation tile
 constexpr int kFwEarlyGroups = (kWideNC / kWideKC) / kFwGroup;    // block groups under N chunk 0 (256 bf16 columns)
 static_assert(kFwGroup == 2 || kFwGroup == 4, "block groups of 2 or 4 K blocks");
-constexpr int kFwBars = 31;
+constexpr int FB_S1 = 31;            // second row-tile stream: A0_FULL, A0_EMPTY, LAYER_DONE, HEAD_DRAINED at FB_S1 + 0 .. 3; its A_RDY at FB_A_RDY + 4 + g
+constexpr int kFwBars = 35;
 static_assert(kFwBars * 8 + 16 <= 512, "barrier area");
 constexpr uint32_t kFwBarBytes = 512;   // barriers + TMEM slot, padded so the bias words behind them are 16-byte aligned
 constexpr int kFwBiasFloats = 512;   // widest hidden layer (8 blocks x 64 bf16 columns)
@@ -137,14 +138,28 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
   const long long n_rows = p.n_rows_dev ? (long long)(*p.n_rows_dev) : p.n_rows;
   const long long n_tiles = (n_rows + 2 * kTileRows - 1) / (2 * kTileRows);
   const int E = p.E, L = p.L, S = p.stages;
-  const long long total = n_tiles * E;
+  // Row-tile streams.  Nets whose layers are all ONE N chunk (<= 256 columns) leave half of TMEM and of the activation
+  // area free: they run TWO row tiles per instance (unit = tile pair, stream s = tile 2 unit + s), each with its own
+  // accumulator, activation tile, input tile and barriers, through the same weight ring -- the conversion of one stream's
+  // layer runs under the other stream's MMAs (a one-chunk layer has nothing of its own to hide it behind).
+  const int NS = p.streams;
+  const long long n_units = (NS == 2) ? (n_tiles + 1) >> 1 : n_tiles;
+  auto tile_of = [&](long long unit, int s) -> long long { return NS == 2 ? 2 * unit + s : unit; };
+  auto streams_of = [&](long long unit) -> int { return (NS == 2 && 2 * unit + 1 < n_tiles) ? 2 : 1; };   // the last pair may be a lone tile
+  const long long total = n_units * E;
   const long long i_begin = total * cluster_id / n_clusters, i_end = total * (cluster_id + 1) / n_clusters;
 
-  const uint32_t off_a0 = (uint32_t)p.a_blocks * kWideBlk;
-  const uint32_t off_ring = off_a0 + (uint32_t)p.a0_blocks * kWideBlk;
+  const uint32_t a_bytes = (uint32_t)p.a_blocks * kWideBlk, a0_bytes = (uint32_t)p.a0_blocks * kWideBlk;
+  const uint32_t off_a0 = (uint32_t)NS * a_bytes;
+  const uint32_t off_ring = off_a0 + (uint32_t)NS * a0_bytes;
   const uint32_t off_bar = off_ring + (uint32_t)S * kWideBlk;
   const uint32_t bar0 = smem_u32(smem + off_bar);
   auto bar = [bar0](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
+  auto bar_a_rdy = [&](int s, int g) -> uint32_t { return bar(FB_A_RDY + 4 * s + g); };
+  auto bar_a0_full = [&](int s) -> uint32_t { return bar(s ? FB_S1 + 0 : FB_A0_FULL); };
+  auto bar_a0_empty = [&](int s) -> uint32_t { return bar(s ? FB_S1 + 1 : FB_A0_EMPTY); };
+  auto bar_layer_done = [&](int s) -> uint32_t { return bar(s ? FB_S1 + 2 : FB_LAYER_DONE); };
+  auto bar_head_drained = [&](int s) -> uint32_t { return bar(s ? FB_S1 + 3 : FB_HEAD_DRAINED); };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + off_bar + kFwBars * 8u);
   float* bias_s = reinterpret_cast<float*>(smem + off_bar + kFwBarBytes);   // [kFwBiasFloats] bias of the pass being converted
 
@@ -154,10 +169,12 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
       mbar_init(bar(FB_W_EMPTY + s), 1);                  // tcgen05.commit
     }
     for (int j = 0; j < kFusedWideMaxABlocks; ++j) mbar_init(bar(FB_A_RDY + j), 2 * kFwEpiWarps);
-    mbar_init(bar(FB_A0_FULL), cta == 0 ? 2 : 1);
-    mbar_init(bar(FB_A0_EMPTY), 1);                       // tcgen05.commit
-    mbar_init(bar(FB_LAYER_DONE), 1);                     // tcgen05.commit
-    mbar_init(bar(FB_HEAD_DRAINED), 2 * kFwEpiWarps);
+    for (int st = 0; st < 2; ++st) {
+      mbar_init(bar_a0_full(st), cta == 0 ? 2 : 1);
+      mbar_init(bar_a0_empty(st), 1);                     // tcgen05.commit
+      mbar_init(bar_layer_done(st), 1);                   // tcgen05.commit
+      mbar_init(bar_head_drained(st), 2 * kFwEpiWarps);
+    }
     mbar_init(bar(FB_ACC0_FULL), 1);                      // tcgen05.commit
     for (int g = 0; g < kFwEarlyGroups; ++g) mbar_init(bar(FB_A_FREE + g), 1);   // tcgen05.commit
     fence_mbar_init();
@@ -177,11 +194,12 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
     if (lane == 0) {
       long long per_inst = 0;
       for (int l = 0; l < L; ++l) per_inst += (long long)p.lp[l].n_chunks * p.lp[l].k_chunks;
-      const long long n_fill = (i_end - i_begin) * per_inst;
+      long long n_fill = 0;            // every stream of an instance walks the layer's blocks on its own
+      for (FwInst ic(i_begin, i_end, E, p.per_slot_input); ic.valid(); ic.next()) n_fill += per_inst * streams_of(ic.tile);
       long long fill_n = 0, relay_n = 0;
       int f_stage = 0, r_stage = 0; uint32_t f_use = 0, r_use = 0, idle = 0;
       FwInst it(i_begin, i_end, E, p.per_slot_input);
-      int l = 0, c = 0, j = 0;
+      int l = 0, st = 0, c = 0, j = 0;
       const uint8_t* b_src = nullptr; uint32_t b_bytes = 0;
       while (fill_n < n_fill || (cta == 1 && relay_n < n_fill)) {
         bool progress = false;
@@ -198,7 +216,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
           mbar_arrive_expect_tx(bar(FB_W_FULL + f_stage), b_bytes);
           bulk_g2s(smem_u32(smem + off_ring + (uint32_t)f_stage * kWideBlk), b_src, b_bytes, bar(FB_W_FULL + f_stage));
           b_src += kWideBlk;
-          if (++j == lp.k_chunks) { j = 0; if (++c == lp.n_chunks) { c = 0; if (++l == L) { l = 0; it.next(); } } }
+          if (++j == lp.k_chunks) { j = 0; if (++c == lp.n_chunks) { c = 0; if (++st == streams_of(it.tile)) { st = 0; if (++l == L) { l = 0; it.next(); } } } }
           if (++f_stage == S) { f_stage = 0; ++f_use; }
           ++fill_n; progress = true;
         }
@@ -218,25 +236,29 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
   } else if (warp == 3) {
     // ===== input-tile loader: K0's staged layer-0 operand blocks of this CTA's 128 rows, one fill per input tile
     if (lane == 0) {
-      long long n_fill = 0;
-      for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next()) if (it.new_input()) ++n_fill;
-      long long fill_n = 0, relay_n = 0; uint32_t idle = 0;
-      FwInst it(i_begin, i_end, E, p.per_slot_input);
-      const uint32_t a0_bytes = (uint32_t)p.a0_blocks * kWideBlk;
-      while (fill_n < n_fill || (cta == 1 && relay_n < n_fill)) {
+      long long n_fill[2] = {0, 0}, fill_n[2] = {0, 0}, relay_n[2] = {0, 0};
+      for (FwInst ic(i_begin, i_end, E, p.per_slot_input); ic.valid(); ic.next())
+        if (ic.new_input()) { ++n_fill[0]; if (streams_of(ic.tile) == 2) ++n_fill[1]; }
+      uint32_t idle = 0;
+      FwInst it0(i_begin, i_end, E, p.per_slot_input), it1 = it0;       // next instance to stage, per stream
+      while (fill_n[0] < n_fill[0] || fill_n[1] < n_fill[1] || (cta == 1 && (relay_n[0] < n_fill[0] || relay_n[1] < n_fill[1]))) {
         bool progress = false;
-        if (fill_n < n_fill && (fill_n == 0 || FW_POLL(bar(FB_A0_EMPTY), (uint32_t)(fill_n - 1) & 1))) {
-          while (!it.new_input()) it.next();
-          const int in_slot = p.per_slot_input ? fw_input_of(p, it.e) : 0;
-          const uint8_t* src = p.a0_img + (size_t)in_slot * p.a0_slot_stride + (size_t)(it.tile * 2 + cta) * a0_bytes;
-          mbar_arrive_expect_tx(bar(FB_A0_FULL), a0_bytes);
-          bulk_g2s(smem_u32(smem + off_a0), src, a0_bytes, bar(FB_A0_FULL));
-          it.next();
-          ++fill_n; progress = true;
-        }
-        if (cta == 1 && relay_n < fill_n && FW_POLL(bar(FB_A0_FULL), (uint32_t)relay_n & 1)) {
-          mbar_arrive_cluster_light(bar(FB_A0_FULL), 0);
-          ++relay_n; progress = true;
+#pragma unroll
+        for (int st = 0; st < 2; ++st) {
+          FwInst& it = st ? it1 : it0;
+          if (fill_n[st] < n_fill[st] && (fill_n[st] == 0 || FW_POLL(bar_a0_empty(st), (uint32_t)(fill_n[st] - 1) & 1))) {
+            while (!(it.new_input() && st < streams_of(it.tile))) it.next();
+            const int in_slot = p.per_slot_input ? fw_input_of(p, it.e) : 0;
+            const uint8_t* src = p.a0_img + (size_t)in_slot * p.a0_slot_stride + (size_t)(tile_of(it.tile, st) * 2 + cta) * a0_bytes;
+            mbar_arrive_expect_tx(bar_a0_full(st), a0_bytes);
+            bulk_g2s(smem_u32(smem + off_a0 + st * a0_bytes), src, a0_bytes, bar_a0_full(st));
+            it.next();
+            ++fill_n[st]; progress = true;
+          }
+          if (cta == 1 && relay_n[st] < fill_n[st] && FW_POLL(bar_a0_full(st), (uint32_t)relay_n[st] & 1)) {
+            mbar_arrive_cluster_light(bar_a0_full(st), 0);
+            ++relay_n[st]; progress = true;
+          }
         }
         if (progress) { idle = 0; continue; }
         __nanosleep(64);
@@ -256,8 +278,8 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
       FTR_DECL(0, cluster_id == 0 && lane == 0);
       const bool leader = elect_one();
       uint32_t stage = 0, use = 0;
-      uint32_t a_par = 0;          // bit g: parity of the completion of A_RDY[g] the next consuming layer waits for
-      uint32_t a0_n = 0, n_inst = 0;
+      uint32_t a_par[2] = {0, 0};  // per stream, bit g: parity of the completion of A_RDY[g] the next consuming layer waits for
+      uint32_t a0_n[2] = {0, 0}, hd_n[2] = {0, 0};     // input tiles / heads of the stream so far
       // operand descriptors as (lo, hi) words: the 14-bit address field of lo counts 16-byte units, so a K block is
       // +kWideBlk/16 and a k-step +16; hi (SBO, version) never changes
       const uint64_t d0 = make_smem_desc(0, 128, 1024);
@@ -265,29 +287,33 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
       const uint32_t a_lo_tile = desc_lo0 | (smem_u32(smem) >> 4), a0_lo_tile = desc_lo0 | (smem_u32(smem + off_a0) >> 4);
       const uint32_t b_lo_ring = desc_lo0 | (smem_u32(smem + off_ring) >> 4);
       const uint32_t w_full0 = bar(FB_W_FULL), w_empty0 = bar(FB_W_EMPTY);
-      for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next(), ++n_inst) {
+      for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next()) {
+        const int ns_inst = streams_of(it.tile);
         for (int l = 0; l < L; ++l) {
           const WideLayerPlan& lp = p.lp[l];
           const int KC = lp.k_chunks, NCH = lp.n_chunks;
           const int n_kgrp = (KC + kFwGroup - 1) / kFwGroup;     // block groups of this layer's K axis
+#pragma unroll
+         for (int st = 0; st < 2; ++st) {                         // streams alternate layer by layer: X.l, Y.l, X.l+1, ...
+          if (st >= ns_inst) break;
           uint32_t seen = 0;
-          auto wait_group = [&](int g) {     // group g of the activation tile written by the previous layer's conversion
+          auto wait_group = [&](int g) {     // group g of the stream's activation tile written by the previous layer's conversion
             if (!((seen >> g) & 1u)) {
-              mbar_wait(bar(FB_A_RDY + g), (a_par >> g) & 1u, p.status, FWC_MMA_A);
+              mbar_wait(bar_a_rdy(st, g), (a_par[st] >> g) & 1u, p.status, FWC_MMA_A);
               seen |= 1u << g;
             }
           };
           for (int c = 0; c < NCH; ++c) {
             const int chunk_n = min(kWideNC, lp.npad - c * kWideNC);
             const uint32_t idesc = make_idesc(256, chunk_n, TF32 ? kFmtTF32 : kFmtBF16);
-            const uint32_t d_tmem = tmem_base + (uint32_t)(c * kWideNC);
-            FTR(10000 + l * 1000 + c * 100);
+            const uint32_t d_tmem = tmem_base + (uint32_t)((st + c) * kWideNC);     // (two streams: one chunk each)
+            FTR(10000 + l * 1000 + c * 100 + st * 10);
             if (l == 0) {
               if (c == 0) {
-                if (it.new_input()) { mbar_wait(bar(FB_A0_FULL), a0_n & 1, p.status, FWC_MMA_A0); ++a0_n; }
-                // the previous instance's head sits in accumulator columns 0..; everything above was drained by its last
+                if (it.new_input()) { mbar_wait(bar_a0_full(st), a0_n[st] & 1, p.status, FWC_MMA_A0); ++a0_n[st]; }
+                // the stream's previous head sits in its accumulator columns 0..; everything above was drained by its last
                 // hidden conversion, which completed before the head MMAs were issued
-                if (n_inst > 0) mbar_wait(bar(FB_HEAD_DRAINED), (n_inst - 1) & 1, p.status, FWC_MMA_HEAD);
+                if (hd_n[st] > 0) mbar_wait(bar_head_drained(st), (hd_n[st] - 1) & 1, p.status, FWC_MMA_HEAD);
               }
             } else {
               // accumulator columns [256 c, 256 c + chunk_n) must have been read by the conversion of layer l - 1, which
@@ -296,7 +322,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
               if (drain > KC) drain = KC;
               wait_group((drain - 1) / kFwGroup);
             }
-            uint32_t a_lo = (l == 0) ? a0_lo_tile : a_lo_tile;
+            uint32_t a_lo = (l == 0) ? a0_lo_tile + (uint32_t)st * (a0_bytes >> 4) : a_lo_tile + (uint32_t)st * (a_bytes >> 4);
             uint32_t acc = 0;
             for (int g = 0; g < n_kgrp; ++g) {
               if (l > 0) wait_group(g);
@@ -327,14 +353,17 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
               if (NCH == 2 && c == 1)                                             // groups this layer's K axis does not reach
                 for (int g = n_kgrp; g < kFwEarlyGroups; ++g) mma_commit_2sm(bar(FB_A_FREE + g), 0x3);
               if (c == NCH - 1) {
-                mma_commit_2sm(bar(FB_LAYER_DONE), 0x3);
-                if (l == 0 && it.last_use()) mma_commit_2sm(bar(FB_A0_EMPTY), 0x3);
+                mma_commit_2sm(bar_layer_done(st), 0x3);
+                if (l == 0 && it.last_use()) mma_commit_2sm(bar_a0_empty(st), 0x3);
               }
             }
             __syncwarp();
           }
-          if (l > 0) a_par ^= (1u << n_kgrp) - 1u;     // one completion of every group's A_RDY consumed
+          if (l > 0) a_par[st] ^= (1u << n_kgrp) - 1u;     // one completion of every group's A_RDY consumed
+         }
         }
+#pragma unroll
+        for (int st = 0; st < 2; ++st) if (st < ns_inst) ++hd_n[st];
       }
     }
   } else if (warp >= 4) {
@@ -344,14 +373,14 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const int row_in_tile = q * 32 + lane;
     const uint32_t row_off = (uint32_t)(row_in_tile >> 3) * 1024u + (uint32_t)(row_in_tile & 7) * 16u;
-    const uint32_t d_addr = tmem_base + lane_base;
-    uint8_t* a_row = smem + row_off;
-    uint32_t ld_n = 0, two_n = 0;     // completions of LAYER_DONE / of the two-chunk barriers consumed
+    const uint32_t d_addr0 = tmem_base + lane_base;
+    uint8_t* a_row0 = smem + row_off;
+    uint32_t ld_n[2] = {0, 0}, two_n = 0;     // completions of LAYER_DONE (per stream) / of the two-chunk barriers consumed
     FTR_DECL(part == 0 ? 1 : 2, cluster_id == 0 && cta == 0 && q == 0 && (part == 0 || part == 3) && lane == 0);
     for (FwInst it(i_begin, i_end, E, p.per_slot_input); it.valid(); it.next()) {
       const int e = it.e;
       const int member = fw_member_of(p, e);
-      const long long blk = it.tile * 2 + cta;           // 128-row block of the batch
+      const int ns_inst = streams_of(it.tile);
       for (int l = 0; l < L; ++l) {
         const WideLayerPlan& lp = p.lp[l];
         const float* bias = p.bias + lp.b_off + (size_t)member * lp.npad;
@@ -383,6 +412,11 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
             if (act) *reinterpret_cast<float4*>(bias_s + col) = v;
             __syncwarp();
           }
+#pragma unroll
+         for (int st = 0; st < 2; ++st) {                       // the streams' conversions alternate: X under Y's MMAs, Y under X's next layer
+          if (st >= ns_inst) break;
+          const uint32_t d_addr = d_addr0 + (uint32_t)(st * kWideNC);
+          uint8_t* a_row = a_row0 + (size_t)st * a_bytes;
           // two-chunk layers: the columns under N chunk 0 (groups 0 .. kFwEarlyGroups) are converted while chunk 1's MMAs run
           const bool two = lp.n_chunks == 2;
           const int n_early = two ? min(n_t, kFwEarlyGroups * PPG) : 0;
@@ -392,7 +426,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
 #endif
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster_light(bar(FB_A_RDY + g), 0);
+            if (lane == 0) mbar_arrive_cluster_light(bar_a_rdy(st, g), 0);
           };
           auto finish = [&](int t, const uint32_t (&r)[16], const float (&b)[16]) {
             const int n0 = col_of(t);
@@ -453,20 +487,26 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
             run(0, n_early);
             FTR(32000 + l);
           }
-          FW_EPI_WAIT(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
-          ++ld_n;
+          FW_EPI_WAIT(bar_layer_done(st), ld_n[st] & 1, p.status, FWC_EPI);
+          ++ld_n[st];
           tc_fence_after();
           FTR(33000 + l);
           run(n_early, n_t);
           FTR(34000 + l);
           if (two) ++two_n;
           for (int g = n_t / PPG; g < n_grp; ++g) arrive_group(g, false);   // groups this warp has no columns in
+         }
         } else {
           // head: (acc + b) * s + shift into the tile-major fp32 scratch (bnn.py:878-893); the accumulator is released
           // (HEAD_DRAINED) as soon as the warp's columns are in registers, before the global stores
+#pragma unroll
+         for (int st = 0; st < 2; ++st) {
+          if (st >= ns_inst) break;
+          const uint32_t d_addr = d_addr0 + (uint32_t)(st * kWideNC);
+          const long long blk = tile_of(it.tile, st) * 2 + cta;           // 128-row block of the batch
           FTR(30000 + l);
-          FW_EPI_WAIT(bar(FB_LAYER_DONE), ld_n & 1, p.status, FWC_EPI);
-          ++ld_n;
+          FW_EPI_WAIT(bar_layer_done(st), ld_n[st] & 1, p.status, FWC_EPI);
+          ++ld_n[st];
           tc_fence_after();
           FTR(33000 + l);
           const int nch = lp.npad >> 4;
@@ -476,7 +516,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
           auto drained = [&]() {
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster_light(bar(FB_HEAD_DRAINED), 0);
+            if (lane == 0) mbar_arrive_cluster_light(bar_head_drained(st), 0);
           };
           auto store16 = [&](int c0, const uint32_t (&r)[16]) {
             if (live_row) {
@@ -502,6 +542,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
             if (two) store16(c0 + 16, rb);
           }
           FTR(37000 + l);
+         }
         }
       }
     }
@@ -514,7 +555,7 @@ __global__ void __launch_bounds__(kFwThreads, 1) fused_wide_kernel(const __grid_
 }
 
 size_t fused_wide_smem_bytes(const FusedWideParams& p) {
-  return (size_t)(p.a_blocks + p.a0_blocks + p.stages) * kWideBlk + kFwBarBytes + kFwBiasFloats * sizeof(float);
+  return (size_t)(p.streams * (p.a_blocks + p.a0_blocks) + p.stages) * kWideBlk + kFwBarBytes + kFwBiasFloats * sizeof(float);
 }
 
 template <int HACT, bool TF32>
@@ -529,7 +570,7 @@ static cudaError_t launch_fused_wide_variant2(const FusedWideParams& p, int num_
   int clusters = num_sms / 2;
   if (!p.n_rows_dev) {
     const long long n_tiles = (p.n_rows + 2 * kTileRows - 1) / (2 * kTileRows);
-    const long long inst = n_tiles * p.E;
+    const long long inst = (p.streams == 2 ? (n_tiles + 1) / 2 : n_tiles) * p.E;
     if (inst < clusters) clusters = (int)(inst > 0 ? inst : 1);
   }
   cudaLaunchConfig_t cfg{};

@@ -198,15 +198,17 @@ def test_predict_wide_beyond_one_slab(hidden, B):
     assert rel.max() < (5e-2 if len(hidden) < 3 else VAR_RTOL_BF16), f"variance rel err max {rel.max():.3e}"
 
 
-def test_full_rollout_at_benchmark_size_matches_chunked_rollouts():
+@pytest.mark.parametrize("hidden,B,T,n_shards", [(HIDDEN, 100_000, 30, 10), ((512, 512), 30_000, 12, 3)])
+def test_full_rollout_at_benchmark_size_matches_chunked_rollouts(hidden, B, T, n_shards):
     """The captured-graph rollout bench.py times (configs[1]: 100 k start states, 'uncertainty', H = 30) against the
     same rollout run as 10 independent shards of 10 k rows with their global row ids: every pool array must be
-    bit-identical (row independence of the whole sampler step, shrinking live row counts included)."""
+    bit-identical (row independence of the whole sampler step, shrinking live row counts included).  Second case: the
+    shipped (512, 512) shape on the fused wide kernel (device-side live row counts, CTA pairs that run out of work)."""
     import torch
     import constrainedmbpo_b200 as cm
-    env, B, T = "antsafe", 100_000, 30
-    p = make_params(env, HIDDEN, parity_scalers=False, bias=False)
-    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True, seed=5)
+    env = "antsafe"
+    p = make_params(env, hidden, parity_scalers=False, bias=False)
+    fe = build_cuda_env(p, env, hidden, cares_about_cost=True, seed=5)
     obs, _ = make_inputs(env, B)
     obs[:, 0] = np.random.default_rng(3).uniform(0.3, 0.9, B)
     start = torch.from_numpy(obs).cuda()
@@ -222,9 +224,9 @@ def test_full_rollout_at_benchmark_size_matches_chunked_rollouts():
     n_alive, ptr, total, finished = ro.counters()
     assert finished == 1 and total > B
     full = {k: v.clone() for k, v in ro.pool.items()}
-    shard = B // 10
+    shard = B // n_shards
     tot = 0
-    for r in range(10):
+    for r in range(n_shards):
         fe._rng_offset = 100
         rs = cm.ModelRollout(fe, T, rollout_mode="uncertainty", dkl_lim=dkl_lim, row_offset=r * shard)
         rs.reset(start[r * shard:(r + 1) * shard].contiguous())

@@ -164,7 +164,9 @@ def _wide_model(p, hidden, fused, **kw):
 @pytest.mark.parametrize("env,hidden,B,dtype", [
     ("antsafe", (512, 512), 3000, "bf16"),                 # the shipped shape: two N chunks, 8 K blocks
     ("antsafe", (512, 512, 512, 512), 40_000, "bf16"),     # ~15 (tile, member) instances per CTA pair: ring / phase wrap
-    ("halfcheetah", (256, 256, 256, 256), 2500, "bf16"),   # one N chunk
+    ("halfcheetah", (256, 256, 256, 256), 2500, "bf16"),   # one N chunk: two row tiles per instance (two streams)
+    ("halfcheetah", (256, 256, 256, 256), 40_100, "bf16"), # two streams in steady state, odd tile count (a lone last tile)
+    ("antsafe", (256, 192), 1100, "bf16"),                 # two streams, 5 tiles: the last unit has no second tile
     ("antsafe", (512, 200, 384), 1500, "bf16"),            # widths change from layer to layer (chunk 1 of 128 columns)
     ("antsafe", (300, 260), 777, "bf16"),                  # ragged widths
     ("antsafe", (200, 200, 200, 200), 5000, "tf32"),       # tf32 operands: 32-column blocks, 3xTF32 layer 0 (4 input blocks)
