@@ -28,7 +28,8 @@
 // Warp roles: 0 = weight loader (+ relay of the peer CTA's arrivals to the leader's barrier), 1 = MMA issuer (leader
 // CTA), 2 = TMEM alloc, 3 = input-tile loader, 4..19 = epilogue (TMEM lane quadrant = warp % 4, column quarter of every
 // block group = (warp - 4) / 4).  Work split: the flat list of (tile, member) instances, member fastest, is cut into one
-// contiguous range per CTA pair.  Measurements and what bounds the kernel: profiles/r02_fused_wide_trace_notes.txt.
+// contiguous range per CTA pair.  Nets whose layers are all one N chunk run two row tiles per instance (see NS below).
+// Measurements and what bounds the kernel: profiles/r02_fused_wide_trace_notes.txt.
 #include "cmbpo_internal.cuh"
 #include "sm100_ptx.cuh"
 

@@ -2,7 +2,7 @@
 # timing experiments on the fused wide kernel: builds of the same library with one switch each (results of the NO* builds are wrong)
 # usage (here, CPU): bash tools/fw_variants.sh build   |  (GPU box): bash tools/fw_variants.sh run
 SRC=constrainedmbpo_b200/csrc
-VARS="base:-DFW_GROUP=2 trypoll:-DFW_EXP_TRYPOLL $FW_EXTRA_VARS"
+VARS="base:-DFW_GROUP=2 notanh:-DFW_EXP_NOTANH nofence:-DFW_EXP_NOFENCE nosts:-DFW_EXP_NOSTS noepi:-DFW_EXP_NOEPI group4:-DFW_GROUP=4 $FW_EXTRA_VARS"
 if [ "$1" = build ]; then
   mkdir -p build/fwv
   for v in $VARS; do
@@ -18,7 +18,7 @@ else
   for v in $VARS; do
     name=${v%%:*}
     echo "== $name"
-    CMBPO_LIB=build/fwv/lib_$name.so timeout 200 python tools/wide_bench.py --widths 512 --rows 1000000 --layers 4 --reps 3 2>&1 | tail -1
-    CMBPO_LIB=build/fwv/lib_$name.so timeout 200 python tools/wide_bench.py --widths 512 --rows 1000000 --layers 2 --reps 3 2>&1 | tail -1
+    CMBPO_LIB=build/fwv/lib_$name.so timeout 200 python tools/wide_bench.py --widths ${FW_W:-512} --rows 1000000 --layers 4 --reps 3 2>&1 | tail -1
+    CMBPO_LIB=build/fwv/lib_$name.so timeout 200 python tools/wide_bench.py --widths ${FW_W:-512} --rows 1000000 --layers 2 --reps 3 2>&1 | tail -1
   done | tee gpurun_out/fw_variants.log
 fi
