@@ -31,3 +31,6 @@ PY
 done
 timeout 900 python tools/tolerance_report.py > $O/${TAG}_tolerance_report.txt 2>&1; cat $O/${TAG}_tolerance_report.txt
 for B in 65536 262144 1000000 4000000; do timeout 300 python tools/fwd_bench.py $B 10 antsafe_step_1M 2>&1 | tail -1; done | tee $O/${TAG}_fwd_bench.log
+# width x batch sweep of BASELINE configs[4] (4 hidden layers; 200: ensemble_fwd_kernel, 256-512: fused_wide_kernel, 1024: wide_layer_kernel)
+timeout 900 python tools/wide_bench.py --widths 200,256,384,512,1024 --rows 65536,262144,1000000 --layers 4 --reps 3 2>&1 | grep hidden | tee $O/${TAG}_sweep.log
+timeout 300 python tools/wide_bench.py --widths 512 --rows 25000,100000,1000000 --layers 2 --reps 3 2>&1 | grep hidden | tee -a $O/${TAG}_sweep.log
