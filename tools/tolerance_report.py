@@ -72,7 +72,7 @@ for dt, rtol in (("bf16", 1e-2), ("tf32", 1e-3)):
         dims = [37] + list(hidden) + [60]
         F = 2 * 7 * sum(a * b for a, b in zip(dims[:-1], dims[1:]))
         tf = F * Bt / (fwd * 1e-3) / 1e12
-        kern = "ensemble_fwd (fused)" if (H <= 254 and dt == "bf16") else ("wide_layer tf32" if dt == "tf32" else "wide_layer")
+        kern = ("ensemble_fwd", "wide_layer", "fused_wide")[lib.cmbpo_forward_path(h)] + (" tf32" if dt == "tf32" else "")
         print(f"{dt:>5} {H:>6} {kern:>20} {err.mean():13.2e} {np.quantile(err, 0.999):14.2e} {err.max():12.2e} {inside:11.6f} "
               f"{dlv.max():14.2e} {fwd * 1e3:15.1f} {tf:8.1f} {tf / peaks[dt]:8.3f}", flush=True)
         del fe, xt
