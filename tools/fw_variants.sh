@@ -2,7 +2,7 @@
 # timing experiments on the fused wide kernel: builds of the same library with one switch each (results of the NO* builds are wrong)
 # usage (here, CPU): bash tools/fw_variants.sh build   |  (GPU box): bash tools/fw_variants.sh run
 SRC=constrainedmbpo_b200/csrc
-VARS="base:-DFW_GROUP=2 notanh:-DFW_EXP_NOTANH nofence:-DFW_EXP_NOFENCE nosts:-DFW_EXP_NOSTS noepi:-DFW_EXP_NOEPI group4:-DFW_GROUP=4 $FW_EXTRA_VARS"
+VARS="base:-DFW_GROUP=2 notanh:-DFW_EXP_NOTANH nofence:-DFW_EXP_NOFENCE nosts:-DFW_EXP_NOSTS noepi:-DFW_EXP_NOEPI halfw:-DFW_EXP_HALFW testpoll:-DFW_EXP_TESTPOLL plainwait:-DFW_EXP_PLAINWAIT group4:-DFW_GROUP=4 $FW_EXTRA_VARS"
 if [ "$1" = build ]; then
   mkdir -p build/fwv
   for v in $VARS; do
