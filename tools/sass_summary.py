@@ -5,7 +5,7 @@ import collections, re, subprocess, sys, os
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pat = re.compile(r"\b(UTC[A-Z]*MMA|UTCBAR|UTCCP|LDTM|STTM|UBLKCP|UTMALDG|UTMASTG|SYNCS|LDGSTS|HMMA|MUFU\.[A-Z0-9]+)")
 print("# " + __doc__.strip().replace("\n", "\n# "))
-for obj in ("ensemble_fwd", "wide_fwd", "step_post", "rollout_ops", "gae_ops", "archive_ops", "actor_ops"):
+for obj in ("ensemble_fwd", "fused_wide", "wide_fwd", "step_post", "rollout_ops", "gae_ops", "archive_ops", "actor_ops"):
     out = subprocess.run(["cuobjdump", "-sass", os.path.join(ROOT, "build", obj + ".o")], capture_output=True, text=True).stdout
     fn, counts = None, collections.defaultdict(collections.Counter)
     for line in out.splitlines():
