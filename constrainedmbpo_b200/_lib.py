@@ -215,3 +215,27 @@ def require_device(device_index: int = 0):
         raise CmbpoError("no sm_100 (B200) CUDA device visible: the rollout path is CUDA-only, "
                          "there is no CPU fallback")
     return lib
+
+
+# ---- NumPy boundary -----------------------------------------------------------------------------
+# The reference's callers (ModelSampler.sample, MBPO._rollout_model) hand NumPy arrays to FakeEnv.step / BNN.predict and
+# get NumPy arrays back, every sampler step.  `tensor.cpu().numpy()` lands in freshly allocated pageable memory: the driver
+# bounces the copy through its own pinned buffers and every first touch of the new pages faults (16.8 MB of predict outputs:
+# ~4 ms; 133 MB of step outputs at 1 M rows: tens of ms).  Results therefore go to pinned host blocks of torch's caching
+# host allocator (reused from call to call, handed back when the NumPy array dies): all copies are enqueued first, one
+# synchronisation follows.
+def to_host(tensors):
+    """Device tensors -> NumPy arrays backed by cached pinned host memory (None stays None)."""
+    import torch
+    hosts, dev = [], None
+    for t in tensors:
+        if t is None:
+            hosts.append(None)
+            continue
+        dev = t.device
+        h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        h.copy_(t, non_blocking=True)
+        hosts.append(h)
+    if dev is not None:
+        torch.cuda.current_stream(dev).synchronize()
+    return [None if h is None else h.numpy() for h in hosts]

@@ -425,31 +425,33 @@ class BNN:
         if x.dim() not in (2, 3) or (x.dim() == 3 and x.shape[0] != self.num_nets) \
                 or x.shape[-1] != self.layers[0].get_input_dim():
             raise ValueError("Invalid input dimension.")  # fc.py:110-111
-        out = lambda t: t.cpu().numpy() if is_np else t
+        def out(*ts):      # NumPy in -> NumPy out through pinned host blocks, one synchronisation for all results
+            r = _lib.to_host(ts) if is_np else list(ts)
+            return r[0] if len(r) == 1 else r
         prob = self.is_probabilistic
         if x.dim() == 2:
             if factored:
                 mean, var = self.predict_device([x], 2, 0, want_var=inc_var and prob)
                 if inc_var and prob:
-                    return [out(mean), out(var)]  # :713-717 (sess.run returns a list)
+                    return list(out(mean, var))  # :713-717 (sess.run returns a list)
                 if inc_var:
                     rep = mean.var(dim=0, unbiased=False)[None].repeat(mean.shape[0], 1, 1)  # :718-724
-                    return out(mean), out(rep)
+                    return tuple(out(mean, rep))
                 return out(mean)
             mean, var = self.predict_device([x], 2, 1, want_var=inc_var)
             if inc_var and prob:
-                return [out(mean), out(var)]  # :731-735
+                return list(out(mean, var))  # :731-735
             if inc_var:
-                return out(mean), out(var)  # :736-743
+                return tuple(out(mean, var))  # :736-743
             return out(mean)
         mean, var = self.predict_device([x], 3, 0, want_var=inc_var and prob)
         if inc_var and prob:
-            return [out(mean), out(var)]  # :750-754
+            return list(out(mean, var))  # :750-754
         if inc_var:  # :755-771: variance across members of the flattened 2-D pass
             flat = x.reshape(-1, x.shape[-1])
             m2d, _ = self.predict_device([flat], 2, 0, want_var=False)
             v3d = m2d.var(dim=0, unbiased=False).reshape(x.shape[0], x.shape[1], -1)
-            return out(mean), out(v3d)
+            return tuple(out(mean, v3d))
         return out(mean)
 
     def check_status(self):

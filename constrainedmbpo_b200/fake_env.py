@@ -210,17 +210,18 @@ class FakeEnv:
         if noise is not None and not torch.is_tensor(noise):
             noise = torch.as_tensor(np.asarray(noise, dtype=np.float32))
         o = self.step_device(obs_d, act_d, elite_idx=elite_idx, perm=perm, noise=noise)
-        conv = (lambda t: t.cpu().numpy()) if is_np else (lambda t: t)
-        sc = o["scalars"].cpu().numpy() if is_np else o["scalars"]
-        next_obs = conv(o["next_obs"])
-        rewards = conv(o["rew"])
-        terminals = conv(o["term"].bool())
-        costs = conv(o["cost"])
+        term_b = o["term"].bool()
+        if is_np:      # one batch of device -> pinned-host copies, one synchronisation (see _lib.to_host)
+            sc, next_obs, rewards, terminals, costs, dkl_path, ep_var = _lib.to_host(
+                [o["scalars"], o["next_obs"], o["rew"], term_b, o["cost"], o["dkl_path"], o["ep_var"]])
+        else:
+            sc, next_obs, rewards, terminals, costs = o["scalars"], o["next_obs"], o["rew"], term_b, o["cost"]
+            dkl_path, ep_var = o["dkl_path"], o["ep_var"]
         info = {
             'ensemble_dkl_mean': sc[0],
-            'ensemble_dkl_path': conv(o["dkl_path"]),
+            'ensemble_dkl_path': dkl_path,
             'ensemble_mean_var': sc[1],
-            'ensemble_ep_var': conv(o["ep_var"]),
+            'ensemble_ep_var': ep_var,
             'rew': rewards,
             'rew_mean': sc[2],
             'cost': costs,
