@@ -372,17 +372,19 @@ def test_step_logvar_soft_bounding_option():
     assert np.median(rel) < 2e-2
 
 
-def test_step_3d_device_drawn_permutation():
+@pytest.mark.parametrize("hidden", [HIDDEN, (256, 256), (512, 512)])
+def test_step_3d_device_drawn_permutation(hidden):
     """perm="device": np.random.permutation(E) of forward_shuffle (fake_env.py:314) drawn by cmbpo_draw_permutation --
     the kernel's Fisher-Yates over Philox words restated in tests/helpers.philox_permutation -- and consumed by the
-    forward kernels from device memory; the step then equals the one with the same permutation injected from the host."""
+    forward kernels from device memory; the step then equals the one with the same permutation injected from the host.
+    All three forward kernels' slot maps: ensemble_fwd_kernel, fused_wide_kernel with two row-tile streams and with one."""
     import torch
     from tests.helpers import philox_permutation
     env = "humanoidsafe"
-    p = make_params(env, HIDDEN)
+    p = make_params(env, hidden)
     E, B = 7, 700
     obs, act = make_inputs(env, B, E=E)
-    fe = build_cuda_env(p, env, HIDDEN, cares_about_cost=True, seed=11)
+    fe = build_cuda_env(p, env, hidden, cares_about_cost=True, seed=11)
     o_d, a_d = torch.from_numpy(obs).cuda(), torch.from_numpy(act).cuda()
     seen = set()
     for call in range(6):

@@ -187,15 +187,16 @@ def test_fused_wide_matches_layer_at_a_time_bit_for_bit(env, hidden, B, dtype):
 
 def test_fused_wide_3d_input_and_activations():
     """3-D inputs (every member its own rows, fc.py:107-108) and the non-swish activations through the fused kernel."""
-    for activation in ("ReLU", "tanh", "sigmoid", "swish"):
-        p = _generic(40, 3, (320, 288), 4, prob=True, activation=activation, seed=11)
+    for activation, hidden in (("ReLU", (320, 288)), ("tanh", (320, 288)), ("sigmoid", (320, 288)), ("swish", (320, 288)),
+                               ("swish", (256, 192)), ("tanh", (256, 256))):     # the last two: one N chunk, two row-tile streams
+        p = _generic(40, 3, hidden, 4, prob=True, activation=activation, seed=11)
         x = np.random.default_rng(12).standard_normal((4, 900, 40)).astype(np.float32)
-        mf, vf = _wide_model(p, (320, 288), True, loss="NLL", activation=activation).predict(x, factored=True)
-        ml, vl = _wide_model(p, (320, 288), False, loss="NLL", activation=activation).predict(x, factored=True)
+        mf, vf = _wide_model(p, hidden, True, loss="NLL", activation=activation).predict(x, factored=True)
+        ml, vl = _wide_model(p, hidden, False, loss="NLL", activation=activation).predict(x, factored=True)
         np.testing.assert_array_equal(mf, ml)
         np.testing.assert_array_equal(vf, vl)
         rm, rv = orc.predict(p, x.astype(np.float64), factored=True)
-        assert_means_close(mf, rm, out_scale(p), atol_scale=_atol((320, 288)))
+        assert_means_close(mf, rm, out_scale(p), atol_scale=_atol(hidden))
 
 
 def test_fused_wide_at_size_shipped_shape():
